@@ -1,0 +1,431 @@
+/*
+ * oracle/host_kernels.c -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+ *
+ * CPU restatement (plain C, gcc) of the reference's HostPlacement arithmetic
+ * kernels for the replicated-secret-sharing hot path.  Nothing under
+ * moose_b200/ may include, link or call this file: only tests/, the smoke
+ * check and bench.py's cpu_baseline / --impl reference legs use it, and only
+ * as the checker / reported CPU baseline.
+ *
+ * Each function cites the reference code it follows (paths relative to
+ * /root/reference/).  The reference is Rust and cannot be built in this
+ * image (no cargo/rustc), so this is a port ("kind": "port" in bench.py).
+ *
+ * Third-party arithmetic that is NOT under /root/reference:
+ *   aes-prng ~0.2 (moose/Cargo.toml:40, no lockfile): AesRng::from_seed /
+ *   next_u64 / get_bit.  Restated here as AES-128 in counter mode with the
+ *   seed as key and 128-bit little-endian counters 0,1,2,..., output bytes
+ *   consumed in order.  Pinned by the reference's own golden vectors
+ *   ring_sample (moose/src/host/mod.rs:1050-1079; 5 u64 + 5 u128 values) --
+ *   see tests/test_oracle_kat.py.  get_bit() is pinned only by 5 bits
+ *   (moose/src/host/mod.rs:941-951,1081-1085): "parity partially pinned";
+ *   two policies consistent with those 5 bits are implemented, see
+ *   orc_sample_bits().
+ *
+ * Layouts: Ring64 = uint64_t; Ring128 = unsigned __int128 (little endian,
+ * memory-identical to Rust u128 on x86-64 and to numpy uint64[...,2] =
+ * [lo, hi]).  Bit tensors = packed bytes, flat row-major bit index j lives in
+ * byte j/8, bit j%8 (BitVec<u8, Lsb0>, moose/src/host/bitarray.rs:10-13).
+ */
+#include <stdint.h>
+#include <stddef.h>
+#include <string.h>
+#include <stdlib.h>
+
+typedef unsigned __int128 u128;
+
+/* ------------------------------------------------------------------ */
+/* AES-128 (FIPS-197), portable byte-oriented + AES-NI when available  */
+/* ------------------------------------------------------------------ */
+
+static const uint8_t SBOX[256] = {
+  0x63,0x7c,0x77,0x7b,0xf2,0x6b,0x6f,0xc5,0x30,0x01,0x67,0x2b,0xfe,0xd7,0xab,0x76,
+  0xca,0x82,0xc9,0x7d,0xfa,0x59,0x47,0xf0,0xad,0xd4,0xa2,0xaf,0x9c,0xa4,0x72,0xc0,
+  0xb7,0xfd,0x93,0x26,0x36,0x3f,0xf7,0xcc,0x34,0xa5,0xe5,0xf1,0x71,0xd8,0x31,0x15,
+  0x04,0xc7,0x23,0xc3,0x18,0x96,0x05,0x9a,0x07,0x12,0x80,0xe2,0xeb,0x27,0xb2,0x75,
+  0x09,0x83,0x2c,0x1a,0x1b,0x6e,0x5a,0xa0,0x52,0x3b,0xd6,0xb3,0x29,0xe3,0x2f,0x84,
+  0x53,0xd1,0x00,0xed,0x20,0xfc,0xb1,0x5b,0x6a,0xcb,0xbe,0x39,0x4a,0x4c,0x58,0xcf,
+  0xd0,0xef,0xaa,0xfb,0x43,0x4d,0x33,0x85,0x45,0xf9,0x02,0x7f,0x50,0x3c,0x9f,0xa8,
+  0x51,0xa3,0x40,0x8f,0x92,0x9d,0x38,0xf5,0xbc,0xb6,0xda,0x21,0x10,0xff,0xf3,0xd2,
+  0xcd,0x0c,0x13,0xec,0x5f,0x97,0x44,0x17,0xc4,0xa7,0x7e,0x3d,0x64,0x5d,0x19,0x73,
+  0x60,0x81,0x4f,0xdc,0x22,0x2a,0x90,0x88,0x46,0xee,0xb8,0x14,0xde,0x5e,0x0b,0xdb,
+  0xe0,0x32,0x3a,0x0a,0x49,0x06,0x24,0x5c,0xc2,0xd3,0xac,0x62,0x91,0x95,0xe4,0x79,
+  0xe7,0xc8,0x37,0x6d,0x8d,0xd5,0x4e,0xa9,0x6c,0x56,0xf4,0xea,0x65,0x7a,0xae,0x08,
+  0xba,0x78,0x25,0x2e,0x1c,0xa6,0xb4,0xc6,0xe8,0xdd,0x74,0x1f,0x4b,0xbd,0x8b,0x8a,
+  0x70,0x3e,0xb5,0x66,0x48,0x03,0xf6,0x0e,0x61,0x35,0x57,0xb9,0x86,0xc1,0x1d,0x9e,
+  0xe1,0xf8,0x98,0x11,0x69,0xd9,0x8e,0x94,0x9b,0x1e,0x87,0xe9,0xce,0x55,0x28,0xdf,
+  0x8c,0xa1,0x89,0x0d,0xbf,0xe6,0x42,0x68,0x41,0x99,0x2d,0x0f,0xb0,0x54,0xbb,0x16};
+
+static void aes128_expand(const uint8_t key[16], uint8_t rk[176]) {
+  static const uint8_t rcon[10] = {1,2,4,8,16,32,64,128,0x1b,0x36};
+  memcpy(rk, key, 16);
+  for (int i = 4; i < 44; i++) {
+    uint8_t t[4];
+    memcpy(t, rk + 4 * (i - 1), 4);
+    if (i % 4 == 0) {
+      uint8_t u = t[0];
+      t[0] = SBOX[t[1]] ^ rcon[i / 4 - 1];
+      t[1] = SBOX[t[2]];
+      t[2] = SBOX[t[3]];
+      t[3] = SBOX[u];
+    }
+    for (int j = 0; j < 4; j++) rk[4 * i + j] = rk[4 * (i - 4) + j] ^ t[j];
+  }
+}
+
+static inline uint8_t xtime(uint8_t x) { return (uint8_t)((x << 1) ^ ((x >> 7) * 0x1b)); }
+
+static void aes128_encrypt_portable(const uint8_t rk[176], const uint8_t in[16], uint8_t out[16]) {
+  uint8_t s[16], t[16];
+  for (int i = 0; i < 16; i++) s[i] = in[i] ^ rk[i];
+  for (int r = 1; r <= 10; r++) {
+    /* SubBytes + ShiftRows: state is column-major, s[4*c + row] */
+    for (int c = 0; c < 4; c++)
+      for (int row = 0; row < 4; row++)
+        t[4 * c + row] = SBOX[s[4 * ((c + row) & 3) + row]];
+    if (r < 10) {
+      for (int c = 0; c < 4; c++) {
+        uint8_t a0 = t[4*c], a1 = t[4*c+1], a2 = t[4*c+2], a3 = t[4*c+3];
+        uint8_t x = a0 ^ a1 ^ a2 ^ a3;
+        s[4*c]   = a0 ^ x ^ xtime(a0 ^ a1);
+        s[4*c+1] = a1 ^ x ^ xtime(a1 ^ a2);
+        s[4*c+2] = a2 ^ x ^ xtime(a2 ^ a3);
+        s[4*c+3] = a3 ^ x ^ xtime(a3 ^ a0);
+      }
+    } else {
+      memcpy(s, t, 16);
+    }
+    for (int i = 0; i < 16; i++) s[i] ^= rk[16 * r + i];
+  }
+  memcpy(out, s, 16);
+}
+
+#if defined(__x86_64__)
+#include <immintrin.h>
+__attribute__((target("aes,sse2")))
+static void aes128_ctr_aesni(const uint8_t rk[176], uint64_t start_block, uint64_t nblocks, uint8_t *out) {
+  __m128i k[11];
+  for (int i = 0; i < 11; i++) k[i] = _mm_loadu_si128((const __m128i *)(rk + 16 * i));
+  uint64_t b = 0;
+  for (; b + 4 <= nblocks; b += 4) {
+    __m128i c0 = _mm_set_epi64x(0, (long long)(start_block + b));
+    __m128i c1 = _mm_set_epi64x(0, (long long)(start_block + b + 1));
+    __m128i c2 = _mm_set_epi64x(0, (long long)(start_block + b + 2));
+    __m128i c3 = _mm_set_epi64x(0, (long long)(start_block + b + 3));
+    c0 = _mm_xor_si128(c0, k[0]); c1 = _mm_xor_si128(c1, k[0]);
+    c2 = _mm_xor_si128(c2, k[0]); c3 = _mm_xor_si128(c3, k[0]);
+    for (int r = 1; r < 10; r++) {
+      c0 = _mm_aesenc_si128(c0, k[r]); c1 = _mm_aesenc_si128(c1, k[r]);
+      c2 = _mm_aesenc_si128(c2, k[r]); c3 = _mm_aesenc_si128(c3, k[r]);
+    }
+    c0 = _mm_aesenclast_si128(c0, k[10]); c1 = _mm_aesenclast_si128(c1, k[10]);
+    c2 = _mm_aesenclast_si128(c2, k[10]); c3 = _mm_aesenclast_si128(c3, k[10]);
+    _mm_storeu_si128((__m128i *)(out + 16 * b), c0);
+    _mm_storeu_si128((__m128i *)(out + 16 * (b + 1)), c1);
+    _mm_storeu_si128((__m128i *)(out + 16 * (b + 2)), c2);
+    _mm_storeu_si128((__m128i *)(out + 16 * (b + 3)), c3);
+  }
+  for (; b < nblocks; b++) {
+    __m128i c = _mm_set_epi64x(0, (long long)(start_block + b));
+    c = _mm_xor_si128(c, k[0]);
+    for (int r = 1; r < 10; r++) c = _mm_aesenc_si128(c, k[r]);
+    c = _mm_aesenclast_si128(c, k[10]);
+    _mm_storeu_si128((__m128i *)(out + 16 * b), c);
+  }
+}
+static int have_aesni(void) { return __builtin_cpu_supports("aes"); }
+#else
+static int have_aesni(void) { return 0; }
+#endif
+
+static int g_force_portable = 0;
+void orc_force_portable_aes(int on) { g_force_portable = on; }
+
+/* AES-CTR keystream of the aes-prng stream: block i = AES_seed(LE128(i)).
+ * Counters stay below 2^64 for any tensor that fits in memory. */
+void orc_aes_ctr(const uint8_t seed[16], uint64_t start_block, uint64_t nblocks, uint8_t *out) {
+  uint8_t rk[176];
+  aes128_expand(seed, rk);
+#if defined(__x86_64__)
+  if (!g_force_portable && have_aesni()) { aes128_ctr_aesni(rk, start_block, nblocks, out); return; }
+#endif
+  for (uint64_t b = 0; b < nblocks; b++) {
+    uint8_t ctr[16] = {0};
+    uint64_t v = start_block + b;
+    memcpy(ctr, &v, 8); /* little endian */
+    aes128_encrypt_portable(rk, ctr, out + 16 * b);
+  }
+}
+
+/* Single block encryption (FIPS-197 KATs in the tests). */
+void orc_aes_block(const uint8_t key[16], const uint8_t in[16], uint8_t out[16]) {
+  uint8_t rk[176];
+  aes128_expand(key, rk);
+  aes128_encrypt_portable(rk, in, out);
+}
+
+/* ------------------------------------------------------------------ */
+/* SampleSeededOp / SampleOp   (moose/src/host/ops.rs:1883-2036)       */
+/* ------------------------------------------------------------------ */
+
+/* ring64_kernel, max_value=None: element e = next_u64() = stream bytes
+ * [8e, 8e+8) little endian (host/ops.rs:1969). */
+void orc_sample_ring64(const uint8_t seed[16], uint64_t n, uint64_t *out) {
+  uint64_t nblocks = (n + 1) / 2;
+  uint8_t *buf = (uint8_t *)malloc(nblocks * 16 + 16);
+  orc_aes_ctr(seed, 0, nblocks, buf);
+  memcpy(out, buf, n * 8);
+  free(buf);
+}
+
+/* ring128_kernel, max_value=None: element = (next_u64() << 64) + next_u64()
+ * (host/ops.rs:1998-2000): FIRST u64 of the 16 stream bytes is the HIGH half. */
+void orc_sample_ring128(const uint8_t seed[16], uint64_t n, u128 *out) {
+  uint8_t *buf = (uint8_t *)malloc(n * 16 + 16);
+  orc_aes_ctr(seed, 0, n, buf);
+  for (uint64_t e = 0; e < n; e++) {
+    uint64_t a, b;
+    memcpy(&a, buf + 16 * e, 8);
+    memcpy(&b, buf + 16 * e + 8, 8);
+    out[e] = ((u128)a << 64) + (u128)b;
+  }
+  free(buf);
+}
+
+/* get_bit() stream (host/ops.rs:1973,2003,2032).  The aes-prng source is not
+ * in the reference tree; two policies reproduce the only golden vector
+ * ([0,1,1,0,0] for seed 0^16):
+ *   policy 0: successive bits of the keystream, LSB-first within each byte
+ *             (Lsb0, the BitVec convention moose uses) -- DEFAULT;
+ *   policy 1: one little-endian u16 per call, & 1.
+ * Writes one byte (0/1) per bit into `out`. */
+void orc_sample_bits_unpacked(const uint8_t seed[16], uint64_t nbits, int policy, uint8_t *out) {
+  if (policy == 0) {
+    uint64_t nblocks = (nbits + 127) / 128;
+    uint8_t *buf = (uint8_t *)malloc(nblocks * 16 + 16);
+    orc_aes_ctr(seed, 0, nblocks, buf);
+    for (uint64_t j = 0; j < nbits; j++) out[j] = (buf[j >> 3] >> (j & 7)) & 1;
+    free(buf);
+  } else {
+    uint64_t nblocks = (nbits * 2 + 15) / 16;
+    uint8_t *buf = (uint8_t *)malloc(nblocks * 16 + 16);
+    orc_aes_ctr(seed, 0, nblocks, buf);
+    for (uint64_t j = 0; j < nbits; j++) out[j] = buf[2 * j] & 1;
+    free(buf);
+  }
+}
+
+/* bit_kernel: HostBitTensor from get_bit() calls, packed Lsb0. */
+void orc_sample_bits(const uint8_t seed[16], uint64_t nbits, int policy, uint8_t *out_packed) {
+  uint8_t *tmp = (uint8_t *)malloc(nbits + 1);
+  orc_sample_bits_unpacked(seed, nbits, policy, tmp);
+  memset(out_packed, 0, (nbits + 7) / 8);
+  for (uint64_t j = 0; j < nbits; j++) out_packed[j >> 3] |= (uint8_t)(tmp[j] << (j & 7));
+  free(tmp);
+}
+
+/* ring kernels with max_value = Some(1): element = get_bit() as T. */
+void orc_sample_ring64_bits(const uint8_t seed[16], uint64_t n, int policy, uint64_t *out) {
+  uint8_t *tmp = (uint8_t *)malloc(n + 1);
+  orc_sample_bits_unpacked(seed, n, policy, tmp);
+  for (uint64_t j = 0; j < n; j++) out[j] = tmp[j];
+  free(tmp);
+}
+void orc_sample_ring128_bits(const uint8_t seed[16], uint64_t n, int policy, u128 *out) {
+  uint8_t *tmp = (uint8_t *)malloc(n + 1);
+  orc_sample_bits_unpacked(seed, n, policy, tmp);
+  for (uint64_t j = 0; j < n; j++) out[j] = tmp[j];
+  free(tmp);
+}
+
+/* ------------------------------------------------------------------ */
+/* Elementwise ring kernels (host/ops.rs:299-310,1709-1752,1853-1881)  */
+/* Operands are pre-broadcast to n contiguous elements by the caller.  */
+/* ------------------------------------------------------------------ */
+#define EW2(NAME, T, EXPR)                                                     \
+  void NAME(const T *x, const T *y, T *z, uint64_t n) {                        \
+    for (uint64_t i = 0; i < n; i++) { T a = x[i], b = y[i]; z[i] = (EXPR); }  \
+  }
+EW2(orc_add64, uint64_t, a + b)
+EW2(orc_sub64, uint64_t, a - b)
+EW2(orc_mul64, uint64_t, a * b)
+EW2(orc_add128, u128, a + b)
+EW2(orc_sub128, u128, a - b)
+EW2(orc_mul128, u128, a * b)
+EW2(orc_and64, uint64_t, a & b)
+EW2(orc_and128, u128, a & b)
+
+void orc_neg64(const uint64_t *x, uint64_t *z, uint64_t n) { for (uint64_t i = 0; i < n; i++) z[i] = (uint64_t)0 - x[i]; }
+void orc_neg128(const u128 *x, u128 *z, uint64_t n) { for (uint64_t i = 0; i < n; i++) z[i] = (u128)0 - x[i]; }
+
+/* Rust `Wrapping<T> << usize` masks the amount by (bits-1): shl(64) on u64 is
+ * the identity (host/ops.rs:1864,1879 inherit std's wrapping_shl). */
+void orc_shl64(const uint64_t *x, uint64_t *z, uint64_t n, uint64_t amount) { unsigned s = amount & 63; for (uint64_t i = 0; i < n; i++) z[i] = x[i] << s; }
+void orc_shr64(const uint64_t *x, uint64_t *z, uint64_t n, uint64_t amount) { unsigned s = amount & 63; for (uint64_t i = 0; i < n; i++) z[i] = x[i] >> s; }
+void orc_shl128(const u128 *x, u128 *z, uint64_t n, uint64_t amount) { unsigned s = amount & 127; for (uint64_t i = 0; i < n; i++) z[i] = x[i] << s; }
+void orc_shr128(const u128 *x, u128 *z, uint64_t n, uint64_t amount) { unsigned s = amount & 127; for (uint64_t i = 0; i < n; i++) z[i] = x[i] >> s; }
+
+/* ------------------------------------------------------------------ */
+/* Dot (host/ops.rs:1754-1851): ndarray generic dot on Wrapping<T>.    */
+/* [M,K] x [K,N] row-major; rank-1 operands are handled by the caller. */
+/* Integer arithmetic mod 2^k is order independent, so the loop order  */
+/* (i,k,j) and OpenMP row partitioning do not affect the result.       */
+/* nthreads = 1 mirrors the reference (single-threaded, no BLAS for    */
+/* integer types); >1 is the "all host cores" baseline arm.            */
+/* ------------------------------------------------------------------ */
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+void orc_dot64(const uint64_t *a, const uint64_t *b, uint64_t *c, uint64_t M, uint64_t K, uint64_t N, int nthreads) {
+  (void)nthreads;
+#pragma omp parallel for num_threads(nthreads > 0 ? nthreads : 1) schedule(static)
+  for (int64_t i = 0; i < (int64_t)M; i++) {
+    uint64_t *ci = c + i * N;
+    for (uint64_t j = 0; j < N; j++) ci[j] = 0;
+    for (uint64_t k = 0; k < K; k++) {
+      uint64_t aik = a[i * K + k];
+      const uint64_t *bk = b + k * N;
+      for (uint64_t j = 0; j < N; j++) ci[j] += aik * bk[j];
+    }
+  }
+}
+void orc_dot128(const u128 *a, const u128 *b, u128 *c, uint64_t M, uint64_t K, uint64_t N, int nthreads) {
+  (void)nthreads;
+#pragma omp parallel for num_threads(nthreads > 0 ? nthreads : 1) schedule(static)
+  for (int64_t i = 0; i < (int64_t)M; i++) {
+    u128 *ci = c + i * N;
+    for (uint64_t j = 0; j < N; j++) ci[j] = 0;
+    for (uint64_t k = 0; k < K; k++) {
+      u128 aik = a[i * K + k];
+      const u128 *bk = b + k * N;
+      for (uint64_t j = 0; j < N; j++) ci[j] += aik * bk[j];
+    }
+  }
+}
+
+int orc_max_threads(void) {
+#ifdef _OPENMP
+  return omp_get_max_threads();
+#else
+  return 1;
+#endif
+}
+
+/* Sum over axis for a [outer, len, inner] view (host/mod.rs:476-487). */
+void orc_sum_axis64(const uint64_t *x, uint64_t *z, uint64_t outer, uint64_t len, uint64_t inner) {
+  for (uint64_t o = 0; o < outer; o++)
+    for (uint64_t i = 0; i < inner; i++) {
+      uint64_t acc = 0;
+      for (uint64_t l = 0; l < len; l++) acc += x[(o * len + l) * inner + i];
+      z[o * inner + i] = acc;
+    }
+}
+void orc_sum_axis128(const u128 *x, u128 *z, uint64_t outer, uint64_t len, uint64_t inner) {
+  for (uint64_t o = 0; o < outer; o++)
+    for (uint64_t i = 0; i < inner; i++) {
+      u128 acc = 0;
+      for (uint64_t l = 0; l < len; l++) acc += x[(o * len + l) * inner + i];
+      z[o * inner + i] = acc;
+    }
+}
+
+/* ------------------------------------------------------------------ */
+/* Bit kernels on packed Lsb0 buffers                                  */
+/* ------------------------------------------------------------------ */
+static inline int getbit(const uint8_t *p, uint64_t j) { return (p[j >> 3] >> (j & 7)) & 1; }
+static inline void setbit(uint8_t *p, uint64_t j, int v) { if (v) p[j >> 3] |= (uint8_t)(1u << (j & 7)); }
+
+/* XorOp/AndOp/OrOp::host_kernel, NegOp::bit_kernel (host/ops.rs:1507-1565;
+ * bitarray.rs:191-236).  nbits for tail masking. */
+void orc_bit_xor(const uint8_t *x, const uint8_t *y, uint8_t *z, uint64_t nbits) { for (uint64_t i = 0; i < (nbits + 7) / 8; i++) z[i] = x[i] ^ y[i]; }
+void orc_bit_and(const uint8_t *x, const uint8_t *y, uint8_t *z, uint64_t nbits) { for (uint64_t i = 0; i < (nbits + 7) / 8; i++) z[i] = x[i] & y[i]; }
+void orc_bit_or(const uint8_t *x, const uint8_t *y, uint8_t *z, uint64_t nbits) { for (uint64_t i = 0; i < (nbits + 7) / 8; i++) z[i] = x[i] | y[i]; }
+void orc_bit_not(const uint8_t *x, uint8_t *z, uint64_t nbits) {
+  uint64_t nb = (nbits + 7) / 8;
+  for (uint64_t i = 0; i < nb; i++) z[i] = (uint8_t)~x[i];
+  if (nbits & 7) z[nb - 1] &= (uint8_t)((1u << (nbits & 7)) - 1);
+}
+
+/* BitDecomposeOp::host_bit64/128_kernel (host/ops.rs:896-936): output shape
+ * [k, n], plane i = (x >> i) & 1, flat bit index i*n + e. */
+void orc_bit_decompose64(const uint64_t *x, uint64_t n, uint8_t *out) {
+  memset(out, 0, (64 * n + 7) / 8);
+  for (uint64_t i = 0; i < 64; i++)
+    for (uint64_t e = 0; e < n; e++) setbit(out, i * n + e, (int)((x[e] >> i) & 1));
+}
+void orc_bit_decompose128(const u128 *x, uint64_t n, uint8_t *out) {
+  memset(out, 0, (128 * n + 7) / 8);
+  for (uint64_t i = 0; i < 128; i++)
+    for (uint64_t e = 0; e < n; e++) setbit(out, i * n + e, (int)((x[e] >> i) & 1));
+}
+/* BitExtractOp::kernel64/128 (host/ops.rs:1567-1595). */
+void orc_bit_extract64(const uint64_t *x, uint64_t n, uint64_t bit_idx, uint8_t *out) {
+  memset(out, 0, (n + 7) / 8);
+  for (uint64_t e = 0; e < n; e++) setbit(out, e, (int)((x[e] >> bit_idx) & 1));
+}
+void orc_bit_extract128(const u128 *x, uint64_t n, uint64_t bit_idx, uint8_t *out) {
+  memset(out, 0, (n + 7) / 8);
+  for (uint64_t e = 0; e < n; e++) setbit(out, e, (int)((x[e] >> bit_idx) & 1));
+}
+/* RingInjectOp::host_kernel (host/ops.rs:1597-1621): bit b -> b << bit_idx
+ * (Wrapping shl: amount masked). */
+void orc_ring_inject64(const uint8_t *bits, uint64_t n, uint64_t bit_idx, uint64_t *out) {
+  for (uint64_t e = 0; e < n; e++) out[e] = (uint64_t)getbit(bits, e) << (bit_idx & 63);
+}
+void orc_ring_inject128(const uint8_t *bits, uint64_t n, uint64_t bit_idx, u128 *out) {
+  for (uint64_t e = 0; e < n; e++) out[e] = (u128)getbit(bits, e) << (bit_idx & 127);
+}
+/* ShlDimOp::host_bit_kernel (host/ops.rs:835-853): x is [bit_length, height];
+ * out = zeros(height*amount) ++ x[0 .. height*(bit_length-amount)). */
+void orc_shl_dim(const uint8_t *x, uint64_t height, uint64_t bit_length, uint64_t amount, uint8_t *out) {
+  uint64_t total = height * bit_length;
+  memset(out, 0, (total + 7) / 8);
+  uint64_t off = height * amount;
+  for (uint64_t j = off; j < total; j++) setbit(out, j, getbit(x, j - off));
+}
+/* Copy a bit range [start, start+len) of x into out at bit 0 (index_axis /
+ * slicing of bit tensors, bitarray.rs:85-108). */
+void orc_bit_copy_range(const uint8_t *x, uint64_t start, uint64_t len, uint8_t *out) {
+  memset(out, 0, (len + 7) / 8);
+  for (uint64_t j = 0; j < len; j++) setbit(out, j, getbit(x, start + j));
+}
+void orc_bit_pack(const uint8_t *unpacked, uint64_t nbits, uint8_t *out) {
+  memset(out, 0, (nbits + 7) / 8);
+  for (uint64_t j = 0; j < nbits; j++) setbit(out, j, unpacked[j] & 1);
+}
+void orc_bit_unpack(const uint8_t *packed, uint64_t nbits, uint8_t *out) {
+  for (uint64_t j = 0; j < nbits; j++) out[j] = (uint8_t)getbit(packed, j);
+}
+
+/* ------------------------------------------------------------------ */
+/* Fixed-point edges (host/ops.rs:1362-1418)                           */
+/* ------------------------------------------------------------------ */
+/* Rust `f64 as i128` saturates and maps NaN to 0. */
+static u128 f64_to_i128_sat(double v) {
+  if (v != v) return 0;
+  const double lim = 170141183460469231731687303715884105728.0; /* 2^127 */
+  if (v >= lim) return (u128)(((u128)1 << 127) - 1);
+  if (v <= -lim) return (u128)1 << 127;
+  return (u128)(__int128)v;
+}
+static uint64_t f64_to_i64_sat(double v) {
+  if (v != v) return 0;
+  if (v >= 9223372036854775808.0) return (uint64_t)INT64_MAX;
+  if (v <= -9223372036854775808.0) return (uint64_t)INT64_MIN;
+  return (uint64_t)(int64_t)v;
+}
+/* float64_kernel: (x * scaling_factor as f64) as i128 as u128. */
+void orc_fixed_encode128(const double *x, uint64_t n, double scaling_factor, u128 *out) {
+  for (uint64_t i = 0; i < n; i++) out[i] = f64_to_i128_sat(x[i] * scaling_factor);
+}
+/* Ring64 flavour used by HostFixed64 (host/fixedpoint.rs:10-38 via f64). */
+void orc_fixed_encode64(const double *x, uint64_t n, double scaling_factor, uint64_t *out) {
+  for (uint64_t i = 0; i < n; i++) out[i] = f64_to_i64_sat(x[i] * scaling_factor);
+}
+/* decode: (x as i128) as f64 / scaling_factor. */
+void orc_fixed_decode128(const u128 *x, uint64_t n, double scaling_factor, double *out) {
+  for (uint64_t i = 0; i < n; i++) out[i] = (double)(__int128)x[i] / scaling_factor;
+}
+void orc_fixed_decode64(const uint64_t *x, uint64_t n, double scaling_factor, double *out) {
+  for (uint64_t i = 0; i < n; i++) out[i] = (double)(int64_t)x[i] / scaling_factor;
+}

@@ -1,0 +1,1000 @@
+"""oracle/moose_oracle.py -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+
+CPU restatement of the reference's replicated / additive / mirrored protocol
+layer, op for op, on top of the C restatement of the host kernels
+(oracle/host_kernels.c).  Only tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs may import this module; nothing under
+moose_b200/ does.
+
+Every routine cites the reference code it follows (paths relative to
+/root/reference/moose/src/).  The reference keeps six share tensors per
+replicated value, `shares = [[x00, x10], [x11, x21], [x22, x02]]`
+(replicated/mod.rs:75-77): party i holds (x_i, x_{i+1}).  This oracle keeps
+that layout verbatim so the op order -- and therefore the order in which
+entropy is consumed -- is the reference's.
+
+Determinism contract.  The reference draws PRF
+keys, unseeded Sample seeds and sync keys from OS entropy, so its shares are
+not reproducible.  Here all three come from one explicit `EntropySource`
+(AES-128-CTR keyed by a 16-byte test key, one 16-byte block per request),
+consumed in the reference's program order.  The CUDA library implements the
+same contract, which is what makes share-level bit-exact parity testable.
+
+Parity pinning: AES-CTR u64/u128 streams, DeriveSeed and SessionId hashing are
+pinned by the reference's golden vectors (tests/test_oracle_kat.py).  The
+get_bit() policy is pinned by 5 bits only -> "parity partially pinned" for raw
+bit-share streams; revealed values do not depend on it.
+"""
+from __future__ import annotations
+
+import ctypes
+import math
+import os
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+
+try:  # blake3 is an independent third-party implementation (python wheel)
+    import blake3 as _blake3
+except Exception:  # pragma: no cover
+    _blake3 = None
+
+from . import build as _build
+
+_lib = ctypes.CDLL(_build.build())
+
+_u8p = ctypes.POINTER(ctypes.c_uint8)
+_vp = ctypes.c_void_p
+_u64 = ctypes.c_uint64
+
+
+def _ptr(a: np.ndarray):
+    return a.ctypes.data_as(_vp)
+
+
+def _sig(name, *args):
+    f = getattr(_lib, name)
+    f.argtypes = list(args)
+    f.restype = None
+    return f
+
+
+_aes_ctr = _sig("orc_aes_ctr", _vp, _u64, _u64, _vp)
+_aes_block = _sig("orc_aes_block", _vp, _vp, _vp)
+_sample_ring64 = _sig("orc_sample_ring64", _vp, _u64, _vp)
+_sample_ring128 = _sig("orc_sample_ring128", _vp, _u64, _vp)
+_sample_bits = _sig("orc_sample_bits", _vp, _u64, ctypes.c_int, _vp)
+_sample_ring64_bits = _sig("orc_sample_ring64_bits", _vp, _u64, ctypes.c_int, _vp)
+_sample_ring128_bits = _sig("orc_sample_ring128_bits", _vp, _u64, ctypes.c_int, _vp)
+_force_portable = _sig("orc_force_portable_aes", ctypes.c_int)
+_lib.orc_max_threads.restype = ctypes.c_int
+for _w in ("64", "128"):
+    for _op in ("add", "sub", "mul", "and"):
+        _sig(f"orc_{_op}{_w}", _vp, _vp, _vp, _u64)
+    _sig(f"orc_neg{_w}", _vp, _vp, _u64)
+    _sig(f"orc_shl{_w}", _vp, _vp, _u64, _u64)
+    _sig(f"orc_shr{_w}", _vp, _vp, _u64, _u64)
+    _sig(f"orc_dot{_w}", _vp, _vp, _vp, _u64, _u64, _u64, ctypes.c_int)
+    _sig(f"orc_sum_axis{_w}", _vp, _vp, _u64, _u64, _u64)
+    _sig(f"orc_bit_decompose{_w}", _vp, _u64, _vp)
+    _sig(f"orc_bit_extract{_w}", _vp, _u64, _u64, _vp)
+    _sig(f"orc_ring_inject{_w}", _vp, _u64, _u64, _vp)
+    _sig(f"orc_fixed_encode{_w}", _vp, _u64, ctypes.c_double, _vp)
+    _sig(f"orc_fixed_decode{_w}", _vp, _u64, ctypes.c_double, _vp)
+for _op in ("xor", "and", "or"):
+    _sig(f"orc_bit_{_op}", _vp, _vp, _vp, _u64)
+_sig("orc_bit_not", _vp, _vp, _u64)
+_sig("orc_shl_dim", _vp, _u64, _u64, _u64, _vp)
+_sig("orc_bit_copy_range", _vp, _u64, _u64, _vp)
+_sig("orc_bit_pack", _vp, _u64, _vp)
+_sig("orc_bit_unpack", _vp, _u64, _vp)
+
+DOT_THREADS = 1  # reference host kernels are single threaded
+
+
+def max_threads() -> int:
+    return int(_lib.orc_max_threads())
+
+
+# ---------------------------------------------------------------------------
+# primitives: AES-CTR stream, BLAKE3 seed derivation, session id
+# ---------------------------------------------------------------------------
+
+def aes_ctr(seed: bytes, start_block: int, nblocks: int) -> bytes:
+    """aes-prng stream: block i = AES-128_seed(LE128(i))."""
+    out = np.empty(16 * nblocks, dtype=np.uint8)
+    s = np.frombuffer(bytes(seed), dtype=np.uint8).copy()
+    _aes_ctr(_ptr(s), start_block, nblocks, _ptr(out))
+    return out.tobytes()
+
+
+def aes_block(key: bytes, block: bytes) -> bytes:
+    out = np.empty(16, dtype=np.uint8)
+    k = np.frombuffer(bytes(key), dtype=np.uint8).copy()
+    b = np.frombuffer(bytes(block), dtype=np.uint8).copy()
+    _aes_block(_ptr(k), _ptr(b), _ptr(out))
+    return out.tobytes()
+
+
+def session_id_bytes(logical: str) -> bytes:
+    """SessionId::try_from(&str) (computation.rs:108-124): blake3(s).xof(16)."""
+    return _blake3.blake3(logical.encode()).digest(length=16)
+
+
+def sync_key_from(values: Sequence[int]) -> bytes:
+    """SyncKey::try_from(&[u8]) (host/prim.rs:98-111): zero padded to 16."""
+    b = bytes(values)
+    assert len(b) <= 16
+    return b + bytes(16 - len(b))
+
+
+def derive_seed(sid: bytes, sync_key: bytes, prf_key: bytes) -> bytes:
+    """DeriveSeedOp::kernel (host/prim.rs:123-149)."""
+    dk = _blake3.blake3(prf_key, derive_key_context="Derive Seed").digest()
+    h = _blake3.blake3(key=dk)
+    h.update(sid)
+    h.update(sync_key)
+    return h.digest(length=16)
+
+
+class EntropySource:
+    """Explicit stand-in for the reference's OS entropy (determinism contract).
+
+    Request i returns AES-128_key(LE128(i)).  Consumed by PrfKeyGen
+    (host/prim.rs:118), unseeded Sample (host/ops.rs:1890,1917,1951: the 16
+    bytes are that op's seed) and SyncKey::random() (host/prim.rs:73-79).
+    """
+
+    def __init__(self, key: bytes):
+        assert len(key) == 16
+        self.key = bytes(key)
+        self.counter = 0
+
+    def next16(self) -> bytes:
+        out = aes_ctr(self.key, self.counter, 1)
+        self.counter += 1
+        return out
+
+
+# ---------------------------------------------------------------------------
+# host tensors
+# ---------------------------------------------------------------------------
+
+class Ring:
+    """HostRingTensor<u64|u128> (host/mod.rs:388). 128-bit data is uint64[...,2] = [lo, hi]."""
+
+    def __init__(self, bits: int, data: np.ndarray):
+        assert bits in (64, 128)
+        self.bits = bits
+        shp = np.shape(data)
+        data = np.ascontiguousarray(data, dtype=np.uint64).reshape(shp)  # keep 0-d shapes
+        if bits == 128:
+            assert data.shape[-1] == 2
+        self.data = data
+
+    @property
+    def shape(self) -> Tuple[int, ...]:
+        return tuple(self.data.shape[:-1]) if self.bits == 128 else tuple(self.data.shape)
+
+    @property
+    def size(self) -> int:
+        return int(np.prod(self.shape, dtype=np.int64)) if len(self.shape) else 1
+
+    @staticmethod
+    def from_ints(bits: int, values, shape=None) -> "Ring":
+        arr = np.array(values, dtype=object)
+        if shape is None:
+            shape = arr.shape
+        flat = [int(v) % (1 << bits) for v in arr.reshape(-1)]
+        if bits == 64:
+            return Ring(64, np.array(flat, dtype=np.uint64).reshape(shape))
+        lo = np.array([v & ((1 << 64) - 1) for v in flat], dtype=np.uint64)
+        hi = np.array([v >> 64 for v in flat], dtype=np.uint64)
+        return Ring(128, np.stack([lo, hi], axis=-1).reshape(tuple(shape) + (2,)))
+
+    def to_ints(self) -> np.ndarray:
+        if self.bits == 64:
+            return np.array([int(v) for v in self.data.reshape(-1)], dtype=object).reshape(self.shape)
+        d = self.data.reshape(-1, 2)
+        return np.array([int(lo) | (int(hi) << 64) for lo, hi in d], dtype=object).reshape(self.shape)
+
+    def reshape(self, shape) -> "Ring":
+        shape = tuple(shape)
+        return Ring(self.bits, self.data.reshape(shape + ((2,) if self.bits == 128 else ())))
+
+    def __eq__(self, other):
+        return isinstance(other, Ring) and self.bits == other.bits and self.shape == other.shape \
+            and bool(np.array_equal(self.data, other.data))
+
+    def tobytes(self) -> bytes:
+        return self.data.tobytes()
+
+
+class Bits:
+    """HostBitTensor (host/mod.rs:205; bitarray.rs:10-13): packed Lsb0 bytes + shape."""
+
+    def __init__(self, shape: Sequence[int], packed: np.ndarray):
+        self.shape = tuple(int(s) for s in shape)
+        n = self.size
+        packed = np.ascontiguousarray(packed, dtype=np.uint8)
+        assert packed.size == (n + 7) // 8, (packed.size, n)
+        self.packed = packed
+
+    @property
+    def size(self) -> int:
+        return int(np.prod(self.shape, dtype=np.int64)) if len(self.shape) else 1
+
+    @staticmethod
+    def from_array(values) -> "Bits":
+        a = np.asarray(values, dtype=np.uint8)
+        flat = np.ascontiguousarray(a.reshape(-1) & 1)
+        out = np.zeros((flat.size + 7) // 8, dtype=np.uint8)
+        _lib.orc_bit_pack(_ptr(flat), flat.size, _ptr(out))
+        return Bits(a.shape, out)
+
+    def to_array(self) -> np.ndarray:
+        out = np.zeros(max(self.size, 1), dtype=np.uint8)
+        _lib.orc_bit_unpack(_ptr(self.packed), self.size, _ptr(out))
+        return out[: self.size].reshape(self.shape)
+
+    def __eq__(self, other):
+        return isinstance(other, Bits) and self.shape == other.shape \
+            and bool(np.array_equal(self.packed, other.packed))
+
+
+def _w(x: Ring) -> str:
+    return str(x.bits)
+
+
+def _bcast(x: Ring, y: Ring) -> Tuple[Ring, Ring, Tuple[int, ...]]:
+    """ndarray co-broadcasting in `x.0 + y.0` (host/mod.rs:813-829)."""
+    assert x.bits == y.bits
+    shape = np.broadcast_shapes(x.shape, y.shape)
+    if x.shape != shape:
+        x = broadcast(x, shape)
+    if y.shape != shape:
+        y = broadcast(y, shape)
+    return x, y, shape
+
+
+def broadcast(x: Ring, shape) -> Ring:
+    """BroadcastOp::host_ring_kernel (host/ops.rs:1668-1681)."""
+    shape = tuple(shape)
+    tail = (2,) if x.bits == 128 else ()
+    return Ring(x.bits, np.ascontiguousarray(np.broadcast_to(x.data, shape + tail)))
+
+
+def _ew2(op: str, x, y):
+    if isinstance(x, Bits):
+        # Z2: add = sub = xor, mul = and (kernels/boolean.rs:18-76)
+        bop = {"add": "xor", "sub": "xor", "mul": "and"}[op]
+        return bit_op(bop, x, y)
+    x, y, shape = _bcast(x, y)
+    out = np.empty_like(x.data)
+    getattr(_lib, f"orc_{op}{_w(x)}")(_ptr(x.data), _ptr(y.data), _ptr(out), x.size)
+    return Ring(x.bits, out)
+
+
+def add(x, y):
+    """AddOp::ring_kernel (host/ops.rs:1709-1722)."""
+    return _ew2("add", x, y)
+
+
+def sub(x, y):
+    """SubOp::ring_kernel (host/ops.rs:1724-1737)."""
+    return _ew2("sub", x, y)
+
+
+def mul(x, y):
+    """MulOp::ring_kernel (host/ops.rs:299-310)."""
+    return _ew2("mul", x, y)
+
+
+def neg(x):
+    """NegOp::ring_kernel (host/ops.rs:1739-1752) / NegOp::bit_kernel (:1555-1565)."""
+    if isinstance(x, Bits):
+        out = np.empty_like(x.packed)
+        _lib.orc_bit_not(_ptr(x.packed), _ptr(out), x.size)
+        return Bits(x.shape, out)
+    out = np.empty_like(x.data)
+    getattr(_lib, f"orc_neg{_w(x)}")(_ptr(x.data), _ptr(out), x.size)
+    return Ring(x.bits, out)
+
+
+def shl(amount: int, x: Ring) -> Ring:
+    """ShlOp::ring_kernel (host/ops.rs:1853-1866); amount masked mod k (Wrapping)."""
+    out = np.empty_like(x.data)
+    getattr(_lib, f"orc_shl{_w(x)}")(_ptr(x.data), _ptr(out), x.size, amount)
+    return Ring(x.bits, out)
+
+
+def shr(amount: int, x: Ring) -> Ring:
+    """ShrOp::ring_kernel (host/ops.rs:1868-1881)."""
+    out = np.empty_like(x.data)
+    getattr(_lib, f"orc_shr{_w(x)}")(_ptr(x.data), _ptr(out), x.size, amount)
+    return Ring(x.bits, out)
+
+
+def dot(x: Ring, y: Ring) -> Ring:
+    """HostRingTensor::dot / DotOp::ring_kernel (host/ops.rs:1754-1851)."""
+    assert x.bits == y.bits
+    rx, ry = len(x.shape), len(y.shape)
+    if rx not in (1, 2) or ry not in (1, 2):
+        raise ValueError(f"Dot<HostRingTensor> cannot handle ranks {rx},{ry}")
+    M = x.shape[0] if rx == 2 else 1
+    K = x.shape[-1]
+    N = y.shape[1] if ry == 2 else 1
+    if y.shape[0] != K:
+        raise ValueError("dot: inner dimensions differ")
+    tail = (2,) if x.bits == 128 else ()
+    out = np.empty((M, N) + tail, dtype=np.uint64)
+    getattr(_lib, f"orc_dot{_w(x)}")(_ptr(x.data), _ptr(y.data), _ptr(out), M, K, N, DOT_THREADS)
+    if rx == 2 and ry == 2:
+        oshape = (M, N)
+    elif rx == 2:
+        oshape = (M,)
+    elif ry == 2:
+        oshape = (N,)
+    else:
+        oshape = ()
+    return Ring(x.bits, out.reshape(oshape + tail))
+
+
+def add_n(xs: Sequence[Ring]) -> Ring:
+    """AddNOp::host_kernel (host/ops.rs:1084-1103)."""
+    acc = xs[0]
+    for v in xs[1:]:
+        acc = add(acc, v)
+    return acc
+
+
+def sum_axis(x: Ring, axis: Optional[int]) -> Ring:
+    """SumOp::host_ring_kernel / HostRingTensor::sum (host/ops.rs:1067-1081; host/mod.rs:476-487)."""
+    shape = x.shape
+    tail = (2,) if x.bits == 128 else ()
+    if axis is None:
+        outer, ln, inner, oshape = 1, x.size, 1, ()
+    else:
+        outer = int(np.prod(shape[:axis], dtype=np.int64))
+        ln = shape[axis]
+        inner = int(np.prod(shape[axis + 1:], dtype=np.int64))
+        oshape = shape[:axis] + shape[axis + 1:]
+    out = np.empty((max(outer * inner, 1),) + tail, dtype=np.uint64)
+    getattr(_lib, f"orc_sum_axis{_w(x)}")(_ptr(x.data), _ptr(out), outer, ln, inner)
+    return Ring(x.bits, out.reshape(tuple(oshape) + tail))
+
+
+def fill(bits: int, value: int, shape) -> Ring:
+    """FillOp::host_ring64/128_kernel (host/ops.rs:1635-1655)."""
+    shape = tuple(shape)
+    n = int(np.prod(shape, dtype=np.int64)) if len(shape) else 1
+    return Ring.from_ints(bits, [value] * n, shape)
+
+
+def fill_bits(value: int, shape) -> Bits:
+    """FillOp::host_bit_kernel (host/ops.rs:1623-1633)."""
+    shape = tuple(shape)
+    n = int(np.prod(shape, dtype=np.int64)) if len(shape) else 1
+    return Bits.from_array(np.full(shape, value & 1, dtype=np.uint8)) if n else Bits(shape, np.zeros(0, np.uint8))
+
+
+def zeros_like(x):
+    return fill_bits(0, x.shape) if isinstance(x, Bits) else fill(x.bits, 0, x.shape)
+
+
+def bit_op(op: str, x: Bits, y: Bits) -> Bits:
+    """XorOp/AndOp/OrOp::host_kernel (host/ops.rs:1507-1553)."""
+    assert x.shape == y.shape, (x.shape, y.shape)
+    out = np.empty_like(x.packed)
+    getattr(_lib, f"orc_bit_{op}")(_ptr(x.packed), _ptr(y.packed), _ptr(out), x.size)
+    return Bits(x.shape, out)
+
+
+def ring_and(x: Ring, y: Ring) -> Ring:
+    """AndOp on ring tensors (kernels/boolean.rs): bitwise and."""
+    x, y, _ = _bcast(x, y)
+    out = np.empty_like(x.data)
+    getattr(_lib, f"orc_and{_w(x)}")(_ptr(x.data), _ptr(y.data), _ptr(out), x.size)
+    return Ring(x.bits, out)
+
+
+def bit_decompose(x: Ring) -> Bits:
+    """BitDecomposeOp::host_bit64/128_kernel (host/ops.rs:896-936): [k, shape...]."""
+    n = x.size
+    out = np.zeros((x.bits * n + 7) // 8, dtype=np.uint8)
+    getattr(_lib, f"orc_bit_decompose{_w(x)}")(_ptr(x.data), n, _ptr(out))
+    return Bits((x.bits,) + x.shape, out)
+
+
+def bit_extract(bit_idx: int, x: Ring) -> Bits:
+    """BitExtractOp::kernel64/128 (host/ops.rs:1567-1595)."""
+    n = x.size
+    out = np.zeros((n + 7) // 8, dtype=np.uint8)
+    getattr(_lib, f"orc_bit_extract{_w(x)}")(_ptr(x.data), n, bit_idx, _ptr(out))
+    return Bits(x.shape, out)
+
+
+def ring_inject(bits: int, bit_idx: int, x: Bits) -> Ring:
+    """RingInjectOp::host_kernel (host/ops.rs:1597-1621)."""
+    n = x.size
+    tail = (2,) if bits == 128 else ()
+    out = np.empty((max(n, 1),) + tail, dtype=np.uint64)
+    getattr(_lib, f"orc_ring_inject{bits}")(_ptr(x.packed), n, bit_idx, _ptr(out))
+    return Ring(bits, out[:n].reshape(x.shape + tail))
+
+
+def shl_dim(amount: int, bit_length: int, x: Bits) -> Bits:
+    """ShlDimOp::host_bit_kernel (host/ops.rs:835-853)."""
+    height = x.size // x.shape[0] if x.shape[0] else 0
+    out = np.zeros_like(x.packed)
+    _lib.orc_shl_dim(_ptr(x.packed), height, bit_length, amount, _ptr(out))
+    return Bits(x.shape, out)
+
+
+def index_axis0(index: int, x):
+    """IndexAxisOp with axis 0 (host/ops.rs:740-783; bitarray.rs:85-108)."""
+    if isinstance(x, Bits):
+        height = x.size // x.shape[0]
+        out = np.zeros((height + 7) // 8, dtype=np.uint8)
+        _lib.orc_bit_copy_range(_ptr(x.packed), index * height, height, _ptr(out))
+        return Bits(x.shape[1:], out)
+    return Ring(x.bits, x.data[index].copy())
+
+
+def fixed_encode(bits: int, x: np.ndarray, frac: int) -> Ring:
+    """RingFixedpointEncodeOp (host/ops.rs:1377-1389; host/fixedpoint.rs:10-38)."""
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    tail = (2,) if bits == 128 else ()
+    out = np.empty(x.shape + tail, dtype=np.uint64)
+    getattr(_lib, f"orc_fixed_encode{bits}")(_ptr(x), x.size, float(2 ** frac), _ptr(out))
+    return Ring(bits, out)
+
+
+def fixed_decode(x: Ring, frac: int) -> np.ndarray:
+    """RingFixedpointDecodeOp (host/ops.rs:1403-1417)."""
+    out = np.empty(x.shape, dtype=np.float64)
+    getattr(_lib, f"orc_fixed_decode{_w(x)}")(_ptr(x.data), x.size, float(2 ** frac), _ptr(out))
+    return out
+
+
+# -- sampling ----------------------------------------------------------------
+
+BIT_POLICY_STREAM_LSB0 = 0
+BIT_POLICY_U16_PER_BIT = 1
+
+
+def sample_uniform_seeded(bits: int, shape, seed: bytes) -> Ring:
+    """SampleSeededOp::ring64/128_kernel, max_value=None (host/ops.rs:1959-2017)."""
+    shape = tuple(shape)
+    n = int(np.prod(shape, dtype=np.int64)) if len(shape) else 1
+    tail = (2,) if bits == 128 else ()
+    out = np.empty((max(n, 1),) + tail, dtype=np.uint64)
+    s = np.frombuffer(bytes(seed), dtype=np.uint8).copy()
+    (_sample_ring64 if bits == 64 else _sample_ring128)(_ptr(s), n, _ptr(out))
+    return Ring(bits, out[:n].reshape(shape + tail))
+
+
+def sample_bits_seeded_ring(bits: int, shape, seed: bytes, policy: int = 0) -> Ring:
+    """SampleSeededOp ring kernels with max_value=Some(1) (host/ops.rs:1971-1974,2001-2004)."""
+    shape = tuple(shape)
+    n = int(np.prod(shape, dtype=np.int64)) if len(shape) else 1
+    tail = (2,) if bits == 128 else ()
+    out = np.empty((max(n, 1),) + tail, dtype=np.uint64)
+    s = np.frombuffer(bytes(seed), dtype=np.uint8).copy()
+    (_sample_ring64_bits if bits == 64 else _sample_ring128_bits)(_ptr(s), n, policy, _ptr(out))
+    return Ring(bits, out[:n].reshape(shape + tail))
+
+
+def sample_uniform_seeded_bits(shape, seed: bytes, policy: int = 0) -> Bits:
+    """SampleSeededOp::bit_kernel (host/ops.rs:2019-2036)."""
+    shape = tuple(shape)
+    n = int(np.prod(shape, dtype=np.int64)) if len(shape) else 1
+    out = np.zeros((n + 7) // 8, dtype=np.uint8)
+    s = np.frombuffer(bytes(seed), dtype=np.uint8).copy()
+    _sample_bits(_ptr(s), n, policy, _ptr(out))
+    return Bits(shape, out)
+
+
+# ---------------------------------------------------------------------------
+# session
+# ---------------------------------------------------------------------------
+
+class Session:
+    """SyncSession stand-in (execution/synchronous.rs) with explicit entropy."""
+
+    def __init__(self, session_id: str = "b200-bench", entropy_key: bytes = bytes(range(16)),
+                 bit_policy: int = BIT_POLICY_STREAM_LSB0):
+        self.sid = session_id_bytes(session_id)
+        self.entropy = EntropySource(entropy_key)
+        self.bit_policy = bit_policy
+        self._setup = None
+
+    # host/prim.rs:113-121
+    def gen_key(self) -> bytes:
+        return self.entropy.next16()
+
+    # host/prim.rs:73-79
+    def sync_key_random(self) -> bytes:
+        return self.entropy.next16()
+
+    def derive_seed(self, sync_key: bytes, key: bytes) -> bytes:
+        return derive_seed(self.sid, sync_key, key)
+
+    # replicated/setup.rs:39-58 via execution/synchronous.rs:297-307 (lazy, cached)
+    def setup(self):
+        if self._setup is None:
+            k00 = self.gen_key()
+            k11 = self.gen_key()
+            k22 = self.gen_key()
+            k10, k21, k02 = k11, k22, k00
+            self._setup = [[k00, k10], [k11, k21], [k22, k02]]
+        return self._setup
+
+    def sample_like(self, x, seed: bytes):
+        """sample_uniform_seeded typed by the operand (ring or bit tensor)."""
+        if isinstance(x, Bits):
+            return sample_uniform_seeded_bits(x.shape, seed, self.bit_policy)
+        return sample_uniform_seeded(x.bits, x.shape, seed)
+
+    def sample_uniform(self, like):
+        """SampleOp (host/ops.rs:1883-1957): unseeded = seed drawn from entropy."""
+        return self.sample_like(like, self.entropy.next16())
+
+
+# ---------------------------------------------------------------------------
+# replicated protocols.  RepTensor.shares = [[x00,x10],[x11,x21],[x22,x02]]
+# ---------------------------------------------------------------------------
+
+class RepTensor:
+    def __init__(self, shares):
+        self.shares = shares
+
+    def distinct(self):
+        """(x0, x1, x2) -- also asserts the two copies of each share agree."""
+        (x00, x10), (x11, x21), (x22, x02) = self.shares
+        assert x00 == x02 and x10 == x11 and x21 == x22, "inconsistent replicated sharing"
+        return x00, x10, x21
+
+    @property
+    def shape(self):
+        return self.shares[0][0].shape
+
+
+class AdtTensor:
+    def __init__(self, shares):
+        self.shares = shares
+
+
+class MirTensor:
+    def __init__(self, values):
+        self.values = values
+
+
+def gen_seeds(sess: Session):
+    """SeedsGen::gen_seeds (replicated/zero_share.rs:129-156)."""
+    (k00, k10), (k11, k21), (k22, k02) = sess.setup()
+    sync_key0 = sess.sync_key_random()
+    sync_key1 = sess.sync_key_random()
+    sync_key2 = sess.sync_key_random()
+    s00 = sess.derive_seed(sync_key0, k00)
+    s10 = sess.derive_seed(sync_key1, k10)
+    s11 = sess.derive_seed(sync_key1, k11)
+    s21 = sess.derive_seed(sync_key2, k21)
+    s22 = sess.derive_seed(sync_key2, k22)
+    s02 = sess.derive_seed(sync_key0, k02)
+    return [[s00, s10], [s11, s21], [s22, s02]]
+
+
+def gen_zero_share(sess: Session, like):
+    """ZeroShareGen::gen_zero_share (replicated/zero_share.rs:82-108)."""
+    (s00, s10), (s11, s21), (s22, s02) = gen_seeds(sess)
+    r00 = sess.sample_like(like, s00)
+    r10 = sess.sample_like(like, s10)
+    alpha0 = sub(r00, r10)
+    r11 = sess.sample_like(like, s11)
+    r21 = sess.sample_like(like, s21)
+    alpha1 = sub(r11, r21)
+    r22 = sess.sample_like(like, s22)
+    r02 = sess.sample_like(like, s02)
+    alpha2 = sub(r22, r02)
+    return alpha0, alpha1, alpha2
+
+
+def rep_share(sess: Session, x, owner: int = 0) -> RepTensor:
+    """ShareOp::ring_kernel (replicated/convert.rs:49-160). owner in {0,1,2}, or 3 = outsider."""
+    (k00, k10), (k11, k21), (k22, k02) = sess.setup()
+    if owner == 0:
+        sync_key = sess.sync_key_random()
+        seed0 = sess.derive_seed(sync_key, k00)
+        x00 = sess.sample_like(x, seed0)
+        x10 = sub(x, x00)
+        seed2 = sess.derive_seed(sync_key, k02)
+        x22 = zeros_like(x)
+        x02 = sess.sample_like(x, seed2)
+        x11 = x10
+        x21 = zeros_like(x)
+    elif owner == 1:
+        sync_key = sess.sync_key_random()
+        seed1 = sess.derive_seed(sync_key, k11)
+        x11 = sess.sample_like(x, seed1)
+        x21 = sub(x, x11)
+        seed0 = sess.derive_seed(sync_key, k10)
+        x00 = zeros_like(x)
+        x10 = sess.sample_like(x, seed0)
+        x22 = x21
+        x02 = zeros_like(x)
+    elif owner == 2:
+        sync_key = sess.sync_key_random()
+        seed2 = sess.derive_seed(sync_key, k22)
+        x22 = sess.sample_like(x, seed2)
+        x02 = sub(x, x22)
+        seed1 = sess.derive_seed(sync_key, k21)
+        x11 = zeros_like(x)
+        x21 = sess.sample_like(x, seed1)
+        x00 = x02
+        x10 = zeros_like(x)
+    else:
+        sync_key0 = sess.sync_key_random()
+        sync_key1 = sess.sync_key_random()
+        seed00 = sess.derive_seed(sync_key0, k00)
+        seed02 = sess.derive_seed(sync_key0, k02)
+        seed11 = sess.derive_seed(sync_key1, k11)
+        seed10 = sess.derive_seed(sync_key1, k10)
+        x0 = sess.sample_like(x, seed00)
+        x1 = sess.sample_like(x, seed11)
+        x2 = sub(sub(x, x0), x1)
+        x00 = sess.sample_like(x, seed00)
+        x10 = sess.sample_like(x, seed10)
+        x11 = sess.sample_like(x, seed11)
+        x21 = x2
+        x22 = x2
+        x02 = sess.sample_like(x, seed02)
+    return RepTensor([[x00, x10], [x11, x21], [x22, x02]])
+
+
+def rep_reveal(x: RepTensor, receiver: int = 0):
+    """RevealOp::host_ring_kernel (replicated/convert.rs:280-313)."""
+    (x00, x10), (x11, x21), (x22, x02) = x.shares
+    if receiver == 1:
+        return add(add(x02, x11), x21)
+    if receiver == 2:
+        return add(add(x02, x10), x22)
+    return add(add(x00, x10), x21)
+
+
+def _sharewise2(f, x: RepTensor, y: RepTensor) -> RepTensor:
+    return RepTensor([[f(x.shares[i][j], y.shares[i][j]) for j in range(2)] for i in range(3)])
+
+
+def rep_add(x: RepTensor, y: RepTensor) -> RepTensor:
+    """AddOp::rep_rep_kernel (replicated/arith.rs:7-37); XorOp::rep_kernel for bits (:510-523)."""
+    return _sharewise2(add, x, y)
+
+
+def rep_sub(x: RepTensor, y: RepTensor) -> RepTensor:
+    """SubOp::rep_rep_kernel (replicated/arith.rs:197-228)."""
+    return _sharewise2(sub, x, y)
+
+
+def rep_neg(x: RepTensor) -> RepTensor:
+    """NegOp::rep_rep_kernel (replicated/arith.rs:560-583); bit flavour negates only x00 and x02 (:525-558)."""
+    (x00, x10), (x11, x21), (x22, x02) = x.shares
+    if isinstance(x00, Bits):
+        return RepTensor([[neg(x00), x10], [x11, x21], [x22, neg(x02)]])
+    return RepTensor([[neg(v) for v in row] for row in x.shares])
+
+
+def rep_shl(amount: int, x: RepTensor) -> RepTensor:
+    """ShlOp::rep_kernel (replicated/arith.rs:585-609)."""
+    return RepTensor([[shl(amount, v) for v in row] for row in x.shares])
+
+
+def rep_add_mir(x: RepTensor, y: MirTensor) -> RepTensor:
+    """AddOp::rep_mir_kernel (replicated/arith.rs:81-121)."""
+    y0, y1, y2 = y.values
+    (x00, x10), (x11, x21), (x22, x02) = x.shares
+    z00 = add(x00, y0)
+    z02 = add(x02, y2)
+    s0 = z00.shape
+    s1 = add(x11, y1).shape
+    s2 = z02.shape
+    return RepTensor([[z00, broadcast(x10, s0)], [broadcast(x11, s1), broadcast(x21, s1)],
+                      [broadcast(x22, s2), z02]])
+
+
+def rep_mir_add(x: MirTensor, y: RepTensor) -> RepTensor:
+    """AddOp::mir_rep_kernel (replicated/arith.rs:39-79)."""
+    x0, x1, x2 = x.values
+    (y00, y10), (y11, y21), (y22, y02) = y.shares
+    z00 = add(x0, y00)
+    z02 = add(x2, y02)
+    s0, s1, s2 = z00.shape, add(x1, y11).shape, z02.shape
+    return RepTensor([[z00, broadcast(y10, s0)], [broadcast(y11, s1), broadcast(y21, s1)],
+                      [broadcast(y22, s2), z02]])
+
+
+def rep_sub_mir(x: RepTensor, y: MirTensor) -> RepTensor:
+    """SubOp::rep_mir_kernel (replicated/arith.rs:275-315)."""
+    y0, y1, y2 = y.values
+    (x00, x10), (x11, x21), (x22, x02) = x.shares
+    z00 = sub(x00, y0)
+    z02 = sub(x02, y2)
+    s0, s1, s2 = z00.shape, sub(x11, y1).shape, z02.shape
+    return RepTensor([[z00, broadcast(x10, s0)], [broadcast(x11, s1), broadcast(x21, s1)],
+                      [broadcast(x22, s2), z02]])
+
+
+def rep_mir_sub(x: MirTensor, y: RepTensor) -> RepTensor:
+    """SubOp::mir_rep_kernel (replicated/arith.rs:230-273)."""
+    x0, x1, x2 = x.values
+    (y00, y10), (y11, y21), (y22, y02) = y.shares
+    z00 = sub(x0, y00)
+    z10, z11, z21, z22 = neg(y10), neg(y11), neg(y21), neg(y22)
+    z02 = sub(x2, y02)
+    s0, s1, s2 = z00.shape, sub(x1, y11).shape, z02.shape
+    return RepTensor([[z00, broadcast(z10, s0)], [broadcast(z11, s1), broadcast(z21, s1)],
+                      [broadcast(z22, s2), z02]])
+
+
+def rep_mul_mir(x: RepTensor, y: MirTensor) -> RepTensor:
+    """MulOp::rep_mir_kernel (replicated/arith.rs:402-434)."""
+    return RepTensor([[mul(v, y.values[i]) for v in x.shares[i]] for i in range(3)])
+
+
+def rep_mir_mul(x: MirTensor, y: RepTensor) -> RepTensor:
+    """MulOp::mir_rep_kernel (replicated/arith.rs:369-400)."""
+    return RepTensor([[mul(x.values[i], v) for v in y.shares[i]] for i in range(3)])
+
+
+def _rep_bilinear(sess: Session, op, x: RepTensor, y: RepTensor) -> RepTensor:
+    (x00, x10), (x11, x21), (x22, x02) = x.shares
+    (y00, y10), (y11, y21), (y22, y02) = y.shares
+    v0 = add(add(op(x00, y00), op(x00, y10)), op(x10, y00))
+    v1 = add(add(op(x11, y11), op(x11, y21)), op(x21, y11))
+    v2 = add(add(op(x22, y22), op(x22, y02)), op(x02, y22))
+    a0, a1, a2 = gen_zero_share(sess, v0)
+    z0, z1, z2 = add(v0, a0), add(v1, a1), add(v2, a2)
+    return RepTensor([[z0, z1], [z1, z2], [z2, z0]])
+
+
+def rep_mul(sess: Session, x: RepTensor, y: RepTensor) -> RepTensor:
+    """MulOp::rep_rep_kernel (replicated/arith.rs:317-367); AndOp::rep_kernel for bits (:495-508)."""
+    return _rep_bilinear(sess, mul, x, y)
+
+
+def rep_dot(sess: Session, x: RepTensor, y: RepTensor) -> RepTensor:
+    """DotOp::rep_rep_kernel (replicated/arith.rs:436-493)."""
+    return _rep_bilinear(sess, dot, x, y)
+
+
+rep_and = rep_mul
+rep_xor = rep_add
+
+
+# -- additive (2-party) helpers: adt = (player0, player1), provider = player2 --
+
+def rep_to_adt(x: RepTensor) -> AdtTensor:
+    """RepToAdtOp::rep_to_adt_kernel, adt=(rep0,rep1) branch (additive/convert.rs:28-37)."""
+    (x00, x10), (_x11, x21), _ = x.shares
+    return AdtTensor([add(x00, x10), x21])
+
+
+def adt_reveal(x: AdtTensor):
+    """RevealOp::host_adt_kernel (additive/ops.rs:72-84)."""
+    return add(x.shares[0], x.shares[1])
+
+
+def gen_trunc_mask(sess: Session, amount: int, like: Ring):
+    """TruncMaskGen::gen_trunc_mask at the provider (additive/trunc.rs:22-65)."""
+    r = sess.sample_uniform(like)
+    r_msb = shr(like.bits - 1, r)
+    r_top = shr(amount + 1, shl(1, r))
+    key = sess.gen_key()
+
+    def share(v):
+        sync_key = sess.sync_key_random()
+        seed = sess.derive_seed(sync_key, key)
+        x0 = sess.sample_like(like, seed)
+        x1 = sub(v, x0)
+        return AdtTensor([x0, x1])
+
+    r_shared = share(r)
+    r_top_shared = share(r_top)
+    r_msb_shared = share(r_msb)
+    return r_shared, r_top_shared, r_msb_shared
+
+
+def adt_trunc_pr(sess: Session, amount: int, x: AdtTensor) -> AdtTensor:
+    """TruncPrProvider::trunc_pr (additive/trunc.rs:114-169)."""
+    x0, x1 = x.shares
+    bits = x0.bits
+    r, r_top, r_msb = gen_trunc_mask(sess, amount, x0)
+    k = bits - 1
+    ones = fill(bits, 1, x0.shape)
+    upshifter = shl(k - 1, ones)
+    downshifter = shl(k - amount - 1, ones)
+    # adt + host(player0): public value lands on share 0 (additive/ops.rs:105-126)
+    x_positive = AdtTensor([add(x0, upshifter), x1])
+    masked = AdtTensor([add(x_positive.shares[0], r.shares[0]), add(x_positive.shares[1], r.shares[1])])
+    c = adt_reveal(masked)
+    c_no_msb = shl(1, c)
+    c_top = shr(amount + 1, c_no_msb)
+    c_msb = shr(bits - 1, c)
+    # overflow = r_msb + c_msb - r_msb*c_msb - r_msb*c_msb
+    t = AdtTensor([add(r_msb.shares[0], c_msb), r_msb.shares[1]])
+    m = AdtTensor([mul(r_msb.shares[0], c_msb), mul(r_msb.shares[1], c_msb)])
+    t = AdtTensor([sub(t.shares[0], m.shares[0]), sub(t.shares[1], m.shares[1])])
+    overflow = AdtTensor([sub(t.shares[0], m.shares[0]), sub(t.shares[1], m.shares[1])])
+    shifted_overflow = AdtTensor([shl(k - amount, overflow.shares[0]), shl(k - amount, overflow.shares[1])])
+    # c_top - r_top: host(player0) - adt (additive/ops.rs:205-229)
+    y = AdtTensor([sub(c_top, r_top.shares[0]), neg(r_top.shares[1])])
+    y_positive = AdtTensor([add(y.shares[0], shifted_overflow.shares[0]),
+                            add(y.shares[1], shifted_overflow.shares[1])])
+    return AdtTensor([sub(y_positive.shares[0], downshifter), y_positive.shares[1]])
+
+
+def adt_to_rep(sess: Session, x: AdtTensor) -> RepTensor:
+    """AdtToRepOp::kernel, provider = rep player2 branch (replicated/convert.rs:392-497)."""
+    x0, x1 = x.shares
+    sync_key0 = sess.sync_key_random()
+    sync_key1 = sess.sync_key_random()
+    k = sess.gen_key()
+    seed1 = sess.derive_seed(sync_key0, k)
+    seed2 = sess.derive_seed(sync_key1, k)
+    y0 = sess.sample_like(x0, seed1)
+    y1 = sess.sample_like(x1, seed2)
+    y0_provider = sess.sample_like(x0, seed1)
+    y1_provider = sess.sample_like(x0, seed2)
+    c = add(sub(x0, y0), sub(x1, y1))
+    return RepTensor([[y0, c], [c, y1], [y1_provider, y0_provider]])
+
+
+def rep_trunc_pr(sess: Session, amount: int, x: RepTensor) -> RepTensor:
+    """TruncPrOp::rep_kernel (replicated/fixedpoint.rs:80-103)."""
+    x_adt = rep_to_adt(x)
+    y_adt = adt_trunc_pr(sess, amount, x_adt)
+    return adt_to_rep(sess, y_adt)
+
+
+# -- bits ---------------------------------------------------------------------
+
+def rep_split(sess: Session, x: RepTensor):
+    """PlacementSplit::split (replicated/bits.rs:84-134)."""
+    (x00, x10), (_x11, x21), (x22, _x02) = x.shares
+    left = add(x00, x10)
+    bsl = bit_decompose(left)
+    x2_on_1 = bit_decompose(x21)
+    x2_on_2 = bit_decompose(x22)
+    p0_zero = fill_bits(0, bsl.shape)
+    p1_zero = fill_bits(0, x2_on_1.shape)
+    p2_zero = fill_bits(0, x2_on_2.shape)
+    rep_bsl = rep_share(sess, bsl, owner=0)
+    rep_bsr = RepTensor([[p0_zero, p0_zero], [p1_zero, x2_on_1], [x2_on_2, p2_zero]])
+    return rep_bsl, rep_bsr
+
+
+def rep_shl_dim(amount: int, bit_length: int, x: RepTensor) -> RepTensor:
+    """ShlDimOp::rep_kernel: share-wise shl_dim (replicated/ops.rs)."""
+    return RepTensor([[shl_dim(amount, bit_length, v) for v in row] for row in x.shares])
+
+
+def binary_adder(sess: Session, x: RepTensor, y: RepTensor, ring_size: int) -> RepTensor:
+    """BinaryAdder::binary_adder, Kogge-Stone (replicated/misc.rs:176-242)."""
+    log_r = int(math.log2(ring_size))
+    g = rep_and(sess, x, y)
+    p_store = rep_xor(x, y)
+    p = p_store
+    for i in range(log_r):
+        p1 = rep_shl_dim(1 << i, ring_size, p)
+        g1 = rep_shl_dim(1 << i, ring_size, g)
+        p_and_g = rep_and(sess, p, g1)
+        g = rep_xor(g, p_and_g)
+        p = rep_and(sess, p, p1)
+    c = rep_shl_dim(1, ring_size, g)
+    return rep_xor(c, p_store)
+
+
+def rep_bit_decompose(sess: Session, x: RepTensor) -> RepTensor:
+    """BitDecomposeOp::rep_ring_kernel (replicated/bits.rs:6-20)."""
+    bits = x.shares[0][0].bits
+    x0, x1 = rep_split(sess, x)
+    return binary_adder(sess, x0, x1, bits)
+
+
+def rep_index(index: int, x: RepTensor) -> RepTensor:
+    """IndexOp on RepBitArray: share-wise index_axis(0, index) (replicated/ops.rs)."""
+    return RepTensor([[index_axis0(index, v) for v in row] for row in x.shares])
+
+
+def rep_msb(sess: Session, x: RepTensor) -> RepTensor:
+    """MsbOp::rep_bit_kernel (replicated/arith.rs:611-626): full decomposition, plane k-1."""
+    bits = x.shares[0][0].bits
+    return rep_index(bits - 1, rep_bit_decompose(sess, x))
+
+
+def gen_dabit(sess: Session, bits: int, shape):
+    """DaBitProvider::gen_dabit (additive/dabit.rs:38-69)."""
+    like_b = Bits(shape, np.zeros((int(np.prod(shape, dtype=np.int64)) + 7) // 8, np.uint8))
+    like_r = fill(bits, 0, shape)
+    b = sess.sample_uniform(like_b)
+    br = ring_inject(bits, 0, b)
+    key = sess.gen_key()
+    seed_b = sess.derive_seed(sess.sync_key_random(), key)
+    seed_br = sess.derive_seed(sess.sync_key_random(), key)
+    b0_provider = sess.sample_like(like_b, seed_b)
+    b0 = sess.sample_like(like_b, seed_b)
+    b1 = sub(b, b0_provider)
+    br0_provider = sess.sample_like(like_r, seed_br)
+    br0 = sess.sample_like(like_r, seed_br)
+    br1 = sub(br, br0_provider)
+    return AdtTensor([br0, br1]), AdtTensor([b0, b1])
+
+
+def rep_ring_inject(sess: Session, bits: int, bit_idx: int, x: RepTensor) -> RepTensor:
+    """RingInjectOp::rep_kernel (replicated/convert.rs:316-390)."""
+    (x00, _), _, (x22, _) = x.shares
+    b_ring, b_bin = gen_dabit(sess, bits, x22.shape)
+    x_adt = rep_to_adt(x)
+    c = AdtTensor([add(x_adt.shares[0], b_bin.shares[0]), add(x_adt.shares[1], b_bin.shares[1])])
+    c_open = adt_reveal(c)
+    c_ring = ring_inject(bits, 0, c_open)
+    # b_ring + c_ring - b_ring*c_ring - b_ring*c_ring   (adt op host(player0))
+    t = AdtTensor([add(b_ring.shares[0], c_ring), b_ring.shares[1]])
+    m = AdtTensor([mul(b_ring.shares[0], c_ring), mul(b_ring.shares[1], c_ring)])
+    t = AdtTensor([sub(t.shares[0], m.shares[0]), sub(t.shares[1], m.shares[1])])
+    x_adt_ring = AdtTensor([sub(t.shares[0], m.shares[0]), sub(t.shares[1], m.shares[1])])
+    shifted = AdtTensor([shl(bit_idx, x_adt_ring.shares[0]), shl(bit_idx, x_adt_ring.shares[1])])
+    return adt_to_rep(sess, shifted)
+
+
+def rep_msb_ring(sess: Session, x: RepTensor) -> RepTensor:
+    """MsbOp::rep_ring_kernel (replicated/arith.rs:628-641)."""
+    bits = x.shares[0][0].bits
+    return rep_ring_inject(sess, bits, 0, rep_msb(sess, x))
+
+
+def rep_less(sess: Session, x: RepTensor, y: RepTensor) -> RepTensor:
+    """LessOp::rep_kernel (replicated/compare.rs:91-104): msb(x - y)."""
+    return rep_msb(sess, rep_sub(x, y))
+
+
+def rep_greater(sess: Session, x: RepTensor, y: RepTensor) -> RepTensor:
+    """GreaterOp::rep_kernel (replicated/compare.rs:136-149): msb(y - x)."""
+    return rep_msb(sess, rep_sub(y, x))
+
+
+def rep_mux(sess: Session, s: RepTensor, x: RepTensor, y: RepTensor) -> RepTensor:
+    """MuxOp::rep_kernel (replicated/control_flow.rs:9-25): s*(x-y)+y."""
+    return rep_add(rep_mul(sess, s, rep_sub(x, y)), y)
+
+
+def mir_fill(bits: int, value: int, shape) -> MirTensor:
+    v = fill(bits, value, shape)
+    return MirTensor([v, v, v])
+
+
+def rep_maximum(sess: Session, xs: List[RepTensor]) -> RepTensor:
+    """MaximumOp::kernel (replicated/softmax.rs:10-53)."""
+    n = len(xs)
+    if n == 0:
+        raise ValueError("maximum op needs a non-empty array of tensors")
+    if n == 1:
+        return xs[0]
+    max1 = rep_maximum(sess, xs[: n // 2])
+    max2 = rep_maximum(sess, xs[n // 2:])
+    bits = max1.shares[0][0].bits
+    lesser = rep_less(sess, max1, max2)
+    lesser_ring = rep_ring_inject(sess, bits, 0, lesser)
+    ones = mir_fill(bits, 1, lesser_ring.shape)
+    # lesser_ring * max2 + (ones - lesser_ring) * max1   (left-to-right evaluation)
+    a = rep_mul(sess, lesser_ring, max2)
+    b = rep_mul(sess, rep_mir_sub(ones, lesser_ring), max1)
+    return rep_add(a, b)
+
+
+def rep_relu(sess: Session, x: RepTensor) -> RepTensor:
+    """ReluOp::rep_ring_kernel (fixedpoint/ops.rs:314-330): mux(msb_ring(x), 0, x)."""
+    bits = x.shares[0][0].bits
+    sign = rep_msb_ring(sess, x)
+    zeros = RepTensor([[zeros_like(v) for v in row] for row in x.shares])
+    return rep_mux(sess, sign, zeros, x)

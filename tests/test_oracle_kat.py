@@ -1,0 +1,147 @@
+"""Pin the oracle against every golden vector the reference's own tests hold
+for the hot path.  Paths cite /root/reference/moose/src."""
+import numpy as np
+import pytest
+
+from oracle import moose_oracle as mo
+
+
+def ints(t):
+    return [int(v) for v in t.to_ints().reshape(-1)]
+
+
+def test_aes128_fips197_vectors():
+    # FIPS-197 appendix B and C.1
+    assert mo.aes_block(bytes.fromhex("2b7e151628aed2a6abf7158809cf4f3c"),
+                        bytes.fromhex("3243f6a8885a308d313198a2e0370734")).hex() == "3925841d02dc09fbdc118597196a0b32"
+    assert mo.aes_block(bytes(range(16)), bytes.fromhex("00112233445566778899aabbccddeeff")).hex() \
+        == "69c4e0d86a7b0430d8cdb78070b4c55a"
+
+
+@pytest.mark.parametrize("portable", [0, 1])
+def test_ring_sample_golden(portable):
+    """host/mod.rs:1050-1079 (ring_sample): seed 0^16, shape [5]."""
+    mo._force_portable(portable)
+    try:
+        seed = bytes(16)
+        assert ints(mo.sample_uniform_seeded(64, (5,), seed)) == [
+            4263935709876578662, 3326810793440857224, 17325099178452873543,
+            15208531650305571673, 9619880027406922172]
+        assert ints(mo.sample_uniform_seeded(128, (5,), seed)) == [
+            78655730786844307471556614669614075016, 319591670596555766473793801091584867161,
+            177455464885365520564027128957528354027, 72628979995024532377123578937486303732,
+            299726520301515014350190124791858941972]
+    finally:
+        mo._force_portable(0)
+
+
+@pytest.mark.parametrize("policy", [mo.BIT_POLICY_STREAM_LSB0, mo.BIT_POLICY_U16_PER_BIT])
+def test_bit_sample_golden(policy):
+    """host/mod.rs:941-951 (bit_sample) and :1081-1085 (sample_bits_seeded)."""
+    seed = bytes(16)
+    assert mo.sample_uniform_seeded_bits((5,), seed, policy).to_array().tolist() == [0, 1, 1, 0, 0]
+    assert ints(mo.sample_bits_seeded_ring(64, (5,), seed, policy)) == [0, 1, 1, 0, 0]
+    assert ints(mo.sample_bits_seeded_ring(128, (5,), seed, policy)) == [0, 1, 1, 0, 0]
+
+
+def test_derive_seed_golden():
+    """execution/mod.rs:172-199 (test_constants_derive_seed): key 0^16, sync_key [1,2,3],
+    session id "foobar" (TestSyncExecutor default)."""
+    sid = mo.session_id_bytes("foobar")
+    seed = mo.derive_seed(sid, mo.sync_key_from([1, 2, 3]), bytes(16))
+    assert list(seed) == [79, 203, 243, 208, 77, 199, 116, 216, 2, 206, 173, 36, 20, 204, 200, 146]
+
+
+def test_host_mul_u128_wrap():
+    """host/mod.rs:1291-1299 (test_host_mul)."""
+    x = mo.Ring.from_ints(128, [340282366920938463463374415046855271599])
+    assert ints(mo.mul(x, x)) == [37011954726876357358499180449]
+
+
+def test_ring_dot_kats():
+    """host/mod.rs:1011-1047."""
+    x = mo.Ring.from_ints(64, [[1, 2], [3, 4]])
+    assert ints(mo.dot(x, mo.Ring.from_ints(64, [1, 1]))) == [3, 7]
+    z = mo.dot(x, mo.Ring.from_ints(64, [[1, 0], [0, 1]]))
+    assert z.shape == (2, 2) and ints(z) == [1, 2, 3, 4]
+    z = mo.dot(mo.Ring.from_ints(64, [1, 2]), mo.Ring.from_ints(64, [1, 1]))
+    assert z.shape == () and ints(z) == [3]
+
+
+def test_ring_add_n():
+    """host/mod.rs:1119-1148."""
+    x = mo.Ring.from_ints(64, [[1, 4], [9, 16], [25, 36]])
+    y = mo.Ring.from_ints(64, [[1, 3], [6, 10], [15, 21]])
+    z = mo.Ring.from_ints(64, [[1, 36], [1225, 41616], [1413721, 48024900]])
+    assert ints(mo.add_n([x])) == [1, 4, 9, 16, 25, 36]
+    assert ints(mo.add_n([x, y, z])) == [3, 43, 1240, 41642, 1413761, 48024957]
+    w = mo.Ring.from_ints(128, [[6, 3, 10], [5, 16, 8], [4, 2, 1]])
+    x = mo.Ring.from_ints(128, [[40, 20, 10], [5, 16, 8], [4, 2, 1]])
+    y = mo.Ring.from_ints(128, [[42, 21, 64], [32, 16, 8], [4, 2, 1]])
+    z = mo.Ring.from_ints(128, [[256, 128, 64], [32, 16, 8], [4, 2, 1]])
+    assert ints(mo.add_n([w, x, y, z])) == [344, 172, 148, 74, 64, 32, 16, 8, 4]
+
+
+BITS_6743 = [0, 0, 1, 0, 1, 0, 0, 0, 1, 0, 0, 1, 1, 0, 0, 1, 0, 1, 1, 1, 1, 1, 0, 1, 0, 0, 1, 0,
+             0, 0, 1, 1, 0, 0, 0, 1, 0, 0, 1, 1, 1, 1, 1, 0, 1, 1, 0, 1, 0, 0, 1, 0, 1, 0, 0, 1,
+             1, 0, 1, 1, 1, 0, 1, 0]
+
+
+def test_bit_decompose_and_extract():
+    """host/mod.rs:1151-1204 (bit_extract, bit_decompose1, bit_decompose2)."""
+    x = mo.Ring.from_ints(64, [6743216615002642708])
+    b = mo.bit_decompose(x)
+    assert b.shape == (64, 1) and b.to_array().reshape(-1).tolist() == BITS_6743
+    x = mo.Ring.from_ints(64, [[[1, 2], [3, 4]], [[4, 5], [6, 7]]])
+    xb = mo.bit_decompose(x)
+    for i in range(64):
+        assert mo.index_axis0(i, xb) == mo.bit_extract(i, x)
+    v = mo.fill(64, 7, (5,))
+    assert mo.bit_extract(2, v).to_array().tolist() == [1] * 5
+    assert mo.bit_extract(3, v).to_array().tolist() == [0] * 5
+
+
+def test_bit_shl_dim():
+    """host/mod.rs:1206-1225."""
+    x = mo.Ring.from_ints(64, [6743216615002642708])
+    out = mo.shl_dim(6, 64, mo.bit_decompose(x))
+    assert out.to_array().reshape(-1).tolist() == [0] * 6 + BITS_6743[:58]
+
+
+def test_shift_masks_amount_like_rust_wrapping():
+    """Wrapping<T> << usize masks the amount (host/ops.rs:1864,1879)."""
+    x = mo.Ring.from_ints(64, [5])
+    assert ints(mo.shl(64, x)) == [5] and ints(mo.shr(64, x)) == [5]
+    x = mo.Ring.from_ints(128, [5])
+    assert ints(mo.shl(128, x)) == [5] and ints(mo.shl(127, x)) == [1 << 127]
+
+
+def test_fixed_encode_decode():
+    """host/ops.rs:1377-1417, host/fixedpoint.rs:10-38: truncation toward zero."""
+    v = np.array([1.5, -1.5, 0.3, -0.3])
+    e = mo.fixed_encode(128, v, 40)
+    assert ints(e) == [int(t * 2 ** 40) % (1 << 128) for t in v]
+    assert np.allclose(mo.fixed_decode(e, 40), v, atol=2 ** -40)
+    e = mo.fixed_encode(64, v, 23)
+    assert ints(e) == [int(t * 2 ** 23) % (1 << 64) for t in v]
+
+
+def test_elementwise_against_python_ints():
+    rng = np.random.default_rng(0)
+    for bits in (64, 128):
+        mod = 1 << bits
+        a = [int.from_bytes(rng.bytes(bits // 8), "little") for _ in range(37)]
+        b = [int.from_bytes(rng.bytes(bits // 8), "little") for _ in range(37)]
+        A, B = mo.Ring.from_ints(bits, a), mo.Ring.from_ints(bits, b)
+        assert ints(mo.add(A, B)) == [(x + y) % mod for x, y in zip(a, b)]
+        assert ints(mo.sub(A, B)) == [(x - y) % mod for x, y in zip(a, b)]
+        assert ints(mo.mul(A, B)) == [(x * y) % mod for x, y in zip(a, b)]
+        assert ints(mo.neg(A)) == [(-x) % mod for x in a]
+        assert ints(mo.shl(13, A)) == [(x << 13) % mod for x in a]
+        assert ints(mo.shr(13, A)) == [x >> 13 for x in a]
+        M, K, N = 3, 5, 4
+        a = [int.from_bytes(rng.bytes(bits // 8), "little") for _ in range(M * K)]
+        b = [int.from_bytes(rng.bytes(bits // 8), "little") for _ in range(K * N)]
+        C = mo.dot(mo.Ring.from_ints(bits, a, (M, K)), mo.Ring.from_ints(bits, b, (K, N)))
+        exp = [sum(a[i * K + k] * b[k * N + j] for k in range(K)) % mod for i in range(M) for j in range(N)]
+        assert ints(C) == exp
