@@ -1,0 +1,260 @@
+/*
+ * moose_b200.h -- C ABI of libmoose_b200.so: B200 (sm_100a) kernels for Moose's
+ * replicated-secret-sharing hot path.
+ *
+ * Drop-in boundary.  After Moose's lowering pass only `[runtime]` HostPlacement
+ * kernels survive in a computation (moose/src/compilation/lowering.rs:4-6); they
+ * are plain Rust fns `fn(&S, &HostPlacement, attrs.., T0[, T1]) -> Result<U>`
+ * registered by modelled_kernel! (moose/src/kernels/*.rs) and implemented in
+ * moose/src/host/ops.rs and moose/src/host/prim.rs.  Section "host kernels"
+ * below has one entry point per such kernel on ring / bit / seed / key types;
+ * each comment cites the Rust kernel it replaces.  Section "replicated
+ * protocols" adds fused entry points that execute a whole replicated protocol
+ * (moose/src/replicated/*.rs, moose/src/additive/*.rs) in a handful of kernel
+ * launches and produce bit-identical shares to the op-by-op path.
+ *
+ * Conventions (mirroring moose/src/kernels/mod.rs:34-106 and error.rs:8-59):
+ *  - every call returns MB_OK (0) or a negative mb_status; mb_last_error()
+ *    gives the message a Rust shim maps to Error::KernelError(String);
+ *  - operands are immutable, results are freshly allocated device tensors
+ *    owned by the caller (free with mb_tensor_free / mb_rep_free);
+ *  - no torch / C++ types cross the boundary: opaque handles, plain pointers,
+ *    sizes;
+ *  - all device work of a context is issued on that context's CUDA stream and
+ *    is asynchronous; mb_tensor_to_host / mb_ctx_sync synchronise;
+ *  - thread safe: concurrent calls on one context serialise on its stream;
+ *  - there is NO CPU fallback: creating a context without a CUDA device fails.
+ *
+ * Layouts: MB_RING64 = uint64_t, MB_RING128 = little-endian 128-bit integer
+ * (identical to Rust u128 / unsigned __int128 on x86-64), row-major "standard
+ * layout" (moose/src/host/mod.rs:388).  MB_BIT = packed bits, flat row-major
+ * bit j in byte j/8, bit j%8 (BitVec<u8, Lsb0>, moose/src/host/bitarray.rs:10-13).
+ *
+ * Determinism contract: PrfKeyGen, unseeded Sample and
+ * SyncKey::random() draw 16 bytes each from the context's entropy source in
+ * program order.  By default that is the OS (getrandom); with
+ * mb_ctx_set_entropy_key() it is AES-128-CTR(key) block i for the i-th request,
+ * which makes every share reproducible (used by the parity tests).
+ */
+#ifndef MOOSE_B200_H
+#define MOOSE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mb_ctx mb_ctx;       /* one per (device, session) */
+typedef struct mb_tensor mb_tensor; /* device tensor: HostRingTensor<u64|u128> / HostBitTensor */
+typedef struct mb_rep mb_rep;       /* RepTensor: three distinct shares x0,x1,x2 (party i holds x_i, x_{i+1}) */
+
+typedef enum { MB_RING64 = 0, MB_RING128 = 1, MB_BIT = 2, MB_FLOAT64 = 3 } mb_dtype;
+
+typedef enum {
+  MB_OK = 0,
+  MB_ERR_INVALID_ARGUMENT = -1, /* Error::InvalidArgument */
+  MB_ERR_KERNEL = -2,           /* Error::KernelError */
+  MB_ERR_UNIMPLEMENTED = -3,    /* Error::UnimplementedOperator */
+  MB_ERR_TYPE_MISMATCH = -4,    /* Error::TypeMismatch */
+  MB_ERR_CUDA = -5,
+  MB_ERR_NO_DEVICE = -6
+} mb_status;
+
+#define MB_MAX_RANK 6
+
+/* ---------------------------------------------------------------- context */
+
+/* Creates a context bound to CUDA device `device`. Fails with MB_ERR_NO_DEVICE
+ * when no CUDA device is present (there is no CPU path). */
+int mb_ctx_create(int device, mb_ctx **out);
+int mb_ctx_destroy(mb_ctx *ctx);
+/* Message of the last failing call on this thread for `ctx` (ctx may be NULL
+ * for mb_ctx_create failures). */
+const char *mb_last_error(const mb_ctx *ctx);
+/* SessionId::try_from(&str): secure id = blake3(logical)[0..16]
+ * (moose/src/computation.rs:108-124). */
+int mb_ctx_set_session(mb_ctx *ctx, const char *logical_id);
+int mb_ctx_set_session_raw(mb_ctx *ctx, const uint8_t sid[16]);
+int mb_ctx_get_session_raw(const mb_ctx *ctx, uint8_t sid[16]);
+/* Deterministic entropy source (see header comment); resets the request counter
+ * and forgets the cached replicated setup. */
+int mb_ctx_set_entropy_key(mb_ctx *ctx, const uint8_t key[16]);
+int mb_ctx_sync(mb_ctx *ctx);
+/* cudaStream_t of the context, for callers that interoperate (e.g. torch). */
+void *mb_ctx_stream(mb_ctx *ctx);
+/* CUDA-event timer on the context stream. */
+int mb_ctx_timer_start(mb_ctx *ctx);
+int mb_ctx_timer_stop(mb_ctx *ctx, float *elapsed_ms);
+/* Number of kernels this library launched on `ctx` since creation. */
+uint64_t mb_ctx_launch_count(const mb_ctx *ctx);
+
+/* ---------------------------------------------------------------- tensors */
+
+int mb_tensor_from_host(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape,
+                        const void *host_data, mb_tensor **out);
+int mb_tensor_alloc(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, mb_tensor **out);
+/* Copies the tensor to host memory (nbytes must equal mb_tensor_nbytes) and
+ * synchronises the stream. */
+int mb_tensor_to_host(mb_ctx *ctx, const mb_tensor *t, void *host_out, size_t nbytes);
+int mb_tensor_free(mb_ctx *ctx, mb_tensor *t);
+mb_dtype mb_tensor_dtype(const mb_tensor *t);
+int mb_tensor_rank(const mb_tensor *t);
+const int64_t *mb_tensor_shape(const mb_tensor *t);
+int64_t mb_tensor_numel(const mb_tensor *t);
+size_t mb_tensor_nbytes(const mb_tensor *t); /* bits: (numel+7)/8 */
+void *mb_tensor_device_ptr(const mb_tensor *t);
+/* ReshapeOp (host/ops.rs:1465-1505): new handle sharing no storage (copy). */
+int mb_reshape(mb_ctx *ctx, const mb_tensor *x, int rank, const int64_t *shape, mb_tensor **out);
+
+/* ------------------------------------------------- host kernels: primitives */
+
+/* PrfKeyGenOp::kernel (moose/src/host/prim.rs:113-121). */
+int mb_prf_key_gen(mb_ctx *ctx, uint8_t key_out[16]);
+/* SyncKey::random() (moose/src/host/prim.rs:73-79). */
+int mb_sync_key_random(mb_ctx *ctx, uint8_t sync_key_out[16]);
+/* DeriveSeedOp::kernel (moose/src/host/prim.rs:123-149):
+ * blake3_keyed(derive_key("Derive Seed", key))(sid || sync_key)[0..16]. */
+int mb_derive_seed(mb_ctx *ctx, const uint8_t sync_key[16], const uint8_t key[16], uint8_t seed_out[16]);
+/* SampleSeededOp::{ring64,ring128,bit}_kernel (moose/src/host/ops.rs:1959-2036).
+ * max_value < 0: None (uniform); max_value == 1: ring element = get_bit();
+ * any other value: MB_ERR_UNIMPLEMENTED like the reference. For MB_BIT a
+ * max_value >= 0 is MB_ERR_UNIMPLEMENTED (ops.rs:2025-2029). */
+int mb_sample_seeded(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape,
+                     const uint8_t seed[16], int64_t max_value, mb_tensor **out);
+/* SampleOp::* (moose/src/host/ops.rs:1883-1957): seed drawn from the entropy source. */
+int mb_sample(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, int64_t max_value,
+              mb_tensor **out);
+/* FillOp::host_{ring64,ring128,bit}_kernel (moose/src/host/ops.rs:1623-1655). */
+int mb_fill(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, uint64_t value_lo,
+            uint64_t value_hi, mb_tensor **out);
+
+/* ------------------------------------------------ host kernels: ring arithmetic */
+
+/* AddOp/SubOp/MulOp::ring_kernel (moose/src/host/ops.rs:1709-1737,299-310) with
+ * ndarray co-broadcasting; on MB_BIT operands add = sub = xor, mul = and
+ * (moose/src/kernels/boolean.rs:18-76). */
+int mb_add(mb_ctx *ctx, const mb_tensor *x, const mb_tensor *y, mb_tensor **out);
+int mb_sub(mb_ctx *ctx, const mb_tensor *x, const mb_tensor *y, mb_tensor **out);
+int mb_mul(mb_ctx *ctx, const mb_tensor *x, const mb_tensor *y, mb_tensor **out);
+/* NegOp::ring_kernel / NegOp::bit_kernel (moose/src/host/ops.rs:1739-1752,1555-1565). */
+int mb_neg(mb_ctx *ctx, const mb_tensor *x, mb_tensor **out);
+/* ShlOp/ShrOp::ring_kernel (moose/src/host/ops.rs:1853-1881); the amount is
+ * masked mod the ring width like Rust's Wrapping<T> shifts. */
+int mb_shl(mb_ctx *ctx, uint64_t amount, const mb_tensor *x, mb_tensor **out);
+int mb_shr(mb_ctx *ctx, uint64_t amount, const mb_tensor *x, mb_tensor **out);
+/* DotOp::ring_kernel / HostRingTensor::dot (moose/src/host/ops.rs:1754-1851):
+ * rank (1,1), (1,2), (2,1), (2,2) contraction mod 2^k. */
+int mb_dot(mb_ctx *ctx, const mb_tensor *x, const mb_tensor *y, mb_tensor **out);
+/* AddNOp::host_kernel (moose/src/host/ops.rs:1084-1103). */
+int mb_add_n(mb_ctx *ctx, const mb_tensor *const *xs, int n, mb_tensor **out);
+/* SumOp::host_ring_kernel (moose/src/host/ops.rs:1067-1081); axis < 0 = all. */
+int mb_sum(mb_ctx *ctx, const mb_tensor *x, int axis, mb_tensor **out);
+/* BroadcastOp::host_ring_kernel (moose/src/host/ops.rs:1668-1681). */
+int mb_broadcast(mb_ctx *ctx, const mb_tensor *x, int rank, const int64_t *shape, mb_tensor **out);
+/* RingFixedpointEncodeOp / DecodeOp (moose/src/host/ops.rs:1362-1418,
+ * moose/src/host/fixedpoint.rs:10-38): (x * 2^f) as iK as uK, truncation toward
+ * zero, saturating; decode = (x as iK) as f64 / 2^f.  MB_FLOAT64 tensors hold
+ * IEEE doubles. */
+int mb_fixedpoint_encode(mb_ctx *ctx, mb_dtype ring, uint32_t fractional_precision,
+                         const mb_tensor *x_f64, mb_tensor **out);
+int mb_fixedpoint_decode(mb_ctx *ctx, uint32_t fractional_precision, const mb_tensor *x,
+                         mb_tensor **out_f64);
+
+/* ------------------------------------------------ host kernels: bit tensors */
+
+/* XorOp/AndOp/OrOp::host_kernel (moose/src/host/ops.rs:1507-1553). */
+int mb_xor(mb_ctx *ctx, const mb_tensor *x, const mb_tensor *y, mb_tensor **out);
+int mb_and(mb_ctx *ctx, const mb_tensor *x, const mb_tensor *y, mb_tensor **out);
+int mb_or(mb_ctx *ctx, const mb_tensor *x, const mb_tensor *y, mb_tensor **out);
+/* BitDecomposeOp::host_bit64/128_kernel (moose/src/host/ops.rs:896-936):
+ * result shape [k, shape...], plane i = (x >> i) & 1. */
+int mb_bit_decompose(mb_ctx *ctx, const mb_tensor *x, mb_tensor **out);
+/* BitExtractOp::kernel64/128 (moose/src/host/ops.rs:1567-1595). */
+int mb_bit_extract(mb_ctx *ctx, uint64_t bit_idx, const mb_tensor *x, mb_tensor **out);
+/* RingInjectOp::host_kernel (moose/src/host/ops.rs:1597-1621). */
+int mb_ring_inject(mb_ctx *ctx, mb_dtype ring, uint64_t bit_idx, const mb_tensor *x_bits,
+                   mb_tensor **out);
+/* ShlDimOp::host_bit_kernel (moose/src/host/ops.rs:835-853). */
+int mb_shl_dim(mb_ctx *ctx, uint64_t amount, uint64_t bit_length, const mb_tensor *x,
+               mb_tensor **out);
+/* IndexAxisOp (moose/src/host/ops.rs:740-783, bitarray.rs:85-108), axis 0 only. */
+int mb_index_axis0(mb_ctx *ctx, int64_t index, const mb_tensor *x, mb_tensor **out);
+
+/* ----------------------------------------------------- replicated protocols */
+
+/* Party indices 0,1,2 = the replicated placement's owners; 3 = a host outside it. */
+
+/* Takes ownership of nothing: the three share tensors are copied by reference
+ * count.  Shares must have identical dtype and shape. */
+int mb_rep_from_shares(mb_ctx *ctx, const mb_tensor *x0, const mb_tensor *x1, const mb_tensor *x2,
+                       mb_rep **out);
+/* Borrowed handle to share i (valid until mb_rep_free). */
+const mb_tensor *mb_rep_share_tensor(const mb_rep *x, int i);
+int mb_rep_free(mb_ctx *ctx, mb_rep *x);
+
+/* RepSetup generation (moose/src/replicated/setup.rs:39-58 via
+ * SyncSession::setup, execution/synchronous.rs:297-307): lazily draws the three
+ * PRF keys; exposed so callers can force the entropy order. */
+int mb_rep_setup(mb_ctx *ctx);
+/* ShareOp::ring_kernel (moose/src/replicated/convert.rs:49-160). */
+int mb_rep_share(mb_ctx *ctx, const mb_tensor *x, int owner, mb_rep **out);
+/* RevealOp::host_ring_kernel (moose/src/replicated/convert.rs:280-313). */
+int mb_rep_reveal(mb_ctx *ctx, const mb_rep *x, int receiver, mb_tensor **out);
+/* AddOp/SubOp::rep_rep_kernel (moose/src/replicated/arith.rs:7-37,197-228);
+ * XorOp::rep_kernel on bit shares (:510-523). */
+int mb_rep_add(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out);
+int mb_rep_sub(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out);
+/* NegOp::rep_rep_kernel / rep_bit_kernel (moose/src/replicated/arith.rs:525-583). */
+int mb_rep_neg(mb_ctx *ctx, const mb_rep *x, mb_rep **out);
+/* ShlOp::rep_kernel (moose/src/replicated/arith.rs:585-609). */
+int mb_rep_shl(mb_ctx *ctx, uint64_t amount, const mb_rep *x, mb_rep **out);
+/* AddOp::rep_mir_kernel / SubOp::rep_mir_kernel / SubOp::mir_rep_kernel /
+ * MulOp::rep_mir_kernel (moose/src/replicated/arith.rs:81-121,275-315,230-273,
+ * 402-434) with the mirrored value given once as a public tensor. */
+int mb_rep_add_public(mb_ctx *ctx, const mb_rep *x, const mb_tensor *pub, mb_rep **out);
+int mb_rep_sub_public(mb_ctx *ctx, const mb_rep *x, const mb_tensor *pub, mb_rep **out);
+int mb_rep_public_sub(mb_ctx *ctx, const mb_tensor *pub, const mb_rep *x, mb_rep **out);
+int mb_rep_mul_public(mb_ctx *ctx, const mb_rep *x, const mb_tensor *pub, mb_rep **out);
+/* MulOp::rep_rep_kernel (moose/src/replicated/arith.rs:317-367) incl. the
+ * zero-share (replicated/zero_share.rs:82-156); AndOp::rep_kernel on bits. */
+int mb_rep_mul(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out);
+/* DotOp::rep_rep_kernel (moose/src/replicated/arith.rs:436-493). */
+int mb_rep_dot(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out);
+/* TruncPrOp::rep_kernel (moose/src/replicated/fixedpoint.rs:80-103) =
+ * rep_to_adt (additive/convert.rs:12-79) + TruncPrProvider::trunc_pr
+ * (additive/trunc.rs:22-65,114-169) + AdtToRepOp (replicated/convert.rs:392-497). */
+int mb_rep_trunc_pr(mb_ctx *ctx, uint32_t amount, const mb_rep *x, mb_rep **out);
+/* BitDecomposeOp::rep_ring_kernel (moose/src/replicated/bits.rs:6-20,84-134;
+ * misc.rs:176-242): replicated bit shares of shape [k, shape...]. */
+int mb_rep_bit_decompose(mb_ctx *ctx, const mb_rep *x, mb_rep **out);
+/* MsbOp::rep_bit_kernel (moose/src/replicated/arith.rs:611-626). */
+int mb_rep_msb(mb_ctx *ctx, const mb_rep *x, mb_rep **out_bits);
+/* RingInjectOp::rep_kernel (moose/src/replicated/convert.rs:316-390) with
+ * gen_dabit (additive/dabit.rs:38-69). */
+int mb_rep_ring_inject(mb_ctx *ctx, mb_dtype ring, uint64_t bit_idx, const mb_rep *x_bits,
+                       mb_rep **out);
+/* MuxOp::rep_kernel (moose/src/replicated/control_flow.rs:9-25). */
+int mb_rep_mux(mb_ctx *ctx, const mb_rep *s, const mb_rep *x, const mb_rep *y, mb_rep **out);
+/* LessOp::rep_kernel (moose/src/replicated/compare.rs:91-104). */
+int mb_rep_less(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out_bits);
+/* MaximumOp::kernel (moose/src/replicated/softmax.rs:10-53). */
+int mb_rep_maximum(mb_ctx *ctx, const mb_rep *const *xs, int n, mb_rep **out);
+/* ReluOp::rep_ring_kernel (moose/src/fixedpoint/ops.rs:314-330). */
+int mb_rep_relu(mb_ctx *ctx, const mb_rep *x, mb_rep **out);
+/* IndexAxisOp::rep_kernel axis 0 / ShlDimOp::rep_bit_kernel
+ * (moose/src/replicated/ops.rs:331-376,475-504). */
+int mb_rep_index_axis0(mb_ctx *ctx, int64_t index, const mb_rep *x, mb_rep **out);
+int mb_rep_shl_dim(mb_ctx *ctx, uint64_t amount, uint64_t bit_length, const mb_rep *x, mb_rep **out);
+
+/* Selects the ring-GEMM implementation used by mb_dot / mb_rep_dot:
+ * 0 = automatic (int8 tensor pipe for large shapes, 64-bit IMAD CUDA-core
+ * kernel for skinny / small ones), 1 = force IMAD, 2 = force tensor pipe
+ * (fails for shapes it cannot tile).  For ncu comparisons and tests. */
+int mb_ctx_set_gemm_mode(mb_ctx *ctx, int mode);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MOOSE_B200_H */

@@ -1,0 +1,185 @@
+// Host-placement kernels on packed bit tensors.
+// Bit tensors are flat, row-major, LSB-first packed (BitVec<u8, Lsb0>,
+// moose/src/host/bitarray.rs:10-13); allocations are padded to 16 bytes and the
+// bits past numel are always zero.
+#include "common.h"
+
+namespace {
+
+constexpr int TPB = 256;
+
+template <typename T>
+__device__ __forceinline__ unsigned bit_of(T x, unsigned p) {
+  return (unsigned)((x >> p) & 1);
+}
+
+// BitDecomposeOp::host_bit64/128_kernel (host/ops.rs:896-936), n % 128 == 0:
+// a warp transposes 128 elements x KBITS planes with ballots and writes 16 bytes
+// per plane.
+template <typename T, int KBITS>
+__global__ void __launch_bounds__(TPB) bit_decompose_aligned_kernel(const T *__restrict__ x, uint32_t *__restrict__ out,
+                                                                   int64_t n) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * TPB + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * TPB) >> 5;
+  const int64_t ngroups = n / 128;
+  constexpr int PL = KBITS / 32;  // planes kept per lane
+  for (int64_t grp = warp; grp < ngroups; grp += nwarps) {
+    uint32_t keep[PL][4];
+#pragma unroll
+    for (int it = 0; it < 4; it++) {
+      T v = x[grp * 128 + it * 32 + lane];
+#pragma unroll
+      for (int p = 0; p < KBITS; p++) {
+        unsigned b = __ballot_sync(0xffffffffu, bit_of(v, p));
+        if (lane == (p & 31)) keep[p >> 5][it] = b;
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < PL; q++) {
+      int p = q * 32 + lane;
+      uint4 *dst = (uint4 *)(out + ((int64_t)p * n + grp * 128) / 32);
+      *dst = make_uint4(keep[q][0], keep[q][1], keep[q][2], keep[q][3]);
+    }
+  }
+}
+
+// Generic fallback: one thread per output word.
+template <typename T, int KBITS>
+__global__ void __launch_bounds__(TPB) bit_decompose_generic_kernel(const T *__restrict__ x, uint32_t *__restrict__ out,
+                                                                   int64_t n, int64_t nwords) {
+  int64_t w = (int64_t)blockIdx.x * TPB + threadIdx.x;
+  if (w >= nwords) return;
+  uint32_t word = 0;
+  int64_t total = (int64_t)KBITS * n;
+  for (int j = 0; j < 32; j++) {
+    int64_t idx = w * 32 + j;
+    if (idx < total) {
+      int64_t p = idx / n, e = idx % n;
+      word |= bit_of(x[e], (unsigned)p) << j;
+    }
+  }
+  out[w] = word;
+}
+
+// BitExtractOp::kernel64/128 (host/ops.rs:1567-1595).
+template <typename T>
+__global__ void __launch_bounds__(TPB) bit_extract_kernel(const T *__restrict__ x, uint32_t *__restrict__ out, int64_t n,
+                                                          unsigned bit_idx) {
+  int64_t e = (int64_t)blockIdx.x * TPB + threadIdx.x;
+  unsigned b = e < n ? bit_of(x[e], bit_idx) : 0u;
+  unsigned word = __ballot_sync(0xffffffffu, b);
+  if ((threadIdx.x & 31) == 0 && (e & ~31ll) < n) out[e >> 5] = word;
+}
+
+// RingInjectOp::host_kernel (host/ops.rs:1597-1621): bit b -> b << bit_idx.
+template <typename T>
+__global__ void __launch_bounds__(TPB) ring_inject_kernel(const uint32_t *__restrict__ bits, T *__restrict__ out, int64_t n,
+                                                          unsigned bit_idx) {
+  int64_t e = (int64_t)blockIdx.x * TPB + threadIdx.x;
+  if (e >= n) return;
+  uint32_t w = bits[e >> 5];
+  out[e] = (T)((w >> (e & 31)) & 1u) << bit_idx;
+}
+
+// out bits [dst, dst+nbits) = x bits [src, src+nbits), zero elsewhere.  Used by
+// ShlDimOp::host_bit_kernel (host/ops.rs:835-853) and IndexAxisOp on bit tensors
+// (bitarray.rs:85-108).
+__global__ void __launch_bounds__(TPB) bit_shift_copy_kernel(const uint32_t *__restrict__ x, int64_t x_words,
+                                                             uint32_t *__restrict__ out, int64_t out_words, int64_t src,
+                                                             int64_t dst, int64_t nbits) {
+  int64_t w = (int64_t)blockIdx.x * TPB + threadIdx.x;
+  if (w >= out_words) return;
+  int64_t lo = max(w * 32, dst), hi = min(w * 32 + 32, dst + nbits);
+  uint32_t word = 0;
+  if (lo < hi) {
+    int64_t s = lo - dst + src;
+    int64_t sw = s >> 5;
+    unsigned so = (unsigned)(s & 31);
+    uint64_t two = (uint64_t)x[sw];
+    if (sw + 1 < x_words) two |= (uint64_t)x[sw + 1] << 32;
+    unsigned len = (unsigned)(hi - lo);
+    uint32_t val = (uint32_t)(two >> so);
+    if (len < 32) val &= (1u << len) - 1;
+    word = val << (unsigned)(lo - w * 32);
+  }
+  out[w] = word;
+}
+
+__global__ void __launch_bounds__(TPB) bit_not_kernel(const uint32_t *__restrict__ x, uint32_t *__restrict__ out, int64_t nwords,
+                                                      int64_t numel) {
+  int64_t w = (int64_t)blockIdx.x * TPB + threadIdx.x;
+  if (w >= nwords) return;
+  uint32_t v = ~x[w];
+  int64_t lo = w * 32;
+  if (lo >= numel) v = 0;
+  else if (lo + 32 > numel) v &= (1u << (unsigned)(numel - lo)) - 1;
+  out[w] = v;
+}
+
+inline unsigned blocks(int64_t n) { return (unsigned)((n + TPB - 1) / TPB); }
+
+}  // namespace
+
+int k_bit_decompose(mb_ctx *ctx, const mb_tensor *x, mb_tensor *out) {
+  int64_t n = x->numel;
+  if (n == 0) return MB_OK;
+  uint32_t *o = (uint32_t *)out->dptr;
+  if (n % 128 == 0) {
+    int64_t warps = n / 128;
+    int g = (int)std::min<int64_t>((warps * 32 + TPB - 1) / TPB, (int64_t)ctx->sm_count * 8);
+    if (x->dtype == MB_RING128)
+      bit_decompose_aligned_kernel<u128, 128><<<g, TPB, 0, ctx->stream>>>((const u128 *)x->dptr, o, n);
+    else
+      bit_decompose_aligned_kernel<uint64_t, 64><<<g, TPB, 0, ctx->stream>>>((const uint64_t *)x->dptr, o, n);
+  } else {
+    int64_t nwords = (int64_t)(out->alloc_bytes / 4);
+    if (x->dtype == MB_RING128)
+      bit_decompose_generic_kernel<u128, 128><<<blocks(nwords), TPB, 0, ctx->stream>>>((const u128 *)x->dptr, o, n, nwords);
+    else
+      bit_decompose_generic_kernel<uint64_t, 64><<<blocks(nwords), TPB, 0, ctx->stream>>>((const uint64_t *)x->dptr, o, n, nwords);
+  }
+  MB_LAUNCH_CHECK(ctx);
+  return MB_OK;
+}
+
+int k_bit_extract(mb_ctx *ctx, unsigned bit_idx, const mb_tensor *x, mb_tensor *out) {
+  int64_t n = x->numel;
+  if (n == 0) return MB_OK;
+  // zero the padded tail first (the kernel writes whole words only where elements exist)
+  MB_CUDA(ctx, cudaMemsetAsync(out->dptr, 0, out->alloc_bytes, ctx->stream));
+  int64_t threads = ((n + 31) / 32) * 32;
+  if (x->dtype == MB_RING128)
+    bit_extract_kernel<u128><<<blocks(threads), TPB, 0, ctx->stream>>>((const u128 *)x->dptr, (uint32_t *)out->dptr, n, bit_idx & 127);
+  else
+    bit_extract_kernel<uint64_t><<<blocks(threads), TPB, 0, ctx->stream>>>((const uint64_t *)x->dptr, (uint32_t *)out->dptr, n, bit_idx & 63);
+  MB_LAUNCH_CHECK(ctx);
+  return MB_OK;
+}
+
+int k_ring_inject(mb_ctx *ctx, unsigned bit_idx, const mb_tensor *bits, mb_tensor *out) {
+  int64_t n = out->numel;
+  if (n == 0) return MB_OK;
+  if (out->dtype == MB_RING128)
+    ring_inject_kernel<u128><<<blocks(n), TPB, 0, ctx->stream>>>((const uint32_t *)bits->dptr, (u128 *)out->dptr, n, bit_idx & 127);
+  else
+    ring_inject_kernel<uint64_t><<<blocks(n), TPB, 0, ctx->stream>>>((const uint32_t *)bits->dptr, (uint64_t *)out->dptr, n, bit_idx & 63);
+  MB_LAUNCH_CHECK(ctx);
+  return MB_OK;
+}
+
+int k_bit_shift_copy(mb_ctx *ctx, const mb_tensor *x, int64_t src_bit, int64_t dst_bit, int64_t nbits, mb_tensor *out) {
+  int64_t out_words = (int64_t)(out->alloc_bytes / 4);
+  int64_t x_words = (int64_t)(x->alloc_bytes / 4);
+  bit_shift_copy_kernel<<<blocks(out_words), TPB, 0, ctx->stream>>>((const uint32_t *)x->dptr, x_words, (uint32_t *)out->dptr,
+                                                                   out_words, src_bit, dst_bit, nbits);
+  MB_LAUNCH_CHECK(ctx);
+  return MB_OK;
+}
+
+int k_bit_not(mb_ctx *ctx, const mb_tensor *x, mb_tensor *out) {
+  int64_t nwords = (int64_t)(out->alloc_bytes / 4);
+  bit_not_kernel<<<blocks(nwords), TPB, 0, ctx->stream>>>((const uint32_t *)x->dptr, (uint32_t *)out->dptr, nwords, x->numel);
+  MB_LAUNCH_CHECK(ctx);
+  return MB_OK;
+}

@@ -1,0 +1,142 @@
+// Internal declarations shared by the translation units of libmoose_b200.so.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/moose_b200.h"
+
+typedef unsigned __int128 u128;
+
+struct mb_tensor {
+  mb_dtype dtype;
+  int rank;
+  int64_t shape[MB_MAX_RANK];
+  int64_t numel;
+  size_t nbytes;        // logical bytes (bits: (numel+7)/8)
+  size_t alloc_bytes;   // allocation size (multiple of 16)
+  void *dptr;
+  std::atomic<int> refs;
+  int device;
+};
+
+struct mb_rep {
+  mb_tensor *s[3];
+};
+
+// AES-128 expanded key as 44 little-endian column words.
+struct AesKey {
+  uint32_t rk[44];
+};
+
+struct mb_ctx {
+  int device;
+  cudaStream_t stream;
+  cudaEvent_t ev0, ev1;
+  int sm_count;
+  std::mutex mu;             // guards entropy, setup, last-error bookkeeping
+  uint8_t sid[16];
+  bool deterministic;
+  uint8_t entropy_key[16];
+  uint64_t entropy_counter;
+  bool have_setup;
+  uint8_t setup_keys[3][16]; // k0,k1,k2 (k10=k11 etc., replicated/setup.rs:39-58)
+  int gemm_mode;
+  std::atomic<uint64_t> launches;
+  // scratch for the limb GEMM (grown on demand, stream ordered)
+  void *scratch[4];
+  size_t scratch_bytes[4];
+};
+
+// ---- error handling ---------------------------------------------------------
+void mb_set_error(const mb_ctx *ctx, const std::string &msg);
+int mb_fail(const mb_ctx *ctx, int code, const std::string &msg);
+
+#define MB_CUDA(ctx, expr)                                                           \
+  do {                                                                               \
+    cudaError_t _e = (expr);                                                         \
+    if (_e != cudaSuccess)                                                           \
+      return mb_fail((ctx), MB_ERR_CUDA,                                             \
+                     std::string(#expr) + ": " + cudaGetErrorString(_e));            \
+  } while (0)
+
+#define MB_CHECK(expr)            \
+  do {                            \
+    int _rc = (expr);             \
+    if (_rc != MB_OK) return _rc; \
+  } while (0)
+
+#define MB_LAUNCH_CHECK(ctx)                 \
+  do {                                       \
+    (ctx)->launches.fetch_add(1);            \
+    MB_CUDA((ctx), cudaGetLastError());      \
+  } while (0)
+
+// ---- tensors (tensor.cpp) ---------------------------------------------------
+static inline int mb_elem_bytes(mb_dtype d) { return d == MB_RING128 ? 16 : 8; }
+static inline bool mb_is_ring(mb_dtype d) { return d == MB_RING64 || d == MB_RING128; }
+int mb_tensor_new(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, mb_tensor **out);
+mb_tensor *mb_tensor_retain(mb_tensor *t);
+bool mb_same_shape(const mb_tensor *a, const mb_tensor *b);
+int mb_scratch(mb_ctx *ctx, int slot, size_t bytes, void **out);
+
+// ---- host-side crypto (blake3.cpp, aes_host.cpp) ----------------------------
+void mb_blake3_session_id(const char *s, size_t len, uint8_t out[16]);
+void mb_blake3_derive_seed(const uint8_t sid[16], const uint8_t sync_key[16], const uint8_t key[16],
+                           uint8_t out[16]);
+void mb_aes_expand(const uint8_t key[16], AesKey *out);
+void mb_aes_encrypt_host(const AesKey *k, const uint8_t in[16], uint8_t out[16]);
+int mb_entropy16(mb_ctx *ctx, uint8_t out[16]);  // takes ctx->mu
+
+// ---- kernel launchers (elementwise.cu, sample.cu, bits.cu, gemm_*.cu, rep.cu)
+enum EwOp { EW_ADD = 0, EW_SUB = 1, EW_MUL = 2, EW_AND = 3, EW_XOR = 4, EW_OR = 5 };
+
+// Binary op with ndarray co-broadcasting: strides in elements, 0 for broadcast axes.
+int k_ew_binary(mb_ctx *ctx, EwOp op, const mb_tensor *x, const mb_tensor *y, mb_tensor *out);
+int k_ew_neg(mb_ctx *ctx, const mb_tensor *x, mb_tensor *out);
+int k_ew_shift(mb_ctx *ctx, bool left, unsigned amount, const mb_tensor *x, mb_tensor *out);
+int k_fill(mb_ctx *ctx, mb_tensor *out, uint64_t lo, uint64_t hi);
+int k_broadcast(mb_ctx *ctx, const mb_tensor *x, mb_tensor *out);
+int k_sum_axis(mb_ctx *ctx, const mb_tensor *x, int64_t outer, int64_t len, int64_t inner, mb_tensor *out);
+int k_fixed_encode(mb_ctx *ctx, const mb_tensor *x, double scale, mb_tensor *out);
+int k_fixed_decode(mb_ctx *ctx, const mb_tensor *x, double scale, mb_tensor *out);
+
+int k_sample(mb_ctx *ctx, const AesKey &key, mb_tensor *out, bool bits_as_ring);
+
+int k_bit_decompose(mb_ctx *ctx, const mb_tensor *x, mb_tensor *out);
+int k_bit_extract(mb_ctx *ctx, unsigned bit_idx, const mb_tensor *x, mb_tensor *out);
+int k_ring_inject(mb_ctx *ctx, unsigned bit_idx, const mb_tensor *bits, mb_tensor *out);
+int k_bit_shift_copy(mb_ctx *ctx, const mb_tensor *x, int64_t src_bit, int64_t dst_bit, int64_t nbits,
+                     mb_tensor *out);  // out must be zero-filled where not covered
+int k_bit_not(mb_ctx *ctx, const mb_tensor *x, mb_tensor *out);
+
+// Ring GEMM C[M,N] (+)= A[M,K] * B[K,N] mod 2^k on raw device pointers.
+int k_gemm_imad(mb_ctx *ctx, mb_dtype dtype, const void *A, const void *B, void *C, int64_t M, int64_t K,
+                int64_t N, bool accumulate);
+bool k_gemm_limb_supported(mb_dtype dtype, int64_t M, int64_t K, int64_t N);
+// C = sum_t A_t * B_t for nterms (1 or 2) operand pairs, optional fused epilogue.
+struct GemmTerm { const void *A; const void *B0; const void *B1; };  // B = B0 (+ B1 if non-null)
+int k_gemm_limb(mb_ctx *ctx, mb_dtype dtype, const GemmTerm *terms, int nterms, void *C, int64_t M,
+                int64_t K, int64_t N);
+
+// Fused replicated kernels (rep.cu)
+int k_rep_share(mb_ctx *ctx, const AesKey &key, int owner, const mb_tensor *x, mb_tensor *o0, mb_tensor *o1,
+                mb_tensor *o2);
+int k_rep_share_outsider(mb_ctx *ctx, const AesKey &k0, const AesKey &k1, const mb_tensor *x, mb_tensor *o0,
+                         mb_tensor *o1, mb_tensor *o2);
+int k_reveal3(mb_ctx *ctx, const mb_tensor *a, const mb_tensor *b, const mb_tensor *c, mb_tensor *out);
+// z_i = x_i*y_i + x_i*y_{i+1} + x_{i+1}*y_i + PRF(s_i) - PRF(s_{i+1})
+int k_rep_mul(mb_ctx *ctx, const AesKey seeds[3], const mb_rep *x, const mb_rep *y, mb_tensor *z[3]);
+// z_i = v_i + PRF(s_i) - PRF(s_{i+1})  (v_i may alias z_i)
+int k_add_zero_share(mb_ctx *ctx, const AesKey seeds[3], mb_tensor *v[3], mb_tensor *z[3]);
+// seeds: r, r0, rtop0, rmsb0, y0, y1
+int k_rep_trunc_pr(mb_ctx *ctx, const AesKey seeds[6], unsigned amount, const mb_rep *x, mb_tensor *z[3]);

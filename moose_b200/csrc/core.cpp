@@ -1,0 +1,242 @@
+// Context, tensor handles, error reporting.
+#include "common.h"
+
+static thread_local std::string g_last_error;
+
+void mb_set_error(const mb_ctx *, const std::string &msg) { g_last_error = msg; }
+int mb_fail(const mb_ctx *ctx, int code, const std::string &msg) {
+  mb_set_error(ctx, msg);
+  return code;
+}
+
+extern "C" const char *mb_last_error(const mb_ctx *) { return g_last_error.c_str(); }
+
+extern "C" int mb_ctx_create(int device, mb_ctx **out) {
+  if (!out) return mb_fail(nullptr, MB_ERR_INVALID_ARGUMENT, "mb_ctx_create: out is NULL");
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0)
+    return mb_fail(nullptr, MB_ERR_NO_DEVICE,
+                   std::string("mb_ctx_create: no CUDA device (libmoose_b200 has no CPU path): ") +
+                       cudaGetErrorString(e));
+  if (device < 0 || device >= n) return mb_fail(nullptr, MB_ERR_INVALID_ARGUMENT, "mb_ctx_create: bad device index");
+  mb_ctx *ctx = new mb_ctx();
+  ctx->device = device;
+  ctx->deterministic = false;
+  ctx->entropy_counter = 0;
+  ctx->have_setup = false;
+  ctx->gemm_mode = 0;
+  ctx->launches = 0;
+  memset(ctx->scratch, 0, sizeof(ctx->scratch));
+  memset(ctx->scratch_bytes, 0, sizeof(ctx->scratch_bytes));
+  MB_CUDA(ctx, cudaSetDevice(device));
+  MB_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  MB_CUDA(ctx, cudaEventCreate(&ctx->ev0));
+  MB_CUDA(ctx, cudaEventCreate(&ctx->ev1));
+  MB_CUDA(ctx, cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device));
+  // keep freed blocks in the stream-ordered pool (tensors are allocated per op, like the reference)
+  cudaMemPool_t pool;
+  if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+    uint64_t thresh = UINT64_MAX;
+    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thresh);
+  }
+  // default session id: SessionId::try_from("b200") -- callers normally set their own
+  mb_blake3_session_id("b200", 4, ctx->sid);
+  *out = ctx;
+  return MB_OK;
+}
+
+extern "C" int mb_ctx_destroy(mb_ctx *ctx) {
+  if (!ctx) return MB_OK;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  for (int i = 0; i < 4; i++)
+    if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
+  cudaEventDestroy(ctx->ev0);
+  cudaEventDestroy(ctx->ev1);
+  cudaStreamDestroy(ctx->stream);
+  delete ctx;
+  return MB_OK;
+}
+
+extern "C" int mb_ctx_set_session(mb_ctx *ctx, const char *logical_id) {
+  if (!ctx || !logical_id) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_set_session: NULL argument");
+  size_t len = strlen(logical_id);
+  if (len > 1024) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_set_session: id longer than 1024 bytes");
+  std::lock_guard<std::mutex> lock(ctx->mu);
+  mb_blake3_session_id(logical_id, len, ctx->sid);
+  return MB_OK;
+}
+extern "C" int mb_ctx_set_session_raw(mb_ctx *ctx, const uint8_t sid[16]) {
+  if (!ctx || !sid) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_set_session_raw: NULL argument");
+  std::lock_guard<std::mutex> lock(ctx->mu);
+  memcpy(ctx->sid, sid, 16);
+  return MB_OK;
+}
+extern "C" int mb_ctx_get_session_raw(const mb_ctx *ctx, uint8_t sid[16]) {
+  if (!ctx || !sid) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_get_session_raw: NULL argument");
+  memcpy(sid, ctx->sid, 16);
+  return MB_OK;
+}
+extern "C" int mb_ctx_set_entropy_key(mb_ctx *ctx, const uint8_t key[16]) {
+  if (!ctx || !key) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_set_entropy_key: NULL argument");
+  std::lock_guard<std::mutex> lock(ctx->mu);
+  memcpy(ctx->entropy_key, key, 16);
+  ctx->deterministic = true;
+  ctx->entropy_counter = 0;
+  ctx->have_setup = false;
+  return MB_OK;
+}
+extern "C" int mb_ctx_sync(mb_ctx *ctx) {
+  if (!ctx) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_sync: NULL ctx");
+  MB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return MB_OK;
+}
+extern "C" void *mb_ctx_stream(mb_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
+extern "C" int mb_ctx_timer_start(mb_ctx *ctx) {
+  MB_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  return MB_OK;
+}
+extern "C" int mb_ctx_timer_stop(mb_ctx *ctx, float *ms) {
+  MB_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  MB_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
+  MB_CUDA(ctx, cudaEventElapsedTime(ms, ctx->ev0, ctx->ev1));
+  return MB_OK;
+}
+extern "C" uint64_t mb_ctx_launch_count(const mb_ctx *ctx) { return ctx ? ctx->launches.load() : 0; }
+extern "C" int mb_ctx_set_gemm_mode(mb_ctx *ctx, int mode) {
+  if (!ctx || mode < 0 || mode > 2) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_set_gemm_mode: bad mode");
+  ctx->gemm_mode = mode;
+  return MB_OK;
+}
+
+int mb_scratch(mb_ctx *ctx, int slot, size_t bytes, void **out) {
+  if (ctx->scratch_bytes[slot] < bytes) {
+    if (ctx->scratch[slot]) {
+      MB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+      MB_CUDA(ctx, cudaFree(ctx->scratch[slot]));
+      ctx->scratch[slot] = nullptr;
+      ctx->scratch_bytes[slot] = 0;
+    }
+    MB_CUDA(ctx, cudaMalloc(&ctx->scratch[slot], bytes));
+    ctx->scratch_bytes[slot] = bytes;
+  }
+  *out = ctx->scratch[slot];
+  return MB_OK;
+}
+
+// ---- tensors ------------------------------------------------------------------
+
+int mb_tensor_new(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, mb_tensor **out) {
+  if (!ctx || !out) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "tensor: NULL argument");
+  if (rank < 0 || rank > MB_MAX_RANK) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "tensor: rank out of range");
+  if (dtype != MB_RING64 && dtype != MB_RING128 && dtype != MB_BIT && dtype != MB_FLOAT64)
+    return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "tensor: bad dtype");
+  int64_t numel = 1;
+  for (int i = 0; i < rank; i++) {
+    if (shape[i] < 0) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "tensor: negative dimension");
+    numel *= shape[i];
+  }
+  mb_tensor *t = new mb_tensor();
+  t->dtype = dtype;
+  t->rank = rank;
+  for (int i = 0; i < MB_MAX_RANK; i++) t->shape[i] = i < rank ? shape[i] : 1;
+  t->numel = numel;
+  t->nbytes = dtype == MB_BIT ? (size_t)(numel + 7) / 8 : (size_t)numel * (dtype == MB_RING128 ? 16 : 8);
+  t->alloc_bytes = ((t->nbytes + 15) / 16) * 16;
+  if (t->alloc_bytes == 0) t->alloc_bytes = 16;
+  t->refs = 1;
+  t->device = ctx->device;
+  t->dptr = nullptr;
+  cudaError_t e = cudaMallocAsync(&t->dptr, t->alloc_bytes, ctx->stream);
+  if (e != cudaSuccess) {
+    delete t;
+    return mb_fail(ctx, MB_ERR_CUDA, std::string("cudaMallocAsync: ") + cudaGetErrorString(e));
+  }
+  if (dtype == MB_BIT) {
+    // packed-bit invariant: bits beyond numel (and padding bytes) are zero
+    e = cudaMemsetAsync((char *)t->dptr + (t->alloc_bytes - 16), 0, 16, ctx->stream);
+    if (e != cudaSuccess) {
+      cudaFreeAsync(t->dptr, ctx->stream);
+      delete t;
+      return mb_fail(ctx, MB_ERR_CUDA, std::string("cudaMemsetAsync: ") + cudaGetErrorString(e));
+    }
+  }
+  *out = t;
+  return MB_OK;
+}
+
+mb_tensor *mb_tensor_retain(mb_tensor *t) {
+  t->refs.fetch_add(1);
+  return t;
+}
+
+bool mb_same_shape(const mb_tensor *a, const mb_tensor *b) {
+  if (a->rank != b->rank) return false;
+  for (int i = 0; i < a->rank; i++)
+    if (a->shape[i] != b->shape[i]) return false;
+  return true;
+}
+
+extern "C" int mb_tensor_alloc(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, mb_tensor **out) {
+  return mb_tensor_new(ctx, dtype, rank, shape, out);
+}
+
+extern "C" int mb_tensor_from_host(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, const void *host_data,
+                                   mb_tensor **out) {
+  if (!host_data && rank >= 0) {
+    int64_t n = 1;
+    for (int i = 0; i < rank; i++) n *= shape[i];
+    if (n > 0) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_tensor_from_host: NULL data");
+  }
+  mb_tensor *t = nullptr;
+  MB_CHECK(mb_tensor_new(ctx, dtype, rank, shape, &t));
+  if (t->nbytes) {
+    cudaError_t e = cudaMemcpyAsync(t->dptr, host_data, t->nbytes, cudaMemcpyHostToDevice, ctx->stream);
+    if (e != cudaSuccess) {
+      mb_tensor_free(ctx, t);
+      return mb_fail(ctx, MB_ERR_CUDA, std::string("cudaMemcpyAsync H2D: ") + cudaGetErrorString(e));
+    }
+    // pageable host memory: the copy has been staged when the call returns only after a sync
+    MB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  }
+  *out = t;
+  return MB_OK;
+}
+
+extern "C" int mb_tensor_to_host(mb_ctx *ctx, const mb_tensor *t, void *host_out, size_t nbytes) {
+  if (!ctx || !t || (!host_out && nbytes)) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_tensor_to_host: NULL");
+  if (nbytes != t->nbytes) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_tensor_to_host: size mismatch");
+  if (nbytes) MB_CUDA(ctx, cudaMemcpyAsync(host_out, t->dptr, nbytes, cudaMemcpyDeviceToHost, ctx->stream));
+  MB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return MB_OK;
+}
+
+extern "C" int mb_tensor_free(mb_ctx *ctx, mb_tensor *t) {
+  if (!t) return MB_OK;
+  if (t->refs.fetch_sub(1) == 1) {
+    if (t->dptr) cudaFreeAsync(t->dptr, ctx ? ctx->stream : 0);
+    delete t;
+  }
+  return MB_OK;
+}
+
+extern "C" mb_dtype mb_tensor_dtype(const mb_tensor *t) { return t->dtype; }
+extern "C" int mb_tensor_rank(const mb_tensor *t) { return t->rank; }
+extern "C" const int64_t *mb_tensor_shape(const mb_tensor *t) { return t->shape; }
+extern "C" int64_t mb_tensor_numel(const mb_tensor *t) { return t->numel; }
+extern "C" size_t mb_tensor_nbytes(const mb_tensor *t) { return t->nbytes; }
+extern "C" void *mb_tensor_device_ptr(const mb_tensor *t) { return t->dptr; }
+
+extern "C" int mb_reshape(mb_ctx *ctx, const mb_tensor *x, int rank, const int64_t *shape, mb_tensor **out) {
+  if (!x) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_reshape: NULL");
+  int64_t n = 1;
+  for (int i = 0; i < rank; i++) n *= shape[i];
+  if (n != x->numel) return mb_fail(ctx, MB_ERR_KERNEL, "mb_reshape: element count differs");
+  mb_tensor *t = nullptr;
+  MB_CHECK(mb_tensor_new(ctx, x->dtype, rank, shape, &t));
+  if (x->nbytes)
+    MB_CUDA(ctx, cudaMemcpyAsync(t->dptr, x->dptr, x->nbytes, cudaMemcpyDeviceToDevice, ctx->stream));
+  *out = t;
+  return MB_OK;
+}

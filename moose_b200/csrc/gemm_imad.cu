@@ -1,0 +1,143 @@
+// Ring GEMM mod 2^64 / 2^128 on the CUDA cores (64-bit IMAD chains).
+//
+// DotOp::ring_kernel (moose/src/host/ops.rs:1754-1851) for the shapes the int8
+// tensor-pipe kernel (gemm_limb.cu) is the wrong tool for:
+//  * skinny outputs (N <= 32: LogReg [B,513]x[513,2], the last MLP layer
+//    [B,512]x[512,10]) -- these stream A once and are HBM bound;
+//  * small / ragged problems (unit tests, KATs, rank-1 operands).
+// Integer arithmetic mod 2^k is associative and commutative, so the summation
+// order does not affect the result: bit-exact against ndarray's generic dot.
+#include "common.h"
+
+namespace {
+
+constexpr int BM = 64, BN = 64, BK = 16, TPB = 256;
+
+// Tiled kernel: 64x64 output tile per CTA, 4x4 outputs per thread.
+template <typename T>
+__global__ void __launch_bounds__(TPB) gemm_tiled_kernel(const T *__restrict__ A, const T *__restrict__ B, T *__restrict__ C,
+                                                         int64_t M, int64_t K, int64_t N, bool accumulate) {
+  __shared__ T sA[BK][BM + 1];
+  __shared__ T sB[BK][BN];
+  const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;
+  const int64_t m0 = (int64_t)blockIdx.y * BM, n0 = (int64_t)blockIdx.x * BN;
+  T acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 4; j++) acc[i][j] = 0;
+
+  for (int64_t k0 = 0; k0 < K; k0 += BK) {
+    // A tile: 64 rows x 16 k  (k contiguous in memory)
+    for (int idx = threadIdx.x; idx < BM * BK; idx += TPB) {
+      int r = idx / BK, kk = idx % BK;
+      int64_t gm = m0 + r, gk = k0 + kk;
+      sA[kk][r] = (gm < M && gk < K) ? A[gm * K + gk] : (T)0;
+    }
+    // B tile: 16 k x 64 cols (n contiguous)
+    for (int idx = threadIdx.x; idx < BK * BN; idx += TPB) {
+      int kk = idx / BN, c = idx % BN;
+      int64_t gk = k0 + kk, gn = n0 + c;
+      sB[kk][c] = (gk < K && gn < N) ? B[gk * N + gn] : (T)0;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < BK; kk++) {
+      T a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; i++) a[i] = sA[kk][ty * 4 + i];
+#pragma unroll
+      for (int j = 0; j < 4; j++) b[j] = sB[kk][tx + 16 * j];
+#pragma unroll
+      for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j] += a[i] * b[j];
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    int64_t gm = m0 + ty * 4 + i;
+    if (gm >= M) continue;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      int64_t gn = n0 + tx + 16 * j;
+      if (gn < N) {
+        T v = acc[i][j];
+        if (accumulate) v += C[gm * N + gn];
+        C[gm * N + gn] = v;
+      }
+    }
+  }
+}
+
+// Skinny kernel (N <= 32): one warp per output row, lanes stride over K so the A
+// row is read with coalesced 8/16-byte loads exactly once; B (K x N, small) stays
+// in L1/L2.  Columns are processed in chunks of NC to bound registers.
+template <typename T, int NC>
+__global__ void __launch_bounds__(TPB) gemm_skinny_kernel(const T *__restrict__ A, const T *__restrict__ B, T *__restrict__ C,
+                                                          int64_t M, int64_t K, int64_t N, bool accumulate) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * TPB + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * TPB) >> 5;
+  for (int64_t m = warp; m < M; m += nwarps) {
+    const T *a = A + m * K;
+    for (int64_t n0 = 0; n0 < N; n0 += NC) {
+      T acc[NC];
+#pragma unroll
+      for (int j = 0; j < NC; j++) acc[j] = 0;
+      for (int64_t k = lane; k < K; k += 32) {
+        T av = a[k];
+#pragma unroll
+        for (int j = 0; j < NC; j++)
+          if (n0 + j < N) acc[j] += av * B[k * N + n0 + j];
+      }
+#pragma unroll
+      for (int j = 0; j < NC; j++) {
+        T v = acc[j];
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+          uint64_t lo = __shfl_xor_sync(0xffffffffu, (uint64_t)v, off);
+          if (sizeof(T) == 16) {
+            uint64_t hi = __shfl_xor_sync(0xffffffffu, (uint64_t)((u128)v >> 64), off);
+            v += (T)(((u128)hi << 64) | lo);
+          } else {
+            v += (T)lo;
+          }
+        }
+        if (lane == 0 && n0 + j < N) {
+          if (accumulate) v += C[m * N + n0 + j];
+          C[m * N + n0 + j] = v;
+        }
+      }
+    }
+  }
+}
+
+}  // namespace
+
+int k_gemm_imad(mb_ctx *ctx, mb_dtype dtype, const void *A, const void *B, void *C, int64_t M, int64_t K, int64_t N,
+                bool accumulate) {
+  if (M == 0 || N == 0) return MB_OK;
+  if (K == 0) {
+    if (!accumulate) MB_CUDA(ctx, cudaMemsetAsync(C, 0, (size_t)(M * N) * (dtype == MB_RING128 ? 16 : 8), ctx->stream));
+    return MB_OK;
+  }
+  if (N <= 32 && M >= 64) {
+    int64_t warps = M;
+    int g = (int)std::min<int64_t>((warps * 32 + TPB - 1) / TPB, (int64_t)ctx->sm_count * 16);
+    if (dtype == MB_RING128)
+      gemm_skinny_kernel<u128, 2><<<g, TPB, 0, ctx->stream>>>((const u128 *)A, (const u128 *)B, (u128 *)C, M, K, N, accumulate);
+    else
+      gemm_skinny_kernel<uint64_t, 4><<<g, TPB, 0, ctx->stream>>>((const uint64_t *)A, (const uint64_t *)B, (uint64_t *)C, M, K, N, accumulate);
+    MB_LAUNCH_CHECK(ctx);
+    return MB_OK;
+  }
+  dim3 grid((unsigned)((N + BN - 1) / BN), (unsigned)((M + BM - 1) / BM));
+  if (dtype == MB_RING128)
+    gemm_tiled_kernel<u128><<<grid, TPB, 0, ctx->stream>>>((const u128 *)A, (const u128 *)B, (u128 *)C, M, K, N, accumulate);
+  else
+    gemm_tiled_kernel<uint64_t><<<grid, TPB, 0, ctx->stream>>>((const uint64_t *)A, (const uint64_t *)B, (uint64_t *)C, M, K, N, accumulate);
+  MB_LAUNCH_CHECK(ctx);
+  return MB_OK;
+}

@@ -1,0 +1,572 @@
+// C ABI: replicated-placement protocols (moose/src/replicated/*.rs,
+// moose/src/additive/*.rs).  The host side only derives keys / seeds (16-byte
+// values, in the reference's entropy order) and launches fused kernels.
+#include "common.h"
+
+int mb_dot_dims(const mb_ctx *ctx, const mb_tensor *x, const mb_tensor *y, int64_t *M, int64_t *K, int64_t *N, int *orank,
+                int64_t *oshape);
+
+#define MB_ENTER(ctx, what)                                                              \
+  do {                                                                                   \
+    if (!(ctx)) return mb_fail(nullptr, MB_ERR_INVALID_ARGUMENT, what ": NULL context"); \
+    MB_CUDA((ctx), cudaSetDevice((ctx)->device));                                        \
+  } while (0)
+#define MB_REQUIRE(ctx, cond, code, msg)               \
+  do {                                                 \
+    if (!(cond)) return mb_fail((ctx), (code), (msg)); \
+  } while (0)
+
+namespace {
+
+// Owning tensor handle for temporaries.
+struct Tmp {
+  mb_ctx *ctx;
+  mb_tensor *p;
+  explicit Tmp(mb_ctx *c) : ctx(c), p(nullptr) {}
+  ~Tmp() { if (p) mb_tensor_free(ctx, p); }
+  Tmp(const Tmp &) = delete;
+  Tmp &operator=(const Tmp &) = delete;
+  mb_tensor *release() { mb_tensor *t = p; p = nullptr; return t; }
+  int alloc_like(const mb_tensor *x) { return mb_tensor_new(ctx, x->dtype, x->rank, x->shape, &p); }
+  int alloc(mb_dtype d, int rank, const int64_t *shape) { return mb_tensor_new(ctx, d, rank, shape, &p); }
+};
+
+struct RepTmp {
+  mb_ctx *ctx;
+  mb_rep *p;
+  explicit RepTmp(mb_ctx *c) : ctx(c), p(nullptr) {}
+  ~RepTmp() { if (p) mb_rep_free(ctx, p); }
+  RepTmp(const RepTmp &) = delete;
+  RepTmp &operator=(const RepTmp &) = delete;
+  mb_rep *release() { mb_rep *t = p; p = nullptr; return t; }
+};
+
+mb_rep *rep_make(mb_tensor *a, mb_tensor *b, mb_tensor *c) {
+  mb_rep *r = new mb_rep();
+  r->s[0] = a; r->s[1] = b; r->s[2] = c;
+  return r;
+}
+
+int rep_alloc_like(mb_ctx *ctx, const mb_tensor *like, mb_rep **out) {
+  Tmp a(ctx), b(ctx), c(ctx);
+  MB_CHECK(a.alloc_like(like));
+  MB_CHECK(b.alloc_like(like));
+  MB_CHECK(c.alloc_like(like));
+  *out = rep_make(a.release(), b.release(), c.release());
+  return MB_OK;
+}
+
+int rep_alloc(mb_ctx *ctx, mb_dtype d, int rank, const int64_t *shape, mb_rep **out) {
+  Tmp a(ctx), b(ctx), c(ctx);
+  MB_CHECK(a.alloc(d, rank, shape));
+  MB_CHECK(b.alloc(d, rank, shape));
+  MB_CHECK(c.alloc(d, rank, shape));
+  *out = rep_make(a.release(), b.release(), c.release());
+  return MB_OK;
+}
+
+bool rep_valid(const mb_rep *x) { return x && x->s[0] && x->s[1] && x->s[2]; }
+
+int ensure_setup(mb_ctx *ctx) {
+  // RepSetup: k00, k11, k22 generated in this order (replicated/setup.rs:46-48);
+  // k10 = k11, k21 = k22, k02 = k00 are relabelled copies (:50-52).
+  bool need;
+  {
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    need = !ctx->have_setup;
+  }
+  if (need) {
+    uint8_t k[3][16];
+    for (int i = 0; i < 3; i++) MB_CHECK(mb_entropy16(ctx, k[i]));
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    memcpy(ctx->setup_keys, k, sizeof(k));
+    ctx->have_setup = true;
+  }
+  return MB_OK;
+}
+
+void seed_to_aes(mb_ctx *ctx, const uint8_t sync_key[16], const uint8_t key[16], AesKey *out) {
+  uint8_t seed[16];
+  mb_blake3_derive_seed(ctx->sid, sync_key, key, seed);
+  mb_aes_expand(seed, out);
+}
+
+// SeedsGen::gen_seeds (replicated/zero_share.rs:129-156): s_i = DeriveSeed(k_i, sync_i);
+// s10 == s11, s21 == s22, s02 == s00 because the keys are copies.
+int gen_zero_seeds(mb_ctx *ctx, AesKey seeds[3]) {
+  MB_CHECK(ensure_setup(ctx));
+  uint8_t sync[3][16];
+  for (int i = 0; i < 3; i++) MB_CHECK(mb_entropy16(ctx, sync[i]));
+  for (int i = 0; i < 3; i++) seed_to_aes(ctx, sync[i], ctx->setup_keys[i], &seeds[i]);
+  return MB_OK;
+}
+
+int sharewise_binary(mb_ctx *ctx, EwOp op, const mb_rep *x, const mb_rep *y, mb_rep **out, const char *name) {
+  MB_REQUIRE(ctx, rep_valid(x) && rep_valid(y) && out, MB_ERR_INVALID_ARGUMENT, std::string(name) + ": NULL argument");
+  MB_REQUIRE(ctx, x->s[0]->dtype == y->s[0]->dtype, MB_ERR_TYPE_MISMATCH, std::string(name) + ": dtypes differ");
+  mb_tensor *z[3] = {nullptr, nullptr, nullptr};
+  for (int i = 0; i < 3; i++) {
+    int rc = op == EW_ADD ? mb_add(ctx, x->s[i], y->s[i], &z[i]) : op == EW_SUB ? mb_sub(ctx, x->s[i], y->s[i], &z[i])
+                                                                                 : mb_mul(ctx, x->s[i], y->s[i], &z[i]);
+    if (rc != MB_OK) {
+      for (int j = 0; j < i; j++) mb_tensor_free(ctx, z[j]);
+      return rc;
+    }
+  }
+  *out = rep_make(z[0], z[1], z[2]);
+  return MB_OK;
+}
+
+}  // namespace
+
+// ---- handles ------------------------------------------------------------------------
+
+extern "C" int mb_rep_from_shares(mb_ctx *ctx, const mb_tensor *x0, const mb_tensor *x1, const mb_tensor *x2, mb_rep **out) {
+  MB_REQUIRE(ctx, x0 && x1 && x2 && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_from_shares: NULL argument");
+  MB_REQUIRE(ctx, x0->dtype == x1->dtype && x1->dtype == x2->dtype && mb_same_shape(x0, x1) && mb_same_shape(x1, x2),
+             MB_ERR_TYPE_MISMATCH, "mb_rep_from_shares: shares differ in dtype or shape");
+  *out = rep_make(mb_tensor_retain((mb_tensor *)x0), mb_tensor_retain((mb_tensor *)x1), mb_tensor_retain((mb_tensor *)x2));
+  return MB_OK;
+}
+extern "C" const mb_tensor *mb_rep_share_tensor(const mb_rep *x, int i) { return (x && i >= 0 && i < 3) ? x->s[i] : nullptr; }
+extern "C" int mb_rep_free(mb_ctx *ctx, mb_rep *x) {
+  if (!x) return MB_OK;
+  for (int i = 0; i < 3; i++) mb_tensor_free(ctx, x->s[i]);
+  delete x;
+  return MB_OK;
+}
+
+extern "C" int mb_rep_setup(mb_ctx *ctx) {
+  MB_ENTER(ctx, "mb_rep_setup");
+  return ensure_setup(ctx);
+}
+
+// ---- share / reveal -------------------------------------------------------------------
+
+extern "C" int mb_rep_share(mb_ctx *ctx, const mb_tensor *x, int owner, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_share");
+  MB_REQUIRE(ctx, x && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_share: NULL argument");
+  MB_REQUIRE(ctx, x->dtype != MB_FLOAT64, MB_ERR_TYPE_MISMATCH, "mb_rep_share: float tensors must be fixed-point encoded first");
+  MB_REQUIRE(ctx, owner >= 0 && owner <= 3, MB_ERR_INVALID_ARGUMENT, "mb_rep_share: owner must be 0..3");
+  MB_CHECK(ensure_setup(ctx));  // convert.rs:67: sess.setup(plc) precedes SyncKey::random()
+  RepTmp r(ctx);
+  MB_CHECK(rep_alloc_like(ctx, x, &r.p));
+  if (owner < 3) {
+    uint8_t sync[16];
+    MB_CHECK(mb_entropy16(ctx, sync));
+    AesKey k;
+    seed_to_aes(ctx, sync, ctx->setup_keys[owner], &k);
+    MB_CHECK(k_rep_share(ctx, k, owner, x, r.p->s[0], r.p->s[1], r.p->s[2]));
+  } else {
+    uint8_t sync0[16], sync1[16];
+    MB_CHECK(mb_entropy16(ctx, sync0));
+    MB_CHECK(mb_entropy16(ctx, sync1));
+    AesKey k0, k1;
+    seed_to_aes(ctx, sync0, ctx->setup_keys[0], &k0);  // seed00 (= seed02)
+    seed_to_aes(ctx, sync1, ctx->setup_keys[1], &k1);  // seed11 (= seed10)
+    MB_CHECK(k_rep_share_outsider(ctx, k0, k1, x, r.p->s[0], r.p->s[1], r.p->s[2]));
+  }
+  *out = r.release();
+  return MB_OK;
+}
+
+extern "C" int mb_rep_reveal(mb_ctx *ctx, const mb_rep *x, int receiver, mb_tensor **out) {
+  MB_ENTER(ctx, "mb_rep_reveal");
+  MB_REQUIRE(ctx, rep_valid(x) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_reveal: NULL argument");
+  (void)receiver;  // every receiver adds the same three distinct shares (convert.rs:295-311)
+  Tmp t(ctx);
+  MB_CHECK(t.alloc_like(x->s[0]));
+  MB_CHECK(k_reveal3(ctx, x->s[0], x->s[1], x->s[2], t.p));
+  *out = t.release();
+  return MB_OK;
+}
+
+// ---- linear ops -----------------------------------------------------------------------
+
+extern "C" int mb_rep_add(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_add");
+  return sharewise_binary(ctx, EW_ADD, x, y, out, "mb_rep_add");
+}
+extern "C" int mb_rep_sub(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_sub");
+  return sharewise_binary(ctx, EW_SUB, x, y, out, "mb_rep_sub");
+}
+
+extern "C" int mb_rep_neg(mb_ctx *ctx, const mb_rep *x, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_neg");
+  MB_REQUIRE(ctx, rep_valid(x) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_neg: NULL argument");
+  mb_tensor *z[3] = {nullptr, nullptr, nullptr};
+  for (int i = 0; i < 3; i++) {
+    int rc;
+    // NegOp::rep_bit_kernel flips only x00 / x02 = share 0 (arith.rs:525-558)
+    if (x->s[0]->dtype == MB_BIT && i != 0) rc = mb_reshape(ctx, x->s[i], x->s[i]->rank, x->s[i]->shape, &z[i]);
+    else rc = mb_neg(ctx, x->s[i], &z[i]);
+    if (rc != MB_OK) {
+      for (int j = 0; j < i; j++) mb_tensor_free(ctx, z[j]);
+      return rc;
+    }
+  }
+  *out = rep_make(z[0], z[1], z[2]);
+  return MB_OK;
+}
+
+extern "C" int mb_rep_shl(mb_ctx *ctx, uint64_t amount, const mb_rep *x, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_shl");
+  MB_REQUIRE(ctx, rep_valid(x) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_shl: NULL argument");
+  mb_tensor *z[3] = {nullptr, nullptr, nullptr};
+  for (int i = 0; i < 3; i++) {
+    int rc = mb_shl(ctx, amount, x->s[i], &z[i]);
+    if (rc != MB_OK) {
+      for (int j = 0; j < i; j++) mb_tensor_free(ctx, z[j]);
+      return rc;
+    }
+  }
+  *out = rep_make(z[0], z[1], z[2]);
+  return MB_OK;
+}
+
+// Mirrored operand: only share 0 (= x00 and x02) sees the public value, the other shares are
+// broadcast to the result shape (arith.rs:81-121, 275-315).
+static int rep_public_linear(mb_ctx *ctx, bool subtract, const mb_rep *x, const mb_tensor *pub, mb_rep **out) {
+  MB_REQUIRE(ctx, rep_valid(x) && pub && out, MB_ERR_INVALID_ARGUMENT, "rep op public: NULL argument");
+  mb_tensor *z[3] = {nullptr, nullptr, nullptr};
+  int rc = subtract ? mb_sub(ctx, x->s[0], pub, &z[0]) : mb_add(ctx, x->s[0], pub, &z[0]);
+  if (rc != MB_OK) return rc;
+  for (int i = 1; i < 3; i++) {
+    rc = mb_broadcast(ctx, x->s[i], z[0]->rank, z[0]->shape, &z[i]);
+    if (rc != MB_OK) {
+      for (int j = 0; j < i; j++) mb_tensor_free(ctx, z[j]);
+      return rc;
+    }
+  }
+  *out = rep_make(z[0], z[1], z[2]);
+  return MB_OK;
+}
+extern "C" int mb_rep_add_public(mb_ctx *ctx, const mb_rep *x, const mb_tensor *pub, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_add_public");
+  return rep_public_linear(ctx, false, x, pub, out);
+}
+extern "C" int mb_rep_sub_public(mb_ctx *ctx, const mb_rep *x, const mb_tensor *pub, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_sub_public");
+  return rep_public_linear(ctx, true, x, pub, out);
+}
+extern "C" int mb_rep_public_sub(mb_ctx *ctx, const mb_tensor *pub, const mb_rep *x, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_public_sub");
+  // SubOp::mir_rep_kernel (arith.rs:230-273): z0 = pub - x0, z1 = -x1, z2 = -x2 (broadcast)
+  MB_REQUIRE(ctx, rep_valid(x) && pub && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_public_sub: NULL argument");
+  mb_tensor *z[3] = {nullptr, nullptr, nullptr};
+  int rc = mb_sub(ctx, pub, x->s[0], &z[0]);
+  if (rc != MB_OK) return rc;
+  for (int i = 1; i < 3; i++) {
+    Tmp n(ctx);
+    rc = mb_neg(ctx, x->s[i], &n.p);
+    if (rc == MB_OK) rc = mb_broadcast(ctx, n.p, z[0]->rank, z[0]->shape, &z[i]);
+    if (rc != MB_OK) {
+      for (int j = 0; j < i; j++) mb_tensor_free(ctx, z[j]);
+      return rc;
+    }
+  }
+  *out = rep_make(z[0], z[1], z[2]);
+  return MB_OK;
+}
+extern "C" int mb_rep_mul_public(mb_ctx *ctx, const mb_rep *x, const mb_tensor *pub, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_mul_public");
+  MB_REQUIRE(ctx, rep_valid(x) && pub && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_mul_public: NULL argument");
+  mb_tensor *z[3] = {nullptr, nullptr, nullptr};
+  for (int i = 0; i < 3; i++) {
+    int rc = mb_mul(ctx, x->s[i], pub, &z[i]);
+    if (rc != MB_OK) {
+      for (int j = 0; j < i; j++) mb_tensor_free(ctx, z[j]);
+      return rc;
+    }
+  }
+  *out = rep_make(z[0], z[1], z[2]);
+  return MB_OK;
+}
+
+// ---- multiplication -------------------------------------------------------------------
+
+extern "C" int mb_rep_mul(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_mul");
+  MB_REQUIRE(ctx, rep_valid(x) && rep_valid(y) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_mul: NULL argument");
+  MB_REQUIRE(ctx, x->s[0]->dtype == y->s[0]->dtype, MB_ERR_TYPE_MISMATCH, "mb_rep_mul: dtypes differ");
+  const mb_rep *xx = x, *yy = y;
+  RepTmp xb(ctx), yb(ctx);
+  if (!mb_same_shape(x->s[0], y->s[0])) {
+    // ndarray co-broadcast of the share products: materialise broadcast operands
+    MB_REQUIRE(ctx, mb_is_ring(x->s[0]->dtype), MB_ERR_KERNEL, "mb_rep_mul: bit operands must have equal shapes");
+    Tmp probe(ctx);
+    MB_CHECK(mb_add(ctx, x->s[0], y->s[0], &probe.p));  // result shape (and validity) of the broadcast
+    mb_tensor *a[3] = {nullptr, nullptr, nullptr}, *b[3] = {nullptr, nullptr, nullptr};
+    int rc = MB_OK;
+    for (int i = 0; i < 3 && rc == MB_OK; i++) rc = mb_broadcast(ctx, x->s[i], probe.p->rank, probe.p->shape, &a[i]);
+    for (int i = 0; i < 3 && rc == MB_OK; i++) rc = mb_broadcast(ctx, y->s[i], probe.p->rank, probe.p->shape, &b[i]);
+    if (rc != MB_OK) {
+      for (int i = 0; i < 3; i++) { mb_tensor_free(ctx, a[i]); mb_tensor_free(ctx, b[i]); }
+      return rc;
+    }
+    xb.p = rep_make(a[0], a[1], a[2]);
+    yb.p = rep_make(b[0], b[1], b[2]);
+    xx = xb.p; yy = yb.p;
+  }
+  RepTmp z(ctx);
+  MB_CHECK(rep_alloc_like(ctx, xx->s[0], &z.p));
+  AesKey seeds[3];
+  MB_CHECK(gen_zero_seeds(ctx, seeds));
+  MB_CHECK(k_rep_mul(ctx, seeds, xx, yy, z.p->s));
+  *out = z.release();
+  return MB_OK;
+}
+
+extern "C" int mb_rep_dot(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_dot");
+  MB_REQUIRE(ctx, rep_valid(x) && rep_valid(y) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_dot: NULL argument");
+  mb_dtype dt = x->s[0]->dtype;
+  MB_REQUIRE(ctx, mb_is_ring(dt) && dt == y->s[0]->dtype, MB_ERR_TYPE_MISMATCH, "mb_rep_dot: needs ring tensors of one width");
+  int64_t M, K, N, oshape[2];
+  int orank;
+  MB_CHECK(mb_dot_dims(ctx, x->s[0], y->s[0], &M, &K, &N, &orank, oshape));
+  RepTmp z(ctx);
+  MB_CHECK(rep_alloc(ctx, dt, orank, oshape, &z.p));
+  bool limb_ok = k_gemm_limb_supported(dt, M, 2 * K, N);
+  MB_REQUIRE(ctx, !(ctx->gemm_mode == 2 && !limb_ok), MB_ERR_KERNEL,
+             "mb_rep_dot: shape not supported by the tensor-pipe GEMM (gemm mode 2)");
+  // v_i = x_i.y_i + x_i.y_{i+1} + x_{i+1}.y_i = x_i.(y_i + y_{i+1}) + x_{i+1}.y_i   (arith.rs:461-469;
+  // identical mod 2^k, one GEMM less per party)
+  for (int i = 0; i < 3; i++) {
+    int j = (i + 1) % 3;
+    if (limb_ok && ctx->gemm_mode != 1) {
+      GemmTerm terms[2] = {{x->s[i]->dptr, y->s[i]->dptr, y->s[j]->dptr}, {x->s[j]->dptr, y->s[i]->dptr, nullptr}};
+      MB_CHECK(k_gemm_limb(ctx, dt, terms, 2, z.p->s[i]->dptr, M, K, N));
+    } else {
+      Tmp ysum(ctx);
+      MB_CHECK(mb_add(ctx, y->s[i], y->s[j], &ysum.p));
+      MB_CHECK(k_gemm_imad(ctx, dt, x->s[i]->dptr, ysum.p->dptr, z.p->s[i]->dptr, M, K, N, false));
+      MB_CHECK(k_gemm_imad(ctx, dt, x->s[j]->dptr, y->s[i]->dptr, z.p->s[i]->dptr, M, K, N, true));
+    }
+  }
+  AesKey seeds[3];
+  MB_CHECK(gen_zero_seeds(ctx, seeds));
+  MB_CHECK(k_add_zero_share(ctx, seeds, z.p->s, z.p->s));
+  *out = z.release();
+  return MB_OK;
+}
+
+// ---- truncation -----------------------------------------------------------------------
+
+extern "C" int mb_rep_trunc_pr(mb_ctx *ctx, uint32_t amount, const mb_rep *x, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_trunc_pr");
+  MB_REQUIRE(ctx, rep_valid(x) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_trunc_pr: NULL argument");
+  mb_dtype dt = x->s[0]->dtype;
+  MB_REQUIRE(ctx, mb_is_ring(dt), MB_ERR_TYPE_MISMATCH, "mb_rep_trunc_pr: needs ring shares");
+  const unsigned k = (dt == MB_RING128 ? 128 : 64) - 1;
+  // trunc.rs:139-140: `k - amount - 1` on usize panics when it underflows
+  MB_REQUIRE(ctx, amount + 1 <= k, MB_ERR_INVALID_ARGUMENT, "mb_rep_trunc_pr: amount too large for the ring");
+  // Entropy order: gen_trunc_mask (trunc.rs:45-63): Sample seed, PrfKeyGen, 3 x SyncKey::random();
+  // adt_to_rep (convert.rs:426-431): 2 x SyncKey::random(), PrfKeyGen.
+  uint8_t seed_r[16], key[16], sync[3][16], sync0[16], sync1[16], key2[16];
+  MB_CHECK(mb_entropy16(ctx, seed_r));
+  MB_CHECK(mb_entropy16(ctx, key));
+  for (int i = 0; i < 3; i++) MB_CHECK(mb_entropy16(ctx, sync[i]));
+  MB_CHECK(mb_entropy16(ctx, sync0));
+  MB_CHECK(mb_entropy16(ctx, sync1));
+  MB_CHECK(mb_entropy16(ctx, key2));
+  AesKey seeds[6];
+  mb_aes_expand(seed_r, &seeds[0]);
+  for (int i = 0; i < 3; i++) seed_to_aes(ctx, sync[i], key, &seeds[1 + i]);  // r, r_top, r_msb shares
+  seed_to_aes(ctx, sync0, key2, &seeds[4]);
+  seed_to_aes(ctx, sync1, key2, &seeds[5]);
+  RepTmp z(ctx);
+  MB_CHECK(rep_alloc_like(ctx, x->s[0], &z.p));
+  MB_CHECK(k_rep_trunc_pr(ctx, seeds, amount, x, z.p->s));
+  *out = z.release();
+  return MB_OK;
+}
+
+// ---- bits -----------------------------------------------------------------------------
+
+extern "C" int mb_rep_index_axis0(mb_ctx *ctx, int64_t index, const mb_rep *x, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_index_axis0");
+  MB_REQUIRE(ctx, rep_valid(x) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_index_axis0: NULL argument");
+  mb_tensor *z[3] = {nullptr, nullptr, nullptr};
+  for (int i = 0; i < 3; i++) {
+    int rc = mb_index_axis0(ctx, index, x->s[i], &z[i]);
+    if (rc != MB_OK) {
+      for (int j = 0; j < i; j++) mb_tensor_free(ctx, z[j]);
+      return rc;
+    }
+  }
+  *out = rep_make(z[0], z[1], z[2]);
+  return MB_OK;
+}
+
+extern "C" int mb_rep_shl_dim(mb_ctx *ctx, uint64_t amount, uint64_t bit_length, const mb_rep *x, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_shl_dim");
+  MB_REQUIRE(ctx, rep_valid(x) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_shl_dim: NULL argument");
+  mb_tensor *z[3] = {nullptr, nullptr, nullptr};
+  for (int i = 0; i < 3; i++) {
+    int rc = mb_shl_dim(ctx, amount, bit_length, x->s[i], &z[i]);
+    if (rc != MB_OK) {
+      for (int j = 0; j < i; j++) mb_tensor_free(ctx, z[j]);
+      return rc;
+    }
+  }
+  *out = rep_make(z[0], z[1], z[2]);
+  return MB_OK;
+}
+
+// BitDecomposeOp::rep_ring_kernel = split (bits.rs:84-134) + Kogge-Stone binary_adder
+// (misc.rs:176-242), composed from the fused share / and / xor kernels.
+extern "C" int mb_rep_bit_decompose(mb_ctx *ctx, const mb_rep *x, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_bit_decompose");
+  MB_REQUIRE(ctx, rep_valid(x) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_bit_decompose: NULL argument");
+  mb_dtype dt = x->s[0]->dtype;
+  MB_REQUIRE(ctx, mb_is_ring(dt), MB_ERR_TYPE_MISMATCH, "mb_rep_bit_decompose: needs ring shares");
+  const unsigned L = dt == MB_RING128 ? 128 : 64;
+  // split: bsl = bits(x0 + x1) shared by player0; bsr = (0, 0, bits(x2))
+  Tmp left(ctx), bsl(ctx), x2b(ctx);
+  MB_CHECK(mb_add(ctx, x->s[0], x->s[1], &left.p));
+  MB_CHECK(mb_bit_decompose(ctx, left.p, &bsl.p));
+  MB_CHECK(mb_bit_decompose(ctx, x->s[2], &x2b.p));
+  RepTmp a(ctx), b(ctx);
+  MB_CHECK(mb_rep_share(ctx, bsl.p, 0, &a.p));
+  {
+    Tmp z0(ctx), z1(ctx);
+    MB_CHECK(mb_fill(ctx, MB_BIT, x2b.p->rank, x2b.p->shape, 0, 0, &z0.p));
+    MB_CHECK(mb_fill(ctx, MB_BIT, x2b.p->rank, x2b.p->shape, 0, 0, &z1.p));
+    b.p = rep_make(z0.release(), z1.release(), x2b.release());
+  }
+  // binary adder
+  RepTmp g(ctx), p_store(ctx), p(ctx);
+  MB_CHECK(mb_rep_mul(ctx, a.p, b.p, &g.p));
+  MB_CHECK(mb_rep_add(ctx, a.p, b.p, &p_store.p));
+  MB_CHECK(mb_rep_from_shares(ctx, p_store.p->s[0], p_store.p->s[1], p_store.p->s[2], &p.p));
+  unsigned log_r = L == 128 ? 7 : 6;
+  for (unsigned i = 0; i < log_r; i++) {
+    RepTmp p1(ctx), g1(ctx), pg(ctx), gn(ctx), pn(ctx);
+    MB_CHECK(mb_rep_shl_dim(ctx, 1ull << i, L, p.p, &p1.p));
+    MB_CHECK(mb_rep_shl_dim(ctx, 1ull << i, L, g.p, &g1.p));
+    MB_CHECK(mb_rep_mul(ctx, p.p, g1.p, &pg.p));
+    MB_CHECK(mb_rep_add(ctx, g.p, pg.p, &gn.p));
+    MB_CHECK(mb_rep_mul(ctx, p.p, p1.p, &pn.p));
+    mb_rep_free(ctx, g.p); g.p = gn.release();
+    mb_rep_free(ctx, p.p); p.p = pn.release();
+  }
+  RepTmp c(ctx);
+  MB_CHECK(mb_rep_shl_dim(ctx, 1, L, g.p, &c.p));
+  return mb_rep_add(ctx, c.p, p_store.p, out);
+}
+
+extern "C" int mb_rep_msb(mb_ctx *ctx, const mb_rep *x, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_msb");
+  MB_REQUIRE(ctx, rep_valid(x) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_msb: NULL argument");
+  RepTmp bits(ctx);
+  MB_CHECK(mb_rep_bit_decompose(ctx, x, &bits.p));
+  int L = x->s[0]->dtype == MB_RING128 ? 128 : 64;
+  return mb_rep_index_axis0(ctx, L - 1, bits.p, out);
+}
+
+// RingInjectOp::rep_kernel (convert.rs:316-390) with gen_dabit (dabit.rs:38-69).
+extern "C" int mb_rep_ring_inject(mb_ctx *ctx, mb_dtype ring, uint64_t bit_idx, const mb_rep *x, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_ring_inject");
+  MB_REQUIRE(ctx, rep_valid(x) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_ring_inject: NULL argument");
+  MB_REQUIRE(ctx, x->s[0]->dtype == MB_BIT && mb_is_ring(ring), MB_ERR_TYPE_MISMATCH, "mb_rep_ring_inject: bit shares -> ring");
+  const mb_tensor *like = x->s[0];
+  // gen_dabit: b = Sample (bits), br = ring_inject(b); key; seed_b, seed_br
+  Tmp b(ctx), br(ctx), b0(ctx), b1(ctx), br0(ctx), br1(ctx);
+  MB_CHECK(mb_sample(ctx, MB_BIT, like->rank, like->shape, -1, &b.p));
+  MB_CHECK(mb_ring_inject(ctx, ring, 0, b.p, &br.p));
+  uint8_t key[16], sync_b[16], sync_br[16], seed_b[16], seed_br[16];
+  MB_CHECK(mb_entropy16(ctx, key));
+  MB_CHECK(mb_entropy16(ctx, sync_b));
+  MB_CHECK(mb_entropy16(ctx, sync_br));
+  mb_blake3_derive_seed(ctx->sid, sync_b, key, seed_b);
+  mb_blake3_derive_seed(ctx->sid, sync_br, key, seed_br);
+  MB_CHECK(mb_sample_seeded(ctx, MB_BIT, like->rank, like->shape, seed_b, -1, &b0.p));
+  MB_CHECK(mb_sub(ctx, b.p, b0.p, &b1.p));
+  MB_CHECK(mb_sample_seeded(ctx, ring, like->rank, like->shape, seed_br, -1, &br0.p));
+  MB_CHECK(mb_sub(ctx, br.p, br0.p, &br1.p));
+  // x_adt = rep_to_adt(x) = [x0 + x1, x2]; c = open(x_adt + b_bin)
+  Tmp xa0(ctx), c0(ctx), c1(ctx), c_open(ctx), c_ring(ctx);
+  MB_CHECK(mb_add(ctx, x->s[0], x->s[1], &xa0.p));
+  MB_CHECK(mb_add(ctx, xa0.p, b0.p, &c0.p));
+  MB_CHECK(mb_add(ctx, x->s[2], b1.p, &c1.p));
+  MB_CHECK(mb_add(ctx, c0.p, c1.p, &c_open.p));
+  MB_CHECK(mb_ring_inject(ctx, ring, 0, c_open.p, &c_ring.p));
+  // x_adt_ring = b_ring + c_ring - 2 b_ring c_ring  (public c_ring lands on share 0)
+  Tmp m0(ctx), m1(ctx), t0(ctx), t0b(ctx), s0(ctx), t1(ctx), s1(ctx), sh0(ctx), sh1(ctx);
+  MB_CHECK(mb_mul(ctx, br0.p, c_ring.p, &m0.p));
+  MB_CHECK(mb_mul(ctx, br1.p, c_ring.p, &m1.p));
+  MB_CHECK(mb_add(ctx, br0.p, c_ring.p, &t0.p));
+  MB_CHECK(mb_sub(ctx, t0.p, m0.p, &t0b.p));
+  MB_CHECK(mb_sub(ctx, t0b.p, m0.p, &s0.p));
+  MB_CHECK(mb_sub(ctx, br1.p, m1.p, &t1.p));
+  MB_CHECK(mb_sub(ctx, t1.p, m1.p, &s1.p));
+  MB_CHECK(mb_shl(ctx, bit_idx, s0.p, &sh0.p));
+  MB_CHECK(mb_shl(ctx, bit_idx, s1.p, &sh1.p));
+  // adt_to_rep (convert.rs:426-447,480-484)
+  uint8_t sync0[16], sync1[16], key2[16], seed1[16], seed2[16];
+  MB_CHECK(mb_entropy16(ctx, sync0));
+  MB_CHECK(mb_entropy16(ctx, sync1));
+  MB_CHECK(mb_entropy16(ctx, key2));
+  mb_blake3_derive_seed(ctx->sid, sync0, key2, seed1);
+  mb_blake3_derive_seed(ctx->sid, sync1, key2, seed2);
+  Tmp y0(ctx), y1(ctx), d0(ctx), d1(ctx), cc(ctx);
+  MB_CHECK(mb_sample_seeded(ctx, ring, like->rank, like->shape, seed1, -1, &y0.p));
+  MB_CHECK(mb_sample_seeded(ctx, ring, like->rank, like->shape, seed2, -1, &y1.p));
+  MB_CHECK(mb_sub(ctx, sh0.p, y0.p, &d0.p));
+  MB_CHECK(mb_sub(ctx, sh1.p, y1.p, &d1.p));
+  MB_CHECK(mb_add(ctx, d0.p, d1.p, &cc.p));
+  *out = rep_make(y0.release(), cc.release(), y1.release());
+  return MB_OK;
+}
+
+extern "C" int mb_rep_less(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_less");
+  RepTmp d(ctx);
+  MB_CHECK(mb_rep_sub(ctx, x, y, &d.p));
+  return mb_rep_msb(ctx, d.p, out);
+}
+
+extern "C" int mb_rep_mux(mb_ctx *ctx, const mb_rep *s, const mb_rep *x, const mb_rep *y, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_mux");
+  RepTmp d(ctx), m(ctx);
+  MB_CHECK(mb_rep_sub(ctx, x, y, &d.p));
+  MB_CHECK(mb_rep_mul(ctx, s, d.p, &m.p));
+  return mb_rep_add(ctx, m.p, y, out);
+}
+
+extern "C" int mb_rep_maximum(mb_ctx *ctx, const mb_rep *const *xs, int n, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_maximum");
+  MB_REQUIRE(ctx, xs && out && n > 0, MB_ERR_INVALID_ARGUMENT, "maximum op needs a non-empty array of tensors");
+  if (n == 1) {
+    MB_REQUIRE(ctx, rep_valid(xs[0]), MB_ERR_INVALID_ARGUMENT, "mb_rep_maximum: NULL operand");
+    return mb_rep_from_shares(ctx, xs[0]->s[0], xs[0]->s[1], xs[0]->s[2], out);
+  }
+  RepTmp m1(ctx), m2(ctx);
+  MB_CHECK(mb_rep_maximum(ctx, xs, n / 2, &m1.p));
+  MB_CHECK(mb_rep_maximum(ctx, xs + n / 2, n - n / 2, &m2.p));
+  mb_dtype dt = m1.p->s[0]->dtype;
+  RepTmp lesser(ctx), lr(ctx), a(ctx), om(ctx), b(ctx);
+  MB_CHECK(mb_rep_less(ctx, m1.p, m2.p, &lesser.p));
+  MB_CHECK(mb_rep_ring_inject(ctx, dt, 0, lesser.p, &lr.p));
+  Tmp ones(ctx);
+  MB_CHECK(mb_fill(ctx, dt, lr.p->s[0]->rank, lr.p->s[0]->shape, 1, 0, &ones.p));
+  // lesser_ring * max2 + (ones - lesser_ring) * max1, evaluated left to right (softmax.rs:45-49)
+  MB_CHECK(mb_rep_mul(ctx, lr.p, m2.p, &a.p));
+  MB_CHECK(mb_rep_public_sub(ctx, ones.p, lr.p, &om.p));
+  MB_CHECK(mb_rep_mul(ctx, om.p, m1.p, &b.p));
+  return mb_rep_add(ctx, a.p, b.p, out);
+}
+
+extern "C" int mb_rep_relu(mb_ctx *ctx, const mb_rep *x, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_relu");
+  MB_REQUIRE(ctx, rep_valid(x) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_relu: NULL argument");
+  mb_dtype dt = x->s[0]->dtype;
+  RepTmp msb(ctx), sign(ctx), zeros(ctx);
+  MB_CHECK(mb_rep_msb(ctx, x, &msb.p));
+  MB_CHECK(mb_rep_ring_inject(ctx, dt, 0, msb.p, &sign.p));
+  MB_CHECK(rep_alloc_like(ctx, x->s[0], &zeros.p));
+  for (int i = 0; i < 3; i++) MB_CHECK(k_fill(ctx, zeros.p->s[i], 0, 0));
+  return mb_rep_mux(ctx, sign.p, zeros.p, x, out);
+}

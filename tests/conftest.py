@@ -4,28 +4,15 @@ import sys
 import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-if ROOT not in sys.path:
-    sys.path.insert(0, ROOT)
+for p in (ROOT, os.path.dirname(os.path.abspath(__file__))):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+from _util import HAS_GPU  # noqa: E402
 
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: test needs a CUDA device (run with -m gpu on a B200)")
-
-
-def _has_gpu() -> bool:
-    try:
-        import ctypes
-        cuda = ctypes.CDLL("libcuda.so.1")
-        if cuda.cuInit(0) != 0:
-            return False
-        n = ctypes.c_int(0)
-        cuda.cuDeviceGetCount(ctypes.byref(n))
-        return n.value > 0
-    except Exception:
-        return False
-
-
-HAS_GPU = _has_gpu()
 
 
 def pytest_collection_modifyitems(config, items):

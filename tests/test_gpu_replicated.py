@@ -1,0 +1,202 @@
+"""GPU parity tests of the fused replicated protocols.  The CUDA library and the oracle are
+given the same session id and entropy key; every replicated result is compared SHARE BY
+SHARE (bit-exact), then revealed and compared with the plaintext expectation the
+reference's own tests use (replicated/mod.rs, additive/trunc.rs)."""
+import numpy as np
+import pytest
+
+import moose_b200 as mb
+from moose_b200 import BIT, RING64, RING128
+from oracle import moose_oracle as mo
+from _util import ENTROPY_KEY, SESSION_ID, rand_ring, same, same_rep, same_ring
+
+pytestmark = pytest.mark.gpu
+DT = {64: RING64, 128: RING128}
+
+
+def pair():
+    return mb.Session(0, SESSION_ID, ENTROPY_KEY), mo.Session(SESSION_ID, ENTROPY_KEY)
+
+
+def signed(vals, bits):
+    return [int(v) - (1 << bits) if int(v) >> (bits - 1) else int(v) for v in vals]
+
+
+@pytest.mark.parametrize("bits", [64, 128])
+@pytest.mark.parametrize("owner", [0, 1, 2, 3])
+def test_share_reveal_parity(bits, owner):
+    g, o = pair()
+    rng = np.random.default_rng(bits + owner)
+    for shape in [(5,), (3, 7), (), (130, 9)]:
+        a = rand_ring(rng, bits, shape)
+        gx = g.share(g.from_host(DT[bits], a), owner)
+        ox = mo.rep_share(o, mo.Ring(bits, a), owner)
+        assert same_rep(gx, ox)
+        for recv in (0, 1, 2):
+            r = g.reveal(gx, recv)
+            assert same_ring(r, mo.rep_reveal(ox, recv))
+            assert np.array_equal(r.to_host(), a)
+    g.close()
+
+
+@pytest.mark.parametrize("bits", [64, 128])
+def test_rep_linear_ops_parity(bits):
+    g, o = pair()
+    rng = np.random.default_rng(bits)
+    a, b, p = rand_ring(rng, bits, (6, 5)), rand_ring(rng, bits, (6, 5)), rand_ring(rng, bits, (5,))
+    gx, gy = g.share(g.from_host(DT[bits], a), 0), g.share(g.from_host(DT[bits], b), 1)
+    ox, oy = mo.rep_share(o, mo.Ring(bits, a), 0), mo.rep_share(o, mo.Ring(bits, b), 1)
+    gp, op = g.from_host(DT[bits], p), mo.Ring(bits, p)
+    mir = mo.MirTensor([op, op, op])
+    assert same_rep(g.rep_add(gx, gy), mo.rep_add(ox, oy))
+    assert same_rep(g.rep_sub(gx, gy), mo.rep_sub(ox, oy))
+    assert same_rep(g.rep_neg(gx), mo.rep_neg(ox))
+    assert same_rep(g.rep_shl(7, gx), mo.rep_shl(7, ox))
+    assert same_rep(g.rep_add_public(gx, gp), mo.rep_add_mir(ox, mir))
+    assert same_rep(g.rep_sub_public(gx, gp), mo.rep_sub_mir(ox, mir))
+    assert same_rep(g.rep_public_sub(gp, gx), mo.rep_mir_sub(mir, ox))
+    assert same_rep(g.rep_mul_public(gx, gp), mo.rep_mul_mir(ox, mir))
+    g.close()
+
+
+@pytest.mark.parametrize("bits", [64, 128])
+@pytest.mark.parametrize("shape", [(1,), (5,), (33, 3), (4, 3, 5), (1025,)])
+def test_rep_mul_parity(bits, shape):
+    """replicated/mod.rs:653-696 style wrap-around products, share-level parity."""
+    g, o = pair()
+    rng = np.random.default_rng(1)
+    a, b = rand_ring(rng, bits, shape), rand_ring(rng, bits, shape)
+    gx, gy = g.share(g.from_host(DT[bits], a), 0), g.share(g.from_host(DT[bits], b), 1)
+    ox, oy = mo.rep_share(o, mo.Ring(bits, a), 0), mo.rep_share(o, mo.Ring(bits, b), 1)
+    gz, oz = g.rep_mul(gx, gy), mo.rep_mul(o, ox, oy)
+    assert same_rep(gz, oz)
+    gz2, oz2 = g.rep_mul(gz, gx), mo.rep_mul(o, oz, ox)  # second mul: fresh sync keys, same setup
+    assert same_rep(gz2, oz2)
+    assert same_ring(g.reveal(gz), mo.mul(mo.Ring(bits, a), mo.Ring(bits, b)))
+    g.close()
+
+
+@pytest.mark.parametrize("bits", [64, 128])
+@pytest.mark.parametrize("M,K,N", [(1, 3, 1), (4, 5, 6), (70, 33, 5), (130, 64, 66)])
+def test_rep_dot_parity_imad(bits, M, K, N):
+    g, o = pair()
+    g.set_gemm_mode(1)
+    rng = np.random.default_rng(M + K + N)
+    a, b = rand_ring(rng, bits, (M, K)), rand_ring(rng, bits, (K, N))
+    gx, gy = g.share(g.from_host(DT[bits], a), 0), g.share(g.from_host(DT[bits], b), 1)
+    ox, oy = mo.rep_share(o, mo.Ring(bits, a), 0), mo.rep_share(o, mo.Ring(bits, b), 1)
+    gz, oz = g.rep_dot(gx, gy), mo.rep_dot(o, ox, oy)
+    assert same_rep(gz, oz)
+    assert same_ring(g.reveal(gz), mo.dot(mo.Ring(bits, a), mo.Ring(bits, b)))
+    g.close()
+
+
+@pytest.mark.parametrize("bits,amount", [(64, 23), (64, 1), (64, 40), (128, 40), (128, 1), (128, 100)])
+def test_trunc_pr_parity(bits, amount):
+    """additive/trunc.rs:206-217,272-286 and replicated/mod.rs:847-859,965-980: |trunc - x>>amount| <= 1,
+    plus bit-exact shares against the oracle under the shared entropy source."""
+    g, o = pair()
+    rng = np.random.default_rng(amount)
+    k = bits - 1
+    n = 1000
+    vals = [int(v) for v in rng.integers(-(2 ** 62), 2 ** 62, n)]
+    if bits == 128:
+        vals = [v * int(rng.integers(1, 2 ** 62)) for v in vals]  # |x| < 2^124 <= 2^(k-2) holds for 125
+        vals = [v >> 0 for v in vals]
+    lim = 1 << (k - 2)
+    vals = [max(-lim, min(lim - 1, v)) for v in vals] + [0, 1, -1, lim - 1, -lim]
+    gx = g.share(g.from_ints(DT[bits], vals), 0)
+    ox = mo.rep_share(o, mo.Ring.from_ints(bits, vals), 0)
+    gz, oz = g.trunc_pr(amount, gx), mo.rep_trunc_pr(o, amount, ox)
+    assert same_rep(gz, oz)
+    got = signed(g.reveal(gz).to_ints(), bits)
+    for v, t in zip(vals, got):
+        assert abs(t - (v >> amount)) <= 1, (v, t, v >> amount)
+    g.close()
+
+
+def test_trunc_pr_rejects_large_amount():
+    g, _ = pair()
+    x = g.share(g.fill(RING64, 5, (3,)), 0)
+    with pytest.raises(mb.MooseB200Error):
+        g.trunc_pr(63, x)
+    g.close()
+
+
+@pytest.mark.parametrize("bits", [64, 128])
+@pytest.mark.parametrize("shape", [(3,), (128,), (5, 7), (256,)])
+def test_bit_decompose_msb_parity(bits, shape):
+    """replicated/mod.rs:999-1032 (msb), :1100+ (bit_dec): share-level parity and plaintext check."""
+    g, o = pair()
+    rng = np.random.default_rng(9)
+    a = rand_ring(rng, bits, shape)
+    gx, ox = g.share(g.from_host(DT[bits], a), 0), mo.rep_share(o, mo.Ring(bits, a), 0)
+    gb, ob = g.rep_bit_decompose(gx), mo.rep_bit_decompose(o, ox)
+    assert same_rep(gb, ob)
+    assert same(g.reveal(gb), mo.bit_decompose(mo.Ring(bits, a)))
+    gm, om = g.msb(gx), mo.rep_msb(o, ox)
+    assert same_rep(gm, om)
+    assert same(g.reveal(gm), mo.bit_extract(bits - 1, mo.Ring(bits, a)))
+    g.close()
+
+
+@pytest.mark.parametrize("bits", [64, 128])
+def test_ring_inject_parity(bits):
+    """replicated/mod.rs ring_inject tests: b -> b << idx as a replicated ring value."""
+    g, o = pair()
+    rng = np.random.default_rng(4)
+    b = rng.integers(0, 2, (9, 5)).astype(np.uint8)
+    gb, ob = g.share(g.from_bits(b), 0), mo.rep_share(o, mo.Bits.from_array(b), 0)
+    assert same_rep(gb, ob)
+    for idx in (0, 7, bits - 1):
+        gr, orr = g.rep_ring_inject(DT[bits], idx, gb), mo.rep_ring_inject(o, bits, idx, ob)
+        assert same_rep(gr, orr)
+        assert [int(v) for v in g.reveal(gr).to_ints().reshape(-1)] == [int(v) << idx for v in b.reshape(-1)]
+    g.close()
+
+
+@pytest.mark.parametrize("bits,frac", [(64, 23), (128, 40)])
+def test_relu_maximum_mux_parity(bits, frac):
+    """fixedpoint/ops.rs:314-330 (relu), replicated/softmax.rs:10-53 (maximum), control_flow.rs (mux)."""
+    g, o = pair()
+    rng = np.random.default_rng(12)
+    f = rng.uniform(-100, 100, (6, 7))
+    vals = [int(v * 2 ** frac) for v in f.reshape(-1)]
+    gx = g.share(g.from_ints(DT[bits], vals, f.shape), 0)
+    ox = mo.rep_share(o, mo.Ring.from_ints(bits, vals, f.shape), 0)
+    gr, orr = g.relu(gx), mo.rep_relu(o, ox)
+    assert same_rep(gr, orr)
+    assert signed(g.reveal(gr).to_ints().reshape(-1), bits) == [max(v, 0) for v in vals]
+    # maximum([zeros, z]) as the MLP predictor builds it (zeros shared by bob)
+    gz = g.share(g.fill(DT[bits], 0, f.shape), 1)
+    oz = mo.rep_share(o, mo.fill(bits, 0, f.shape), 1)
+    gm, om = g.maximum([gz, gx]), mo.rep_maximum(o, [oz, ox])
+    assert same_rep(gm, om)
+    assert signed(g.reveal(gm).to_ints().reshape(-1), bits) == [max(v, 0) for v in vals]
+    w = [int(v) for v in rng.integers(-1000, 1000, f.size)]
+    gw = g.share(g.from_ints(DT[bits], w, f.shape), 2)
+    ow = mo.rep_share(o, mo.Ring.from_ints(bits, w, f.shape), 2)
+    g3, o3 = g.maximum([gx, gw, gz]), mo.rep_maximum(o, [ox, ow, oz])
+    assert same_rep(g3, o3)
+    assert signed(g.reveal(g3).to_ints().reshape(-1), bits) == [max(a, b, 0) for a, b in zip(vals, w)]
+    gl, ol = g.rep_less(gx, gw), mo.rep_less(o, ox, ow)
+    assert same_rep(gl, ol)
+    assert g.reveal(gl).bits().reshape(-1).tolist() == [int(a < b) for a, b in zip(vals, w)]
+    g.close()
+
+
+def test_fixed_dot_trunc_end_to_end():
+    """tutorials/dotprod.moose: Fixed128(24,40) x=[[1,2,3]] . y=[[4],[5],[6]] = 32.0 (BASELINE config 1)."""
+    g, o = pair()
+    x = np.array([[1.0, 2.0, 3.0]])
+    y = np.array([[4.0], [5.0], [6.0]])
+    gx = g.share(g.fixedpoint_encode(RING128, 40, g.from_host(mb.FLOAT64, x)), 0)
+    gy = g.share(g.fixedpoint_encode(RING128, 40, g.from_host(mb.FLOAT64, y)), 1)
+    ox = mo.rep_share(o, mo.fixed_encode(128, x, 40), 0)
+    oy = mo.rep_share(o, mo.fixed_encode(128, y, 40), 1)
+    gz = g.trunc_pr(40, g.rep_dot(gx, gy))
+    oz = mo.rep_trunc_pr(o, 40, mo.rep_dot(o, ox, oy))
+    assert same_rep(gz, oz)
+    out = g.fixedpoint_decode(40, g.reveal(gz)).to_host()
+    assert abs(out[0, 0] - 32.0) < 1e-9
+    g.close()
