@@ -289,15 +289,16 @@ class Session:
     def from_host(self, dtype: int, data: np.ndarray, shape: Optional[Sequence[int]] = None) -> Tensor:
         """data: uint64[shape] (ring64), uint64[shape+(2,)] (ring128), packed uint8 + shape (bit),
         float64[shape]."""
+        in_shape = np.shape(data)  # np.ascontiguousarray promotes 0-d arrays to 1-d
         if dtype == RING64:
             a = np.ascontiguousarray(data, dtype=np.uint64)
-            shape = a.shape if shape is None else tuple(shape)
+            shape = in_shape if shape is None else tuple(shape)
         elif dtype == RING128:
             a = np.ascontiguousarray(data, dtype=np.uint64)
-            shape = a.shape[:-1] if shape is None else tuple(shape)
+            shape = in_shape[:-1] if shape is None else tuple(shape)
         elif dtype == FLOAT64:
             a = np.ascontiguousarray(data, dtype=np.float64)
-            shape = a.shape if shape is None else tuple(shape)
+            shape = in_shape if shape is None else tuple(shape)
         else:
             a = np.ascontiguousarray(data, dtype=np.uint8)
             assert shape is not None, "bit tensors need an explicit shape"
