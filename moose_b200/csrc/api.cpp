@@ -333,7 +333,7 @@ extern "C" int mb_dot(mb_ctx *ctx, const mb_tensor *x, const mb_tensor *y, mb_te
     mb_tensor_free(ctx, t);
     return mb_fail(ctx, MB_ERR_KERNEL, "mb_dot: shape not supported by the tensor-pipe GEMM (gemm mode 2)");
   }
-  if (limb_ok && ctx->gemm_mode != 1) {
+  if (limb_ok && (ctx->gemm_mode == 2 || (ctx->gemm_mode == 0 && k_gemm_limb_preferred(M, K, N)))) {
     GemmTerm term = {x->dptr, y->dptr, nullptr};
     rc = k_gemm_limb(ctx, x->dtype, &term, 1, t->dptr, M, K, N);
   } else {

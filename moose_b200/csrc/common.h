@@ -123,6 +123,7 @@ int k_bit_not(mb_ctx *ctx, const mb_tensor *x, mb_tensor *out);
 int k_gemm_imad(mb_ctx *ctx, mb_dtype dtype, const void *A, const void *B, void *C, int64_t M, int64_t K,
                 int64_t N, bool accumulate);
 bool k_gemm_limb_supported(mb_dtype dtype, int64_t M, int64_t K, int64_t N);
+bool k_gemm_limb_preferred(int64_t M, int64_t K, int64_t N);
 // C = sum_t A_t * B_t for nterms (1 or 2) operand pairs, optional fused epilogue.
 struct GemmTerm { const void *A; const void *B0; const void *B1; };  // B = B0 (+ B1 if non-null)
 int k_gemm_limb(mb_ctx *ctx, mb_dtype dtype, const GemmTerm *terms, int nterms, void *C, int64_t M,

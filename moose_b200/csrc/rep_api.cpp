@@ -331,11 +331,12 @@ extern "C" int mb_rep_dot(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep 
   bool limb_ok = k_gemm_limb_supported(dt, M, 2 * K, N);
   MB_REQUIRE(ctx, !(ctx->gemm_mode == 2 && !limb_ok), MB_ERR_KERNEL,
              "mb_rep_dot: shape not supported by the tensor-pipe GEMM (gemm mode 2)");
+  const bool use_limb = limb_ok && (ctx->gemm_mode == 2 || (ctx->gemm_mode == 0 && k_gemm_limb_preferred(M, 2 * K, N)));
   // v_i = x_i.y_i + x_i.y_{i+1} + x_{i+1}.y_i = x_i.(y_i + y_{i+1}) + x_{i+1}.y_i   (arith.rs:461-469;
   // identical mod 2^k, one GEMM less per party)
   for (int i = 0; i < 3; i++) {
     int j = (i + 1) % 3;
-    if (limb_ok && ctx->gemm_mode != 1) {
+    if (use_limb) {
       GemmTerm terms[2] = {{x->s[i]->dptr, y->s[i]->dptr, y->s[j]->dptr}, {x->s[j]->dptr, y->s[i]->dptr, nullptr}};
       MB_CHECK(k_gemm_limb(ctx, dt, terms, 2, z.p->s[i]->dptr, M, K, N));
     } else {

@@ -263,3 +263,34 @@ def test_fixedpoint_encode_decode(sess, bits, frac):
     w = rand_ring(rng, bits, (4096,))
     assert np.array_equal(sess.fixedpoint_decode(frac, sess.from_host(DT[bits], w)).to_host(),
                           mo.fixed_decode(mo.Ring(bits, w), frac))
+
+
+@pytest.mark.parametrize("bits", [64, 128])
+@pytest.mark.parametrize("M,K,N", [(128, 128, 64), (128, 256, 256), (256, 128, 128), (300, 200, 130), (129, 1000, 514),
+                                   (512, 1024, 512)])
+def test_dot_parity_tensor_pipe(sess, bits, M, K, N):
+    """tcgen05 int8 limb GEMM (gemm mode 2) against the oracle: full-range random ring elements, ragged
+    M / K / N (TMA zero fill, padded K, predicated epilogue)."""
+    rng = np.random.default_rng(M * 7 + K * 3 + N)
+    a, b = rand_ring(rng, bits, (M, K)), rand_ring(rng, bits, (K, N))
+    sess.set_gemm_mode(2)
+    try:
+        z = sess.dot(sess.from_host(DT[bits], a), sess.from_host(DT[bits], b))
+    finally:
+        sess.set_gemm_mode(0)
+    assert same_ring(z, mo.dot(mo.Ring(bits, a), mo.Ring(bits, b)))
+
+
+def test_dot_tensor_pipe_extreme_values(sess):
+    """All-ones limbs (0xff..ff) maximise every u8 x u8 product: checks the accumulator-exactness
+    planning (pass splitting) of the limb GEMM, K = 2048 > 66051 / 34."""
+    M, K, N = 128, 2048, 64
+    for bits in (64, 128):
+        a = np.full((M, K) + ((2,) if bits == 128 else ()), 0xFFFFFFFFFFFFFFFF, dtype=np.uint64)
+        b = np.full((K, N) + ((2,) if bits == 128 else ()), 0xFFFFFFFFFFFFFFFF, dtype=np.uint64)
+        sess.set_gemm_mode(2)
+        try:
+            z = sess.dot(sess.from_host(DT[bits], a), sess.from_host(DT[bits], b))
+        finally:
+            sess.set_gemm_mode(0)
+        assert same_ring(z, mo.dot(mo.Ring(bits, a), mo.Ring(bits, b)))

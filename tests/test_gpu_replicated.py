@@ -200,3 +200,19 @@ def test_fixed_dot_trunc_end_to_end():
     out = g.fixedpoint_decode(40, g.reveal(gz)).to_host()
     assert abs(out[0, 0] - 32.0) < 1e-9
     g.close()
+
+
+@pytest.mark.parametrize("bits", [64, 128])
+@pytest.mark.parametrize("M,K,N", [(128, 128, 64), (256, 384, 320)])
+def test_rep_dot_parity_tensor_pipe(bits, M, K, N):
+    """Replicated dot through the two-term tensor-pipe GEMM: x_i.(y_i + y_{i+1}) + x_{i+1}.y_i."""
+    g, o = pair()
+    g.set_gemm_mode(2)
+    rng = np.random.default_rng(M + K + N + 1)
+    a, b = rand_ring(rng, bits, (M, K)), rand_ring(rng, bits, (K, N))
+    gx, gy = g.share(g.from_host(DT[bits], a), 0), g.share(g.from_host(DT[bits], b), 1)
+    ox, oy = mo.rep_share(o, mo.Ring(bits, a), 0), mo.rep_share(o, mo.Ring(bits, b), 1)
+    gz, oz = g.rep_dot(gx, gy), mo.rep_dot(o, ox, oy)
+    assert same_rep(gz, oz)
+    assert same_ring(g.reveal(gz), mo.dot(mo.Ring(bits, a), mo.Ring(bits, b)))
+    g.close()
