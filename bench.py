@@ -1,0 +1,317 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the replicated-secret-sharing hot path.
+
+Workload at every N (BASELINE.json configs[1], the config the metric is quoted on):
+    Replicated Ring128 fixed(24,40) matmul 4096 x 4096 x 4096 + TruncPr(40),
+    synthetic shares, all three parties resident on one B200.
+One "step" = one replicated dot (DotOp::rep_rep_kernel) + one TruncPr
+(TruncPrOp::rep_kernel) over device-resident shares.  With --gpus N every rank runs
+that workload on its own GPU (independent sessions, no data-path collective: weak
+scaling); `value` is the job aggregate.
+
+Metric: ring GOP/s = 3 parties x 2 GEMMs x 2*M*N*K ring multiply-adds per step / time
+(SURVEY.md 8d).  `e2e` is the same metric through the C ABI starting from HOST buffers:
+H2D of the two plaintext fixed-point matrices from pinned memory, share, dot, trunc,
+reveal, D2H of the revealed product -- all inside the timed region.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--size S]
+
+--impl reference times the CPU restatement of the reference's kernels (oracle/, a port:
+the Rust reference cannot be built here) on the box's host cores on a bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FRAC = 40
+SESSION_ID = "b200-bench"
+ENTROPY_KEY = bytes(range(16))
+
+
+def ring_ops_per_step(M, K, N):
+    # 3 parties x 2 GEMMs x (M*N*K multiplies + M*N*K adds)
+    return 3 * 2 * 2 * M * N * K
+
+
+def fixed128(vals):
+    """fixed(24,40) encoding as uint64[..., 2] = [lo, hi] (truncation toward zero, two's complement)."""
+    scaled = np.trunc(vals * float(2 ** FRAC)).astype(np.int64)
+    lo = scaled.astype(np.uint64)
+    hi = np.where(scaled < 0, np.uint64(0xFFFFFFFFFFFFFFFF), np.uint64(0)).astype(np.uint64)
+    return np.stack([lo, hi], axis=-1)
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons of one GPU during the timed region."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+                for name, v in zip(names, r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max((float(r[3]) for r in self.rows if len(r) > 3 and r[3].replace('.', '', 1).isdigit()),
+                                   default=None),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f), "measured"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+def cpu_baseline_run(size, threads, with_trunc=True):
+    """Oracle (CPU port of the reference kernels) on a size^3 sample of the workload."""
+    from oracle import moose_oracle as mo
+    rng = np.random.default_rng(0)
+    a = mo.Ring(128, fixed128(rng.uniform(-1, 1, (size, size))))
+    b = mo.Ring(128, fixed128(rng.uniform(-1, 1, (size, size))))
+    sess = mo.Session(SESSION_ID, ENTROPY_KEY)
+    x, y = mo.rep_share(sess, a, 0), mo.rep_share(sess, b, 1)
+    mo.DOT_THREADS = threads
+    t0 = time.perf_counter()
+    z = mo.rep_dot(sess, x, y)
+    if with_trunc:
+        z = mo.rep_trunc_pr(sess, FRAC, z)
+    dt = time.perf_counter() - t0
+    mo.DOT_THREADS = 1
+    return ring_ops_per_step(size, size, size) / dt / 1e9, dt
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    from oracle import moose_oracle as mo
+    threads = mo.max_threads()
+    size = max(args.ref_size, 1024)
+    for _ in range(min(args.warmup, 1)):
+        cpu_baseline_run(min(size, 128), threads)
+    vals, times = [], []
+    for _ in range(args.steps):
+        v, dt = cpu_baseline_run(size, threads)
+        vals.append(v)
+        times.append(dt)
+    value = ring_ops_per_step(size, size, size) * len(times) / sum(times) / 1e9
+    sample = (f"replicated Ring128 dot {size}x{size}x{size} + TruncPr(40) per step (bounded sample of the 4096^3 "
+              f"workload; 9 host GEMMs like the reference, OpenMP over rows)")
+    line = {
+        "impl": "reference", "metric": "replicated_ring128_matmul_gops", "value": value, "unit": "GOP/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * sum(times) / len(times), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u128", "data": "synthetic",
+        "config": {"workload": "replicated_ring128_matmul_4096x4096x4096_truncpr40",
+                   "fixed": "fixed(24,40)", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "GOP/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "GOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--size", type=int, default=4096, help="M=N=K (default: the BASELINE config, 4096)")
+    ap.add_argument("--ref-size", type=int, default=640, help="sample size of the CPU baseline arms")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import moose_b200 as mb
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist_mod
+        torch.cuda.set_device(local_rank)
+        dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist = dist_mod
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    M = N = K = args.size
+    sess = mb.Session(local_rank, f"{SESSION_ID}-{rank}", ENTROPY_KEY)
+    rng = np.random.default_rng(rank)
+    # pinned host staging buffers with the plaintext fixed(24,40) operands
+    hA = sess.pinned_empty((M, K, 2), np.uint64)
+    hB = sess.pinned_empty((K, N, 2), np.uint64)
+    hA[...] = fixed128(rng.uniform(-1, 1, (M, K)))
+    hB[...] = fixed128(rng.uniform(-1, 1, (K, N)))
+    hOut = sess.pinned_empty((M, N, 2), np.uint64)
+
+    # device-resident shares for the kernel-only number
+    x = sess.share(sess.from_host(mb.RING128, hA), 0)
+    y = sess.share(sess.from_host(mb.RING128, hB), 1)
+    sess.sync()
+
+    def step():
+        z = sess.rep_dot(x, y)
+        return sess.trunc_pr(FRAC, z)
+
+    def step_e2e():
+        a = sess.from_host(mb.RING128, hA)
+        b = sess.from_host(mb.RING128, hB)
+        z = sess.trunc_pr(FRAC, sess.rep_dot(sess.share(a, 0), sess.share(b, 1)))
+        r = sess.reveal(z, 0)
+        sess._check(mb.lib().mb_tensor_to_host(sess.ctx, r.h, hOut.ctypes.data_as(mb._P), hOut.nbytes))
+
+    for _ in range(args.warmup):
+        out = step()
+    sess.sync()
+
+    # ---- kernel-only timed region (inputs resident in HBM; 6 x 268 MB of shares > 126 MB L2) ----
+    sampler = ClockSampler(local_rank)
+    sess.profile_enable(True)
+    sess.profile_read()
+    barrier()
+    sess.sync()
+    sampler.start()
+    launches0 = sess.launch_count
+    sess.timer_start()
+    for _ in range(args.steps):
+        out = step()
+    ms = sess.timer_stop()
+    sess.sync()
+    barrier()
+    launches = sess.launch_count - launches0
+    clocks = sampler.stop()
+    gemm_ms, gemm_launches = sess.profile_read()
+    sess.profile_enable(False)
+
+    # ---- end-to-end timed region (host buffers in, host buffer out) ----
+    step_e2e()
+    sess.sync()
+    barrier()
+    sess.timer_start()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    ms_e2e_dev = sess.timer_stop()
+    sess.sync()
+    ms_e2e = max(ms_e2e_dev, 1e3 * (time.perf_counter() - t0))
+    barrier()
+
+    if dist is not None:
+        import torch
+        t = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=f"cuda:{local_rank}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, ms_e2e = float(t[0]), float(t[1])
+        tl = torch.tensor([launches], dtype=torch.int64, device=f"cuda:{local_rank}")
+        dist.all_reduce(tl, op=dist.ReduceOp.SUM)
+        launches = int(tl[0])
+
+    # spot check: the revealed product decodes to A @ B (plaintext) within the TruncPr error
+    ok = True
+    if rank == 0:
+        a0 = hA[:4, :, 0].astype(np.int64).astype(np.float64) / 2 ** FRAC
+        b0 = hB[:, :4, 0].astype(np.int64).astype(np.float64) / 2 ** FRAC
+        got = hOut[:4, :4, 0].astype(np.int64).astype(np.float64) / 2 ** FRAC
+        ok = bool(np.allclose(got, a0 @ b0, atol=K * 2.0 ** -FRAC * 4 + 2.0 ** -38))
+
+    if rank == 0:
+        ops = ring_ops_per_step(M, K, N)
+        value = world * ops * args.steps / (ms * 1e-3) / 1e9
+        e2e = world * ops * args.steps / (ms_e2e * 1e-3) / 1e9
+        peaks, peak_src = measured_peaks()
+        # dominant kernel: limb_gemm_kernel, one launch per party = [M, 2K] x [2K, N] ring GEMM as 136 u8 limb GEMMs
+        int8_ops_per_launch = 2.0 * M * N * (2 * K) * 136
+        avg_ms = gemm_ms / max(gemm_launches, 1)
+        achieved = int8_ops_per_launch / (avg_ms * 1e-3) / 1e12 if gemm_launches else None
+        peak = 2.0 * peaks.get("bf16_tflops_sustained", peaks["bf16_tflops"])
+        line = {
+            "metric": "replicated_ring128_matmul_gops", "value": value, "unit": "GOP/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u128",
+            "data": "synthetic",
+            "config": {"workload": f"replicated_ring128_matmul_{M}x{K}x{N}_truncpr40", "fixed": "fixed(24,40)",
+                       "parties": "3 parties resident on each GPU; one independent session per GPU",
+                       "l2": "inputs larger than L2 (6 x 268 MB of shares vs 126 MB)",
+                       "result_check": "ok" if ok else "MISMATCH"},
+            "clocks": clocks,
+            "e2e": {"value": e2e, "unit": "GOP/s", "ms_per_step": ms_e2e / args.steps,
+                    "h2d_bytes_per_step": int(hA.nbytes + hB.nbytes), "d2h_bytes_per_step": int(hOut.nbytes)},
+            "gpu_launches": int(launches),
+            "roofline": {"kernel": "limb_gemm_kernel", "bound": "tensor", "achieved": achieved, "peak": peak,
+                         "unit": "TOP/s (int8)", "frac": (achieved / peak) if achieved else None, "traffic": None,
+                         "avg_launch_ms": avg_ms, "launches_timed": gemm_launches,
+                         "share_of_step": gemm_ms / ms if ms else None,
+                         "peak_source": f"2 x bf16_tflops_sustained of {peak_src} MEASURED_PEAKS.json "
+                                        "(no int8 figure is measured; int8 dense = 2 x bf16 nominally)"},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            from oracle import moose_oracle as mo
+            v, dt = cpu_baseline_run(args.ref_size, 1)
+            line["cpu_baseline"] = {
+                "value": v, "unit": "GOP/s", "cores": 1, "kind": "port",
+                "sample": f"replicated Ring128 dot {args.ref_size}^3 + TruncPr(40), {dt:.1f} s, single-threaded host "
+                          "kernels like the reference (ndarray generic dot, SURVEY F9); box has "
+                          f"{os.cpu_count()} logical cores"}
+        print(json.dumps(line), flush=True)
+
+    sess.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -89,6 +89,16 @@ int mb_ctx_timer_start(mb_ctx *ctx);
 int mb_ctx_timer_stop(mb_ctx *ctx, float *elapsed_ms);
 /* Number of kernels this library launched on `ctx` since creation. */
 uint64_t mb_ctx_launch_count(const mb_ctx *ctx);
+/* Per-kernel device timing for roofline reports: while enabled, launches of the
+ * ring-GEMM main kernel are bracketed by CUDA events on the context stream.
+ * mb_ctx_profile_read synchronises, returns the summed duration and launch count
+ * since the last read and resets the counters.  kernel: 0 = tensor-pipe limb GEMM. */
+int mb_ctx_profile_enable(mb_ctx *ctx, int enable);
+int mb_ctx_profile_read(mb_ctx *ctx, int kernel, float *total_ms, uint64_t *launches);
+/* Page-locked host buffers for callers that stage tensors (H2D / D2H at full
+ * PCIe rate); plain malloc'ed memory is accepted everywhere too. */
+int mb_host_alloc_pinned(mb_ctx *ctx, size_t nbytes, void **out);
+int mb_host_free_pinned(mb_ctx *ctx, void *ptr);
 
 /* ---------------------------------------------------------------- tensors */
 

@@ -64,6 +64,9 @@ ABI = {
     "mb_ctx_get_session_raw": [_P, _P], "mb_ctx_set_entropy_key": [_P, _U8P], "mb_ctx_sync": [_P],
     "mb_ctx_stream": [_P], "mb_ctx_timer_start": [_P], "mb_ctx_timer_stop": [_P, ctypes.POINTER(ctypes.c_float)],
     "mb_ctx_launch_count": [_P], "mb_ctx_set_gemm_mode": [_P, _I],
+    "mb_ctx_profile_enable": [_P, _I],
+    "mb_ctx_profile_read": [_P, _I, ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_uint64)],
+    "mb_host_alloc_pinned": [_P, ctypes.c_size_t, _PP], "mb_host_free_pinned": [_P, _P],
     "mb_tensor_from_host": [_P, _I, _I, _I64P, _P, _PP], "mb_tensor_alloc": [_P, _I, _I, _I64P, _PP],
     "mb_tensor_to_host": [_P, _P, _P, ctypes.c_size_t], "mb_tensor_free": [_P, _P],
     "mb_tensor_dtype": [_P], "mb_tensor_rank": [_P], "mb_tensor_shape": [_P], "mb_tensor_numel": [_P],
@@ -222,6 +225,7 @@ class Session:
 
     def __init__(self, device: int = 0, session_id: str = "b200-bench", entropy_key: Optional[bytes] = None):
         self.ctx = None
+        self._pinned = []
         ctx = ctypes.c_void_p()
         rc = lib().mb_ctx_create(device, ctypes.byref(ctx))
         if rc != 0:
@@ -233,6 +237,9 @@ class Session:
 
     def close(self):
         if self.ctx:
+            for p in self._pinned:
+                lib().mb_host_free_pinned(self.ctx, p)
+            self._pinned = []
             lib().mb_ctx_destroy(self.ctx)
             self.ctx = None
 
@@ -265,6 +272,25 @@ class Session:
     @property
     def stream(self) -> int:
         return int(lib().mb_ctx_stream(self.ctx) or 0)
+
+    def profile_enable(self, on: bool = True):
+        self._check(lib().mb_ctx_profile_enable(self.ctx, 1 if on else 0))
+
+    def profile_read(self, kernel: int = 0) -> Tuple[float, int]:
+        """(summed device ms, launches) of the ring-GEMM main kernel since the last read."""
+        ms, n = ctypes.c_float(), ctypes.c_uint64()
+        self._check(lib().mb_ctx_profile_read(self.ctx, kernel, ctypes.byref(ms), ctypes.byref(n)))
+        return float(ms.value), int(n.value)
+
+    def pinned_empty(self, shape, dtype) -> np.ndarray:
+        """numpy array backed by page-locked host memory (freed with the session)."""
+        dt = np.dtype(dtype)
+        n = int(np.prod(shape, dtype=np.int64)) * dt.itemsize
+        ptr = ctypes.c_void_p()
+        self._check(lib().mb_host_alloc_pinned(self.ctx, n, ctypes.byref(ptr)))
+        self._pinned.append(ptr)
+        buf = (ctypes.c_uint8 * max(n, 1)).from_address(ptr.value)
+        return np.frombuffer(buf, dtype=dt, count=n // dt.itemsize).reshape(shape)
 
     def set_gemm_mode(self, mode: int):
         self._check(lib().mb_ctx_set_gemm_mode(self.ctx, mode))

@@ -52,6 +52,9 @@ struct mb_ctx {
   uint8_t setup_keys[3][16]; // k0,k1,k2 (k10=k11 etc., replicated/setup.rs:39-58)
   int gemm_mode;
   std::atomic<uint64_t> launches;
+  bool profile;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;  // pending (start, stop) pairs
+  std::vector<cudaEvent_t> prof_pool;
   // scratch for the limb GEMM (grown on demand, stream ordered)
   void *scratch[4];
   size_t scratch_bytes[4];
@@ -88,6 +91,8 @@ int mb_tensor_new(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, m
 mb_tensor *mb_tensor_retain(mb_tensor *t);
 bool mb_same_shape(const mb_tensor *a, const mb_tensor *b);
 int mb_scratch(mb_ctx *ctx, int slot, size_t bytes, void **out);
+int mb_prof_begin(mb_ctx *ctx, cudaEvent_t *start);  // no-ops unless profiling is enabled
+int mb_prof_end(mb_ctx *ctx, cudaEvent_t start);
 
 // ---- host-side crypto (blake3.cpp, aes_host.cpp) ----------------------------
 void mb_blake3_session_id(const char *s, size_t len, uint8_t out[16]);

@@ -27,6 +27,7 @@ extern "C" int mb_ctx_create(int device, mb_ctx **out) {
   ctx->have_setup = false;
   ctx->gemm_mode = 0;
   ctx->launches = 0;
+  ctx->profile = false;
   memset(ctx->scratch, 0, sizeof(ctx->scratch));
   memset(ctx->scratch_bytes, 0, sizeof(ctx->scratch_bytes));
   MB_CUDA(ctx, cudaSetDevice(device));
@@ -52,6 +53,8 @@ extern "C" int mb_ctx_destroy(mb_ctx *ctx) {
   cudaStreamSynchronize(ctx->stream);
   for (int i = 0; i < 4; i++)
     if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
+  for (auto &pr : ctx->prof_events) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+  for (auto ev : ctx->prof_pool) cudaEventDestroy(ev);
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
   cudaStreamDestroy(ctx->stream);
@@ -107,6 +110,63 @@ extern "C" uint64_t mb_ctx_launch_count(const mb_ctx *ctx) { return ctx ? ctx->l
 extern "C" int mb_ctx_set_gemm_mode(mb_ctx *ctx, int mode) {
   if (!ctx || mode < 0 || mode > 2) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_set_gemm_mode: bad mode");
   ctx->gemm_mode = mode;
+  return MB_OK;
+}
+
+static int prof_event(mb_ctx *ctx, cudaEvent_t *ev) {
+  if (!ctx->prof_pool.empty()) {
+    *ev = ctx->prof_pool.back();
+    ctx->prof_pool.pop_back();
+    return MB_OK;
+  }
+  MB_CUDA(ctx, cudaEventCreate(ev));
+  return MB_OK;
+}
+int mb_prof_begin(mb_ctx *ctx, cudaEvent_t *start) {
+  *start = nullptr;
+  if (!ctx->profile) return MB_OK;
+  MB_CHECK(prof_event(ctx, start));
+  MB_CUDA(ctx, cudaEventRecord(*start, ctx->stream));
+  return MB_OK;
+}
+int mb_prof_end(mb_ctx *ctx, cudaEvent_t start) {
+  if (!start) return MB_OK;
+  cudaEvent_t stop;
+  MB_CHECK(prof_event(ctx, &stop));
+  MB_CUDA(ctx, cudaEventRecord(stop, ctx->stream));
+  ctx->prof_events.emplace_back(start, stop);
+  return MB_OK;
+}
+extern "C" int mb_ctx_profile_enable(mb_ctx *ctx, int enable) {
+  if (!ctx) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_profile_enable: NULL ctx");
+  ctx->profile = enable != 0;
+  return MB_OK;
+}
+extern "C" int mb_ctx_profile_read(mb_ctx *ctx, int kernel, float *total_ms, uint64_t *launches) {
+  if (!ctx || !total_ms || !launches || kernel != 0)
+    return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_profile_read: bad argument");
+  MB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  float total = 0.f;
+  for (auto &pr : ctx->prof_events) {
+    float ms = 0.f;
+    MB_CUDA(ctx, cudaEventElapsedTime(&ms, pr.first, pr.second));
+    total += ms;
+    ctx->prof_pool.push_back(pr.first);
+    ctx->prof_pool.push_back(pr.second);
+  }
+  *total_ms = total;
+  *launches = ctx->prof_events.size();
+  ctx->prof_events.clear();
+  return MB_OK;
+}
+extern "C" int mb_host_alloc_pinned(mb_ctx *ctx, size_t nbytes, void **out) {
+  if (!ctx || !out) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_host_alloc_pinned: NULL argument");
+  MB_CUDA(ctx, cudaSetDevice(ctx->device));
+  MB_CUDA(ctx, cudaHostAlloc(out, nbytes ? nbytes : 1, cudaHostAllocDefault));
+  return MB_OK;
+}
+extern "C" int mb_host_free_pinned(mb_ctx *ctx, void *ptr) {
+  if (ptr) MB_CUDA(ctx, cudaFreeHost(ptr));
   return MB_OK;
 }
 

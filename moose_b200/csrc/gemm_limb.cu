@@ -576,8 +576,11 @@ int k_gemm_limb(mb_ctx *ctx, mb_dtype dtype, const GemmTerm *terms, int nterms, 
 
   MB_CUDA(ctx, cudaFuncSetAttribute(limb_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
   const int grid = std::min(gp.tiles_m * gp.tiles_n, ctx->sm_count);
+  cudaEvent_t prof_start;
+  MB_CHECK(mb_prof_begin(ctx, &prof_start));
   limb_gemm_kernel<<<grid, NUM_THREADS, SMEM_BYTES, ctx->stream>>>(map_a, map_b, gp);
   MB_LAUNCH_CHECK(ctx);
+  MB_CHECK(mb_prof_end(ctx, prof_start));
 
   RecombineDesc rd;
   rd.num_passes = (int)passes.size();
