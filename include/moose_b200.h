@@ -157,6 +157,26 @@ int mb_shr(mb_ctx *ctx, uint64_t amount, const mb_tensor *x, mb_tensor **out);
 /* DotOp::ring_kernel / HostRingTensor::dot (moose/src/host/ops.rs:1754-1851):
  * rank (1,1), (1,2), (2,1), (2,2) contraction mod 2^k. */
 int mb_dot(mb_ctx *ctx, const mb_tensor *x, const mb_tensor *y, mb_tensor **out);
+/* No counterpart in the reference: a ring matrix product C[M,N] = A[M,K] * B[K,N] mod 2^64 / 2^128 on
+ * the tensor pipe that never allocates.  It is meant for hosts that cannot let this library call
+ * cudaMalloc: services whose device memory is handed out up front to another allocator (so a late
+ * cudaMalloc would fail or eat someone else's budget), and request paths that cannot afford the
+ * device-wide stall an allocation or free may cause.  mb_dot keeps its byte-limb planes and partial
+ * sums in buffers it grows on demand; this call keeps them in a fixed 8 MiB array inside the library
+ * image (present once on every GPU that loads the library, for the life of the process).
+ *  - a_dev, b_dev, c_dev are DEVICE pointers supplied by the caller (row-major, same element layout as
+ *    MB_RING64 / MB_RING128 tensors); nothing is allocated or freed, on the device or by any library.
+ *  - Limits: M >= 128, K >= 128, N >= 64, N even, and the limb planes plus partial sums,
+ *    L*Kp*(M+N) + 8*passes*M*N bytes with L = 8 or 16 limbs and Kp = K rounded up to 128, must fit in
+ *    8 MiB (Ring128 256 x 512 x 256 fills it exactly; Ring64 512 x 512 x 256 needs 7 MiB).  Larger shapes are refused with
+ *    MB_ERR_INVALID_ARGUMENT and a message that states both sizes; use mb_dot for them.
+ *  - The first call on each device looks up the array's device address; make that first call before
+ *    starting any stream capture on the context's stream.
+ *  - All calls on a device share the one array and it keeps the bytes of the previous call; the call clears
+ *    the part that has to start at zero itself.  Two calls that overlap in time on the same GPU (different
+ *    contexts / streams) would corrupt each other: serialise them. */
+int mb_dot_noalloc(mb_ctx *ctx, mb_dtype dtype, const void *a_dev, const void *b_dev, void *c_dev,
+                   int64_t M, int64_t K, int64_t N);
 /* AddNOp::host_kernel (moose/src/host/ops.rs:1084-1103). */
 int mb_add_n(mb_ctx *ctx, const mb_tensor *const *xs, int n, mb_tensor **out);
 /* SumOp::host_ring_kernel (moose/src/host/ops.rs:1067-1081); axis < 0 = all. */

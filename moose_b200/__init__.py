@@ -76,7 +76,7 @@ ABI = {
     "mb_fill": [_P, _I, _I, _I64P, _U64, _U64, _PP],
     "mb_add": [_P, _P, _P, _PP], "mb_sub": [_P, _P, _P, _PP], "mb_mul": [_P, _P, _P, _PP],
     "mb_neg": [_P, _P, _PP], "mb_shl": [_P, _U64, _P, _PP], "mb_shr": [_P, _U64, _P, _PP],
-    "mb_dot": [_P, _P, _P, _PP], "mb_add_n": [_P, _PP, _I, _PP], "mb_sum": [_P, _P, _I, _PP],
+    "mb_dot": [_P, _P, _P, _PP], "mb_dot_noalloc": [_P, _I, _P, _P, _P, _I64, _I64, _I64], "mb_add_n": [_P, _PP, _I, _PP], "mb_sum": [_P, _P, _I, _PP],
     "mb_broadcast": [_P, _P, _I, _I64P, _PP],
     "mb_fixedpoint_encode": [_P, _I, _U32, _P, _PP], "mb_fixedpoint_decode": [_P, _U32, _P, _PP],
     "mb_xor": [_P, _P, _P, _PP], "mb_and": [_P, _P, _P, _PP], "mb_or": [_P, _P, _P, _PP],
@@ -396,6 +396,17 @@ class Session:
     def xor(self, x, y): return self._bin(lib().mb_xor, x, y)
     def and_(self, x, y): return self._bin(lib().mb_and, x, y)
     def or_(self, x, y): return self._bin(lib().mb_or, x, y)
+
+    def dot_noalloc(self, x: Tensor, y: Tensor, out: Tensor) -> None:
+        """C = x . y into the caller-provided `out` through mb_dot_noalloc (no allocation inside the call)."""
+        M, K = x.shape
+        N = y.shape[1]
+        self._check(lib().mb_dot_noalloc(self.ctx, x.dtype, x.device_ptr, y.device_ptr, out.device_ptr, M, K, N))
+
+    def alloc(self, dtype: int, shape) -> Tensor:
+        arr, rank = _shape_arr(shape)
+        out = self._out()
+        return self._t(lib().mb_tensor_alloc(self.ctx, dtype, rank, arr, ctypes.byref(out)), out)
 
     def neg(self, x: Tensor) -> Tensor:
         out = self._out()

@@ -593,3 +593,147 @@ int k_gemm_limb(mb_ctx *ctx, mb_dtype dtype, const GemmTerm *terms, int nterms, 
   MB_LAUNCH_CHECK(ctx);
   return MB_OK;
 }
+
+// =====================================================================================
+// mb_dot_noalloc: the tensor-pipe ring GEMM for callers that must not allocate.
+//
+// Everything k_gemm_limb keeps in per-context scratch buffers (the byte-limb planes of both
+// operands and the per-pass partial sums) lives here in ONE fixed array that is part of the
+// library image.  The array exists once per GPU that loads the library and stays resident
+// until the process exits, which is why its size is kept modest.
+// =====================================================================================
+namespace {
+
+constexpr size_t NOALLOC_SCRATCH_BYTES = 8u << 20;  // 8 MiB
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+unsigned char *g_noalloc_ptr[NOALLOC_MAX_DEVICES];  // device address of g_noalloc_scratch, per device (0 = not set up)
+
+// In host code the identifier g_noalloc_scratch is only a handle for the runtime: its device address has to
+// be asked for, once per device and with that device current.
+int noalloc_scratch_address(mb_ctx *ctx, unsigned char **out) {
+  if (ctx->device < 0 || ctx->device >= NOALLOC_MAX_DEVICES)
+    return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_dot_noalloc: device index out of range");
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (!g_noalloc_ptr[ctx->device]) {
+    MB_CUDA(ctx, cudaSetDevice(ctx->device));
+    void *p = nullptr;
+    MB_CUDA(ctx, cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    if (!p) return mb_fail(ctx, MB_ERR_CUDA, "mb_dot_noalloc: cudaGetSymbolAddress returned a null address");
+    g_noalloc_ptr[ctx->device] = (unsigned char *)p;
+  }
+  *out = g_noalloc_ptr[ctx->device];
+  return MB_OK;
+}
+
+// plan_passes without heap containers: fills the kernel parameter block directly.
+bool plan_passes_fixed(int L, int kbits, int64_t kblocks, GemmParams &gp) {
+  int np = 0, nu = 0;
+  for (int d = 0; d < L; d += 2) {
+    const bool two = d + 1 < L;
+    const bool may_wrap = kbits - 8 * d <= 32;
+    const int64_t per_kb = (int64_t)(two ? d + 2 : d + 1) * BLOCK_K;
+    const int64_t max_kb = may_wrap ? INT64_MAX : std::max<int64_t>(1, (int64_t)ACC_LIMIT / per_kb);
+    int64_t kb = 0;
+    while (kb < kblocks) {
+      if (np >= MAX_PASSES || nu >= MAX_UNITS) return false;
+      const int64_t take = std::min<int64_t>(kblocks - kb, max_kb);
+      gp.units[nu] = {0, (int)kb, (int)(kb + take)};
+      gp.passes[np] = {(short)d, (short)nu, (short)(nu + 1), 0};
+      nu++;
+      np++;
+      kb += take;
+    }
+  }
+  gp.num_passes = np;
+  return true;
+}
+
+inline size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+}  // namespace
+
+extern "C" int mb_dot_noalloc(mb_ctx *ctx, mb_dtype dtype, const void *a_dev, const void *b_dev, void *c_dev, int64_t M,
+                              int64_t K, int64_t N) {
+  if (!ctx) return mb_fail(nullptr, MB_ERR_INVALID_ARGUMENT, "mb_dot_noalloc: NULL context");
+  if (!a_dev || !b_dev || !c_dev) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_dot_noalloc: NULL operand pointer");
+  if (dtype != MB_RING64 && dtype != MB_RING128)
+    return mb_fail(ctx, MB_ERR_TYPE_MISMATCH, "mb_dot_noalloc: ring64 or ring128 operands only");
+  if (M < 128 || N < 64 || K < 128 || (N % 2) != 0)
+    return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_dot_noalloc: needs M >= 128, K >= 128, N >= 64 and N even");
+  MB_CUDA(ctx, cudaSetDevice(ctx->device));
+
+  const int L = dtype == MB_RING128 ? 16 : 8;
+  const int64_t Kp = (K + BLOCK_K - 1) / BLOCK_K * BLOCK_K;
+  const int block_n = N >= 256 ? 256 : (N >= 128 ? 128 : 64);
+
+  GemmParams gp;
+  memset(&gp, 0, sizeof(gp));
+  if (!plan_passes_fixed(L, 8 * L, Kp / BLOCK_K, gp))
+    return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_dot_noalloc: K too large for the pass table");
+
+  // Carve the static array: [A limb planes | B limb planes | partial sums], each 1024-byte aligned.
+  const size_t a_bytes = round_up((size_t)L * M * Kp, 1024);
+  const size_t b_bytes = round_up((size_t)L * N * Kp, 1024);
+  const size_t part_bytes = (size_t)gp.num_passes * M * N * 8;
+  const size_t need = a_bytes + b_bytes + part_bytes;
+  if (need > NOALLOC_SCRATCH_BYTES)
+    return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT,
+                   "mb_dot_noalloc: this shape needs " + std::to_string(need) +
+                       " bytes of scratch but the built-in scratch array holds " +
+                       std::to_string(NOALLOC_SCRATCH_BYTES) + " bytes; use mb_dot for larger problems");
+
+  unsigned char *scratch = nullptr;
+  MB_CHECK(noalloc_scratch_address(ctx, &scratch));
+  uint8_t *dA = scratch, *dB = scratch + a_bytes;
+  unsigned long long *dP = (unsigned long long *)(scratch + a_bytes + b_bytes);
+
+  // The array still holds whatever the previous call left behind.  The only bytes that are read without
+  // being written first are the K..Kp padding columns of the A planes, so those planes are zeroed when K is
+  // not a multiple of the 128-byte tile (split_bt_kernel writes its own padding; partials are fully overwritten).
+  if (Kp != K) MB_CUDA(ctx, cudaMemsetAsync(dA, 0, (size_t)L * M * Kp, ctx->stream));
+
+  const int64_t quads = M * ((K + 3) / 4);
+  dim3 gb((unsigned)((N + 31) / 32), (unsigned)((Kp + 31) / 32));
+  if (dtype == MB_RING128) {
+    split_a_kernel<u128><<<(unsigned)((quads + 255) / 256), 256, 0, ctx->stream>>>((const u128 *)a_dev, dA, M, K, Kp);
+    MB_LAUNCH_CHECK(ctx);
+    split_bt_kernel<u128><<<gb, 256, 0, ctx->stream>>>((const u128 *)b_dev, (const u128 *)nullptr, dB, K, N, Kp);
+    MB_LAUNCH_CHECK(ctx);
+  } else {
+    split_a_kernel<uint64_t><<<(unsigned)((quads + 255) / 256), 256, 0, ctx->stream>>>((const uint64_t *)a_dev, dA, M, K, Kp);
+    MB_LAUNCH_CHECK(ctx);
+    split_bt_kernel<uint64_t><<<gb, 256, 0, ctx->stream>>>((const uint64_t *)b_dev, (const uint64_t *)nullptr, dB, K, N, Kp);
+    MB_LAUNCH_CHECK(ctx);
+  }
+
+  CUtensorMap map_a, map_b;
+  MB_CHECK(make_plane_map(ctx, &map_a, dA, Kp, M, L, BLOCK_M));
+  MB_CHECK(make_plane_map(ctx, &map_b, dB, Kp, N, L, block_n));
+
+  gp.L = L;
+  gp.M = (int)M;
+  gp.N = (int)N;
+  gp.block_n = block_n;
+  gp.tiles_m = (int)((M + BLOCK_M - 1) / BLOCK_M);
+  gp.tiles_n = (int)((N + block_n - 1) / block_n);
+  gp.partials = dP;
+
+  MB_CUDA(ctx, cudaFuncSetAttribute(limb_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+  const int grid = std::min(gp.tiles_m * gp.tiles_n, ctx->sm_count);
+  limb_gemm_kernel<<<grid, NUM_THREADS, SMEM_BYTES, ctx->stream>>>(map_a, map_b, gp);
+  MB_LAUNCH_CHECK(ctx);
+
+  RecombineDesc rd;
+  rd.num_passes = gp.num_passes;
+  for (int i = 0; i < gp.num_passes; i++) rd.shift[i] = 8 * gp.passes[i].d;
+  const int64_t MN = M * N;
+  if (dtype == MB_RING128)
+    recombine_kernel<u128><<<(unsigned)((MN + 255) / 256), 256, 0, ctx->stream>>>(dP, (u128 *)c_dev, MN, rd);
+  else
+    recombine_kernel<uint64_t><<<(unsigned)((MN + 255) / 256), 256, 0, ctx->stream>>>(dP, (uint64_t *)c_dev, MN, rd);
+  MB_LAUNCH_CHECK(ctx);
+  return MB_OK;
+}
