@@ -273,8 +273,9 @@ def main():
         value = world * ops * args.steps / (ms * 1e-3) / 1e9
         e2e = world * ops * args.steps / (ms_e2e * 1e-3) / 1e9
         peaks, peak_src = measured_peaks()
-        # dominant kernel: limb_gemm_kernel, one launch per party = [M, 2K] x [2K, N] ring GEMM as 136 u8 limb GEMMs
-        int8_ops_per_launch = 2.0 * M * N * (2 * K) * 136
+        # dominant kernel: limb_gemm_kernel, one batched launch per step = 3 parties x ([M, 2K] x [2K, N] ring GEMM
+        # as 136 u8 x u8 limb GEMMs)
+        int8_ops_per_launch = 3 * 2.0 * M * N * (2 * K) * 136
         avg_ms = gemm_ms / max(gemm_launches, 1)
         achieved = int8_ops_per_launch / (avg_ms * 1e-3) / 1e12 if gemm_launches else None
         peak = 2.0 * peaks.get("bf16_tflops_sustained", peaks["bf16_tflops"])

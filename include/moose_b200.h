@@ -281,7 +281,8 @@ int mb_rep_shl_dim(mb_ctx *ctx, uint64_t amount, uint64_t bit_length, const mb_r
 /* Selects the ring-GEMM implementation used by mb_dot / mb_rep_dot:
  * 0 = automatic (int8 tensor pipe for large shapes, 64-bit IMAD CUDA-core
  * kernel for skinny / small ones), 1 = force IMAD, 2 = force tensor pipe
- * (fails for shapes it cannot tile).  For ncu comparisons and tests. */
+ * (fails for shapes it cannot tile), 3 = like 2 but single-CTA tiles only (no
+ * cta_group::2 pairs).  For ncu comparisons and tests. */
 int mb_ctx_set_gemm_mode(mb_ctx *ctx, int mode);
 
 #ifdef __cplusplus

@@ -51,6 +51,7 @@ struct mb_ctx {
   bool have_setup;
   uint8_t setup_keys[3][16]; // k0,k1,k2 (k10=k11 etc., replicated/setup.rs:39-58)
   int gemm_mode;
+  int gemm_pair_mode;         // 0 = CTA pairs when possible, 1 = single-CTA tiles only (A/B comparison)
   std::atomic<uint64_t> launches;
   bool profile;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;  // pending (start, stop) pairs
@@ -133,6 +134,12 @@ bool k_gemm_limb_preferred(int64_t M, int64_t K, int64_t N);
 struct GemmTerm { const void *A; const void *B0; const void *B1; };  // B = B0 (+ B1 if non-null)
 int k_gemm_limb(mb_ctx *ctx, mb_dtype dtype, const GemmTerm *terms, int nterms, void *C, int64_t M,
                 int64_t K, int64_t N);
+// Batched form with de-duplicated operands: C[b] = sum_t A[a_idx[b][t]] * B[b_idx[b][t]].
+struct LimbOperandA { const void *ptr; };
+struct LimbOperandB { const void *b0; const void *b1; };  // B = b0 (+ b1 if non-null)
+int k_gemm_limb_batched(mb_ctx *ctx, mb_dtype dtype, const LimbOperandA *As, int nA, const LimbOperandB *Bs, int nB,
+                        const int (*a_idx)[2], const int (*b_idx)[2], int nbatch, int nterms, void *const *C,
+                        int64_t M, int64_t K, int64_t N);
 
 // Fused replicated kernels (rep.cu)
 int k_rep_share(mb_ctx *ctx, const AesKey &key, int owner, const mb_tensor *x, mb_tensor *o0, mb_tensor *o1,

@@ -21,6 +21,11 @@
 //     C = sum_p partial_p << (8 d_p)   mod 2^k
 // (HBM traffic of the partials is a few % of the MMA time at K = 4096).
 //
+// Scheduling: the unit of work is one (batch, tile, pass) triple -- passes of a tile are independent because
+// each writes its own partial slot.  Passes are sorted by cost (MMA steps) and the flat work list is dealt to
+// the persistent CTAs in snake order (0..G-1, G-1..0, ...), a static longest-first schedule that removes the
+// wave tail of a tile-granular launch; the three parties of a replicated dot are one batched launch.
+//
 // Warp roles (192 threads): warps 0-3 epilogue (TMEM -> registers -> global), warp 4 TMA
 // producer, warp 5 TMEM allocator + single-thread MMA issuer.
 #include <cuda.h>
@@ -54,16 +59,42 @@ struct UnitDesc {
   int kb_end;
 };
 
+constexpr int MAX_BATCH = 4;
+
 struct GemmParams {
-  PassDesc passes[MAX_PASSES];
+  PassDesc passes[MAX_PASSES];   // sorted by decreasing cost; index = partial slot
   UnitDesc units[MAX_UNITS];
+  short plane_a[MAX_BATCH][2];   // first limb plane of the A operand of (batch, term)
+  short plane_b[MAX_BATCH][2];
   int num_passes;
+  int nbatch;
   int L;            // limbs per element
   int M, N;
   int block_n;
   int tiles_m, tiles_n;
-  unsigned long long *partials;  // [num_passes][M][N] u64
+  int total_items;  // num_passes * nbatch * tiles_m * tiles_n
+  unsigned long long *partials;  // [nbatch][num_passes][M][N] u64
 };
+
+// Work item j of CTA c in snake order over the flat list [pass rank][batch][tile].
+struct WorkItem {
+  int pass, batch, m0, n0;
+};
+__device__ __forceinline__ bool next_item(const GemmParams &p, int j, WorkItem &w) {
+  const int G = (int)gridDim.x;
+  const int c = (j & 1) ? G - 1 - (int)blockIdx.x : (int)blockIdx.x;
+  const long long idx = (long long)j * G + c;
+  if (idx >= p.total_items) return false;
+  const int tiles = p.tiles_m * p.tiles_n;
+  const int per_pass = p.nbatch * tiles;
+  w.pass = (int)(idx / per_pass);
+  const int rem = (int)(idx % per_pass);
+  w.batch = rem / tiles;
+  const int tile = rem % tiles;
+  w.m0 = (tile / p.tiles_n) * BLOCK_M;
+  w.n0 = (tile % p.tiles_n) * p.block_n;
+  return true;
+}
 
 // ---------------------------------------------------------------- PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -89,6 +120,25 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         : "r"(bar), "r"(parity)
         : "memory");
     if (!done && ++spins > (1u << 26)) __trap();  // watchdog: turn a protocol bug into an error, not a hang
+  }
+}
+// Same, for the 128 epilogue threads: they wait for whole passes (10^5..10^6 cycles), so they sleep between
+// polls instead of competing with the TMA / MMA issuing threads for issue slots.
+__device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  uint32_t spins = 0;
+  while (!done) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (!done) {
+      __nanosleep(256);
+      if (++spins > (1u << 24)) __trap();
+    }
   }
 }
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1, int c2) {
@@ -178,7 +228,6 @@ limb_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int num_tiles = p.tiles_m * p.tiles_n;
   const uint32_t b_tile_bytes = (uint32_t)p.block_n * BLOCK_K;
   const int L = p.L;
 
@@ -186,52 +235,49 @@ limb_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     // ===================== TMA producer =====================
     if (lane == 0) {
       int a_it = 0, b_it = 0;  // running slot counters
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m0 = (tile / p.tiles_n) * BLOCK_M;
-        const int n0 = (tile % p.tiles_n) * p.block_n;
-        for (int pi = 0; pi < p.num_passes; pi++) {
-          const PassDesc pd = p.passes[pi];
-          const int d = pd.d;
-          const bool two = d + 1 < L;              // pair has an upper diagonal
-          const int last = two ? 2 * d + 2 : -1;   // last zig-zag step (two diagonals)
-          for (int u = pd.unit_begin; u < pd.unit_end; u++) {
-            const UnitDesc ud = p.units[u];
-            const int plane0 = ud.term * L;
-            for (int kb = ud.kb_begin; kb < ud.kb_end; kb++) {
-              const int k0 = kb * BLOCK_K;
-              if (two) {
-                for (int s = 0; s <= last; s++) {
-                  const int t = s >> 1;
-                  if (s == 0 || (s & 1) == 0) {  // new A_t at even steps
-                    const int slot = a_it % A_SLOTS;
-                    mbar_wait(emptyA(slot), ((a_it / A_SLOTS) & 1) ^ 1);
-                    mbar_expect_tx(fullA(slot), A_TILE_BYTES);
-                    tma_load_3d(smem_u32(sA + slot * A_TILE_BYTES), &map_a, fullA(slot), k0, m0, plane0 + t);
-                    a_it++;
-                  }
-                  if (s == 0 || (s & 1) == 1) {  // new B at step 0 (B_{d+1}) and odd steps (B_{d-t})
-                    const int j = (s == 0) ? d + 1 : d - t;
-                    const int slot = b_it % B_SLOTS;
-                    mbar_wait(emptyB(slot), ((b_it / B_SLOTS) & 1) ^ 1);
-                    mbar_expect_tx(fullB(slot), b_tile_bytes);
-                    tma_load_3d(smem_u32(sB + slot * B_TILE_BYTES), &map_b, fullB(slot), k0, n0, plane0 + j);
-                    b_it++;
-                  }
-                }
-              } else {
-                // single (last, odd-L) diagonal: plain pairs (i, d-i)
-                for (int i = 0; i <= d; i++) {
-                  int slot = a_it % A_SLOTS;
+      WorkItem w;
+      for (int item = 0; next_item(p, item, w); item++) {
+        const PassDesc pd = p.passes[w.pass];
+        const int d = pd.d;
+        const bool two = d + 1 < L;              // pair has an upper diagonal
+        const int last = two ? 2 * d + 2 : -1;   // last zig-zag step (two diagonals)
+        for (int u = pd.unit_begin; u < pd.unit_end; u++) {
+          const UnitDesc ud = p.units[u];
+          const int pa0 = p.plane_a[w.batch][ud.term], pb0 = p.plane_b[w.batch][ud.term];
+          for (int kb = ud.kb_begin; kb < ud.kb_end; kb++) {
+            const int k0 = kb * BLOCK_K;
+            if (two) {
+              for (int s = 0; s <= last; s++) {
+                const int t = s >> 1;
+                if ((s & 1) == 0) {  // new A_t at even steps
+                  const int slot = a_it % A_SLOTS;
                   mbar_wait(emptyA(slot), ((a_it / A_SLOTS) & 1) ^ 1);
                   mbar_expect_tx(fullA(slot), A_TILE_BYTES);
-                  tma_load_3d(smem_u32(sA + slot * A_TILE_BYTES), &map_a, fullA(slot), k0, m0, plane0 + i);
+                  tma_load_3d(smem_u32(sA + slot * A_TILE_BYTES), &map_a, fullA(slot), k0, w.m0, pa0 + t);
                   a_it++;
-                  slot = b_it % B_SLOTS;
+                }
+                if (s == 0 || (s & 1) == 1) {  // new B at step 0 (B_{d+1}) and odd steps (B_{d-t})
+                  const int j = (s == 0) ? d + 1 : d - t;
+                  const int slot = b_it % B_SLOTS;
                   mbar_wait(emptyB(slot), ((b_it / B_SLOTS) & 1) ^ 1);
                   mbar_expect_tx(fullB(slot), b_tile_bytes);
-                  tma_load_3d(smem_u32(sB + slot * B_TILE_BYTES), &map_b, fullB(slot), k0, n0, plane0 + d - i);
+                  tma_load_3d(smem_u32(sB + slot * B_TILE_BYTES), &map_b, fullB(slot), k0, w.n0, pb0 + j);
                   b_it++;
                 }
+              }
+            } else {
+              // single (last, odd-L) diagonal: plain pairs (i, d-i)
+              for (int i = 0; i <= d; i++) {
+                int slot = a_it % A_SLOTS;
+                mbar_wait(emptyA(slot), ((a_it / A_SLOTS) & 1) ^ 1);
+                mbar_expect_tx(fullA(slot), A_TILE_BYTES);
+                tma_load_3d(smem_u32(sA + slot * A_TILE_BYTES), &map_a, fullA(slot), k0, w.m0, pa0 + i);
+                a_it++;
+                slot = b_it % B_SLOTS;
+                mbar_wait(emptyB(slot), ((b_it / B_SLOTS) & 1) ^ 1);
+                mbar_expect_tx(fullB(slot), b_tile_bytes);
+                tma_load_3d(smem_u32(sB + slot * B_TILE_BYTES), &map_b, fullB(slot), k0, w.n0, pb0 + d - i);
+                b_it++;
               }
             }
           }
@@ -246,103 +292,101 @@ limb_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       int a_it = 0, b_it = 0;
       int a_slot = 0, b_slot = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        for (int pi = 0; pi < p.num_passes; pi++) {
-          const PassDesc pd = p.passes[pi];
-          const int d = pd.d;
-          const bool two = d + 1 < L;
-          const int last = 2 * d + 2;
-          // wait until the epilogue has drained the accumulators of the previous pass
-          mbar_wait(tmem_empty, acc_phase ^ 1);
-          tcgen05_fence_after();
-          bool first_lo = true, first_hi = true;  // first MMA into acc(d) / acc(d+1) of this pass
-          for (int u = pd.unit_begin; u < pd.unit_end; u++) {
-            const UnitDesc ud = p.units[u];
-            for (int kb = ud.kb_begin; kb < ud.kb_end; kb++) {
-              const int nsteps = two ? last + 1 : d + 1;
-              for (int s = 0; s < nsteps; s++) {
-                bool new_a, new_b, hi, rel_a, rel_b;
-                if (two) {
-                  new_a = (s & 1) == 0;
-                  new_b = s == 0 || (s & 1) == 1;
-                  hi = (s & 1) == 0;             // even steps accumulate into diagonal d+1
-                  rel_a = (s & 1) == 1 || s == last;
-                  rel_b = (s & 1) == 0;
-                } else {
-                  new_a = new_b = rel_a = rel_b = true;
-                  hi = false;
-                }
-                if (new_a) {
-                  a_slot = a_it % A_SLOTS;
-                  mbar_wait(fullA(a_slot), (a_it / A_SLOTS) & 1);
-                  a_it++;
-                }
-                if (new_b) {
-                  b_slot = b_it % B_SLOTS;
-                  mbar_wait(fullB(b_slot), (b_it / B_SLOTS) & 1);
-                  b_it++;
-                }
-                tcgen05_fence_after();
-                const uint64_t adesc = make_smem_desc(smem_u32(sA + a_slot * A_TILE_BYTES));
-                const uint64_t bdesc = make_smem_desc(smem_u32(sB + b_slot * B_TILE_BYTES));
-                const uint32_t tmem_d = tmem_base + (hi ? (uint32_t)MAX_BLOCK_N : 0u);
-                bool &first = hi ? first_hi : first_lo;
-#pragma unroll
-                for (int k = 0; k < BLOCK_K / UMMA_K; k++) {
-                  // advance both descriptors by k * 32 bytes inside the swizzle atom
-                  umma_i8(tmem_d, adesc + (uint64_t)(k * UMMA_K >> 4), bdesc + (uint64_t)(k * UMMA_K >> 4), idesc,
-                          (first && k == 0) ? 0u : 1u);
-                }
-                first = false;
-                if (rel_a) umma_commit(emptyA(a_slot));
-                if (rel_b) umma_commit(emptyB(b_slot));
+      WorkItem w;
+      for (int item = 0; next_item(p, item, w); item++) {
+        const PassDesc pd = p.passes[w.pass];
+        const int d = pd.d;
+        const bool two = d + 1 < L;
+        const int last = 2 * d + 2;
+        // wait until the epilogue has drained the accumulators of the previous work item
+        mbar_wait(tmem_empty, acc_phase ^ 1);
+        tcgen05_fence_after();
+        bool first_lo = true, first_hi = true;  // first MMA into acc(d) / acc(d+1) of this pass
+        for (int u = pd.unit_begin; u < pd.unit_end; u++) {
+          const UnitDesc ud = p.units[u];
+          for (int kb = ud.kb_begin; kb < ud.kb_end; kb++) {
+            const int nsteps = two ? last + 1 : d + 1;
+            for (int s = 0; s < nsteps; s++) {
+              bool new_a, new_b, hi, rel_a, rel_b;
+              if (two) {
+                new_a = (s & 1) == 0;
+                new_b = s == 0 || (s & 1) == 1;
+                hi = (s & 1) == 0;             // even steps accumulate into diagonal d+1
+                rel_a = (s & 1) == 1 || s == last;
+                rel_b = (s & 1) == 0;
+              } else {
+                new_a = new_b = rel_a = rel_b = true;
+                hi = false;
               }
+              if (new_a) {
+                a_slot = a_it % A_SLOTS;
+                mbar_wait(fullA(a_slot), (a_it / A_SLOTS) & 1);
+                a_it++;
+              }
+              if (new_b) {
+                b_slot = b_it % B_SLOTS;
+                mbar_wait(fullB(b_slot), (b_it / B_SLOTS) & 1);
+                b_it++;
+              }
+              tcgen05_fence_after();
+              const uint64_t adesc = make_smem_desc(smem_u32(sA + a_slot * A_TILE_BYTES));
+              const uint64_t bdesc = make_smem_desc(smem_u32(sB + b_slot * B_TILE_BYTES));
+              const uint32_t tmem_d = tmem_base + (hi ? (uint32_t)MAX_BLOCK_N : 0u);
+              bool &first = hi ? first_hi : first_lo;
+#pragma unroll
+              for (int k = 0; k < BLOCK_K / UMMA_K; k++) {
+                // advance both descriptors by k * 32 bytes inside the swizzle atom
+                umma_i8(tmem_d, adesc + (uint64_t)(k * UMMA_K >> 4), bdesc + (uint64_t)(k * UMMA_K >> 4), idesc,
+                        (first && k == 0) ? 0u : 1u);
+              }
+              first = false;
+              if (rel_a) umma_commit(emptyA(a_slot));
+              if (rel_b) umma_commit(emptyB(b_slot));
             }
           }
-          umma_commit(tmem_full);  // accumulators of this pass are complete
-          acc_phase ^= 1;
         }
+        umma_commit(tmem_full);  // accumulators of this work item are complete
+        acc_phase ^= 1;
       }
     }
   } else {
     // ===================== epilogue (warps 0-3; warp w owns TMEM lanes 32w..32w+31) =====================
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m0 = (tile / p.tiles_n) * BLOCK_M;
-      const int n0 = (tile % p.tiles_n) * p.block_n;
-      const int row = m0 + warp * 32 + lane;
-      for (int pi = 0; pi < p.num_passes; pi++) {
-        const bool two = p.passes[pi].d + 1 < L;
-        mbar_wait(tmem_full, acc_phase);
-        tcgen05_fence_after();
-        unsigned long long *out = p.partials + ((size_t)pi * p.M + (size_t)row) * p.N + n0;
-        for (int c = 0; c < p.block_n; c += 32) {
-          uint32_t lo[32], hi[32];
-          const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c;
-          tmem_ld32(taddr, lo);
-          if (two) tmem_ld32(taddr + MAX_BLOCK_N, hi);
-          tmem_ld_wait();
-          if (row < p.M) {
-            if (n0 + c + 32 <= p.N) {
+    WorkItem w;
+    for (int item = 0; next_item(p, item, w); item++) {
+      const int row = w.m0 + warp * 32 + lane;
+      const int n0 = w.n0;
+      const bool two = p.passes[w.pass].d + 1 < L;
+      mbar_wait_relaxed(tmem_full, acc_phase);
+      tcgen05_fence_after();
+      unsigned long long *out =
+          p.partials + (((size_t)w.batch * p.num_passes + (size_t)w.pass) * p.M + (size_t)row) * p.N + n0;
+      for (int c = 0; c < p.block_n; c += 32) {
+        uint32_t lo[32], hi[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c;
+        tmem_ld32(taddr, lo);
+        if (two) tmem_ld32(taddr + MAX_BLOCK_N, hi);
+        tmem_ld_wait();
+        if (row < p.M) {
+          if (n0 + c + 32 <= p.N) {
 #pragma unroll
-              for (int q = 0; q < 32; q += 2) {
-                unsigned long long v0 = (unsigned long long)lo[q] + (two ? ((unsigned long long)hi[q] << 8) : 0ull);
-                unsigned long long v1 = (unsigned long long)lo[q + 1] + (two ? ((unsigned long long)hi[q + 1] << 8) : 0ull);
-                *(ulonglong2 *)(out + c + q) = make_ulonglong2(v0, v1);
-              }
-            } else {
+            for (int q = 0; q < 32; q += 2) {
+              unsigned long long v0 = (unsigned long long)lo[q] + (two ? ((unsigned long long)hi[q] << 8) : 0ull);
+              unsigned long long v1 = (unsigned long long)lo[q + 1] + (two ? ((unsigned long long)hi[q + 1] << 8) : 0ull);
+              *(ulonglong2 *)(out + c + q) = make_ulonglong2(v0, v1);
+            }
+          } else {
 #pragma unroll
-              for (int q = 0; q < 32; q++) {
-                if (n0 + c + q < p.N)
-                  out[c + q] = (unsigned long long)lo[q] + (two ? ((unsigned long long)hi[q] << 8) : 0ull);
-              }
+            for (int q = 0; q < 32; q++) {
+              if (n0 + c + q < p.N)
+                out[c + q] = (unsigned long long)lo[q] + (two ? ((unsigned long long)hi[q] << 8) : 0ull);
             }
           }
         }
-        tcgen05_fence_before();
-        mbar_arrive(tmem_empty);
-        acc_phase ^= 1;
       }
+      tcgen05_fence_before();
+      mbar_arrive(tmem_empty);
+      acc_phase ^= 1;
     }
   }
 
@@ -350,6 +394,265 @@ limb_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   __syncthreads();
   if (warp == 5) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
+  }
+}
+
+// ---------------------------------------------------------------- 2-CTA kernel (cta_group::2)
+// Same algorithm on CTA pairs: a cluster of two CTAs (one TPC) owns a 256 x BLOCK_N tile.  CTA r loads A rows
+// [m0 + 128 r, +128) and B rows (n) [n0 + BLOCK_N/2 * r, +BLOCK_N/2) into ITS shared memory; the leader (rank 0)
+// issues tcgen05.mma.cta_group::2 with M = 256, which reads A from both CTAs and the two halves of B, and
+// accumulates 128 rows in each CTA's TMEM.  Per MMA step each SM now pulls 16 KB from L2 instead of 24 KB
+// (B is shared by the pair): the 1-CTA kernel is bound by L2 -> SM operand delivery, not by the tensor pipe.
+//   full barriers   : leader's; both CTAs' TMA transfers complete_tx on them (peer bit cleared in the address)
+//   empty barriers  : per CTA; released by tcgen05.commit.cta_group::2 multicast to both CTAs
+//   tmem_full       : per CTA (multicast commit); tmem_empty: leader's, all 256 epilogue threads arrive remotely
+constexpr int A2_SLOTS = 6, B2_SLOTS = 6;
+constexpr int B2_TILE_BYTES = (MAX_BLOCK_N / 2) * BLOCK_K;  // 16 KB: half of the B tile per CTA
+constexpr int SMEM2_BYTES = A2_SLOTS * A_TILE_BYTES + B2_SLOTS * B2_TILE_BYTES + 1024 + 256;
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// TMA into THIS CTA's shared memory, transaction bytes reported to the LEADER CTA's barrier (`leader_bar` is the
+// shared::cluster address of that barrier, see leader_address()).
+__device__ __forceinline__ uint32_t leader_address(uint32_t local) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(r) : "r"(local));
+  return r;
+}
+__device__ __forceinline__ void tma_load_3d_2sm(uint32_t dst, const CUtensorMap *map, uint32_t leader_bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(dst), "l"(map), "r"(leader_bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void umma_i8_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on the barrier at this shared-memory offset in BOTH CTAs of the pair once the MMAs issued so far are done
+__device__ __forceinline__ void umma_commit_2sm(uint32_t bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+      ::"r"(bar), "h"((uint16_t)3)
+      : "memory");
+}
+// arrive on the LEADER CTA's copy of a barrier
+__device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, 0;\n\t"
+      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}"
+      ::"r"(bar)
+      : "memory");
+}
+
+__device__ __forceinline__ bool next_item_2cta(const GemmParams &p, int j, WorkItem &w) {
+  const int G = (int)(gridDim.x >> 1);           // clusters
+  const int me = (int)(blockIdx.x >> 1);
+  const int c = (j & 1) ? G - 1 - me : me;
+  const long long idx = (long long)j * G + c;
+  if (idx >= p.total_items) return false;
+  const int tiles = p.tiles_m * p.tiles_n;       // tiles of 256 x block_n
+  const int per_pass = p.nbatch * tiles;
+  w.pass = (int)(idx / per_pass);
+  const int rem = (int)(idx % per_pass);
+  w.batch = rem / tiles;
+  const int tile = rem % tiles;
+  w.m0 = (tile / p.tiles_n) * (2 * BLOCK_M);
+  w.n0 = (tile % p.tiles_n) * p.block_n;
+  return true;
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+limb_gemm_kernel_2cta(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                      const __grid_constant__ GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t *sA = smem;
+  uint8_t *sB = smem + A2_SLOTS * A_TILE_BYTES;
+  uint64_t *bars = (uint64_t *)(sB + B2_SLOTS * B2_TILE_BYTES);
+  const uint32_t bar_base = smem_u32(bars);
+  auto fullA = [&](int s) { return bar_base + 8u * s; };
+  auto emptyA = [&](int s) { return bar_base + 8u * (A2_SLOTS + s); };
+  auto fullB = [&](int s) { return bar_base + 8u * (2 * A2_SLOTS + s); };
+  auto emptyB = [&](int s) { return bar_base + 8u * (2 * A2_SLOTS + B2_SLOTS + s); };
+  const uint32_t tmem_full = bar_base + 8u * (2 * A2_SLOTS + 2 * B2_SLOTS);
+  const uint32_t tmem_empty = tmem_full + 8u;
+  uint32_t *tmem_slot = (uint32_t *)(bars + 2 * A2_SLOTS + 2 * B2_SLOTS + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < A2_SLOTS; s++) { mbar_init(fullA(s), 1); mbar_init(emptyA(s), 1); }
+    for (int s = 0; s < B2_SLOTS; s++) { mbar_init(fullB(s), 1); mbar_init(emptyB(s), 1); }
+    mbar_init(tmem_full, 1);
+    mbar_init(tmem_empty, 256);  // 128 epilogue threads of each CTA
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 5) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_slot)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  cluster_sync_all();  // both CTAs' barriers are initialised before anything is signalled across the pair
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int half_n = p.block_n >> 1;
+  const uint32_t b_half_bytes = (uint32_t)half_n * BLOCK_K;
+  const int L = p.L;
+
+  if (warp == 4) {
+    // ===================== TMA producer (both CTAs) =====================
+    if (lane == 0) {
+      int a_it = 0, b_it = 0;
+      WorkItem w;
+      for (int item = 0; next_item_2cta(p, item, w); item++) {
+        const PassDesc pd = p.passes[w.pass];
+        const int d = pd.d;
+        const int last = 2 * d + 2;
+        const int my_m0 = w.m0 + (int)rank * BLOCK_M;
+        const int my_n0 = w.n0 + (int)rank * half_n;
+        for (int u = pd.unit_begin; u < pd.unit_end; u++) {
+          const UnitDesc ud = p.units[u];
+          const int pa0 = p.plane_a[w.batch][ud.term], pb0 = p.plane_b[w.batch][ud.term];
+          for (int kb = ud.kb_begin; kb < ud.kb_end; kb++) {
+            const int k0 = kb * BLOCK_K;
+            for (int s = 0; s <= last; s++) {
+              const int t = s >> 1;
+              if ((s & 1) == 0) {
+                const int slot = a_it % A2_SLOTS;
+                mbar_wait(emptyA(slot), ((a_it / A2_SLOTS) & 1) ^ 1);
+                if (leader) mbar_expect_tx(fullA(slot), 2 * A_TILE_BYTES);  // both CTAs' halves
+                tma_load_3d_2sm(smem_u32(sA + slot * A_TILE_BYTES), &map_a, leader_address(fullA(slot)), k0, my_m0, pa0 + t);
+                a_it++;
+              }
+              if (s == 0 || (s & 1) == 1) {
+                const int j = (s == 0) ? d + 1 : d - t;
+                const int slot = b_it % B2_SLOTS;
+                mbar_wait(emptyB(slot), ((b_it / B2_SLOTS) & 1) ^ 1);
+                if (leader) mbar_expect_tx(fullB(slot), 2 * b_half_bytes);
+                tma_load_3d_2sm(smem_u32(sB + slot * B2_TILE_BYTES), &map_b, leader_address(fullB(slot)), k0, my_n0, pb0 + j);
+                b_it++;
+              }
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 5) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (leader && lane == 0) {
+      // D = S32, A = B = U8, K-major, N = block_n, M = 256 (cta_group::2)
+      const uint32_t idesc = (2u << 4) | ((uint32_t)(p.block_n >> 3) << 17) | ((uint32_t)((2 * BLOCK_M) >> 4) << 24);
+      int a_it = 0, b_it = 0;
+      int a_slot = 0, b_slot = 0;
+      uint32_t acc_phase = 0;
+      WorkItem w;
+      for (int item = 0; next_item_2cta(p, item, w); item++) {
+        const PassDesc pd = p.passes[w.pass];
+        const int d = pd.d;
+        const int last = 2 * d + 2;
+        mbar_wait(tmem_empty, acc_phase ^ 1);
+        tcgen05_fence_after();
+        bool first_lo = true, first_hi = true;
+        for (int u = pd.unit_begin; u < pd.unit_end; u++) {
+          const UnitDesc ud = p.units[u];
+          for (int kb = ud.kb_begin; kb < ud.kb_end; kb++) {
+            for (int s = 0; s <= last; s++) {
+              const bool new_a = (s & 1) == 0;
+              const bool new_b = s == 0 || (s & 1) == 1;
+              const bool hi = (s & 1) == 0;
+              const bool rel_a = (s & 1) == 1 || s == last;
+              const bool rel_b = (s & 1) == 0;
+              if (new_a) {
+                a_slot = a_it % A2_SLOTS;
+                mbar_wait(fullA(a_slot), (a_it / A2_SLOTS) & 1);
+                a_it++;
+              }
+              if (new_b) {
+                b_slot = b_it % B2_SLOTS;
+                mbar_wait(fullB(b_slot), (b_it / B2_SLOTS) & 1);
+                b_it++;
+              }
+              tcgen05_fence_after();
+              const uint64_t adesc = make_smem_desc(smem_u32(sA + a_slot * A_TILE_BYTES));
+              const uint64_t bdesc = make_smem_desc(smem_u32(sB + b_slot * B2_TILE_BYTES));
+              const uint32_t tmem_d = tmem_base + (hi ? (uint32_t)MAX_BLOCK_N : 0u);
+              bool &first = hi ? first_hi : first_lo;
+#pragma unroll
+              for (int k = 0; k < BLOCK_K / UMMA_K; k++) {
+                umma_i8_2sm(tmem_d, adesc + (uint64_t)(k * UMMA_K >> 4), bdesc + (uint64_t)(k * UMMA_K >> 4), idesc,
+                            (first && k == 0) ? 0u : 1u);
+              }
+              first = false;
+              if (rel_a) umma_commit_2sm(emptyA(a_slot));
+              if (rel_b) umma_commit_2sm(emptyB(b_slot));
+            }
+          }
+        }
+        umma_commit_2sm(tmem_full);
+        acc_phase ^= 1;
+      }
+    }
+  } else {
+    // ===================== epilogue (both CTAs; this CTA owns rows m0 + 128 rank ..) =====================
+    uint32_t acc_phase = 0;
+    WorkItem w;
+    for (int item = 0; next_item_2cta(p, item, w); item++) {
+      const int row = w.m0 + (int)rank * BLOCK_M + warp * 32 + lane;
+      const int n0 = w.n0;
+      mbar_wait_relaxed(tmem_full, acc_phase);
+      tcgen05_fence_after();
+      unsigned long long *out =
+          p.partials + (((size_t)w.batch * p.num_passes + (size_t)w.pass) * p.M + (size_t)row) * p.N + n0;
+      for (int c = 0; c < p.block_n; c += 32) {
+        uint32_t lo[32], hi[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c;
+        tmem_ld32(taddr, lo);
+        tmem_ld32(taddr + MAX_BLOCK_N, hi);
+        tmem_ld_wait();
+        if (row < p.M) {
+          if (n0 + c + 32 <= p.N) {
+#pragma unroll
+            for (int q = 0; q < 32; q += 2) {
+              unsigned long long v0 = (unsigned long long)lo[q] + ((unsigned long long)hi[q] << 8);
+              unsigned long long v1 = (unsigned long long)lo[q + 1] + ((unsigned long long)hi[q + 1] << 8);
+              *(ulonglong2 *)(out + c + q) = make_ulonglong2(v0, v1);
+            }
+          } else {
+#pragma unroll
+            for (int q = 0; q < 32; q++) {
+              if (n0 + c + q < p.N) out[c + q] = (unsigned long long)lo[q] + ((unsigned long long)hi[q] << 8);
+            }
+          }
+        }
+      }
+      tcgen05_fence_before();
+      mbar_arrive_leader(tmem_empty);
+      acc_phase ^= 1;
+    }
+  }
+
+  tcgen05_fence_before();
+  cluster_sync_all();  // neither CTA may exit (or free TMEM) while the pair still signals / reads across
+  if (warp == 5) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
   }
 }
 
@@ -511,74 +814,105 @@ bool k_gemm_limb_supported(mb_dtype dtype, int64_t M, int64_t K, int64_t N) {
   return plan_fits(dtype, 2, K, passes, units);  // worst case: the two-term form used by mb_rep_dot
 }
 
-int k_gemm_limb(mb_ctx *ctx, mb_dtype dtype, const GemmTerm *terms, int nterms, void *C, int64_t M, int64_t K, int64_t N) {
+// Batched ring GEMM:  C[b] = sum_{t < nterms} A[a_idx[b][t]] * B[b_idx[b][t]]   for b < nbatch,
+// where the distinct operands are limb-split once (A: nA matrices [M,K]; B: nB matrices [K,N], each optionally
+// the sum of two tensors).  mb_rep_dot uses nbatch = 3, nterms = 2, nA = 3 (x_0,x_1,x_2) and nB = 6.
+int k_gemm_limb_batched(mb_ctx *ctx, mb_dtype dtype, const LimbOperandA *As, int nA, const LimbOperandB *Bs, int nB,
+                        const int (*a_idx)[2], const int (*b_idx)[2], int nbatch, int nterms, void *const *C, int64_t M,
+                        int64_t K, int64_t N) {
   const int L = dtype == MB_RING128 ? 16 : 8;
-  const int kbits = 8 * L;
   const int64_t Kp = (K + BLOCK_K - 1) / BLOCK_K * BLOCK_K;
-  const int64_t kblocks = Kp / BLOCK_K;
   const int block_n = N >= 256 ? 256 : (N >= 128 ? 128 : 64);
 
   std::vector<PassDesc> passes;
   std::vector<UnitDesc> units;
   if (nterms < 1 || nterms > 2) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "limb GEMM: 1 or 2 operand pairs");
+  if (nbatch < 1 || nbatch > MAX_BATCH) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "limb GEMM: batch out of range");
+  if ((int64_t)(nA > nB ? nA : nB) * L > 32000) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "limb GEMM: too many operands");
   if (!plan_fits(dtype, nterms, K, passes, units))
     return mb_fail(ctx, MB_ERR_KERNEL, "limb GEMM: K too large for the pass table");
-  (void)kbits;
-  (void)kblocks;
+  // longest passes first (static LPT schedule); cost = MMA steps
+  auto cost = [&](const PassDesc &pd) {
+    int64_t kb = 0;
+    for (int u = pd.unit_begin; u < pd.unit_end; u++) kb += units[u].kb_end - units[u].kb_begin;
+    return kb * (pd.d + 1 < L ? 2 * pd.d + 3 : pd.d + 1);
+  };
+  std::stable_sort(passes.begin(), passes.end(), [&](const PassDesc &x, const PassDesc &y) { return cost(x) > cost(y); });
 
-  const size_t a_bytes = (size_t)nterms * L * M * Kp;
-  const size_t b_bytes = (size_t)nterms * L * N * Kp;
-  const size_t part_bytes = passes.size() * (size_t)M * N * 8;
+  const size_t a_plane_bytes = (size_t)L * M * Kp, b_plane_bytes = (size_t)L * N * Kp;
+  const size_t a_bytes = (size_t)nA * a_plane_bytes;
+  const size_t b_bytes = (size_t)nB * b_plane_bytes;
+  const size_t part_bytes = (size_t)nbatch * passes.size() * (size_t)M * N * 8;
   void *dA, *dB, *dP;
   MB_CHECK(mb_scratch(ctx, 0, a_bytes, &dA));
   MB_CHECK(mb_scratch(ctx, 1, b_bytes, &dB));
   MB_CHECK(mb_scratch(ctx, 2, part_bytes, &dP));
 
-  // operand preparation
-  if (Kp != K) {
-    MB_CUDA(ctx, cudaMemsetAsync(dA, 0, a_bytes, ctx->stream));
-    MB_CUDA(ctx, cudaMemsetAsync(dB, 0, b_bytes, ctx->stream));
+  // operand preparation: every distinct operand is split into byte planes once
+  if (Kp != K) MB_CUDA(ctx, cudaMemsetAsync(dA, 0, a_bytes, ctx->stream));
+  const int64_t quads = M * ((K + 3) / 4);
+  dim3 gb((unsigned)((N + 31) / 32), (unsigned)((Kp + 31) / 32));
+  for (int i = 0; i < nA; i++) {
+    uint8_t *pa = (uint8_t *)dA + (size_t)i * a_plane_bytes;
+    if (dtype == MB_RING128)
+      split_a_kernel<u128><<<(unsigned)((quads + 255) / 256), 256, 0, ctx->stream>>>((const u128 *)As[i].ptr, pa, M, K, Kp);
+    else
+      split_a_kernel<uint64_t><<<(unsigned)((quads + 255) / 256), 256, 0, ctx->stream>>>((const uint64_t *)As[i].ptr, pa, M, K, Kp);
+    MB_LAUNCH_CHECK(ctx);
   }
-  for (int t = 0; t < nterms; t++) {
-    uint8_t *pa = (uint8_t *)dA + (size_t)t * L * M * Kp;
-    uint8_t *pb = (uint8_t *)dB + (size_t)t * L * N * Kp;
-    const int64_t quads = M * ((K + 3) / 4);
-    dim3 gb((unsigned)((N + 31) / 32), (unsigned)((Kp + 31) / 32));
-    if (dtype == MB_RING128) {
-      split_a_kernel<u128><<<(unsigned)((quads + 255) / 256), 256, 0, ctx->stream>>>((const u128 *)terms[t].A, pa, M, K, Kp);
-      MB_LAUNCH_CHECK(ctx);
-      split_bt_kernel<u128><<<gb, 256, 0, ctx->stream>>>((const u128 *)terms[t].B0, (const u128 *)terms[t].B1, pb, K, N, Kp);
-      MB_LAUNCH_CHECK(ctx);
-    } else {
-      split_a_kernel<uint64_t><<<(unsigned)((quads + 255) / 256), 256, 0, ctx->stream>>>((const uint64_t *)terms[t].A, pa, M, K, Kp);
-      MB_LAUNCH_CHECK(ctx);
-      split_bt_kernel<uint64_t><<<gb, 256, 0, ctx->stream>>>((const uint64_t *)terms[t].B0, (const uint64_t *)terms[t].B1, pb, K, N, Kp);
-      MB_LAUNCH_CHECK(ctx);
-    }
+  for (int i = 0; i < nB; i++) {
+    uint8_t *pb = (uint8_t *)dB + (size_t)i * b_plane_bytes;
+    if (dtype == MB_RING128)
+      split_bt_kernel<u128><<<gb, 256, 0, ctx->stream>>>((const u128 *)Bs[i].b0, (const u128 *)Bs[i].b1, pb, K, N, Kp);
+    else
+      split_bt_kernel<uint64_t><<<gb, 256, 0, ctx->stream>>>((const uint64_t *)Bs[i].b0, (const uint64_t *)Bs[i].b1, pb, K, N, Kp);
+    MB_LAUNCH_CHECK(ctx);
   }
 
+  const bool use_pair = ctx->gemm_pair_mode != 1 && M >= 2 * BLOCK_M && N >= 128;
   CUtensorMap map_a, map_b;
-  MB_CHECK(make_plane_map(ctx, &map_a, dA, Kp, M, (int64_t)nterms * L, BLOCK_M));
-  MB_CHECK(make_plane_map(ctx, &map_b, dB, Kp, N, (int64_t)nterms * L, block_n));
+  MB_CHECK(make_plane_map(ctx, &map_a, dA, Kp, M, (int64_t)nA * L, BLOCK_M));
+  MB_CHECK(make_plane_map(ctx, &map_b, dB, Kp, N, (int64_t)nB * L, use_pair ? block_n / 2 : block_n));
 
   GemmParams gp;
   memset(&gp, 0, sizeof(gp));
   memcpy(gp.passes, passes.data(), passes.size() * sizeof(PassDesc));
   memcpy(gp.units, units.data(), units.size() * sizeof(UnitDesc));
+  for (int b = 0; b < nbatch; b++)
+    for (int t = 0; t < nterms; t++) {
+      if (a_idx[b][t] < 0 || a_idx[b][t] >= nA || b_idx[b][t] < 0 || b_idx[b][t] >= nB)
+        return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "limb GEMM: operand index out of range");
+      gp.plane_a[b][t] = (short)(a_idx[b][t] * L);
+      gp.plane_b[b][t] = (short)(b_idx[b][t] * L);
+    }
   gp.num_passes = (int)passes.size();
+  gp.nbatch = nbatch;
   gp.L = L;
   gp.M = (int)M;
   gp.N = (int)N;
   gp.block_n = block_n;
-  gp.tiles_m = (int)((M + BLOCK_M - 1) / BLOCK_M);
+  // CTA pairs (cta_group::2, 256-row tiles) whenever the problem is large enough; L = 8 / 16 is even, so
+  // every pass is a full diagonal pair as the 2-CTA kernel assumes
+  const bool pair = use_pair;
+  const int tile_m = pair ? 2 * BLOCK_M : BLOCK_M;
+  gp.tiles_m = (int)((M + tile_m - 1) / tile_m);
   gp.tiles_n = (int)((N + block_n - 1) / block_n);
+  const int64_t total = (int64_t)gp.num_passes * nbatch * gp.tiles_m * gp.tiles_n;
+  if (total > INT32_MAX) return mb_fail(ctx, MB_ERR_KERNEL, "limb GEMM: too many work items");
+  gp.total_items = (int)total;
   gp.partials = (unsigned long long *)dP;
 
-  MB_CUDA(ctx, cudaFuncSetAttribute(limb_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-  const int grid = std::min(gp.tiles_m * gp.tiles_n, ctx->sm_count);
   cudaEvent_t prof_start;
   MB_CHECK(mb_prof_begin(ctx, &prof_start));
-  limb_gemm_kernel<<<grid, NUM_THREADS, SMEM_BYTES, ctx->stream>>>(map_a, map_b, gp);
+  if (pair) {
+    MB_CUDA(ctx, cudaFuncSetAttribute(limb_gemm_kernel_2cta, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES));
+    const int clusters = (int)std::min<int64_t>(total, ctx->sm_count / 2);
+    limb_gemm_kernel_2cta<<<2 * clusters, NUM_THREADS, SMEM2_BYTES, ctx->stream>>>(map_a, map_b, gp);
+  } else {
+    MB_CUDA(ctx, cudaFuncSetAttribute(limb_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    const int grid = (int)std::min<int64_t>(total, ctx->sm_count);
+    limb_gemm_kernel<<<grid, NUM_THREADS, SMEM_BYTES, ctx->stream>>>(map_a, map_b, gp);
+  }
   MB_LAUNCH_CHECK(ctx);
   MB_CHECK(mb_prof_end(ctx, prof_start));
 
@@ -586,12 +920,29 @@ int k_gemm_limb(mb_ctx *ctx, mb_dtype dtype, const GemmTerm *terms, int nterms, 
   rd.num_passes = (int)passes.size();
   for (size_t i = 0; i < passes.size(); i++) rd.shift[i] = 8 * passes[i].d;
   const int64_t MN = M * N;
-  if (dtype == MB_RING128)
-    recombine_kernel<u128><<<(unsigned)((MN + 255) / 256), 256, 0, ctx->stream>>>((const unsigned long long *)dP, (u128 *)C, MN, rd);
-  else
-    recombine_kernel<uint64_t><<<(unsigned)((MN + 255) / 256), 256, 0, ctx->stream>>>((const unsigned long long *)dP, (uint64_t *)C, MN, rd);
-  MB_LAUNCH_CHECK(ctx);
+  for (int b = 0; b < nbatch; b++) {
+    const unsigned long long *pp = (const unsigned long long *)dP + (size_t)b * passes.size() * MN;
+    if (dtype == MB_RING128)
+      recombine_kernel<u128><<<(unsigned)((MN + 255) / 256), 256, 0, ctx->stream>>>(pp, (u128 *)C[b], MN, rd);
+    else
+      recombine_kernel<uint64_t><<<(unsigned)((MN + 255) / 256), 256, 0, ctx->stream>>>(pp, (uint64_t *)C[b], MN, rd);
+    MB_LAUNCH_CHECK(ctx);
+  }
   return MB_OK;
+}
+
+int k_gemm_limb(mb_ctx *ctx, mb_dtype dtype, const GemmTerm *terms, int nterms, void *C, int64_t M, int64_t K, int64_t N) {
+  if (nterms < 1 || nterms > 2) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "limb GEMM: 1 or 2 operand pairs");
+  LimbOperandA As[2];
+  LimbOperandB Bs[2];
+  int a_idx[1][2] = {{0, 1}}, b_idx[1][2] = {{0, 1}};
+  for (int t = 0; t < nterms; t++) {
+    As[t].ptr = terms[t].A;
+    Bs[t].b0 = terms[t].B0;
+    Bs[t].b1 = terms[t].B1;
+  }
+  void *Cs[1] = {C};
+  return k_gemm_limb_batched(ctx, dtype, As, nterms, Bs, nterms, a_idx, b_idx, 1, nterms, Cs, M, K, N);
 }
 
 // =====================================================================================
@@ -713,16 +1064,18 @@ extern "C" int mb_dot_noalloc(mb_ctx *ctx, mb_dtype dtype, const void *a_dev, co
   MB_CHECK(make_plane_map(ctx, &map_a, dA, Kp, M, L, BLOCK_M));
   MB_CHECK(make_plane_map(ctx, &map_b, dB, Kp, N, L, block_n));
 
+  gp.nbatch = 1;  // plane_a / plane_b stay 0: one operand pair
   gp.L = L;
   gp.M = (int)M;
   gp.N = (int)N;
   gp.block_n = block_n;
   gp.tiles_m = (int)((M + BLOCK_M - 1) / BLOCK_M);
   gp.tiles_n = (int)((N + block_n - 1) / block_n);
+  gp.total_items = gp.num_passes * gp.tiles_m * gp.tiles_n;
   gp.partials = dP;
 
   MB_CUDA(ctx, cudaFuncSetAttribute(limb_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-  const int grid = std::min(gp.tiles_m * gp.tiles_n, ctx->sm_count);
+  const int grid = std::min(gp.total_items, ctx->sm_count);
   limb_gemm_kernel<<<grid, NUM_THREADS, SMEM_BYTES, ctx->stream>>>(map_a, map_b, gp);
   MB_LAUNCH_CHECK(ctx);
 

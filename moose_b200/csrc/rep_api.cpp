@@ -334,12 +334,25 @@ extern "C" int mb_rep_dot(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep 
   const bool use_limb = limb_ok && (ctx->gemm_mode == 2 || (ctx->gemm_mode == 0 && k_gemm_limb_preferred(M, 2 * K, N)));
   // v_i = x_i.y_i + x_i.y_{i+1} + x_{i+1}.y_i = x_i.(y_i + y_{i+1}) + x_{i+1}.y_i   (arith.rs:461-469;
   // identical mod 2^k, one GEMM less per party)
-  for (int i = 0; i < 3; i++) {
-    int j = (i + 1) % 3;
-    if (use_limb) {
-      GemmTerm terms[2] = {{x->s[i]->dptr, y->s[i]->dptr, y->s[j]->dptr}, {x->s[j]->dptr, y->s[i]->dptr, nullptr}};
-      MB_CHECK(k_gemm_limb(ctx, dt, terms, 2, z.p->s[i]->dptr, M, K, N));
-    } else {
+  if (use_limb) {
+    // one batched launch for the three parties; x_0,x_1,x_2 are limb-split once each
+    LimbOperandA As[3];
+    LimbOperandB Bs[6];
+    int a_idx[3][2], b_idx[3][2];
+    void *Cs[3];
+    for (int i = 0; i < 3; i++) {
+      int j = (i + 1) % 3;
+      As[i].ptr = x->s[i]->dptr;
+      Bs[i].b0 = y->s[i]->dptr;      Bs[i].b1 = y->s[j]->dptr;   // y_i + y_{i+1}
+      Bs[3 + i].b0 = y->s[i]->dptr;  Bs[3 + i].b1 = nullptr;     // y_i
+      a_idx[i][0] = i;  b_idx[i][0] = i;
+      a_idx[i][1] = j;  b_idx[i][1] = 3 + i;
+      Cs[i] = z.p->s[i]->dptr;
+    }
+    MB_CHECK(k_gemm_limb_batched(ctx, dt, As, 3, Bs, 6, a_idx, b_idx, 3, 2, Cs, M, K, N));
+  } else {
+    for (int i = 0; i < 3; i++) {
+      int j = (i + 1) % 3;
       Tmp ysum(ctx);
       MB_CHECK(mb_add(ctx, y->s[i], y->s[j], &ysum.p));
       MB_CHECK(k_gemm_imad(ctx, dt, x->s[i]->dptr, ysum.p->dptr, z.p->s[i]->dptr, M, K, N, false));

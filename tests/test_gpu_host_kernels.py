@@ -265,15 +265,17 @@ def test_fixedpoint_encode_decode(sess, bits, frac):
                           mo.fixed_decode(mo.Ring(bits, w), frac))
 
 
+@pytest.mark.parametrize("mode", [2, 3])
 @pytest.mark.parametrize("bits", [64, 128])
 @pytest.mark.parametrize("M,K,N", [(128, 128, 64), (128, 256, 256), (256, 128, 128), (300, 200, 130), (129, 1000, 514),
-                                   (512, 1024, 512)])
-def test_dot_parity_tensor_pipe(sess, bits, M, K, N):
-    """tcgen05 int8 limb GEMM (gemm mode 2) against the oracle: full-range random ring elements, ragged
-    M / K / N (TMA zero fill, padded K, predicated epilogue)."""
+                                   (512, 1024, 512), (700, 384, 258)])
+def test_dot_parity_tensor_pipe(sess, bits, M, K, N, mode):
+    """tcgen05 int8 limb GEMM against the oracle: full-range random ring elements, ragged M / K / N (TMA
+    zero fill, padded K, predicated epilogue).  Mode 2 uses CTA pairs (cta_group::2, 256-row tiles) where
+    the shape allows, mode 3 forces single-CTA tiles."""
     rng = np.random.default_rng(M * 7 + K * 3 + N)
     a, b = rand_ring(rng, bits, (M, K)), rand_ring(rng, bits, (K, N))
-    sess.set_gemm_mode(2)
+    sess.set_gemm_mode(mode)
     try:
         z = sess.dot(sess.from_host(DT[bits], a), sess.from_host(DT[bits], b))
     finally:
