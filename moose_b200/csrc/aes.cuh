@@ -2,78 +2,104 @@
 //   block(i) = AES-128_seed(LE128(i)),   i = 0, 1, 2, ...
 // (restatement pinned by moose/src/host/mod.rs:1050-1079, see oracle/).
 //
-// T-table formulation with ONE 256-entry table (Te0) and byte rotations.  The
-// table is replicated 32x in shared memory, laid out [256][32] words, and lane l
-// only ever reads column l: every lookup of a warp hits 32 distinct banks, so
-// the data-dependent lookups are bank-conflict free (1 LDS wavefront each).
-// Cost: 32 KB of shared memory per CTA.
+// The PRF kernels are issue-bound (every SMSP issues one instruction per clock and an AES block is
+// several hundred of them), so the formulation minimises INSTRUCTIONS per block, not memory traffic:
+//  * T-table rounds with two tables, Te0 and Te2 = rotl16(Te0), interleaved in shared memory as
+//    sT[256][64] words: row idx holds 32 copies of Te0[idx] then 32 copies of Te2[idx].  Lane l reads
+//    column l (or 32 + l), so the data-dependent lookups never bank-conflict, and -- the row stride
+//    being exactly 256 bytes -- the byte offset of a lookup, (byte_k(x) << 8) | lane*4 [| 128], is
+//    ONE PRMT of the state word with a per-lane constant.  Lookups of byte positions 1 and 3 take
+//    rotl8 of the Te0 / Te2 value (one more PRMT); positions 0 and 2 need no rotation.
+//  * Round 1: the counter block is LE128(ctr) with ctr < 2^32 for every tensor below 64 GB, so only
+//    the first state word depends on ctr; the 12 constant lookups of round 1 are folded on the host into
+//    four words per key (AesKey::r1c).  Larger counters take the generic path.
+//  * Last round: S[x] is byte 0 / 3 of Te2[x] and byte 1 / 2 of Te0[x]; three PRMTs assemble a column.
+// Cost: 64 KB of dynamic shared memory per CTA (3 CTAs of 256 threads per SM).
 #pragma once
 #include <cstdint>
 
 #include "common.h"
 
-#define AES_TABLE_WORDS (256 * 32)
+#define AES_TABLE_WORDS (256 * 64)
+#define AES_SMEM_BYTES (AES_TABLE_WORDS * 4)
 
-// Te0[x] = {2*S[x], S[x], S[x], 3*S[x]} as a little-endian word (one copy per
-// translation unit, read once per CTA when the shared-memory table is built).
+// Te0[x] = {2*S[x], S[x], S[x], 3*S[x]} as a little-endian word (one copy per translation unit,
+// read once per CTA when the shared-memory table is built).
 static __device__ const uint32_t c_Te0[256] = {
 #include "aes_te0.inc"
 };
 
+// sT[idx][0..31] = Te0[idx], sT[idx][32..63] = rotl16(Te0[idx])
 __device__ __forceinline__ void aes_load_table(uint32_t *sT) {
-  // sT[idx * 32 + lane]
-  for (int i = threadIdx.x; i < AES_TABLE_WORDS; i += blockDim.x) sT[i] = c_Te0[i >> 5];
+  for (int i = threadIdx.x; i < AES_TABLE_WORDS; i += blockDim.x) {
+    uint32_t t = c_Te0[i >> 6];
+    sT[i] = (i & 32) ? __byte_perm(t, t, 0x1032) : t;
+  }
   __syncthreads();
 }
 
-__device__ __forceinline__ uint32_t rotl8(uint32_t x) { return __byte_perm(x, x, 0x2103); }
-__device__ __forceinline__ uint32_t rotl16(uint32_t x) { return __byte_perm(x, x, 0x1032); }
-__device__ __forceinline__ uint32_t rotl24(uint32_t x) { return __byte_perm(x, x, 0x0321); }
+struct AesLane {
+  const unsigned char *tab;  // shared-memory table base
+  uint32_t l0, l2;           // lane*4 (Te0 half) and lane*4 + 128 (Te2 half)
+};
+__device__ __forceinline__ AesLane aes_lane(const uint32_t *sT) {
+  AesLane a;
+  a.tab = (const unsigned char *)sT;
+  a.l0 = (threadIdx.x & 31) * 4;
+  a.l2 = a.l0 + 128;
+  return a;
+}
 
-// Encrypts the counter block LE128(ctr) (ctr < 2^64).  `sTl` = sT + lane.
-// out[0..3] are the 16 keystream bytes as little-endian words.
-__device__ __forceinline__ void aes_ctr_block(const uint32_t *__restrict__ sTl, const AesKey &k, uint64_t ctr,
-                                              uint32_t out[4]) {
+// table value for byte K of x: one PRMT builds the byte offset (byte_K(x) << 8) | lane constant
+template <int K>
+__device__ __forceinline__ uint32_t te0(const AesLane &a, uint32_t x) {
+  return *(const uint32_t *)(a.tab + __byte_perm(x, a.l0, 0x6504 | (K << 4)));
+}
+template <int K>
+__device__ __forceinline__ uint32_t te2(const AesLane &a, uint32_t x) {
+  return *(const uint32_t *)(a.tab + __byte_perm(x, a.l2, 0x6504 | (K << 4)));
+}
+__device__ __forceinline__ uint32_t rotl8(uint32_t x) { return __byte_perm(x, x, 0x2103); }
+
+// Encrypts the counter block LE128(ctr) (ctr < 2^64).  out[0..3] are the 16 keystream bytes as
+// little-endian words.
+__device__ __forceinline__ void aes_ctr_block(const AesLane &a, const AesKey &k, uint64_t ctr, uint32_t out[4]) {
   uint32_t s0 = (uint32_t)ctr ^ k.rk[0];
-  uint32_t s1 = (uint32_t)(ctr >> 32) ^ k.rk[1];
-  uint32_t s2 = k.rk[2];
-  uint32_t s3 = k.rk[3];
-#define TE(x) sTl[((x)&0xffu) << 5]
-#pragma unroll
-  for (int r = 1; r < 10; r++) {
-    uint32_t t0 = TE(s0) ^ rotl8(TE(s1 >> 8)) ^ rotl16(TE(s2 >> 16)) ^ rotl24(TE(s3 >> 24)) ^ k.rk[4 * r];
-    uint32_t t1 = TE(s1) ^ rotl8(TE(s2 >> 8)) ^ rotl16(TE(s3 >> 16)) ^ rotl24(TE(s0 >> 24)) ^ k.rk[4 * r + 1];
-    uint32_t t2 = TE(s2) ^ rotl8(TE(s3 >> 8)) ^ rotl16(TE(s0 >> 16)) ^ rotl24(TE(s1 >> 24)) ^ k.rk[4 * r + 2];
-    uint32_t t3 = TE(s3) ^ rotl8(TE(s0 >> 8)) ^ rotl16(TE(s1 >> 16)) ^ rotl24(TE(s2 >> 24)) ^ k.rk[4 * r + 3];
+  uint32_t s1, s2, s3;
+  const uint32_t hi = (uint32_t)(ctr >> 32);
+  if (hi == 0) {
+    // round 1 with the constant lookups pre-folded into k.r1c
+    uint32_t t0 = te0<0>(a, s0) ^ k.r1c[0];
+    uint32_t t1 = rotl8(te2<3>(a, s0)) ^ k.r1c[1];
+    uint32_t t2 = te2<2>(a, s0) ^ k.r1c[2];
+    uint32_t t3 = rotl8(te0<1>(a, s0)) ^ k.r1c[3];
+    s0 = t0; s1 = t1; s2 = t2; s3 = t3;
+  } else {
+    s1 = hi ^ k.rk[1];
+    s2 = k.rk[2];
+    s3 = k.rk[3];
+    uint32_t t0 = te0<0>(a, s0) ^ rotl8(te0<1>(a, s1)) ^ te2<2>(a, s2) ^ rotl8(te2<3>(a, s3)) ^ k.rk[4];
+    uint32_t t1 = te0<0>(a, s1) ^ rotl8(te0<1>(a, s2)) ^ te2<2>(a, s3) ^ rotl8(te2<3>(a, s0)) ^ k.rk[5];
+    uint32_t t2 = te0<0>(a, s2) ^ rotl8(te0<1>(a, s3)) ^ te2<2>(a, s0) ^ rotl8(te2<3>(a, s1)) ^ k.rk[6];
+    uint32_t t3 = te0<0>(a, s3) ^ rotl8(te0<1>(a, s0)) ^ te2<2>(a, s1) ^ rotl8(te2<3>(a, s2)) ^ k.rk[7];
     s0 = t0; s1 = t1; s2 = t2; s3 = t3;
   }
-  // Last round: SubBytes + ShiftRows only.  S[x] is byte 1 of Te0[x].
-  // out byte j of column c = S[ byte j of s_{c+j} ].
-#define SB(x, pos) ((TE(x) & 0x0000ff00u) >> 8 << (pos))
-  out[0] = (SB(s0, 0) | SB(s1 >> 8, 8) | SB(s2 >> 16, 16) | SB(s3 >> 24, 24)) ^ k.rk[40];
-  out[1] = (SB(s1, 0) | SB(s2 >> 8, 8) | SB(s3 >> 16, 16) | SB(s0 >> 24, 24)) ^ k.rk[41];
-  out[2] = (SB(s2, 0) | SB(s3 >> 8, 8) | SB(s0 >> 16, 16) | SB(s1 >> 24, 24)) ^ k.rk[42];
-  out[3] = (SB(s3, 0) | SB(s0 >> 8, 8) | SB(s1 >> 16, 16) | SB(s2 >> 24, 24)) ^ k.rk[43];
-#undef SB
-#undef TE
-}
-
-// PRF stream element helpers -------------------------------------------------
-// Ring128 element e = (first_u64 << 64) + second_u64 of block e
-// (moose/src/host/ops.rs:1998-2000): hi = bytes 0..7, lo = bytes 8..15.
-__device__ __forceinline__ u128 aes_ring128(const uint32_t *sTl, const AesKey &k, uint64_t e) {
-  uint32_t o[4];
-  aes_ctr_block(sTl, k, e, o);
-  uint64_t hi = (uint64_t)o[0] | ((uint64_t)o[1] << 32);
-  uint64_t lo = (uint64_t)o[2] | ((uint64_t)o[3] << 32);
-  return ((u128)hi << 64) | (u128)lo;
-}
-// Ring64 elements 2b and 2b+1 = the two little-endian u64 halves of block b
-// (moose/src/host/ops.rs:1969).
-__device__ __forceinline__ void aes_ring64_pair(const uint32_t *sTl, const AesKey &k, uint64_t b, uint64_t &e0,
-                                                uint64_t &e1) {
-  uint32_t o[4];
-  aes_ctr_block(sTl, k, b, o);
-  e0 = (uint64_t)o[0] | ((uint64_t)o[1] << 32);
-  e1 = (uint64_t)o[2] | ((uint64_t)o[3] << 32);
+#pragma unroll
+  for (int r = 2; r < 10; r++) {
+    uint32_t t0 = te0<0>(a, s0) ^ rotl8(te0<1>(a, s1)) ^ te2<2>(a, s2) ^ rotl8(te2<3>(a, s3)) ^ k.rk[4 * r];
+    uint32_t t1 = te0<0>(a, s1) ^ rotl8(te0<1>(a, s2)) ^ te2<2>(a, s3) ^ rotl8(te2<3>(a, s0)) ^ k.rk[4 * r + 1];
+    uint32_t t2 = te0<0>(a, s2) ^ rotl8(te0<1>(a, s3)) ^ te2<2>(a, s0) ^ rotl8(te2<3>(a, s1)) ^ k.rk[4 * r + 2];
+    uint32_t t3 = te0<0>(a, s3) ^ rotl8(te0<1>(a, s0)) ^ te2<2>(a, s1) ^ rotl8(te2<3>(a, s2)) ^ k.rk[4 * r + 3];
+    s0 = t0; s1 = t1; s2 = t2; s3 = t3;
+  }
+  // Last round: SubBytes + ShiftRows.  Output byte j of column c is S[byte j of s_{c+j}]:
+  //   byte 0 = Te2[.].b0, byte 1 = Te0[.].b1, byte 2 = Te0[.].b2, byte 3 = Te2[.].b3.
+#define AES_LAST(w0, w1, w2, w3, rkw)                                                     \
+  (__byte_perm(__byte_perm(te2<0>(a, w0), te0<1>(a, w1), 0x0050),                         \
+               __byte_perm(te0<2>(a, w2), te2<3>(a, w3), 0x7200), 0x7610) ^ (rkw))
+  out[0] = AES_LAST(s0, s1, s2, s3, k.rk[40]);
+  out[1] = AES_LAST(s1, s2, s3, s0, k.rk[41]);
+  out[2] = AES_LAST(s2, s3, s0, s1, k.rk[42]);
+  out[3] = AES_LAST(s3, s0, s1, s2, k.rk[43]);
+#undef AES_LAST
 }

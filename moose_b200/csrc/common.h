@@ -33,9 +33,11 @@ struct mb_rep {
   mb_tensor *s[3];
 };
 
-// AES-128 expanded key as 44 little-endian column words.
+// AES-128 expanded key as 44 little-endian column words, plus the round-1 constants of the counter-mode
+// stream (the part of round 1 that does not depend on a counter < 2^32, see aes.cuh).
 struct AesKey {
   uint32_t rk[44];
+  uint32_t r1c[4];
 };
 
 struct mb_ctx {

@@ -147,6 +147,26 @@ void mb_aes_expand(const uint8_t key[16], AesKey *out) {
     }
     w[i] = w[i - 4] ^ t;
   }
+  // Round-1 constants for counter blocks LE128(ctr), ctr < 2^32: state words 1..3 are rk[1..3].
+  auto te0 = [](uint32_t x) {
+    uint32_t sb = SBOX[x & 0xff];
+    uint32_t s2 = xt((uint8_t)sb), s3 = s2 ^ sb;
+    return s2 | (sb << 8) | (sb << 16) | (s3 << 24);
+  };
+  auto rotl = [](uint32_t v, int n) { return (v << n) | (v >> (32 - n)); };
+  auto col = [&](uint32_t b0, int use0, uint32_t b1, int use1, uint32_t b2, int use2, uint32_t b3, int use3, uint32_t rk) {
+    uint32_t v = rk;
+    if (use0) v ^= te0(b0);
+    if (use1) v ^= rotl(te0(b1 >> 8), 8);
+    if (use2) v ^= rotl(te0(b2 >> 16), 16);
+    if (use3) v ^= rotl(te0(b3 >> 24), 24);
+    return v;
+  };
+  const uint32_t s1 = w[1], s2 = w[2], s3 = w[3];
+  out->r1c[0] = col(0, 0, s1, 1, s2, 1, s3, 1, w[4]);  // t0 = Te0[s0.b0] ^ ...
+  out->r1c[1] = col(s1, 1, s2, 1, s3, 1, 0, 0, w[5]);  // t1 = ... ^ rotl24(Te0[s0.b3])
+  out->r1c[2] = col(s2, 1, s3, 1, 0, 0, s1, 1, w[6]);  // t2 = ... ^ rotl16(Te0[s0.b2]) ...
+  out->r1c[3] = col(s3, 1, 0, 0, s1, 1, s2, 1, w[7]);  // t3 = ... ^ rotl8(Te0[s0.b1]) ...
 }
 
 void mb_aes_encrypt_host(const AesKey *k, const uint8_t in[16], uint8_t out[16]) {

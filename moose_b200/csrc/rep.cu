@@ -13,10 +13,17 @@ namespace {
 
 constexpr int TPB = 256;
 
-#define PRF_PROLOGUE()                     \
-  __shared__ uint32_t sT[AES_TABLE_WORDS]; \
-  aes_load_table(sT);                      \
-  const uint32_t *sTl = sT + (threadIdx.x & 31)
+#define PRF_PROLOGUE()                             \
+  extern __shared__ __align__(16) uint32_t sT[];   \
+  aes_load_table(sT);                              \
+  const AesLane sTl = aes_lane(sT)
+
+// AES kernels need 64 KB of dynamic shared memory for the lookup table.
+#define AES_LAUNCH(ctx, kern, grid, ...)                                                                        \
+  do {                                                                                                          \
+    MB_CUDA((ctx), cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, AES_SMEM_BYTES));    \
+    kern<<<(grid), TPB, AES_SMEM_BYTES, (ctx)->stream>>>(__VA_ARGS__);                                          \
+  } while (0)
 
 #define VEC_LOOP(v, nvec) \
   for (int64_t v = (int64_t)blockIdx.x * TPB + threadIdx.x; v < (nvec); v += (int64_t)gridDim.x * TPB)
@@ -193,7 +200,7 @@ __global__ void __launch_bounds__(TPB) trunc_pr_kernel(AesKey kr, AesKey ka, Aes
 }
 
 inline int grid_for(mb_ctx *ctx, int64_t nvec) {
-  return (int)std::max<int64_t>(1, std::min<int64_t>((nvec + TPB - 1) / TPB, (int64_t)ctx->sm_count * 6));
+  return (int)std::max<int64_t>(1, std::min<int64_t>((nvec + TPB - 1) / TPB, (int64_t)ctx->sm_count * 3));
 }
 
 }  // namespace
@@ -208,9 +215,9 @@ int k_rep_share(mb_ctx *ctx, const AesKey &key, int owner, const mb_tensor *x, m
   int64_t nvec = vec_count(x);
   int g = grid_for(ctx, nvec);
   switch (vec_kind(x->dtype)) {
-    case VK_RING128: share_kernel<VK_RING128><<<g, TPB, 0, ctx->stream>>>(key, CVP(x), VP(prf), VP(diff), VP(zero), nvec, x->numel); break;
-    case VK_RING64: share_kernel<VK_RING64><<<g, TPB, 0, ctx->stream>>>(key, CVP(x), VP(prf), VP(diff), VP(zero), nvec, x->numel); break;
-    case VK_BIT: share_kernel<VK_BIT><<<g, TPB, 0, ctx->stream>>>(key, CVP(x), VP(prf), VP(diff), VP(zero), nvec, x->numel); break;
+    case VK_RING128: AES_LAUNCH(ctx, share_kernel<VK_RING128>, g, key, CVP(x), VP(prf), VP(diff), VP(zero), nvec, x->numel); break;
+    case VK_RING64: AES_LAUNCH(ctx, share_kernel<VK_RING64>, g, key, CVP(x), VP(prf), VP(diff), VP(zero), nvec, x->numel); break;
+    case VK_BIT: AES_LAUNCH(ctx, share_kernel<VK_BIT>, g, key, CVP(x), VP(prf), VP(diff), VP(zero), nvec, x->numel); break;
   }
   MB_LAUNCH_CHECK(ctx);
   return MB_OK;
@@ -222,9 +229,9 @@ int k_rep_share_outsider(mb_ctx *ctx, const AesKey &k0, const AesKey &k1, const 
   int64_t nvec = vec_count(x);
   int g = grid_for(ctx, nvec);
   switch (vec_kind(x->dtype)) {
-    case VK_RING128: share_outsider_kernel<VK_RING128><<<g, TPB, 0, ctx->stream>>>(k0, k1, CVP(x), VP(o0), VP(o1), VP(o2), nvec, x->numel); break;
-    case VK_RING64: share_outsider_kernel<VK_RING64><<<g, TPB, 0, ctx->stream>>>(k0, k1, CVP(x), VP(o0), VP(o1), VP(o2), nvec, x->numel); break;
-    case VK_BIT: share_outsider_kernel<VK_BIT><<<g, TPB, 0, ctx->stream>>>(k0, k1, CVP(x), VP(o0), VP(o1), VP(o2), nvec, x->numel); break;
+    case VK_RING128: AES_LAUNCH(ctx, share_outsider_kernel<VK_RING128>, g, k0, k1, CVP(x), VP(o0), VP(o1), VP(o2), nvec, x->numel); break;
+    case VK_RING64: AES_LAUNCH(ctx, share_outsider_kernel<VK_RING64>, g, k0, k1, CVP(x), VP(o0), VP(o1), VP(o2), nvec, x->numel); break;
+    case VK_BIT: AES_LAUNCH(ctx, share_outsider_kernel<VK_BIT>, g, k0, k1, CVP(x), VP(o0), VP(o1), VP(o2), nvec, x->numel); break;
   }
   MB_LAUNCH_CHECK(ctx);
   return MB_OK;
@@ -251,9 +258,9 @@ int k_rep_mul(mb_ctx *ctx, const AesKey seeds[3], const mb_rep *x, const mb_rep 
 #define ARGS seeds[0], seeds[1], seeds[2], CVP(x->s[0]), CVP(x->s[1]), CVP(x->s[2]), CVP(y->s[0]), CVP(y->s[1]), CVP(y->s[2]), \
              VP(z[0]), VP(z[1]), VP(z[2]), nvec, t->numel
   switch (vec_kind(t->dtype)) {
-    case VK_RING128: rep_mul_kernel<VK_RING128><<<g, TPB, 0, ctx->stream>>>(ARGS); break;
-    case VK_RING64: rep_mul_kernel<VK_RING64><<<g, TPB, 0, ctx->stream>>>(ARGS); break;
-    case VK_BIT: rep_mul_kernel<VK_BIT><<<g, TPB, 0, ctx->stream>>>(ARGS); break;
+    case VK_RING128: AES_LAUNCH(ctx, rep_mul_kernel<VK_RING128>, g, ARGS); break;
+    case VK_RING64: AES_LAUNCH(ctx, rep_mul_kernel<VK_RING64>, g, ARGS); break;
+    case VK_BIT: AES_LAUNCH(ctx, rep_mul_kernel<VK_BIT>, g, ARGS); break;
   }
 #undef ARGS
   MB_LAUNCH_CHECK(ctx);
@@ -267,9 +274,9 @@ int k_add_zero_share(mb_ctx *ctx, const AesKey seeds[3], mb_tensor *v[3], mb_ten
   int g = grid_for(ctx, nvec);
 #define ARGS seeds[0], seeds[1], seeds[2], CVP(v[0]), CVP(v[1]), CVP(v[2]), VP(z[0]), VP(z[1]), VP(z[2]), nvec, t->numel
   switch (vec_kind(t->dtype)) {
-    case VK_RING128: add_zero_share_kernel<VK_RING128><<<g, TPB, 0, ctx->stream>>>(ARGS); break;
-    case VK_RING64: add_zero_share_kernel<VK_RING64><<<g, TPB, 0, ctx->stream>>>(ARGS); break;
-    case VK_BIT: add_zero_share_kernel<VK_BIT><<<g, TPB, 0, ctx->stream>>>(ARGS); break;
+    case VK_RING128: AES_LAUNCH(ctx, add_zero_share_kernel<VK_RING128>, g, ARGS); break;
+    case VK_RING64: AES_LAUNCH(ctx, add_zero_share_kernel<VK_RING64>, g, ARGS); break;
+    case VK_BIT: AES_LAUNCH(ctx, add_zero_share_kernel<VK_BIT>, g, ARGS); break;
   }
 #undef ARGS
   MB_LAUNCH_CHECK(ctx);
@@ -294,9 +301,9 @@ int k_rep_trunc_pr(mb_ctx *ctx, const AesKey seeds[6], unsigned amount, const mb
 #define ARGS seeds[0], seeds[1], seeds[2], seeds[3], seeds[4], seeds[5], p, CVP(x->s[0]), CVP(x->s[1]), CVP(x->s[2]), \
              VP(z[0]), VP(z[1]), VP(z[2]), nvec
   if (t->dtype == MB_RING128)
-    trunc_pr_kernel<VK_RING128><<<g, TPB, 0, ctx->stream>>>(ARGS);
+    AES_LAUNCH(ctx, trunc_pr_kernel<VK_RING128>, g, ARGS);
   else
-    trunc_pr_kernel<VK_RING64><<<g, TPB, 0, ctx->stream>>>(ARGS);
+    AES_LAUNCH(ctx, trunc_pr_kernel<VK_RING64>, g, ARGS);
 #undef ARGS
   MB_LAUNCH_CHECK(ctx);
   return MB_OK;

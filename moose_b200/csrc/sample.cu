@@ -7,11 +7,17 @@ namespace {
 
 constexpr int TPB = 256;
 
+#define AES_LAUNCH(ctx, kern, grid, ...)                                                                        \
+  do {                                                                                                          \
+    MB_CUDA((ctx), cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, AES_SMEM_BYTES));    \
+    kern<<<(grid), TPB, AES_SMEM_BYTES, (ctx)->stream>>>(__VA_ARGS__);                                          \
+  } while (0)
+
 template <int K>
 __global__ void __launch_bounds__(TPB) sample_kernel(AesKey key, vec_t *__restrict__ out, int64_t nvec, int64_t numel) {
-  __shared__ uint32_t sT[AES_TABLE_WORDS];
+  extern __shared__ __align__(16) uint32_t sT[];
   aes_load_table(sT);
-  const uint32_t *sTl = sT + (threadIdx.x & 31);
+  const AesLane sTl = aes_lane(sT);
   for (int64_t v = (int64_t)blockIdx.x * TPB + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * TPB) {
     vec_t r = prf_vec<K>(sTl, key, (uint64_t)v);
     if (K == VK_BIT) r = bit_tail_mask(r, v, numel);
@@ -24,9 +30,9 @@ __global__ void __launch_bounds__(TPB) sample_kernel(AesKey key, vec_t *__restri
 // ring elements; a rarely used op, kept simple.
 template <typename T>
 __global__ void __launch_bounds__(TPB) sample_bits_as_ring_kernel(AesKey key, T *__restrict__ out, int64_t numel) {
-  __shared__ uint32_t sT[AES_TABLE_WORDS];
+  extern __shared__ __align__(16) uint32_t sT[];
   aes_load_table(sT);
-  const uint32_t *sTl = sT + (threadIdx.x & 31);
+  const AesLane sTl = aes_lane(sT);
   int64_t nblocks = (numel + 127) / 128;
   for (int64_t b = (int64_t)blockIdx.x * TPB + threadIdx.x; b < nblocks; b += (int64_t)gridDim.x * TPB) {
     uint32_t o[4];
@@ -43,23 +49,23 @@ __global__ void __launch_bounds__(TPB) sample_bits_as_ring_kernel(AesKey key, T 
 
 int k_sample(mb_ctx *ctx, const AesKey &key, mb_tensor *out, bool bits_as_ring) {
   if (out->numel == 0) return MB_OK;
-  int maxg = ctx->sm_count * 6;
+  int maxg = ctx->sm_count * 3;
   if (bits_as_ring) {
     int64_t nblocks = (out->numel + 127) / 128;
     int g = (int)std::min<int64_t>((nblocks + TPB - 1) / TPB, maxg);
     if (out->dtype == MB_RING128)
-      sample_bits_as_ring_kernel<u128><<<g, TPB, 0, ctx->stream>>>(key, (u128 *)out->dptr, out->numel);
+      AES_LAUNCH(ctx, sample_bits_as_ring_kernel<u128>, g, key, (u128 *)out->dptr, out->numel);
     else
-      sample_bits_as_ring_kernel<uint64_t><<<g, TPB, 0, ctx->stream>>>(key, (uint64_t *)out->dptr, out->numel);
+      AES_LAUNCH(ctx, sample_bits_as_ring_kernel<uint64_t>, g, key, (uint64_t *)out->dptr, out->numel);
     MB_LAUNCH_CHECK(ctx);
     return MB_OK;
   }
   int64_t nvec = vec_count(out);
   int g = (int)std::min<int64_t>((nvec + TPB - 1) / TPB, maxg);
   switch (vec_kind(out->dtype)) {
-    case VK_RING128: sample_kernel<VK_RING128><<<g, TPB, 0, ctx->stream>>>(key, (vec_t *)out->dptr, nvec, out->numel); break;
-    case VK_RING64: sample_kernel<VK_RING64><<<g, TPB, 0, ctx->stream>>>(key, (vec_t *)out->dptr, nvec, out->numel); break;
-    case VK_BIT: sample_kernel<VK_BIT><<<g, TPB, 0, ctx->stream>>>(key, (vec_t *)out->dptr, nvec, out->numel); break;
+    case VK_RING128: AES_LAUNCH(ctx, sample_kernel<VK_RING128>, g, key, (vec_t *)out->dptr, nvec, out->numel); break;
+    case VK_RING64: AES_LAUNCH(ctx, sample_kernel<VK_RING64>, g, key, (vec_t *)out->dptr, nvec, out->numel); break;
+    case VK_BIT: AES_LAUNCH(ctx, sample_kernel<VK_BIT>, g, key, (vec_t *)out->dptr, nvec, out->numel); break;
   }
   MB_LAUNCH_CHECK(ctx);
   return MB_OK;

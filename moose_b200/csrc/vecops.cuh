@@ -56,7 +56,7 @@ struct VOps {
 //  Ring64 : elements 2v, 2v+1 = the two little-endian u64 halves           (host/ops.rs:1969)
 //  Bit    : bits 128v .. 128v+127 = keystream bits, LSB-first per byte     (get_bit policy 0)
 template <int K>
-__device__ __forceinline__ vec_t prf_vec(const uint32_t *sTl, const AesKey &k, uint64_t v) {
+__device__ __forceinline__ vec_t prf_vec(const AesLane &sTl, const AesKey &k, uint64_t v) {
   uint32_t o[4];
   aes_ctr_block(sTl, k, v, o);
   uint64_t first = (uint64_t)o[0] | ((uint64_t)o[1] << 32);
