@@ -157,6 +157,64 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def run_mlp(args):
+    """BASELINE configs[3]: MLP 784-512-512-10, ReLU = maximum([0, z]), fixed(14,23) on Ring64, logits revealed.
+    One step = one forward pass over a device-resident fixed-point batch (sharing included)."""
+    import moose_b200 as mb
+    from moose_b200.predictors import MLPPredictor
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dims = (784, 512, 512, 10)
+    rng = np.random.default_rng(3 + rank)
+    ws = [np.random.default_rng(4 + i).normal(0, dims[i] ** -0.5, (dims[i], dims[i + 1])) for i in range(3)]
+    bs = [np.random.default_rng(40 + i).normal(0, 0.1, dims[i + 1]) for i in range(3)]
+    sess = mb.Session(local_rank, f"{SESSION_ID}-mlp-{rank}", ENTROPY_KEY)
+    pred = MLPPredictor(sess, ws, bs, mb.RING64, 23, "maximum")
+    x = rng.uniform(0, 1, (args.batch, dims[0]))
+    xf = pred.encode(x)
+    for _ in range(args.warmup):
+        out = pred.forward_shared(xf)
+    sess.sync()
+    if dist is not None:
+        dist.barrier()
+    l0 = sess.launch_count
+    sess.timer_start()
+    for _ in range(args.steps):
+        out = pred.forward_shared(xf)
+    ms = sess.timer_stop()
+    launches = sess.launch_count - l0
+    if dist is not None:
+        import torch
+        t = torch.tensor([ms], dtype=torch.float64, device=f"cuda:{local_rank}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0])
+    got = sess.fixedpoint_decode(23, sess.reveal(out)).to_host()[:64]
+    ref = x[:64]
+    for i in range(3):
+        ref = ref @ ws[i] + bs[i]
+        if i < 2:
+            ref = np.maximum(ref, 0)
+    if rank == 0:
+        print(json.dumps({
+            "metric": "mlp_inference_rows_per_s", "value": world * args.batch * args.steps / (ms * 1e-3),
+            "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u64", "data": "synthetic",
+            "config": {"workload": f"mlp_784-512-512-10_relu_ring64_fixed(14,23)_batch{args.batch}",
+                       "max_abs_err_vs_float": float(np.abs(got - ref).max())},
+            "gpu_launches": int(launches)}), flush=True)
+    sess.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -166,7 +224,12 @@ def main():
     ap.add_argument("--size", type=int, default=4096, help="M=N=K (default: the BASELINE config, 4096)")
     ap.add_argument("--ref-size", type=int, default=640, help="sample size of the CPU baseline arms")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="matmul", choices=["matmul", "mlp"],
+                    help="matmul = BASELINE configs[1] (the bench contract); mlp = configs[3], a secondary line")
+    ap.add_argument("--batch", type=int, default=65536)
     args = ap.parse_args()
+    if args.workload == "mlp":
+        return run_mlp(args)
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

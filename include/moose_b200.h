@@ -284,6 +284,9 @@ int mb_rep_shl_dim(mb_ctx *ctx, uint64_t amount, uint64_t bit_length, const mb_r
  * (fails for shapes it cannot tile), 3 = like 2 but single-CTA tiles only (no
  * cta_group::2 pairs).  For ncu comparisons and tests. */
 int mb_ctx_set_gemm_mode(mb_ctx *ctx, int mode);
+/* 1 (default): mb_rep_bit_decompose / mb_rep_msb / mb_rep_ring_inject use the fused per-level adder and
+ * dabit kernels; 0: the op-by-op composition of the same protocols (identical shares; for tests and ncu). */
+int mb_ctx_set_fused_bits(mb_ctx *ctx, int enable);
 
 #ifdef __cplusplus
 }

@@ -63,7 +63,7 @@ ABI = {
     "mb_ctx_set_session": [_P, ctypes.c_char_p], "mb_ctx_set_session_raw": [_P, _U8P],
     "mb_ctx_get_session_raw": [_P, _P], "mb_ctx_set_entropy_key": [_P, _U8P], "mb_ctx_sync": [_P],
     "mb_ctx_stream": [_P], "mb_ctx_timer_start": [_P], "mb_ctx_timer_stop": [_P, ctypes.POINTER(ctypes.c_float)],
-    "mb_ctx_launch_count": [_P], "mb_ctx_set_gemm_mode": [_P, _I],
+    "mb_ctx_launch_count": [_P], "mb_ctx_set_gemm_mode": [_P, _I], "mb_ctx_set_fused_bits": [_P, _I],
     "mb_ctx_profile_enable": [_P, _I],
     "mb_ctx_profile_read": [_P, _I, ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_uint64)],
     "mb_host_alloc_pinned": [_P, ctypes.c_size_t, _PP], "mb_host_free_pinned": [_P, _P],
@@ -291,6 +291,9 @@ class Session:
         self._pinned.append(ptr)
         buf = (ctypes.c_uint8 * max(n, 1)).from_address(ptr.value)
         return np.frombuffer(buf, dtype=dt, count=n // dt.itemsize).reshape(shape)
+
+    def set_fused_bits(self, on: bool):
+        self._check(lib().mb_ctx_set_fused_bits(self.ctx, 1 if on else 0))
 
     def set_gemm_mode(self, mode: int):
         self._check(lib().mb_ctx_set_gemm_mode(self.ctx, mode))

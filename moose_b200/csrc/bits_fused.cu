@@ -1,0 +1,412 @@
+// Fused arithmetic -> boolean conversion:
+//   BitDecomposeOp::rep_ring_kernel = PlacementSplit::split (replicated/bits.rs:84-134) +
+//   BinaryAdder::binary_adder, Kogge-Stone (replicated/misc.rs:176-242), MsbOp (arith.rs:611-626) and
+//   RingInjectOp::rep_kernel with gen_dabit (replicated/convert.rs:316-390, additive/dabit.rs:38-69).
+//
+// The reference runs the adder as ~60 host ops per call (13 replicated ANDs for k = 64, each 3 ANDs + zero
+// share, plus xor / shl_dim copies) over [k, n] bit tensors.  Here every adder LEVEL is one kernel over
+// 128-bit plane vectors:  g' = g ^ AND(p, g << 2^i),  p' = AND(p, p << 2^i)  with the shift resolved as a plane
+// index, the xor fused, and the zero-share bits of both ANDs generated in registers at exactly the stream
+// positions the reference uses (AND number, plane, element) -- so every share bit is identical.
+//
+// msb-only pruning: the most significant bit needs only the carry into position k-1.  Walking the recurrence
+// backwards gives, per level, the set of planes whose g / p values are ever read; only those planes (183 AND
+// planes instead of 832 for k = 64) are computed, stored and given PRF bits.  The msb shares are bit-identical
+// to plane k-1 of the full decomposition because the skipped planes never feed it.
+//
+// Layout requirement of the fused path: n % 128 == 0 (every plane starts on a 16-byte vector); other shapes
+// use the op-by-op composition in rep_api.cpp.
+#include "vecops.cuh"
+
+namespace {
+
+constexpr int TPB = 256;
+
+#define AES_LAUNCH(ctx, kern, grid, ...)                                                                        \
+  do {                                                                                                          \
+    MB_CUDA((ctx), cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, AES_SMEM_BYTES));    \
+    kern<<<(grid), TPB, AES_SMEM_BYTES, (ctx)->stream>>>(__VA_ARGS__);                                          \
+  } while (0)
+
+__device__ __forceinline__ vec_t vxor(vec_t a, vec_t b) { return make_ulonglong2(a.x ^ b.x, a.y ^ b.y); }
+__device__ __forceinline__ vec_t vand(vec_t a, vec_t b) { return make_ulonglong2(a.x & b.x, a.y & b.y); }
+__device__ __forceinline__ vec_t vzero() { return make_ulonglong2(0, 0); }
+
+// bit planes of (x0 + x1) and of x2: [KBITS, n] packed, n % 128 == 0.  A warp transposes 128 elements with ballots.
+template <typename T, int KBITS>
+__global__ void __launch_bounds__(TPB) split_planes_kernel(const T *__restrict__ x0, const T *__restrict__ x1,
+                                                          const T *__restrict__ x2, uint32_t *__restrict__ outB,
+                                                          uint32_t *__restrict__ outC, int64_t n) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * TPB + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * TPB) >> 5;
+  const int64_t ngroups = n / 128;
+  constexpr int PL = KBITS / 32;
+  for (int64_t grp = warp; grp < 2 * ngroups; grp += nwarps) {
+    const bool second = grp >= ngroups;  // first half of the work list: B = bits(x0 + x1); second half: C = bits(x2)
+    const int64_t g = second ? grp - ngroups : grp;
+    uint32_t keep[PL][4];
+#pragma unroll
+    for (int it = 0; it < 4; it++) {
+      const int64_t e = g * 128 + it * 32 + lane;
+      T v = second ? x2[e] : (T)(x0[e] + x1[e]);
+#pragma unroll
+      for (int p = 0; p < KBITS; p++) {
+        unsigned b = __ballot_sync(0xffffffffu, (unsigned)((v >> p) & 1));
+        if (lane == (p & 31)) keep[p >> 5][it] = b;
+      }
+    }
+    uint32_t *out = second ? outC : outB;
+#pragma unroll
+    for (int q = 0; q < PL; q++) {
+      const int p = q * 32 + lane;
+      *(uint4 *)(out + ((int64_t)p * n + g * 128) / 32) = make_uint4(keep[q][0], keep[q][1], keep[q][2], keep[q][3]);
+    }
+  }
+}
+
+// split + first AND of the adder, per plane vector v (flat index over [k, n]):
+//   a = share_by_player0(B) = (R, B ^ R, 0)      R = PRF_bits(seed_share)        (convert.rs:72-94)
+//   b = (0, 0, C)                                                                (bits.rs:124-130)
+//   g0 = AND(a, b) = (0, (B^R)&C, R&C) ^ zero-share,   p0 = a ^ b = (R, B^R, C)
+struct PlanePtrs {
+  vec_t *s[3];
+};
+__global__ void __launch_bounds__(TPB) adder_init_kernel(AesKey k_share, AesKey a0, AesKey a1, AesKey a2,
+                                                        const vec_t *__restrict__ B, const vec_t *__restrict__ C,
+                                                        PlanePtrs g0, PlanePtrs p0, int64_t nvec) {
+  extern __shared__ __align__(16) uint32_t sT[];
+  aes_load_table(sT);
+  const AesLane L = aes_lane(sT);
+  for (int64_t v = (int64_t)blockIdx.x * TPB + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * TPB) {
+    const vec_t b = B[v], c = C[v];
+    const vec_t R = prf_vec<VK_BIT>(L, k_share, (uint64_t)v);
+    const vec_t r0 = prf_vec<VK_BIT>(L, a0, (uint64_t)v);
+    const vec_t r1 = prf_vec<VK_BIT>(L, a1, (uint64_t)v);
+    const vec_t r2 = prf_vec<VK_BIT>(L, a2, (uint64_t)v);
+    const vec_t bR = vxor(b, R);
+    g0.s[0][v] = vxor(r0, r1);
+    g0.s[1][v] = vxor(vand(bR, c), vxor(r1, r2));
+    g0.s[2][v] = vxor(vand(R, c), vxor(r2, r0));
+    p0.s[0][v] = R;
+    p0.s[1][v] = bR;
+    p0.s[2][v] = c;
+  }
+}
+
+struct LevelDesc {
+  int nout;                 // number of output planes
+  int shift;                // 2^i
+  unsigned char plane[128]; // output plane numbers
+  unsigned char gslot[128]; // input slot of plane q in g_in (255 = not stored)
+  unsigned char pslot[128]; // input slot of plane q in p_in
+  unsigned char pout[128];  // output slot in p_out for output index j (255 = p' not needed)
+};
+
+__device__ __forceinline__ void rep_and3(const vec_t x[3], const vec_t y[3], const vec_t r[3], vec_t z[3]) {
+  // z_i = x_i&y_i ^ x_i&y_{i+1} ^ x_{i+1}&y_i ^ (r_i ^ r_{i+1})   (arith.rs:342-358, zero_share.rs:96-106)
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+    const int j = (i + 1) % 3;
+    vec_t v = vxor(vand(x[i], vxor(y[i], y[j])), vand(x[j], y[i]));
+    z[i] = vxor(v, vxor(r[i], r[j]));
+  }
+}
+
+// One Kogge-Stone level (misc.rs:216-232) on the planes listed in `d`:
+//   g'[q] = g[q] ^ AND_pg(p[q], g[q - shift]),   p'[q] = AND_pp(p[q], p[q - shift])   (operands below plane
+//   `shift` are the zeros shl_dim inserts).  nv = vectors per plane.
+__global__ void __launch_bounds__(TPB) adder_level_kernel(AesKey pg0, AesKey pg1, AesKey pg2, AesKey pp0, AesKey pp1,
+                                                         AesKey pp2, LevelDesc d, PlanePtrs g_in, PlanePtrs p_in,
+                                                         PlanePtrs g_out, PlanePtrs p_out, int64_t nv) {
+  extern __shared__ __align__(16) uint32_t sT[];
+  aes_load_table(sT);
+  const AesLane L = aes_lane(sT);
+  const int64_t total = (int64_t)d.nout * nv;
+  for (int64_t t = (int64_t)blockIdx.x * TPB + threadIdx.x; t < total; t += (int64_t)gridDim.x * TPB) {
+    const int j = (int)(t / nv);
+    const int64_t v = t - (int64_t)j * nv;
+    const int q = d.plane[j];
+    const uint64_t pos = (uint64_t)q * (uint64_t)nv + (uint64_t)v;  // vector index in the [k, n] bit tensor
+    vec_t G[3], P[3], Gs[3], Ps[3];
+    const int64_t ig = (int64_t)d.gslot[q] * nv + v, ip = (int64_t)d.pslot[q] * nv + v;
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+      G[i] = g_in.s[i][ig];
+      P[i] = p_in.s[i][ip];
+    }
+    const bool shifted = q >= d.shift;
+    const bool want_p = d.pout[j] != 255;
+    if (shifted) {
+      const int64_t jg = (int64_t)d.gslot[q - d.shift] * nv + v;
+#pragma unroll
+      for (int i = 0; i < 3; i++) Gs[i] = g_in.s[i][jg];
+      if (want_p) {
+        const int64_t jp = (int64_t)d.pslot[q - d.shift] * nv + v;
+#pragma unroll
+        for (int i = 0; i < 3; i++) Ps[i] = p_in.s[i][jp];
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 3; i++) Gs[i] = Ps[i] = vzero();
+    }
+    vec_t r[3], z[3];
+    r[0] = prf_vec<VK_BIT>(L, pg0, pos);
+    r[1] = prf_vec<VK_BIT>(L, pg1, pos);
+    r[2] = prf_vec<VK_BIT>(L, pg2, pos);
+    rep_and3(P, Gs, r, z);
+    const int64_t og = (int64_t)j * nv + v;
+#pragma unroll
+    for (int i = 0; i < 3; i++) g_out.s[i][og] = vxor(G[i], z[i]);
+    if (want_p) {
+      r[0] = prf_vec<VK_BIT>(L, pp0, pos);
+      r[1] = prf_vec<VK_BIT>(L, pp1, pos);
+      r[2] = prf_vec<VK_BIT>(L, pp2, pos);
+      rep_and3(P, Ps, r, z);
+      const int64_t op = (int64_t)d.pout[j] * nv + v;
+#pragma unroll
+      for (int i = 0; i < 3; i++) p_out.s[i][op] = z[i];
+    }
+  }
+}
+
+// z = shl_dim(g, 1) ^ p_store (misc.rs:236-240): z[q] = g[q-1] ^ p0[q], z[0] = p0[0].  Full decomposition.
+__global__ void __launch_bounds__(TPB) adder_final_full_kernel(PlanePtrs g, PlanePtrs p0, PlanePtrs z, int64_t nv, int k) {
+  const int64_t total = (int64_t)k * nv;
+  for (int64_t t = (int64_t)blockIdx.x * TPB + threadIdx.x; t < total; t += (int64_t)gridDim.x * TPB) {
+    const bool low = t < nv;
+#pragma unroll
+    for (int i = 0; i < 3; i++) z.s[i][t] = low ? p0.s[i][t] : vxor(g.s[i][t - nv], p0.s[i][t]);
+  }
+}
+// msb only: out = g_final[k-2] ^ p0[k-1]
+__global__ void __launch_bounds__(TPB) adder_final_msb_kernel(PlanePtrs g, int64_t gslot, PlanePtrs p0, PlanePtrs z,
+                                                             int64_t nv, int k) {
+  for (int64_t v = (int64_t)blockIdx.x * TPB + threadIdx.x; v < nv; v += (int64_t)gridDim.x * TPB) {
+#pragma unroll
+    for (int i = 0; i < 3; i++) z.s[i][v] = vxor(g.s[i][gslot * nv + v], p0.s[i][(int64_t)(k - 1) * nv + v]);
+  }
+}
+
+// RingInjectOp::rep_kernel after the dabit bits b, b0 have been expanded (they are n-bit tensors, 1/64 .. 1/128 of
+// the ring data): per ring vector
+//   c      = open(x + b_bin)                 = x0 ^ x1 ^ x2 ^ b                  (convert.rs:369-371)
+//   br     = ring(b), br0 = PRF(seed_br), br1 = br - br0                         (dabit.rs:50-66)
+//   s      = b_ring + c - 2 b_ring c   (public c lands on share 0)               (convert.rs:374-378)
+//   s    <<= bit_idx                                                             (convert.rs:379)
+//   adt_to_rep: y0 = PRF(seed1), y1 = PRF(seed2), cc = (s0 - y0) + (s1 - y1)     (convert.rs:426-447)
+// Output shares (y0, cc, y1).
+template <int K>
+__global__ void __launch_bounds__(TPB) ring_inject_fused_kernel(AesKey k_br0, AesKey k_y0, AesKey k_y1,
+                                                               const uint32_t *__restrict__ x0, const uint32_t *__restrict__ x1,
+                                                               const uint32_t *__restrict__ x2, const uint32_t *__restrict__ b,
+                                                               vec_t *__restrict__ z0, vec_t *__restrict__ z1,
+                                                               vec_t *__restrict__ z2, int64_t nvec, unsigned bit_idx) {
+  extern __shared__ __align__(16) uint32_t sT[];
+  aes_load_table(sT);
+  const AesLane L = aes_lane(sT);
+  typedef VOps<K> O;
+  constexpr int EPV = K == VK_RING128 ? 1 : 2;  // ring elements per vector
+  for (int64_t v = (int64_t)blockIdx.x * TPB + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * TPB) {
+    const int64_t e = v * EPV;
+    const uint32_t wb = b[e >> 5];
+    const uint32_t wc = x0[e >> 5] ^ x1[e >> 5] ^ x2[e >> 5] ^ wb;
+    const unsigned sh = (unsigned)(e & 31);
+    vec_t br, c;
+    if (K == VK_RING128) {
+      br = make_ulonglong2((wb >> sh) & 1u, 0);
+      c = make_ulonglong2((wc >> sh) & 1u, 0);
+    } else {
+      br = make_ulonglong2((wb >> sh) & 1u, (wb >> (sh + 1)) & 1u);
+      c = make_ulonglong2((wc >> sh) & 1u, (wc >> (sh + 1)) & 1u);
+    }
+    const vec_t br0 = prf_vec<K>(L, k_br0, (uint64_t)v);
+    const vec_t br1 = O::sub(br, br0);
+    const vec_t m0 = O::mul01(br0, c), m1 = O::mul01(br1, c);
+    vec_t s0 = O::sub(O::sub(O::add(br0, c), m0), m0);
+    vec_t s1 = O::sub(O::sub(br1, m1), m1);
+    s0 = O::shl(s0, bit_idx);
+    s1 = O::shl(s1, bit_idx);
+    const vec_t y0 = prf_vec<K>(L, k_y0, (uint64_t)v);
+    const vec_t y1 = prf_vec<K>(L, k_y1, (uint64_t)v);
+    z0[v] = y0;
+    z1[v] = O::add(O::sub(s0, y0), O::sub(s1, y1));
+    z2[v] = y1;
+  }
+}
+
+inline int aes_grid(mb_ctx *ctx, int64_t items) {
+  return (int)std::max<int64_t>(1, std::min<int64_t>((items + TPB - 1) / TPB, (int64_t)ctx->sm_count * 3));
+}
+
+PlanePtrs ptrs_of(mb_tensor *const t[3]) {
+  PlanePtrs p;
+  for (int i = 0; i < 3; i++) p.s[i] = (vec_t *)t[i]->dptr;
+  return p;
+}
+
+struct Tmp3 {
+  mb_ctx *ctx;
+  mb_tensor *t[3];
+  explicit Tmp3(mb_ctx *c) : ctx(c) { t[0] = t[1] = t[2] = nullptr; }
+  ~Tmp3() { for (int i = 0; i < 3; i++) if (t[i]) mb_tensor_free(ctx, t[i]); }
+  Tmp3(const Tmp3 &) = delete;
+  Tmp3 &operator=(const Tmp3 &) = delete;
+  int alloc(int64_t planes, int64_t n) {
+    int64_t shape[2] = {planes, n};
+    for (int i = 0; i < 3; i++) MB_CHECK(mb_tensor_new(ctx, MB_BIT, 2, shape, &t[i]));
+    return MB_OK;
+  }
+  void swap(Tmp3 &o) { for (int i = 0; i < 3; i++) std::swap(t[i], o.t[i]); }
+};
+
+}  // namespace
+
+bool k_rep_adder_supported(const mb_tensor *x) { return mb_is_ring(x->dtype) && x->numel > 0 && x->numel % 128 == 0; }
+
+// keys: [0] split share seed, [1..3] first AND, then per level i: [4 + 6i .. 4 + 6i + 2] = AND(p, g1),
+// [4 + 6i + 3 .. 4 + 6i + 5] = AND(p, p1).  out[3]: bit tensors of shape [k, shape...] (full) or [shape...] (msb).
+int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only, mb_tensor *out[3]) {
+  const mb_tensor *x0 = x->s[0];
+  const int k = x0->dtype == MB_RING128 ? 128 : 64;
+  const int levels = k == 128 ? 7 : 6;
+  const int64_t n = x0->numel, nv = n / 128;
+
+  // 1. bit planes of x0 + x1 and of x2
+  mb_tensor *B = nullptr, *C = nullptr;
+  int64_t pshape[2] = {k, n};
+  MB_CHECK(mb_tensor_new(ctx, MB_BIT, 2, pshape, &B));
+  int rc = mb_tensor_new(ctx, MB_BIT, 2, pshape, &C);
+  if (rc != MB_OK) { mb_tensor_free(ctx, B); return rc; }
+  struct Guard { mb_ctx *c; mb_tensor *a, *b; ~Guard() { mb_tensor_free(c, a); mb_tensor_free(c, b); } } guard{ctx, B, C};
+  {
+    const int64_t warps = 2 * (n / 128);
+    const int g = (int)std::min<int64_t>((warps * 32 + TPB - 1) / TPB, (int64_t)ctx->sm_count * 8);
+    if (k == 128)
+      split_planes_kernel<u128, 128><<<g, TPB, 0, ctx->stream>>>((const u128 *)x->s[0]->dptr, (const u128 *)x->s[1]->dptr,
+                                                                (const u128 *)x->s[2]->dptr, (uint32_t *)B->dptr, (uint32_t *)C->dptr, n);
+    else
+      split_planes_kernel<uint64_t, 64><<<g, TPB, 0, ctx->stream>>>((const uint64_t *)x->s[0]->dptr, (const uint64_t *)x->s[1]->dptr,
+                                                                   (const uint64_t *)x->s[2]->dptr, (uint32_t *)B->dptr, (uint32_t *)C->dptr, n);
+    MB_LAUNCH_CHECK(ctx);
+  }
+
+  // 2. g0, p0 on all planes
+  Tmp3 g(ctx), p(ctx), p0(ctx);
+  MB_CHECK(g.alloc(k, n));
+  MB_CHECK(p0.alloc(k, n));
+  {
+    const int64_t total = (int64_t)k * nv;
+    AES_LAUNCH(ctx, adder_init_kernel, aes_grid(ctx, total), keys[0], keys[1], keys[2], keys[3], (const vec_t *)B->dptr,
+               (const vec_t *)C->dptr, ptrs_of(g.t), ptrs_of(p0.t), total);
+    MB_LAUNCH_CHECK(ctx);
+  }
+
+  // 3. plane sets needed per level (all planes for the full decomposition)
+  std::vector<std::vector<int>> need_g(levels + 1), need_p(levels + 1);
+  if (msb_only) {
+    std::vector<char> ng(k, 0), np(k, 0);
+    ng[k - 2] = 1;
+    for (int i = levels; i >= 0; i--) {
+      for (int q = 0; q < k; q++) {
+        if (ng[q]) need_g[i].push_back(q);
+        if (np[q]) need_p[i].push_back(q);
+      }
+      if (i == 0) break;
+      const int s = 1 << (i - 1);
+      std::vector<char> g2(k, 0), p2(k, 0);
+      for (int q = 0; q < k; q++) {
+        if (ng[q]) {  // g'[q] = g[q] ^ AND(p[q], g[q-s])
+          g2[q] = 1;
+          p2[q] = 1;
+          if (q >= s) g2[q - s] = 1;
+        }
+        if (np[q]) {  // p'[q] = AND(p[q], p[q-s])
+          p2[q] = 1;
+          if (q >= s) p2[q - s] = 1;
+        }
+      }
+      ng = g2;
+      np = p2;
+    }
+  } else {
+    for (int i = 0; i <= levels; i++)
+      for (int q = 0; q < k; q++) {
+        need_g[i].push_back(q);
+        if (i < levels) need_p[i].push_back(q);  // p after the last level is never read (misc.rs:236-240)
+      }
+  }
+
+  // 4. levels.  Level 0 reads the init outputs (slot = plane); p of level 0 is p0 itself.
+  std::vector<int> gslot(k), pslot(k);
+  for (int q = 0; q < k; q++) gslot[q] = pslot[q] = q;
+  Tmp3 *p_cur = &p0;  // not owned by the loop on level 0
+  for (int i = 0; i < levels; i++) {
+    LevelDesc d;
+    memset(&d, 255, sizeof(d));
+    d.shift = 1 << i;
+    d.nout = (int)need_g[i + 1].size();
+    for (int q = 0; q < k; q++) {
+      d.gslot[q] = (unsigned char)(gslot[q] < 0 ? 255 : gslot[q]);
+      d.pslot[q] = (unsigned char)(pslot[q] < 0 ? 255 : pslot[q]);
+    }
+    std::vector<int> pslot_next(k, -1), gslot_next(k, -1);
+    int np_out = 0;
+    for (int j = 0; j < d.nout; j++) {
+      const int q = need_g[i + 1][j];
+      d.plane[j] = (unsigned char)q;
+      gslot_next[q] = j;
+      const bool want_p = std::find(need_p[i + 1].begin(), need_p[i + 1].end(), q) != need_p[i + 1].end();
+      if (want_p) {
+        d.pout[j] = (unsigned char)np_out;
+        pslot_next[q] = np_out++;
+      }
+    }
+    // every plane whose p' is needed also needs g' in this recurrence; assert the planner's invariant
+    for (int q : need_p[i + 1])
+      if (gslot_next[q] < 0) return mb_fail(ctx, MB_ERR_KERNEL, "adder plan: p needed without g");
+    Tmp3 g_next(ctx), p_next(ctx);
+    MB_CHECK(g_next.alloc(std::max(d.nout, 1), n));
+    MB_CHECK(p_next.alloc(std::max(np_out, 1), n));
+    const AesKey *kk = keys + 4 + 6 * i;
+    AES_LAUNCH(ctx, adder_level_kernel, aes_grid(ctx, (int64_t)d.nout * nv), kk[0], kk[1], kk[2], kk[3], kk[4], kk[5], d,
+               ptrs_of(g.t), ptrs_of(p_cur->t), ptrs_of(g_next.t), ptrs_of(p_next.t), nv);
+    MB_LAUNCH_CHECK(ctx);
+    g.swap(g_next);
+    p.swap(p_next);
+    p_cur = &p;
+    gslot = gslot_next;
+    pslot = pslot_next;
+  }
+
+  // 5. z = shl_dim(g, 1) ^ p_store
+  PlanePtrs zp = ptrs_of(out);
+  if (msb_only) {
+    adder_final_msb_kernel<<<(unsigned)std::max<int64_t>(1, (nv + TPB - 1) / TPB), TPB, 0, ctx->stream>>>(
+        ptrs_of(g.t), (int64_t)gslot[k - 2], ptrs_of(p0.t), zp, nv, k);
+  } else {
+    const int64_t total = (int64_t)k * nv;
+    adder_final_full_kernel<<<(unsigned)std::min<int64_t>((total + TPB - 1) / TPB, (int64_t)ctx->sm_count * 16), TPB, 0,
+                              ctx->stream>>>(ptrs_of(g.t), ptrs_of(p0.t), zp, nv, k);
+  }
+  MB_LAUNCH_CHECK(ctx);
+  return MB_OK;
+}
+
+// x: replicated bit shares (n bits); b: the dealer's dabit bits; out: ring shares (y0, cc, y1).
+int k_ring_inject_fused(mb_ctx *ctx, const AesKey &k_br0, const AesKey &k_y0, const AesKey &k_y1, unsigned bit_idx,
+                        const mb_rep *x, const mb_tensor *b, mb_tensor *out[3]) {
+  const mb_tensor *t = out[0];
+  if (t->numel == 0) return MB_OK;
+  const int64_t nvec = vec_count(t);
+  const int g = aes_grid(ctx, nvec);
+#define ARGS k_br0, k_y0, k_y1, (const uint32_t *)x->s[0]->dptr, (const uint32_t *)x->s[1]->dptr, (const uint32_t *)x->s[2]->dptr, \
+             (const uint32_t *)b->dptr, (vec_t *)out[0]->dptr, (vec_t *)out[1]->dptr, (vec_t *)out[2]->dptr, nvec
+  if (t->dtype == MB_RING128)
+    AES_LAUNCH(ctx, ring_inject_fused_kernel<VK_RING128>, g, ARGS, bit_idx & 127);
+  else
+    AES_LAUNCH(ctx, ring_inject_fused_kernel<VK_RING64>, g, ARGS, bit_idx & 63);
+#undef ARGS
+  MB_LAUNCH_CHECK(ctx);
+  return MB_OK;
+}

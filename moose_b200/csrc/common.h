@@ -53,6 +53,7 @@ struct mb_ctx {
   bool have_setup;
   uint8_t setup_keys[3][16]; // k0,k1,k2 (k10=k11 etc., replicated/setup.rs:39-58)
   int gemm_mode;
+  bool fused_bits;            // fused adder / ring_inject kernels (false = op-by-op composition, for A/B tests)
   int gemm_pair_mode;         // 0 = CTA pairs when possible, 1 = single-CTA tiles only (A/B comparison)
   std::atomic<uint64_t> launches;
   bool profile;
@@ -142,6 +143,12 @@ struct LimbOperandB { const void *b0; const void *b1; };  // B = b0 (+ b1 if non
 int k_gemm_limb_batched(mb_ctx *ctx, mb_dtype dtype, const LimbOperandA *As, int nA, const LimbOperandB *Bs, int nB,
                         const int (*a_idx)[2], const int (*b_idx)[2], int nbatch, int nterms, void *const *C,
                         int64_t M, int64_t K, int64_t N);
+
+// Fused arithmetic->boolean conversion (bits_fused.cu)
+bool k_rep_adder_supported(const mb_tensor *x);
+int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only, mb_tensor *out[3]);
+int k_ring_inject_fused(mb_ctx *ctx, const AesKey &k_br0, const AesKey &k_y0, const AesKey &k_y1, unsigned bit_idx,
+                        const mb_rep *x, const mb_tensor *b, mb_tensor *out[3]);
 
 // Fused replicated kernels (rep.cu)
 int k_rep_share(mb_ctx *ctx, const AesKey &key, int owner, const mb_tensor *x, mb_tensor *o0, mb_tensor *o1,

@@ -27,6 +27,7 @@ extern "C" int mb_ctx_create(int device, mb_ctx **out) {
   ctx->have_setup = false;
   ctx->gemm_mode = 0;
   ctx->gemm_pair_mode = 0;
+  ctx->fused_bits = true;
   ctx->launches = 0;
   ctx->profile = false;
   memset(ctx->scratch, 0, sizeof(ctx->scratch));
@@ -108,6 +109,11 @@ extern "C" int mb_ctx_timer_stop(mb_ctx *ctx, float *ms) {
   return MB_OK;
 }
 extern "C" uint64_t mb_ctx_launch_count(const mb_ctx *ctx) { return ctx ? ctx->launches.load() : 0; }
+extern "C" int mb_ctx_set_fused_bits(mb_ctx *ctx, int enable) {
+  if (!ctx) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_set_fused_bits: NULL ctx");
+  ctx->fused_bits = enable != 0;
+  return MB_OK;
+}
 extern "C" int mb_ctx_set_gemm_mode(mb_ctx *ctx, int mode) {
   // modes 0..2 select the implementation; 3 = tensor pipe restricted to single-CTA tiles (no cta_group::2)
   if (!ctx || mode < 0 || mode > 3) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_set_gemm_mode: bad mode");

@@ -429,13 +429,43 @@ extern "C" int mb_rep_shl_dim(mb_ctx *ctx, uint64_t amount, uint64_t bit_length,
   return MB_OK;
 }
 
+// Fused split + Kogge-Stone adder (bits_fused.cu).  Seeds are derived in the order the op-by-op protocol draws
+// them: share of bits(x0+x1) by player0 (setup, 1 sync key), first AND (3), then per level AND(p,g1) (3), AND(p,p1) (3).
+static int rep_adder_fused(mb_ctx *ctx, const mb_rep *x, bool msb_only, mb_rep **out) {
+  const mb_tensor *x0 = x->s[0];
+  const int k = x0->dtype == MB_RING128 ? 128 : 64;
+  const int levels = k == 128 ? 7 : 6;
+  std::vector<AesKey> keys(4 + 6 * levels);
+  MB_CHECK(ensure_setup(ctx));
+  uint8_t sync[16];
+  MB_CHECK(mb_entropy16(ctx, sync));
+  seed_to_aes(ctx, sync, ctx->setup_keys[0], &keys[0]);
+  MB_CHECK(gen_zero_seeds(ctx, &keys[1]));
+  for (int i = 0; i < levels; i++) {
+    MB_CHECK(gen_zero_seeds(ctx, &keys[4 + 6 * i]));
+    MB_CHECK(gen_zero_seeds(ctx, &keys[4 + 6 * i + 3]));
+  }
+  int64_t shape[MB_MAX_RANK];
+  int rank = 0;
+  if (!msb_only) shape[rank++] = k;
+  for (int d = 0; d < x0->rank; d++) shape[rank++] = x0->shape[d];
+  RepTmp z(ctx);
+  MB_CHECK(rep_alloc(ctx, MB_BIT, rank, shape, &z.p));
+  MB_CHECK(k_rep_adder(ctx, keys.data(), x, msb_only, z.p->s));
+  *out = z.release();
+  return MB_OK;
+}
+
 // BitDecomposeOp::rep_ring_kernel = split (bits.rs:84-134) + Kogge-Stone binary_adder
-// (misc.rs:176-242), composed from the fused share / and / xor kernels.
+// (misc.rs:176-242): fused per-level kernels when every plane is vector aligned, else composed from
+// the fused share / and / xor kernels.
 extern "C" int mb_rep_bit_decompose(mb_ctx *ctx, const mb_rep *x, mb_rep **out) {
   MB_ENTER(ctx, "mb_rep_bit_decompose");
   MB_REQUIRE(ctx, rep_valid(x) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_bit_decompose: NULL argument");
   mb_dtype dt = x->s[0]->dtype;
   MB_REQUIRE(ctx, mb_is_ring(dt), MB_ERR_TYPE_MISMATCH, "mb_rep_bit_decompose: needs ring shares");
+  MB_REQUIRE(ctx, x->s[0]->rank < MB_MAX_RANK, MB_ERR_KERNEL, "mb_rep_bit_decompose: rank too large");
+  if (ctx->fused_bits && k_rep_adder_supported(x->s[0])) return rep_adder_fused(ctx, x, false, out);
   const unsigned L = dt == MB_RING128 ? 128 : 64;
   // split: bsl = bits(x0 + x1) shared by player0; bsr = (0, 0, bits(x2))
   Tmp left(ctx), bsl(ctx), x2b(ctx);
@@ -474,6 +504,9 @@ extern "C" int mb_rep_bit_decompose(mb_ctx *ctx, const mb_rep *x, mb_rep **out) 
 extern "C" int mb_rep_msb(mb_ctx *ctx, const mb_rep *x, mb_rep **out) {
   MB_ENTER(ctx, "mb_rep_msb");
   MB_REQUIRE(ctx, rep_valid(x) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_msb: NULL argument");
+  MB_REQUIRE(ctx, mb_is_ring(x->s[0]->dtype), MB_ERR_TYPE_MISMATCH, "mb_rep_msb: needs ring shares");
+  // msb-only pruned adder: bit-identical to plane k-1 of the full decomposition
+  if (ctx->fused_bits && k_rep_adder_supported(x->s[0])) return rep_adder_fused(ctx, x, true, out);
   RepTmp bits(ctx);
   MB_CHECK(mb_rep_bit_decompose(ctx, x, &bits.p));
   int L = x->s[0]->dtype == MB_RING128 ? 128 : 64;
@@ -486,6 +519,32 @@ extern "C" int mb_rep_ring_inject(mb_ctx *ctx, mb_dtype ring, uint64_t bit_idx, 
   MB_REQUIRE(ctx, rep_valid(x) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_ring_inject: NULL argument");
   MB_REQUIRE(ctx, x->s[0]->dtype == MB_BIT && mb_is_ring(ring), MB_ERR_TYPE_MISMATCH, "mb_rep_ring_inject: bit shares -> ring");
   const mb_tensor *like = x->s[0];
+  if (ctx->fused_bits) {
+    // Entropy order: gen_dabit (dabit.rs:49-55): Sample seed, PrfKeyGen, 2 x SyncKey; adt_to_rep
+    // (convert.rs:426-431): 2 x SyncKey, PrfKeyGen.  The additive share b0 of the dabit bit cancels in the
+    // opened value c = x ^ b, so its stream (seed_b) is never expanded.
+    uint8_t seed_bits[16], key[16], sync_b[16], sync_br[16], sync0[16], sync1[16], key2[16];
+    MB_CHECK(mb_entropy16(ctx, seed_bits));
+    MB_CHECK(mb_entropy16(ctx, key));
+    MB_CHECK(mb_entropy16(ctx, sync_b));
+    MB_CHECK(mb_entropy16(ctx, sync_br));
+    MB_CHECK(mb_entropy16(ctx, sync0));
+    MB_CHECK(mb_entropy16(ctx, sync1));
+    MB_CHECK(mb_entropy16(ctx, key2));
+    AesKey kb, k_br0, k_y0, k_y1;
+    mb_aes_expand(seed_bits, &kb);
+    seed_to_aes(ctx, sync_br, key, &k_br0);
+    seed_to_aes(ctx, sync0, key2, &k_y0);
+    seed_to_aes(ctx, sync1, key2, &k_y1);
+    Tmp b(ctx);
+    MB_CHECK(b.alloc_like(like));
+    MB_CHECK(k_sample(ctx, kb, b.p, false));
+    RepTmp z(ctx);
+    MB_CHECK(rep_alloc(ctx, ring, like->rank, like->shape, &z.p));
+    MB_CHECK(k_ring_inject_fused(ctx, k_br0, k_y0, k_y1, (unsigned)bit_idx, x, b.p, z.p->s));
+    *out = z.release();
+    return MB_OK;
+  }
   // gen_dabit: b = Sample (bits), br = ring_inject(b); key; seed_b, seed_br
   Tmp b(ctx), br(ctx), b0(ctx), b1(ctx), br0(ctx), br1(ctx);
   MB_CHECK(mb_sample(ctx, MB_BIT, like->rank, like->shape, -1, &b.p));

@@ -1,0 +1,74 @@
+"""Host-side mirrors of the pymoose predictors on the path (op sequence only; all arithmetic is in
+libmoose_b200).  They follow pymoose/pymoose/predictors/{multilayer_perceptron,linear}_predictor.py:
+
+  MLP  (multilayer_perceptron_predictor.py:86-123): per layer  y = dot(x, w); z = y + b;
+       hidden layers  z = maximum([zeros@bob, z])  (Activation.RELU, :98-111); logits out.
+       The logical dot on fixed-point operands appends trunc_pr(f) (moose/src/logical/ops.rs:776-821).
+  Linear (linear_predictor.py:41-63): x' = concatenate([1, x]); y = dot(x', w) with the intercepts as
+       the first row of w.
+
+Operands: x is a Host fixed-point tensor at alice (shared by party 0 inside the first dot,
+fixedpoint/ops.rs:788-812); weights and biases are mirrored fixed-point constants (weights are shared
+from mirrored player 0, mirrored/ops.rs:154-180; biases are added as public values, arith.rs:81-121);
+the ReLU zeros are a Host tensor at bob (shared by party 1).
+"""
+from __future__ import annotations
+
+from typing import List, Sequence
+
+import numpy as np
+
+from . import FLOAT64, RING64, RING128, RepTensor, Session, Tensor
+
+
+class MLPPredictor:
+    def __init__(self, sess: Session, weights: Sequence[np.ndarray], biases: Sequence[np.ndarray],
+                 ring: int = RING64, frac: int = 23, relu_via: str = "maximum"):
+        self.sess, self.ring, self.frac, self.relu_via = sess, ring, frac, relu_via
+        enc = lambda a: sess.fixedpoint_encode(ring, frac, sess.from_host(FLOAT64, np.asarray(a, dtype=np.float64)))
+        self.w: List[Tensor] = [enc(w) for w in weights]                      # [in, out] each
+        self.b: List[Tensor] = [enc(np.asarray(b).reshape(1, -1)) for b in biases]
+
+    def encode(self, x: np.ndarray) -> Tensor:
+        return self.sess.fixedpoint_encode(self.ring, self.frac, self.sess.from_host(FLOAT64, x))
+
+    def forward_shared(self, x_fixed: Tensor) -> RepTensor:
+        s = self.sess
+        x = s.share(x_fixed, 0)
+        n = len(self.w)
+        for i in range(n):
+            w = s.share(self.w[i], 0)
+            y = s.trunc_pr(self.frac, s.rep_dot(x, w))
+            z = s.rep_add_public(y, self.b[i])
+            if i < n - 1:
+                if self.relu_via == "maximum":
+                    zeros = s.share(s.fill(self.ring, 0, z.shape), 1)
+                    z = s.maximum([zeros, z])
+                else:
+                    z = s.relu(z)
+            x = z
+        return x
+
+    def __call__(self, x: np.ndarray) -> np.ndarray:
+        out = self.forward_shared(self.encode(x))
+        return self.sess.fixedpoint_decode(self.frac, self.sess.reveal(out, 0)).to_host()
+
+
+class LinearPredictor:
+    """dot + trunc prefix of LinearRegressor / LinearClassifier (the sigmoid post-transform is not built yet)."""
+
+    def __init__(self, sess: Session, coeffs: np.ndarray, intercepts: np.ndarray, ring: int = RING128, frac: int = 40):
+        self.sess, self.ring, self.frac = sess, ring, frac
+        w = np.concatenate([np.asarray(intercepts, dtype=np.float64).reshape(1, -1).T.T, np.asarray(coeffs, dtype=np.float64).T], axis=0)
+        self.w = sess.fixedpoint_encode(ring, frac, sess.from_host(FLOAT64, w))  # [1 + features, classes]
+
+    def forward_shared(self, x_with_bias_fixed: Tensor) -> RepTensor:
+        s = self.sess
+        x = s.share(x_with_bias_fixed, 0)
+        w = s.share(self.w, 0)
+        return s.trunc_pr(self.frac, s.rep_dot(x, w))
+
+    def __call__(self, x: np.ndarray) -> np.ndarray:
+        xb = np.concatenate([np.ones((x.shape[0], 1)), x], axis=1)
+        out = self.forward_shared(self.sess.fixedpoint_encode(self.ring, self.frac, self.sess.from_host(FLOAT64, xb)))
+        return self.sess.fixedpoint_decode(self.frac, self.sess.reveal(out, 0)).to_host()

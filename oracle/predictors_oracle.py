@@ -1,0 +1,31 @@
+"""TEST INFRASTRUCTURE: the same predictor op sequences as moose_b200/predictors.py, on the oracle."""
+import numpy as np
+
+from . import moose_oracle as mo
+
+
+def mlp_forward_shared(sess, x_fixed, w_fixed, b_fixed, frac, relu_via="maximum"):
+    bits = x_fixed.bits
+    x = mo.rep_share(sess, x_fixed, 0)
+    n = len(w_fixed)
+    for i in range(n):
+        w = mo.rep_share(sess, w_fixed[i], 0)
+        y = mo.rep_trunc_pr(sess, frac, mo.rep_dot(sess, x, w))
+        b = b_fixed[i]
+        z = mo.rep_add_mir(y, mo.MirTensor([b, b, b]))
+        if i < n - 1:
+            if relu_via == "maximum":
+                zeros = mo.rep_share(sess, mo.fill(bits, 0, z.shape), 1)
+                z = mo.rep_maximum(sess, [zeros, z])
+            else:
+                z = mo.rep_relu(sess, z)
+        x = z
+    return x
+
+
+def mlp(sess, x, weights, biases, bits=64, frac=23, relu_via="maximum"):
+    xf = mo.fixed_encode(bits, x, frac)
+    wf = [mo.fixed_encode(bits, np.asarray(w, dtype=np.float64), frac) for w in weights]
+    bf = [mo.fixed_encode(bits, np.asarray(b, dtype=np.float64).reshape(1, -1), frac) for b in biases]
+    out = mlp_forward_shared(sess, xf, wf, bf, frac, relu_via)
+    return out, mo.fixed_decode(mo.rep_reveal(out), frac)

@@ -1,0 +1,63 @@
+"""Predictor-level parity (BASELINE configs 3/4 at oracle-sized batches): the MLP op sequence of the pymoose
+MLPRegressor on Ring64 fixed(14,23), shares compared bit for bit with the oracle under the shared entropy
+source, outputs compared with a float64 numpy MLP at the tolerance the reference's own predictor tests use
+(decimal=1 for MLP regressors, multilayer_perceptron_predictor_test.py:100-206)."""
+import numpy as np
+import pytest
+
+import moose_b200 as mb
+from moose_b200.predictors import LinearPredictor, MLPPredictor
+from oracle import moose_oracle as mo
+from oracle import predictors_oracle as po
+from _util import ENTROPY_KEY, SESSION_ID, same_rep
+
+pytestmark = pytest.mark.gpu
+
+
+def make_mlp(rng, dims):
+    ws = [rng.normal(0, dims[i] ** -0.5, (dims[i], dims[i + 1])) for i in range(len(dims) - 1)]
+    bs = [rng.normal(0, 0.1, dims[i + 1]) for i in range(len(dims) - 1)]
+    return ws, bs
+
+
+def numpy_mlp(x, ws, bs):
+    for i, (w, b) in enumerate(zip(ws, bs)):
+        x = x @ w + b
+        if i < len(ws) - 1:
+            x = np.maximum(x, 0)
+    return x
+
+
+@pytest.mark.parametrize("dims,batch", [((32, 16, 16, 4), 24), ((784, 512, 512, 10), 128)])
+@pytest.mark.parametrize("relu_via", ["maximum", "relu"])
+def test_mlp_ring64_share_parity(dims, batch, relu_via):
+    if relu_via == "relu" and dims[0] == 784:
+        pytest.skip("one large case is enough")
+    rng = np.random.default_rng(3)
+    ws, bs = make_mlp(rng, dims)
+    x = rng.uniform(0, 1, (batch, dims[0]))
+    g, o = mb.Session(0, SESSION_ID, ENTROPY_KEY), mo.Session(SESSION_ID, ENTROPY_KEY)
+    try:
+        pred = MLPPredictor(g, ws, bs, mb.RING64, 23, relu_via)
+        gout = pred.forward_shared(pred.encode(x))
+        oout, odec = po.mlp(o, x, ws, bs, 64, 23, relu_via)
+        assert same_rep(gout, oout)
+        dec = g.fixedpoint_decode(23, g.reveal(gout)).to_host()
+        assert np.array_equal(dec, odec)
+        np.testing.assert_almost_equal(dec, numpy_mlp(x, ws, bs), decimal=1)
+        assert np.abs(dec - numpy_mlp(x, ws, bs)).max() < 1e-3
+    finally:
+        g.close()
+
+
+def test_linear_ring128_dot_trunc_prefix():
+    rng = np.random.default_rng(2)
+    feats, batch = 512, 300
+    coeffs, intercepts = rng.normal(0, feats ** -0.5, (2, feats)), rng.normal(0, 0.1, (1, 2))
+    x = rng.uniform(-1, 1, (batch, feats))
+    g = mb.Session(0, SESSION_ID, ENTROPY_KEY)
+    try:
+        out = LinearPredictor(g, coeffs, intercepts)(x)
+        np.testing.assert_almost_equal(out, x @ coeffs.T + intercepts, decimal=5)
+    finally:
+        g.close()

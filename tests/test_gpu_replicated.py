@@ -123,11 +123,14 @@ def test_trunc_pr_rejects_large_amount():
     g.close()
 
 
+@pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("bits", [64, 128])
-@pytest.mark.parametrize("shape", [(3,), (128,), (5, 7), (256,)])
-def test_bit_decompose_msb_parity(bits, shape):
-    """replicated/mod.rs:999-1032 (msb), :1100+ (bit_dec): share-level parity and plaintext check."""
+@pytest.mark.parametrize("shape", [(3,), (128,), (5, 7), (256,), (3, 128), (1024,)])
+def test_bit_decompose_msb_parity(bits, shape, fused):
+    """replicated/mod.rs:999-1032 (msb), :1100+ (bit_dec): share-level parity and plaintext check, for the
+    fused per-level adder (n % 128 == 0; msb with carry pruning) and for the op-by-op composition."""
     g, o = pair()
+    g.set_fused_bits(fused)
     rng = np.random.default_rng(9)
     a = rand_ring(rng, bits, shape)
     gx, ox = g.share(g.from_host(DT[bits], a), 0), mo.rep_share(o, mo.Ring(bits, a), 0)
@@ -140,10 +143,12 @@ def test_bit_decompose_msb_parity(bits, shape):
     g.close()
 
 
+@pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("bits", [64, 128])
-def test_ring_inject_parity(bits):
+def test_ring_inject_parity(bits, fused):
     """replicated/mod.rs ring_inject tests: b -> b << idx as a replicated ring value."""
     g, o = pair()
+    g.set_fused_bits(fused)
     rng = np.random.default_rng(4)
     b = rng.integers(0, 2, (9, 5)).astype(np.uint8)
     gb, ob = g.share(g.from_bits(b), 0), mo.rep_share(o, mo.Bits.from_array(b), 0)
