@@ -13,9 +13,22 @@ __device__ __forceinline__ unsigned bit_of(T x, unsigned p) {
   return (unsigned)((x >> p) & 1);
 }
 
+// 32 x 32 bit-matrix transpose across the lanes of a warp (LSB-first): lane r holds row r on entry, lane c
+// holds column c on exit.
+__device__ __forceinline__ uint32_t warp_transpose32(uint32_t x, int lane) {
+#pragma unroll
+  for (int s = 0; s < 5; s++) {
+    const int j = 16 >> s;
+    const uint32_t m = s == 0 ? 0x0000FFFFu : s == 1 ? 0x00FF00FFu : s == 2 ? 0x0F0F0F0Fu : s == 3 ? 0x33333333u : 0x55555555u;
+    const uint32_t p = __shfl_xor_sync(0xffffffffu, x, j);
+    x = (lane & j) ? ((x & ~m) | ((p >> j) & m)) : ((x & m) | ((p & m) << j));
+  }
+  return x;
+}
+
 // BitDecomposeOp::host_bit64/128_kernel (host/ops.rs:896-936), n % 128 == 0:
-// a warp transposes 128 elements x KBITS planes with ballots and writes 16 bytes
-// per plane.
+// a warp transposes 128 elements x KBITS planes (32 x 32 bit blocks, shuffle butterflies)
+// and writes 16 bytes per plane.
 template <typename T, int KBITS>
 __global__ void __launch_bounds__(TPB) bit_decompose_aligned_kernel(const T *__restrict__ x, uint32_t *__restrict__ out,
                                                                    int64_t n) {
@@ -30,10 +43,7 @@ __global__ void __launch_bounds__(TPB) bit_decompose_aligned_kernel(const T *__r
     for (int it = 0; it < 4; it++) {
       T v = x[grp * 128 + it * 32 + lane];
 #pragma unroll
-      for (int p = 0; p < KBITS; p++) {
-        unsigned b = __ballot_sync(0xffffffffu, bit_of(v, p));
-        if (lane == (p & 31)) keep[p >> 5][it] = b;
-      }
+      for (int h = 0; h < PL; h++) keep[h][it] = warp_transpose32((uint32_t)(v >> (32 * h)), lane);
     }
 #pragma unroll
     for (int q = 0; q < PL; q++) {

@@ -32,7 +32,22 @@ __device__ __forceinline__ vec_t vxor(vec_t a, vec_t b) { return make_ulonglong2
 __device__ __forceinline__ vec_t vand(vec_t a, vec_t b) { return make_ulonglong2(a.x & b.x, a.y & b.y); }
 __device__ __forceinline__ vec_t vzero() { return make_ulonglong2(0, 0); }
 
-// bit planes of (x0 + x1) and of x2: [KBITS, n] packed, n % 128 == 0.  A warp transposes 128 elements with ballots.
+// 32 x 32 bit-matrix transpose across the lanes of a warp (LSB-first): on entry lane r holds row r, on exit
+// lane c holds column c, i.e. bit r of the result in lane c is bit c of the input of lane r.  Five butterfly
+// stages; each exchanges the off-diagonal j x j blocks between lanes r and r ^ j.
+__device__ __forceinline__ uint32_t warp_transpose32(uint32_t x, int lane) {
+#pragma unroll
+  for (int s = 0; s < 5; s++) {
+    const int j = 16 >> s;
+    const uint32_t m = s == 0 ? 0x0000FFFFu : s == 1 ? 0x00FF00FFu : s == 2 ? 0x0F0F0F0Fu : s == 3 ? 0x33333333u : 0x55555555u;
+    const uint32_t p = __shfl_xor_sync(0xffffffffu, x, j);
+    x = (lane & j) ? ((x & ~m) | ((p >> j) & m)) : ((x & m) | ((p & m) << j));
+  }
+  return x;
+}
+
+// bit planes of (x0 + x1) and of x2: [KBITS, n] packed, n % 128 == 0.  A warp transposes 128 elements x KBITS
+// bits as KBITS/32 x 4 blocks of 32 x 32 bits; lane l ends up with planes l, l+32, ... and stores 16 bytes each.
 template <typename T, int KBITS>
 __global__ void __launch_bounds__(TPB) split_planes_kernel(const T *__restrict__ x0, const T *__restrict__ x1,
                                                           const T *__restrict__ x2, uint32_t *__restrict__ outB,
@@ -51,10 +66,7 @@ __global__ void __launch_bounds__(TPB) split_planes_kernel(const T *__restrict__
       const int64_t e = g * 128 + it * 32 + lane;
       T v = second ? x2[e] : (T)(x0[e] + x1[e]);
 #pragma unroll
-      for (int p = 0; p < KBITS; p++) {
-        unsigned b = __ballot_sync(0xffffffffu, (unsigned)((v >> p) & 1));
-        if (lane == (p & 31)) keep[p >> 5][it] = b;
-      }
+      for (int h = 0; h < PL; h++) keep[h][it] = warp_transpose32((uint32_t)(v >> (32 * h)), lane);
     }
     uint32_t *out = second ? outC : outB;
 #pragma unroll

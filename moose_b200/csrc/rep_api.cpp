@@ -233,6 +233,11 @@ static int rep_public_linear(mb_ctx *ctx, bool subtract, const mb_rep *x, const 
   int rc = subtract ? mb_sub(ctx, x->s[0], pub, &z[0]) : mb_add(ctx, x->s[0], pub, &z[0]);
   if (rc != MB_OK) return rc;
   for (int i = 1; i < 3; i++) {
+    // tensors are immutable, so a share whose shape already is the result shape is shared, not copied
+    if (mb_same_shape(x->s[i], z[0])) {
+      z[i] = mb_tensor_retain(x->s[i]);
+      continue;
+    }
     rc = mb_broadcast(ctx, x->s[i], z[0]->rank, z[0]->shape, &z[i]);
     if (rc != MB_OK) {
       for (int j = 0; j < i; j++) mb_tensor_free(ctx, z[j]);
@@ -260,7 +265,10 @@ extern "C" int mb_rep_public_sub(mb_ctx *ctx, const mb_tensor *pub, const mb_rep
   for (int i = 1; i < 3; i++) {
     Tmp n(ctx);
     rc = mb_neg(ctx, x->s[i], &n.p);
-    if (rc == MB_OK) rc = mb_broadcast(ctx, n.p, z[0]->rank, z[0]->shape, &z[i]);
+    if (rc == MB_OK) {
+      if (mb_same_shape(n.p, z[0])) z[i] = n.release();
+      else rc = mb_broadcast(ctx, n.p, z[0]->rank, z[0]->shape, &z[i]);
+    }
     if (rc != MB_OK) {
       for (int j = 0; j < i; j++) mb_tensor_free(ctx, z[j]);
       return rc;
