@@ -101,6 +101,50 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def dist_setup(world, local_rank, backend=None):
+    """One process per GPU (torchrun): returns torch.distributed or None.  `backend` defaults to nccl; the CPU
+    tests of the multi-rank logic pass "gloo"."""
+    if world <= 1:
+        return None
+    import torch
+    import torch.distributed as dist
+    backend = backend or "nccl"
+    if backend == "nccl":
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    else:
+        dist.init_process_group(backend)
+    return dist
+
+
+def _reduce_device(dist, local_rank):
+    return f"cuda:{local_rank}" if dist.get_backend() == "nccl" else "cpu"
+
+
+def reduce_max(dist, values, local_rank=0):
+    """Max over ranks of each entry (device times of the timed regions)."""
+    if dist is None:
+        return [float(v) for v in values]
+    import torch
+    t = torch.tensor(list(values), dtype=torch.float64, device=_reduce_device(dist, local_rank))
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return [float(v) for v in t]
+
+
+def reduce_sum_int(dist, value, local_rank=0):
+    if dist is None:
+        return int(value)
+    import torch
+    t = torch.tensor([int(value)], dtype=torch.int64, device=_reduce_device(dist, local_rank))
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return int(t[0])
+
+
+def aggregate_value(units_per_rank_step, steps, world, max_ms):
+    """Whole-job throughput: every rank processes the same number of units (weak scaling), time = max over ranks."""
+    return world * units_per_rank_step * steps / (max_ms * 1e-3)
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -165,12 +209,7 @@ def run_mlp(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    dist = None
-    if world > 1:
-        import torch
-        import torch.distributed as dist
-        torch.cuda.set_device(local_rank)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dist = dist_setup(world, local_rank)
     dims = (784, 512, 512, 10)
     rng = np.random.default_rng(3 + rank)
     ws = [np.random.default_rng(4 + i).normal(0, dims[i] ** -0.5, (dims[i], dims[i + 1])) for i in range(3)]
@@ -190,11 +229,8 @@ def run_mlp(args):
         out = pred.forward_shared(xf)
     ms = sess.timer_stop()
     launches = sess.launch_count - l0
-    if dist is not None:
-        import torch
-        t = torch.tensor([ms], dtype=torch.float64, device=f"cuda:{local_rank}")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t[0])
+    ms = reduce_max(dist, [ms], local_rank)[0]
+    launches = reduce_sum_int(dist, launches, local_rank)
     got = sess.fixedpoint_decode(23, sess.reveal(out)).to_host()[:64]
     ref = x[:64]
     for i in range(3):
@@ -203,7 +239,7 @@ def run_mlp(args):
             ref = np.maximum(ref, 0)
     if rank == 0:
         print(json.dumps({
-            "metric": "mlp_inference_rows_per_s", "value": world * args.batch * args.steps / (ms * 1e-3),
+            "metric": "mlp_inference_rows_per_s", "value": aggregate_value(args.batch, args.steps, world, ms),
             "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u64", "data": "synthetic",
@@ -240,13 +276,7 @@ def main():
         return
 
     import moose_b200 as mb
-    dist = None
-    if world > 1:
-        import torch
-        import torch.distributed as dist_mod
-        torch.cuda.set_device(local_rank)
-        dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-        dist = dist_mod
+    dist = dist_setup(world, local_rank)
 
     def barrier():
         if dist is not None:
@@ -314,14 +344,8 @@ def main():
     ms_e2e = max(ms_e2e_dev, 1e3 * (time.perf_counter() - t0))
     barrier()
 
-    if dist is not None:
-        import torch
-        t = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=f"cuda:{local_rank}")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, ms_e2e = float(t[0]), float(t[1])
-        tl = torch.tensor([launches], dtype=torch.int64, device=f"cuda:{local_rank}")
-        dist.all_reduce(tl, op=dist.ReduceOp.SUM)
-        launches = int(tl[0])
+    ms, ms_e2e = reduce_max(dist, [ms, ms_e2e], local_rank)
+    launches = reduce_sum_int(dist, launches, local_rank)
 
     # spot check: the revealed product decodes to A @ B (plaintext) within the TruncPr error
     ok = True
@@ -333,8 +357,8 @@ def main():
 
     if rank == 0:
         ops = ring_ops_per_step(M, K, N)
-        value = world * ops * args.steps / (ms * 1e-3) / 1e9
-        e2e = world * ops * args.steps / (ms_e2e * 1e-3) / 1e9
+        value = aggregate_value(ops, args.steps, world, ms) / 1e9
+        e2e = aggregate_value(ops, args.steps, world, ms_e2e) / 1e9
         peaks, peak_src = measured_peaks()
         # dominant kernel: limb_gemm_kernel, one batched launch per step = 3 parties x ([M, 2K] x [2K, N] ring GEMM
         # as 136 u8 x u8 limb GEMMs)

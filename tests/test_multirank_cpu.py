@@ -1,0 +1,52 @@
+"""CPU tests (gloo, world_size 2) of the N>1 path of bench.py: one independent session per rank, no data-path
+collective; the only cross-rank steps are the barrier, the max-over-ranks device time and the summed launch
+count, then the whole-job aggregate computed on rank 0."""
+import os
+import sys
+
+import pytest
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update({"MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port), "RANK": str(rank),
+                       "WORLD_SIZE": str(world), "LOCAL_RANK": str(rank)})
+    import bench
+    dist = bench.dist_setup(world, rank, backend="gloo")
+    dist.barrier()
+    ms, ms_e2e = bench.reduce_max(dist, [10.0 + 5 * rank, 30.0 - 7 * rank], rank)
+    launches = bench.reduce_sum_int(dist, 100 + rank, rank)
+    value = bench.aggregate_value(bench.ring_ops_per_step(8, 8, 8), steps=4, world=world, max_ms=ms)
+    q.put((rank, ms, ms_e2e, launches, value))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_world2_reduction_and_aggregate():
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29611 + os.getpid() % 200
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = sorted(q.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, ms, ms_e2e, launches, value in results:
+        assert ms == 15.0 and ms_e2e == 30.0        # max over ranks
+        assert launches == 201                      # summed
+        ops = 3 * 2 * 2 * 8 * 8 * 8
+        assert value == pytest.approx(world * ops * 4 / 15e-3)
+
+
+def test_single_rank_helpers_are_identity():
+    sys.path.insert(0, ROOT)
+    import bench
+    assert bench.dist_setup(1, 0) is None
+    assert bench.reduce_max(None, [1.5, 2.5]) == [1.5, 2.5]
+    assert bench.reduce_sum_int(None, 7) == 7
