@@ -174,8 +174,11 @@ def cpu_baseline_run(size, threads, with_trunc=True):
 def run_reference(args, rank, world):
     if rank != 0:
         return
-    from oracle import moose_oracle as mo
-    threads = mo.max_threads()
+    # all host threads the process may use (torchrun exports OMP_NUM_THREADS=1, so ask the OS, not OpenMP)
+    try:
+        threads = len(os.sched_getaffinity(0))
+    except AttributeError:
+        threads = os.cpu_count() or 1
     size = max(args.ref_size, 1024)
     for _ in range(min(args.warmup, 1)):
         cpu_baseline_run(min(size, 128), threads)
