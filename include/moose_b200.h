@@ -273,6 +273,24 @@ int mb_rep_less(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out_bits
 int mb_rep_maximum(mb_ctx *ctx, const mb_rep *const *xs, int n, mb_rep **out);
 /* ReluOp::rep_ring_kernel (moose/src/fixedpoint/ops.rs:314-330). */
 int mb_rep_relu(mb_ctx *ctx, const mb_rep *x, mb_rep **out);
+/* FillOp::rep_ring64/128_kernel (moose/src/replicated/ops.rs:91-160): public constant as a replicated tensor,
+ * shares (v, 0, 0). */
+int mb_rep_fill(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, uint64_t value_lo, uint64_t value_hi,
+                mb_rep **out);
+/* GreaterOp::rep_kernel (moose/src/replicated/compare.rs:136-149): msb(y - x). */
+int mb_rep_greater(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out_bits);
+/* Fixed-point math on replicated ring shares with RepFixedTensor's (integral, fractional) precision passed
+ * explicitly.  DivOp::rep_rep_kernel (moose/src/replicated/division.rs:5-86, Goldschmidt; requires
+ * 2*(i+f) <= ring bits like the reference), Pow2Op / ExpOp (moose/src/replicated/exp.rs:11-111,219-244,
+ * polynomial P_1045 via fixedpoint/mod.rs:95-151), SigmoidOp (moose/src/replicated/arith.rs:676-743). */
+int mb_rep_div(mb_ctx *ctx, uint32_t integral_precision, uint32_t fractional_precision, const mb_rep *x,
+               const mb_rep *y, mb_rep **out);
+int mb_rep_pow2(mb_ctx *ctx, uint32_t integral_precision, uint32_t fractional_precision, const mb_rep *x,
+                mb_rep **out);
+int mb_rep_exp(mb_ctx *ctx, uint32_t integral_precision, uint32_t fractional_precision, const mb_rep *x,
+               mb_rep **out);
+int mb_rep_sigmoid(mb_ctx *ctx, uint32_t integral_precision, uint32_t fractional_precision, const mb_rep *x,
+                   mb_rep **out);
 /* IndexAxisOp::rep_kernel axis 0 / ShlDimOp::rep_bit_kernel
  * (moose/src/replicated/ops.rs:331-376,475-504). */
 int mb_rep_index_axis0(mb_ctx *ctx, int64_t index, const mb_rep *x, mb_rep **out);

@@ -93,6 +93,9 @@ ABI = {
     "mb_rep_bit_decompose": [_P, _P, _PP], "mb_rep_msb": [_P, _P, _PP],
     "mb_rep_ring_inject": [_P, _I, _U64, _P, _PP], "mb_rep_mux": [_P, _P, _P, _P, _PP],
     "mb_rep_less": [_P, _P, _P, _PP], "mb_rep_maximum": [_P, _PP, _I, _PP], "mb_rep_relu": [_P, _P, _PP],
+    "mb_rep_fill": [_P, _I, _I, _I64P, _U64, _U64, _PP], "mb_rep_greater": [_P, _P, _P, _PP],
+    "mb_rep_div": [_P, _U32, _U32, _P, _P, _PP], "mb_rep_pow2": [_P, _U32, _U32, _P, _PP],
+    "mb_rep_exp": [_P, _U32, _U32, _P, _PP], "mb_rep_sigmoid": [_P, _U32, _U32, _P, _PP],
     "mb_rep_index_axis0": [_P, _I64, _P, _PP], "mb_rep_shl_dim": [_P, _U64, _U64, _P, _PP],
 }
 _RESTYPES = {
@@ -539,6 +542,27 @@ class Session:
     def relu(self, x) -> RepTensor:
         out = self._out()
         return self._r(lib().mb_rep_relu(self.ctx, x.h, ctypes.byref(out)), out)
+
+    def rep_fill(self, dtype: int, value: int, shape) -> RepTensor:
+        arr, rank = _shape_arr(shape)
+        out = self._out()
+        value = int(value) % (1 << 128)
+        return self._r(lib().mb_rep_fill(self.ctx, dtype, rank, arr, value & ((1 << 64) - 1), value >> 64,
+                                         ctypes.byref(out)), out)
+
+    def rep_greater(self, x, y): return self._rbin(lib().mb_rep_greater, x, y)
+
+    def rep_div(self, i_prec: int, f_prec: int, x, y) -> RepTensor:
+        out = self._out()
+        return self._r(lib().mb_rep_div(self.ctx, i_prec, f_prec, x.h, y.h, ctypes.byref(out)), out)
+
+    def _fixed_unary(self, fn, i_prec, f_prec, x) -> RepTensor:
+        out = self._out()
+        return self._r(fn(self.ctx, i_prec, f_prec, x.h, ctypes.byref(out)), out)
+
+    def rep_pow2(self, i_prec, f_prec, x): return self._fixed_unary(lib().mb_rep_pow2, i_prec, f_prec, x)
+    def rep_exp(self, i_prec, f_prec, x): return self._fixed_unary(lib().mb_rep_exp, i_prec, f_prec, x)
+    def sigmoid(self, i_prec, f_prec, x): return self._fixed_unary(lib().mb_rep_sigmoid, i_prec, f_prec, x)
 
     def rep_index_axis0(self, index: int, x) -> RepTensor:
         out = self._out()

@@ -1,0 +1,362 @@
+// C ABI: the replicated fixed-point math protocols of the LogReg path:
+//   GreaterOp (replicated/compare.rs:136-149), ExpOp / Pow2Op / pow2_from_bits / exp_from_parts
+//   (replicated/exp.rs), PolynomialEval / PrefixMul (fixedpoint/mod.rs:74-151), prefix_op / prefix_or
+//   (replicated/misc.rs:5-40), DivOp / approximate_reciprocal / norm / top_most(_index) / sign_from_msb
+//   (replicated/division.rs), SigmoidOp (replicated/arith.rs:676-743).
+// These are pure orchestration in the reference (hundreds of replicated ops per call); here they replay the
+// same op sequence on the fused replicated entry points, so the entropy order -- and with it every share --
+// matches the op-by-op protocol.  No arithmetic happens on the host.
+#include "common.h"
+
+namespace {
+
+struct Err { int code; };
+inline void ck(int rc) { if (rc != MB_OK) throw Err{rc}; }
+
+struct R {  // owning replicated tensor
+  mb_ctx *c;
+  mb_rep *p;
+  R(mb_ctx *c_, mb_rep *p_) : c(c_), p(p_) {}
+  R(R &&o) noexcept : c(o.c), p(o.p) { o.p = nullptr; }
+  R &operator=(R &&o) noexcept { if (this != &o) { if (p) mb_rep_free(c, p); c = o.c; p = o.p; o.p = nullptr; } return *this; }
+  R(const R &) = delete;
+  R &operator=(const R &) = delete;
+  ~R() { if (p) mb_rep_free(c, p); }
+  R clone() const { mb_rep *q; ck(mb_rep_from_shares(c, p->s[0], p->s[1], p->s[2], &q)); return R(c, q); }
+  const mb_tensor *like() const { return p->s[0]; }
+  mb_rep *release() { mb_rep *q = p; p = nullptr; return q; }
+};
+struct T {  // owning public tensor
+  mb_ctx *c;
+  mb_tensor *p;
+  T(mb_ctx *c_, mb_tensor *p_) : c(c_), p(p_) {}
+  T(T &&o) noexcept : c(o.c), p(o.p) { o.p = nullptr; }
+  T(const T &) = delete;
+  T &operator=(const T &) = delete;
+  ~T() { if (p) mb_tensor_free(c, p); }
+};
+
+#define REP1(name, call) \
+  R name { mb_rep *q = nullptr; ck(call); return R(c, q); }
+
+R add(mb_ctx *c, const R &a, const R &b) { mb_rep *q = nullptr; ck(mb_rep_add(c, a.p, b.p, &q)); return R(c, q); }
+R sub(mb_ctx *c, const R &a, const R &b) { mb_rep *q = nullptr; ck(mb_rep_sub(c, a.p, b.p, &q)); return R(c, q); }
+R mul(mb_ctx *c, const R &a, const R &b) { mb_rep *q = nullptr; ck(mb_rep_mul(c, a.p, b.p, &q)); return R(c, q); }
+R neg(mb_ctx *c, const R &a) { mb_rep *q = nullptr; ck(mb_rep_neg(c, a.p, &q)); return R(c, q); }
+R shl(mb_ctx *c, uint64_t amount, const R &a) { mb_rep *q = nullptr; ck(mb_rep_shl(c, amount, a.p, &q)); return R(c, q); }
+R trunc(mb_ctx *c, uint32_t amount, const R &a) { mb_rep *q = nullptr; ck(mb_rep_trunc_pr(c, amount, a.p, &q)); return R(c, q); }
+R bitdec(mb_ctx *c, const R &a) { mb_rep *q = nullptr; ck(mb_rep_bit_decompose(c, a.p, &q)); return R(c, q); }
+R index0(mb_ctx *c, int64_t i, const R &a) { mb_rep *q = nullptr; ck(mb_rep_index_axis0(c, i, a.p, &q)); return R(c, q); }
+R inject(mb_ctx *c, mb_dtype ring, uint64_t idx, const R &a) { mb_rep *q = nullptr; ck(mb_rep_ring_inject(c, ring, idx, a.p, &q)); return R(c, q); }
+R mux(mb_ctx *c, const R &s, const R &x, const R &y) { mb_rep *q = nullptr; ck(mb_rep_mux(c, s.p, x.p, y.p, &q)); return R(c, q); }
+R msb_bit(mb_ctx *c, const R &a) { mb_rep *q = nullptr; ck(mb_rep_msb(c, a.p, &q)); return R(c, q); }
+R add_pub(mb_ctx *c, const R &a, const T &pub) { mb_rep *q = nullptr; ck(mb_rep_add_public(c, a.p, pub.p, &q)); return R(c, q); }
+R pub_sub(mb_ctx *c, const T &pub, const R &a) { mb_rep *q = nullptr; ck(mb_rep_public_sub(c, pub.p, a.p, &q)); return R(c, q); }
+R mul_pub(mb_ctx *c, const R &a, const T &pub) { mb_rep *q = nullptr; ck(mb_rep_mul_public(c, a.p, pub.p, &q)); return R(c, q); }
+
+mb_dtype ring_of(const R &x) { return x.like()->dtype; }
+int bits_of(const R &x) { return ring_of(x) == MB_RING128 ? 128 : 64; }
+
+// Constant::Fixed -> ring value (kernels/constants.rs:68-72,103-105): ((v * 2^p as f64) as iK) as uK.
+u128 fixed_constant(int bits, double value, unsigned precision) {
+  const double scaled = value * ldexp(1.0, (int)precision);
+  u128 v;
+  const double lim = ldexp(1.0, bits - 1);
+  if (scaled != scaled) v = 0;
+  else if (scaled >= lim) v = ((u128)1 << (bits - 1)) - 1;
+  else if (scaled <= -lim) v = (u128)1 << (bits - 1);
+  else v = (u128)(__int128)scaled;
+  if (bits == 64) v &= (u128)0xFFFFFFFFFFFFFFFFull;
+  return v;
+}
+
+// Mirrored (public) constant with the shape of `like` (ShapeFill, misc.rs:136-170).
+T pub_fill(mb_ctx *c, const mb_tensor *like, u128 v) {
+  mb_tensor *t = nullptr;
+  ck(mb_fill(c, like->dtype, like->rank, like->shape, (uint64_t)v, (uint64_t)(v >> 64), &t));
+  return T(c, t);
+}
+// FillOp::rep_ring64/128_kernel (replicated/ops.rs:91-160): shares (v, 0, 0).
+R rep_fill(mb_ctx *c, const mb_tensor *like, u128 v) {
+  mb_tensor *a = nullptr, *z1 = nullptr, *z2 = nullptr;
+  ck(mb_fill(c, like->dtype, like->rank, like->shape, (uint64_t)v, (uint64_t)(v >> 64), &a));
+  T ta(c, a);
+  ck(mb_fill(c, like->dtype, like->rank, like->shape, 0, 0, &z1));
+  T t1(c, z1);
+  ck(mb_fill(c, like->dtype, like->rank, like->shape, 0, 0, &z2));
+  T t2(c, z2);
+  mb_rep *q = nullptr;
+  ck(mb_rep_from_shares(c, a, z1, z2, &q));
+  return R(c, q);
+}
+
+R greater(mb_ctx *c, const R &x, const R &y) { return msb_bit(c, sub(c, y, x)); }  // msb(y - x), compare.rs:136-149
+
+R msb_ring(mb_ctx *c, const R &x) { return inject(c, ring_of(x), 0, msb_bit(c, x)); }  // arith.rs:628-641
+
+// prefix_op (misc.rs:5-28) with op(res[y], res[y+k])
+template <typename Op>
+void prefix_op(std::vector<R> &res, Op op) {
+  const int v_len = (int)res.size();
+  int log_r = 0;
+  while ((1 << log_r) < v_len) log_r++;
+  for (int i = 0; i < log_r; i++)
+    for (int j = 0; j < (1 << log_r) / (1 << (i + 1)); j++) {
+      const int y = (1 << i) + j * (1 << (i + 1)) - 1;
+      for (int k = 1; k < (1 << i) + 1; k++)
+        if (y + k < v_len) res[y + k] = op(res[y], res[y + k]);
+    }
+}
+
+// division.rs:88-104
+R sign_from_msb(mb_ctx *c, const R &msb) {
+  R dbl = shl(c, 1, msb);
+  T ones = pub_fill(c, msb.like(), 1);
+  return pub_sub(c, ones, dbl);
+}
+
+// division.rs:146-206
+R top_most_index(mb_ctx *c, int max_bits, const R &x) {
+  R x_bits = bitdec(c, x);
+  std::vector<R> y;
+  for (int i = 0; i < max_bits; i++) y.push_back(index0(c, max_bits - i - 1, x_bits));
+  prefix_op(y, [&](const R &a, const R &b) { return add(c, add(c, a, b), mul(c, a, b)); });  // or = xor(xor, and)
+  std::reverse(y.begin(), y.end());
+  std::vector<R> z;
+  for (int i = 0; i + 1 < max_bits; i++) z.push_back(sub(c, y[i], y[i + 1]));
+  z.push_back(y[max_bits - 1].clone());
+  const mb_dtype ring = ring_of(x);
+  std::vector<R> s_vec;
+  for (int i = 0; i < max_bits; i++) {
+    R zi = inject(c, ring, 0, z[i]);
+    s_vec.push_back(shl(c, (uint64_t)(max_bits - i - 1), zi));
+  }
+  R res = shl(c, 0, s_vec[max_bits - 1]);
+  for (int i = 1; i < max_bits; i++) res = add(c, res, s_vec[i]);
+  return res;
+}
+
+// division.rs:110-139
+void div_norm(mb_ctx *c, int max_bits, const R &x, R &upshifted, R &signed_topmost) {
+  R msb = msb_ring(c, x);
+  R sign = sign_from_msb(c, msb);
+  R abs_x = mul(c, sign, x);
+  R tm = top_most_index(c, max_bits, abs_x);
+  upshifted = mul(c, x, tm);
+  signed_topmost = mul(c, sign, tm);
+}
+
+// division.rs:208-249
+R approximate_reciprocal(mb_ctx *c, int i_prec, int f_prec, const R &x) {
+  const int total = i_prec + f_prec;
+  R upshifted(c, nullptr), signed_topmost(c, nullptr);
+  div_norm(c, total, x, upshifted, signed_topmost);
+  T alpha = pub_fill(c, x.like(), fixed_constant(bits_of(x), 2.9142, (unsigned)total));
+  R d = pub_sub(c, alpha, shl(c, 1, upshifted));
+  R w = mul(c, d, signed_topmost);
+  return trunc(c, (uint32_t)(2 * i_prec), w);
+}
+
+// DivOp::rep_rep_kernel (division.rs:5-86)
+R rep_div(mb_ctx *c, int i_prec, int f_prec, const R &x, const R &y) {
+  const int bits = bits_of(x);
+  const int k = i_prec + f_prec;
+  if (2 * k > bits) {
+    mb_fail(c, MB_ERR_INVALID_ARGUMENT, "2 * (fractional_precision + integral_precision) = " + std::to_string(2 * k) +
+                                             ", BitLength = " + std::to_string(bits));
+    throw Err{MB_ERR_INVALID_ARGUMENT};
+  }
+  const int theta = (int)std::ceil(std::log2((double)k / std::log2(17.0)));
+  R w = approximate_reciprocal(c, i_prec, f_prec, y);
+  T alpha = pub_fill(c, x.like(), fixed_constant(bits, 1.0, (unsigned)(2 * f_prec)));
+  R init_prod = mul(c, y, w);  // broadcast to x's shape happens inside the share-wise ops below
+  R a = pub_sub(c, alpha, init_prod);
+  R b = mul(c, x, w);
+  b = trunc(c, (uint32_t)f_prec, b);
+  for (int i = 0; i < theta; i++) {
+    R next_a = mul(c, a, a);
+    R next_b = mul(c, b, add_pub(c, a, alpha));
+    a = trunc(c, (uint32_t)(2 * f_prec), next_a);
+    b = trunc(c, (uint32_t)(2 * f_prec), next_b);
+  }
+  b = mul(c, b, add_pub(c, a, alpha));
+  return trunc(c, (uint32_t)(2 * f_prec), b);
+}
+
+const double P_1045[100] = {
+#include "p1045.inc"
+};
+
+// PolynomialEval::polynomial_eval (fixedpoint/mod.rs:95-151); x has fractional precision f_prec
+R polynomial_eval(mb_ctx *c, int f_prec, const R &x) {
+  const int bits = bits_of(x);
+  int degree = 99;
+  for (int i = 99; i >= 0; i--) {
+    if (P_1045[i] < std::ldexp(1.0, -(f_prec + 1))) degree--;
+    else break;
+  }
+  std::vector<T> coeffs;
+  for (int i = 0; i <= degree; i++) coeffs.push_back(pub_fill(c, x.like(), fixed_constant(bits, P_1045[i], (unsigned)f_prec)));
+  std::vector<R> pre;
+  for (int i = 0; i < degree; i++) pre.push_back(x.clone());
+  prefix_op(pre, [&](const R &a, const R &b) { return trunc(c, (uint32_t)f_prec, mul(c, a, b)); });
+  R acc = mul_pub(c, pre[0], coeffs[1]);
+  for (int i = 1; i < (int)pre.size(); i++) acc = add(c, acc, mul_pub(c, pre[i], coeffs[i + 1]));
+  acc = trunc(c, (uint32_t)f_prec, acc);
+  return add_pub(c, acc, coeffs[0]);
+}
+
+// Pow2FromBits (exp.rs:124-157)
+R pow2_from_bits(mb_ctx *c, const std::vector<R> &xs, int count) {
+  R ones = rep_fill(c, xs[0].like(), 1);
+  std::vector<R> selectors;
+  for (int i = 0; i < count; i++) {
+    R pos = shl(c, (uint64_t)1 << i, xs[i]);
+    R ng = sub(c, ones, xs[i]);
+    selectors.push_back(add(c, pos, ng));
+  }
+  R acc = ones.clone();
+  for (auto &y : selectors) acc = mul(c, acc, y);
+  return acc;
+}
+
+// ExpFromParts (exp.rs:176-217)
+R exp_from_parts(mb_ctx *c, const R &e_int, const R &e_frac, int f, int k) {
+  const int amount = k - 2 - f;
+  R x = shl(c, (uint64_t)amount, e_frac);
+  R e_approx = polynomial_eval(c, k - 2, x);
+  R e_prod = mul(c, e_int, e_approx);
+  return trunc(c, (uint32_t)amount, e_prod);
+}
+
+// Pow2Op::rep_rep_kernel (exp.rs:11-111)
+R rep_pow2(mb_ctx *c, int i_prec, int f_prec, const R &x) {
+  const int bits = bits_of(x);
+  const mb_dtype ring = ring_of(x);
+  R x_bits = bitdec(c, x);
+  R msb = inject(c, ring, 0, index0(c, bits - 1, x_bits));
+  R abs_x = mux(c, msb, neg(c, x), x);
+  R absolute_bits = bitdec(c, abs_x);
+  std::vector<R> higher_bits;
+  for (int i = f_prec; i < bits; i++) higher_bits.push_back(inject(c, ring, 0, index0(c, i, absolute_bits)));
+  R acc = rep_fill(c, x.like(), 0);
+  for (int i = 0; i < (int)higher_bits.size(); i++) acc = add(c, acc, shl(c, (uint64_t)(f_prec + i), higher_bits[i]));
+  R fractional_part = sub(c, abs_x, acc);
+  R d = pow2_from_bits(c, higher_bits, i_prec);
+  R g = exp_from_parts(c, d, fractional_part, f_prec, f_prec + i_prec);
+  R one_fixed = shl(c, (uint64_t)f_prec, rep_fill(c, x.like(), 1));
+  R inverse = rep_div(c, i_prec, f_prec, one_fixed, g);
+  return mux(c, msb, inverse, g);
+}
+
+// ExpOp::rep_rep_kernel (exp.rs:219-244)
+R rep_exp(mb_ctx *c, int i_prec, int f_prec, const R &x) {
+  T log2e = pub_fill(c, x.like(), fixed_constant(bits_of(x), std::log2(std::exp(1.0)), (unsigned)f_prec));
+  R exponent = trunc(c, (uint32_t)f_prec, mul_pub(c, x, log2e));
+  return rep_pow2(c, i_prec, f_prec, exponent);
+}
+
+// SigmoidOp::rep_rep_kernel (arith.rs:676-743)
+R rep_sigmoid(mb_ctx *c, int i_prec, int f_prec, const R &x) {
+  const int bits = bits_of(x);
+  const mb_dtype ring = ring_of(x);
+  R ones_rep = rep_fill(c, x.like(), fixed_constant(bits, 1.0, (unsigned)f_prec));
+  R zeros_rep = rep_fill(c, x.like(), 0);
+  R denominator = add(c, ones_rep, rep_exp(c, i_prec, f_prec, neg(c, x)));
+  R output = rep_div(c, i_prec, f_prec, ones_rep, denominator);
+  const double max_val = std::log(std::pow(2.0, (double)(i_prec - 1)));
+  R max_val_rep = rep_fill(c, x.like(), fixed_constant(bits, max_val, (unsigned)f_prec));
+  R upper_ring = inject(c, ring, 0, greater(c, x, max_val_rep));
+  R upper_wall = mux(c, upper_ring, ones_rep, output);
+  R lower_ring = inject(c, ring, 0, greater(c, neg(c, max_val_rep), x));
+  return mux(c, lower_ring, zeros_rep, upper_wall);
+}
+
+bool valid(const mb_rep *x) { return x && x->s[0] && x->s[1] && x->s[2]; }
+
+template <typename F>
+int guarded(mb_ctx *ctx, const char *name, F f) {
+  if (!ctx) return mb_fail(nullptr, MB_ERR_INVALID_ARGUMENT, std::string(name) + ": NULL context");
+  try {
+    return f();
+  } catch (const Err &e) {
+    return e.code;  // message already recorded by the failing call
+  } catch (const std::exception &e) {
+    return mb_fail(ctx, MB_ERR_KERNEL, std::string(name) + ": " + e.what());
+  }
+}
+
+int check_fixed(mb_ctx *ctx, const mb_rep *x, uint32_t i_prec, uint32_t f_prec, const char *name) {
+  if (!valid(x)) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, std::string(name) + ": NULL argument");
+  if (!mb_is_ring(x->s[0]->dtype)) return mb_fail(ctx, MB_ERR_TYPE_MISMATCH, std::string(name) + ": needs ring shares");
+  const int bits = x->s[0]->dtype == MB_RING128 ? 128 : 64;
+  if (i_prec == 0 || f_prec == 0 || (int)(i_prec + f_prec) >= bits)
+    return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, std::string(name) + ": bad fixed-point precision");
+  return MB_OK;
+}
+
+}  // namespace
+
+extern "C" int mb_rep_fill(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, uint64_t lo, uint64_t hi, mb_rep **out) {
+  return guarded(ctx, "mb_rep_fill", [&]() {
+    if (!out) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_rep_fill: NULL out");
+    mb_tensor *like = nullptr;
+    ck(mb_fill(ctx, dtype, rank, shape, lo, hi, &like));
+    T tl(ctx, like);
+    mb_tensor *z1 = nullptr, *z2 = nullptr;
+    ck(mb_fill(ctx, dtype, rank, shape, 0, 0, &z1));
+    T t1(ctx, z1);
+    ck(mb_fill(ctx, dtype, rank, shape, 0, 0, &z2));
+    T t2(ctx, z2);
+    return mb_rep_from_shares(ctx, like, z1, z2, out);
+  });
+}
+
+extern "C" int mb_rep_greater(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out) {
+  return guarded(ctx, "mb_rep_greater", [&]() { return mb_rep_less(ctx, y, x, out); });  // msb(y - x)
+}
+
+#define BORROW(x) R(ctx, nullptr)
+static R borrow(mb_ctx *ctx, const mb_rep *x) {
+  mb_rep *q = nullptr;
+  ck(mb_rep_from_shares(ctx, x->s[0], x->s[1], x->s[2], &q));
+  return R(ctx, q);
+}
+
+extern "C" int mb_rep_div(mb_ctx *ctx, uint32_t i_prec, uint32_t f_prec, const mb_rep *x, const mb_rep *y, mb_rep **out) {
+  return guarded(ctx, "mb_rep_div", [&]() {
+    MB_CHECK(check_fixed(ctx, x, i_prec, f_prec, "mb_rep_div"));
+    MB_CHECK(check_fixed(ctx, y, i_prec, f_prec, "mb_rep_div"));
+    if (!out) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_rep_div: NULL out");
+    R r = rep_div(ctx, (int)i_prec, (int)f_prec, borrow(ctx, x), borrow(ctx, y));
+    *out = r.release();
+    return (int)MB_OK;
+  });
+}
+extern "C" int mb_rep_pow2(mb_ctx *ctx, uint32_t i_prec, uint32_t f_prec, const mb_rep *x, mb_rep **out) {
+  return guarded(ctx, "mb_rep_pow2", [&]() {
+    MB_CHECK(check_fixed(ctx, x, i_prec, f_prec, "mb_rep_pow2"));
+    if (!out) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_rep_pow2: NULL out");
+    R r = rep_pow2(ctx, (int)i_prec, (int)f_prec, borrow(ctx, x));
+    *out = r.release();
+    return (int)MB_OK;
+  });
+}
+extern "C" int mb_rep_exp(mb_ctx *ctx, uint32_t i_prec, uint32_t f_prec, const mb_rep *x, mb_rep **out) {
+  return guarded(ctx, "mb_rep_exp", [&]() {
+    MB_CHECK(check_fixed(ctx, x, i_prec, f_prec, "mb_rep_exp"));
+    if (!out) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_rep_exp: NULL out");
+    R r = rep_exp(ctx, (int)i_prec, (int)f_prec, borrow(ctx, x));
+    *out = r.release();
+    return (int)MB_OK;
+  });
+}
+extern "C" int mb_rep_sigmoid(mb_ctx *ctx, uint32_t i_prec, uint32_t f_prec, const mb_rep *x, mb_rep **out) {
+  return guarded(ctx, "mb_rep_sigmoid", [&]() {
+    MB_CHECK(check_fixed(ctx, x, i_prec, f_prec, "mb_rep_sigmoid"));
+    if (!out) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_rep_sigmoid: NULL out");
+    R r = rep_sigmoid(ctx, (int)i_prec, (int)f_prec, borrow(ctx, x));
+    *out = r.release();
+    return (int)MB_OK;
+  });
+}

@@ -55,10 +55,12 @@ class MLPPredictor:
 
 
 class LinearPredictor:
-    """dot + trunc prefix of LinearRegressor / LinearClassifier (the sigmoid post-transform is not built yet)."""
+    """LinearRegressor (post_transform None) / LinearClassifier with PostTransform.SIGMOID for two classes
+    (linear_predictor.py:160-175): y = sigmoid(dot([1, x], w))."""
 
-    def __init__(self, sess: Session, coeffs: np.ndarray, intercepts: np.ndarray, ring: int = RING128, frac: int = 40):
-        self.sess, self.ring, self.frac = sess, ring, frac
+    def __init__(self, sess: Session, coeffs: np.ndarray, intercepts: np.ndarray, ring: int = RING128, frac: int = 40,
+                 integral: int = 24, post_transform: str = "none"):
+        self.sess, self.ring, self.frac, self.integral, self.post = sess, ring, frac, integral, post_transform
         w = np.concatenate([np.asarray(intercepts, dtype=np.float64).reshape(1, -1).T.T, np.asarray(coeffs, dtype=np.float64).T], axis=0)
         self.w = sess.fixedpoint_encode(ring, frac, sess.from_host(FLOAT64, w))  # [1 + features, classes]
 
@@ -66,7 +68,10 @@ class LinearPredictor:
         s = self.sess
         x = s.share(x_with_bias_fixed, 0)
         w = s.share(self.w, 0)
-        return s.trunc_pr(self.frac, s.rep_dot(x, w))
+        y = s.trunc_pr(self.frac, s.rep_dot(x, w))
+        if self.post == "sigmoid":
+            y = s.sigmoid(self.integral, self.frac, y)
+        return y
 
     def __call__(self, x: np.ndarray) -> np.ndarray:
         xb = np.concatenate([np.ones((x.shape[0], 1)), x], axis=1)

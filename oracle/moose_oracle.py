@@ -998,3 +998,228 @@ def rep_relu(sess: Session, x: RepTensor) -> RepTensor:
     sign = rep_msb_ring(sess, x)
     zeros = RepTensor([[zeros_like(v) for v in row] for row in x.shares])
     return rep_mux(sess, sign, zeros, x)
+
+
+# ---------------------------------------------------------------------------
+# exp / pow2 / division / sigmoid (replicated/exp.rs, division.rs, arith.rs:676-743,
+# fixedpoint/mod.rs:74-151, misc.rs:5-40).  Fixed-point values are plain RepTensors plus
+# (integral, fractional) precision passed explicitly, like RepFixedTensor's fields.
+# ---------------------------------------------------------------------------
+
+def fixed_constant(bits: int, value: float, precision: int) -> int:
+    """Constant::Fixed -> ring value (kernels/constants.rs:68-72,103-105): ((v * 2^p as f64) as iK) as uK."""
+    import struct
+    scaled = float(value) * float(1 << precision)
+    if scaled != scaled:
+        v = 0
+    else:
+        lim = float(1 << (bits - 1))
+        v = (1 << (bits - 1)) - 1 if scaled >= lim else (-(1 << (bits - 1)) if scaled <= -lim else int(scaled))
+    return v % (1 << bits)
+
+
+def rep_fill(bits: int, value: int, shape) -> RepTensor:
+    """FillOp::rep_ring64/128_kernel (replicated/ops.rs:91-160): shares [[v,0],[0,0],[0,v]]."""
+    v, z = fill(bits, value, shape), fill(bits, 0, shape)
+    return RepTensor([[v, z], [z, z], [z, v]])
+
+
+def rep_fill_bits(value: int, shape) -> RepTensor:
+    v, z = fill_bits(value, shape), fill_bits(0, shape)
+    return RepTensor([[v, z], [z, z], [z, v]])
+
+
+def rep_broadcast(x: RepTensor, shape) -> RepTensor:
+    return RepTensor([[v if v.shape == tuple(shape) else broadcast(v, shape) for v in row] for row in x.shares])
+
+
+def prefix_op(sess, xs, op):
+    """ReplicatedPlacement::prefix_op (replicated/misc.rs:5-28)."""
+    v_len = len(xs)
+    log_r = int(math.ceil(math.log2(v_len))) if v_len > 1 else 0
+    res = list(xs)
+    for i in range(log_r):
+        for j in range((2 ** log_r) // (2 ** (i + 1))):
+            y = 2 ** i + j * 2 ** (i + 1) - 1
+            for k in range(1, 2 ** i + 1):
+                if y + k < v_len:
+                    res[y + k] = op(sess, res[y], res[y + k])
+    return res
+
+
+def prefix_or(sess, xs):
+    """misc.rs:30-40: or(x, y) = xor(xor(x, y), and(x, y))."""
+    return prefix_op(sess, xs, lambda s, x, y: rep_xor(rep_xor(x, y), rep_and(s, x, y)))
+
+
+def sign_from_msb(bits: int, msb_ring: RepTensor) -> RepTensor:
+    """SignFromMsb (division.rs:88-104): 1 - 2 msb."""
+    double = rep_shl(1, msb_ring)
+    return rep_mir_sub(mir_fill(bits, 1, msb_ring.shape), double)
+
+
+def top_most(sess, max_bits: int, x: RepTensor):
+    """TopMost::top_most (division.rs:146-177)."""
+    x_bits = rep_bit_decompose(sess, x)
+    x_rev = [rep_index(max_bits - i - 1, x_bits) for i in range(max_bits)]
+    y = prefix_or(sess, x_rev)
+    y.reverse()
+    z = [rep_sub(y[i], y[i + 1]) for i in range(max_bits - 1)]
+    z.append(y[max_bits - 1])
+    return z
+
+
+def top_most_index(sess, bits: int, max_bits: int, x: RepTensor) -> RepTensor:
+    """TopMostIndex::top_most_index (division.rs:183-206)."""
+    z = top_most(sess, max_bits, x)
+    z_ring = [rep_ring_inject(sess, bits, 0, e) for e in z]
+    s_vec = [rep_shl(max_bits - i - 1, zi) for i, zi in enumerate(z_ring)]
+    res = rep_shl(0, s_vec[max_bits - 1])
+    for item in s_vec[1:max_bits]:
+        res = rep_add(res, item)
+    return res
+
+
+def div_norm(sess, bits: int, max_bits: int, x: RepTensor):
+    """DivNorm::norm (division.rs:110-139)."""
+    msb = rep_msb_ring(sess, x)
+    sign = sign_from_msb(bits, msb)
+    abs_x = rep_mul(sess, sign, x)
+    tm = top_most_index(sess, bits, max_bits, abs_x)
+    upshifted = rep_mul(sess, x, tm)
+    signed_topmost = rep_mul(sess, sign, tm)
+    return upshifted, signed_topmost
+
+
+def approximate_reciprocal(sess, bits: int, int_precision: int, frac_precision: int, x: RepTensor) -> RepTensor:
+    """ApproximateReciprocal (division.rs:208-249)."""
+    total = int_precision + frac_precision
+    upshifted, signed_topmost = div_norm(sess, bits, total, x)
+    alpha = mir_fill(bits, fixed_constant(bits, 2.9142, total), x.shape)
+    d = rep_mir_sub(alpha, rep_shl(1, upshifted))
+    w = rep_mul(sess, d, signed_topmost)
+    return rep_trunc_pr(sess, 2 * int_precision, w)
+
+
+def rep_div(sess, i_prec: int, f_prec: int, x: RepTensor, y: RepTensor) -> RepTensor:
+    """DivOp::rep_rep_kernel (division.rs:5-86), Goldschmidt."""
+    bits = x.shares[0][0].bits
+    k = i_prec + f_prec
+    assert 2 * k <= bits, f"2 * (fractional_precision + integral_precision) = {2 * k}, BitLength = {bits}"
+    theta = int(math.ceil(math.log2(k / math.log2(17.0))))
+    w = approximate_reciprocal(sess, bits, i_prec, f_prec, y)
+    rep_alpha = mir_fill(bits, fixed_constant(bits, 1.0, 2 * f_prec), x.shape)
+    init_prod = rep_mul(sess, y, w)
+    init_prod_resized = rep_broadcast(init_prod, x.shape)
+    a = rep_mir_sub(rep_alpha, init_prod_resized)
+    b = rep_mul(sess, x, w)
+    b = rep_trunc_pr(sess, f_prec, b)
+    for _ in range(theta):
+        next_a = rep_mul(sess, a, a)
+        next_b = rep_mul(sess, b, rep_mir_add(rep_alpha, a))
+        a = rep_trunc_pr(sess, 2 * f_prec, next_a)
+        b = rep_trunc_pr(sess, 2 * f_prec, next_b)
+    b = rep_mul(sess, b, rep_mir_add(rep_alpha, a))
+    return rep_trunc_pr(sess, 2 * f_prec, b)
+
+
+def p_1045():
+    """P_1045 (exp.rs:159-170): ln(2)^i / i! for i < 100, from the exact rational of the f64 power."""
+    from fractions import Fraction
+    out = []
+    for i in range(100):
+        ln2i = Fraction(math.pow(math.log(2.0), float(i)))
+        out.append(float(ln2i / math.factorial(i)))
+    return out
+
+
+def polynomial_eval(sess, f_prec: int, coeffs, x: RepTensor) -> RepTensor:
+    """PolynomialEval::polynomial_eval (fixedpoint/mod.rs:95-151); x has fractional precision f_prec."""
+    bits = x.shares[0][0].bits
+    degree = len(coeffs) - 1
+    for c in reversed(coeffs):
+        if c < 2.0 ** (-(f_prec + 1)):
+            degree -= 1
+        else:
+            break
+    coeffs_mir = [mir_fill(bits, fixed_constant(bits, c, f_prec), x.shape) for c in coeffs[: degree + 1]]
+    x_n = [x for _ in range(degree)]
+    x_pre_mul = prefix_op(sess, x_n, lambda s, a, b: rep_trunc_pr(s, f_prec, rep_mul(s, a, b)))
+    x_mul_coeffs = [rep_mir_mul(coeffs_mir[i + 1], x_pre_mul[i]) for i in range(len(x_pre_mul))]
+    acc = x_mul_coeffs[0]
+    for t in x_mul_coeffs[1:]:
+        acc = rep_add(acc, t)      # AddNOp::rep_kernel: share-wise add_n
+    acc = rep_trunc_pr(sess, f_prec, acc)
+    return rep_add_mir(acc, coeffs_mir[0])
+
+
+def pow2_from_bits(sess, bits: int, xs) -> RepTensor:
+    """Pow2FromBits (exp.rs:124-157)."""
+    ones = rep_fill(bits, 1, xs[0].shape)
+    selectors = []
+    for i, bit in enumerate(xs):
+        pos = rep_shl(1 << i, bit)
+        neg_ = rep_sub(ones, bit)
+        selectors.append(rep_add(pos, neg_))
+    acc = ones
+    for y in selectors:
+        acc = rep_mul(sess, acc, y)
+    return acc
+
+
+def exp_from_parts(sess, e_int: RepTensor, e_frac: RepTensor, f: int, k: int) -> RepTensor:
+    """ExpFromParts (exp.rs:176-217)."""
+    amount = k - 2 - f
+    x = rep_shl(amount, e_frac)
+    e_approx = polynomial_eval(sess, k - 2, p_1045(), x)
+    e_prod = rep_mul(sess, e_int, e_approx)
+    return rep_trunc_pr(sess, amount, e_prod)
+
+
+def rep_pow2(sess, i_prec: int, f_prec: int, x: RepTensor) -> RepTensor:
+    """Pow2Op::rep_rep_kernel (exp.rs:11-111)."""
+    bits = x.shares[0][0].bits
+    bit_len_prec = f_prec + i_prec
+    x_bits = rep_bit_decompose(sess, x)
+    msb_bit = rep_index(bits - 1, x_bits)
+    msb = rep_ring_inject(sess, bits, 0, msb_bit)
+    abs_x = rep_mux(sess, msb, rep_neg(x), x)
+    absolute_bits = rep_bit_decompose(sess, abs_x)
+    x_bits_vec = [rep_index(i, absolute_bits) for i in range(bits)]
+    higher_bits = [rep_ring_inject(sess, bits, 0, x_bits_vec[i]) for i in range(f_prec, bits)]
+    acc = rep_fill(bits, 0, x.shape)
+    for i, item in enumerate(higher_bits):
+        acc = rep_add(acc, rep_shl(f_prec + i, item))
+    fractional_part = rep_sub(abs_x, acc)
+    d = pow2_from_bits(sess, bits, higher_bits[0:i_prec])
+    g = exp_from_parts(sess, d, fractional_part, f_prec, bit_len_prec)
+    one = rep_fill(bits, 1, x.shape)
+    one_fixed = rep_shl(f_prec, one)
+    inverse = rep_div(sess, i_prec, f_prec, one_fixed, g)
+    return rep_mux(sess, msb, inverse, g)
+
+
+def rep_exp(sess, i_prec: int, f_prec: int, x: RepTensor) -> RepTensor:
+    """ExpOp::rep_rep_kernel (exp.rs:219-244)."""
+    bits = x.shares[0][0].bits
+    log2e = mir_fill(bits, fixed_constant(bits, math.log2(math.exp(1.0)), f_prec), x.shape)
+    shifted_exponent = rep_mir_mul(log2e, x)
+    exponent = rep_trunc_pr(sess, f_prec, shifted_exponent)
+    return rep_pow2(sess, i_prec, f_prec, exponent)
+
+
+def rep_sigmoid(sess, i_prec: int, f_prec: int, x: RepTensor) -> RepTensor:
+    """SigmoidOp::rep_rep_kernel (arith.rs:676-743)."""
+    bits = x.shares[0][0].bits
+    ones_rep = rep_fill(bits, fixed_constant(bits, 1.0, f_prec), x.shape)
+    zeros_rep = rep_fill(bits, 0, x.shape)
+    denominator = rep_add(ones_rep, rep_exp(sess, i_prec, f_prec, rep_neg(x)))
+    output = rep_div(sess, i_prec, f_prec, ones_rep, denominator)
+    max_val = math.log(2.0 ** (i_prec - 1))
+    max_val_rep = rep_fill(bits, fixed_constant(bits, max_val, f_prec), x.shape)
+    upper = rep_greater(sess, x, max_val_rep)
+    upper_ring = rep_ring_inject(sess, bits, 0, upper)
+    upper_wall = rep_mux(sess, upper_ring, ones_rep, output)
+    lower = rep_greater(sess, rep_neg(max_val_rep), x)
+    lower_ring = rep_ring_inject(sess, bits, 0, lower)
+    return rep_mux(sess, lower_ring, zeros_rep, upper_wall)

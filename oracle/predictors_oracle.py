@@ -29,3 +29,14 @@ def mlp(sess, x, weights, biases, bits=64, frac=23, relu_via="maximum"):
     bf = [mo.fixed_encode(bits, np.asarray(b, dtype=np.float64).reshape(1, -1), frac) for b in biases]
     out = mlp_forward_shared(sess, xf, wf, bf, frac, relu_via)
     return out, mo.fixed_decode(mo.rep_reveal(out), frac)
+
+
+def linear(sess, x, coeffs, intercepts, bits=128, frac=40, integral=24, post_transform="none"):
+    xb = np.concatenate([np.ones((x.shape[0], 1)), x], axis=1)
+    w = np.concatenate([np.asarray(intercepts, dtype=np.float64).reshape(1, -1), np.asarray(coeffs, dtype=np.float64).T], axis=0)
+    xr = mo.rep_share(sess, mo.fixed_encode(bits, xb, frac), 0)
+    wr = mo.rep_share(sess, mo.fixed_encode(bits, w, frac), 0)
+    y = mo.rep_trunc_pr(sess, frac, mo.rep_dot(sess, xr, wr))
+    if post_transform == "sigmoid":
+        y = mo.rep_sigmoid(sess, integral, frac, y)
+    return y, mo.fixed_decode(mo.rep_reveal(y), frac)

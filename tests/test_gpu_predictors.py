@@ -61,3 +61,25 @@ def test_linear_ring128_dot_trunc_prefix():
         np.testing.assert_almost_equal(out, x @ coeffs.T + intercepts, decimal=5)
     finally:
         g.close()
+
+
+def test_logreg_sigmoid_ring128_share_parity():
+    """BASELINE config 3 at an oracle-sized batch: LinearClassifier(SIGMOID, 2 classes), 512 features, Ring128
+    fixed(24,40); classifier outputs are checked at decimal=2 like the reference's predictor tests
+    (linear_predictor_test.py:81-115)."""
+    rng = np.random.default_rng(1)
+    feats, batch = 512, 64
+    coeffs, intercepts = rng.normal(0, feats ** -0.5, (2, feats)), rng.normal(0, 0.1, (1, 2))
+    x = rng.uniform(-1, 1, (batch, feats))
+    g, o = mb.Session(0, SESSION_ID, ENTROPY_KEY), mo.Session(SESSION_ID, ENTROPY_KEY)
+    try:
+        pred = LinearPredictor(g, coeffs, intercepts, post_transform="sigmoid")
+        xb = np.concatenate([np.ones((batch, 1)), x], axis=1)
+        gout = pred.forward_shared(g.fixedpoint_encode(mb.RING128, 40, g.from_host(mb.FLOAT64, xb)))
+        oout, odec = po.linear(o, x, coeffs, intercepts, post_transform="sigmoid")
+        assert same_rep(gout, oout)
+        dec = g.fixedpoint_decode(40, g.reveal(gout)).to_host()
+        ref = 1.0 / (1.0 + np.exp(-(x @ coeffs.T + intercepts)))
+        np.testing.assert_almost_equal(dec, ref, decimal=2)
+    finally:
+        g.close()
