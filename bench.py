@@ -254,6 +254,61 @@ def run_mlp(args):
         dist.destroy_process_group()
 
 
+def run_logreg(args):
+    """BASELINE configs[2]: LinearClassifier, 512 features, 2 classes, sigmoid post-transform, Ring128 fixed(24,40).
+    One step = share + dot [B,513]x[513,2] + TruncPr + sigmoid over a device-resident fixed-point batch."""
+    import moose_b200 as mb
+    from moose_b200.predictors import LinearPredictor
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = dist_setup(world, local_rank)
+    feats = 512
+    B = args.batch
+    coeffs = np.random.default_rng(2).normal(0, feats ** -0.5, (2, feats))
+    intercepts = np.random.default_rng(22).normal(0, 0.1, (1, 2))
+    sess = mb.Session(local_rank, f"{SESSION_ID}-logreg-{rank}", ENTROPY_KEY)
+    pred = LinearPredictor(sess, coeffs, intercepts, mb.RING128, 40, 24, "sigmoid")
+    rng = np.random.default_rng(1 + rank)
+    # build the fixed-point input on the device in chunks (the f64 matrix alone is 4 GB at B = 10^6)
+    x_head = None
+    chunks = []
+    for lo in range(0, B, 1 << 17):
+        n = min(1 << 17, B - lo)
+        xc = np.concatenate([np.ones((n, 1)), rng.uniform(-1, 1, (n, feats))], axis=1)
+        if x_head is None:
+            x_head = xc[:64].copy()
+        chunks.append(fixed128(xc))
+    xf = sess.from_host(mb.RING128, np.concatenate(chunks, axis=0))
+    del chunks
+    for _ in range(args.warmup):
+        out = pred.forward_shared(xf)
+    sess.sync()
+    if dist is not None:
+        dist.barrier()
+    l0 = sess.launch_count
+    sess.timer_start()
+    for _ in range(args.steps):
+        out = pred.forward_shared(xf)
+    ms = sess.timer_stop()
+    launches = reduce_sum_int(dist, sess.launch_count - l0, local_rank)
+    ms = reduce_max(dist, [ms], local_rank)[0]
+    got = sess.fixedpoint_decode(40, sess.reveal(out)).to_host()[:64]
+    ref = 1.0 / (1.0 + np.exp(-(x_head[:, 1:] @ coeffs.T + intercepts)))
+    if rank == 0:
+        print(json.dumps({
+            "metric": "logreg_inference_rows_per_s", "value": aggregate_value(B, args.steps, world, ms),
+            "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u128", "data": "synthetic",
+            "config": {"workload": f"logreg_512features_2classes_sigmoid_ring128_fixed(24,40)_batch{B}",
+                       "max_abs_err_vs_float": float(np.abs(got - ref).max())},
+            "gpu_launches": int(launches)}), flush=True)
+    sess.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -263,12 +318,14 @@ def main():
     ap.add_argument("--size", type=int, default=4096, help="M=N=K (default: the BASELINE config, 4096)")
     ap.add_argument("--ref-size", type=int, default=640, help="sample size of the CPU baseline arms")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="matmul", choices=["matmul", "mlp"],
+    ap.add_argument("--workload", default="matmul", choices=["matmul", "mlp", "logreg"],
                     help="matmul = BASELINE configs[1] (the bench contract); mlp = configs[3], a secondary line")
     ap.add_argument("--batch", type=int, default=65536)
     args = ap.parse_args()
     if args.workload == "mlp":
         return run_mlp(args)
+    if args.workload == "logreg":
+        return run_logreg(args)
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

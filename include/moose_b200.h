@@ -109,6 +109,11 @@ int mb_tensor_alloc(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape,
  * synchronises the stream. */
 int mb_tensor_to_host(mb_ctx *ctx, const mb_tensor *t, void *host_out, size_t nbytes);
 int mb_tensor_free(mb_ctx *ctx, mb_tensor *t);
+/* Device-to-device copies between a tensor and a caller-owned device buffer of mb_tensor_nbytes bytes,
+ * asynchronous on the context stream (for callers that move tensors with their own transport, e.g.
+ * NCCL send/recv in party-per-GPU mode: the Send/Receive ops of moose/src/networking/mod.rs:16-54). */
+int mb_tensor_copy_to_device(mb_ctx *ctx, const mb_tensor *t, void *dst_dev);
+int mb_tensor_copy_from_device(mb_ctx *ctx, mb_tensor *t, const void *src_dev);
 mb_dtype mb_tensor_dtype(const mb_tensor *t);
 int mb_tensor_rank(const mb_tensor *t);
 const int64_t *mb_tensor_shape(const mb_tensor *t);

@@ -69,6 +69,7 @@ ABI = {
     "mb_host_alloc_pinned": [_P, ctypes.c_size_t, _PP], "mb_host_free_pinned": [_P, _P],
     "mb_tensor_from_host": [_P, _I, _I, _I64P, _P, _PP], "mb_tensor_alloc": [_P, _I, _I, _I64P, _PP],
     "mb_tensor_to_host": [_P, _P, _P, ctypes.c_size_t], "mb_tensor_free": [_P, _P],
+    "mb_tensor_copy_to_device": [_P, _P, _P], "mb_tensor_copy_from_device": [_P, _P, _P],
     "mb_tensor_dtype": [_P], "mb_tensor_rank": [_P], "mb_tensor_shape": [_P], "mb_tensor_numel": [_P],
     "mb_tensor_nbytes": [_P], "mb_tensor_device_ptr": [_P], "mb_reshape": [_P, _P, _I, _I64P, _PP],
     "mb_prf_key_gen": [_P, _P], "mb_sync_key_random": [_P, _P], "mb_derive_seed": [_P, _U8P, _U8P, _P],

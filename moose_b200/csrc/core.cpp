@@ -290,6 +290,18 @@ extern "C" int mb_tensor_free(mb_ctx *ctx, mb_tensor *t) {
   return MB_OK;
 }
 
+extern "C" int mb_tensor_copy_to_device(mb_ctx *ctx, const mb_tensor *t, void *dst) {
+  if (!ctx || !t || (!dst && t->nbytes)) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_tensor_copy_to_device: NULL");
+  MB_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (t->nbytes) MB_CUDA(ctx, cudaMemcpyAsync(dst, t->dptr, t->nbytes, cudaMemcpyDeviceToDevice, ctx->stream));
+  return MB_OK;
+}
+extern "C" int mb_tensor_copy_from_device(mb_ctx *ctx, mb_tensor *t, const void *src) {
+  if (!ctx || !t || (!src && t->nbytes)) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_tensor_copy_from_device: NULL");
+  MB_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (t->nbytes) MB_CUDA(ctx, cudaMemcpyAsync(t->dptr, src, t->nbytes, cudaMemcpyDeviceToDevice, ctx->stream));
+  return MB_OK;
+}
 extern "C" mb_dtype mb_tensor_dtype(const mb_tensor *t) { return t->dtype; }
 extern "C" int mb_tensor_rank(const mb_tensor *t) { return t->rank; }
 extern "C" const int64_t *mb_tensor_shape(const mb_tensor *t) { return t->shape; }

@@ -1,0 +1,66 @@
+"""GPU replay of the reference's own lowered computations through the per-op C ABI (moose_b200/executor.py):
+tutorials/dotprod-compiled.moose (BASELINE configs[0]), its networked variant and the 19 045-op
+moose/benches/rep_computation.moose.  Every operation's result is compared bit for bit with the oracle replay
+run under the same session id and entropy key."""
+import gzip
+import os
+
+import numpy as np
+import pytest
+
+import moose_b200 as mb
+from moose_b200 import textual as tx
+from moose_b200.executor import Executor, toposort
+from oracle import moose_oracle as mo
+from oracle import replay_oracle as ro
+from _util import ENTROPY_KEY
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def load(name):
+    return tx.loads_json(gzip.open(os.path.join(GOLDEN, name + ".json.gz")).read().decode())
+
+
+def same_value(g, o):
+    if isinstance(g, mb.Tensor):
+        if isinstance(o, mo.Ring):
+            return g.shape == o.shape and np.array_equal(g.to_host(), o.data)
+        if isinstance(o, mo.Bits):
+            return g.shape == o.shape and np.array_equal(g.to_host(), o.packed)
+        return np.array_equal(g.to_host(), np.asarray(o, dtype=np.float64))
+    return g == o
+
+
+@pytest.mark.parametrize("name,tag,expected", [("dotprod_compiled", "output_0", 32.0), ("dotprod_networked", "output_0", 32.0)])
+def test_replay_dotprod(name, tag, expected):
+    ops = load(name)
+    sess = mb.Session(0, "replay", ENTROPY_KEY)
+    try:
+        ex = Executor(sess)
+        outs = ex.run(ops)
+        assert ex.executed == len(ops)
+        got = outs[tag].to_host()
+        assert got.shape == (1, 1) and abs(got[0, 0] - expected) < 1e-9
+        ovals, _ = ro.replay(toposort(ops), mo.Session("replay", ENTROPY_KEY), tx.parse_constant, tx.attr_hex16)
+        for op in ops:
+            assert same_value(ex.values[op.name], ovals[op.name]), op.name
+    finally:
+        sess.close()
+
+
+def test_replay_rep_computation_19045_ops():
+    ops = load("rep_computation")
+    sess = mb.Session(0, "replay", ENTROPY_KEY)
+    try:
+        ex = Executor(sess)
+        ex.run(ops)
+        out = ex.saved["y_uri"].to_host()
+        assert abs(out[0] - np.exp(2.0)) < 1e-5
+        ovals, oouts = ro.replay(toposort(ops), mo.Session("replay", ENTROPY_KEY), tx.parse_constant, tx.attr_hex16)
+        assert np.array_equal(out, oouts["saved:y_uri"])
+        mismatches = [op.name for op in ops if op.kind not in ("Save", "Output") and not same_value(ex.values[op.name], ovals[op.name])]
+        assert not mismatches, mismatches[:5]
+    finally:
+        sess.close()

@@ -1,0 +1,89 @@
+"""CPU tests of the host-dialect textual reader, the replay order and the oracle-side replay
+(moose/src/textual/parsing.rs grammar; lowered exemplar tutorials/dotprod-compiled.moose)."""
+import glob
+import gzip
+import os
+
+import numpy as np
+import pytest
+
+from moose_b200 import textual as tx
+from moose_b200.executor import toposort
+from oracle import moose_oracle as mo
+from oracle import replay_oracle as ro
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def load(name):
+    return tx.loads_json(gzip.open(os.path.join(GOLDEN, name + ".json.gz")).read().decode())
+
+
+def test_parse_host_dialect_lines():
+    text = '''
+    k = PrfKeyGen: () -> HostPrfKey () @Host(carole)
+    s = DeriveSeed{sync_key = 0102030405060708090a0b0c0d0e0f10}: (HostPrfKey) -> HostSeed (k) @Host(carole)
+    c = Constant{value = HostFloat64Tensor([[1.5, -2.0], [0.25, 4.0]])}: () -> HostFloat64Tensor () @Host(alice)
+    e = RingFixedpointEncode{scaling_base = 2, scaling_exp = 23}: (HostFloat64Tensor) -> HostRing64Tensor (c) @Host(alice)
+    n = AddN: [HostRing64Tensor] -> HostRing64Tensor (e, e, e) @Host(alice)
+    snd = Send{rendezvous_key = 07000000000000000000000000000000, receiver = "bob"}: (HostRing64Tensor) -> HostUnit (n) @Host(alice)
+    rcv = Receive{rendezvous_key = 07000000000000000000000000000000, sender = "alice"}: () -> HostRing64Tensor () @Host(bob)
+    o = Output{tag = "out, with (brackets)"}: (HostRing64Tensor) -> HostRing64Tensor (rcv) @Host(bob)
+    '''
+    ops = tx.parse_computation(text)
+    assert [o.kind for o in ops] == ["PrfKeyGen", "DeriveSeed", "Constant", "RingFixedpointEncode", "AddN", "Send",
+                                     "Receive", "Output"]
+    assert ops[1].inputs == ["k"] and tx.attr_hex16(ops[1], "sync_key") == bytes(range(1, 17))
+    assert tx.parse_constant(ops[2].attrs["value"]) == ("HostFloat64Tensor", [[1.5, -2.0], [0.25, 4.0]])
+    assert ops[4].variadic and ops[4].inputs == ["e", "e", "e"] and ops[4].input_types == ["HostRing64Tensor"]
+    assert tx.attr_str(ops[5], "receiver") == "bob" and ops[6].owners == ["bob"]
+    assert tx.attr_str(ops[7], "tag") == "out, with (brackets)"
+    assert tx.loads_json(tx.dumps_json(ops)) == ops
+
+
+def test_parse_logical_dialect_types_and_placements():
+    op = tx.parse_line('dot_0 = Dot: (Tensor<Fixed128(24, 40)>, Tensor<Fixed128(24, 40)>) -> Tensor<Fixed128(24, 40)> '
+                       '(cast_0, cast_1) @Replicated(player0, player1, player2)')
+    assert op.input_types == ["Tensor<Fixed128(24, 40)>"] * 2 and op.output_type == "Tensor<Fixed128(24, 40)>"
+    assert op.placement_kind == "Replicated" and op.owners == ["player0", "player1", "player2"]
+    with pytest.raises(tx.ParseError):
+        tx.parse_line("x = Add: (A, B) -> C (a, b)")  # no placement
+
+
+def test_sync_key_byte_list_form():
+    """execution/mod.rs:176: `DeriveSeed {sync_key = [1, 2, 3]}`."""
+    op = tx.parse_line("seed = DeriveSeed {sync_key = [1, 2, 3]}: (HostPrfKey) -> HostSeed (key) @Host(alice)")
+    assert tx.attr_hex16(op, "sync_key") == bytes([1, 2, 3]) + bytes(13)
+
+
+def test_toposort_keeps_receive_after_send():
+    ops = load("dotprod_networked")
+    order = toposort(ops)
+    idx = {op.name: i for i, op in enumerate(order)}
+    for op in order:
+        for i in op.inputs:
+            assert idx[i] < idx[op.name]
+    sends = {op.attrs["rendezvous_key"]: idx[op.name] for op in order if op.kind == "Send"}
+    for op in order:
+        if op.kind == "Receive":
+            assert idx[op.name] == sends[op.attrs["rendezvous_key"]] + 1
+
+
+@pytest.mark.parametrize("name,tag,expected", [("dotprod_compiled", "output_0", 32.0), ("dotprod_networked", "output_0", 32.0),
+                                               ("rep_computation", "saved:y_uri", np.exp(2.0))])
+def test_oracle_replays_reference_lowered_graphs(name, tag, expected):
+    """The reference's own compiled graphs -- tutorials/dotprod-compiled.moose (x.w = 32.0, BASELINE configs[0]) and
+    the 19 045-op moose/benches/rep_computation.moose (exp(2.0) on Fixed128(8,27)) -- run on the oracle's host
+    kernels: an end-to-end pin of the kernels' semantics against the reference's op sequences."""
+    order = toposort(load(name))
+    _, outs = ro.replay(order, mo.Session("replay", bytes(range(16))), tx.parse_constant, tx.attr_hex16)
+    assert abs(float(np.asarray(outs[tag]).reshape(-1)[0]) - expected) < 1e-5
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference"), reason="reference tree only exists in the build container")
+def test_reader_on_every_reference_moose_file_and_fixtures_are_current():
+    files = glob.glob("/root/reference/**/*.moose", recursive=True)
+    assert len(files) >= 6
+    for f in files:
+        assert len(tx.parse_computation(open(f).read())) > 0
+    assert load("dotprod_compiled") == tx.parse_computation(open("/root/reference/tutorials/dotprod-compiled.moose").read())
