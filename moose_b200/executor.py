@@ -73,10 +73,12 @@ class NcclComm:
 
     K_TENSOR, K_BYTES, K_SHAPE, K_UNIT, K_STRING = 0, 1, 2, 3, 4
 
-    def __init__(self, dist, sess: Session, role_to_rank: Dict[str, int], device: int):
+    def __init__(self, dist, sess: Optional[Session], role_to_rank: Dict[str, int], device):
+        """`device`: CUDA ordinal for NCCL; "cpu" for the gloo tests of the wire format (keys, seeds, shapes,
+        units -- tensors need a GPU session)."""
         import torch
         self.torch, self.dist, self.sess, self.role_to_rank = torch, dist, sess, role_to_rank
-        self.dev = torch.device("cuda", device)
+        self.dev = torch.device("cpu") if device == "cpu" else torch.device("cuda", device)
         self.bytes_sent = 0
 
     def _hdr(self, vals):
@@ -117,7 +119,8 @@ class NcclComm:
             if nbytes:
                 buf = t.empty(nbytes, dtype=t.uint8, device=self.dev)
                 self.dist.recv(buf, src)
-                t.cuda.synchronize(self.dev)
+                if self.dev.type == "cuda":
+                    t.cuda.synchronize(self.dev)
                 self.sess._check(lib().mb_tensor_copy_from_device(self.sess.ctx, out.h, buf.data_ptr()))
                 self.sess.sync()
             return out
@@ -131,8 +134,12 @@ class NcclComm:
 
 
 class Executor:
-    def __init__(self, sess: Session, role: Optional[str] = None, comm: Optional[NcclComm] = None):
+    def __init__(self, sess: Session, role: Optional[str] = None, comm: Optional[NcclComm] = None,
+                 overrides: Optional[Dict[str, object]] = None):
+        """`overrides` replaces the result of named ops (e.g. the Constant inputs of a compiled graph by larger
+        tensors of the same rank: lowered graphs are shape-agnostic)."""
         self.sess, self.role, self.comm = sess, role, comm
+        self.overrides = overrides or {}
         self.values: Dict[str, object] = {}
         self.outputs: Dict[str, object] = {}
         self.saved: Dict[str, object] = {}
@@ -267,7 +274,9 @@ class Executor:
                 continue
             if not mine:
                 continue
-            if op.kind == "Input":
+            if op.name in self.overrides:
+                self.values[op.name] = self.overrides[op.name]
+            elif op.kind == "Input":
                 self.values[op.name] = arguments[attr_str(op, "arg_name")]
             else:
                 self.values[op.name] = self._execute(op, [self.values[i] for i in op.inputs])

@@ -1,0 +1,106 @@
+"""Party-per-GPU execution of a networked lowered computation (BASELINE config 5 mode): one process per
+party, each on its own GPU, every Send/Receive pair of the graph (inserted by the reference's networking
+pass, moose/src/compilation/networking.rs:75-118) carried by NCCL send/recv between the GPUs.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 3 --master-addr 127.0.0.1 --master-port P \
+        -m moose_b200.party --graph tests/golden/dotprod_networked.json.gz [--repeat R]
+
+Roles are mapped to ranks in order of first appearance in the graph.  Every party keeps its own session
+(same session id, its own entropy), exactly like three comet workers of the reference.
+"""
+import argparse
+import gzip
+import json
+import os
+import time
+
+import numpy as np
+
+
+def roles_of(ops):
+    roles = []
+    for op in ops:
+        for o in op.owners:
+            if o not in roles:
+                roles.append(o)
+    return roles
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--graph", required=True, help=".moose text or the .json(.gz) re-encoding of tests/golden")
+    ap.add_argument("--session-id", default="b200-party")
+    ap.add_argument("--repeat", type=int, default=1)
+    ap.add_argument("--scale", type=int, nargs=3, metavar=("M", "K", "N"), default=None,
+                    help="replace the two HostFloat64Tensor constants of the graph by U(-1,1) matrices [M,K] and [K,N]")
+    args = ap.parse_args()
+
+    import torch
+    import torch.distributed as dist
+    import moose_b200 as mb
+    from moose_b200 import textual as tx
+    from moose_b200.executor import Executor, NcclComm
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    raw = gzip.open(args.graph).read().decode() if args.graph.endswith(".gz") else open(args.graph).read()
+    ops = tx.loads_json(raw) if args.graph.endswith((".json", ".json.gz")) else tx.parse_computation(raw)
+    roles = roles_of(ops)
+    if world != len(roles):
+        raise SystemExit(f"graph has {len(roles)} parties {roles}, launched with {world} ranks")
+    torch.cuda.set_device(local_rank)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    role = roles[rank]
+    sess = mb.Session(local_rank, args.session_id, None)  # OS entropy, like PrfKeyGen in the reference
+    comm = NcclComm(dist, sess, {r: i for i, r in enumerate(roles)}, local_rank)
+    # the two float constants, left operand first: decided by the constant's own shape ([1,3] . [3,1] in the exemplar)
+    consts = [op for op in ops if op.kind == "Constant" and "Float64Tensor" in op.attrs.get("value", "")]
+    consts.sort(key=lambda op: np.array(tx.parse_constant(op.attrs["value"])[1]).shape[0])
+    overrides = {}
+    if args.scale:
+        M, K, N = args.scale
+        shapes = [(M, K), (K, N)]
+        for i, op in enumerate(consts[:2]):
+            if op.owners[0] == role:
+                overrides[op.name] = sess.from_host(mb.FLOAT64, np.random.default_rng(100 + i).uniform(-1, 1, shapes[i]))
+    dist.barrier()
+    # one untimed run (NCCL connection setup, scratch growth), then the timed ones
+    Executor(sess, role=role, comm=comm, overrides=overrides).run(ops)
+    sess.sync()
+    comm.bytes_sent = 0
+    dist.barrier()
+    outputs, t0 = {}, time.perf_counter()
+    for _ in range(args.repeat):
+        ex = Executor(sess, role=role, comm=comm, overrides=overrides)
+        outputs = ex.run(ops)
+        sess.sync()
+    dt = (time.perf_counter() - t0) / args.repeat
+    dist.barrier()
+    sent = torch.tensor([comm.bytes_sent], dtype=torch.int64, device=f"cuda:{local_rank}")
+    dist.all_reduce(sent)
+    result = {}
+    for k, v in outputs.items():
+        if isinstance(v, mb.Tensor):
+            h = v.to_host()
+            if args.scale:  # check the first rows against a float matmul of the regenerated inputs
+                M, K, N = args.scale
+                a = np.random.default_rng(100).uniform(-1, 1, (M, K))[:4]
+                b = np.random.default_rng(101).uniform(-1, 1, (K, N))
+                result[k] = {"shape": list(h.shape), "max_abs_err_first_rows": float(np.abs(h[:4] - a @ b).max())}
+            else:
+                result[k] = h.tolist()
+        else:
+            result[k] = v
+    gathered = [None] * world
+    dist.all_gather_object(gathered, {"role": role, "executed": ex.executed, "outputs": result})
+    if rank == 0:
+        print(json.dumps({"mode": "party-per-gpu", "parties": roles, "transport": "nccl send/recv",
+                          "ops": len(ops), "seconds_per_run": dt, "payload_bytes_per_run": int(sent[0]) // args.repeat,
+                          "per_party": gathered}), flush=True)
+    sess.close()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -50,3 +50,41 @@ def test_single_rank_helpers_are_identity():
     assert bench.dist_setup(1, 0) is None
     assert bench.reduce_max(None, [1.5, 2.5]) == [1.5, 2.5]
     assert bench.reduce_sum_int(None, 7) == 7
+
+
+def _party_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update({"MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port), "RANK": str(rank), "WORLD_SIZE": str(world)})
+    import torch.distributed as dist
+    from moose_b200.executor import NcclComm
+    dist.init_process_group("gloo")
+    comm = NcclComm(dist, None, {"alice": 0, "bob": 1}, "cpu")
+    seed, shape = bytes(range(16)), (65536, 512)
+    if rank == 0:
+        comm.send(seed, "bob")
+        comm.send(shape, "bob")
+        comm.send(None, "bob")
+        got = comm.recv("bob")
+    else:
+        got = (comm.recv("alice"), comm.recv("alice"), comm.recv("alice"))
+        comm.send(bytes(reversed(seed)), "alice")
+    q.put((rank, got))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_party_wire_format_over_gloo():
+    """Send/Receive of the non-tensor value kinds of a lowered graph (HostSeed / HostPrfKey, HostShape, HostUnit)
+    between two parties: header + payload framing of moose_b200.executor.NcclComm."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29811 + os.getpid() % 100
+    procs = [ctx.Process(target=_party_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = dict(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert res[1] == (bytes(range(16)), (65536, 512), None)
+    assert res[0] == bytes(reversed(range(16)))
