@@ -440,7 +440,11 @@ def main():
                     "h2d_bytes_per_step": int(hA.nbytes + hB.nbytes), "d2h_bytes_per_step": int(hOut.nbytes)},
             "gpu_launches": int(launches),
             "roofline": {"kernel": "limb_gemm_kernel", "bound": "tensor", "achieved": achieved, "peak": peak,
-                         "unit": "TOP/s (int8)", "frac": (achieved / peak) if achieved else None, "traffic": None,
+                         "unit": "TOP/s (int8)", "frac": (achieved / peak) if achieved else None,
+                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full capture of this
+                         # command (profiles/r1_limb_gemm_2cta_roundbarrier_ncu_full_raw.csv); algorithmic operand +
+                         # partial bytes of the launch are 2.4 GB + 4.0 GB
+                         "traffic": 43.45e9 if (M, K, N) == (4096, 4096, 4096) else None,
                          "avg_launch_ms": avg_ms, "launches_timed": gemm_launches,
                          "share_of_step": gemm_ms / ms if ms else None,
                          "peak_source": f"2 x bf16_tflops_sustained of {peak_src} MEASURED_PEAKS.json "

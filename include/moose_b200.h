@@ -197,6 +197,18 @@ int mb_fixedpoint_encode(mb_ctx *ctx, mb_dtype ring, uint32_t fractional_precisi
 int mb_fixedpoint_decode(mb_ctx *ctx, uint32_t fractional_precision, const mb_tensor *x,
                          mb_tensor **out_f64);
 
+/* Plaintext-side helpers on ring tensors (host-placed tails of a computation):
+ * LessOp / GreaterOp::host_ring64/128_kernel (moose/src/host/ops.rs:2051-2087,2125-2161): bit = (x - y) as signed
+ * < 0 / > 0; MuxOp::host_ring_kernel (:2227-2252): s * (x - y) + y with a bit selector; SignOp (:2482-2506): -1 / 1;
+ * CastOp::ring_reduction_kernel (:2277-2288): Ring128 -> Ring64 = low 64 bits; MaximumOp::host_ring_kernel
+ * (:1432-1452): element-wise maximum under the UNSIGNED order of Wrapping<T>. */
+int mb_less(mb_ctx *ctx, const mb_tensor *x, const mb_tensor *y, mb_tensor **out_bits);
+int mb_greater(mb_ctx *ctx, const mb_tensor *x, const mb_tensor *y, mb_tensor **out_bits);
+int mb_mux(mb_ctx *ctx, const mb_tensor *s_bits, const mb_tensor *x, const mb_tensor *y, mb_tensor **out);
+int mb_sign(mb_ctx *ctx, const mb_tensor *x, mb_tensor **out);
+int mb_cast_ring128_to_ring64(mb_ctx *ctx, const mb_tensor *x, mb_tensor **out);
+int mb_maximum(mb_ctx *ctx, const mb_tensor *const *xs, int n, mb_tensor **out);
+
 /* ------------------------------------------------ host kernels: bit tensors */
 
 /* XorOp/AndOp/OrOp::host_kernel (moose/src/host/ops.rs:1507-1553). */

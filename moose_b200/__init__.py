@@ -80,6 +80,8 @@ ABI = {
     "mb_dot": [_P, _P, _P, _PP], "mb_dot_noalloc": [_P, _I, _P, _P, _P, _I64, _I64, _I64], "mb_add_n": [_P, _PP, _I, _PP], "mb_sum": [_P, _P, _I, _PP],
     "mb_broadcast": [_P, _P, _I, _I64P, _PP],
     "mb_fixedpoint_encode": [_P, _I, _U32, _P, _PP], "mb_fixedpoint_decode": [_P, _U32, _P, _PP],
+    "mb_less": [_P, _P, _P, _PP], "mb_greater": [_P, _P, _P, _PP], "mb_mux": [_P, _P, _P, _P, _PP],
+    "mb_sign": [_P, _P, _PP], "mb_cast_ring128_to_ring64": [_P, _P, _PP], "mb_maximum": [_P, _PP, _I, _PP],
     "mb_xor": [_P, _P, _P, _PP], "mb_and": [_P, _P, _P, _PP], "mb_or": [_P, _P, _P, _PP],
     "mb_bit_decompose": [_P, _P, _PP], "mb_bit_extract": [_P, _U64, _P, _PP],
     "mb_ring_inject": [_P, _I, _U64, _P, _PP], "mb_shl_dim": [_P, _U64, _U64, _P, _PP],
@@ -414,6 +416,26 @@ class Session:
         arr, rank = _shape_arr(shape)
         out = self._out()
         return self._t(lib().mb_tensor_alloc(self.ctx, dtype, rank, arr, ctypes.byref(out)), out)
+
+    def less(self, x, y): return self._bin(lib().mb_less, x, y)
+    def greater(self, x, y): return self._bin(lib().mb_greater, x, y)
+
+    def host_mux(self, s: Tensor, x: Tensor, y: Tensor) -> Tensor:
+        out = self._out()
+        return self._t(lib().mb_mux(self.ctx, s.h, x.h, y.h, ctypes.byref(out)), out)
+
+    def sign(self, x: Tensor) -> Tensor:
+        out = self._out()
+        return self._t(lib().mb_sign(self.ctx, x.h, ctypes.byref(out)), out)
+
+    def cast_ring128_to_ring64(self, x: Tensor) -> Tensor:
+        out = self._out()
+        return self._t(lib().mb_cast_ring128_to_ring64(self.ctx, x.h, ctypes.byref(out)), out)
+
+    def host_maximum(self, xs: Sequence[Tensor]) -> Tensor:
+        arr = (ctypes.c_void_p * max(len(xs), 1))(*[x.h for x in xs])
+        out = self._out()
+        return self._t(lib().mb_maximum(self.ctx, arr, len(xs), ctypes.byref(out)), out)
 
     def neg(self, x: Tensor) -> Tensor:
         out = self._out()

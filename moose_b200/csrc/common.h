@@ -53,6 +53,7 @@ struct mb_ctx {
   bool have_setup;
   uint8_t setup_keys[3][16]; // k0,k1,k2 (k10=k11 etc., replicated/setup.rs:39-58)
   int gemm_mode;
+  bool gemm_round_barrier;    // 2-CTA limb GEMM: keep clusters in step per scheduling round (L2 sharing)
   bool fused_bits;            // fused adder / ring_inject kernels (false = op-by-op composition, for A/B tests)
   int gemm_pair_mode;         // 0 = CTA pairs when possible, 1 = single-CTA tiles only (A/B comparison)
   std::atomic<uint64_t> launches;

@@ -1,6 +1,8 @@
 // Context, tensor handles, error reporting.
 #include "common.h"
 
+#include <cstdlib>
+
 static thread_local std::string g_last_error;
 
 void mb_set_error(const mb_ctx *, const std::string &msg) { g_last_error = msg; }
@@ -28,6 +30,7 @@ extern "C" int mb_ctx_create(int device, mb_ctx **out) {
   ctx->gemm_mode = 0;
   ctx->gemm_pair_mode = 0;
   ctx->fused_bits = true;
+  ctx->gemm_round_barrier = getenv("MOOSE_B200_NO_ROUND_BARRIER") == nullptr;
   ctx->launches = 0;
   ctx->profile = false;
   memset(ctx->scratch, 0, sizeof(ctx->scratch));

@@ -74,6 +74,7 @@ struct GemmParams {
   int tiles_m, tiles_n;
   int total_items;  // num_passes * nbatch * tiles_m * tiles_n
   unsigned long long *partials;  // [nbatch][num_passes][M][N] u64
+  int *round_barrier;  // 2-CTA kernel: one zeroed counter per scheduling round (nullptr = free running)
 };
 
 // Work item j of CTA c in snake order over the flat list [pass rank][batch][tile].
@@ -523,6 +524,23 @@ limb_gemm_kernel_2cta(const __grid_constant__ CUtensorMap map_a, const __grid_co
       int a_it = 0, b_it = 0;
       WorkItem w;
       for (int item = 0; next_item_2cta(p, item, w); item++) {
+        if (p.round_barrier) {
+          // Round barrier: no cluster starts loading work item `item` before every cluster has reached it.
+          // Clusters working on tiles that share operand planes then stay within a few MMA steps of each other,
+          // so a tile fetched by one is still in L2 when its neighbours ask for it (free-running clusters drift
+          // apart by more than the L2 holds and re-read the planes from HBM ~50x).  All CTAs of this persistent
+          // grid are co-resident (one per SM), so the spin cannot deadlock; only the TMA threads wait.
+          const int G = (int)(gridDim.x >> 1);
+          const long long left = (long long)p.total_items - (long long)item * G;
+          const int expect = (int)(left < G ? left : G);
+          volatile int *bar = p.round_barrier + item;
+          if (leader) atomicAdd((int *)bar, 1);
+          uint32_t spins = 0;
+          while (*bar < expect) {
+            __nanosleep(64);
+            if (++spins > (1u << 26)) __trap();
+          }
+        }
         const PassDesc pd = p.passes[w.pass];
         const int d = pd.d;
         const int last = 2 * d + 2;
@@ -902,6 +920,15 @@ int k_gemm_limb_batched(mb_ctx *ctx, mb_dtype dtype, const LimbOperandA *As, int
   gp.total_items = (int)total;
   gp.partials = (unsigned long long *)dP;
 
+  gp.round_barrier = nullptr;
+  if (pair && ctx->gemm_round_barrier) {
+    const int clusters = (int)std::min<int64_t>(total, ctx->sm_count / 2);
+    const int64_t rounds = (total + clusters - 1) / clusters;
+    void *dR;
+    MB_CHECK(mb_scratch(ctx, 3, (size_t)rounds * sizeof(int), &dR));
+    MB_CUDA(ctx, cudaMemsetAsync(dR, 0, (size_t)rounds * sizeof(int), ctx->stream));
+    gp.round_barrier = (int *)dR;
+  }
   cudaEvent_t prof_start;
   MB_CHECK(mb_prof_begin(ctx, &prof_start));
   if (pair) {

@@ -1223,3 +1223,43 @@ def rep_sigmoid(sess, i_prec: int, f_prec: int, x: RepTensor) -> RepTensor:
     lower = rep_greater(sess, rep_neg(max_val_rep), x)
     lower_ring = rep_ring_inject(sess, bits, 0, lower)
     return rep_mux(sess, lower_ring, zeros_rep, upper_wall)
+
+
+# -- plaintext-side helpers ---------------------------------------------------
+
+def _signed_ints(x: Ring):
+    m = 1 << x.bits
+    return [v - m if v >> (x.bits - 1) else v for v in (int(t) for t in x.to_ints().reshape(-1))]
+
+
+def host_less(x: Ring, y: Ring) -> Bits:
+    """LessOp::host_ring64/128_kernel (host/ops.rs:2051-2087): (x - y) as signed < 0."""
+    d = sub(x, y)
+    return Bits.from_array(np.array([int(v < 0) for v in _signed_ints(d)], dtype=np.uint8).reshape(d.shape))
+
+
+def host_greater(x: Ring, y: Ring) -> Bits:
+    """GreaterOp::host_ring64/128_kernel (host/ops.rs:2125-2161): (x - y) as signed > 0."""
+    d = sub(x, y)
+    return Bits.from_array(np.array([int(v > 0) for v in _signed_ints(d)], dtype=np.uint8).reshape(d.shape))
+
+
+def host_mux(s: Bits, x: Ring, y: Ring) -> Ring:
+    """MuxOp::host_ring_kernel (host/ops.rs:2227-2252): s * (x - y) + y."""
+    return add(mul(ring_inject(x.bits, 0, s), sub(x, y)), y)
+
+
+def host_sign(x: Ring) -> Ring:
+    """SignOp::ring64/128_kernel (host/ops.rs:2482-2506)."""
+    return Ring.from_ints(x.bits, [-1 if v < 0 else 1 for v in _signed_ints(x)], x.shape)
+
+
+def cast_ring128_to_ring64(x: Ring) -> Ring:
+    """CastOp::ring_reduction_kernel (host/ops.rs:2277-2288)."""
+    return Ring(64, x.data[..., 0].copy())
+
+
+def host_maximum(xs) -> Ring:
+    """MaximumOp::host_ring_kernel (host/ops.rs:1432-1452): unsigned order of Wrapping<T>."""
+    vals = [t.to_ints().reshape(-1) for t in xs]
+    return Ring.from_ints(xs[0].bits, [max(int(v[i]) for v in vals) for i in range(xs[0].size)], xs[0].shape)

@@ -296,3 +296,31 @@ def test_dot_tensor_pipe_extreme_values(sess):
         finally:
             sess.set_gemm_mode(0)
         assert same_ring(z, mo.dot(mo.Ring(bits, a), mo.Ring(bits, b)))
+
+
+@pytest.mark.parametrize("bits", [64, 128])
+def test_plaintext_helpers_parity(sess, bits):
+    """host/ops.rs:2051-2087,2125-2161 (less/greater), :2227-2252 (mux), :2482-2506 (sign), :2277-2288 (cast),
+    :1432-1452 (maximum, unsigned order)."""
+    rng = np.random.default_rng(bits + 5)
+    shape = (7, 19)
+    a, b, c = (rand_ring(rng, bits, shape) for _ in range(3))
+    small = (rng.integers(-5, 5, shape).astype(np.int64)).astype(np.uint64)
+    if bits == 128:
+        small = np.stack([small, np.where(small.astype(np.int64) < 0, np.uint64(0xFFFFFFFFFFFFFFFF), np.uint64(0))], axis=-1)
+    A, B, C, S = (sess.from_host(DT[bits], t) for t in (a, b, c, small))
+    oa, ob, oc, osm = (mo.Ring(bits, t) for t in (a, b, c, small))
+    for (X, Y, ox, oy) in ((A, B, oa, ob), (S, sess.fill(DT[bits], 0, shape), osm, mo.fill(bits, 0, shape)), (A, A, oa, oa)):
+        assert same_bits(sess.less(X, Y), mo.host_less(ox, oy))
+        assert same_bits(sess.greater(X, Y), mo.host_greater(ox, oy))
+    sel, osel = sess.less(A, B), mo.host_less(oa, ob)
+    assert same_ring(sess.host_mux(sel, B, C), mo.host_mux(osel, ob, oc))
+    assert same_ring(sess.sign(S), mo.host_sign(osm)) and same_ring(sess.sign(A), mo.host_sign(oa))
+    assert same_ring(sess.host_maximum([A, B, C]), mo.host_maximum([oa, ob, oc]))
+    with pytest.raises(mb.MooseB200Error):
+        sess.host_maximum([])
+    if bits == 128:
+        assert same_ring(sess.cast_ring128_to_ring64(A), mo.cast_ring128_to_ring64(oa))
+    # broadcasting compare: [7,19] vs [19]
+    v = rand_ring(rng, bits, (19,))
+    assert same_bits(sess.less(A, sess.from_host(DT[bits], v)), mo.host_less(oa, mo.Ring(bits, v)))
