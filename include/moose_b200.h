@@ -228,6 +228,47 @@ int mb_shl_dim(mb_ctx *ctx, uint64_t amount, uint64_t bit_length, const mb_tenso
                mb_tensor **out);
 /* IndexAxisOp (moose/src/host/ops.rs:740-783, bitarray.rs:85-108), axis 0 only. */
 int mb_index_axis0(mb_ctx *ctx, int64_t index, const mb_tensor *x, mb_tensor **out);
+/* IndexAxisOp on any axis (moose/src/host/ops.rs:740-783). Rings: the selected sub-array. Bits: like
+ * BitArrayRepr::index_axis (bitarray.rs:85-108) the result is the run of CONSECUTIVE bits that starts at
+ * index * stride[axis], which equals the sub-array only for axis 0 / unit leading axes. */
+int mb_index_axis(mb_ctx *ctx, int axis, int64_t index, const mb_tensor *x, mb_tensor **out);
+/* ExpandDimsOp (moose/src/host/ops.rs:1135-1165; RawShape::extend_singletons, host/mod.rs:83-92):
+ * axes are positions in the resulting shape, any order. */
+int mb_expand_dims(mb_ctx *ctx, const int64_t *axes, int naxes, const mb_tensor *x, mb_tensor **out);
+/* SqueezeOp (moose/src/host/ops.rs:1167-1209; RawShape::squeeze, host/mod.rs:99-113): axis < 0 = None
+ * (drop every unit axis); a named axis of extent != 1 is MB_ERR_KERNEL (the reference panics). */
+int mb_squeeze(mb_ctx *ctx, int axis, const mb_tensor *x, mb_tensor **out);
+/* TransposeOp = reversed axes (moose/src/host/ops.rs:1270-1299); bit tensors up to rank 3
+ * (bitarray.rs:135-188). The result is materialised row-major. */
+int mb_transpose(mb_ctx *ctx, const mb_tensor *x, mb_tensor **out);
+/* ConcatOp (moose/src/host/ops.rs:1211-1268). Bit tensors: the flat bit streams are appended in order and
+ * only shape[axis] is summed, exactly like ConcatOp::bit_kernel (correct for axis 0). */
+int mb_concat(mb_ctx *ctx, int axis, const mb_tensor *const *xs, int n, mb_tensor **out);
+/* SliceOp::host_ring_kernel (moose/src/host/ops.rs:523-535, 686-704; SliceInfo -> ndarray Slice,
+ * host/mod.rs:153-165): per axis start, optional end (has_end[k] == 0: to the end), step (1 when the
+ * reference has None); negative start/end count from the back, a negative step walks the selected range
+ * backwards. Bit tensors: MB_ERR_KERNEL "slicing not implemented for BitArray yet" (bitarray.rs:130-133). */
+int mb_slice(mb_ctx *ctx, int n, const int64_t *start, const int64_t *end, const uint8_t *has_end,
+             const int64_t *step, const mb_tensor *x, mb_tensor **out);
+/* DiagOp::ring_kernel / bit_kernel (moose/src/host/ops.rs:549-582; bitarray.rs:110-128: bit diagonals of
+ * length 1 and 2 only, longer ones are MB_ERR_UNIMPLEMENTED where the reference hits todo!()). */
+int mb_diag(mb_ctx *ctx, const mb_tensor *x, mb_tensor **out);
+/* SelectOp::host_ring_kernel (moose/src/host/ops.rs:803-818, 662-684): keep the positions along `axis`
+ * whose index bit is set. Reads the index bits back to the host (the output extent depends on them). */
+int mb_select(mb_ctx *ctx, int axis, const mb_tensor *index_bits, const mb_tensor *x, mb_tensor **out);
+/* DivOp::ring_kernel (moose/src/host/ops.rs:332-343): elementwise unsigned integer quotient. A zero
+ * divisor is MB_ERR_KERNEL (the reference panics); the call synchronises the stream to find out. */
+int mb_div(mb_ctx *ctx, const mb_tensor *x, const mb_tensor *y, mb_tensor **out);
+/* BitDecomposeOp::host_ring64/128_kernel (moose/src/host/ops.rs:856-894): [k, shape...] ring tensor,
+ * plane i = (x >> i) & 1. */
+int mb_bit_decompose_ring(mb_ctx *ctx, const mb_tensor *x, mb_tensor **out);
+/* RingFixedpointMeanOp::ring64/128_kernel (moose/src/host/fixedpoint.rs:41-113): sum over `axis`
+ * (axis < 0 = all) times encode(1 / len, scaling_base^scaling_exp). */
+int mb_fixedpoint_mean(mb_ctx *ctx, int axis, uint64_t scaling_base, uint32_t scaling_exp,
+                       const mb_tensor *x, mb_tensor **out);
+/* RingFixedpointArgmaxOp::host_ring64/128_kernel (moose/src/host/ops.rs:2375-2437): index (Ring64) of the
+ * first maximum along `axis` under the signed interpretation. */
+int mb_fixedpoint_argmax(mb_ctx *ctx, int axis, const mb_tensor *x, mb_tensor **out);
 
 /* ----------------------------------------------------- replicated protocols */
 

@@ -85,7 +85,12 @@ ABI = {
     "mb_xor": [_P, _P, _P, _PP], "mb_and": [_P, _P, _P, _PP], "mb_or": [_P, _P, _P, _PP],
     "mb_bit_decompose": [_P, _P, _PP], "mb_bit_extract": [_P, _U64, _P, _PP],
     "mb_ring_inject": [_P, _I, _U64, _P, _PP], "mb_shl_dim": [_P, _U64, _U64, _P, _PP],
-    "mb_index_axis0": [_P, _I64, _P, _PP],
+    "mb_index_axis0": [_P, _I64, _P, _PP], "mb_index_axis": [_P, _I, _I64, _P, _PP],
+    "mb_expand_dims": [_P, _I64P, _I, _P, _PP], "mb_squeeze": [_P, _I, _P, _PP], "mb_transpose": [_P, _P, _PP],
+    "mb_concat": [_P, _I, _PP, _I, _PP], "mb_slice": [_P, _I, _I64P, _I64P, _U8P, _I64P, _P, _PP],
+    "mb_diag": [_P, _P, _PP], "mb_select": [_P, _I, _P, _P, _PP], "mb_div": [_P, _P, _P, _PP],
+    "mb_bit_decompose_ring": [_P, _P, _PP], "mb_fixedpoint_mean": [_P, _I, _U64, _U32, _P, _PP],
+    "mb_fixedpoint_argmax": [_P, _I, _P, _PP],
     "mb_rep_from_shares": [_P, _P, _P, _P, _PP], "mb_rep_share_tensor": [_P, _I], "mb_rep_free": [_P, _P],
     "mb_rep_setup": [_P], "mb_rep_share": [_P, _P, _I, _PP], "mb_rep_reveal": [_P, _P, _I, _PP],
     "mb_rep_add": [_P, _P, _P, _PP], "mb_rep_sub": [_P, _P, _P, _PP], "mb_rep_neg": [_P, _P, _PP],
@@ -495,6 +500,65 @@ class Session:
     def index_axis0(self, index: int, x: Tensor) -> Tensor:
         out = self._out()
         return self._t(lib().mb_index_axis0(self.ctx, index, x.h, ctypes.byref(out)), out)
+
+    def index_axis(self, axis: int, index: int, x: Tensor) -> Tensor:
+        out = self._out()
+        return self._t(lib().mb_index_axis(self.ctx, axis, index, x.h, ctypes.byref(out)), out)
+
+    def expand_dims(self, axis, x: Tensor) -> Tensor:
+        axes = [axis] if isinstance(axis, int) else list(axis)
+        arr = (ctypes.c_int64 * max(len(axes), 1))(*axes)
+        out = self._out()
+        return self._t(lib().mb_expand_dims(self.ctx, arr, len(axes), x.h, ctypes.byref(out)), out)
+
+    def squeeze(self, axis: Optional[int], x: Tensor) -> Tensor:
+        out = self._out()
+        return self._t(lib().mb_squeeze(self.ctx, -1 if axis is None else axis, x.h, ctypes.byref(out)), out)
+
+    def transpose(self, x: Tensor) -> Tensor:
+        out = self._out()
+        return self._t(lib().mb_transpose(self.ctx, x.h, ctypes.byref(out)), out)
+
+    def concat(self, axis: int, xs: Sequence[Tensor]) -> Tensor:
+        arr = (ctypes.c_void_p * max(len(xs), 1))(*[x.h for x in xs])
+        out = self._out()
+        return self._t(lib().mb_concat(self.ctx, axis, arr, len(xs), ctypes.byref(out)), out)
+
+    def slice(self, info, x: Tensor) -> Tensor:
+        """`info`: one (start, end | None, step | None) triple or python slice per axis (SliceInfo, host/mod.rs:153)."""
+        trip = [(e.start or 0, e.stop, e.step) if isinstance(e, slice) else tuple(e) for e in info]
+        n = len(trip)
+        start = (ctypes.c_int64 * max(n, 1))(*[t[0] for t in trip])
+        end = (ctypes.c_int64 * max(n, 1))(*[0 if t[1] is None else t[1] for t in trip])
+        has_end = bytes(0 if t[1] is None else 1 for t in trip) + b"\0"
+        step = (ctypes.c_int64 * max(n, 1))(*[1 if t[2] is None else t[2] for t in trip])
+        out = self._out()
+        return self._t(lib().mb_slice(self.ctx, n, start, end, has_end, step, x.h, ctypes.byref(out)), out)
+
+    def diag(self, x: Tensor) -> Tensor:
+        out = self._out()
+        return self._t(lib().mb_diag(self.ctx, x.h, ctypes.byref(out)), out)
+
+    def select(self, axis: int, index_bits: Tensor, x: Tensor) -> Tensor:
+        out = self._out()
+        return self._t(lib().mb_select(self.ctx, axis, index_bits.h, x.h, ctypes.byref(out)), out)
+
+    def div(self, x: Tensor, y: Tensor) -> Tensor:
+        out = self._out()
+        return self._t(lib().mb_div(self.ctx, x.h, y.h, ctypes.byref(out)), out)
+
+    def bit_decompose_ring(self, x: Tensor) -> Tensor:
+        out = self._out()
+        return self._t(lib().mb_bit_decompose_ring(self.ctx, x.h, ctypes.byref(out)), out)
+
+    def fixedpoint_mean(self, axis: Optional[int], scaling_base: int, scaling_exp: int, x: Tensor) -> Tensor:
+        out = self._out()
+        return self._t(lib().mb_fixedpoint_mean(self.ctx, -1 if axis is None else axis, scaling_base, scaling_exp,
+                                                x.h, ctypes.byref(out)), out)
+
+    def fixedpoint_argmax(self, axis: int, x: Tensor) -> Tensor:
+        out = self._out()
+        return self._t(lib().mb_fixedpoint_argmax(self.ctx, axis, x.h, ctypes.byref(out)), out)
 
     # -- ReplicatedPlacement kernels ---------------------------------------------
     def rep_setup(self):

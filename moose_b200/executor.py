@@ -21,7 +21,7 @@ from typing import Dict, List, Optional
 import numpy as np
 
 from . import BIT, FLOAT64, RING64, RING128, Session, Tensor, lib, _P
-from .textual import Operation, attr_hex16, attr_int, attr_str, parse_constant
+from .textual import Operation, attr_hex16, attr_int, attr_int_list, attr_slice, attr_str, parse_constant
 
 _RING_TYPES = {"HostRing64Tensor": RING64, "HostRing128Tensor": RING128, "Ring64Tensor": RING64, "Ring128Tensor": RING128}
 _BIT_TYPES = {"HostBitTensor", "BitTensor"}
@@ -224,7 +224,7 @@ class Executor:
         if k == "Or":
             return s.or_(x[0], x[1])
         if k == "BitDecompose":
-            return s.bit_decompose(x[0])
+            return s.bit_decompose(x[0]) if op.output_type in _BIT_TYPES else s.bit_decompose_ring(x[0])
         if k == "BitExtract":
             return s.bit_extract(attr_int(op, "bit_idx"), x[0])
         if k == "RingInject":
@@ -232,9 +232,43 @@ class Executor:
         if k == "ShlDim":
             return s.shl_dim(attr_int(op, "amount"), attr_int(op, "bit_length"), x[0])
         if k == "IndexAxis":
-            if attr_int(op, "axis") != 0:
-                raise ExecutionError("IndexAxis: only axis 0 is built")
-            return s.index_axis0(attr_int(op, "index"), x[0])
+            return s.index_axis(attr_int(op, "axis"), attr_int(op, "index"), x[0])
+        if k == "ExpandDims":
+            return s.expand_dims(attr_int_list(op, "axis"), x[0])
+        if k == "Squeeze":
+            return s.squeeze(attr_int(op, "axis") if "axis" in op.attrs else None, x[0])
+        if k == "Transpose":
+            return s.transpose(x[0])
+        if k == "Concat":
+            return s.concat(attr_int(op, "axis"), x)
+        if k == "Slice":
+            info = attr_slice(op, "slice")
+            if isinstance(x[0], tuple):  # SliceOp::shape_kernel (host/ops.rs:537-546)
+                return tuple(x[0][info[0][0]:info[0][1]])
+            return s.slice(info, x[0])
+        if k == "Diag":
+            return s.diag(x[0])
+        if k == "Select":
+            return s.select(attr_int(op, "axis"), x[1], x[0])
+        if k == "Div":
+            return s.div(x[0], x[1])
+        if k == "Less":
+            return s.less(x[0], x[1])
+        if k == "Greater":
+            return s.greater(x[0], x[1])
+        if k == "Mux":
+            return s.host_mux(x[0], x[1], x[2])
+        if k == "Sign":
+            return s.sign(x[0])
+        if k == "Cast":
+            return s.cast_ring128_to_ring64(x[0])
+        if k == "Maximum":
+            return s.host_maximum(x)
+        if k == "RingFixedpointMean":
+            axis = attr_int(op, "axis") if "axis" in op.attrs else None
+            return s.fixedpoint_mean(axis, attr_int(op, "scaling_base"), attr_int(op, "scaling_exp"), x[0])
+        if k == "RingFixedpointArgmax":
+            return s.fixedpoint_argmax(attr_int(op, "axis"), x[0])
         if k == "Reshape":
             return s.reshape(x[0], x[1])
         if k == "Broadcast":

@@ -189,6 +189,26 @@ def attr_int(op: Operation, key: str) -> int:
     return int(op.attrs[key])
 
 
+def attr_int_list(op: Operation, key: str) -> List[int]:
+    """`axis = [0, 2]` (ExpandDims, parsing.rs:327-331)."""
+    return [int(v) for v in ast.literal_eval(op.attrs[key])]
+
+
+def attr_slice(op: Operation, key: str) -> List[Tuple[int, Optional[int], Optional[int]]]:
+    """`slice = {start = 1, end = 10, step = -1}`: the textual form carries ONE SliceInfoElem
+    (slice_info_literal, parsing.rs:902-913), end and step optional."""
+    body = op.attrs[key].strip()
+    if not (body.startswith("{") and body.endswith("}")):
+        raise ParseError(f"bad slice literal {body!r} in {op.name}")
+    fields = {}
+    for part in _split_top(body[1:-1]):
+        k, v = part.split("=", 1)
+        fields[k.strip()] = int(v)
+    if "start" not in fields:
+        raise ParseError(f"slice literal without start in {op.name}")
+    return [(fields["start"], fields.get("end"), fields.get("step"))]
+
+
 def attr_str(op: Operation, key: str) -> str:
     v = op.attrs[key]
     return ast.literal_eval(v) if v.startswith('"') else v

@@ -1263,3 +1263,174 @@ def host_maximum(xs) -> Ring:
     """MaximumOp::host_ring_kernel (host/ops.rs:1432-1452): unsigned order of Wrapping<T>."""
     vals = [t.to_ints().reshape(-1) for t in xs]
     return Ring.from_ints(xs[0].bits, [max(int(v[i]) for v in vals) for i in range(xs[0].size)], xs[0].shape)
+
+
+# -- shape / indexing host kernels (SURVEY 8a row a19) ---------------------------------------------
+
+def _ring_view(x: Ring) -> np.ndarray:
+    """Structured view with one item per ring element, so numpy indexing acts on ring elements."""
+    if x.bits == 64:
+        return x.data
+    return x.data.view(np.dtype([("lo", np.uint64), ("hi", np.uint64)])).reshape(x.shape)
+
+
+def _ring_from_view(bits: int, v: np.ndarray) -> Ring:
+    shape = np.shape(v)
+    v = np.ascontiguousarray(v).reshape(shape)  # ascontiguousarray promotes 0-d to 1-d
+    if bits == 64:
+        return Ring(64, v)
+    return Ring(128, v.reshape(-1).view(np.uint64).reshape(shape + (2,)))
+
+
+def expand_dims_shape(shape, axes):
+    """RawShape::extend_singletons (host/mod.rs:83-92) after the descending sort of ExpandDimsOp
+    (host/ops.rs:1126-1131): pop() yields the axes in ascending order, each inserted into the shape so far."""
+    shape = list(shape)
+    for a in sorted(axes):
+        shape.insert(a, 1)
+    return tuple(shape)
+
+
+def squeeze_shape(shape, axis: Optional[int]):
+    """RawShape::squeeze (host/mod.rs:99-113)."""
+    shape = list(shape)
+    if axis is None:
+        return tuple(s for s in shape if s != 1)
+    removed = shape.pop(axis)
+    if removed != 1:
+        raise ValueError("Cannot select an axis to squeeze out which has size not equal to one")
+    return tuple(shape)
+
+
+def expand_dims(axes, x):
+    shape = expand_dims_shape(x.shape, axes)
+    return x.reshape(shape) if isinstance(x, Ring) else Bits(shape, x.packed)
+
+
+def squeeze(axis: Optional[int], x):
+    shape = squeeze_shape(x.shape, axis)
+    return x.reshape(shape) if isinstance(x, Ring) else Bits(shape, x.packed)
+
+
+def transpose(x):
+    """TransposeOp (host/ops.rs:1270-1299): reversed axes; bits up to rank 3 (bitarray.rs:135-188)."""
+    if isinstance(x, Bits):
+        if len(x.shape) > 3:
+            raise NotImplementedError("tranposing not implemented for 4D tensors or larger yet")
+        return Bits.from_array(np.ascontiguousarray(x.to_array().T))
+    return _ring_from_view(x.bits, _ring_view(x).T)
+
+
+def concat(axis: int, xs):
+    """ConcatOp::ring_kernel / bit_kernel (host/ops.rs:1228-1266).  The bit kernel appends the flat streams
+    whatever the axis and sums shape[axis]."""
+    if isinstance(xs[0], Bits):
+        flat = np.concatenate([t.to_array().reshape(-1) for t in xs])
+        shape = list(xs[0].shape)
+        shape[axis] = sum(t.shape[axis] for t in xs)
+        return Bits.from_array(flat.reshape(shape))
+    return _ring_from_view(xs[0].bits, np.concatenate([_ring_view(t) for t in xs], axis=axis))
+
+
+def index_axis(axis: int, index: int, x):
+    """IndexAxisOp (host/ops.rs:740-783).  Bits: BitArrayRepr::index_axis (bitarray.rs:85-108) copies
+    new_dim.size() consecutive bits from offset index * stride[axis]."""
+    if isinstance(x, Bits):
+        shape = list(x.shape)
+        stride = int(np.prod(shape[axis + 1:], dtype=np.int64))
+        new_shape = shape[:axis] + shape[axis + 1:]
+        size = int(np.prod(new_shape, dtype=np.int64)) if new_shape else 1
+        flat = x.to_array().reshape(-1)
+        off = index * stride
+        return Bits.from_array(flat[off:off + size].reshape(new_shape))
+    return _ring_from_view(x.bits, np.take(_ring_view(x), index, axis=axis))
+
+
+def ndarray_slice(length: int, start: int, end: Optional[int], step: Optional[int]):
+    """ndarray::Slice semantics (used by SliceInfo, host/mod.rs:153-165): negative start / end count from
+    the back, None end = len, negative step walks the selected range backwards from its last element."""
+    step = 1 if step is None else step
+    s = start + length if start < 0 else start
+    e = length if end is None else (end + length if end < 0 else end)
+    if not (0 <= s <= length and 0 <= e <= length) or step == 0:
+        raise IndexError("slice out of bounds")
+    e = max(e, s)
+    idx = list(range(s, e))
+    return idx[::step] if step > 0 else idx[::-1][::-step]
+
+
+def slice_ring(info, x: Ring) -> Ring:
+    """SliceOp::host_ring_kernel (host/ops.rs:523-535, 686-704); info = [(start, end, step), ...]."""
+    if len(info) != len(x.shape):
+        raise ValueError("The input dimension of `info` must match the array to be sliced.")
+    v = _ring_view(x)
+    for ax, (st, en, sp) in enumerate(info):
+        v = np.take(v, ndarray_slice(x.shape[ax], st, en, sp), axis=ax)
+    return _ring_from_view(x.bits, v)
+
+
+def diag(x):
+    """DiagOp (host/ops.rs:549-582); bits: lengths 1 and 2 only (bitarray.rs:110-128)."""
+    if isinstance(x, Bits):
+        n = min(x.shape) if x.shape else 1
+        flat = x.to_array().reshape(-1)
+        if n == 1:
+            return Bits.from_array(flat[:1])
+        if n == 2:
+            strides = [int(np.prod(x.shape[k + 1:], dtype=np.int64)) for k in range(len(x.shape))]
+            return Bits.from_array(np.array([flat[0], flat[sum(strides[:2])]], dtype=np.uint8))
+        raise NotImplementedError("todo!() in BitArrayRepr::into_diag")
+    v = _ring_view(x)
+    n = min(x.shape) if x.shape else 1
+    idx = tuple(np.arange(n) for _ in x.shape)
+    return _ring_from_view(x.bits, v[idx] if x.shape else v.reshape(1))
+
+
+def select(axis: int, index: Bits, x: Ring) -> Ring:
+    """SelectOp::host_ring_kernel (host/ops.rs:662-684, 803-818)."""
+    picks = np.nonzero(index.to_array().reshape(-1))[0]
+    return _ring_from_view(x.bits, np.take(_ring_view(x), picks, axis=axis))
+
+
+def ring_div(x: Ring, y: Ring) -> Ring:
+    """DivOp::ring_kernel (host/ops.rs:332-343): unsigned quotient, ndarray broadcasting."""
+    xb, yb, shape = _bcast(x, y)
+    a, b = xb.to_ints().reshape(-1), yb.to_ints().reshape(-1)
+    if any(int(v) == 0 for v in b):
+        raise ZeroDivisionError("attempt to divide by zero")
+    return Ring.from_ints(x.bits, [int(p) // int(q) for p, q in zip(a, b)], shape)
+
+
+def bit_decompose_ring(x: Ring) -> Ring:
+    """BitDecomposeOp::host_ring64/128_kernel (host/ops.rs:856-894): [k, shape...] ring planes."""
+    vals = [int(v) for v in x.to_ints().reshape(-1)]
+    planes = [[(v >> i) & 1 for v in vals] for i in range(x.bits)]
+    return Ring.from_ints(x.bits, planes, (x.bits,) + tuple(x.shape))
+
+
+def fixedpoint_mean(axis: Optional[int], scaling_base: int, scaling_exp: int, x: Ring) -> Ring:
+    """RingFixedpointMeanOp (host/fixedpoint.rs:41-113): sum(axis) * encode(1 / len, base^exp)."""
+    length = x.shape[axis] if axis is not None else x.size
+    scale = (scaling_base ** scaling_exp) % (1 << x.bits)
+    up = (1.0 / float(length)) * float(scale)
+    lim = float(1 << (x.bits - 1))
+    w = (1 << (x.bits - 1)) - 1 if up >= lim else (-(1 << (x.bits - 1)) if up <= -lim else int(up))
+    s = sum_axis(x, axis)
+    return mul(s, Ring.from_ints(x.bits, [w] * s.size, s.shape))
+
+
+def fixedpoint_argmax(axis: int, x: Ring) -> Ring:
+    """RingFixedpointArgmaxOp (host/ops.rs:2375-2437): first strict maximum of the signed values."""
+    signed = np.array(_signed_ints(x), dtype=object).reshape(x.shape)
+    moved = np.moveaxis(signed, axis, 0)
+    best = moved[0].copy() if moved.ndim > 1 else moved[0]
+    out_shape = moved.shape[1:]
+    flat_best = np.array(best, dtype=object).reshape(-1)
+    arg = [0] * flat_best.size
+    for j in range(moved.shape[0]):
+        row = np.array(moved[j], dtype=object).reshape(-1)
+        for t in range(flat_best.size):
+            if flat_best[t] < row[t]:
+                flat_best[t] = row[t]
+                arg[t] = j
+    return Ring.from_ints(64, arg, out_shape)

@@ -57,14 +57,61 @@ def replay(ops_in_order, sess: mo.Session, parse_constant, attr_hex16):
         elif k == "And":
             v = mo.bit_op("and", x[0], x[1]) if isinstance(x[0], mo.Bits) else mo.ring_and(x[0], x[1])
         elif k == "BitDecompose":
-            v = mo.bit_decompose(x[0])
+            v = mo.bit_decompose(x[0]) if op.output_type == "HostBitTensor" else mo.bit_decompose_ring(x[0])
         elif k == "RingInject":
             v = mo.ring_inject(_RING_BITS[op.output_type], int(op.attrs["bit_idx"]), x[0])
         elif k == "ShlDim":
             v = mo.shl_dim(int(op.attrs["amount"]), int(op.attrs["bit_length"]), x[0])
         elif k == "IndexAxis":
-            assert int(op.attrs["axis"]) == 0
-            v = mo.index_axis0(int(op.attrs["index"]), x[0])
+            v = mo.index_axis(int(op.attrs["axis"]), int(op.attrs["index"]), x[0])
+        elif k == "Identity":
+            v = x[0]
+        elif k == "ExpandDims":
+            v = mo.expand_dims([int(a) for a in op.attrs["axis"].strip("[] ").split(",") if a.strip()], x[0])
+        elif k == "Squeeze":
+            v = mo.squeeze(int(op.attrs["axis"]) if "axis" in op.attrs else None, x[0])
+        elif k == "Transpose":
+            v = mo.transpose(x[0])
+        elif k == "Concat":
+            v = mo.concat(int(op.attrs["axis"]), x)
+        elif k == "Slice":
+            f = {p.split("=")[0].strip(): int(p.split("=")[1]) for p in op.attrs["slice"].strip("{} ").split(",")}
+            info = [(f["start"], f.get("end"), f.get("step"))]
+            v = tuple(x[0][info[0][0]:info[0][1]]) if isinstance(x[0], tuple) else mo.slice_ring(info, x[0])
+        elif k == "Diag":
+            v = mo.diag(x[0])
+        elif k == "Select":
+            v = mo.select(int(op.attrs["axis"]), x[1], x[0])
+        elif k == "Div":
+            v = mo.ring_div(x[0], x[1])
+        elif k == "Less":
+            v = mo.host_less(x[0], x[1])
+        elif k == "Greater":
+            v = mo.host_greater(x[0], x[1])
+        elif k == "Mux":
+            v = mo.host_mux(x[0], x[1], x[2])
+        elif k == "Sign":
+            v = mo.host_sign(x[0])
+        elif k == "Cast":
+            v = mo.cast_ring128_to_ring64(x[0])
+        elif k == "Maximum":
+            v = mo.host_maximum(x)
+        elif k == "Sum":
+            axis = op.attrs.get("axis")
+            v = mo.sum_axis(x[0], None if axis in (None, "None") else int(axis))
+        elif k == "Or":
+            v = mo.bit_op("or", x[0], x[1])
+        elif k == "BitExtract":
+            v = mo.bit_extract(int(op.attrs["bit_idx"]), x[0])
+        elif k == "Reshape":
+            v = x[0].reshape(x[1]) if isinstance(x[0], mo.Ring) else mo.Bits(x[1], x[0].packed)
+        elif k == "Broadcast":
+            v = mo.broadcast(x[1], x[0])
+        elif k == "RingFixedpointMean":
+            v = mo.fixedpoint_mean(int(op.attrs["axis"]) if "axis" in op.attrs else None, int(op.attrs["scaling_base"]),
+                                   int(op.attrs["scaling_exp"]), x[0])
+        elif k == "RingFixedpointArgmax":
+            v = mo.fixedpoint_argmax(int(op.attrs["axis"]), x[0])
         elif k == "Send":
             mailbox[op.attrs["rendezvous_key"]] = x[0]
             v = None

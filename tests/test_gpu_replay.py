@@ -64,3 +64,20 @@ def test_replay_rep_computation_19045_ops():
         assert not mismatches, mismatches[:5]
     finally:
         sess.close()
+
+
+def test_replay_host_tail_graph():
+    """Shape / indexing / plaintext-helper operators through the executor, op for op against the oracle replay."""
+    from _util import HOST_TAIL_GRAPH
+    ops = tx.parse_computation(HOST_TAIL_GRAPH)
+    sess = mb.Session(0, "t", ENTROPY_KEY)
+    try:
+        ex = Executor(sess)
+        outs = ex.run(ops)
+        assert ex.executed == len(ops)
+        ovals, oouts = ro.replay(toposort(ops), mo.Session("t", ENTROPY_KEY), tx.parse_constant, tx.attr_hex16)
+        for op in ops:
+            assert same_value(ex.values[op.name], ovals[op.name]), op.name
+        assert np.array_equal(outs["mean"].to_host(), oouts["mean"])
+    finally:
+        sess.close()

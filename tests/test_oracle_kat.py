@@ -145,3 +145,35 @@ def test_elementwise_against_python_ints():
         C = mo.dot(mo.Ring.from_ints(bits, a, (M, K)), mo.Ring.from_ints(bits, b, (K, N)))
         exp = [sum(a[i * K + k] * b[k * N + j] for k in range(K)) % mod for i in range(M) for j in range(N)]
         assert ints(C) == exp
+
+
+def test_shape_ops_reference_vectors():
+    """Oracle restatement of the shape / indexing kernels against the reference's unit-test vectors:
+    host/mod.rs:613-663 (slice), :693-714 (diag), :717-761 (index_axis), :764-787 (transpose, concatenate),
+    :1232-1288 (bit transposes), host/fixedpoint.rs:120-145 (fixed-point mean)."""
+    x = mo.Ring.from_ints(64, [[1, 2], [3, 4]])
+    assert mo.slice_ring([(1, None, None), (0, None, None)], x).to_ints().tolist() == [[3, 4]]
+    assert mo.slice_ring([(-1, None, 2), (-1, None, 2)], x).to_ints().tolist() == [[4]]
+    with pytest.raises(ValueError):
+        mo.slice_ring([(-1, None, 2)] * 3, x)
+    assert mo.diag(x).to_ints().tolist() == [1, 4]
+    assert mo.diag(mo.Bits.from_array(np.array([[1, 1], [1, 0]]))).to_array().tolist() == [1, 0]
+    x3 = mo.Ring.from_ints(64, [[[1, 2], [3, 4]], [[4, 5], [6, 7]]])
+    assert mo.index_axis(0, 1, x3).to_ints().tolist() == [[4, 5], [6, 7]]
+    v = mo.expand_dims([0], mo.index_axis(0, 1, mo.Ring.from_ints(64, [0, 1, 2, 3])))
+    assert v.shape == (1,) and v.to_ints().tolist() == [1]
+    b3 = mo.Bits.from_array(np.array([[[0, 1], [0, 0]], [[1, 1], [0, 0]]]))
+    assert mo.index_axis(0, 1, b3).to_array().tolist() == [[1, 1], [0, 0]]
+    assert mo.index_axis(0, 0, b3).to_array().tolist() == [[0, 1], [0, 0]]
+    assert mo.transpose(x).to_ints().tolist() == [[1, 3], [2, 4]]
+    c = mo.concat(0, [mo.expand_dims([0], x), mo.expand_dims([0], x)])
+    assert c.to_ints().tolist() == [[[1, 2], [3, 4]], [[1, 2], [3, 4]]]
+    xt = mo.transpose(mo.bit_decompose(mo.Ring.from_ints(64, [6743216615002642708])))
+    assert xt.shape == (1, 64) and xt.to_array().reshape(-1).tolist() == [
+        0, 0, 1, 0, 1, 0, 0, 0, 1, 0, 0, 1, 1, 0, 0, 1, 0, 1, 1, 1, 1, 1, 0, 1, 0, 0, 1, 0,
+        0, 0, 1, 1, 0, 0, 0, 1, 0, 0, 1, 1, 1, 1, 1, 0, 1, 1, 0, 1, 0, 0, 1, 0, 1, 0, 0, 1,
+        1, 0, 1, 1, 1, 0, 1, 0]
+    assert mo.transpose(mo.Bits.from_array(np.array([[1, 1, 1], [0, 0, 0]]))).to_array().tolist() == [[1, 0]] * 3
+    e = mo.fixed_encode(64, np.array([[1., 2.], [3., 4.]]), 16)
+    assert mo.fixed_decode(mo.fixedpoint_mean(0, 2, 16, e), 32).tolist() == [2.0, 3.0]
+    assert float(mo.fixed_decode(mo.fixedpoint_mean(None, 2, 16, e), 32)) == 2.5

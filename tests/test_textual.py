@@ -87,3 +87,20 @@ def test_reader_on_every_reference_moose_file_and_fixtures_are_current():
     for f in files:
         assert len(tx.parse_computation(open(f).read())) > 0
     assert load("dotprod_compiled") == tx.parse_computation(open("/root/reference/tutorials/dotprod-compiled.moose").read())
+
+
+def test_host_tail_graph_on_oracle():
+    """Shape / indexing / plaintext-helper operators: parse a host-dialect graph written for these tests and
+    replay it on the oracle; plain values checked with numpy."""
+    from _util import ENTROPY_KEY, HOST_TAIL_GRAPH
+    ops = tx.parse_computation(HOST_TAIL_GRAPH)
+    assert len(ops) == 33 and tx.attr_slice(ops[11], "slice") == [(0, None, -1)] and tx.attr_int_list(ops[4], "axis") == [1]
+    vals, outs = ro.replay(toposort(ops), mo.Session("t", ENTROPY_KEY), tx.parse_constant, tx.attr_hex16)
+    x = np.array([[1.5, -2.0, 3.25], [0.5, 4.0, -1.0]])
+    cat = np.concatenate([x[:, :1], x], axis=1)
+    assert np.array_equal(outs["mean"], cat.mean(axis=0)) and np.array_equal(outs["abs"], np.abs(x))
+    assert vals["amax"].to_ints().tolist() == cat.argmax(axis=1).tolist()
+    assert vals["tail"] == (4,) and vals["sel"].shape == (3, 2) and vals["planes"].shape == (64, 2)
+    assert vals["dg"].to_ints().tolist() == [int(1.5 * 65536), int(4.0 * 65536)]
+    assert vals["either"].to_array().tolist() == [[1, 1, 1], [1, 1, 1]] and vals["nlt"].to_array().tolist() == [[1, 0, 1], [1, 1, 0]]
+    assert vals["total"].to_ints().tolist() == int(np.abs(x).sum() * 65536)
