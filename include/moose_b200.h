@@ -353,6 +353,35 @@ int mb_rep_sigmoid(mb_ctx *ctx, uint32_t integral_precision, uint32_t fractional
  * (moose/src/replicated/ops.rs:331-376,475-504). */
 int mb_rep_index_axis0(mb_ctx *ctx, int64_t index, const mb_rep *x, mb_rep **out);
 int mb_rep_shl_dim(mb_ctx *ctx, uint64_t amount, uint64_t bit_length, const mb_rep *x, mb_rep **out);
+/* Share-wise (local) replicated shape / reduction operators: the host kernel of the same name applied to each
+ * share (moose/src/replicated/ops.rs:48-89 Concat, :267-295 ExpandDims, :297-329 Reshape, :331-360 IndexAxis,
+ * :378-405 Diag, :407-473 Slice, :540-576 Broadcast, :578-620 Squeeze, :622-650 Transpose;
+ * moose/src/replicated/arith.rs:123-165 AddN, :167-195 Sum; moose/src/replicated/convert.rs:499-530 Cast
+ * (Ring128 -> Ring64 reduction of every share); moose/src/replicated/fixedpoint.rs:49-78 mean). */
+int mb_rep_index_axis(mb_ctx *ctx, int axis, int64_t index, const mb_rep *x, mb_rep **out);
+int mb_rep_expand_dims(mb_ctx *ctx, const int64_t *axes, int naxes, const mb_rep *x, mb_rep **out);
+int mb_rep_squeeze(mb_ctx *ctx, int axis, const mb_rep *x, mb_rep **out);
+int mb_rep_transpose(mb_ctx *ctx, const mb_rep *x, mb_rep **out);
+int mb_rep_reshape(mb_ctx *ctx, const mb_rep *x, int rank, const int64_t *shape, mb_rep **out);
+int mb_rep_broadcast(mb_ctx *ctx, const mb_rep *x, int rank, const int64_t *shape, mb_rep **out);
+int mb_rep_slice(mb_ctx *ctx, int n, const int64_t *start, const int64_t *end, const uint8_t *has_end,
+                 const int64_t *step, const mb_rep *x, mb_rep **out);
+int mb_rep_diag(mb_ctx *ctx, const mb_rep *x, mb_rep **out);
+int mb_rep_concat(mb_ctx *ctx, int axis, const mb_rep *const *xs, int n, mb_rep **out);
+int mb_rep_add_n(mb_ctx *ctx, const mb_rep *const *xs, int n, mb_rep **out);
+int mb_rep_sum(mb_ctx *ctx, const mb_rep *x, int axis, mb_rep **out);
+int mb_rep_cast_ring128_to_ring64(mb_ctx *ctx, const mb_rep *x, mb_rep **out);
+int mb_rep_fixedpoint_mean(mb_ctx *ctx, int axis, uint64_t scaling_base, uint32_t scaling_exp,
+                           const mb_rep *x, mb_rep **out);
+/* AbsOp::rep_ring_kernel (moose/src/replicated/arith.rs:655-674): (1 - 2 msb(x)) * x. */
+int mb_rep_abs(mb_ctx *ctx, const mb_rep *x, mb_rep **out);
+/* SoftmaxOp::rep_fixed_kernel (moose/src/replicated/softmax.rs:55-127): max over the first `upmost_index`
+ * entries of `axis`, exp of the difference, entries below -ln 2^(i-1) forced to 0, division by the sum. */
+int mb_rep_softmax(mb_ctx *ctx, int axis, int upmost_index, uint32_t integral_precision,
+                   uint32_t fractional_precision, const mb_rep *x, mb_rep **out);
+/* RingFixedpointArgmaxOp::rep_ring_kernel + TreeReduceArgmax (moose/src/replicated/argmax.rs:10-92): shared
+ * Ring64 index of the maximum over the first `upmost_index` (<= 256) entries of `axis`. */
+int mb_rep_argmax(mb_ctx *ctx, int axis, int upmost_index, const mb_rep *x, mb_rep **out);
 
 /* Selects the ring-GEMM implementation used by mb_dot / mb_rep_dot:
  * 0 = automatic (int8 tensor pipe for large shapes, 64-bit IMAD CUDA-core

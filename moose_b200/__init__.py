@@ -104,6 +104,13 @@ ABI = {
     "mb_rep_fill": [_P, _I, _I, _I64P, _U64, _U64, _PP], "mb_rep_greater": [_P, _P, _P, _PP],
     "mb_rep_div": [_P, _U32, _U32, _P, _P, _PP], "mb_rep_pow2": [_P, _U32, _U32, _P, _PP],
     "mb_rep_exp": [_P, _U32, _U32, _P, _PP], "mb_rep_sigmoid": [_P, _U32, _U32, _P, _PP],
+    "mb_rep_index_axis": [_P, _I, _I64, _P, _PP], "mb_rep_expand_dims": [_P, _I64P, _I, _P, _PP],
+    "mb_rep_squeeze": [_P, _I, _P, _PP], "mb_rep_transpose": [_P, _P, _PP], "mb_rep_reshape": [_P, _P, _I, _I64P, _PP],
+    "mb_rep_broadcast": [_P, _P, _I, _I64P, _PP], "mb_rep_slice": [_P, _I, _I64P, _I64P, _U8P, _I64P, _P, _PP],
+    "mb_rep_diag": [_P, _P, _PP], "mb_rep_concat": [_P, _I, _PP, _I, _PP], "mb_rep_add_n": [_P, _PP, _I, _PP],
+    "mb_rep_sum": [_P, _P, _I, _PP], "mb_rep_cast_ring128_to_ring64": [_P, _P, _PP],
+    "mb_rep_fixedpoint_mean": [_P, _I, _U64, _U32, _P, _PP], "mb_rep_abs": [_P, _P, _PP],
+    "mb_rep_softmax": [_P, _I, _I, _U32, _U32, _P, _PP], "mb_rep_argmax": [_P, _I, _I, _P, _PP],
     "mb_rep_index_axis0": [_P, _I64, _P, _PP], "mb_rep_shl_dim": [_P, _U64, _U64, _P, _PP],
 }
 _RESTYPES = {
@@ -650,6 +657,84 @@ class Session:
     def rep_pow2(self, i_prec, f_prec, x): return self._fixed_unary(lib().mb_rep_pow2, i_prec, f_prec, x)
     def rep_exp(self, i_prec, f_prec, x): return self._fixed_unary(lib().mb_rep_exp, i_prec, f_prec, x)
     def sigmoid(self, i_prec, f_prec, x): return self._fixed_unary(lib().mb_rep_sigmoid, i_prec, f_prec, x)
+
+    # share-wise shape / reduction operators (replicated/ops.rs, arith.rs:123-195)
+    def rep_index_axis(self, axis: int, index: int, x) -> RepTensor:
+        out = self._out()
+        return self._r(lib().mb_rep_index_axis(self.ctx, axis, index, x.h, ctypes.byref(out)), out)
+
+    def rep_expand_dims(self, axis, x) -> RepTensor:
+        axes = [axis] if isinstance(axis, int) else list(axis)
+        arr = (ctypes.c_int64 * max(len(axes), 1))(*axes)
+        out = self._out()
+        return self._r(lib().mb_rep_expand_dims(self.ctx, arr, len(axes), x.h, ctypes.byref(out)), out)
+
+    def rep_squeeze(self, axis: Optional[int], x) -> RepTensor:
+        out = self._out()
+        return self._r(lib().mb_rep_squeeze(self.ctx, -1 if axis is None else axis, x.h, ctypes.byref(out)), out)
+
+    def rep_transpose(self, x) -> RepTensor:
+        out = self._out()
+        return self._r(lib().mb_rep_transpose(self.ctx, x.h, ctypes.byref(out)), out)
+
+    def rep_reshape(self, x, shape) -> RepTensor:
+        arr, rank = _shape_arr(shape)
+        out = self._out()
+        return self._r(lib().mb_rep_reshape(self.ctx, x.h, rank, arr, ctypes.byref(out)), out)
+
+    def rep_broadcast(self, x, shape) -> RepTensor:
+        arr, rank = _shape_arr(shape)
+        out = self._out()
+        return self._r(lib().mb_rep_broadcast(self.ctx, x.h, rank, arr, ctypes.byref(out)), out)
+
+    def rep_slice(self, info, x) -> RepTensor:
+        trip = [(e.start or 0, e.stop, e.step) if isinstance(e, slice) else tuple(e) for e in info]
+        n = len(trip)
+        start = (ctypes.c_int64 * max(n, 1))(*[t[0] for t in trip])
+        end = (ctypes.c_int64 * max(n, 1))(*[0 if t[1] is None else t[1] for t in trip])
+        has_end = bytes(0 if t[1] is None else 1 for t in trip) + b"\0"
+        step = (ctypes.c_int64 * max(n, 1))(*[1 if t[2] is None else t[2] for t in trip])
+        out = self._out()
+        return self._r(lib().mb_rep_slice(self.ctx, n, start, end, has_end, step, x.h, ctypes.byref(out)), out)
+
+    def rep_diag(self, x) -> RepTensor:
+        out = self._out()
+        return self._r(lib().mb_rep_diag(self.ctx, x.h, ctypes.byref(out)), out)
+
+    def rep_concat(self, axis: int, xs) -> RepTensor:
+        arr = (ctypes.c_void_p * max(len(xs), 1))(*[x.h for x in xs])
+        out = self._out()
+        return self._r(lib().mb_rep_concat(self.ctx, axis, arr, len(xs), ctypes.byref(out)), out)
+
+    def rep_add_n(self, xs) -> RepTensor:
+        arr = (ctypes.c_void_p * max(len(xs), 1))(*[x.h for x in xs])
+        out = self._out()
+        return self._r(lib().mb_rep_add_n(self.ctx, arr, len(xs), ctypes.byref(out)), out)
+
+    def rep_sum(self, x, axis: Optional[int] = None) -> RepTensor:
+        out = self._out()
+        return self._r(lib().mb_rep_sum(self.ctx, x.h, -1 if axis is None else axis, ctypes.byref(out)), out)
+
+    def rep_cast_ring128_to_ring64(self, x) -> RepTensor:
+        out = self._out()
+        return self._r(lib().mb_rep_cast_ring128_to_ring64(self.ctx, x.h, ctypes.byref(out)), out)
+
+    def rep_fixedpoint_mean(self, axis: Optional[int], scaling_base: int, scaling_exp: int, x) -> RepTensor:
+        out = self._out()
+        return self._r(lib().mb_rep_fixedpoint_mean(self.ctx, -1 if axis is None else axis, scaling_base, scaling_exp,
+                                                    x.h, ctypes.byref(out)), out)
+
+    def rep_abs(self, x) -> RepTensor:
+        out = self._out()
+        return self._r(lib().mb_rep_abs(self.ctx, x.h, ctypes.byref(out)), out)
+
+    def softmax(self, axis: int, upmost_index: int, i_prec: int, f_prec: int, x) -> RepTensor:
+        out = self._out()
+        return self._r(lib().mb_rep_softmax(self.ctx, axis, upmost_index, i_prec, f_prec, x.h, ctypes.byref(out)), out)
+
+    def argmax(self, axis: int, upmost_index: int, x) -> RepTensor:
+        out = self._out()
+        return self._r(lib().mb_rep_argmax(self.ctx, axis, upmost_index, x.h, ctypes.byref(out)), out)
 
     def rep_index_axis0(self, index: int, x) -> RepTensor:
         out = self._out()

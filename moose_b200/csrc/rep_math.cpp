@@ -272,6 +272,65 @@ R rep_sigmoid(mb_ctx *c, int i_prec, int f_prec, const R &x) {
   return mux(c, lower_ring, zeros_rep, upper_wall);
 }
 
+// share-wise helpers (rep_shape.cpp)
+R index_axis(mb_ctx *c, int axis, int64_t i, const R &a) { mb_rep *q = nullptr; ck(mb_rep_index_axis(c, axis, i, a.p, &q)); return R(c, q); }
+R expand_dim(mb_ctx *c, int axis, const R &a) { const int64_t ax = axis; mb_rep *q = nullptr; ck(mb_rep_expand_dims(c, &ax, 1, a.p, &q)); return R(c, q); }
+R sum_axis(mb_ctx *c, int axis, const R &a) { mb_rep *q = nullptr; ck(mb_rep_sum(c, a.p, axis, &q)); return R(c, q); }
+R less_bit(mb_ctx *c, const R &x, const R &y) { return msb_bit(c, sub(c, x, y)); }  // compare.rs:91-104
+
+// AbsOp::rep_ring_kernel (arith.rs:655-674)
+R rep_abs(mb_ctx *c, const R &x) {
+  R msb = msb_ring(c, x);
+  return mul(c, sign_from_msb(c, msb), x);
+}
+
+// SoftmaxOp::rep_fixed_kernel (softmax.rs:55-127)
+R rep_softmax(mb_ctx *c, int axis, int upmost_index, int i_prec, int f_prec, const R &x) {
+  const int bits = bits_of(x);
+  std::vector<mb_rep *> raw;
+  std::vector<R> xs;
+  for (int i = 0; i < upmost_index; i++) xs.push_back(index_axis(c, axis, i, x));
+  for (auto &t : xs) raw.push_back(t.p);
+  mb_rep *mq = nullptr;
+  ck(mb_rep_maximum(c, raw.data(), (int)raw.size(), &mq));
+  R xmax = expand_dim(c, axis, R(c, mq));
+  R max_diff = sub(c, x, xmax);
+  R e_x = rep_exp(c, i_prec, f_prec, max_diff);
+  R zeros_rep = rep_fill(c, e_x.like(), 0);
+  const double min_val = -1.0 * std::log(std::pow(2.0, (double)(i_prec - 1)));
+  R lower_bound = rep_fill(c, max_diff.like(), fixed_constant(bits, min_val, (unsigned)f_prec));
+  R threshold_ring = inject(c, ring_of(x), 0, greater(c, lower_bound, max_diff));
+  R normalized = mux(c, threshold_ring, zeros_rep, e_x);
+  R e_x_sum = expand_dim(c, axis, sum_axis(c, axis, normalized));
+  return rep_div(c, i_prec, f_prec, normalized, e_x_sum);
+}
+
+// RingFixedpointArgmaxOp::rep_ring_kernel with TreeReduceArgmax (argmax.rs:10-92); the result is Ring64
+struct IdxVal { R idx, val; };
+IdxVal argmax_tree(mb_ctx *c, std::vector<IdxVal> &v, size_t lo, size_t hi) {
+  if (hi - lo == 1) return IdxVal{v[lo].idx.clone(), v[lo].val.clone()};
+  const size_t mid = lo + (hi - lo) / 2;
+  IdxVal a = argmax_tree(c, v, lo, mid);
+  IdxVal b = argmax_tree(c, v, mid, hi);
+  R comp_ring = inject(c, ring_of(a.val), 0, less_bit(c, a.val, b.val));
+  R idx = mux(c, comp_ring, b.idx, a.idx);
+  R val = mux(c, comp_ring, b.val, a.val);
+  return IdxVal{std::move(idx), std::move(val)};
+}
+R rep_argmax(mb_ctx *c, int axis, int upmost_index, const R &x) {
+  std::vector<IdxVal> pairs;
+  for (int i = 0; i < upmost_index; i++) {
+    R item = index_axis(c, axis, i, x);
+    R idx = rep_fill(c, item.like(), (u128)(uint8_t)i);  // (i as u8).into()
+    pairs.push_back(IdxVal{std::move(idx), std::move(item)});
+  }
+  IdxVal top = argmax_tree(c, pairs, 0, pairs.size());
+  if (ring_of(x) == MB_RING64) return std::move(top.idx);
+  mb_rep *q = nullptr;
+  ck(mb_rep_cast_ring128_to_ring64(c, top.idx.p, &q));
+  return R(c, q);
+}
+
 bool valid(const mb_rep *x) { return x && x->s[0] && x->s[1] && x->s[2]; }
 
 template <typename F>
@@ -356,6 +415,38 @@ extern "C" int mb_rep_sigmoid(mb_ctx *ctx, uint32_t i_prec, uint32_t f_prec, con
     MB_CHECK(check_fixed(ctx, x, i_prec, f_prec, "mb_rep_sigmoid"));
     if (!out) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_rep_sigmoid: NULL out");
     R r = rep_sigmoid(ctx, (int)i_prec, (int)f_prec, borrow(ctx, x));
+    *out = r.release();
+    return (int)MB_OK;
+  });
+}
+
+extern "C" int mb_rep_abs(mb_ctx *ctx, const mb_rep *x, mb_rep **out) {
+  return guarded(ctx, "mb_rep_abs", [&]() {
+    if (!valid(x) || !out) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_rep_abs: NULL argument");
+    if (!mb_is_ring(x->s[0]->dtype)) return mb_fail(ctx, MB_ERR_TYPE_MISMATCH, "mb_rep_abs: needs ring shares");
+    R r = rep_abs(ctx, borrow(ctx, x));
+    *out = r.release();
+    return (int)MB_OK;
+  });
+}
+extern "C" int mb_rep_softmax(mb_ctx *ctx, int axis, int upmost_index, uint32_t i_prec, uint32_t f_prec, const mb_rep *x, mb_rep **out) {
+  return guarded(ctx, "mb_rep_softmax", [&]() {
+    MB_CHECK(check_fixed(ctx, x, i_prec, f_prec, "mb_rep_softmax"));
+    if (!out) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_rep_softmax: NULL out");
+    if (axis < 0 || axis >= x->s[0]->rank || upmost_index < 1 || upmost_index > x->s[0]->shape[axis])
+      return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_rep_softmax: axis / upmost_index out of range");
+    R r = rep_softmax(ctx, axis, upmost_index, (int)i_prec, (int)f_prec, borrow(ctx, x));
+    *out = r.release();
+    return (int)MB_OK;
+  });
+}
+extern "C" int mb_rep_argmax(mb_ctx *ctx, int axis, int upmost_index, const mb_rep *x, mb_rep **out) {
+  return guarded(ctx, "mb_rep_argmax", [&]() {
+    if (!valid(x) || !out) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_rep_argmax: NULL argument");
+    if (!mb_is_ring(x->s[0]->dtype)) return mb_fail(ctx, MB_ERR_TYPE_MISMATCH, "mb_rep_argmax: needs ring shares");
+    if (axis < 0 || axis >= x->s[0]->rank || upmost_index < 1 || upmost_index > x->s[0]->shape[axis] || upmost_index > 256)
+      return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_rep_argmax: axis / upmost_index out of range");
+    R r = rep_argmax(ctx, axis, upmost_index, borrow(ctx, x));
     *out = r.release();
     return (int)MB_OK;
   });

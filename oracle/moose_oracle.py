@@ -261,7 +261,7 @@ def broadcast(x: Ring, shape) -> Ring:
     """BroadcastOp::host_ring_kernel (host/ops.rs:1668-1681)."""
     shape = tuple(shape)
     tail = (2,) if x.bits == 128 else ()
-    return Ring(x.bits, np.ascontiguousarray(np.broadcast_to(x.data, shape + tail)))
+    return Ring(x.bits, np.ascontiguousarray(np.broadcast_to(x.data, shape + tail)).reshape(shape + tail))
 
 
 def _ew2(op: str, x, y):
@@ -1434,3 +1434,98 @@ def fixedpoint_argmax(axis: int, x: Ring) -> Ring:
                 flat_best[t] = row[t]
                 arg[t] = j
     return Ring.from_ints(64, arg, out_shape)
+
+
+# -- replicated share-wise shape ops, softmax, argmax ------------------------------
+
+def _sharewise(f, x: RepTensor) -> RepTensor:
+    return RepTensor([[f(v) for v in row] for row in x.shares])
+
+
+def rep_index_axis(axis: int, index: int, x: RepTensor) -> RepTensor:
+    """IndexAxisOp::rep_kernel (replicated/ops.rs:331-360)."""
+    return _sharewise(lambda v: index_axis(axis, index, v), x)
+
+
+def rep_expand_dims(axes, x: RepTensor) -> RepTensor:
+    """ExpandDimsOp::rep_kernel (replicated/ops.rs:267-295)."""
+    return _sharewise(lambda v: expand_dims(axes, v), x)
+
+
+def rep_squeeze(axis, x: RepTensor) -> RepTensor:
+    """SqueezeOp::rep_kernel (replicated/ops.rs:578-620)."""
+    return _sharewise(lambda v: squeeze(axis, v), x)
+
+
+def rep_transpose(x: RepTensor) -> RepTensor:
+    """TransposeOp::rep_kernel (replicated/ops.rs:622-650)."""
+    return _sharewise(transpose, x)
+
+
+def rep_sum(axis, x: RepTensor) -> RepTensor:
+    """SumOp::rep_kernel (replicated/arith.rs:167-195)."""
+    return _sharewise(lambda v: sum_axis(v, axis), x)
+
+
+def rep_concat(axis: int, xs) -> RepTensor:
+    """ConcatOp::rep_kernel (replicated/ops.rs:48-89)."""
+    return RepTensor([[concat(axis, [t.shares[i][j] for t in xs]) for j in range(2)] for i in range(3)])
+
+
+def rep_cast_64(x: RepTensor) -> RepTensor:
+    """CastOp::rep_reduction_kernel (replicated/convert.rs:499-530): share-wise mod 2^64."""
+    return _sharewise(cast_ring128_to_ring64, x)
+
+
+def rep_fixedpoint_mean(axis, scaling_base: int, scaling_exp: int, x: RepTensor) -> RepTensor:
+    """RingFixedpointMeanOp::rep_kernel (replicated/fixedpoint.rs:49-78)."""
+    return _sharewise(lambda v: fixedpoint_mean(axis, scaling_base, scaling_exp, v), x)
+
+
+def rep_softmax(sess, axis: int, upmost_index: int, i_prec: int, f_prec: int, x: RepTensor) -> RepTensor:
+    """SoftmaxOp::rep_fixed_kernel (replicated/softmax.rs:55-127)."""
+    import math
+    bits = x.shares[0][0].bits
+    xs = [rep_index_axis(axis, i, x) for i in range(upmost_index)]
+    xmax = rep_expand_dims([axis], rep_maximum(sess, xs))
+    max_diff = rep_sub(x, xmax)
+    e_x = rep_exp(sess, i_prec, f_prec, max_diff)
+    zeros_rep = rep_fill(bits, 0, e_x.shape)
+    min_val = -1.0 * math.log(2.0 ** (i_prec - 1))
+    lower_bound = rep_fill(bits, fixed_constant(bits, min_val, f_prec), max_diff.shape)
+    threshold = rep_greater(sess, lower_bound, max_diff)
+    threshold_ring = rep_ring_inject(sess, bits, 0, threshold)
+    normalized = rep_mux(sess, threshold_ring, zeros_rep, e_x)
+    e_x_sum = rep_expand_dims([axis], rep_sum(axis, normalized))
+    return rep_div(sess, i_prec, f_prec, normalized, e_x_sum)
+
+
+def rep_argmax(sess, axis: int, upmost_index: int, x: RepTensor) -> RepTensor:
+    """RingFixedpointArgmaxOp::rep_ring_kernel + TreeReduceArgmax (replicated/argmax.rs:10-92); result Ring64."""
+    bits = x.shares[0][0].bits
+    xs = [rep_index_axis(axis, i, x) for i in range(upmost_index)]
+    pairs = [(rep_fill(bits, i, item.shape), item) for i, item in enumerate(xs)]
+
+    def combine(a, b):
+        comp_ring = rep_ring_inject(sess, bits, 0, rep_less(sess, a[1], b[1]))
+        return rep_mux(sess, comp_ring, b[0], a[0]), rep_mux(sess, comp_ring, b[1], a[1])
+
+    def tree(v):
+        if len(v) == 1:
+            return v[0]
+        return combine(tree(v[: len(v) // 2]), tree(v[len(v) // 2:]))
+
+    secret_index, _ = tree(pairs)
+    return rep_cast_64(secret_index) if bits == 128 else secret_index
+
+
+def rep_abs(sess, x: RepTensor) -> RepTensor:
+    """AbsOp::rep_ring_kernel (replicated/arith.rs:655-674)."""
+    bits = x.shares[0][0].bits
+    msb_ring = rep_msb_ring(sess, x)
+    return rep_mul(sess, sign_from_msb(bits, msb_ring), x)
+
+
+def rep_add_n(xs) -> RepTensor:
+    """AddNOp::rep_kernel (replicated/arith.rs:123-165)."""
+    return RepTensor([[add_n([t.shares[i][j] for t in xs]) for j in range(2)] for i in range(3)])

@@ -177,3 +177,22 @@ def test_shape_ops_reference_vectors():
     e = mo.fixed_encode(64, np.array([[1., 2.], [3., 4.]]), 16)
     assert mo.fixed_decode(mo.fixedpoint_mean(0, 2, 16, e), 32).tolist() == [2.0, 3.0]
     assert float(mo.fixed_decode(mo.fixedpoint_mean(None, 2, 16, e), 32)) == 2.5
+
+
+def test_softmax_argmax_reference_vectors():
+    """Oracle restatement of softmax / argmax against the reference's own test vectors and tolerances:
+    replicated/softmax.rs:189-230 (abs error < 0.01), replicated/argmax.rs:123-200 (exact)."""
+    s = mo.Session("kat", bytes(range(16)))
+    x = np.array([1, 2.5, -3.0, 4.0, 2.0, -2.0, -2.0, -3.0, 3.0])
+    e = np.exp(x - x.max())
+    e /= e.sum()
+    for bits, i_p, f_p in ((64, 8, 10), (128, 8, 27)):
+        r = mo.rep_softmax(s, 0, 9, i_p, f_p, mo.rep_share(s, mo.fixed_encode(bits, x, f_p), 0))
+        assert r.shape == (9,) and np.abs(mo.fixed_decode(mo.rep_reveal(r), f_p) - e).max() < 0.01
+    cases = [(64, 0, 9, [1, 2, -3, 4, 2, 2, 2, 3, 105], 8),
+             (64, 1, 4, [[1231, -323, -3, 12321], [93213, 12312321, -321, -3249], [3921, 4012, 3221, -321]], [3, 1, 1]),
+             (128, 0, 9, [1, 2, -3, 10000, 10000, 10000, 10000, 10000, 10000], 3),
+             (128, 1, 3, [[-3233, 329423, 54843], [3994, 123, -31326], [-324, 55321, 23441]], [1, 0, 1])]
+    for bits, axis, upmost, vals, expect in cases:
+        r = mo.rep_reveal(mo.rep_argmax(s, axis, upmost, mo.rep_share(s, mo.Ring.from_ints(bits, vals), 0)))
+        assert r.bits == 64 and r.to_ints().tolist() == expect
