@@ -256,7 +256,7 @@ def run_mlp(args):
 
 def run_logreg(args):
     """BASELINE configs[2]: LinearClassifier, 512 features, 2 classes, sigmoid post-transform, Ring128 fixed(24,40).
-    One step = share + dot [B,513]x[513,2] + TruncPr + sigmoid over a device-resident fixed-point batch."""
+    One step = share + bias concat + dot [B,513]x[513,2] + TruncPr + sigmoid over a device-resident fixed-point batch."""
     import moose_b200 as mb
     from moose_b200.predictors import LinearPredictor
     rank = int(os.environ.get("RANK", "0"))
@@ -275,7 +275,7 @@ def run_logreg(args):
     chunks = []
     for lo in range(0, B, 1 << 17):
         n = min(1 << 17, B - lo)
-        xc = np.concatenate([np.ones((n, 1)), rng.uniform(-1, 1, (n, feats))], axis=1)
+        xc = rng.uniform(-1, 1, (n, feats))
         if x_head is None:
             x_head = xc[:64].copy()
         chunks.append(fixed128(xc))
@@ -294,7 +294,7 @@ def run_logreg(args):
     launches = reduce_sum_int(dist, sess.launch_count - l0, local_rank)
     ms = reduce_max(dist, [ms], local_rank)[0]
     got = sess.fixedpoint_decode(40, sess.reveal(out)).to_host()[:64]
-    ref = 1.0 / (1.0 + np.exp(-(x_head[:, 1:] @ coeffs.T + intercepts)))
+    ref = 1.0 / (1.0 + np.exp(-(x_head @ coeffs.T + intercepts)))
     if rank == 0:
         print(json.dumps({
             "metric": "logreg_inference_rows_per_s", "value": aggregate_value(B, args.steps, world, ms),

@@ -383,6 +383,51 @@ int mb_rep_softmax(mb_ctx *ctx, int axis, int upmost_index, uint32_t integral_pr
  * Ring64 index of the maximum over the first `upmost_index` (<= 256) entries of `axis`. */
 int mb_rep_argmax(mb_ctx *ctx, int axis, int upmost_index, const mb_rep *x, mb_rep **out);
 
+/* ------------------------------------------------------------ graph replay */
+
+/* Reader for Moose's textual computation format, host dialect (grammar of moose/src/textual/parsing.rs), and a
+ * replay executor that walks a lowered computation in topological order and dispatches every operation to the
+ * entry point above that replaces its Rust kernel -- the role SyncSession / AsyncSession play in the reference
+ * (moose/src/execution/synchronous.rs:347-361, asynchronous.rs:453-531; dispatch table moose/src/kernels/mod.rs:34-106).
+ * Only @Host operations are executable (what remains after moose/src/compilation/lowering.rs). */
+typedef struct mb_graph mb_graph;
+typedef struct mb_exec mb_exec;
+int mb_graph_parse(mb_ctx *ctx, const char *text, mb_graph **out);
+int mb_graph_free(mb_graph *g);
+int64_t mb_graph_num_ops(const mb_graph *g);
+/* Name of the i-th operation in execution order (every Receive directly after its Send); NULL past the end. */
+const char *mb_graph_op_name(const mb_graph *g, int64_t i);
+/* role == NULL: all parties in this process, Send/Receive are a mailbox hand-off (networking/local.rs:10-53).
+ * role != NULL: run only the operations placed on `role`; Send/Receive go through the transport. */
+int mb_exec_create(mb_ctx *ctx, const mb_graph *g, const char *role, mb_exec **out);
+int mb_exec_free(mb_exec *e);
+/* Transport for Send / Receive (moose/src/networking/mod.rs:16-54) in party-per-process mode.  The executor
+ * calls it once for a 10-word int64 header in host memory (kind, dtype, rank, shape[6], payload bytes) and once
+ * more for the payload; tensor payloads are DEVICE memory (on_device = 1), keys / seeds / strings host memory.
+ * Return 0 on success.  The caller binds it to NCCL send/recv between the parties' GPUs. */
+typedef int (*mb_transport_fn)(void *user, int is_send, const char *peer_role, void *buf, size_t nbytes, int on_device);
+int mb_exec_set_transport(mb_exec *e, mb_transport_fn fn, void *user);
+/* Binds a tensor to an Input operation (by arg_name) or replaces the result of the named operation (e.g. the
+ * Constant inputs of a compiled graph by larger tensors: lowered graphs are shape-agnostic). */
+int mb_exec_bind_tensor(mb_exec *e, const char *name, const mb_tensor *t);
+/* keep = 1 (default): every operation's result stays readable through mb_exec_value after the run.
+ * keep = 0: a value is released once its last consumer in this process has run (outputs and saved values stay). */
+int mb_exec_set_keep_values(mb_exec *e, int keep);
+int mb_exec_run(mb_exec *e);
+uint64_t mb_exec_executed(const mb_exec *e);
+uint64_t mb_exec_bytes_sent(const mb_exec *e);
+/* Host wall-clock seconds of the last runs spent inside the transport (which = 0) and waiting for the
+ * context's stream before handing a buffer to it (which = 1). */
+double mb_exec_seconds(const mb_exec *e, int which);
+/* Result of the named operation after a run.  kind: 0 tensor (a new reference in *tensor, free it with
+ * mb_tensor_free), 1 key / seed bytes, 2 shape, 3 unit, 4 string, -1 not executed. */
+int mb_exec_value(mb_exec *e, const char *op_name, int *kind, mb_tensor **tensor, uint8_t *bytes, size_t bytes_cap,
+                  size_t *nbytes, int64_t *shape, int *rank);
+/* Tensor recorded by an Output operation under its tag (saved = 0) or by a Save operation under its key
+ * (saved = 1); a new reference. */
+int mb_exec_output(mb_exec *e, int saved, const char *key, mb_tensor **tensor);
+const char *mb_exec_output_key(const mb_exec *e, int saved, int64_t i);
+
 /* Selects the ring-GEMM implementation used by mb_dot / mb_rep_dot:
  * 0 = automatic (int8 tensor pipe for large shapes, 64-bit IMAD CUDA-core
  * kernel for skinny / small ones), 1 = force IMAD, 2 = force tensor pipe

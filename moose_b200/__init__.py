@@ -111,12 +111,21 @@ ABI = {
     "mb_rep_sum": [_P, _P, _I, _PP], "mb_rep_cast_ring128_to_ring64": [_P, _P, _PP],
     "mb_rep_fixedpoint_mean": [_P, _I, _U64, _U32, _P, _PP], "mb_rep_abs": [_P, _P, _PP],
     "mb_rep_softmax": [_P, _I, _I, _U32, _U32, _P, _PP], "mb_rep_argmax": [_P, _I, _I, _P, _PP],
+    "mb_graph_parse": [_P, ctypes.c_char_p, _PP], "mb_graph_free": [_P], "mb_graph_num_ops": [_P],
+    "mb_graph_op_name": [_P, _I64], "mb_exec_create": [_P, _P, ctypes.c_char_p, _PP], "mb_exec_free": [_P],
+    "mb_exec_set_transport": [_P, _P, _P], "mb_exec_bind_tensor": [_P, ctypes.c_char_p, _P], "mb_exec_run": [_P], "mb_exec_set_keep_values": [_P, _I],
+    "mb_exec_executed": [_P], "mb_exec_bytes_sent": [_P], "mb_exec_seconds": [_P, _I],
+    "mb_exec_value": [_P, ctypes.c_char_p, ctypes.POINTER(ctypes.c_int), _PP, _P, ctypes.c_size_t,
+                      ctypes.POINTER(ctypes.c_size_t), _I64P, ctypes.POINTER(ctypes.c_int)],
+    "mb_exec_output": [_P, _I, ctypes.c_char_p, _PP], "mb_exec_output_key": [_P, _I, _I64],
     "mb_rep_index_axis0": [_P, _I64, _P, _PP], "mb_rep_shl_dim": [_P, _U64, _U64, _P, _PP],
 }
 _RESTYPES = {
     "mb_last_error": ctypes.c_char_p, "mb_ctx_stream": _P, "mb_ctx_launch_count": _U64,
     "mb_tensor_shape": _I64P, "mb_tensor_numel": _I64, "mb_tensor_nbytes": ctypes.c_size_t,
     "mb_tensor_device_ptr": _P, "mb_rep_share_tensor": _P,
+    "mb_graph_num_ops": _I64, "mb_graph_op_name": ctypes.c_char_p, "mb_exec_executed": _U64, "mb_exec_bytes_sent": _U64,
+    "mb_exec_output_key": ctypes.c_char_p, "mb_exec_seconds": ctypes.c_double,
 }
 
 
@@ -255,6 +264,8 @@ class Session:
 
     def close(self):
         if self.ctx:
+            for child in list(getattr(self, "_children", ())):  # native executors hold tensors of this context
+                child._free()
             for p in self._pinned:
                 lib().mb_host_free_pinned(self.ctx, p)
             self._pinned = []

@@ -43,6 +43,7 @@ struct AesKey {
 struct mb_ctx {
   int device;
   cudaStream_t stream;
+  cudaStream_t aux_stream;    // allocations that must not be ordered after `stream` (receive buffers)
   cudaEvent_t ev0, ev1;
   int sm_count;
   std::mutex mu;             // guards entropy, setup, last-error bookkeeping
@@ -93,6 +94,7 @@ int mb_fail(const mb_ctx *ctx, int code, const std::string &msg);
 static inline int mb_elem_bytes(mb_dtype d) { return d == MB_RING128 ? 16 : 8; }
 static inline bool mb_is_ring(mb_dtype d) { return d == MB_RING64 || d == MB_RING128; }
 int mb_tensor_new(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, mb_tensor **out);
+int mb_tensor_new_detached(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, mb_tensor **out);
 mb_tensor *mb_tensor_retain(mb_tensor *t);
 bool mb_same_shape(const mb_tensor *a, const mb_tensor *b);
 int mb_scratch(mb_ctx *ctx, int slot, size_t bytes, void **out);

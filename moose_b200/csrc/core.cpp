@@ -37,6 +37,7 @@ extern "C" int mb_ctx_create(int device, mb_ctx **out) {
   memset(ctx->scratch_bytes, 0, sizeof(ctx->scratch_bytes));
   MB_CUDA(ctx, cudaSetDevice(device));
   MB_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  MB_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->aux_stream, cudaStreamNonBlocking));
   MB_CUDA(ctx, cudaEventCreate(&ctx->ev0));
   MB_CUDA(ctx, cudaEventCreate(&ctx->ev1));
   MB_CUDA(ctx, cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device));
@@ -45,6 +46,9 @@ extern "C" int mb_ctx_create(int device, mb_ctx **out) {
   if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
     uint64_t thresh = UINT64_MAX;
     cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thresh);
+    // an allocation on the auxiliary stream must never wait for work of the main stream (mb_tensor_new_detached)
+    int no = 0;
+    cudaMemPoolSetAttribute(pool, cudaMemPoolReuseAllowInternalDependencies, &no);
   }
   // default session id: SessionId::try_from("b200") -- callers normally set their own
   mb_blake3_session_id("b200", 4, ctx->sid);
@@ -62,6 +66,7 @@ extern "C" int mb_ctx_destroy(mb_ctx *ctx) {
   for (auto ev : ctx->prof_pool) cudaEventDestroy(ev);
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
+  cudaStreamDestroy(ctx->aux_stream);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
   return MB_OK;
@@ -199,7 +204,23 @@ int mb_scratch(mb_ctx *ctx, int slot, size_t bytes, void **out) {
 
 // ---- tensors ------------------------------------------------------------------
 
+static int tensor_new_on(mb_ctx *ctx, cudaStream_t stream, mb_dtype dtype, int rank, const int64_t *shape, mb_tensor **out);
+
 int mb_tensor_new(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, mb_tensor **out) {
+  return tensor_new_on(ctx, ctx ? ctx->stream : nullptr, dtype, rank, shape, out);
+}
+
+// A tensor whose memory is NOT ordered after the context's stream: allocated on the auxiliary stream, which is
+// drained before returning, so another stream or library (a transport receiving into it) may write it at once
+// while earlier work of the context is still running.  The writer must be complete before the context reads it.
+int mb_tensor_new_detached(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, mb_tensor **out) {
+  if (!ctx) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "tensor: NULL argument");
+  MB_CHECK(tensor_new_on(ctx, ctx->aux_stream, dtype, rank, shape, out));
+  MB_CUDA(ctx, cudaStreamSynchronize(ctx->aux_stream));
+  return MB_OK;
+}
+
+static int tensor_new_on(mb_ctx *ctx, cudaStream_t stream, mb_dtype dtype, int rank, const int64_t *shape, mb_tensor **out) {
   if (!ctx || !out) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "tensor: NULL argument");
   if (rank < 0 || rank > MB_MAX_RANK) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "tensor: rank out of range");
   if (dtype != MB_RING64 && dtype != MB_RING128 && dtype != MB_BIT && dtype != MB_FLOAT64)
@@ -220,16 +241,16 @@ int mb_tensor_new(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, m
   t->refs = 1;
   t->device = ctx->device;
   t->dptr = nullptr;
-  cudaError_t e = cudaMallocAsync(&t->dptr, t->alloc_bytes, ctx->stream);
+  cudaError_t e = cudaMallocAsync(&t->dptr, t->alloc_bytes, stream);
   if (e != cudaSuccess) {
     delete t;
     return mb_fail(ctx, MB_ERR_CUDA, std::string("cudaMallocAsync: ") + cudaGetErrorString(e));
   }
   if (dtype == MB_BIT) {
     // packed-bit invariant: bits beyond numel (and padding bytes) are zero
-    e = cudaMemsetAsync((char *)t->dptr + (t->alloc_bytes - 16), 0, 16, ctx->stream);
+    e = cudaMemsetAsync((char *)t->dptr + (t->alloc_bytes - 16), 0, 16, stream);
     if (e != cudaSuccess) {
-      cudaFreeAsync(t->dptr, ctx->stream);
+      cudaFreeAsync(t->dptr, stream);
       delete t;
       return mb_fail(ctx, MB_ERR_CUDA, std::string("cudaMemsetAsync: ") + cudaGetErrorString(e));
     }

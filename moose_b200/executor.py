@@ -1,30 +1,30 @@
-"""Replay executor for lowered (host-dialect) Moose computations over libmoose_b200.
+"""Replay of lowered (host-dialect) Moose computations: Python face of the C++ reader + executor in
+libmoose_b200 (csrc/executor.cpp, entry points mb_graph_* / mb_exec_* of include/moose_b200.h).
 
-Stand-in for the reference's executors (moose/src/execution/synchronous.rs:347-361 and
-asynchronous.rs:453-531) on the other side of the C-ABI boundary: those are Rust and cannot be built in this
-image, so this module walks a parsed computation (moose_b200/textual.py) in topological order and dispatches
-every operation to the host-kernel entry point that replaces its Rust kernel -- the same (operator,
-placement, operand types) -> kernel mapping as `DispatchKernel::compile` (moose/src/kernels/mod.rs:34-106).
+The executor stands where the reference's executors stand (moose/src/execution/synchronous.rs:347-361 and
+asynchronous.rs:453-531): it walks a parsed computation in topological order and dispatches every operation to the
+host-kernel entry point that replaces its Rust kernel -- the same (operator, placement, operand types) -> kernel
+mapping as `DispatchKernel::compile` (moose/src/kernels/mod.rs:34-106).  Parsing, scheduling, dispatch and the value
+store are native; this module only marshals graphs / tensors and binds the transport.
 
 Two modes:
   * all parties on one GPU: every `@Host(role)` op runs on the one session; a Send/Receive pair
-    (moose/src/networking/mod.rs:16-54) is a handle hand-off keyed by the rendezvous key, exactly like the
-    reference's in-memory LocalSyncNetworking (networking/local.rs:10-53);
-  * party per GPU: each process owns one role and one GPU, runs only that role's ops, and maps Send/Receive
-    to NCCL send/recv (torch.distributed) between the parties' GPUs.  Receives directly follow their sends in
-    the shared topological order, so all parties post matching transfers in the same order.
+    (moose/src/networking/mod.rs:16-54) is a hand-off keyed by the rendezvous key, like the reference's in-memory
+    LocalSyncNetworking (networking/local.rs:10-53);
+  * party per GPU: each process owns one role and one GPU, runs only that role's ops, and Send/Receive become NCCL
+    send/recv (torch.distributed) between the parties' GPUs, straight from / into the tensors' device memory.
+    Receives directly follow their sends in the shared topological order, so all parties post matching transfers
+    in the same order.
 """
 from __future__ import annotations
 
-from typing import Dict, List, Optional
+import ctypes
+from typing import Dict, List, Optional, Union
 
 import numpy as np
 
-from . import BIT, FLOAT64, RING64, RING128, Session, Tensor, lib, _P
-from .textual import Operation, attr_hex16, attr_int, attr_int_list, attr_slice, attr_str, parse_constant
-
-_RING_TYPES = {"HostRing64Tensor": RING64, "HostRing128Tensor": RING128, "Ring64Tensor": RING64, "Ring128Tensor": RING128}
-_BIT_TYPES = {"HostBitTensor", "BitTensor"}
+from . import Session, Tensor, lib
+from .textual import Operation, dumps_text
 
 
 class ExecutionError(RuntimeError):
@@ -108,6 +108,40 @@ class NcclComm:
         else:
             raise ExecutionError(f"cannot send value of type {type(value)}")
 
+    def transport(self, _user, is_send, peer, buf, nbytes, on_device):
+        """mb_transport_fn: raw buffers of the native executor.  Device payloads go straight from / into the
+        tensor's memory; host buffers (headers, keys, seeds) are staged through a small device tensor for NCCL."""
+        try:
+            t, other = self.torch, self.role_to_rank[peer.decode()]
+            if on_device:
+                view = t.as_tensor(_DeviceBytes(buf, nbytes), device=self.dev)
+                if is_send:
+                    self.dist.send(view, other)  # asynchronous on the NCCL stream; flush() before the memory is reused
+                else:
+                    # wait for THIS transfer only (not for the party's own kernels on the context's stream)
+                    self.dist.irecv(view, other).wait()
+                    done = t.cuda.Event()
+                    done.record()
+                    done.synchronize()
+                return 0
+            host = (ctypes.c_uint8 * nbytes).from_address(buf)
+            if is_send:
+                self.dist.send(t.frombuffer(bytearray(host), dtype=t.uint8).to(self.dev), other)
+            else:
+                staged = t.empty(nbytes, dtype=t.uint8, device=self.dev)
+                self.dist.recv(staged, other)
+                ctypes.memmove(buf, bytes(staged.cpu().numpy().tobytes()), nbytes)
+            return 0
+        except Exception as e:  # an exception must not cross the C boundary
+            import sys
+            print(f"transport error: {e!r}", file=sys.stderr, flush=True)
+            return 1
+
+    def flush(self):
+        """All posted transfers have completed (their buffers may be freed / reused afterwards)."""
+        if self.dev.type == "cuda":
+            self.torch.cuda.synchronize(self.dev)
+
     def recv(self, sender: str):
         t, src = self.torch, self.role_to_rank[sender]
         hdr = t.zeros(10, dtype=t.int64, device=self.dev)
@@ -133,186 +167,126 @@ class NcclComm:
         return None
 
 
+TRANSPORT_FN = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p, ctypes.c_void_p,
+                                ctypes.c_size_t, ctypes.c_int)
+
+
+class _DeviceBytes:
+    """Zero-copy view of `nbytes` of device memory for torch (CUDA array interface)."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+class _Values:
+    """Results of the executed operations by name (fetched from the native value store on demand)."""
+
+    def __init__(self, ex: "Executor"):
+        import weakref
+        self._ex = weakref.ref(ex)  # no reference cycle: dropping the executor frees its device tensors at once
+
+    def __getitem__(self, name: str):
+        ex = self._ex()
+        kind, rank, nbytes = ctypes.c_int(-1), ctypes.c_int(0), ctypes.c_size_t(0)
+        handle = ctypes.c_void_p()
+        buf = (ctypes.c_uint8 * 4096)()
+        shape = (ctypes.c_int64 * 6)()
+        ex.sess._check(lib().mb_exec_value(ex._exec, name.encode(), ctypes.byref(kind), ctypes.byref(handle), buf, 4096,
+                                           ctypes.byref(nbytes), shape, ctypes.byref(rank)))
+        if kind.value == 0:
+            return Tensor(ex.sess, handle.value)
+        if kind.value == 1:
+            return bytes(buf[:nbytes.value])
+        if kind.value == 2:
+            return tuple(int(shape[i]) for i in range(rank.value))
+        if kind.value == 4:
+            return bytes(buf[:nbytes.value]).decode()
+        if kind.value == 3:
+            return None
+        raise KeyError(f"{name} was not executed in this process")
+
+
 class Executor:
     def __init__(self, sess: Session, role: Optional[str] = None, comm: Optional[NcclComm] = None,
-                 overrides: Optional[Dict[str, object]] = None):
+                 overrides: Optional[Dict[str, Tensor]] = None, keep_values: bool = True):
         """`overrides` replaces the result of named ops (e.g. the Constant inputs of a compiled graph by larger
-        tensors of the same rank: lowered graphs are shape-agnostic)."""
-        self.sess, self.role, self.comm = sess, role, comm
+        tensors of the same rank: lowered graphs are shape-agnostic).  keep_values=False releases every intermediate
+        value after its last use (only outputs / saved values can be read afterwards)."""
+        self.sess, self.role, self.comm, self.keep_values = sess, role, comm, keep_values
         self.overrides = overrides or {}
-        self.values: Dict[str, object] = {}
-        self.outputs: Dict[str, object] = {}
-        self.saved: Dict[str, object] = {}
-        self.mailbox: Dict[str, object] = {}
+        self.values = _Values(self)
+        self.outputs: Dict[str, Tensor] = {}
+        self.saved: Dict[str, Tensor] = {}
         self.executed = 0
+        self._graph = ctypes.c_void_p()
+        self._exec = ctypes.c_void_p()
+        self._cb = None
+        if not hasattr(sess, "_children"):
+            import weakref
+            sess._children = weakref.WeakSet()
+        sess._children.add(self)
 
-    # -- helpers -------------------------------------------------------------------------------
-    def _dtype_of(self, ty: str) -> int:
-        if ty in _RING_TYPES:
-            return _RING_TYPES[ty]
-        if ty in _BIT_TYPES:
-            return BIT
-        raise ExecutionError(f"no device dtype for type {ty}")
+    def _free(self):
+        if not self.sess.ctx:  # the context is gone (and with it the stream the tensors would be freed on)
+            self._exec, self._graph = ctypes.c_void_p(), ctypes.c_void_p()
+            return
+        if self._exec:
+            lib().mb_exec_free(self._exec)
+            self._exec = ctypes.c_void_p()
+        if self._graph:
+            lib().mb_graph_free(self._graph)
+            self._graph = ctypes.c_void_p()
 
-    def _const(self, op: Operation):
-        ty, val = parse_constant(op.attrs["value"])
-        s = self.sess
-        if ty in ("HostFloat64Tensor", "Float64Tensor"):
-            return s.from_host(FLOAT64, np.array(val, dtype=np.float64))
-        if ty in _RING_TYPES:
-            return s.from_ints(_RING_TYPES[ty], val)
-        if ty in _BIT_TYPES:
-            return s.from_bits(np.array(val, dtype=np.uint8))
-        return val  # shapes, strings, keys, seeds, scalars
+    def close(self):
+        self.outputs, self.saved = {}, {}
+        self._free()
 
-    def _max_value(self, op: Operation):
-        return int(op.attrs["max_value"]) if "max_value" in op.attrs else None
+    def __del__(self):
+        try:
+            self._free()
+        except Exception:
+            pass
 
-    # -- one operation ----------------------------------------------------------------------------
-    def _execute(self, op: Operation, x: List[object]):
-        s, k = self.sess, op.kind
-        if k == "PrfKeyGen":
-            return s.gen_key()
-        if k == "DeriveSeed":
-            return s.derive_seed(attr_hex16(op, "sync_key"), x[0])
-        if k == "Constant":
-            return self._const(op)
-        if k == "Input":
-            raise ExecutionError("Input ops need `arguments`")
-        if k in ("Identity",):
-            return x[0]
-        if k == "RingFixedpointEncode":
-            if attr_int(op, "scaling_base") != 2:
-                raise ExecutionError("RingFixedpointEncode: only scaling_base = 2")
-            return s.fixedpoint_encode(self._dtype_of(op.output_type), attr_int(op, "scaling_exp"), x[0])
-        if k == "RingFixedpointDecode":
-            if attr_int(op, "scaling_base") != 2:
-                raise ExecutionError("RingFixedpointDecode: only scaling_base = 2")
-            return s.fixedpoint_decode(attr_int(op, "scaling_exp"), x[0])
-        if k == "Shape":
-            return tuple(x[0].shape)
-        if k == "Fill":
-            ty, val = parse_constant(op.attrs["value"])
-            return s.fill(self._dtype_of(op.output_type), int(val), x[0])
-        if k == "SampleSeeded":
-            return s.sample_uniform_seeded(self._dtype_of(op.output_type), x[0], x[1], self._max_value(op))
-        if k == "Sample":
-            return s.sample_uniform(self._dtype_of(op.output_type), x[0], self._max_value(op))
-        if k == "Add":
-            return s.add(x[0], x[1])
-        if k == "Sub":
-            return s.sub(x[0], x[1])
-        if k == "Mul":
-            return s.mul(x[0], x[1])
-        if k == "Dot":
-            return s.dot(x[0], x[1])
-        if k == "Neg":
-            return s.neg(x[0])
-        if k == "Shl":
-            return s.shl(attr_int(op, "amount"), x[0])
-        if k == "Shr":
-            return s.shr(attr_int(op, "amount"), x[0])
-        if k == "AddN":
-            return s.add_n(x)
-        if k == "Sum":
-            axis = op.attrs.get("axis")
-            return s.sum(x[0], None if axis in (None, "None") else int(axis))
-        if k == "Xor":
-            return s.xor(x[0], x[1])
-        if k == "And":
-            return s.and_(x[0], x[1])
-        if k == "Or":
-            return s.or_(x[0], x[1])
-        if k == "BitDecompose":
-            return s.bit_decompose(x[0]) if op.output_type in _BIT_TYPES else s.bit_decompose_ring(x[0])
-        if k == "BitExtract":
-            return s.bit_extract(attr_int(op, "bit_idx"), x[0])
-        if k == "RingInject":
-            return s.ring_inject(self._dtype_of(op.output_type), attr_int(op, "bit_idx"), x[0])
-        if k == "ShlDim":
-            return s.shl_dim(attr_int(op, "amount"), attr_int(op, "bit_length"), x[0])
-        if k == "IndexAxis":
-            return s.index_axis(attr_int(op, "axis"), attr_int(op, "index"), x[0])
-        if k == "ExpandDims":
-            return s.expand_dims(attr_int_list(op, "axis"), x[0])
-        if k == "Squeeze":
-            return s.squeeze(attr_int(op, "axis") if "axis" in op.attrs else None, x[0])
-        if k == "Transpose":
-            return s.transpose(x[0])
-        if k == "Concat":
-            return s.concat(attr_int(op, "axis"), x)
-        if k == "Slice":
-            info = attr_slice(op, "slice")
-            if isinstance(x[0], tuple):  # SliceOp::shape_kernel (host/ops.rs:537-546)
-                return tuple(x[0][info[0][0]:info[0][1]])
-            return s.slice(info, x[0])
-        if k == "Diag":
-            return s.diag(x[0])
-        if k == "Select":
-            return s.select(attr_int(op, "axis"), x[1], x[0])
-        if k == "Div":
-            return s.div(x[0], x[1])
-        if k == "Less":
-            return s.less(x[0], x[1])
-        if k == "Greater":
-            return s.greater(x[0], x[1])
-        if k == "Mux":
-            return s.host_mux(x[0], x[1], x[2])
-        if k == "Sign":
-            return s.sign(x[0])
-        if k == "Cast":
-            return s.cast_ring128_to_ring64(x[0])
-        if k == "Maximum":
-            return s.host_maximum(x)
-        if k == "RingFixedpointMean":
-            axis = attr_int(op, "axis") if "axis" in op.attrs else None
-            return s.fixedpoint_mean(axis, attr_int(op, "scaling_base"), attr_int(op, "scaling_exp"), x[0])
-        if k == "RingFixedpointArgmax":
-            return s.fixedpoint_argmax(attr_int(op, "axis"), x[0])
-        if k == "Reshape":
-            return s.reshape(x[0], x[1])
-        if k == "Broadcast":
-            return s.broadcast(x[1], x[0])
-        if k == "Output":
-            self.outputs[attr_str(op, "tag")] = x[0]
-            return x[0]
-        if k == "Save":
-            self.saved[x[0]] = x[1]
-            return None
-        raise ExecutionError(f"operator {k} is not part of the host-dialect subset built here")
+    def order(self) -> List[str]:
+        """Operation names in the native execution order."""
+        n = lib().mb_graph_num_ops(self._graph)
+        return [lib().mb_graph_op_name(self._graph, i).decode() for i in range(n)]
 
-    # -- whole computation --------------------------------------------------------------------------
-    def run(self, ops: List[Operation], arguments: Optional[Dict[str, object]] = None, keep_values: bool = True):
-        arguments = arguments or {}
-        for op in toposort(ops):
-            if op.placement_kind != "Host":
-                raise ExecutionError(f"{op.name}: only lowered graphs (@Host placements) can be replayed")
-            mine = self.role is None or op.owners[0] == self.role
-            if op.kind == "Send":
-                if mine:
-                    val = self.values[op.inputs[0]]
-                    if self.comm is not None:
-                        self.comm.send(val, attr_str(op, "receiver"))
-                    else:
-                        self.mailbox[op.attrs["rendezvous_key"]] = val
-                    self.values[op.name] = None
-                    self.executed += 1
-                continue
-            if op.kind == "Receive":
-                if mine:
-                    if self.comm is not None:
-                        self.values[op.name] = self.comm.recv(attr_str(op, "sender"))
-                    else:
-                        self.values[op.name] = self.mailbox.pop(op.attrs["rendezvous_key"])
-                    self.executed += 1
-                continue
-            if not mine:
-                continue
-            if op.name in self.overrides:
-                self.values[op.name] = self.overrides[op.name]
-            elif op.kind == "Input":
-                self.values[op.name] = arguments[attr_str(op, "arg_name")]
-            else:
-                self.values[op.name] = self._execute(op, [self.values[i] for i in op.inputs])
-            self.executed += 1
+    def load(self, ops: Union[str, List[Operation]]):
+        self._free()
+        text = ops if isinstance(ops, str) else dumps_text(ops)
+        self.sess._check(lib().mb_graph_parse(self.sess.ctx, text.encode(), ctypes.byref(self._graph)))
+        self.sess._check(lib().mb_exec_create(self.sess.ctx, self._graph, self.role.encode() if self.role else None,
+                                              ctypes.byref(self._exec)))
+        self.sess._check(lib().mb_exec_set_keep_values(self._exec, int(self.keep_values)))
+        if self.comm is not None:
+            self._cb = TRANSPORT_FN(self.comm.transport)
+            self.sess._check(lib().mb_exec_set_transport(self._exec, self._cb, None))
+        return self
+
+    def run(self, ops: Union[str, List[Operation], None] = None, arguments: Optional[Dict[str, Tensor]] = None):
+        if ops is not None:
+            self.load(ops)
+        for name, t in list(self.overrides.items()) + list((arguments or {}).items()):
+            self.sess._check(lib().mb_exec_bind_tensor(self._exec, name.encode(), t.h))
+        try:
+            self.sess._check(lib().mb_exec_run(self._exec))
+        except Exception as e:
+            raise ExecutionError(str(e)) from e
+        self.executed = int(lib().mb_exec_executed(self._exec))
+        self.transport_seconds = float(lib().mb_exec_seconds(self._exec, 0))
+        self.sync_seconds = float(lib().mb_exec_seconds(self._exec, 1))
+        if self.comm is not None:
+            self.comm.flush()
+            self.comm.bytes_sent += int(lib().mb_exec_bytes_sent(self._exec))
+        for saved, store in ((0, self.outputs), (1, self.saved)):
+            i = 0
+            while True:
+                key = lib().mb_exec_output_key(self._exec, saved, i)
+                if not key:
+                    break
+                h = ctypes.c_void_p()
+                self.sess._check(lib().mb_exec_output(self._exec, saved, key, ctypes.byref(h)))
+                store[key.decode()] = Tensor(self.sess, h.value)
+                i += 1
         return self.outputs

@@ -66,13 +66,18 @@ def main():
                 overrides[op.name] = sess.from_host(mb.FLOAT64, np.random.default_rng(100 + i).uniform(-1, 1, shapes[i]))
     dist.barrier()
     # one untimed run (NCCL connection setup, scratch growth), then the timed ones
-    Executor(sess, role=role, comm=comm, overrides=overrides).run(ops)
+    warm = Executor(sess, role=role, comm=comm, overrides=overrides, keep_values=False)
+    warm.run(ops)
+    warm.close()
     sess.sync()
     comm.bytes_sent = 0
     dist.barrier()
     outputs, t0 = {}, time.perf_counter()
+    ex = None
     for _ in range(args.repeat):
-        ex = Executor(sess, role=role, comm=comm, overrides=overrides)
+        if ex is not None:
+            ex.close()
+        ex = Executor(sess, role=role, comm=comm, overrides=overrides, keep_values=False)
         outputs = ex.run(ops)
         sess.sync()
     dt = (time.perf_counter() - t0) / args.repeat
@@ -93,7 +98,8 @@ def main():
         else:
             result[k] = v
     gathered = [None] * world
-    dist.all_gather_object(gathered, {"role": role, "executed": ex.executed, "outputs": result})
+    dist.all_gather_object(gathered, {"role": role, "executed": ex.executed, "transport_s": round(ex.transport_seconds, 4),
+                                      "stream_wait_s": round(ex.sync_seconds, 4), "outputs": result})
     if rank == 0:
         print(json.dumps({"mode": "party-per-gpu", "parties": roles, "transport": "nccl send/recv",
                           "ops": len(ops), "seconds_per_run": dt, "payload_bytes_per_run": int(sent[0]) // args.repeat,

@@ -35,6 +35,14 @@ class Operation:
         return [self.name, self.kind, self.attrs, self.input_types, int(self.variadic), self.output_type, self.inputs,
                 self.placement_kind, self.owners]
 
+    def to_text(self) -> str:
+        """One line of the textual format (the printer's layout, moose/src/textual/mod.rs)."""
+        attrs = "{" + ", ".join(f"{k} = {v}" for k, v in self.attrs.items()) + "}" if self.attrs else ""
+        types = ", ".join(self.input_types)
+        sig = f"[{types}]" if self.variadic else f"({types})"
+        return (f"{self.name} = {self.kind}{attrs}: {sig} -> {self.output_type} ({', '.join(self.inputs)}) "
+                f"@{self.placement_kind}({', '.join(self.owners)})")
+
     @staticmethod
     def from_json(row) -> "Operation":
         return Operation(row[0], row[1], row[2], row[3], bool(row[4]), row[5], row[6], row[7], row[8])
@@ -173,6 +181,10 @@ def parse_computation(text: str) -> List[Operation]:
             continue
         ops.append(parse_line(line))
     return ops
+
+
+def dumps_text(ops: List[Operation]) -> str:
+    return "\n".join(op.to_text() for op in ops) + "\n"
 
 
 def dumps_json(ops: List[Operation]) -> str:

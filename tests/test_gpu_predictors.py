@@ -74,12 +74,66 @@ def test_logreg_sigmoid_ring128_share_parity():
     g, o = mb.Session(0, SESSION_ID, ENTROPY_KEY), mo.Session(SESSION_ID, ENTROPY_KEY)
     try:
         pred = LinearPredictor(g, coeffs, intercepts, post_transform="sigmoid")
-        xb = np.concatenate([np.ones((batch, 1)), x], axis=1)
-        gout = pred.forward_shared(g.fixedpoint_encode(mb.RING128, 40, g.from_host(mb.FLOAT64, xb)))
+        gout = pred.forward_shared(pred.encode(x))
         oout, odec = po.linear(o, x, coeffs, intercepts, post_transform="sigmoid")
         assert same_rep(gout, oout)
         dec = g.fixedpoint_decode(40, g.reveal(gout)).to_host()
         ref = 1.0 / (1.0 + np.exp(-(x @ coeffs.T + intercepts)))
+        np.testing.assert_almost_equal(dec, ref, decimal=2)
+    finally:
+        g.close()
+
+
+@pytest.mark.parametrize("post,n_classes", [("softmax", 3), ("normalized_sigmoid", 3)])
+def test_linear_classifier_multiclass_share_parity(post, n_classes):
+    """LinearClassifier with SOFTMAX / multi-class SIGMOID (linear_predictor.py:160-175, 294-301), Ring128 fixed(24,40);
+    decimal=2 like the reference's predictor tests."""
+    rng = np.random.default_rng(11)
+    feats, batch = 16, 24
+    coeffs, intercepts = rng.normal(0, 0.5, (n_classes, feats)), rng.normal(0, 0.1, (1, n_classes))
+    x = rng.uniform(-1, 1, (batch, feats))
+    g, o = mb.Session(0, SESSION_ID, ENTROPY_KEY), mo.Session(SESSION_ID, ENTROPY_KEY)
+    try:
+        pred = LinearPredictor(g, coeffs, intercepts, post_transform=post)
+        gout = pred.forward_shared(pred.encode(x))
+        oout, _ = po.linear(o, x, coeffs, intercepts, post_transform=post)
+        assert same_rep(gout, oout)
+        dec = g.fixedpoint_decode(40, g.reveal(gout)).to_host()
+        z = x @ coeffs.T + intercepts
+        if post == "softmax":
+            e = np.exp(z - z.max(axis=1, keepdims=True))
+            ref = e / e.sum(axis=1, keepdims=True)
+        else:
+            sg = 1.0 / (1.0 + np.exp(-z))
+            ref = sg / sg.sum(axis=1, keepdims=True)
+        np.testing.assert_almost_equal(dec, ref, decimal=2)
+    finally:
+        g.close()
+
+
+@pytest.mark.parametrize("n_out", [1, 4])
+def test_mlp_classifier_ring128_share_parity(n_out):
+    """MLPClassifier post-transform (multilayer_perceptron_predictor.py:131-158): softmax over the classes, or
+    [1 - sigmoid, sigmoid] for a single output; Ring128 fixed(24,40)."""
+    rng = np.random.default_rng(12 + n_out)
+    dims = [12, 8, n_out]
+    ws = [rng.normal(0, dims[i] ** -0.5, (dims[i], dims[i + 1])) for i in range(2)]
+    bs = [rng.normal(0, 0.1, dims[i + 1]) for i in range(2)]
+    x = rng.uniform(0, 1, (10, dims[0]))
+    g, o = mb.Session(0, SESSION_ID, ENTROPY_KEY), mo.Session(SESSION_ID, ENTROPY_KEY)
+    try:
+        pred = MLPPredictor(g, ws, bs, mb.RING128, 40, integral=24, post_transform="classifier")
+        gout = pred.forward_shared(pred.encode(x))
+        oout, _ = po.mlp(o, x, ws, bs, 128, 40, integral=24, post_transform="classifier")
+        assert same_rep(gout, oout)
+        dec = g.fixedpoint_decode(40, g.reveal(gout)).to_host()
+        h = np.maximum(x @ ws[0] + bs[0], 0) @ ws[1] + bs[1]
+        if n_out == 1:
+            p = 1.0 / (1.0 + np.exp(-h))
+            ref = np.concatenate([1 - p, p], axis=1)
+        else:
+            e = np.exp(h - h.max(axis=1, keepdims=True))
+            ref = e / e.sum(axis=1, keepdims=True)
         np.testing.assert_almost_equal(dec, ref, decimal=2)
     finally:
         g.close()

@@ -81,3 +81,23 @@ def test_replay_host_tail_graph():
         assert np.array_equal(outs["mean"].to_host(), oouts["mean"])
     finally:
         sess.close()
+
+
+def test_replay_without_keeping_values():
+    """keep_values=False: intermediates are released after their last use; outputs are unchanged."""
+    ops = load("dotprod_networked")
+    sess = mb.Session(0, "replay", ENTROPY_KEY)
+    try:
+        full = Executor(sess)
+        want = full.run(ops)["output_0"].to_host()
+        full.close()
+        sess2 = mb.Session(0, "replay", ENTROPY_KEY)
+        lean = Executor(sess2, keep_values=False)
+        got = lean.run(ops)["output_0"].to_host()
+        assert np.array_equal(got, want) and lean.executed == len(ops)
+        with pytest.raises(KeyError):
+            lean.values["op_20"]
+        lean.close()
+        sess2.close()
+    finally:
+        sess.close()

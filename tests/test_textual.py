@@ -104,3 +104,24 @@ def test_host_tail_graph_on_oracle():
     assert vals["dg"].to_ints().tolist() == [int(1.5 * 65536), int(4.0 * 65536)]
     assert vals["either"].to_array().tolist() == [[1, 1, 1], [1, 1, 1]] and vals["nlt"].to_array().tolist() == [[1, 0, 1], [1, 1, 0]]
     assert vals["total"].to_ints().tolist() == int(np.abs(x).sum() * 65536)
+
+
+def test_native_parser_matches_python_order():
+    """The C++ reader / scheduler of libmoose_b200 (csrc/executor.cpp) against the Python one: same operation count
+    and the same execution order (Receive directly after its Send) on every fixture.  Parsing needs no GPU."""
+    import ctypes
+    import moose_b200 as mb
+    from _util import HOST_TAIL_GRAPH
+    lib = mb.lib()
+    graphs = [load(n) for n in ("dotprod_compiled", "dotprod_networked", "rep_computation")] + [tx.parse_computation(HOST_TAIL_GRAPH)]
+    for ops in graphs:
+        g = ctypes.c_void_p()
+        assert lib.mb_graph_parse(None, tx.dumps_text(ops).encode(), ctypes.byref(g)) == 0
+        n = lib.mb_graph_num_ops(g)
+        assert n == len(ops)
+        native = [lib.mb_graph_op_name(g, i).decode() for i in range(n)]
+        assert native == [op.name for op in toposort(ops)]
+        lib.mb_graph_free(g)
+    g = ctypes.c_void_p()
+    assert lib.mb_graph_parse(None, b"x = Add (a, b) @Host(alice)\n", ctypes.byref(g)) == -1
+    assert lib.mb_graph_parse(None, b"x = Add: (T, T) -> T (a, x) @Host(alice)\n", ctypes.byref(g)) == -1  # cycle
