@@ -379,6 +379,14 @@ int mb_rep_abs(mb_ctx *ctx, const mb_rep *x, mb_rep **out);
  * entries of `axis`, exp of the difference, entries below -ln 2^(i-1) forced to 0, division by the sum. */
 int mb_rep_softmax(mb_ctx *ctx, int axis, int upmost_index, uint32_t integral_precision,
                    uint32_t fractional_precision, const mb_rep *x, mb_rep **out);
+/* EqualOp::rep_kernel (moose/src/replicated/compare.rs:24-40): shared bit [x == y] = AND-tree over the negated
+ * bits of x - y (EqualZeroOp::bitdec_bit_kernel, compare.rs:53-72). */
+int mb_rep_equal(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out_bits);
+/* Log2Op / LogOp::rep_rep_kernel (moose/src/replicated/log.rs:13-111; Int2FL :166-219, P_2524 / Q_2524 rational
+ * approximation) and SqrtOp::rep_rep_kernel (moose/src/replicated/sqrt.rs:7-34: 2^(0.5 log2 x)); x > 0. */
+int mb_rep_log2(mb_ctx *ctx, uint32_t integral_precision, uint32_t fractional_precision, const mb_rep *x, mb_rep **out);
+int mb_rep_log(mb_ctx *ctx, uint32_t integral_precision, uint32_t fractional_precision, const mb_rep *x, mb_rep **out);
+int mb_rep_sqrt(mb_ctx *ctx, uint32_t integral_precision, uint32_t fractional_precision, const mb_rep *x, mb_rep **out);
 /* RingFixedpointArgmaxOp::rep_ring_kernel + TreeReduceArgmax (moose/src/replicated/argmax.rs:10-92): shared
  * Ring64 index of the maximum over the first `upmost_index` (<= 256) entries of `axis`. */
 int mb_rep_argmax(mb_ctx *ctx, int axis, int upmost_index, const mb_rep *x, mb_rep **out);

@@ -110,6 +110,8 @@ ABI = {
     "mb_rep_diag": [_P, _P, _PP], "mb_rep_concat": [_P, _I, _PP, _I, _PP], "mb_rep_add_n": [_P, _PP, _I, _PP],
     "mb_rep_sum": [_P, _P, _I, _PP], "mb_rep_cast_ring128_to_ring64": [_P, _P, _PP],
     "mb_rep_fixedpoint_mean": [_P, _I, _U64, _U32, _P, _PP], "mb_rep_abs": [_P, _P, _PP],
+    "mb_rep_equal": [_P, _P, _P, _PP], "mb_rep_log2": [_P, _U32, _U32, _P, _PP], "mb_rep_log": [_P, _U32, _U32, _P, _PP],
+    "mb_rep_sqrt": [_P, _U32, _U32, _P, _PP],
     "mb_rep_softmax": [_P, _I, _I, _U32, _U32, _P, _PP], "mb_rep_argmax": [_P, _I, _I, _P, _PP],
     "mb_graph_parse": [_P, ctypes.c_char_p, _PP], "mb_graph_free": [_P], "mb_graph_num_ops": [_P],
     "mb_graph_op_name": [_P, _I64], "mb_exec_create": [_P, _P, ctypes.c_char_p, _PP], "mb_exec_free": [_P],
@@ -668,6 +670,10 @@ class Session:
     def rep_pow2(self, i_prec, f_prec, x): return self._fixed_unary(lib().mb_rep_pow2, i_prec, f_prec, x)
     def rep_exp(self, i_prec, f_prec, x): return self._fixed_unary(lib().mb_rep_exp, i_prec, f_prec, x)
     def sigmoid(self, i_prec, f_prec, x): return self._fixed_unary(lib().mb_rep_sigmoid, i_prec, f_prec, x)
+    def rep_log2(self, i_prec, f_prec, x): return self._fixed_unary(lib().mb_rep_log2, i_prec, f_prec, x)
+    def rep_log(self, i_prec, f_prec, x): return self._fixed_unary(lib().mb_rep_log, i_prec, f_prec, x)
+    def rep_sqrt(self, i_prec, f_prec, x): return self._fixed_unary(lib().mb_rep_sqrt, i_prec, f_prec, x)
+    def rep_equal(self, x, y): return self._rbin(lib().mb_rep_equal, x, y)
 
     # share-wise shape / reduction operators (replicated/ops.rs, arith.rs:123-195)
     def rep_index_axis(self, axis: int, index: int, x) -> RepTensor:

@@ -188,15 +188,19 @@ const double P_1045[100] = {
 };
 
 // PolynomialEval::polynomial_eval (fixedpoint/mod.rs:95-151); x has fractional precision f_prec
-R polynomial_eval(mb_ctx *c, int f_prec, const R &x) {
+R polynomial_eval(mb_ctx *c, int f_prec, const double *coeff, int ncoeff, const R &x) {
   const int bits = bits_of(x);
-  int degree = 99;
-  for (int i = 99; i >= 0; i--) {
-    if (P_1045[i] < std::ldexp(1.0, -(f_prec + 1))) degree--;
+  int degree = ncoeff - 1;
+  for (int i = ncoeff - 1; i >= 0; i--) {
+    if (coeff[i] < std::ldexp(1.0, -(f_prec + 1))) degree--;
     else break;
   }
+  if (degree < 1) {
+    mb_fail(c, MB_ERR_INVALID_ARGUMENT, "polynomial_eval: no coefficient above the precision");
+    throw Err{MB_ERR_INVALID_ARGUMENT};
+  }
   std::vector<T> coeffs;
-  for (int i = 0; i <= degree; i++) coeffs.push_back(pub_fill(c, x.like(), fixed_constant(bits, P_1045[i], (unsigned)f_prec)));
+  for (int i = 0; i <= degree; i++) coeffs.push_back(pub_fill(c, x.like(), fixed_constant(bits, coeff[i], (unsigned)f_prec)));
   std::vector<R> pre;
   for (int i = 0; i < degree; i++) pre.push_back(x.clone());
   prefix_op(pre, [&](const R &a, const R &b) { return trunc(c, (uint32_t)f_prec, mul(c, a, b)); });
@@ -205,6 +209,7 @@ R polynomial_eval(mb_ctx *c, int f_prec, const R &x) {
   acc = trunc(c, (uint32_t)f_prec, acc);
   return add_pub(c, acc, coeffs[0]);
 }
+R polynomial_eval(mb_ctx *c, int f_prec, const R &x) { return polynomial_eval(c, f_prec, P_1045, 100, x); }
 
 // Pow2FromBits (exp.rs:124-157)
 R pow2_from_bits(mb_ctx *c, const std::vector<R> &xs, int count) {
@@ -270,6 +275,88 @@ R rep_sigmoid(mb_ctx *c, int i_prec, int f_prec, const R &x) {
   R upper_wall = mux(c, upper_ring, ones_rep, output);
   R lower_ring = inject(c, ring, 0, greater(c, neg(c, max_val_rep), x));
   return mux(c, lower_ring, zeros_rep, upper_wall);
+}
+
+// xor(ones, x) on shared bits: a public value is added to share 0 only (arith.rs:39-79)
+R not_bits(mb_ctx *c, const R &x) {
+  mb_tensor *n = nullptr;
+  ck(mb_neg(c, x.p->s[0], &n));
+  T tn(c, n);
+  mb_rep *q = nullptr;
+  ck(mb_rep_from_shares(c, n, x.p->s[1], x.p->s[2], &q));
+  return R(c, q);
+}
+
+// EqualZeroOp::bitdec_bit_kernel (compare.rs:53-72): tree_reduce (misc.rs:54-74) of AND over the negated bits
+R and_tree(mb_ctx *c, std::vector<R> &v, size_t lo, size_t hi) {
+  if (hi - lo == 1) return v[lo].clone();
+  const size_t mid = lo + (hi - lo) / 2;
+  R a = and_tree(c, v, lo, mid);
+  R b = and_tree(c, v, mid, hi);
+  return mul(c, a, b);
+}
+R equal_zero(mb_ctx *c, const R &x_bits, int nbits) {
+  std::vector<R> v_not;
+  for (int i = 0; i < nbits; i++) v_not.push_back(not_bits(c, index0(c, i, x_bits)));
+  return and_tree(c, v_not, 0, v_not.size());
+}
+
+// EqualOp::rep_kernel (compare.rs:24-40)
+R rep_equal(mb_ctx *c, const R &x, const R &y) { return equal_zero(c, bitdec(c, sub(c, x, y)), bits_of(x)); }
+
+R sub_pub(mb_ctx *c, const R &a, const T &pub) { mb_rep *q = nullptr; ck(mb_rep_sub_public(c, a.p, pub.p, &q)); return R(c, q); }
+
+// Int2FL::int2fl (log.rs:166-219): v, p with (1 - 2s)(1 - z) v 2^p = x
+void int2fl(mb_ctx *c, const R &x, int max_bit_len, int f_prec, R &v_out, R &p_out) {
+  const int bits = bits_of(x);
+  const mb_dtype ring = ring_of(x);
+  const int lam = max_bit_len - 1;
+  R x_bits = bitdec(c, x);
+  R sign = inject(c, ring, 0, index0(c, bits - 1, x_bits));
+  R is_zero = inject(c, ring, 0, equal_zero(c, x_bits, bits));
+  R x_pos = mux(c, sign, neg(c, x), x);
+  R x_pos_bits = bitdec(c, x_pos);
+  std::vector<R> b;
+  for (int i = lam - 1; i >= 0; i--) b.push_back(index0(c, i, x_pos_bits));
+  prefix_op(b, [&](const R &p, const R &q) { return add(c, add(c, p, q), mul(c, p, q)); });  // prefix_or (misc.rs:30-40)
+  std::vector<R> b_ring;
+  for (int i = 0; i < lam; i++) b_ring.push_back(inject(c, ring, 0, b[i]));
+  T ones = pub_fill(c, x.like(), 1);
+  R neg_b_sum = rep_fill(c, x.like(), 0);
+  for (int i = 0; i < lam; i++) neg_b_sum = add(c, neg_b_sum, shl(c, (uint64_t)i, pub_sub(c, ones, b_ring[i])));
+  R x_upshifted = mul(c, x_pos, add_pub(c, neg_b_sum, ones));
+  v_out = trunc(c, (uint32_t)(max_bit_len - 1 - f_prec), x_upshifted);
+  R bit_count = rep_fill(c, x.like(), 0);
+  for (int i = 0; i < lam; i++) bit_count = add(c, bit_count, b_ring[i]);
+  T ften = pub_fill(c, x.like(), (u128)(uint8_t)f_prec);
+  p_out = mul(c, sub_pub(c, bit_count, ften), pub_sub(c, ones, is_zero));
+}
+
+const double P_2524[4] = {-2.05466671951, -8.8626599391, 6.10585199015, 4.81147460989};  // log.rs:10
+const double Q_2524[4] = {0.353553425277, 4.54517087629, 6.42784209029, 1.0};             // log.rs:11
+
+// Log2Op::rep_rep_kernel (log.rs:13-82)
+R rep_log2(mb_ctx *c, int i_prec, int f_prec, const R &x) {
+  R v(c, nullptr), p(c, nullptr);
+  int2fl(c, x, i_prec + f_prec, f_prec, v, p);
+  R p2524 = polynomial_eval(c, f_prec, P_2524, 4, v);
+  R q2524 = polynomial_eval(c, f_prec, Q_2524, 4, v);
+  R quotient = rep_div(c, i_prec, f_prec, p2524, q2524);
+  return add(c, shl(c, (uint64_t)f_prec, p), quotient);
+}
+
+// LogOp::rep_rep_kernel (log.rs:84-111)
+R rep_log(mb_ctx *c, int i_prec, int f_prec, const R &x) {
+  T ln2 = pub_fill(c, x.like(), fixed_constant(bits_of(x), std::log(2.0), (unsigned)f_prec));
+  return trunc(c, (uint32_t)f_prec, mul_pub(c, rep_log2(c, i_prec, f_prec, x), ln2));
+}
+
+// SqrtOp::rep_rep_kernel (sqrt.rs:7-34): 2^(0.5 * log2 x)
+R rep_sqrt(mb_ctx *c, int i_prec, int f_prec, const R &x) {
+  R log2_x = rep_log2(c, i_prec, f_prec, x);
+  T half = pub_fill(c, x.like(), fixed_constant(bits_of(x), 0.5, (unsigned)f_prec));
+  R exponent = trunc(c, (uint32_t)f_prec, mul_pub(c, log2_x, half));
+  return rep_pow2(c, i_prec, f_prec, exponent);
 }
 
 // share-wise helpers (rep_shape.cpp)
@@ -451,3 +538,26 @@ extern "C" int mb_rep_argmax(mb_ctx *ctx, int axis, int upmost_index, const mb_r
     return (int)MB_OK;
   });
 }
+
+extern "C" int mb_rep_equal(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out_bits) {
+  return guarded(ctx, "mb_rep_equal", [&]() {
+    if (!valid(x) || !valid(y) || !out_bits) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_rep_equal: NULL argument");
+    if (!mb_is_ring(x->s[0]->dtype) || x->s[0]->dtype != y->s[0]->dtype) return mb_fail(ctx, MB_ERR_TYPE_MISMATCH, "mb_rep_equal: needs ring shares of one width");
+    R r = rep_equal(ctx, borrow(ctx, x), borrow(ctx, y));
+    *out_bits = r.release();
+    return (int)MB_OK;
+  });
+}
+#define MB_FIXED_UNARY(NAME, FN)                                                                                             \
+  extern "C" int NAME(mb_ctx *ctx, uint32_t i_prec, uint32_t f_prec, const mb_rep *x, mb_rep **out) {                      \
+    return guarded(ctx, #NAME, [&]() {                                                                                      \
+      MB_CHECK(check_fixed(ctx, x, i_prec, f_prec, #NAME));                                                                 \
+      if (!out) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, #NAME ": NULL out");                                           \
+      R r = FN(ctx, (int)i_prec, (int)f_prec, borrow(ctx, x));                                                              \
+      *out = r.release();                                                                                                   \
+      return (int)MB_OK;                                                                                                    \
+    });                                                                                                                     \
+  }
+MB_FIXED_UNARY(mb_rep_log2, rep_log2)
+MB_FIXED_UNARY(mb_rep_log, rep_log)
+MB_FIXED_UNARY(mb_rep_sqrt, rep_sqrt)

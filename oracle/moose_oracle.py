@@ -1529,3 +1529,86 @@ def rep_abs(sess, x: RepTensor) -> RepTensor:
 def rep_add_n(xs) -> RepTensor:
     """AddNOp::rep_kernel (replicated/arith.rs:123-165)."""
     return RepTensor([[add_n([t.shares[i][j] for t in xs]) for j in range(2)] for i in range(3)])
+
+
+# -- equality, int2fl, log2 / ln / sqrt (replicated/compare.rs, log.rs, sqrt.rs) -------------------------
+
+P_2524 = [-2.05466671951, -8.8626599391, 6.10585199015, 4.81147460989]   # log.rs:10
+Q_2524 = [0.353553425277, 4.54517087629, 6.42784209029, 1.0]             # log.rs:11
+
+
+def rep_not_bits(x: RepTensor) -> RepTensor:
+    """xor(ones_mirrored, x) on shared bits (Z2 add of a public value touches share 0 only, arith.rs:39-79)."""
+    (x00, x10), (x11, x21), (x22, x02) = x.shares
+    return RepTensor([[neg(x00), x10], [x11, x21], [x22, neg(x02)]])
+
+
+def rep_equal_zero(sess, x_bits: RepTensor, nbits: int) -> RepTensor:
+    """EqualZeroOp::bitdec_bit_kernel (compare.rs:53-72): AND-tree over the negated bits."""
+    v_not = [rep_not_bits(rep_index(i, x_bits)) for i in range(nbits)]
+
+    def tree(v):
+        if len(v) == 1:
+            return v[0]
+        a, b = tree(v[: len(v) // 2]), tree(v[len(v) // 2:])
+        return rep_and(sess, a, b)
+
+    return tree(v_not)
+
+
+def rep_equal(sess, x: RepTensor, y: RepTensor) -> RepTensor:
+    """EqualOp::rep_kernel (compare.rs:24-40): equal_zero(bit_decompose(x - y))."""
+    bits = x.shares[0][0].bits
+    return rep_equal_zero(sess, rep_bit_decompose(sess, rep_sub(x, y)), bits)
+
+
+def int2fl(sess, x: RepTensor, max_bit_len: int, f_prec: int):
+    """Int2FL::int2fl (log.rs:166-219): v, p, s, z with (1 - 2s)(1 - z) v 2^p = x."""
+    bits = x.shares[0][0].bits
+    lam = max_bit_len - 1
+    x_bits = rep_bit_decompose(sess, x)
+    sign = rep_ring_inject(sess, bits, 0, rep_index(bits - 1, x_bits))            # MsbOp::rep_bit_dec_kernel
+    is_zero = rep_ring_inject(sess, bits, 0, rep_equal_zero(sess, x_bits, bits))  # EqualZeroOp::bitdec_ring_kernel
+    x_pos = rep_mux(sess, sign, rep_neg(x), x)
+    x_pos_bits = rep_bit_decompose(sess, x_pos)
+    rev = [rep_index(i, x_pos_bits) for i in range(lam)][::-1]
+    b = prefix_or(sess, rev)
+    b_ring = [rep_ring_inject(sess, bits, 0, b[i]) for i in range(lam)]
+    ones = mir_fill(bits, 1, x.shape)
+    zero = rep_fill(bits, 0, x.shape)
+    neg_b_sum = zero
+    for i in range(lam):
+        neg_b_sum = rep_add(neg_b_sum, rep_shl(i, rep_mir_sub(ones, b_ring[i])))
+    x_upshifted = rep_mul(sess, x_pos, rep_mir_add(ones, neg_b_sum))
+    x_norm = rep_trunc_pr(sess, max_bit_len - 1 - f_prec, x_upshifted)
+    bit_count = zero
+    for i in range(lam):
+        bit_count = rep_add(bit_count, b_ring[i])
+    ften = mir_fill(bits, f_prec, x.shape)
+    p_res = rep_mul(sess, rep_sub_mir(bit_count, ften), rep_mir_sub(ones, is_zero))
+    return x_norm, p_res, sign, is_zero
+
+
+def rep_log2(sess, i_prec: int, f_prec: int, x: RepTensor) -> RepTensor:
+    """Log2Op::rep_rep_kernel (log.rs:13-82)."""
+    v, p, _s, _z = int2fl(sess, x, i_prec + f_prec, f_prec)
+    p2524 = polynomial_eval(sess, f_prec, P_2524, v)
+    q2524 = polynomial_eval(sess, f_prec, Q_2524, v)
+    quotient = rep_div(sess, i_prec, f_prec, p2524, q2524)
+    return rep_add(rep_shl(f_prec, p), quotient)
+
+
+def rep_log(sess, i_prec: int, f_prec: int, x: RepTensor) -> RepTensor:
+    """LogOp::rep_rep_kernel (log.rs:84-111): ln 2 * log2(x)."""
+    bits = x.shares[0][0].bits
+    ln2 = mir_fill(bits, fixed_constant(bits, math.log(2.0), f_prec), x.shape)
+    return rep_trunc_pr(sess, f_prec, rep_mir_mul(ln2, rep_log2(sess, i_prec, f_prec, x)))
+
+
+def rep_sqrt(sess, i_prec: int, f_prec: int, x: RepTensor) -> RepTensor:
+    """SqrtOp::rep_rep_kernel (sqrt.rs:7-34): 2^(0.5 log2 x)."""
+    bits = x.shares[0][0].bits
+    log2_x = rep_log2(sess, i_prec, f_prec, x)
+    half = mir_fill(bits, fixed_constant(bits, 0.5, f_prec), x.shape)
+    exponent = rep_trunc_pr(sess, f_prec, rep_mir_mul(half, log2_x))
+    return rep_pow2(sess, i_prec, f_prec, exponent)

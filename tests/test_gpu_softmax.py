@@ -120,3 +120,38 @@ def test_abs_and_sharewise_ops(bits):
     if bits == 128:
         assert same_rep(g.rep_cast_ring128_to_ring64(gy), mo.rep_cast_64(oy))
     g.close()
+
+
+def test_equal_reference_vector():
+    """compare.rs:183-203 (test_equal)."""
+    g, o = pair()
+    gx, ox = shared_ints(g, o, 64, [1024, 5, 4])
+    ry = mo.Ring.from_ints(64, [1024, 4, 5])
+    gy, oy = g.share(g.from_host(RING64, ry.data), 1), mo.rep_share(o, ry, 1)
+    ge, oe = g.rep_equal(gx, gy), mo.rep_equal(o, ox, oy)
+    assert same_rep(ge, oe) and g.reveal(ge).bits().tolist() == [1, 0, 0]
+    g.close()
+
+
+LOG_CASES = [
+    # (bits, i, f, fn, tolerance, x)   -- log.rs:258-298 and :330-432
+    (64, 8, 20, "log2", 0.01, [1.0, 2.0, 4.0, 8.0, 4.5, 10.5]),
+    (128, 10, 30, "log2", 0.01, [[1.0, 2.0, 4.0], [8.0, 4.5, 10.5]]),
+    (64, 8, 20, "log", 0.01, [1.0, 2.5, 3.0, 4.0, 5.0]),
+    (128, 10, 30, "log", 0.001, [[1.0, 2.5, 3.0, 4.0, 5.0]]),
+    (128, 10, 30, "sqrt", 0.001, [0.25, 1.0, 2.0, 9.0, 100.0]),
+    (64, 8, 20, "sqrt", 0.02, [0.25, 1.0, 2.0, 9.0]),
+]
+
+
+@pytest.mark.parametrize("bits,i_p,f_p,fn,tol,x", LOG_CASES)
+def test_log_sqrt(bits, i_p, f_p, fn, tol, x):
+    g, o = pair()
+    x = np.array(x, dtype=np.float64)
+    gx, ox = shared(g, o, bits, f_p, x)
+    gz = getattr(g, "rep_" + fn)(i_p, f_p, gx)
+    oz = getattr(mo, "rep_" + fn)(o, i_p, f_p, ox)
+    assert same_rep(gz, oz)
+    got = g.fixedpoint_decode(f_p, g.reveal(gz)).to_host()
+    assert np.abs(got - getattr(np, fn)(x)).max() < tol
+    g.close()

@@ -196,3 +196,23 @@ def test_softmax_argmax_reference_vectors():
     for bits, axis, upmost, vals, expect in cases:
         r = mo.rep_reveal(mo.rep_argmax(s, axis, upmost, mo.rep_share(s, mo.Ring.from_ints(bits, vals), 0)))
         assert r.bits == 64 and r.to_ints().tolist() == expect
+
+
+def test_int2fl_equal_log_sqrt_reference_vectors():
+    """replicated/log.rs:300-328 (test_int2fl: (1-2s)(1-z) v 2^p == x exactly), compare.rs:183-203 (test_equal),
+    log.rs:330-432 (log2 / ln within 0.01 on Ring64 fixed(8,20), 0.01 / 0.001 on Ring128 fixed(10,30))."""
+    s = mo.Session("kat", bytes(range(16)))
+    x = mo.Ring.from_ints(64, [2, 10, 32, 0, -4])
+    v, p, sg, z = (mo.rep_reveal(t).to_ints() for t in mo.int2fl(s, mo.rep_share(s, x, 0), 32, 5))
+    sgn = lambda a: [int(t) - (1 << 64) if int(t) >> 63 else int(t) for t in a]
+    v, p, sg, z = sgn(v), sgn(p), sgn(sg), sgn(z)
+    assert [(1 - 2 * sg[i]) * (1 - z[i]) * v[i] * 2.0 ** p[i] for i in range(5)] == [2.0, 10.0, 32.0, 0.0, -4.0]
+    a = mo.rep_share(s, mo.Ring.from_ints(64, [1024, 5, 4]), 0)
+    b = mo.rep_share(s, mo.Ring.from_ints(64, [1024, 4, 5]), 1)
+    assert mo.rep_reveal(mo.rep_equal(s, a, b)).to_array().tolist() == [1, 0, 0]
+    xs = np.array([1.0, 2.0, 4.0, 8.0, 4.5, 10.5])
+    X = mo.rep_share(s, mo.fixed_encode(64, xs, 20), 0)
+    assert np.abs(mo.fixed_decode(mo.rep_reveal(mo.rep_log2(s, 8, 20, X)), 20) - np.log2(xs)).max() < 0.01
+    xs = np.array([1.0, 2.5, 3.0, 4.0, 5.0])
+    X = mo.rep_share(s, mo.fixed_encode(128, xs, 30), 0)
+    assert np.abs(mo.fixed_decode(mo.rep_reveal(mo.rep_log(s, 10, 30, X)), 30) - np.log(xs)).max() < 0.001
