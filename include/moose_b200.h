@@ -391,6 +391,22 @@ int mb_rep_sqrt(mb_ctx *ctx, uint32_t integral_precision, uint32_t fractional_pr
  * Ring64 index of the maximum over the first `upmost_index` (<= 256) entries of `axis`. */
 int mb_rep_argmax(mb_ctx *ctx, int axis, int upmost_index, const mb_rep *x, mb_rep **out);
 
+/* ------------------------------------------------------------------ storage */
+
+/* .npy / .csv files straight into device tensors (LoadOp / SaveOp of moose/src/host/ops.rs:193-225 over
+ * moose/src/storage/filesystem/numpy.rs:8-140 and csv.rs:10-140).  Files are streamed through page-locked
+ * staging buffers; little-endian C-order <f8 <f4 <i8 <i4 <u8 <u4 are read (the types read_numpy accepts) and
+ * widened to float64 on the device.  mb_load_npy_fixed additionally applies RingFixedpointEncode (2^frac) chunk
+ * by chunk, so an 8 GB input never exists as a second host copy or as a full float64 image in HBM. */
+int mb_load_npy(mb_ctx *ctx, const char *path, mb_tensor **out);
+int mb_load_npy_fixed(mb_ctx *ctx, const char *path, mb_dtype ring, uint32_t frac, mb_tensor **out);
+/* float64 tensors are written as <f8, ring64 tensors as <u8 (HostUint64Tensor in the reference). */
+int mb_save_npy(mb_ctx *ctx, const mb_tensor *t, const char *path);
+/* read_csv: header row, records parsed to f64, `columns` selects by header name (ncolumns = 0: all). */
+int mb_load_csv(mb_ctx *ctx, const char *path, const char *const *columns, int ncolumns, mb_tensor **out);
+/* write_csv: header col_0 .. col_{n-1}, one record per row. */
+int mb_save_csv(mb_ctx *ctx, const mb_tensor *t, const char *path);
+
 /* ------------------------------------------------------------ graph replay */
 
 /* Reader for Moose's textual computation format, host dialect (grammar of moose/src/textual/parsing.rs), and a

@@ -113,6 +113,9 @@ ABI = {
     "mb_rep_equal": [_P, _P, _P, _PP], "mb_rep_log2": [_P, _U32, _U32, _P, _PP], "mb_rep_log": [_P, _U32, _U32, _P, _PP],
     "mb_rep_sqrt": [_P, _U32, _U32, _P, _PP],
     "mb_rep_softmax": [_P, _I, _I, _U32, _U32, _P, _PP], "mb_rep_argmax": [_P, _I, _I, _P, _PP],
+    "mb_load_npy": [_P, ctypes.c_char_p, _PP], "mb_load_npy_fixed": [_P, ctypes.c_char_p, _I, _U32, _PP],
+    "mb_save_npy": [_P, _P, ctypes.c_char_p], "mb_load_csv": [_P, ctypes.c_char_p, _PP, _I, _PP],
+    "mb_save_csv": [_P, _P, ctypes.c_char_p],
     "mb_graph_parse": [_P, ctypes.c_char_p, _PP], "mb_graph_free": [_P], "mb_graph_num_ops": [_P],
     "mb_graph_op_name": [_P, _I64], "mb_exec_create": [_P, _P, ctypes.c_char_p, _PP], "mb_exec_free": [_P],
     "mb_exec_set_transport": [_P, _P, _P], "mb_exec_bind_tensor": [_P, ctypes.c_char_p, _P], "mb_exec_run": [_P], "mb_exec_set_keep_values": [_P, _I],
@@ -579,6 +582,25 @@ class Session:
     def fixedpoint_argmax(self, axis: int, x: Tensor) -> Tensor:
         out = self._out()
         return self._t(lib().mb_fixedpoint_argmax(self.ctx, axis, x.h, ctypes.byref(out)), out)
+
+    # -- storage (LoadOp / SaveOp) ------------------------------------------------
+    def load_npy(self, path: str, ring: Optional[int] = None, frac: int = 0) -> Tensor:
+        """float64 tensor, or (ring given) the fixed-point encoding computed while the file streams in."""
+        out = self._out()
+        if ring is None:
+            return self._t(lib().mb_load_npy(self.ctx, path.encode(), ctypes.byref(out)), out)
+        return self._t(lib().mb_load_npy_fixed(self.ctx, path.encode(), ring, frac, ctypes.byref(out)), out)
+
+    def save_npy(self, x: Tensor, path: str):
+        self._check(lib().mb_save_npy(self.ctx, x.h, path.encode()))
+
+    def load_csv(self, path: str, columns: Sequence[str] = ()) -> Tensor:
+        arr = (ctypes.c_char_p * max(len(columns), 1))(*[c.encode() for c in columns])
+        out = self._out()
+        return self._t(lib().mb_load_csv(self.ctx, path.encode(), ctypes.cast(arr, _PP), len(columns), ctypes.byref(out)), out)
+
+    def save_csv(self, x: Tensor, path: str):
+        self._check(lib().mb_save_csv(self.ctx, x.h, path.encode()))
 
     # -- ReplicatedPlacement kernels ---------------------------------------------
     def rep_setup(self):

@@ -121,6 +121,7 @@ int k_broadcast(mb_ctx *ctx, const mb_tensor *x, mb_tensor *out);
 int k_sum_axis(mb_ctx *ctx, const mb_tensor *x, int64_t outer, int64_t len, int64_t inner, mb_tensor *out);
 int k_fixed_encode(mb_ctx *ctx, const mb_tensor *x, double scale, mb_tensor *out);
 int k_fixed_decode(mb_ctx *ctx, const mb_tensor *x, double scale, mb_tensor *out);
+int k_fixed_encode_raw(mb_ctx *ctx, const double *x_dev, mb_dtype ring, void *out_dev, int64_t n, double scale);
 
 int k_sample(mb_ctx *ctx, const AesKey &key, mb_tensor *out, bool bits_as_ring);
 

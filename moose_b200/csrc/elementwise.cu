@@ -375,6 +375,18 @@ int k_fixed_encode(mb_ctx *ctx, const mb_tensor *x, double scale, mb_tensor *out
   return MB_OK;
 }
 
+// raw-pointer form for callers that encode a tensor piece by piece (storage.cu)
+int k_fixed_encode_raw(mb_ctx *ctx, const double *x_dev, mb_dtype ring, void *out_dev, int64_t n, double scale) {
+  if (n == 0) return MB_OK;
+  unsigned g = grid_for(n, TPB);
+  if (ring == MB_RING128)
+    fixed_encode_kernel<u128><<<g, TPB, 0, ctx->stream>>>(x_dev, (u128 *)out_dev, n, scale);
+  else
+    fixed_encode_kernel<uint64_t><<<g, TPB, 0, ctx->stream>>>(x_dev, (uint64_t *)out_dev, n, scale);
+  MB_LAUNCH_CHECK(ctx);
+  return MB_OK;
+}
+
 int k_fixed_decode(mb_ctx *ctx, const mb_tensor *x, double scale, mb_tensor *out) {
   if (out->numel == 0) return MB_OK;
   unsigned g = grid_for(out->numel, TPB);

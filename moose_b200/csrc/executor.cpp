@@ -712,6 +712,19 @@ struct Runner {
       e->outputs[tag ? unquote(*tag) : op.name] = idx;
       return copy(in(op, 0));
     }
+    if (k == "Load") {
+      // LoadOp (host/ops.rs:193-208): key (and a column query for csv); bound values stand for in-memory storage
+      const Val &key = in(op, 0);
+      if (key.kind != V_STRING) fail(MB_ERR_TYPE_MISMATCH, op.name + ": Load key is not a string");
+      auto it = e->bound.find(key.str);
+      if (it != e->bound.end()) return copy(it->second);
+      const std::string &p = key.str;
+      if (dtype_of(op.out_type) != MB_FLOAT64) fail(MB_ERR_UNIMPLEMENTED, op.name + ": file storage yields HostFloat64Tensor");
+      if (p.size() > 4 && p.compare(p.size() - 4, 4, ".npy") == 0) ck(mb_load_npy(c, p.c_str(), &t));
+      else if (p.size() > 4 && p.compare(p.size() - 4, 4, ".csv") == 0) ck(mb_load_csv(c, p.c_str(), nullptr, 0, &t));
+      else fail(MB_ERR_KERNEL, "key must provide an extension of either '.csv' or '.npy', got: " + p);
+      return tval(t);
+    }
     if (k == "Save") {
       const Val &key = in(op, 0);
       if (key.kind != V_STRING) fail(MB_ERR_TYPE_MISMATCH, op.name + ": Save key is not a string");
