@@ -425,11 +425,16 @@ const char *mb_graph_op_name(const mb_graph *g, int64_t i);
  * role != NULL: run only the operations placed on `role`; Send/Receive go through the transport. */
 int mb_exec_create(mb_ctx *ctx, const mb_graph *g, const char *role, mb_exec **out);
 int mb_exec_free(mb_exec *e);
-/* Transport for Send / Receive (moose/src/networking/mod.rs:16-54) in party-per-process mode.  The executor
- * calls it once for a 10-word int64 header in host memory (kind, dtype, rank, shape[6], payload bytes) and once
- * more for the payload; tensor payloads are DEVICE memory (on_device = 1), keys / seeds / strings host memory.
+/* Transport for Send / Receive (moose/src/networking/mod.rs:16-54) in party-per-process mode.  `mode`:
+ *   1 send / 0 receive `nbytes` at `buf` to / from `peer_role`.  The executor calls it once for a 10-word int64
+ *     header in host memory (kind, dtype, rank, shape[6], payload bytes) and once more for the payload; tensor
+ *     payloads are DEVICE memory (on_device = 1), keys / seeds / strings host memory.  A receive returns when the
+ *     data is there; a send of device memory may return while the transfer is in flight -- the executor keeps the
+ *     tensor referenced until the transport reports it complete:
+ *   2 poll: write to *(int64_t *)buf the number of device sends completed so far (in posting order);
+ *   3 flush: wait for all posted sends, then report like 2.
  * Return 0 on success.  The caller binds it to NCCL send/recv between the parties' GPUs. */
-typedef int (*mb_transport_fn)(void *user, int is_send, const char *peer_role, void *buf, size_t nbytes, int on_device);
+typedef int (*mb_transport_fn)(void *user, int mode, const char *peer_role, void *buf, size_t nbytes, int on_device);
 int mb_exec_set_transport(mb_exec *e, mb_transport_fn fn, void *user);
 /* Binds a tensor to an Input operation (by arg_name) or replaces the result of the named operation (e.g. the
  * Constant inputs of a compiled graph by larger tensors: lowered graphs are shape-agnostic). */

@@ -17,6 +17,7 @@
 // (the host binds it to NCCL send/recv between the parties' GPUs); a Receive is scheduled directly after its Send
 // in the topological order every party computes identically, so matching transfers are posted in one order.
 #include <chrono>
+#include <deque>
 #include <functional>
 #include <map>
 #include <memory>
@@ -301,6 +302,8 @@ struct mb_exec {
   uint64_t executed, bytes_sent;
   double transport_seconds, sync_seconds;  // host wall time inside the transport / waiting for the stream around it
   bool keep_values;                        // false: a value is released after its last consumer ran
+  std::deque<mb_tensor *> in_flight;       // device payloads handed to the transport, oldest first (each holds a reference)
+  uint64_t sends_reported;                 // completed device sends the transport has reported so far
 };
 
 namespace {
@@ -493,7 +496,21 @@ struct Runner {
     if (xfer(1, peer, hdr, sizeof(hdr), 0) != 0) fail(MB_ERR_KERNEL, "transport: send of header to " + peer + " failed");
     if (nbytes && xfer(1, peer, const_cast<void *>(payload), nbytes, on_device) != 0)
       fail(MB_ERR_KERNEL, "transport: send of payload to " + peer + " failed");
+    if (nbytes && on_device) e->in_flight.push_back(mb_tensor_retain(v.t));  // the transport may still be reading it
     e->bytes_sent += nbytes;
+    reap(false);
+  }
+  // Device payloads stay referenced until the transport reports the send complete (mode 2: number of completed
+  // device sends so far; mode 3: wait for all of them).
+  void reap(bool wait_all) {
+    if (e->in_flight.empty() && !wait_all) return;
+    int64_t done = 0;
+    if (xfer(wait_all ? 3 : 2, "", &done, sizeof(done), 0) != 0) fail(MB_ERR_KERNEL, "transport: completion query failed");
+    while (e->sends_reported < (uint64_t)done && !e->in_flight.empty()) {
+      mb_tensor_free(c, e->in_flight.front());
+      e->in_flight.pop_front();
+      e->sends_reported++;
+    }
   }
   Val recv(const std::string &peer) {
     int64_t hdr[10] = {0};
@@ -813,6 +830,7 @@ struct Runner {
       e->executed++;
       consumed(op);
     }
+    if (e->transport) reap(true);
   }
 };
 
@@ -879,6 +897,7 @@ extern "C" int mb_exec_create(mb_ctx *ctx, const mb_graph *g, const char *role, 
   e->executed = e->bytes_sent = 0;
   e->transport_seconds = e->sync_seconds = 0.0;
   e->keep_values = true;
+  e->sends_reported = 0;
   *out = e;
   return MB_OK;
 }
@@ -887,6 +906,7 @@ extern "C" int mb_exec_free(mb_exec *e) {
   if (!e) return MB_OK;
   for (auto &v : e->values) release(e->ctx, v);
   for (auto &kv : e->bound) release(e->ctx, kv.second);
+  for (auto *t : e->in_flight) mb_tensor_free(e->ctx, t);
   delete e;
   return MB_OK;
 }

@@ -80,6 +80,7 @@ class NcclComm:
         self.torch, self.dist, self.sess, self.role_to_rank = torch, dist, sess, role_to_rank
         self.dev = torch.device("cpu") if device == "cpu" else torch.device("cuda", device)
         self.bytes_sent = 0
+        self._posted, self._completed = [], 0  # device sends in flight (Work handles) / completed so far
 
     def _hdr(self, vals):
         return self.torch.tensor(list(vals) + [0] * (10 - len(vals)), dtype=self.torch.int64, device=self.dev)
@@ -108,15 +109,25 @@ class NcclComm:
         else:
             raise ExecutionError(f"cannot send value of type {type(value)}")
 
-    def transport(self, _user, is_send, peer, buf, nbytes, on_device):
+    def transport(self, _user, mode, peer, buf, nbytes, on_device):
         """mb_transport_fn: raw buffers of the native executor.  Device payloads go straight from / into the
-        tensor's memory; host buffers (headers, keys, seeds) are staged through a small device tensor for NCCL."""
+        tensor's memory; host buffers (headers, keys, seeds) are staged through a small device tensor for NCCL.
+        Modes: 0 receive, 1 send, 2 poll completed device sends, 3 wait for all of them."""
         try:
-            t, other = self.torch, self.role_to_rank[peer.decode()]
+            t = self.torch
+            if mode >= 2:
+                while self._posted and (mode == 3 or self._posted[0].is_completed()):
+                    self._posted.pop(0).wait()
+                    if mode == 3 and self.dev.type == "cuda" and not self._posted:
+                        t.cuda.synchronize(self.dev)
+                    self._completed += 1
+                ctypes.cast(buf, ctypes.POINTER(ctypes.c_int64))[0] = self._completed
+                return 0
+            other = self.role_to_rank[peer.decode()]
             if on_device:
                 view = t.as_tensor(_DeviceBytes(buf, nbytes), device=self.dev)
-                if is_send:
-                    self.dist.send(view, other)  # asynchronous on the NCCL stream; flush() before the memory is reused
+                if mode == 1:
+                    self._posted.append(self.dist.isend(view, other))  # asynchronous on the NCCL stream
                 else:
                     # wait for THIS transfer only (not for the party's own kernels on the context's stream)
                     self.dist.irecv(view, other).wait()
@@ -125,7 +136,7 @@ class NcclComm:
                     done.synchronize()
                 return 0
             host = (ctypes.c_uint8 * nbytes).from_address(buf)
-            if is_send:
+            if mode == 1:
                 self.dist.send(t.frombuffer(bytearray(host), dtype=t.uint8).to(self.dev), other)
             else:
                 staged = t.empty(nbytes, dtype=t.uint8, device=self.dev)
@@ -269,6 +280,9 @@ class Executor:
             self.load(ops)
         for name, t in list(self.overrides.items()) + list((arguments or {}).items()):
             self.sess._check(lib().mb_exec_bind_tensor(self._exec, name.encode(), t.h))
+        if self.comm is not None:
+            self.comm.flush()
+            self.comm._posted, self.comm._completed = [], 0  # the executor counts completed sends per run
         try:
             self.sess._check(lib().mb_exec_run(self._exec))
         except Exception as e:

@@ -28,7 +28,11 @@ def roles_of(ops):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--graph", required=True, help=".moose text or the .json(.gz) re-encoding of tests/golden")
+    ap.add_argument("--graph", default=None, help=".moose text or the .json(.gz) re-encoding of tests/golden")
+    ap.add_argument("--mlp", type=int, default=None, metavar="BATCH",
+                    help="BASELINE config 5: emit the lowered + networked MLP graph (moose_b200/lowering.py) for --dims on "
+                         "Ring64 fixed(14,23) and run it with one party per GPU on a synthetic batch")
+    ap.add_argument("--dims", type=int, nargs="+", default=[784, 512, 512, 10])
     ap.add_argument("--session-id", default="b200-party")
     ap.add_argument("--repeat", type=int, default=1)
     ap.add_argument("--scale", type=int, nargs=3, metavar=("M", "K", "N"), default=None,
@@ -44,8 +48,14 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    raw = gzip.open(args.graph).read().decode() if args.graph.endswith(".gz") else open(args.graph).read()
-    ops = tx.loads_json(raw) if args.graph.endswith((".json", ".json.gz")) else tx.parse_computation(raw)
+    if args.mlp is not None:
+        from moose_b200.lowering import Lowering, networking_pass, prune_pass
+        ops = networking_pass(prune_pass(Lowering(64).mlp_program(len(args.dims) - 1, 23)))
+    elif args.graph is None:
+        raise SystemExit("--graph or --mlp is required")
+    else:
+        raw = gzip.open(args.graph).read().decode() if args.graph.endswith(".gz") else open(args.graph).read()
+        ops = tx.loads_json(raw) if args.graph.endswith((".json", ".json.gz")) else tx.parse_computation(raw)
     roles = roles_of(ops)
     if world != len(roles):
         raise SystemExit(f"graph has {len(roles)} parties {roles}, launched with {world} ranks")
@@ -58,6 +68,22 @@ def main():
     consts = [op for op in ops if op.kind == "Constant" and "Float64Tensor" in op.attrs.get("value", "")]
     consts.sort(key=lambda op: np.array(tx.parse_constant(op.attrs["value"])[1]).shape[0])
     overrides = {}
+    mlp_ref = None
+    if args.mlp is not None:
+        # synthetic model and batch (BASELINE C4 shapes by default); every party binds its copy of the mirrored weights
+        dims, rng = args.dims, np.random.default_rng(3)
+        x = rng.uniform(0, 1, (args.mlp, dims[0]))
+        h = x[:8]
+        for l in range(len(dims) - 1):
+            w = np.random.default_rng(4 + l).normal(0, dims[l] ** -0.5, (dims[l], dims[l + 1]))
+            b = np.random.default_rng(40 + l).normal(0, 0.1, (1, dims[l + 1]))
+            overrides[f"w{l}"], overrides[f"b{l}"] = sess.from_host(mb.FLOAT64, w), sess.from_host(mb.FLOAT64, b)
+            h = h @ w + b
+            if l < len(dims) - 2:
+                h = np.maximum(h, 0)
+        if rank == 0:
+            overrides["x"] = sess.from_host(mb.FLOAT64, x)
+        mlp_ref = h
     if args.scale:
         M, K, N = args.scale
         shapes = [(M, K), (K, N)]
@@ -88,7 +114,9 @@ def main():
     for k, v in outputs.items():
         if isinstance(v, mb.Tensor):
             h = v.to_host()
-            if args.scale:  # check the first rows against a float matmul of the regenerated inputs
+            if mlp_ref is not None:
+                result[k] = {"shape": list(h.shape), "max_abs_err_first_rows": float(np.abs(h[:8] - mlp_ref).max())}
+            elif args.scale:  # check the first rows against a float matmul of the regenerated inputs
                 M, K, N = args.scale
                 a = np.random.default_rng(100).uniform(-1, 1, (M, K))[:4]
                 b = np.random.default_rng(101).uniform(-1, 1, (K, N))
@@ -101,7 +129,9 @@ def main():
     dist.all_gather_object(gathered, {"role": role, "executed": ex.executed, "transport_s": round(ex.transport_seconds, 4),
                                       "stream_wait_s": round(ex.sync_seconds, 4), "outputs": result})
     if rank == 0:
-        print(json.dumps({"mode": "party-per-gpu", "parties": roles, "transport": "nccl send/recv",
+        extra = {} if args.mlp is None else {"workload": "mlp_" + "-".join(map(str, args.dims)) + f"_relu_ring64_fixed(14,23)_batch{args.mlp}",
+                                              "rows_per_s": args.mlp / dt}
+        print(json.dumps({"mode": "party-per-gpu", "parties": roles, "transport": "nccl send/recv", **extra,
                           "ops": len(ops), "seconds_per_run": dt, "payload_bytes_per_run": int(sent[0]) // args.repeat,
                           "per_party": gathered}), flush=True)
     sess.close()

@@ -7,8 +7,9 @@ from . import moose_oracle as mo
 _RING_BITS = {"HostRing64Tensor": 64, "HostRing128Tensor": 128, "Ring64Tensor": 64, "Ring128Tensor": 128}
 
 
-def replay(ops_in_order, sess: mo.Session, parse_constant, attr_hex16):
+def replay(ops_in_order, sess: mo.Session, parse_constant, attr_hex16, arguments=None):
     vals, outputs, mailbox = {}, {}, {}
+    arguments = arguments or {}
     for op in ops_in_order:
         x = [vals[i] for i in op.inputs]
         k = op.kind
@@ -19,6 +20,8 @@ def replay(ops_in_order, sess: mo.Session, parse_constant, attr_hex16):
         elif k == "Constant":
             ty, val = parse_constant(op.attrs["value"])
             v = np.array(val, dtype=np.float64) if ty in ("HostFloat64Tensor", "Float64Tensor") else val
+        elif k == "Input":
+            v = np.asarray(arguments[op.attrs["arg_name"].strip('"')], dtype=np.float64)
         elif k == "RingFixedpointEncode":
             v = mo.fixed_encode(_RING_BITS[op.output_type], x[0], int(op.attrs["scaling_exp"]))
         elif k == "RingFixedpointDecode":

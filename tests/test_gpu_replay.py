@@ -101,3 +101,26 @@ def test_replay_without_keeping_values():
         sess2.close()
     finally:
         sess.close()
+
+
+def test_replay_generated_mlp_graph():
+    """The MLP graph emitted by moose_b200/lowering.py (ReLU via maximum: split, Kogge-Stone adder, dabit ring_inject,
+    replicated mul, TruncPr) through the native executor: every operation bit for bit against the oracle replay, and
+    the logits against a float MLP."""
+    from moose_b200.lowering import Lowering, networking_pass, prune_pass
+    from test_lowering import mlp_case
+    net = networking_pass(prune_pass(Lowering(64).mlp_program(3, 23)))
+    args, want = mlp_case(seed=5, dims=(9, 8, 6, 3), batch=7)
+    sess = mb.Session(0, "t", ENTROPY_KEY)
+    try:
+        ex = Executor(sess)
+        outs = ex.run(net, arguments={k: sess.from_host(mb.FLOAT64, v) for k, v in args.items()})
+        assert ex.executed == len(net)
+        got = outs["output_0"].to_host()
+        assert np.abs(got - want).max() < 1e-5
+        ovals, oouts = ro.replay(toposort(net), mo.Session("t", ENTROPY_KEY), tx.parse_constant, tx.attr_hex16, args)
+        assert np.array_equal(got, oouts["output_0"])
+        bad = [op.name for op in net if op.kind not in ("Send", "Output") and not same_value(ex.values[op.name], ovals[op.name])]
+        assert not bad, bad[:5]
+    finally:
+        sess.close()
