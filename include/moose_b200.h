@@ -310,6 +310,10 @@ int mb_rep_mul_public(mb_ctx *ctx, const mb_rep *x, const mb_tensor *pub, mb_rep
 int mb_rep_mul(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out);
 /* DotOp::rep_rep_kernel (moose/src/replicated/arith.rs:436-493). */
 int mb_rep_dot(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out);
+/* dot(concatenate(xs, axis = 1), y) -- ConcatOp::rep_kernel followed by DotOp::rep_rep_kernel (moose/src/replicated/
+ * ops.rs:48-89, arith.rs:436-493), the bias trick of pymoose's linear predictors (linear_predictor.py:33-58) -- without
+ * writing the concatenated operand when y is skinny (N <= 32): identical values and shares. */
+int mb_rep_dot_concat(mb_ctx *ctx, const mb_rep *const *xs, int n, const mb_rep *y, mb_rep **out);
 /* TruncPrOp::rep_kernel (moose/src/replicated/fixedpoint.rs:80-103) =
  * rep_to_adt (additive/convert.rs:12-79) + TruncPrProvider::trunc_pr
  * (additive/trunc.rs:22-65,114-169) + AdtToRepOp (replicated/convert.rs:392-497). */

@@ -423,6 +423,13 @@ extern "C" int mb_index_axis0(mb_ctx *ctx, int64_t index, const mb_tensor *x, mb
   MB_REQUIRE(ctx, index >= 0 && index < x->shape[0], MB_ERR_KERNEL, "mb_index_axis0: index out of bounds");
   int64_t height = x->numel / x->shape[0];
   mb_tensor *t = nullptr;
+  {
+    // tensors are immutable: a 16-byte aligned slab (bit planes of n % 128 == 0 elements, ring rows) is a view
+    const size_t slab = x->dtype == MB_BIT ? (size_t)height / 8 : (size_t)height * (size_t)mb_elem_bytes(x->dtype);
+    const bool whole = x->dtype == MB_BIT ? height % 128 == 0 : slab % 16 == 0;
+    static const bool no_views = getenv("MOOSE_B200_NO_VIEWS") != nullptr;
+    if (whole && slab > 0 && !no_views) return mb_tensor_view(ctx, x, (size_t)index * slab, x->rank - 1, x->shape + 1, out);
+  }
   MB_CHECK(mb_tensor_new(ctx, x->dtype, x->rank - 1, x->shape + 1, &t));
   int rc = MB_OK;
   if (x->dtype == MB_BIT) {

@@ -22,10 +22,15 @@ namespace {
 
 constexpr int TPB = 256;
 
-#define AES_LAUNCH(ctx, kern, grid, ...)                                                                        \
+// one CTA per SM: the AES table takes the CTA's shared-memory window up to 0x20000 (aes.cuh)
+inline int aes_grid(mb_ctx *ctx, int64_t items, int tpb) {
+  return (int)std::max<int64_t>(1, std::min<int64_t>((items + tpb - 1) / tpb, (int64_t)ctx->sm_count));
+}
+
+#define AES_LAUNCH(ctx, kern, tpb, items, ...)                                                                  \
   do {                                                                                                          \
     MB_CUDA((ctx), cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, AES_SMEM_BYTES));    \
-    kern<<<(grid), TPB, AES_SMEM_BYTES, (ctx)->stream>>>(__VA_ARGS__);                                          \
+    kern<<<aes_grid((ctx), (items), (tpb)), (tpb), AES_SMEM_BYTES, (ctx)->stream>>>(__VA_ARGS__);               \
   } while (0)
 
 __device__ __forceinline__ vec_t vxor(vec_t a, vec_t b) { return make_ulonglong2(a.x ^ b.x, a.y ^ b.y); }
@@ -53,8 +58,8 @@ __global__ void __launch_bounds__(TPB) split_planes_kernel(const T *__restrict__
                                                           const T *__restrict__ x2, uint32_t *__restrict__ outB,
                                                           uint32_t *__restrict__ outC, int64_t n) {
   const int lane = threadIdx.x & 31;
-  const int64_t warp = ((int64_t)blockIdx.x * TPB + threadIdx.x) >> 5;
-  const int64_t nwarps = ((int64_t)gridDim.x * TPB) >> 5;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   const int64_t ngroups = n / 128;
   constexpr int PL = KBITS / 32;
   for (int64_t grp = warp; grp < 2 * ngroups; grp += nwarps) {
@@ -84,13 +89,13 @@ __global__ void __launch_bounds__(TPB) split_planes_kernel(const T *__restrict__
 struct PlanePtrs {
   vec_t *s[3];
 };
-__global__ void __launch_bounds__(TPB) adder_init_kernel(AesKey k_share, AesKey a0, AesKey a1, AesKey a2,
+__global__ void __launch_bounds__(AES_TPB_LIGHT) adder_init_kernel(AesKey k_share, AesKey a0, AesKey a1, AesKey a2,
                                                         const vec_t *__restrict__ B, const vec_t *__restrict__ C,
                                                         PlanePtrs g0, PlanePtrs p0, int64_t nvec) {
   extern __shared__ __align__(16) uint32_t sT[];
   aes_load_table(sT);
   const AesLane L = aes_lane(sT);
-  for (int64_t v = (int64_t)blockIdx.x * TPB + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * TPB) {
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
     const vec_t b = B[v], c = C[v];
     const vec_t R = prf_vec<VK_BIT>(L, k_share, (uint64_t)v);
     const vec_t r0 = prf_vec<VK_BIT>(L, a0, (uint64_t)v);
@@ -128,14 +133,14 @@ __device__ __forceinline__ void rep_and3(const vec_t x[3], const vec_t y[3], con
 // One Kogge-Stone level (misc.rs:216-232) on the planes listed in `d`:
 //   g'[q] = g[q] ^ AND_pg(p[q], g[q - shift]),   p'[q] = AND_pp(p[q], p[q - shift])   (operands below plane
 //   `shift` are the zeros shl_dim inserts).  nv = vectors per plane.
-__global__ void __launch_bounds__(TPB) adder_level_kernel(AesKey pg0, AesKey pg1, AesKey pg2, AesKey pp0, AesKey pp1,
+__global__ void __launch_bounds__(AES_TPB_384) adder_level_kernel(AesKey pg0, AesKey pg1, AesKey pg2, AesKey pp0, AesKey pp1,
                                                          AesKey pp2, LevelDesc d, PlanePtrs g_in, PlanePtrs p_in,
                                                          PlanePtrs g_out, PlanePtrs p_out, int64_t nv) {
   extern __shared__ __align__(16) uint32_t sT[];
   aes_load_table(sT);
   const AesLane L = aes_lane(sT);
   const int64_t total = (int64_t)d.nout * nv;
-  for (int64_t t = (int64_t)blockIdx.x * TPB + threadIdx.x; t < total; t += (int64_t)gridDim.x * TPB) {
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
     const int j = (int)(t / nv);
     const int64_t v = t - (int64_t)j * nv;
     const int q = d.plane[j];
@@ -185,7 +190,7 @@ __global__ void __launch_bounds__(TPB) adder_level_kernel(AesKey pg0, AesKey pg1
 // z = shl_dim(g, 1) ^ p_store (misc.rs:236-240): z[q] = g[q-1] ^ p0[q], z[0] = p0[0].  Full decomposition.
 __global__ void __launch_bounds__(TPB) adder_final_full_kernel(PlanePtrs g, PlanePtrs p0, PlanePtrs z, int64_t nv, int k) {
   const int64_t total = (int64_t)k * nv;
-  for (int64_t t = (int64_t)blockIdx.x * TPB + threadIdx.x; t < total; t += (int64_t)gridDim.x * TPB) {
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
     const bool low = t < nv;
 #pragma unroll
     for (int i = 0; i < 3; i++) z.s[i][t] = low ? p0.s[i][t] : vxor(g.s[i][t - nv], p0.s[i][t]);
@@ -194,7 +199,7 @@ __global__ void __launch_bounds__(TPB) adder_final_full_kernel(PlanePtrs g, Plan
 // msb only: out = g_final[k-2] ^ p0[k-1]
 __global__ void __launch_bounds__(TPB) adder_final_msb_kernel(PlanePtrs g, int64_t gslot, PlanePtrs p0, PlanePtrs z,
                                                              int64_t nv, int k) {
-  for (int64_t v = (int64_t)blockIdx.x * TPB + threadIdx.x; v < nv; v += (int64_t)gridDim.x * TPB) {
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nv; v += (int64_t)gridDim.x * blockDim.x) {
 #pragma unroll
     for (int i = 0; i < 3; i++) z.s[i][v] = vxor(g.s[i][gslot * nv + v], p0.s[i][(int64_t)(k - 1) * nv + v]);
   }
@@ -209,7 +214,7 @@ __global__ void __launch_bounds__(TPB) adder_final_msb_kernel(PlanePtrs g, int64
 //   adt_to_rep: y0 = PRF(seed1), y1 = PRF(seed2), cc = (s0 - y0) + (s1 - y1)     (convert.rs:426-447)
 // Output shares (y0, cc, y1).
 template <int K>
-__global__ void __launch_bounds__(TPB) ring_inject_fused_kernel(AesKey k_br0, AesKey k_y0, AesKey k_y1,
+__global__ void __launch_bounds__(AES_TPB_LIGHT) ring_inject_fused_kernel(AesKey k_br0, AesKey k_y0, AesKey k_y1,
                                                                const uint32_t *__restrict__ x0, const uint32_t *__restrict__ x1,
                                                                const uint32_t *__restrict__ x2, const uint32_t *__restrict__ b,
                                                                vec_t *__restrict__ z0, vec_t *__restrict__ z1,
@@ -219,7 +224,7 @@ __global__ void __launch_bounds__(TPB) ring_inject_fused_kernel(AesKey k_br0, Ae
   const AesLane L = aes_lane(sT);
   typedef VOps<K> O;
   constexpr int EPV = K == VK_RING128 ? 1 : 2;  // ring elements per vector
-  for (int64_t v = (int64_t)blockIdx.x * TPB + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * TPB) {
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
     const int64_t e = v * EPV;
     const uint32_t wb = b[e >> 5];
     const uint32_t wc = x0[e >> 5] ^ x1[e >> 5] ^ x2[e >> 5] ^ wb;
@@ -247,9 +252,7 @@ __global__ void __launch_bounds__(TPB) ring_inject_fused_kernel(AesKey k_br0, Ae
   }
 }
 
-inline int aes_grid(mb_ctx *ctx, int64_t items) {
-  return (int)std::max<int64_t>(1, std::min<int64_t>((items + TPB - 1) / TPB, (int64_t)ctx->sm_count * 3));
-}
+
 
 PlanePtrs ptrs_of(mb_tensor *const t[3]) {
   PlanePtrs p;
@@ -309,7 +312,7 @@ int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only,
   MB_CHECK(p0.alloc(k, n));
   {
     const int64_t total = (int64_t)k * nv;
-    AES_LAUNCH(ctx, adder_init_kernel, aes_grid(ctx, total), keys[0], keys[1], keys[2], keys[3], (const vec_t *)B->dptr,
+    AES_LAUNCH(ctx, adder_init_kernel, AES_TPB_LIGHT, total, keys[0], keys[1], keys[2], keys[3], (const vec_t *)B->dptr,
                (const vec_t *)C->dptr, ptrs_of(g.t), ptrs_of(p0.t), total);
     MB_LAUNCH_CHECK(ctx);
   }
@@ -381,7 +384,7 @@ int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only,
     MB_CHECK(g_next.alloc(std::max(d.nout, 1), n));
     MB_CHECK(p_next.alloc(std::max(np_out, 1), n));
     const AesKey *kk = keys + 4 + 6 * i;
-    AES_LAUNCH(ctx, adder_level_kernel, aes_grid(ctx, (int64_t)d.nout * nv), kk[0], kk[1], kk[2], kk[3], kk[4], kk[5], d,
+    AES_LAUNCH(ctx, adder_level_kernel, AES_TPB_384, (int64_t)d.nout * nv, kk[0], kk[1], kk[2], kk[3], kk[4], kk[5], d,
                ptrs_of(g.t), ptrs_of(p_cur->t), ptrs_of(g_next.t), ptrs_of(p_next.t), nv);
     MB_LAUNCH_CHECK(ctx);
     g.swap(g_next);
@@ -411,13 +414,12 @@ int k_ring_inject_fused(mb_ctx *ctx, const AesKey &k_br0, const AesKey &k_y0, co
   const mb_tensor *t = out[0];
   if (t->numel == 0) return MB_OK;
   const int64_t nvec = vec_count(t);
-  const int g = aes_grid(ctx, nvec);
 #define ARGS k_br0, k_y0, k_y1, (const uint32_t *)x->s[0]->dptr, (const uint32_t *)x->s[1]->dptr, (const uint32_t *)x->s[2]->dptr, \
              (const uint32_t *)b->dptr, (vec_t *)out[0]->dptr, (vec_t *)out[1]->dptr, (vec_t *)out[2]->dptr, nvec
   if (t->dtype == MB_RING128)
-    AES_LAUNCH(ctx, ring_inject_fused_kernel<VK_RING128>, g, ARGS, bit_idx & 127);
+    AES_LAUNCH(ctx, ring_inject_fused_kernel<VK_RING128>, AES_TPB_LIGHT, nvec, ARGS, bit_idx & 127);
   else
-    AES_LAUNCH(ctx, ring_inject_fused_kernel<VK_RING64>, g, ARGS, bit_idx & 63);
+    AES_LAUNCH(ctx, ring_inject_fused_kernel<VK_RING64>, AES_TPB_LIGHT, nvec, ARGS, bit_idx & 63);
 #undef ARGS
   MB_LAUNCH_CHECK(ctx);
   return MB_OK;

@@ -27,6 +27,7 @@ struct mb_tensor {
   void *dptr;
   std::atomic<int> refs;
   int device;
+  mb_tensor *parent;    // non-null: dptr points into parent's allocation (a retained, immutable view)
 };
 
 struct mb_rep {
@@ -96,6 +97,8 @@ static inline bool mb_is_ring(mb_dtype d) { return d == MB_RING64 || d == MB_RIN
 int mb_tensor_new(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, mb_tensor **out);
 int mb_tensor_new_detached(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, mb_tensor **out);
 mb_tensor *mb_tensor_retain(mb_tensor *t);
+// Zero-copy view of `nbytes`-aligned contents of `parent` starting at byte_offset (must be a multiple of 16).
+int mb_tensor_view(mb_ctx *ctx, const mb_tensor *parent, size_t byte_offset, int rank, const int64_t *shape, mb_tensor **out);
 bool mb_same_shape(const mb_tensor *a, const mb_tensor *b);
 int mb_scratch(mb_ctx *ctx, int slot, size_t bytes, void **out);
 int mb_prof_begin(mb_ctx *ctx, cudaEvent_t *start);  // no-ops unless profiling is enabled
@@ -115,6 +118,8 @@ enum EwOp { EW_ADD = 0, EW_SUB = 1, EW_MUL = 2, EW_AND = 3, EW_XOR = 4, EW_OR = 
 // Binary op with ndarray co-broadcasting: strides in elements, 0 for broadcast axes.
 int k_ew_binary(mb_ctx *ctx, EwOp op, const mb_tensor *x, const mb_tensor *y, mb_tensor *out);
 int k_ew_neg(mb_ctx *ctx, const mb_tensor *x, mb_tensor *out);
+int k_ew_binary3(mb_ctx *ctx, EwOp op, const mb_tensor *const x[3], const mb_tensor *const y[3], mb_tensor *const out[3]);
+int k_ew_unary3(mb_ctx *ctx, int mode, unsigned amount, const mb_tensor *const x[3], mb_tensor *const out[3]);
 int k_ew_shift(mb_ctx *ctx, bool left, unsigned amount, const mb_tensor *x, mb_tensor *out);
 int k_fill(mb_ctx *ctx, mb_tensor *out, uint64_t lo, uint64_t hi);
 int k_broadcast(mb_ctx *ctx, const mb_tensor *x, mb_tensor *out);
@@ -135,6 +140,12 @@ int k_bit_not(mb_ctx *ctx, const mb_tensor *x, mb_tensor *out);
 // Ring GEMM C[M,N] (+)= A[M,K] * B[K,N] mod 2^k on raw device pointers.
 int k_gemm_imad(mb_ctx *ctx, mb_dtype dtype, const void *A, const void *B, void *C, int64_t M, int64_t K,
                 int64_t N, bool accumulate);
+// Skinny replicated dot, three parties in one pass; the left operand is the concatenation along K of `n` parts.
+struct RepDotPart { const void *x[3]; int64_t K; int64_t krow0; };
+struct RepDotParts { int n; RepDotPart p[4]; };
+bool k_rep_dot_skinny_supported(int64_t M, int64_t N);
+int k_rep_dot_skinny(mb_ctx *ctx, mb_dtype dtype, const RepDotParts &parts, const void *const ysum[3], const void *const y[3],
+                     void *const z[3], int64_t M, int64_t N);
 bool k_gemm_limb_supported(mb_dtype dtype, int64_t M, int64_t K, int64_t N);
 bool k_gemm_limb_preferred(int64_t M, int64_t K, int64_t N);
 // C = sum_t A_t * B_t for nterms (1 or 2) operand pairs, optional fused epilogue.

@@ -241,6 +241,7 @@ static int tensor_new_on(mb_ctx *ctx, cudaStream_t stream, mb_dtype dtype, int r
   t->refs = 1;
   t->device = ctx->device;
   t->dptr = nullptr;
+  t->parent = nullptr;
   cudaError_t e = cudaMallocAsync(&t->dptr, t->alloc_bytes, stream);
   if (e != cudaSuccess) {
     delete t;
@@ -308,9 +309,38 @@ extern "C" int mb_tensor_to_host(mb_ctx *ctx, const mb_tensor *t, void *host_out
 extern "C" int mb_tensor_free(mb_ctx *ctx, mb_tensor *t) {
   if (!t) return MB_OK;
   if (t->refs.fetch_sub(1) == 1) {
-    if (t->dptr) cudaFreeAsync(t->dptr, ctx ? ctx->stream : 0);
+    mb_tensor *parent = t->parent;
+    if (!parent && t->dptr) cudaFreeAsync(t->dptr, ctx ? ctx->stream : 0);
     delete t;
+    if (parent) return mb_tensor_free(ctx, parent);
   }
+  return MB_OK;
+}
+
+int mb_tensor_view(mb_ctx *ctx, const mb_tensor *parent, size_t byte_offset, int rank, const int64_t *shape, mb_tensor **out) {
+  if (!ctx || !parent || !out || rank < 0 || rank > MB_MAX_RANK) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "view: bad argument");
+  int64_t numel = 1;
+  for (int i = 0; i < rank; i++) numel *= shape[i];
+  mb_tensor *t = new mb_tensor();
+  t->dtype = parent->dtype;
+  t->rank = rank;
+  for (int i = 0; i < MB_MAX_RANK; i++) t->shape[i] = i < rank ? shape[i] : 1;
+  t->numel = numel;
+  t->nbytes = t->dtype == MB_BIT ? (size_t)(numel + 7) / 8 : (size_t)numel * (t->dtype == MB_RING128 ? 16 : 8);
+  t->alloc_bytes = ((t->nbytes + 15) / 16) * 16;
+  if (t->alloc_bytes == 0) t->alloc_bytes = 16;
+  if (byte_offset % 16 || t->nbytes % 16 || byte_offset + t->nbytes > parent->alloc_bytes) {
+    delete t;
+    return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "view: not a 16-byte aligned sub-range");
+  }
+  t->refs = 1;
+  t->device = parent->device;
+  t->dptr = (char *)parent->dptr + byte_offset;
+  // views of views hang off the root allocation
+  mb_tensor *root = const_cast<mb_tensor *>(parent);
+  while (root->parent) root = root->parent;
+  t->parent = mb_tensor_retain(root);
+  *out = t;
   return MB_OK;
 }
 

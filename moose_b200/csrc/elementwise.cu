@@ -48,6 +48,58 @@ __global__ void __launch_bounds__(TPB) ew_same_kernel(const ulonglong2 *__restri
   }
 }
 
+// The three shares of a replicated tensor in one launch (blockIdx.y selects the share): share-wise protocol steps
+// are thousands of small launches per predictor call, a third of them is enough.
+struct Ptr3 {
+  const ulonglong2 *x[3];
+  const ulonglong2 *y[3];
+  ulonglong2 *z[3];
+};
+
+template <bool W128, int OP>
+__global__ void __launch_bounds__(TPB) ew_same3_kernel(Ptr3 p, int64_t nvec) {
+  const ulonglong2 *__restrict__ x = p.x[blockIdx.y];
+  const ulonglong2 *__restrict__ y = p.y[blockIdx.y];
+  ulonglong2 *__restrict__ z = p.z[blockIdx.y];
+  int64_t base = (int64_t)blockIdx.x * (TPB * VPT) + threadIdx.x;
+  ulonglong2 a[VPT], b[VPT];
+#pragma unroll
+  for (int j = 0; j < VPT; j++) {
+    int64_t i = base + (int64_t)j * TPB;
+    if (i < nvec) {
+      a[j] = x[i];
+      b[j] = y[i];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < VPT; j++) {
+    int64_t i = base + (int64_t)j * TPB;
+    if (i < nvec) z[i] = ew_apply<W128, OP>(a[j], b[j]);
+  }
+}
+
+// MODE 0: negate, 1: shift left, 2: shift right
+template <bool W128, int MODE>
+__global__ void __launch_bounds__(TPB) unary3_kernel(Ptr3 p, int64_t nvec, unsigned s) {
+  const ulonglong2 *__restrict__ x = p.x[blockIdx.y];
+  ulonglong2 *__restrict__ z = p.z[blockIdx.y];
+  int64_t base = (int64_t)blockIdx.x * (TPB * VPT) + threadIdx.x;
+#pragma unroll
+  for (int j = 0; j < VPT; j++) {
+    int64_t i = base + (int64_t)j * TPB;
+    if (i >= nvec) continue;
+    const ulonglong2 a = x[i];
+    if (W128) {
+      const u128 v = to128(a);
+      z[i] = from128(MODE == 0 ? (u128)0 - v : MODE == 1 ? v << s : v >> s);
+    } else {
+      z[i] = MODE == 0   ? make_ulonglong2(0ull - a.x, 0ull - a.y)
+             : MODE == 1 ? make_ulonglong2(a.x << s, a.y << s)
+                         : make_ulonglong2(a.x >> s, a.y >> s);
+    }
+  }
+}
+
 struct BcastDesc {
   int rank;
   int64_t shape[MB_MAX_RANK];
@@ -280,6 +332,61 @@ int k_ew_binary(mb_ctx *ctx, EwOp op, const mb_tensor *x, const mb_tensor *y, mb
     }
   }
 #undef LAUNCH_BC
+  MB_LAUNCH_CHECK(ctx);
+  return MB_OK;
+}
+
+// x[i], y[i], out[i] (i = 0..2): same dtype and shape throughout
+int k_ew_binary3(mb_ctx *ctx, EwOp op, const mb_tensor *const x[3], const mb_tensor *const y[3], mb_tensor *const out[3]) {
+  if (out[0]->numel == 0) return MB_OK;
+  int64_t nvec = (int64_t)(out[0]->alloc_bytes / 16);
+  if (out[0]->dtype == MB_BIT) nvec = (int64_t)((out[0]->nbytes + 15) / 16);
+  Ptr3 p;
+  for (int i = 0; i < 3; i++) {
+    p.x[i] = (const ulonglong2 *)x[i]->dptr;
+    p.y[i] = (const ulonglong2 *)y[i]->dptr;
+    p.z[i] = (ulonglong2 *)out[i]->dptr;
+  }
+  const dim3 g(grid_for(nvec, TPB * VPT), 3);
+  const bool w = out[0]->dtype == MB_RING128;
+#define LAUNCH_SAME3(OP)                                           \
+  if (w)                                                           \
+    ew_same3_kernel<true, OP><<<g, TPB, 0, ctx->stream>>>(p, nvec); \
+  else                                                             \
+    ew_same3_kernel<false, OP><<<g, TPB, 0, ctx->stream>>>(p, nvec);
+  switch (op) {
+    case EW_ADD: LAUNCH_SAME3(EW_ADD) break;
+    case EW_SUB: LAUNCH_SAME3(EW_SUB) break;
+    case EW_MUL: LAUNCH_SAME3(EW_MUL) break;
+    case EW_AND: LAUNCH_SAME3(EW_AND) break;
+    case EW_XOR: LAUNCH_SAME3(EW_XOR) break;
+    case EW_OR: LAUNCH_SAME3(EW_OR) break;
+  }
+#undef LAUNCH_SAME3
+  MB_LAUNCH_CHECK(ctx);
+  return MB_OK;
+}
+
+// mode 0: negate, 1: shl, 2: shr (ring tensors of one dtype and shape)
+int k_ew_unary3(mb_ctx *ctx, int mode, unsigned amount, const mb_tensor *const x[3], mb_tensor *const out[3]) {
+  if (out[0]->numel == 0) return MB_OK;
+  const int64_t nvec = (int64_t)(out[0]->alloc_bytes / 16);
+  Ptr3 p;
+  for (int i = 0; i < 3; i++) {
+    p.x[i] = (const ulonglong2 *)x[i]->dptr;
+    p.y[i] = nullptr;
+    p.z[i] = (ulonglong2 *)out[i]->dptr;
+  }
+  const dim3 g(grid_for(nvec, TPB * VPT), 3);
+  const bool w = out[0]->dtype == MB_RING128;
+  const unsigned s = amount & (w ? 127u : 63u);
+#define LAUNCH_U3(M)                                                  \
+  if (w)                                                              \
+    unary3_kernel<true, M><<<g, TPB, 0, ctx->stream>>>(p, nvec, s);   \
+  else                                                                \
+    unary3_kernel<false, M><<<g, TPB, 0, ctx->stream>>>(p, nvec, s);
+  if (mode == 0) { LAUNCH_U3(0) } else if (mode == 1) { LAUNCH_U3(1) } else { LAUNCH_U3(2) }
+#undef LAUNCH_U3
   MB_LAUNCH_CHECK(ctx);
   return MB_OK;
 }

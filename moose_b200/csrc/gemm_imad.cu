@@ -114,7 +114,82 @@ __global__ void __launch_bounds__(TPB) gemm_skinny_kernel(const T *__restrict__ 
   }
 }
 
+// Replicated dot with a skinny right operand, all three parties in one pass: every share of x is read ONCE
+// (the party-by-party form reads each share twice) and the left operand may be a virtual concatenation along K of
+// up to four parts (linear predictors: [bias column, features]).  One warp per row:
+//   v_i[m, :] = sum_k x_i[m, k] * (y_i + y_{i+1})[k, :] + x_{i+1}[m, k] * y_i[k, :]        (arith.rs:461-469)
+template <typename T, int NC>
+__global__ void __launch_bounds__(TPB) rep_dot_skinny_kernel(RepDotParts parts, const T *__restrict__ yb0, const T *__restrict__ yb1,
+                                                              const T *__restrict__ yb2, const T *__restrict__ y0, const T *__restrict__ y1,
+                                                              const T *__restrict__ y2, T *__restrict__ z0, T *__restrict__ z1,
+                                                              T *__restrict__ z2, int64_t M, int64_t N) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * TPB + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * TPB) >> 5;
+  for (int64_t m = warp; m < M; m += nwarps) {
+    for (int64_t n0 = 0; n0 < N; n0 += NC) {
+      T acc[3][NC];
+#pragma unroll
+      for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = 0; j < NC; j++) acc[i][j] = 0;
+      for (int p = 0; p < parts.n; p++) {
+        const int64_t K = parts.p[p].K, r0 = parts.p[p].krow0;
+        const T *a0p = (const T *)parts.p[p].x[0] + m * K, *a1p = (const T *)parts.p[p].x[1] + m * K,
+                *a2p = (const T *)parts.p[p].x[2] + m * K;
+        for (int64_t k = lane; k < K; k += 32) {
+          const T a0 = a0p[k], a1 = a1p[k], a2 = a2p[k];
+          const int64_t row = (r0 + k) * N + n0;
+#pragma unroll
+          for (int j = 0; j < NC; j++)
+            if (n0 + j < N) {
+              acc[0][j] += a0 * yb0[row + j] + a1 * y0[row + j];
+              acc[1][j] += a1 * yb1[row + j] + a2 * y1[row + j];
+              acc[2][j] += a2 * yb2[row + j] + a0 * y2[row + j];
+            }
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = 0; j < NC; j++) {
+          T v = acc[i][j];
+#pragma unroll
+          for (int off = 16; off > 0; off >>= 1) {
+            uint64_t lo = __shfl_xor_sync(0xffffffffu, (uint64_t)v, off);
+            if (sizeof(T) == 16) {
+              uint64_t hi = __shfl_xor_sync(0xffffffffu, (uint64_t)((u128)v >> 64), off);
+              v += (T)(((u128)hi << 64) | lo);
+            } else {
+              v += (T)lo;
+            }
+          }
+          if (lane == 0 && n0 + j < N) (i == 0 ? z0 : i == 1 ? z1 : z2)[m * N + n0 + j] = v;
+        }
+    }
+  }
+}
+
 }  // namespace
+
+bool k_rep_dot_skinny_supported(int64_t M, int64_t N) { return N <= 32 && M >= 64; }
+
+int k_rep_dot_skinny(mb_ctx *ctx, mb_dtype dtype, const RepDotParts &parts, const void *const ysum[3], const void *const y[3],
+                     void *const z[3], int64_t M, int64_t N) {
+  if (M == 0 || N == 0) return MB_OK;
+  const int g = (int)std::min<int64_t>((M * 32 + TPB - 1) / TPB, (int64_t)ctx->sm_count * 16);
+  if (dtype == MB_RING128)
+    rep_dot_skinny_kernel<u128, 2><<<g, TPB, 0, ctx->stream>>>(parts, (const u128 *)ysum[0], (const u128 *)ysum[1], (const u128 *)ysum[2],
+                                                              (const u128 *)y[0], (const u128 *)y[1], (const u128 *)y[2], (u128 *)z[0],
+                                                              (u128 *)z[1], (u128 *)z[2], M, N);
+  else
+    rep_dot_skinny_kernel<uint64_t, 4><<<g, TPB, 0, ctx->stream>>>(parts, (const uint64_t *)ysum[0], (const uint64_t *)ysum[1],
+                                                                  (const uint64_t *)ysum[2], (const uint64_t *)y[0], (const uint64_t *)y[1],
+                                                                  (const uint64_t *)y[2], (uint64_t *)z[0], (uint64_t *)z[1],
+                                                                  (uint64_t *)z[2], M, N);
+  MB_LAUNCH_CHECK(ctx);
+  return MB_OK;
+}
 
 int k_gemm_imad(mb_ctx *ctx, mb_dtype dtype, const void *A, const void *B, void *C, int64_t M, int64_t K, int64_t N,
                 bool accumulate) {

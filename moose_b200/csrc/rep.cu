@@ -19,19 +19,19 @@ constexpr int TPB = 256;
   const AesLane sTl = aes_lane(sT)
 
 // AES kernels need 64 KB of dynamic shared memory for the lookup table.
-#define AES_LAUNCH(ctx, kern, grid, ...)                                                                        \
+#define AES_LAUNCH(ctx, kern, tpb, nvec, ...)                                                                   \
   do {                                                                                                          \
     MB_CUDA((ctx), cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, AES_SMEM_BYTES));    \
-    kern<<<(grid), TPB, AES_SMEM_BYTES, (ctx)->stream>>>(__VA_ARGS__);                                          \
+    kern<<<aes_grid_for((ctx), (nvec), (tpb)), (tpb), AES_SMEM_BYTES, (ctx)->stream>>>(__VA_ARGS__);           \
   } while (0)
 
 #define VEC_LOOP(v, nvec) \
-  for (int64_t v = (int64_t)blockIdx.x * TPB + threadIdx.x; v < (nvec); v += (int64_t)gridDim.x * TPB)
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < (nvec); v += (int64_t)gridDim.x * blockDim.x)
 
 // ShareOp::ring_kernel, owner in the placement (replicated/convert.rs:72-129):
 //   x_owner = PRF(seed), x_{owner+1} = x - x_owner, x_{owner+2} = 0.
 template <int K>
-__global__ void __launch_bounds__(TPB) share_kernel(AesKey key, const vec_t *__restrict__ x, vec_t *__restrict__ o_prf,
+__global__ void __launch_bounds__(AES_TPB_LIGHT) share_kernel(AesKey key, const vec_t *__restrict__ x, vec_t *__restrict__ o_prf,
                                                     vec_t *__restrict__ o_diff, vec_t *__restrict__ o_zero, int64_t nvec,
                                                     int64_t numel) {
   PRF_PROLOGUE();
@@ -48,7 +48,7 @@ __global__ void __launch_bounds__(TPB) share_kernel(AesKey key, const vec_t *__r
 // ShareOp::ring_kernel, owner outside the placement (replicated/convert.rs:130-156):
 //   x0 = PRF(seed00), x1 = PRF(seed11), x2 = x - x0 - x1.
 template <int K>
-__global__ void __launch_bounds__(TPB) share_outsider_kernel(AesKey k0, AesKey k1, const vec_t *__restrict__ x,
+__global__ void __launch_bounds__(AES_TPB_LIGHT) share_outsider_kernel(AesKey k0, AesKey k1, const vec_t *__restrict__ x,
                                                              vec_t *__restrict__ o0, vec_t *__restrict__ o1,
                                                              vec_t *__restrict__ o2, int64_t nvec, int64_t numel) {
   PRF_PROLOGUE();
@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(TPB) reveal_kernel(const vec_t *__restrict__ a
 // The reference expands six PRF streams (two per party); s10==s11 etc., so three
 // distinct streams suffice.  Reads 6 vectors, writes 3, evaluates 3 AES blocks.
 template <int K>
-__global__ void __launch_bounds__(TPB) rep_mul_kernel(AesKey s0, AesKey s1, AesKey s2, const vec_t *__restrict__ x0,
+__global__ void __launch_bounds__(AES_TPB_MID) rep_mul_kernel(AesKey s0, AesKey s1, AesKey s2, const vec_t *__restrict__ x0,
                                                       const vec_t *__restrict__ x1, const vec_t *__restrict__ x2,
                                                       const vec_t *__restrict__ y0, const vec_t *__restrict__ y1,
                                                       const vec_t *__restrict__ y2, vec_t *__restrict__ z0,
@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(TPB) rep_mul_kernel(AesKey s0, AesKey s1, AesK
 // z_i = v_i + PRF(s_i) - PRF(s_{i+1}): tail of DotOp::rep_rep_kernel
 // (replicated/arith.rs:476-484).  v_i may alias z_i.
 template <int K>
-__global__ void __launch_bounds__(TPB) add_zero_share_kernel(AesKey s0, AesKey s1, AesKey s2, const vec_t *v0p,
+__global__ void __launch_bounds__(AES_TPB_LIGHT) add_zero_share_kernel(AesKey s0, AesKey s1, AesKey s2, const vec_t *v0p,
                                                              const vec_t *v1p, const vec_t *v2p, vec_t *z0, vec_t *z1,
                                                              vec_t *z2, int64_t nvec, int64_t numel) {
   PRF_PROLOGUE();
@@ -158,7 +158,7 @@ struct TruncParams {
 //       z1 = open(y - (z0, z2)).
 // Six PRF streams, 3 vectors read, 3 written.
 template <int K>
-__global__ void __launch_bounds__(TPB) trunc_pr_kernel(AesKey kr, AesKey ka, AesKey kb, AesKey kc, AesKey k1, AesKey k2,
+__global__ void __launch_bounds__(AES_TPB_MID) trunc_pr_kernel(AesKey kr, AesKey ka, AesKey kb, AesKey kc, AesKey k1, AesKey k2,
                                                        TruncParams p, const vec_t *__restrict__ x0,
                                                        const vec_t *__restrict__ x1, const vec_t *__restrict__ x2,
                                                        vec_t *__restrict__ z0, vec_t *__restrict__ z1,
@@ -199,8 +199,9 @@ __global__ void __launch_bounds__(TPB) trunc_pr_kernel(AesKey kr, AesKey ka, Aes
   }
 }
 
-inline int grid_for(mb_ctx *ctx, int64_t nvec) {
-  return (int)std::max<int64_t>(1, std::min<int64_t>((nvec + TPB - 1) / TPB, (int64_t)ctx->sm_count * 3));
+// one CTA per SM: the AES table takes the CTA's shared-memory window up to 0x20000 (aes.cuh)
+inline int aes_grid_for(mb_ctx *ctx, int64_t nvec, int tpb) {
+  return (int)std::max<int64_t>(1, std::min<int64_t>((nvec + tpb - 1) / tpb, (int64_t)ctx->sm_count));
 }
 
 }  // namespace
@@ -213,11 +214,10 @@ int k_rep_share(mb_ctx *ctx, const AesKey &key, int owner, const mb_tensor *x, m
   mb_tensor *o[3] = {o0, o1, o2};
   mb_tensor *prf = o[owner], *diff = o[(owner + 1) % 3], *zero = o[(owner + 2) % 3];
   int64_t nvec = vec_count(x);
-  int g = grid_for(ctx, nvec);
   switch (vec_kind(x->dtype)) {
-    case VK_RING128: AES_LAUNCH(ctx, share_kernel<VK_RING128>, g, key, CVP(x), VP(prf), VP(diff), VP(zero), nvec, x->numel); break;
-    case VK_RING64: AES_LAUNCH(ctx, share_kernel<VK_RING64>, g, key, CVP(x), VP(prf), VP(diff), VP(zero), nvec, x->numel); break;
-    case VK_BIT: AES_LAUNCH(ctx, share_kernel<VK_BIT>, g, key, CVP(x), VP(prf), VP(diff), VP(zero), nvec, x->numel); break;
+    case VK_RING128: AES_LAUNCH(ctx, share_kernel<VK_RING128>, AES_TPB_LIGHT, nvec, key, CVP(x), VP(prf), VP(diff), VP(zero), nvec, x->numel); break;
+    case VK_RING64: AES_LAUNCH(ctx, share_kernel<VK_RING64>, AES_TPB_LIGHT, nvec, key, CVP(x), VP(prf), VP(diff), VP(zero), nvec, x->numel); break;
+    case VK_BIT: AES_LAUNCH(ctx, share_kernel<VK_BIT>, AES_TPB_LIGHT, nvec, key, CVP(x), VP(prf), VP(diff), VP(zero), nvec, x->numel); break;
   }
   MB_LAUNCH_CHECK(ctx);
   return MB_OK;
@@ -227,11 +227,10 @@ int k_rep_share_outsider(mb_ctx *ctx, const AesKey &k0, const AesKey &k1, const 
                          mb_tensor *o2) {
   if (x->numel == 0) return MB_OK;
   int64_t nvec = vec_count(x);
-  int g = grid_for(ctx, nvec);
   switch (vec_kind(x->dtype)) {
-    case VK_RING128: AES_LAUNCH(ctx, share_outsider_kernel<VK_RING128>, g, k0, k1, CVP(x), VP(o0), VP(o1), VP(o2), nvec, x->numel); break;
-    case VK_RING64: AES_LAUNCH(ctx, share_outsider_kernel<VK_RING64>, g, k0, k1, CVP(x), VP(o0), VP(o1), VP(o2), nvec, x->numel); break;
-    case VK_BIT: AES_LAUNCH(ctx, share_outsider_kernel<VK_BIT>, g, k0, k1, CVP(x), VP(o0), VP(o1), VP(o2), nvec, x->numel); break;
+    case VK_RING128: AES_LAUNCH(ctx, share_outsider_kernel<VK_RING128>, AES_TPB_LIGHT, nvec, k0, k1, CVP(x), VP(o0), VP(o1), VP(o2), nvec, x->numel); break;
+    case VK_RING64: AES_LAUNCH(ctx, share_outsider_kernel<VK_RING64>, AES_TPB_LIGHT, nvec, k0, k1, CVP(x), VP(o0), VP(o1), VP(o2), nvec, x->numel); break;
+    case VK_BIT: AES_LAUNCH(ctx, share_outsider_kernel<VK_BIT>, AES_TPB_LIGHT, nvec, k0, k1, CVP(x), VP(o0), VP(o1), VP(o2), nvec, x->numel); break;
   }
   MB_LAUNCH_CHECK(ctx);
   return MB_OK;
@@ -254,13 +253,12 @@ int k_rep_mul(mb_ctx *ctx, const AesKey seeds[3], const mb_rep *x, const mb_rep 
   const mb_tensor *t = z[0];
   if (t->numel == 0) return MB_OK;
   int64_t nvec = vec_count(t);
-  int g = grid_for(ctx, nvec);
 #define ARGS seeds[0], seeds[1], seeds[2], CVP(x->s[0]), CVP(x->s[1]), CVP(x->s[2]), CVP(y->s[0]), CVP(y->s[1]), CVP(y->s[2]), \
              VP(z[0]), VP(z[1]), VP(z[2]), nvec, t->numel
   switch (vec_kind(t->dtype)) {
-    case VK_RING128: AES_LAUNCH(ctx, rep_mul_kernel<VK_RING128>, g, ARGS); break;
-    case VK_RING64: AES_LAUNCH(ctx, rep_mul_kernel<VK_RING64>, g, ARGS); break;
-    case VK_BIT: AES_LAUNCH(ctx, rep_mul_kernel<VK_BIT>, g, ARGS); break;
+    case VK_RING128: AES_LAUNCH(ctx, rep_mul_kernel<VK_RING128>, AES_TPB_MID, nvec, ARGS); break;
+    case VK_RING64: AES_LAUNCH(ctx, rep_mul_kernel<VK_RING64>, AES_TPB_MID, nvec, ARGS); break;
+    case VK_BIT: AES_LAUNCH(ctx, rep_mul_kernel<VK_BIT>, AES_TPB_MID, nvec, ARGS); break;
   }
 #undef ARGS
   MB_LAUNCH_CHECK(ctx);
@@ -271,12 +269,11 @@ int k_add_zero_share(mb_ctx *ctx, const AesKey seeds[3], mb_tensor *v[3], mb_ten
   const mb_tensor *t = z[0];
   if (t->numel == 0) return MB_OK;
   int64_t nvec = vec_count(t);
-  int g = grid_for(ctx, nvec);
 #define ARGS seeds[0], seeds[1], seeds[2], CVP(v[0]), CVP(v[1]), CVP(v[2]), VP(z[0]), VP(z[1]), VP(z[2]), nvec, t->numel
   switch (vec_kind(t->dtype)) {
-    case VK_RING128: AES_LAUNCH(ctx, add_zero_share_kernel<VK_RING128>, g, ARGS); break;
-    case VK_RING64: AES_LAUNCH(ctx, add_zero_share_kernel<VK_RING64>, g, ARGS); break;
-    case VK_BIT: AES_LAUNCH(ctx, add_zero_share_kernel<VK_BIT>, g, ARGS); break;
+    case VK_RING128: AES_LAUNCH(ctx, add_zero_share_kernel<VK_RING128>, AES_TPB_LIGHT, nvec, ARGS); break;
+    case VK_RING64: AES_LAUNCH(ctx, add_zero_share_kernel<VK_RING64>, AES_TPB_LIGHT, nvec, ARGS); break;
+    case VK_BIT: AES_LAUNCH(ctx, add_zero_share_kernel<VK_BIT>, AES_TPB_LIGHT, nvec, ARGS); break;
   }
 #undef ARGS
   MB_LAUNCH_CHECK(ctx);
@@ -297,13 +294,12 @@ int k_rep_trunc_pr(mb_ctx *ctx, const AesKey seeds[6], unsigned amount, const mb
   p.up_lo = (uint64_t)up; p.up_hi = (uint64_t)(up >> 64);
   p.down_lo = (uint64_t)down; p.down_hi = (uint64_t)(down >> 64);
   int64_t nvec = vec_count(t);
-  int g = grid_for(ctx, nvec);
 #define ARGS seeds[0], seeds[1], seeds[2], seeds[3], seeds[4], seeds[5], p, CVP(x->s[0]), CVP(x->s[1]), CVP(x->s[2]), \
              VP(z[0]), VP(z[1]), VP(z[2]), nvec
   if (t->dtype == MB_RING128)
-    AES_LAUNCH(ctx, trunc_pr_kernel<VK_RING128>, g, ARGS);
+    AES_LAUNCH(ctx, trunc_pr_kernel<VK_RING128>, AES_TPB_MID, nvec, ARGS);
   else
-    AES_LAUNCH(ctx, trunc_pr_kernel<VK_RING64>, g, ARGS);
+    AES_LAUNCH(ctx, trunc_pr_kernel<VK_RING64>, AES_TPB_MID, nvec, ARGS);
 #undef ARGS
   MB_LAUNCH_CHECK(ctx);
   return MB_OK;

@@ -101,10 +101,44 @@ int gen_zero_seeds(mb_ctx *ctx, AesKey seeds[3]) {
   return MB_OK;
 }
 
+// three fresh tensors shaped like `like`
+int alloc3(mb_ctx *ctx, const mb_tensor *like, mb_tensor *z[3]) {
+  z[0] = z[1] = z[2] = nullptr;
+  for (int i = 0; i < 3; i++) {
+    int rc = mb_tensor_new(ctx, like->dtype, like->rank, like->shape, &z[i]);
+    if (rc != MB_OK) {
+      for (int j = 0; j < i; j++) mb_tensor_free(ctx, z[j]);
+      return rc;
+    }
+  }
+  return MB_OK;
+}
+
+bool uniform_shapes(const mb_rep *x, const mb_rep *y) {
+  static const bool no_batch = getenv("MOOSE_B200_NO_SHARE_BATCH") != nullptr;
+  if (no_batch) return false;
+  for (int i = 0; i < 3; i++)
+    if (!mb_same_shape(x->s[i], x->s[0]) || (y && !mb_same_shape(y->s[i], x->s[0]))) return false;
+  return true;
+}
+
 int sharewise_binary(mb_ctx *ctx, EwOp op, const mb_rep *x, const mb_rep *y, mb_rep **out, const char *name) {
   MB_REQUIRE(ctx, rep_valid(x) && rep_valid(y) && out, MB_ERR_INVALID_ARGUMENT, std::string(name) + ": NULL argument");
   MB_REQUIRE(ctx, x->s[0]->dtype == y->s[0]->dtype, MB_ERR_TYPE_MISMATCH, std::string(name) + ": dtypes differ");
   mb_tensor *z[3] = {nullptr, nullptr, nullptr};
+  if (uniform_shapes(x, y) && x->s[0]->dtype != MB_FLOAT64) {
+    // all six operands of one shape: the three share-wise ops go out as ONE launch
+    EwOp o = op;
+    if (x->s[0]->dtype == MB_BIT) o = op == EW_MUL ? EW_AND : EW_XOR;  // Z2: add = sub = xor, mul = and
+    MB_CHECK(alloc3(ctx, x->s[0], z));
+    int rc = k_ew_binary3(ctx, o, x->s, y->s, z);
+    if (rc != MB_OK) {
+      for (int j = 0; j < 3; j++) mb_tensor_free(ctx, z[j]);
+      return rc;
+    }
+    *out = rep_make(z[0], z[1], z[2]);
+    return MB_OK;
+  }
   for (int i = 0; i < 3; i++) {
     int rc = op == EW_ADD ? mb_add(ctx, x->s[i], y->s[i], &z[i]) : op == EW_SUB ? mb_sub(ctx, x->s[i], y->s[i], &z[i])
                                                                                  : mb_mul(ctx, x->s[i], y->s[i], &z[i]);
@@ -112,6 +146,18 @@ int sharewise_binary(mb_ctx *ctx, EwOp op, const mb_rep *x, const mb_rep *y, mb_
       for (int j = 0; j < i; j++) mb_tensor_free(ctx, z[j]);
       return rc;
     }
+  }
+  *out = rep_make(z[0], z[1], z[2]);
+  return MB_OK;
+}
+
+int sharewise_unary(mb_ctx *ctx, int mode, uint64_t amount, const mb_rep *x, mb_rep **out) {
+  mb_tensor *z[3];
+  MB_CHECK(alloc3(ctx, x->s[0], z));
+  int rc = k_ew_unary3(ctx, mode, (unsigned)(amount & 127), x->s, z);
+  if (rc != MB_OK) {
+    for (int j = 0; j < 3; j++) mb_tensor_free(ctx, z[j]);
+    return rc;
   }
   *out = rep_make(z[0], z[1], z[2]);
   return MB_OK;
@@ -195,11 +241,12 @@ extern "C" int mb_rep_sub(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep 
 extern "C" int mb_rep_neg(mb_ctx *ctx, const mb_rep *x, mb_rep **out) {
   MB_ENTER(ctx, "mb_rep_neg");
   MB_REQUIRE(ctx, rep_valid(x) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_neg: NULL argument");
+  if (mb_is_ring(x->s[0]->dtype) && uniform_shapes(x, nullptr)) return sharewise_unary(ctx, 0, 0, x, out);
   mb_tensor *z[3] = {nullptr, nullptr, nullptr};
   for (int i = 0; i < 3; i++) {
-    int rc;
-    // NegOp::rep_bit_kernel flips only x00 / x02 = share 0 (arith.rs:525-558)
-    if (x->s[0]->dtype == MB_BIT && i != 0) rc = mb_reshape(ctx, x->s[i], x->s[i]->rank, x->s[i]->shape, &z[i]);
+    int rc = MB_OK;
+    // NegOp::rep_bit_kernel flips only x00 / x02 = share 0 (arith.rs:525-558); the other shares are shared as is
+    if (x->s[0]->dtype == MB_BIT && i != 0) z[i] = mb_tensor_retain(x->s[i]);
     else rc = mb_neg(ctx, x->s[i], &z[i]);
     if (rc != MB_OK) {
       for (int j = 0; j < i; j++) mb_tensor_free(ctx, z[j]);
@@ -213,6 +260,7 @@ extern "C" int mb_rep_neg(mb_ctx *ctx, const mb_rep *x, mb_rep **out) {
 extern "C" int mb_rep_shl(mb_ctx *ctx, uint64_t amount, const mb_rep *x, mb_rep **out) {
   MB_ENTER(ctx, "mb_rep_shl");
   MB_REQUIRE(ctx, rep_valid(x) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_shl: NULL argument");
+  if (mb_is_ring(x->s[0]->dtype) && uniform_shapes(x, nullptr)) return sharewise_unary(ctx, 1, amount, x, out);
   mb_tensor *z[3] = {nullptr, nullptr, nullptr};
   for (int i = 0; i < 3; i++) {
     int rc = mb_shl(ctx, amount, x->s[i], &z[i]);
@@ -326,6 +374,62 @@ extern "C" int mb_rep_mul(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep 
   return MB_OK;
 }
 
+// v_i = x_i.(y_i + y_{i+1}) + x_{i+1}.y_i for the three parties in one pass over x (gemm_imad.cu)
+static int rep_dot_skinny(mb_ctx *ctx, mb_dtype dt, const RepDotParts &parts, const mb_rep *y, mb_rep *z, int64_t M, int64_t N) {
+  Tmp ys0(ctx), ys1(ctx), ys2(ctx);
+  MB_CHECK(mb_add(ctx, y->s[0], y->s[1], &ys0.p));
+  MB_CHECK(mb_add(ctx, y->s[1], y->s[2], &ys1.p));
+  MB_CHECK(mb_add(ctx, y->s[2], y->s[0], &ys2.p));
+  const void *ysum[3] = {ys0.p->dptr, ys1.p->dptr, ys2.p->dptr};
+  const void *yy[3] = {y->s[0]->dptr, y->s[1]->dptr, y->s[2]->dptr};
+  void *zz[3] = {z->s[0]->dptr, z->s[1]->dptr, z->s[2]->dptr};
+  return k_rep_dot_skinny(ctx, dt, parts, ysum, yy, zz, M, N);
+}
+
+// dot(concatenate(xs, axis = 1), y) without materialising the concatenation when the skinny kernel applies
+// (LinearPredictor's bias trick, pymoose linear_predictor.py:33-58: the [B, 1 + features] operand is 8 GB per share
+// at BASELINE config 3).  Same values, same zero share, hence the same shares as ConcatOp + DotOp.
+extern "C" int mb_rep_dot_concat(mb_ctx *ctx, const mb_rep *const *xs, int n, const mb_rep *y, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_dot_concat");
+  MB_REQUIRE(ctx, xs && n > 0 && rep_valid(y) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_dot_concat: NULL argument");
+  const mb_dtype dt = y->s[0]->dtype;
+  bool fused = n <= 4 && mb_is_ring(dt) && y->s[0]->rank == 2 && ctx->gemm_mode != 2;
+  int64_t M = 0, Ktot = 0;
+  for (int p = 0; p < n; p++) {
+    MB_REQUIRE(ctx, rep_valid(xs[p]), MB_ERR_INVALID_ARGUMENT, "mb_rep_dot_concat: NULL argument");
+    const mb_tensor *t = xs[p]->s[0];
+    if (t->dtype != dt || t->rank != 2 || (p && t->shape[0] != M)) fused = false;
+    if (p == 0) M = t->rank ? t->shape[0] : 0;
+    Ktot += t->rank == 2 ? t->shape[1] : 0;
+  }
+  const int64_t N = y->s[0]->rank == 2 ? y->s[0]->shape[1] : 0;
+  fused = fused && Ktot == y->s[0]->shape[0] && k_rep_dot_skinny_supported(M, N) &&
+          !(ctx->gemm_mode == 0 && k_gemm_limb_supported(dt, M, 2 * Ktot, N) && k_gemm_limb_preferred(M, 2 * Ktot, N));
+  if (!fused) {
+    RepTmp cat(ctx);
+    MB_CHECK(mb_rep_concat(ctx, 1, xs, n, &cat.p));
+    return mb_rep_dot(ctx, cat.p, y, out);
+  }
+  RepDotParts parts;
+  parts.n = n;
+  int64_t row = 0;
+  for (int p = 0; p < n; p++) {
+    for (int i = 0; i < 3; i++) parts.p[p].x[i] = xs[p]->s[i]->dptr;
+    parts.p[p].K = xs[p]->s[0]->shape[1];
+    parts.p[p].krow0 = row;
+    row += parts.p[p].K;
+  }
+  RepTmp z(ctx);
+  const int64_t oshape[2] = {M, N};
+  MB_CHECK(rep_alloc(ctx, dt, 2, oshape, &z.p));
+  MB_CHECK(rep_dot_skinny(ctx, dt, parts, y, z.p, M, N));
+  AesKey seeds[3];
+  MB_CHECK(gen_zero_seeds(ctx, seeds));
+  MB_CHECK(k_add_zero_share(ctx, seeds, z.p->s, z.p->s));
+  *out = z.release();
+  return MB_OK;
+}
+
 extern "C" int mb_rep_dot(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out) {
   MB_ENTER(ctx, "mb_rep_dot");
   MB_REQUIRE(ctx, rep_valid(x) && rep_valid(y) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_dot: NULL argument");
@@ -358,6 +462,13 @@ extern "C" int mb_rep_dot(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep 
       Cs[i] = z.p->s[i]->dptr;
     }
     MB_CHECK(k_gemm_limb_batched(ctx, dt, As, 3, Bs, 6, a_idx, b_idx, 3, 2, Cs, M, K, N));
+  } else if (k_rep_dot_skinny_supported(M, N) && x->s[0]->rank == 2 && y->s[0]->rank == 2) {
+    RepDotParts parts;
+    parts.n = 1;
+    for (int i = 0; i < 3; i++) parts.p[0].x[i] = x->s[i]->dptr;
+    parts.p[0].K = K;
+    parts.p[0].krow0 = 0;
+    MB_CHECK(rep_dot_skinny(ctx, dt, parts, y, z.p, M, N));
   } else {
     for (int i = 0; i < 3; i++) {
       int j = (i + 1) % 3;

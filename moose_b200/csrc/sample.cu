@@ -5,7 +5,7 @@
 
 namespace {
 
-constexpr int TPB = 256;
+constexpr int TPB = AES_TPB_LIGHT;
 
 #define AES_LAUNCH(ctx, kern, grid, ...)                                                                        \
   do {                                                                                                          \
@@ -18,7 +18,7 @@ __global__ void __launch_bounds__(TPB) sample_kernel(AesKey key, vec_t *__restri
   extern __shared__ __align__(16) uint32_t sT[];
   aes_load_table(sT);
   const AesLane sTl = aes_lane(sT);
-  for (int64_t v = (int64_t)blockIdx.x * TPB + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * TPB) {
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
     vec_t r = prf_vec<K>(sTl, key, (uint64_t)v);
     if (K == VK_BIT) r = bit_tail_mask(r, v, numel);
     out[v] = r;
@@ -34,7 +34,7 @@ __global__ void __launch_bounds__(TPB) sample_bits_as_ring_kernel(AesKey key, T 
   aes_load_table(sT);
   const AesLane sTl = aes_lane(sT);
   int64_t nblocks = (numel + 127) / 128;
-  for (int64_t b = (int64_t)blockIdx.x * TPB + threadIdx.x; b < nblocks; b += (int64_t)gridDim.x * TPB) {
+  for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < nblocks; b += (int64_t)gridDim.x * blockDim.x) {
     uint32_t o[4];
     aes_ctr_block(sTl, key, (uint64_t)b, o);
 #pragma unroll 1
@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(TPB) sample_bits_as_ring_kernel(AesKey key, T 
 
 int k_sample(mb_ctx *ctx, const AesKey &key, mb_tensor *out, bool bits_as_ring) {
   if (out->numel == 0) return MB_OK;
-  int maxg = ctx->sm_count * 3;
+  int maxg = ctx->sm_count;  // one CTA per SM (aes.cuh)
   if (bits_as_ring) {
     int64_t nblocks = (out->numel + 127) / 128;
     int g = (int)std::min<int64_t>((nblocks + TPB - 1) / TPB, maxg);

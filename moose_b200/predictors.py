@@ -87,9 +87,9 @@ class LinearPredictor:
         """x_fixed: [B, features] fixed-point host tensor at alice (no bias column)."""
         s = self.sess
         bias = s.share(s.fill(self.ring, 1 << self.frac, (x_fixed.shape[0], 1)), 1)  # bias_trick at bob
-        x = s.rep_concat(1, [bias, s.share(x_fixed, 0)])
+        x = s.share(x_fixed, 0)
         w = s.share(self.w, 0)
-        y = s.trunc_pr(self.frac, s.rep_dot(x, w))
+        y = s.trunc_pr(self.frac, s.rep_dot_concat([bias, x], w))  # = dot(concatenate([bias, x], axis=1), w)
         if self.post == "sigmoid":
             y = s.sigmoid(self.integral, self.frac, y)
         elif self.post == "normalized_sigmoid":

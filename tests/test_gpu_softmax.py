@@ -155,3 +155,27 @@ def test_log_sqrt(bits, i_p, f_p, fn, tol, x):
     got = g.fixedpoint_decode(f_p, g.reveal(gz)).to_host()
     assert np.abs(got - getattr(np, fn)(x)).max() < tol
     g.close()
+
+
+@pytest.mark.parametrize("bits", [64, 128])
+@pytest.mark.parametrize("widths,n_out", [((1, 37), 2), ((5, 1, 64), 10), ((33,), 3), ((1, 40), 48)])
+def test_dot_concat_equals_concat_then_dot(bits, widths, n_out):
+    """mb_rep_dot_concat (fused skinny kernel over virtual parts; N = 48 takes the concat + dot fallback) against the
+    oracle's ConcatOp + DotOp: same shares."""
+    g, o = pair()
+    rng = np.random.default_rng(sum(widths) + bits)
+    rows = 130
+    gx, ox = [], []
+    for w, owner in zip(widths, (1, 0, 2)):
+        a = rand_ring(rng, bits, (rows, w))
+        gx.append(g.share(g.from_host(DT[bits], a), owner))
+        ox.append(mo.rep_share(o, mo.Ring(bits, a), owner))
+    b = rand_ring(rng, bits, (sum(widths), n_out))
+    gy, oy = g.share(g.from_host(DT[bits], b), 0), mo.rep_share(o, mo.Ring(bits, b), 0)
+    gz = g.rep_dot_concat(gx, gy)
+    oz = mo.rep_dot(o, mo.rep_concat(1, ox), oy)
+    assert same_rep(gz, oz)
+    # the plain replicated dot takes the same fused kernel for skinny right operands
+    assert same_rep(g.rep_dot(gx[0], g.share(g.from_host(DT[bits], b[: widths[0]]), 1)),
+                    mo.rep_dot(o, ox[0], mo.rep_share(o, mo.Ring(bits, b[: widths[0]]), 1)))
+    g.close()
