@@ -254,6 +254,42 @@ def run_mlp(args):
         dist.destroy_process_group()
 
 
+def run_prf(args):
+    """PRF microbenchmark (the ceiling of the PRF-consuming kernels): SampleSeeded of a 4 GB Ring128 tensor.
+    Roofline: the T-table formulation does 148 shared-memory lookups per AES block (4 + 8 x 16 + 16) and an SM retires
+    one 32-lane LDS per clock, so peak = SMs x 32 x f_SM / 148 blocks/s at the SM clock sampled under load."""
+    import moose_b200 as mb
+    sess = mb.Session(0, f"{SESSION_ID}-prf", ENTROPY_KEY)
+    n = 1 << 28
+    seed = bytes(range(16))
+    for _ in range(args.warmup):
+        t = sess.sample_uniform_seeded(mb.RING128, (n,), seed)
+    sess.sync()
+    sampler = ClockSampler(0)
+    sampler.start()
+    sess.timer_start()
+    for _ in range(args.steps):
+        t = sess.sample_uniform_seeded(mb.RING128, (n,), seed)
+    ms = sess.timer_stop()
+    clocks = sampler.stop()
+    blocks_per_s = n * args.steps / (ms * 1e-3)
+    f_hz = (clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965.0) * 1e6
+    peak = 148 * 32 * f_hz / 148.0
+    first = sess.sample_uniform_seeded(mb.RING128, (1,), bytes(16)).to_ints().tolist()
+    print(json.dumps({
+        "metric": "prf_aes128_ctr_blocks_per_s", "value": blocks_per_s / 1e9, "unit": "G blocks/s", "n_gpus": 1,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "sample_seeded_ring128_2^28_elements (4 GB of keystream per step)",
+                   "golden_first_element_ok": first == [78655730786844307471556614669614075016]},
+        "clocks": clocks, "gpu_launches": args.steps,
+        "roofline": {"kernel": "sample_kernel", "bound": "shared-memory pipe (LDS)", "achieved": blocks_per_s / 1e9,
+                     "peak": peak / 1e9, "unit": "G blocks/s", "frac": blocks_per_s / peak,
+                     "keystream_GBps": blocks_per_s * 16 / 1e9,
+                     "peak_source": "148 SMs x 32 lanes x sampled SM clock / 148 lookups per block"}}), flush=True)
+    sess.close()
+
+
 def run_logreg(args):
     """BASELINE configs[2]: LinearClassifier, 512 features, 2 classes, sigmoid post-transform, Ring128 fixed(24,40).
     One step = share + bias concat + dot [B,513]x[513,2] + TruncPr + sigmoid over a device-resident fixed-point batch."""
@@ -318,10 +354,12 @@ def main():
     ap.add_argument("--size", type=int, default=4096, help="M=N=K (default: the BASELINE config, 4096)")
     ap.add_argument("--ref-size", type=int, default=640, help="sample size of the CPU baseline arms")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="matmul", choices=["matmul", "mlp", "logreg"],
+    ap.add_argument("--workload", default="matmul", choices=["matmul", "mlp", "logreg", "prf"],
                     help="matmul = BASELINE configs[1] (the bench contract); mlp = configs[3], a secondary line")
     ap.add_argument("--batch", type=int, default=65536)
     args = ap.parse_args()
+    if args.workload == "prf":
+        return run_prf(args)
     if args.workload == "mlp":
         return run_mlp(args)
     if args.workload == "logreg":

@@ -27,30 +27,38 @@ __device__ __forceinline__ uint32_t warp_transpose32(uint32_t x, int lane) {
 }
 
 // BitDecomposeOp::host_bit64/128_kernel (host/ops.rs:896-936), n % 128 == 0:
-// a warp transposes 128 elements x KBITS planes (32 x 32 bit blocks, shuffle butterflies)
-// and writes 16 bytes per plane.
+// a warp transposes 128 elements x KBITS planes (32 x 32 bit blocks, shuffle butterflies); the eight warps of a
+// CTA take eight consecutive groups and exchange through shared memory so that each plane gets one full 128-byte
+// line per store.
 template <typename T, int KBITS>
 __global__ void __launch_bounds__(TPB) bit_decompose_aligned_kernel(const T *__restrict__ x, uint32_t *__restrict__ out,
                                                                    int64_t n) {
-  const int lane = threadIdx.x & 31;
-  const int64_t warp = ((int64_t)blockIdx.x * TPB + threadIdx.x) >> 5;
-  const int64_t nwarps = ((int64_t)gridDim.x * TPB) >> 5;
-  const int64_t ngroups = n / 128;
+  constexpr int WARPS = TPB / 32;
   constexpr int PL = KBITS / 32;  // planes kept per lane
-  for (int64_t grp = warp; grp < ngroups; grp += nwarps) {
-    uint32_t keep[PL][4];
+  __shared__ uint4 tile[KBITS][WARPS];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int64_t ngroups = n / 128;
+  const int64_t nchunks = (ngroups + WARPS - 1) / WARPS;
+  for (int64_t c = blockIdx.x; c < nchunks; c += gridDim.x) {
+    const int64_t g0 = c * WARPS, grp = g0 + w;
+    if (grp < ngroups) {
+      uint32_t keep[PL][4];
 #pragma unroll
-    for (int it = 0; it < 4; it++) {
-      T v = x[grp * 128 + it * 32 + lane];
+      for (int it = 0; it < 4; it++) {
+        T v = x[grp * 128 + it * 32 + lane];
 #pragma unroll
-      for (int h = 0; h < PL; h++) keep[h][it] = warp_transpose32((uint32_t)(v >> (32 * h)), lane);
+        for (int h = 0; h < PL; h++) keep[h][it] = warp_transpose32((uint32_t)(v >> (32 * h)), lane);
+      }
+#pragma unroll
+      for (int q = 0; q < PL; q++) tile[q * 32 + lane][w] = make_uint4(keep[q][0], keep[q][1], keep[q][2], keep[q][3]);
     }
-#pragma unroll
-    for (int q = 0; q < PL; q++) {
-      int p = q * 32 + lane;
-      uint4 *dst = (uint4 *)(out + ((int64_t)p * n + grp * 128) / 32);
-      *dst = make_uint4(keep[q][0], keep[q][1], keep[q][2], keep[q][3]);
+    __syncthreads();
+    uint4 *o = (uint4 *)out;
+    for (int idx = threadIdx.x; idx < KBITS * WARPS; idx += TPB) {
+      const int p = idx / WARPS, j = idx % WARPS;
+      if (g0 + j < ngroups) o[(int64_t)p * ngroups + g0 + j] = tile[p][j];
     }
+    __syncthreads();
   }
 }
 
@@ -137,7 +145,7 @@ int k_bit_decompose(mb_ctx *ctx, const mb_tensor *x, mb_tensor *out) {
   uint32_t *o = (uint32_t *)out->dptr;
   if (n % 128 == 0) {
     int64_t warps = n / 128;
-    int g = (int)std::min<int64_t>((warps * 32 + TPB - 1) / TPB, (int64_t)ctx->sm_count * 8);
+    int g = (int)std::max<int64_t>(1, std::min<int64_t>((warps * 32 + TPB - 1) / TPB, (int64_t)ctx->sm_count * 8));
     if (x->dtype == MB_RING128)
       bit_decompose_aligned_kernel<u128, 128><<<g, TPB, 0, ctx->stream>>>((const u128 *)x->dptr, o, n);
     else

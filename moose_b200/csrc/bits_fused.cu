@@ -52,33 +52,42 @@ __device__ __forceinline__ uint32_t warp_transpose32(uint32_t x, int lane) {
 }
 
 // bit planes of (x0 + x1) and of x2: [KBITS, n] packed, n % 128 == 0.  A warp transposes 128 elements x KBITS
-// bits as KBITS/32 x 4 blocks of 32 x 32 bits; lane l ends up with planes l, l+32, ... and stores 16 bytes each.
+// bits as KBITS/32 x 4 blocks of 32 x 32 bits; lane l ends up with 16 bytes of planes l, l+32, ...  The eight warps
+// of a CTA take eight consecutive groups and exchange through shared memory, so that every plane receives one full
+// 128-byte line per store instead of eight scattered 16-byte pieces.
 template <typename T, int KBITS>
 __global__ void __launch_bounds__(TPB) split_planes_kernel(const T *__restrict__ x0, const T *__restrict__ x1,
                                                           const T *__restrict__ x2, uint32_t *__restrict__ outB,
                                                           uint32_t *__restrict__ outC, int64_t n) {
-  const int lane = threadIdx.x & 31;
-  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  const int64_t ngroups = n / 128;
+  constexpr int WARPS = TPB / 32;
   constexpr int PL = KBITS / 32;
-  for (int64_t grp = warp; grp < 2 * ngroups; grp += nwarps) {
-    const bool second = grp >= ngroups;  // first half of the work list: B = bits(x0 + x1); second half: C = bits(x2)
-    const int64_t g = second ? grp - ngroups : grp;
-    uint32_t keep[PL][4];
+  __shared__ uint4 tile[KBITS][WARPS];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int64_t ngroups = n / 128;
+  const int64_t nchunks = (ngroups + WARPS - 1) / WARPS;  // chunks of WARPS consecutive groups, per half
+  for (int64_t c = blockIdx.x; c < 2 * nchunks; c += gridDim.x) {
+    const bool second = c >= nchunks;  // first half of the work list: B = bits(x0 + x1); second half: C = bits(x2)
+    const int64_t g0 = (second ? c - nchunks : c) * WARPS, g = g0 + w;
+    if (g < ngroups) {
+      uint32_t keep[PL][4];
 #pragma unroll
-    for (int it = 0; it < 4; it++) {
-      const int64_t e = g * 128 + it * 32 + lane;
-      T v = second ? x2[e] : (T)(x0[e] + x1[e]);
+      for (int it = 0; it < 4; it++) {
+        const int64_t e = g * 128 + it * 32 + lane;
+        T v = second ? x2[e] : (T)(x0[e] + x1[e]);
 #pragma unroll
-      for (int h = 0; h < PL; h++) keep[h][it] = warp_transpose32((uint32_t)(v >> (32 * h)), lane);
+        for (int h = 0; h < PL; h++) keep[h][it] = warp_transpose32((uint32_t)(v >> (32 * h)), lane);
+      }
+#pragma unroll
+      for (int q = 0; q < PL; q++) tile[q * 32 + lane][w] = make_uint4(keep[q][0], keep[q][1], keep[q][2], keep[q][3]);
     }
-    uint32_t *out = second ? outC : outB;
-#pragma unroll
-    for (int q = 0; q < PL; q++) {
-      const int p = q * 32 + lane;
-      *(uint4 *)(out + ((int64_t)p * n + g * 128) / 32) = make_uint4(keep[q][0], keep[q][1], keep[q][2], keep[q][3]);
+    __syncthreads();
+    uint4 *out = (uint4 *)(second ? outC : outB);
+    const int64_t row_vecs = n / 128;  // 16-byte vectors per plane
+    for (int idx = threadIdx.x; idx < KBITS * WARPS; idx += TPB) {
+      const int p = idx / WARPS, j = idx % WARPS;
+      if (g0 + j < ngroups) out[(int64_t)p * row_vecs + g0 + j] = tile[p][j];
     }
+    __syncthreads();
   }
 }
 
