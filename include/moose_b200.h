@@ -109,6 +109,15 @@ int mb_tensor_alloc(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape,
  * synchronises the stream. */
 int mb_tensor_to_host(mb_ctx *ctx, const mb_tensor *t, void *host_out, size_t nbytes);
 int mb_tensor_free(mb_ctx *ctx, mb_tensor *t);
+/* Asynchronous transfers for callers that overlap H2D / compute / D2H with several contexts on one device (one
+ * stream each): the host buffers must be page-locked (mb_host_alloc_pinned) and stay untouched until the stream
+ * has passed the copy.  mb_ctx_wait orders the contexts: work enqueued on `ctx` afterwards starts only when
+ * everything enqueued on `other` so far has finished.  A tensor must be freed through a context whose stream is
+ * ordered after its last use. */
+int mb_tensor_from_host_async(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, const void *pinned_host,
+                              mb_tensor **out);
+int mb_tensor_to_host_async(mb_ctx *ctx, const mb_tensor *t, void *pinned_host_out, size_t nbytes);
+int mb_ctx_wait(mb_ctx *ctx, mb_ctx *other);
 /* Device-to-device copies between a tensor and a caller-owned device buffer of mb_tensor_nbytes bytes,
  * asynchronous on the context stream (for callers that move tensors with their own transport, e.g.
  * NCCL send/recv in party-per-GPU mode: the Send/Receive ops of moose/src/networking/mod.rs:16-54). */

@@ -69,6 +69,8 @@ ABI = {
     "mb_host_alloc_pinned": [_P, ctypes.c_size_t, _PP], "mb_host_free_pinned": [_P, _P],
     "mb_tensor_from_host": [_P, _I, _I, _I64P, _P, _PP], "mb_tensor_alloc": [_P, _I, _I, _I64P, _PP],
     "mb_tensor_to_host": [_P, _P, _P, ctypes.c_size_t], "mb_tensor_free": [_P, _P],
+    "mb_tensor_from_host_async": [_P, _I, _I, _I64P, _P, _PP], "mb_tensor_to_host_async": [_P, _P, _P, ctypes.c_size_t],
+    "mb_ctx_wait": [_P, _P],
     "mb_tensor_copy_to_device": [_P, _P, _P], "mb_tensor_copy_from_device": [_P, _P, _P],
     "mb_tensor_dtype": [_P], "mb_tensor_rank": [_P], "mb_tensor_shape": [_P], "mb_tensor_numel": [_P],
     "mb_tensor_nbytes": [_P], "mb_tensor_device_ptr": [_P], "mb_reshape": [_P, _P, _I, _I64P, _PP],
@@ -379,6 +381,21 @@ class Session:
         lo = np.array([v & ((1 << 64) - 1) for v in flat], dtype=np.uint64)
         hi = np.array([v >> 64 for v in flat], dtype=np.uint64)
         return self.from_host(RING128, np.stack([lo, hi], axis=-1).reshape(tuple(shape) + (2,)))
+
+    def from_host_async(self, dtype: int, pinned: np.ndarray, shape: Optional[Sequence[int]] = None) -> Tensor:
+        """H2D copy of a page-locked array (Session.pinned_empty) enqueued on this session's stream, no wait."""
+        if shape is None:
+            shape = pinned.shape[:-1] if dtype == RING128 else pinned.shape
+        arr, rank = _shape_arr(shape)
+        out = self._out()
+        return self._t(lib().mb_tensor_from_host_async(self.ctx, dtype, rank, arr, pinned.ctypes.data_as(_P), ctypes.byref(out)), out)
+
+    def to_host_async(self, x: Tensor, pinned_out: np.ndarray):
+        self._check(lib().mb_tensor_to_host_async(self.ctx, x.h, pinned_out.ctypes.data_as(_P), pinned_out.nbytes))
+
+    def wait(self, other: "Session"):
+        """Work enqueued on this session from now on starts after everything enqueued on `other` so far."""
+        self._check(lib().mb_ctx_wait(self.ctx, other.ctx))
 
     def from_bits(self, values) -> Tensor:
         a = np.asarray(values, dtype=np.uint8)

@@ -298,6 +298,45 @@ extern "C" int mb_tensor_from_host(mb_ctx *ctx, mb_dtype dtype, int rank, const 
   return MB_OK;
 }
 
+// Asynchronous forms for callers that pipeline transfers against compute with several contexts on one device
+// (loader / compute / drainer streams): the host buffers must be page-locked and stay valid until the stream has
+// passed the copy; ordering between contexts is the caller's (mb_ctx_wait).
+extern "C" int mb_tensor_from_host_async(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, const void *pinned_host,
+                                         mb_tensor **out) {
+  if (!ctx || !out || !pinned_host) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_tensor_from_host_async: NULL argument");
+  MB_CUDA(ctx, cudaSetDevice(ctx->device));
+  mb_tensor *t = nullptr;
+  MB_CHECK(mb_tensor_new(ctx, dtype, rank, shape, &t));
+  if (t->nbytes) {
+    cudaError_t e = cudaMemcpyAsync(t->dptr, pinned_host, t->nbytes, cudaMemcpyHostToDevice, ctx->stream);
+    if (e != cudaSuccess) {
+      mb_tensor_free(ctx, t);
+      return mb_fail(ctx, MB_ERR_CUDA, std::string("cudaMemcpyAsync H2D: ") + cudaGetErrorString(e));
+    }
+  }
+  *out = t;
+  return MB_OK;
+}
+
+extern "C" int mb_tensor_to_host_async(mb_ctx *ctx, const mb_tensor *t, void *pinned_host_out, size_t nbytes) {
+  if (!ctx || !t || (!pinned_host_out && nbytes)) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_tensor_to_host_async: NULL");
+  if (nbytes != t->nbytes) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_tensor_to_host_async: size mismatch");
+  MB_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (nbytes) MB_CUDA(ctx, cudaMemcpyAsync(pinned_host_out, t->dptr, nbytes, cudaMemcpyDeviceToHost, ctx->stream));
+  return MB_OK;
+}
+
+// Work enqueued on `ctx` after this call starts only when everything enqueued on `other` so far has finished.
+extern "C" int mb_ctx_wait(mb_ctx *ctx, mb_ctx *other) {
+  if (!ctx || !other) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_wait: NULL context");
+  if (ctx->device != other->device) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_wait: contexts on different devices");
+  MB_CUDA(ctx, cudaSetDevice(ctx->device));
+  std::lock_guard<std::mutex> lock(other->mu);
+  MB_CUDA(ctx, cudaEventRecord(other->ev1, other->stream));
+  MB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, other->ev1, 0));
+  return MB_OK;
+}
+
 extern "C" int mb_tensor_to_host(mb_ctx *ctx, const mb_tensor *t, void *host_out, size_t nbytes) {
   if (!ctx || !t || (!host_out && nbytes)) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_tensor_to_host: NULL");
   if (nbytes != t->nbytes) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_tensor_to_host: size mismatch");
