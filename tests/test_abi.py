@@ -73,3 +73,18 @@ def test_host_side_aes_key_schedule():
     assert out.raw.hex() == "69c4e0d86a7b0430d8cdb78070b4c55a"  # FIPS-197 C.1
     lib.mb_selftest_aes_block(bytes(16), bytes(16), out)
     assert out.raw == mo.aes_ctr(bytes(16), 0, 1)
+
+
+def test_generated_rust_ffi_is_in_sync():
+    """integration/rust/b200_ffi.rs (the extern block for the Rust shim) is generated from the
+    header: regenerating must reproduce the committed file and cover every ABI entry."""
+    import re
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    path = os.path.join(root, "integration", "rust", "b200_ffi.rs")
+    before = open(path).read()
+    subprocess.run([sys.executable, os.path.join(root, "tools", "gen_rust_ffi.py")], check=True, capture_output=True)
+    assert open(path).read() == before
+    import moose_b200 as mb
+    assert set(re.findall(r"pub fn (mb_\w+)\(", before)) == set(mb.ABI)
