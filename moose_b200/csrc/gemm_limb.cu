@@ -409,7 +409,10 @@ limb_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 //   tmem_full       : per CTA (multicast commit); tmem_empty: leader's, all 256 epilogue threads arrive remotely
 constexpr int A2_SLOTS = 6, B2_SLOTS = 6;
 constexpr int B2_TILE_BYTES = (MAX_BLOCK_N / 2) * BLOCK_K;  // 16 KB: half of the B tile per CTA
-constexpr int SMEM2_BYTES = A2_SLOTS * A_TILE_BYTES + B2_SLOTS * B2_TILE_BYTES + 1024 + 256;
+// epilogue staging: each of the 4 epilogue warps transposes 32 rows x 32 u64 through shared memory (row stride 33)
+constexpr int STAGE_STRIDE = 33;
+constexpr int STAGE_BYTES = 4 * 32 * STAGE_STRIDE * 8;
+constexpr int SMEM2_BYTES = A2_SLOTS * A_TILE_BYTES + B2_SLOTS * B2_TILE_BYTES + 1024 + 256 + STAGE_BYTES;
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
@@ -630,34 +633,42 @@ limb_gemm_kernel_2cta(const __grid_constant__ CUtensorMap map_a, const __grid_co
     }
   } else {
     // ===================== epilogue (both CTAs; this CTA owns rows m0 + 128 rank ..) =====================
+    // TMEM hands lane r the 32 columns of row r.  Written directly, every store instruction would touch 32 rows
+    // with 16 bytes each; the warp transposes through shared memory instead so that a store instruction covers two
+    // rows with 256 contiguous bytes each (8x fewer memory transactions for the 4 GB of partial sums per launch).
     uint32_t acc_phase = 0;
     WorkItem w;
+    unsigned long long *stage = (unsigned long long *)((uint8_t *)bars + 256) + (size_t)warp * 32 * STAGE_STRIDE;
+    const int half = lane >> 4, cpair = (lane & 15) * 2;
     for (int item = 0; next_item_2cta(p, item, w); item++) {
-      const int row = w.m0 + (int)rank * BLOCK_M + warp * 32 + lane;
+      const int row0 = w.m0 + (int)rank * BLOCK_M + warp * 32;
+      const int row = row0 + lane;
       const int n0 = w.n0;
       mbar_wait_relaxed(tmem_full, acc_phase);
       tcgen05_fence_after();
-      unsigned long long *out =
-          p.partials + (((size_t)w.batch * p.num_passes + (size_t)w.pass) * p.M + (size_t)row) * p.N + n0;
+      unsigned long long *tile_out = p.partials + (((size_t)w.batch * p.num_passes + (size_t)w.pass) * p.M) * p.N + n0;
+      unsigned long long *out = tile_out + (size_t)row * p.N;
       for (int c = 0; c < p.block_n; c += 32) {
         uint32_t lo[32], hi[32];
         const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c;
         tmem_ld32(taddr, lo);
         tmem_ld32(taddr + MAX_BLOCK_N, hi);
         tmem_ld_wait();
-        if (row < p.M) {
-          if (n0 + c + 32 <= p.N) {
+        if (n0 + c + 32 <= p.N) {
 #pragma unroll
-            for (int q = 0; q < 32; q += 2) {
-              unsigned long long v0 = (unsigned long long)lo[q] + ((unsigned long long)hi[q] << 8);
-              unsigned long long v1 = (unsigned long long)lo[q + 1] + ((unsigned long long)hi[q + 1] << 8);
-              *(ulonglong2 *)(out + c + q) = make_ulonglong2(v0, v1);
-            }
-          } else {
+          for (int q = 0; q < 32; q++) stage[lane * STAGE_STRIDE + q] = (unsigned long long)lo[q] + ((unsigned long long)hi[q] << 8);
+          __syncwarp();
+#pragma unroll 4
+          for (int r2 = 0; r2 < 32; r2 += 2) {
+            const int rr = r2 + half;
+            const unsigned long long v0 = stage[rr * STAGE_STRIDE + cpair], v1 = stage[rr * STAGE_STRIDE + cpair + 1];
+            if (row0 + rr < p.M) *(ulonglong2 *)(tile_out + (size_t)(row0 + rr) * p.N + c + cpair) = make_ulonglong2(v0, v1);
+          }
+          __syncwarp();
+        } else if (row < p.M) {
 #pragma unroll
-            for (int q = 0; q < 32; q++) {
-              if (n0 + c + q < p.N) out[c + q] = (unsigned long long)lo[q] + ((unsigned long long)hi[q] << 8);
-            }
+          for (int q = 0; q < 32; q++) {
+            if (n0 + c + q < p.N) out[c + q] = (unsigned long long)lo[q] + ((unsigned long long)hi[q] << 8);
           }
         }
       }

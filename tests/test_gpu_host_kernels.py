@@ -324,3 +324,32 @@ def test_plaintext_helpers_parity(sess, bits):
     # broadcasting compare: [7,19] vs [19]
     v = rand_ring(rng, bits, (19,))
     assert same_bits(sess.less(A, sess.from_host(DT[bits], v)), mo.host_less(oa, mo.Ring(bits, v)))
+
+
+def test_async_transfers_across_contexts():
+    """mb_tensor_from_host_async / mb_tensor_to_host_async / mb_ctx_wait: loader -> compute -> drainer contexts on one
+    device give the same bytes as the synchronous path."""
+    loader, compute, drainer = (mb.Session(0, SESSION_ID, ENTROPY_KEY) for _ in range(3))
+    try:
+        rng = np.random.default_rng(21)
+        n = 1 << 20
+        ha, hb, hout = (loader.pinned_empty((n, 2), np.uint64) for _ in range(3))
+        ha[...] = rand_ring(rng, 128, (n,))
+        hb[...] = rand_ring(rng, 128, (n,))
+        for _ in range(3):
+            a, b = loader.from_host_async(RING128, ha), loader.from_host_async(RING128, hb)
+            compute.wait(loader)
+            c = compute.mul(compute.add(a, b), b)
+            c.sess = drainer
+            drainer.wait(compute)
+            drainer.to_host_async(c, hout)
+            loader.wait(compute)
+            del a, b
+            drainer.sync()
+            assert np.array_equal(hout, mo.mul(mo.add(mo.Ring(128, ha), mo.Ring(128, hb)), mo.Ring(128, hb)).data)
+            del c
+        with pytest.raises(mb.MooseB200Error):
+            drainer.to_host_async(compute.fill(RING64, 1, (4,)), hout)
+    finally:
+        for s in (loader, compute, drainer):
+            s.close()

@@ -68,6 +68,17 @@ def _party_worker(rank, world, port, q):
     else:
         got = (comm.recv("alice"), comm.recv("alice"), comm.recv("alice"))
         comm.send(bytes(reversed(seed)), "alice")
+    # the raw-buffer transport the native executor calls (mb_transport_fn): header + host payload, then a poll
+    import ctypes
+    hdr = (ctypes.c_int64 * 10)(*([1, 0, 0, 0, 0, 0, 0, 0, 0, 16] if rank == 0 else [0] * 10))
+    payload = (ctypes.c_uint8 * 16)(*(range(100, 116) if rank == 0 else [0] * 16))
+    peer = b"bob" if rank == 0 else b"alice"
+    mode = 1 if rank == 0 else 0
+    rc = comm.transport(None, mode, peer, ctypes.addressof(hdr), ctypes.sizeof(hdr), 0)
+    rc |= comm.transport(None, mode, peer, ctypes.addressof(payload), 16, 0)
+    done = ctypes.c_int64(-1)
+    rc |= comm.transport(None, 3, b"", ctypes.addressof(done), 8, 0)
+    got = (got, rc, list(hdr), bytes(payload), done.value)
     q.put((rank, got))
     dist.barrier()
     dist.destroy_process_group()
@@ -86,5 +97,7 @@ def test_party_wire_format_over_gloo():
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
-    assert res[1] == (bytes(range(16)), (65536, 512), None)
-    assert res[0] == bytes(reversed(range(16)))
+    assert res[1][0] == (bytes(range(16)), (65536, 512), None)
+    assert res[0][0] == bytes(reversed(range(16)))
+    for r in (0, 1):  # transport callback: both sides succeed, the receiver sees header and payload, no device sends pending
+        assert res[r][1] == 0 and res[r][2] == [1, 0, 0, 0, 0, 0, 0, 0, 0, 16] and res[r][3] == bytes(range(100, 116)) and res[r][4] == 0
