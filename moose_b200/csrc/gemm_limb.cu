@@ -634,12 +634,11 @@ limb_gemm_kernel_2cta(const __grid_constant__ CUtensorMap map_a, const __grid_co
   } else {
     // ===================== epilogue (both CTAs; this CTA owns rows m0 + 128 rank ..) =====================
     // TMEM hands lane r the 32 columns of row r.  Written directly, every store instruction would touch 32 rows
-    // with 16 bytes each; the warp transposes through shared memory instead so that a store instruction covers two
-    // rows with 256 contiguous bytes each (8x fewer memory transactions for the 4 GB of partial sums per launch).
+    // with 16 bytes each; the warp transposes through shared memory instead so that a store instruction covers one
+    // row with 256 contiguous bytes (8x fewer memory transactions for the 4 GB of partial sums per launch).
     uint32_t acc_phase = 0;
     WorkItem w;
     unsigned long long *stage = (unsigned long long *)((uint8_t *)bars + 256) + (size_t)warp * 32 * STAGE_STRIDE;
-    const int half = lane >> 4, cpair = (lane & 15) * 2;
     for (int item = 0; next_item_2cta(p, item, w); item++) {
       const int row0 = w.m0 + (int)rank * BLOCK_M + warp * 32;
       const int row = row0 + lane;
@@ -658,11 +657,10 @@ limb_gemm_kernel_2cta(const __grid_constant__ CUtensorMap map_a, const __grid_co
 #pragma unroll
           for (int q = 0; q < 32; q++) stage[lane * STAGE_STRIDE + q] = (unsigned long long)lo[q] + ((unsigned long long)hi[q] << 8);
           __syncwarp();
-#pragma unroll 4
-          for (int r2 = 0; r2 < 32; r2 += 2) {
-            const int rr = r2 + half;
-            const unsigned long long v0 = stage[rr * STAGE_STRIDE + cpair], v1 = stage[rr * STAGE_STRIDE + cpair + 1];
-            if (row0 + rr < p.M) *(ulonglong2 *)(tile_out + (size_t)(row0 + rr) * p.N + c + cpair) = make_ulonglong2(v0, v1);
+#pragma unroll 8
+          for (int rr = 0; rr < 32; rr++) {  // one row per instruction: 32 lanes x 8 bytes = 256 contiguous bytes
+            const unsigned long long v = stage[rr * STAGE_STRIDE + lane];
+            if (row0 + rr < p.M) tile_out[(size_t)(row0 + rr) * p.N + c + lane] = v;
           }
           __syncwarp();
         } else if (row < p.M) {
