@@ -470,6 +470,39 @@ int mb_exec_value(mb_exec *e, const char *op_name, int *kind, mb_tensor **tensor
 int mb_exec_output(mb_exec *e, int saved, const char *key, mb_tensor **tensor);
 const char *mb_exec_output_key(const mb_exec *e, int saved, int64_t i);
 
+/* ------------------------------------------------------- party per process */
+
+/* ONE party of the replicated protocols per process / GPU (BASELINE config 5).  Party `me` holds the shares
+ * (x_me, x_{me+1}) of every replicated tensor (mb_pshare) and computes what player `me` computes in the reference
+ * (moose/src/replicated/{setup,zero_share,convert,arith,fixedpoint,bits,misc,compare,softmax}.rs,
+ * moose/src/additive/{convert,trunc,dabit}.rs); what the reference moves between hosts -- reshares, the dealer's
+ * messages, openings -- goes through the transport (same callback contract as mb_exec_set_transport; role_names[i]
+ * is the peer name handed to it for party i).  The three parties must issue the same sequence of calls.  The
+ * heavy steps are the fused kernels of the single-GPU path restricted to this party's component: msb-pruned
+ * Kogge-Stone levels with one exchange per level, the two-term tensor-pipe GEMM. */
+typedef struct mb_party mb_party;
+typedef struct mb_pshare mb_pshare;
+int mb_party_create(mb_ctx *ctx, int me, mb_transport_fn fn, void *user, const char *const role_names[3], mb_party **out);
+int mb_party_free(mb_party *p);
+int mb_party_flush(mb_party *p); /* waits for every posted send */
+uint64_t mb_party_bytes_sent(const mb_party *p);
+int mb_pshare_free(mb_party *p, mb_pshare *s);
+const mb_tensor *mb_pshare_tensor(const mb_pshare *s, int i); /* i = 0: share me, 1: share me+1 (borrowed) */
+/* ShareOp (convert.rs:49-160): x is the plaintext on the owner (NULL elsewhere); dtype / shape on every party. */
+int mb_party_share(mb_party *p, int owner, const mb_tensor *x, mb_dtype dtype, int rank, const int64_t *shape, mb_pshare **out);
+/* RevealOp (convert.rs:280-313): *out is the value on the receiver, NULL on the other parties. */
+int mb_party_reveal(mb_party *p, int receiver, const mb_pshare *x, mb_tensor **out);
+int mb_party_add(mb_party *p, const mb_pshare *x, const mb_pshare *y, mb_pshare **out);
+int mb_party_sub(mb_party *p, const mb_pshare *x, const mb_pshare *y, mb_pshare **out);
+int mb_party_add_public(mb_party *p, const mb_pshare *x, const mb_tensor *pub, mb_pshare **out);
+int mb_party_mul(mb_party *p, const mb_pshare *x, const mb_pshare *y, mb_pshare **out);
+int mb_party_dot(mb_party *p, const mb_pshare *x, const mb_pshare *y, mb_pshare **out);
+int mb_party_trunc_pr(mb_party *p, uint32_t amount, const mb_pshare *x, mb_pshare **out);
+int mb_party_msb(mb_party *p, const mb_pshare *x, mb_pshare **out_bits);
+int mb_party_ring_inject(mb_party *p, mb_dtype ring, uint64_t bit_idx, const mb_pshare *x_bits, mb_pshare **out);
+int mb_party_less(mb_party *p, const mb_pshare *x, const mb_pshare *y, mb_pshare **out_bits);
+int mb_party_maximum(mb_party *p, const mb_pshare *const *xs, int n, mb_pshare **out);
+
 /* Selects the ring-GEMM implementation used by mb_dot / mb_rep_dot:
  * 0 = automatic (int8 tensor pipe for large shapes, 64-bit IMAD CUDA-core
  * kernel for skinny / small ones), 1 = force IMAD, 2 = force tensor pipe

@@ -120,15 +120,6 @@ __global__ void __launch_bounds__(AES_TPB_LIGHT) adder_init_kernel(AesKey k_shar
   }
 }
 
-struct LevelDesc {
-  int nout;                 // number of output planes
-  int shift;                // 2^i
-  unsigned char plane[128]; // output plane numbers
-  unsigned char gslot[128]; // input slot of plane q in g_in (255 = not stored)
-  unsigned char pslot[128]; // input slot of plane q in p_in
-  unsigned char pout[128];  // output slot in p_out for output index j (255 = p' not needed)
-};
-
 __device__ __forceinline__ void rep_and3(const vec_t x[3], const vec_t y[3], const vec_t r[3], vec_t z[3]) {
   // z_i = x_i&y_i ^ x_i&y_{i+1} ^ x_{i+1}&y_i ^ (r_i ^ r_{i+1})   (arith.rs:342-358, zero_share.rs:96-106)
 #pragma unroll
@@ -192,6 +183,47 @@ __global__ void __launch_bounds__(AES_TPB_384) adder_level_kernel(AesKey pg0, Ae
       const int64_t op = (int64_t)d.pout[j] * nv + v;
 #pragma unroll
       for (int i = 0; i < 3; i++) p_out.s[i][op] = z[i];
+    }
+  }
+}
+
+// The same level for ONE party of a party-per-GPU run: it holds components me and me+1 of g and p (arrays s[0], s[1])
+// and computes component me of g' and p'; component me+1 arrives from the next party.  Zero share: r_me ^ r_{me+1}.
+struct PairPtrs {
+  const vec_t *s[2];
+};
+__global__ void __launch_bounds__(AES_TPB_MID) adder_level_party_kernel(AesKey pg_a, AesKey pg_b, AesKey pp_a, AesKey pp_b, LevelDesc d,
+                                                                       PairPtrs g_in, PairPtrs p_in, vec_t *__restrict__ g_out,
+                                                                       vec_t *__restrict__ p_out, int64_t nv) {
+  extern __shared__ __align__(16) uint32_t sT[];
+  aes_load_table(sT);
+  const AesLane L = aes_lane(sT);
+  const int64_t total = (int64_t)d.nout * nv;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int j = (int)(t / nv);
+    const int64_t v = t - (int64_t)j * nv;
+    const int q = d.plane[j];
+    const uint64_t pos = (uint64_t)q * (uint64_t)nv + (uint64_t)v;
+    const int64_t ig = (int64_t)d.gslot[q] * nv + v, ip = (int64_t)d.pslot[q] * nv + v;
+    const vec_t G0 = g_in.s[0][ig], P0 = p_in.s[0][ip], P1 = p_in.s[1][ip];
+    const bool shifted = q >= d.shift;
+    const bool want_p = d.pout[j] != 255;
+    vec_t Gs0 = vzero(), Gs1 = vzero(), Ps0 = vzero(), Ps1 = vzero();
+    if (shifted) {
+      const int64_t jg = (int64_t)d.gslot[q - d.shift] * nv + v;
+      Gs0 = g_in.s[0][jg];
+      Gs1 = g_in.s[1][jg];
+      if (want_p) {
+        const int64_t jp = (int64_t)d.pslot[q - d.shift] * nv + v;
+        Ps0 = p_in.s[0][jp];
+        Ps1 = p_in.s[1][jp];
+      }
+    }
+    vec_t z = vxor(vxor(vand(P0, vxor(Gs0, Gs1)), vand(P1, Gs0)), vxor(prf_vec<VK_BIT>(L, pg_a, pos), prf_vec<VK_BIT>(L, pg_b, pos)));
+    g_out[(int64_t)j * nv + v] = vxor(G0, z);
+    if (want_p) {
+      z = vxor(vxor(vand(P0, vxor(Ps0, Ps1)), vand(P1, Ps0)), vxor(prf_vec<VK_BIT>(L, pp_a, pos), prf_vec<VK_BIT>(L, pp_b, pos)));
+      p_out[(int64_t)d.pout[j] * nv + v] = z;
     }
   }
 }
@@ -430,6 +462,83 @@ int k_ring_inject_fused(mb_ctx *ctx, const AesKey &k_br0, const AesKey &k_y0, co
   else
     AES_LAUNCH(ctx, ring_inject_fused_kernel<VK_RING64>, AES_TPB_LIGHT, nvec, ARGS, bit_idx & 63);
 #undef ARGS
+  MB_LAUNCH_CHECK(ctx);
+  return MB_OK;
+}
+
+// Plane sets per level of the msb-only adder (the recurrence walked backwards from plane k-2 of the final g) and the
+// level descriptors, shared by the all-party kernel above and the party-per-GPU path (party.cpp).
+int k_adder_plan_msb(int k, std::vector<LevelDesc> *levels_out, std::vector<int> *np_out, int *final_gslot) {
+  const int levels = k == 128 ? 7 : 6;
+  std::vector<std::vector<int>> need_g((size_t)levels + 1), need_p((size_t)levels + 1);
+  std::vector<char> ng((size_t)k, 0), np((size_t)k, 0);
+  ng[(size_t)k - 2] = 1;
+  for (int i = levels; i >= 0; i--) {
+    for (int q = 0; q < k; q++) {
+      if (ng[(size_t)q]) need_g[(size_t)i].push_back(q);
+      if (np[(size_t)q]) need_p[(size_t)i].push_back(q);
+    }
+    if (i == 0) break;
+    const int s = 1 << (i - 1);
+    std::vector<char> g2((size_t)k, 0), p2((size_t)k, 0);
+    for (int q = 0; q < k; q++) {
+      if (ng[(size_t)q]) {
+        g2[(size_t)q] = 1;
+        p2[(size_t)q] = 1;
+        if (q >= s) g2[(size_t)(q - s)] = 1;
+      }
+      if (np[(size_t)q]) {
+        p2[(size_t)q] = 1;
+        if (q >= s) p2[(size_t)(q - s)] = 1;
+      }
+    }
+    ng = g2;
+    np = p2;
+  }
+  std::vector<int> gslot((size_t)k), pslot((size_t)k);
+  for (int q = 0; q < k; q++) gslot[(size_t)q] = pslot[(size_t)q] = q;
+  levels_out->clear();
+  np_out->clear();
+  for (int i = 0; i < levels; i++) {
+    LevelDesc d;
+    memset(&d, 255, sizeof(d));
+    d.shift = 1 << i;
+    d.nout = (int)need_g[(size_t)i + 1].size();
+    for (int q = 0; q < k; q++) {
+      d.gslot[q] = (unsigned char)(gslot[(size_t)q] < 0 ? 255 : gslot[(size_t)q]);
+      d.pslot[q] = (unsigned char)(pslot[(size_t)q] < 0 ? 255 : pslot[(size_t)q]);
+    }
+    std::vector<int> pslot_next((size_t)k, -1), gslot_next((size_t)k, -1);
+    int npo = 0;
+    for (int j = 0; j < d.nout; j++) {
+      const int q = need_g[(size_t)i + 1][(size_t)j];
+      d.plane[j] = (unsigned char)q;
+      gslot_next[(size_t)q] = j;
+      const auto &np1 = need_p[(size_t)i + 1];
+      if (std::find(np1.begin(), np1.end(), q) != np1.end()) {
+        d.pout[j] = (unsigned char)npo;
+        pslot_next[(size_t)q] = npo++;
+      }
+    }
+    levels_out->push_back(d);
+    np_out->push_back(npo);
+    gslot = gslot_next;
+    pslot = pslot_next;
+  }
+  *final_gslot = gslot[(size_t)k - 2];
+  return MB_OK;
+}
+
+// keys: zero-share streams (me, me+1) of AND(p, g1), then of AND(p, p1).  g_in / p_in: this party's two components.
+int k_party_adder_level(mb_ctx *ctx, const AesKey keys[4], const LevelDesc &d, const mb_tensor *const g_in[2],
+                        const mb_tensor *const p_in[2], mb_tensor *g_out, mb_tensor *p_out, int64_t nv) {
+  PairPtrs g, p;
+  for (int c = 0; c < 2; c++) {
+    g.s[c] = (const vec_t *)g_in[c]->dptr;
+    p.s[c] = (const vec_t *)p_in[c]->dptr;
+  }
+  AES_LAUNCH(ctx, adder_level_party_kernel, AES_TPB_MID, (int64_t)d.nout * nv, keys[0], keys[1], keys[2], keys[3], d, g, p,
+             (vec_t *)g_out->dptr, (vec_t *)p_out->dptr, nv);
   MB_LAUNCH_CHECK(ctx);
   return MB_OK;
 }

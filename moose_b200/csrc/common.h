@@ -159,6 +159,19 @@ int k_gemm_limb_batched(mb_ctx *ctx, mb_dtype dtype, const LimbOperandA *As, int
                         const int (*a_idx)[2], const int (*b_idx)[2], int nbatch, int nterms, void *const *C,
                         int64_t M, int64_t K, int64_t N);
 
+// One Kogge-Stone level on a pruned set of bit planes (bits_fused.cu)
+struct LevelDesc {
+  int nout;                 // number of output planes
+  int shift;                // 2^i
+  unsigned char plane[128]; // output plane numbers
+  unsigned char gslot[128]; // input slot of plane q in g_in (255 = not stored)
+  unsigned char pslot[128]; // input slot of plane q in p_in
+  unsigned char pout[128];  // output slot in p_out for output index j (255 = p' not needed)
+};
+int k_adder_plan_msb(int k, std::vector<LevelDesc> *levels_out, std::vector<int> *np_out, int *final_gslot);
+int k_party_adder_level(mb_ctx *ctx, const AesKey keys[4], const LevelDesc &d, const mb_tensor *const g_in[2],
+                        const mb_tensor *const p_in[2], mb_tensor *g_out, mb_tensor *p_out, int64_t nv);
+
 // Fused arithmetic->boolean conversion (bits_fused.cu)
 bool k_rep_adder_supported(const mb_tensor *x);
 int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only, mb_tensor *out[3]);

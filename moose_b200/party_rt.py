@@ -1,0 +1,172 @@
+"""One party of the replicated protocols per process / GPU: Python face of csrc/party.cpp (mb_party_* entry points).
+
+Each of the three parties creates a `PartySession` on its own GPU with the same session id and issues the same
+sequence of calls (SPMD); reshares, the dealer's messages and openings travel through the transport -- NCCL
+send/recv between the parties' GPUs (`NcclComm.transport` of moose_b200/executor.py), or the in-process
+`LocalTransport` below for tests that run the three parties as threads on one GPU.
+"""
+from __future__ import annotations
+
+import ctypes
+import queue
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+
+from . import FLOAT64, RING64, RING128, Session, Tensor, _shape_arr, lib
+from .executor import TRANSPORT_FN
+
+
+class PShare:
+    """This party's two shares (x_me, x_{me+1}) of a replicated tensor."""
+
+    def __init__(self, party: "PartySession", handle: int):
+        self.party, self.h = party, handle
+
+    def __del__(self):
+        try:
+            if self.h and self.party._p:
+                lib().mb_pshare_free(self.party._p, self.h)
+        except Exception:
+            pass
+        self.h = None
+
+    def share(self, i: int) -> Tensor:
+        return Tensor(self.party.sess, lib().mb_pshare_tensor(self.h, i), owned=False)
+
+
+class PartySession:
+    def __init__(self, sess: Session, me: int, transport, role_names: Sequence[str] = ("player0", "player1", "player2")):
+        """`transport`: a callable with the mb_transport_fn contract (mode, peer, buf, nbytes, on_device)."""
+        self.sess, self.me = sess, me
+        self._cb = TRANSPORT_FN(transport)
+        names = (ctypes.c_char_p * 3)(*[n.encode() for n in role_names])
+        self._names = names
+        self._p = ctypes.c_void_p()
+        sess._check(lib().mb_party_create(sess.ctx, me, self._cb, None, names, ctypes.byref(self._p)))
+
+    def close(self):
+        if self._p:
+            lib().mb_party_free(self._p)
+            self._p = ctypes.c_void_p()
+
+    @property
+    def bytes_sent(self) -> int:
+        return int(lib().mb_party_bytes_sent(self._p))
+
+    def flush(self):
+        self.sess._check(lib().mb_party_flush(self._p))
+
+    def _s(self, rc, out) -> PShare:
+        self.sess._check(rc)
+        return PShare(self, out.value)
+
+    def share(self, owner: int, x: Optional[Tensor], dtype: int, shape) -> PShare:
+        arr, rank = _shape_arr(shape)
+        out = ctypes.c_void_p()
+        return self._s(lib().mb_party_share(self._p, owner, x.h if x is not None else None, dtype, rank, arr, ctypes.byref(out)), out)
+
+    def reveal(self, receiver: int, x: PShare) -> Optional[Tensor]:
+        out = ctypes.c_void_p()
+        self.sess._check(lib().mb_party_reveal(self._p, receiver, x.h, ctypes.byref(out)))
+        return Tensor(self.sess, out.value) if out.value else None
+
+    def _bin(self, fn, x, y) -> PShare:
+        out = ctypes.c_void_p()
+        return self._s(fn(self._p, x.h, y.h, ctypes.byref(out)), out)
+
+    def add(self, x, y): return self._bin(lib().mb_party_add, x, y)
+    def sub(self, x, y): return self._bin(lib().mb_party_sub, x, y)
+    def mul(self, x, y): return self._bin(lib().mb_party_mul, x, y)
+    def dot(self, x, y): return self._bin(lib().mb_party_dot, x, y)
+    def less(self, x, y): return self._bin(lib().mb_party_less, x, y)
+    def add_public(self, x: PShare, pub: Tensor): return self._bin(lib().mb_party_add_public, x, pub)
+
+    def trunc_pr(self, amount: int, x: PShare) -> PShare:
+        out = ctypes.c_void_p()
+        return self._s(lib().mb_party_trunc_pr(self._p, amount, x.h, ctypes.byref(out)), out)
+
+    def msb(self, x: PShare) -> PShare:
+        out = ctypes.c_void_p()
+        return self._s(lib().mb_party_msb(self._p, x.h, ctypes.byref(out)), out)
+
+    def ring_inject(self, ring: int, bit_idx: int, x: PShare) -> PShare:
+        out = ctypes.c_void_p()
+        return self._s(lib().mb_party_ring_inject(self._p, ring, bit_idx, x.h, ctypes.byref(out)), out)
+
+    def maximum(self, xs: Sequence[PShare]) -> PShare:
+        arr = (ctypes.c_void_p * max(len(xs), 1))(*[x.h for x in xs])
+        out = ctypes.c_void_p()
+        return self._s(lib().mb_party_maximum(self._p, arr, len(xs), ctypes.byref(out)), out)
+
+
+class PartyMLP:
+    """pymoose MLPRegressor with ReLU = maximum([zeros, z]) (multilayer_perceptron_predictor.py:86-123), one party's
+    side: x comes from party 0, the mirrored weights are shared from party 0's copy, biases are public, the ReLU zeros
+    are shared by party 1, the logits are revealed to `reveal_to`."""
+
+    def __init__(self, party: PartySession, weights: Sequence[np.ndarray], biases: Sequence[np.ndarray], ring: int = RING64,
+                 frac: int = 23):
+        self.p, self.ring, self.frac = party, ring, frac
+        s = party.sess
+        enc = lambda a: s.fixedpoint_encode(ring, frac, s.from_host(FLOAT64, np.asarray(a, dtype=np.float64)))
+        self.w = [enc(w) for w in weights]
+        self.b = [enc(np.asarray(b).reshape(1, -1)) for b in biases]
+
+    def forward(self, x_fixed: Optional[Tensor], batch: int, reveal_to: int = 0) -> Optional[Tensor]:
+        p, s = self.p, self.p.sess
+        x = p.share(0, x_fixed if p.me == 0 else None, self.ring, (batch, self.w[0].shape[0]))
+        n = len(self.w)
+        for i in range(n):
+            w = p.share(0, self.w[i] if p.me == 0 else None, self.ring, self.w[i].shape)
+            z = p.add_public(p.trunc_pr(self.frac, p.dot(x, w)), self.b[i])
+            if i < n - 1:
+                shape = (batch, self.w[i].shape[1])
+                zeros = p.share(1, s.fill(self.ring, 0, shape) if p.me == 1 else None, self.ring, shape)
+                z = p.maximum([zeros, z])
+            x = z
+        out = p.reveal(reveal_to, x)
+        return s.fixedpoint_decode(self.frac, out) if out is not None else None
+
+
+class LocalTransport:
+    """In-process transport for three parties running as threads on one GPU (tests): values are staged in a device
+    tensor of the sender's session and handed over through a queue per directed pair."""
+
+    def __init__(self, names: Sequence[str] = ("player0", "player1", "player2")):
+        self.names = list(names)
+        self.q: Dict[tuple, "queue.Queue"] = {(a, b): queue.Queue() for a in names for b in names if a != b}
+
+    def endpoint(self, me: str, sess: Session):
+        def fn(_user, mode, peer, buf, nbytes, on_device):
+            try:
+                if mode >= 2:  # every send below is complete when it returns
+                    ctypes.cast(buf, ctypes.POINTER(ctypes.c_int64))[0] = fn.sent
+                    return 0
+                other = peer.decode()
+                if mode == 1:
+                    if on_device:
+                        if nbytes % 8:
+                            raise ValueError("device payloads are multiples of 8 bytes")
+                        stage = sess.alloc(RING64, (nbytes // 8,))
+                        sess._check(lib().mb_tensor_copy_from_device(sess.ctx, stage.h, buf))
+                        sess.sync()
+                        fn.sent += 1
+                        self.q[(me, other)].put(stage)
+                    else:
+                        self.q[(me, other)].put(bytes((ctypes.c_uint8 * nbytes).from_address(buf)))
+                else:
+                    item = self.q[(other, me)].get(timeout=120)
+                    if on_device:
+                        # the staging tensor belongs to the sender's context: copy on ours after its copy is done
+                        sess._check(lib().mb_tensor_copy_to_device(sess.ctx, item.h, buf))
+                        sess.sync()
+                    else:
+                        ctypes.memmove(buf, item, nbytes)
+                return 0
+            except Exception as e:  # must not propagate through the C frames
+                import sys
+                print(f"LocalTransport error: {e!r}", file=sys.stderr, flush=True)
+                return 1
+        fn.sent = 0
+        return fn

@@ -1,0 +1,158 @@
+"""One party per context (csrc/party.cpp): the three parties run as threads on one GPU and talk through the
+in-process transport.  Every party has its own entropy, so results are checked by value (revealed outputs against the
+plaintext computation, TruncPr within its 1-ulp error) and by structure (party i's second share is party i+1's
+first share)."""
+import threading
+
+import numpy as np
+import pytest
+
+import moose_b200 as mb
+from moose_b200 import BIT, RING64, RING128
+from moose_b200.party_rt import LocalTransport, PartyMLP, PartySession
+
+pytestmark = pytest.mark.gpu
+NAMES = ("player0", "player1", "player2")
+DT = {64: RING64, 128: RING128}
+
+
+def run_parties(fn, session_id="party-test"):
+    lt = LocalTransport(NAMES)
+    sessions = [mb.Session(0, session_id, bytes([17 * (i + 1)]) * 16) for i in range(3)]
+    results, errors = [None] * 3, []
+
+    def worker(i):
+        try:
+            ps = PartySession(sessions[i], i, lt.endpoint(NAMES[i], sessions[i]), NAMES)
+            results[i] = fn(ps)
+            ps.flush()
+            ps.close()
+        except Exception as e:  # noqa: BLE001
+            errors.append((i, repr(e)))
+
+    threads = [threading.Thread(target=worker, args=(i,)) for i in range(3)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=300)
+    assert not errors, errors
+    assert all(not t.is_alive() for t in threads), "a party is stuck"
+    for s in sessions:
+        s.close()
+    return results
+
+
+def signed(a, bits):
+    a = a.astype(object)
+    if bits == 128:
+        a = a[..., 0] + (a[..., 1] << 64)
+    m = 1 << bits
+    return np.where(a >= m // 2, a - m, a)
+
+
+def ints(vals, bits, sess):
+    flat = [int(v) % (1 << bits) for v in np.asarray(vals, dtype=object).reshape(-1)]
+    shape = np.shape(vals)
+    if bits == 64:
+        return sess.from_host(RING64, np.array(flat, dtype=np.uint64).reshape(shape))
+    arr = np.array([[v & (2 ** 64 - 1), v >> 64] for v in flat], dtype=np.uint64).reshape(shape + (2,))
+    return sess.from_host(RING128, arr)
+
+
+@pytest.mark.parametrize("bits", [64, 128])
+def test_share_reveal_consistency_and_linear_ops(bits):
+    rng = np.random.default_rng(bits)
+    xv = rng.integers(-10 ** 6, 10 ** 6, (6, 5))
+    yv = rng.integers(-10 ** 6, 10 ** 6, (6, 5))
+    pub = rng.integers(-100, 100, (6, 5))
+
+    def prog(p):
+        s = p.sess
+        x = p.share(0, ints(xv, bits, s) if p.me == 0 else None, DT[bits], xv.shape)
+        y = p.share(2, ints(yv, bits, s) if p.me == 2 else None, DT[bits], yv.shape)
+        z = p.add_public(p.sub(p.add(x, y), y), ints(pub, bits, s))
+        m = p.mul(x, y)
+        outs = [p.reveal(r, z) for r in range(3)]
+        prod = p.reveal(1, m)
+        return (x.share(0).to_host(), x.share(1).to_host(), m.share(0).to_host(), m.share(1).to_host(),
+                [o.to_host() if o is not None else None for o in outs], prod.to_host() if prod is not None else None)
+
+    res = run_parties(prog)
+    for i in range(3):  # replicated structure: (x_i, x_{i+1})
+        assert np.array_equal(res[i][1], res[(i + 1) % 3][0]) and np.array_equal(res[i][3], res[(i + 1) % 3][2])
+        assert res[i][4][i] is not None and all(res[i][4][r] is None for r in range(3) if r != i)
+        assert np.array_equal(signed(res[i][4][i], bits), xv + pub)
+    assert np.array_equal(signed(res[1][5], bits), xv * yv)
+    assert not np.array_equal(res[0][0], res[1][0])  # the shares are not the plaintext in disguise
+
+
+@pytest.mark.parametrize("bits,shape", [(64, (130, 40, 24)), (128, (70, 33, 16)), (64, (256, 512, 256))])
+def test_dot_and_trunc_pr(bits, shape):
+    """Replicated dot (IMAD path and, for the large case, the two-term tensor-pipe GEMM per party) followed by
+    TruncPr: fixed-point matrix product within the truncation error."""
+    M, K, N = shape
+    frac = 20
+    rng = np.random.default_rng(M)
+    a, b = rng.uniform(-2, 2, (M, K)), rng.uniform(-2, 2, (K, N))
+
+    def prog(p):
+        s = p.sess
+        enc = lambda v: s.fixedpoint_encode(DT[bits], frac, s.from_host(mb.FLOAT64, v))
+        x = p.share(0, enc(a) if p.me == 0 else None, DT[bits], a.shape)
+        y = p.share(1, enc(b) if p.me == 1 else None, DT[bits], b.shape)
+        z = p.trunc_pr(frac, p.dot(x, y))
+        out = p.reveal(2, z)
+        return s.fixedpoint_decode(frac, out).to_host() if out is not None else None
+
+    res = run_parties(prog)
+    assert res[0] is None and res[1] is None
+    assert np.abs(res[2] - a @ b).max() < K * 2.0 ** -frac * 4 + 2.0 ** -(frac - 2)
+
+
+@pytest.mark.parametrize("bits", [64, 128])
+def test_msb_ring_inject_and_maximum(bits):
+    rng = np.random.default_rng(5 + bits)
+    xv = rng.integers(-2 ** 40, 2 ** 40, (8, 32))
+    xv[0, :4] = [0, -1, 1, -(2 ** 62)]
+    yv = rng.integers(-2 ** 40, 2 ** 40, (8, 32))
+
+    def prog(p):
+        s = p.sess
+        x = p.share(1, ints(xv, bits, s) if p.me == 1 else None, DT[bits], xv.shape)
+        y = p.share(0, ints(yv, bits, s) if p.me == 0 else None, DT[bits], yv.shape)
+        m = p.msb(x)
+        inj = p.ring_inject(DT[bits], 3, m)
+        mx = p.maximum([x, y])
+        lt = p.less(x, y)
+        r = [p.reveal(0, m), p.reveal(0, inj), p.reveal(0, mx), p.reveal(0, lt)]
+        return [t.bits() if t is not None and t.dtype == BIT else (t.to_host() if t is not None else None) for t in r]
+
+    res = run_parties(prog)[0]
+    assert np.array_equal(res[0], (xv < 0).astype(np.uint8))
+    assert np.array_equal(signed(res[1], bits), (xv < 0).astype(object) * 8)
+    assert np.array_equal(signed(res[2], bits), np.maximum(xv, yv))
+    assert np.array_equal(res[3], (xv < yv).astype(np.uint8))
+
+
+def test_party_mlp_matches_float():
+    rng = np.random.default_rng(9)
+    dims = (24, 16, 16, 4)
+    ws = [rng.normal(0, dims[i] ** -0.5, (dims[i], dims[i + 1])) for i in range(3)]
+    bs = [rng.normal(0, 0.1, dims[i + 1]) for i in range(3)]
+    x = rng.uniform(0, 1, (32, dims[0]))
+
+    def prog(p):
+        mlp = PartyMLP(p, ws, bs, RING64, 23)
+        s = p.sess
+        xf = s.fixedpoint_encode(RING64, 23, s.from_host(mb.FLOAT64, x)) if p.me == 0 else None
+        out = mlp.forward(xf, x.shape[0], reveal_to=0)
+        return out.to_host() if out is not None else None, p.bytes_sent
+
+    res = run_parties(prog)
+    h = x
+    for i in range(3):
+        h = h @ ws[i] + bs[i]
+        if i < 2:
+            h = np.maximum(h, 0)
+    assert np.abs(res[0][0] - h).max() < 1e-4 and res[1][0] is None
+    assert all(r[1] > 0 for r in res)
