@@ -445,8 +445,18 @@ int mb_exec_free(mb_exec *e);
  *     data is there; a send of device memory may return while the transfer is in flight -- the executor keeps the
  *     tensor referenced until the transport reports it complete:
  *   2 poll: write to *(int64_t *)buf the number of device sends completed so far (in posting order);
- *   3 flush: wait for all posted sends, then report like 2.
+ *   3 flush: wait for all posted sends, then report like 2;
+ *   4 grouped exchange (party runtime only): buf points to an mb_sendrecv; send and receive the two device
+ *     buffers concurrently and return when both are complete.
  * Return 0 on success.  The caller binds it to NCCL send/recv between the parties' GPUs. */
+typedef struct {
+  const char *send_peer;
+  void *send_buf;
+  size_t send_bytes;
+  const char *recv_peer;
+  void *recv_buf;
+  size_t recv_bytes;
+} mb_sendrecv;
 typedef int (*mb_transport_fn)(void *user, int mode, const char *peer_role, void *buf, size_t nbytes, int on_device);
 int mb_exec_set_transport(mb_exec *e, mb_transport_fn fn, void *user);
 /* Binds a tensor to an Input operation (by arg_name) or replaces the result of the named operation (e.g. the
@@ -486,6 +496,8 @@ int mb_party_create(mb_ctx *ctx, int me, mb_transport_fn fn, void *user, const c
 int mb_party_free(mb_party *p);
 int mb_party_flush(mb_party *p); /* waits for every posted send */
 uint64_t mb_party_bytes_sent(const mb_party *p);
+/* which: 0 host seconds inside the transport, 1 host seconds waiting for the stream before a send, 2 tensor sends */
+double mb_party_stat(const mb_party *p, int which);
 int mb_pshare_free(mb_party *p, mb_pshare *s);
 const mb_tensor *mb_pshare_tensor(const mb_pshare *s, int i); /* i = 0: share me, 1: share me+1 (borrowed) */
 /* ShareOp (convert.rs:49-160): x is the plaintext on the owner (NULL elsewhere); dtype / shape on every party. */

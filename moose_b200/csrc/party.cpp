@@ -18,6 +18,7 @@
 // Randomness: PRF keys and dealer masks come from this party's own entropy; sync keys are public and must agree on
 // the three parties, so they are drawn from a counter-mode stream keyed by the session id (all parties execute the
 // same protocol sequence, the reference fixes them at compile time, zero_share.rs:82-85).
+#include <chrono>
 #include <deque>
 #include <functional>
 
@@ -37,7 +38,8 @@ struct mb_party {
   AesKey sync_cipher;
   uint64_t sync_counter;
   std::deque<mb_tensor *> in_flight;
-  uint64_t sends_reported, bytes_sent;
+  uint64_t sends_reported, bytes_sent, transfers;
+  double transport_seconds, sync_seconds;
 };
 
 struct mb_pshare {
@@ -83,9 +85,17 @@ struct P {
   [[noreturn]] void fail(int code, const std::string &m) { mb_fail(c, code, m); throw PErr{code}; }
 
   // ---- transport --------------------------------------------------------------------------------------
+  static double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
   void raw(int mode, int peer, void *buf, size_t n, int dev) {
-    if (pt->tx(pt->user, mode, peer >= 0 ? pt->names[peer].c_str() : "", buf, n, dev) != 0)
-      fail(MB_ERR_KERNEL, "party transport failed");
+    const double t0 = now_s();
+    const int rc = pt->tx(pt->user, mode, peer >= 0 ? pt->names[peer].c_str() : "", buf, n, dev);
+    pt->transport_seconds += now_s() - t0;
+    if (rc != 0) fail(MB_ERR_KERNEL, "party transport failed");
+  }
+  void sync_stream() {
+    const double t0 = now_s();
+    ck(mb_ctx_sync(c));
+    pt->sync_seconds += now_s() - t0;
   }
   void reap(bool all) {
     if (pt->in_flight.empty() && !all) return;
@@ -104,7 +114,8 @@ struct P {
     hdr[2] = t->rank;
     for (int k = 0; k < t->rank; k++) hdr[3 + k] = t->shape[k];
     hdr[9] = (int64_t)t->nbytes;
-    ck(mb_ctx_sync(c));  // the payload is read by another stream / library
+    sync_stream();  // the payload is read by another stream / library
+    pt->transfers++;
     raw(1, peer, hdr, sizeof(hdr), 0);
     if (t->nbytes) {
       raw(1, peer, t->dptr, t->nbytes, 1);
@@ -147,14 +158,24 @@ struct P {
     if (me == from) send_b(to, b, n);
     if (me == to) recv_b(from, b, n);
   }
-  // Every party hands its component to the previous party and gets the next party's: transfers 0->2, 1->0, 2->1 in
-  // this order on every party (a symmetric "send, then receive" would deadlock the serialised P2P queues).
+  // Every party hands its component to the previous party and gets the next party's, which has the same dtype and
+  // shape: one grouped send + receive (transport mode 4), the three transfers run concurrently.
   T ring(const mb_tensor *mine) {
-    T got(c, nullptr);
-    for (int from = 0; from < 3; from++) {
-      T r = move(from, (from + 2) % 3, mine);
-      if (r.p) got = std::move(r);
-    }
+    mb_tensor *t = nullptr;
+    ck(mb_tensor_new_detached(c, mine->dtype, mine->rank, mine->shape, &t));
+    T got(c, t);
+    if (mine->nbytes == 0) return got;
+    sync_stream();  // the payload is read by another stream / library
+    mb_sendrecv d;
+    d.send_peer = pt->names[pv].c_str();
+    d.send_buf = mine->dptr;
+    d.send_bytes = mine->nbytes;
+    d.recv_peer = pt->names[nx].c_str();
+    d.recv_buf = t->dptr;
+    d.recv_bytes = t->nbytes;
+    pt->transfers++;
+    raw(4, -1, &d, sizeof(d), 1);
+    pt->bytes_sent += mine->nbytes;
     return got;
   }
 
@@ -353,14 +374,22 @@ struct P {
       T cc = add(masked0.p, masked1.p);
       T c_top = shr(amount + 1, shl(1, cc.p).p);
       T c_msb = shr(bits - 1, cc.p);
-      move(0, 1, c_msb.p);
+      {  // the opened top bit travels as a bit tensor (1/64 .. 1/128 of the ring tensor)
+        mb_tensor *cb = nullptr;
+        ck(mb_bit_extract(c, bits - 1, cc.p, &cb));
+        T cbits(c, cb);
+        move(0, 1, cbits.p);
+      }
       T prod = mul(rmsb0.p, c_msb.p);
       T ov = sub(sub(add(rmsb0.p, c_msb.p).p, prod.p).p, prod.p);    // r_msb + c_msb - 2 r_msb c_msb
       y = sub(add(sub(c_top.p, rtop0.p).p, shl(k - amount, ov.p).p).p, down.p);
     } else if (me == 1) {
       T masked1 = add(x.b.p, r1[0].p);                                 // a1 = x2, masked with r1
       move(1, 0, masked1.p);
-      T c_msb = move(0, 1, nullptr);
+      T cbits = move(0, 1, nullptr);
+      mb_tensor *cm = nullptr;
+      ck(mb_ring_inject(c, d, 0, cbits.p, &cm));
+      T c_msb(c, cm);
       T prod = mul(r1[2].p, c_msb.p);
       T ov = sub(sub(r1[2].p, prod.p).p, prod.p);
       y = add(neg(r1[1].p).p, shl(k - amount, ov.p).p);
@@ -426,21 +455,37 @@ struct P {
       mb_aes_expand(s_pg[1], &kk[1]);
       mb_aes_expand(s_pp[0], &kk[2]);
       mb_aes_expand(s_pp[1], &kk[3]);
-      int64_t gs[MB_MAX_RANK], ps[MB_MAX_RANK];  // [planes, shape...] like the decomposition itself
-      gs[0] = std::max(levels[i].nout, 1);
-      ps[0] = std::max(npo[i], 1);
-      for (int r = 0; r < like->rank; r++) gs[r + 1] = ps[r + 1] = like->shape[r];
-      mb_tensor *go = nullptr, *po = nullptr;
-      ck(mb_tensor_new(c, MB_BIT, like->rank + 1, gs, &go));
-      T g_me(c, go);
-      ck(mb_tensor_new(c, MB_BIT, like->rank + 1, ps, &po));
-      T p_me(c, po);
+      // one buffer [nout + npo, shape...] for this party's g' and p' components: one exchange per level
+      int64_t sh[MB_MAX_RANK];
+      const int64_t ng = std::max(levels[i].nout, 1), np_ = npo[i];
+      sh[0] = ng + np_;
+      for (int r = 0; r < like->rank; r++) sh[r + 1] = like->shape[r];
+      mb_tensor *buf = nullptr;
+      ck(mb_tensor_new(c, MB_BIT, like->rank + 1, sh, &buf));
+      T mine(c, buf);
+      int64_t gsh[MB_MAX_RANK], psh[MB_MAX_RANK];
+      memcpy(gsh, sh, sizeof(sh));
+      memcpy(psh, sh, sizeof(sh));
+      gsh[0] = ng;
+      psh[0] = std::max<int64_t>(np_, 1);
+      const size_t plane_bytes = (size_t)n / 8;
+      auto views = [&](const mb_tensor *whole, T &gv, T &pv_) {
+        mb_tensor *a = nullptr, *b = nullptr;
+        ck(mb_tensor_view(c, whole, 0, like->rank + 1, gsh, &a));
+        gv = T(c, a);
+        if (np_ > 0) {
+          ck(mb_tensor_view(c, whole, (size_t)ng * plane_bytes, like->rank + 1, psh, &b));
+          pv_ = T(c, b);
+        } else {
+          pv_ = gv.clone();  // never read
+        }
+      };
+      T g_me(c, nullptr), p_me(c, nullptr), g_nx(c, nullptr), p_nx(c, nullptr);
+      views(mine.p, g_me, p_me);
       const mb_tensor *gin[2] = {g.a.p, g.b.p}, *pin[2] = {p.a.p, p.b.p};
       ck(k_party_adder_level(c, kk, levels[i], gin, pin, g_me.p, p_me.p, nv));
-      T g_nx = ring(g_me.p);
-      T p_nx(c, nullptr);
-      if (npo[i] > 0) p_nx = ring(p_me.p);
-      else p_nx = p_me.clone();  // never read
+      T theirs = ring(mine.p);
+      views(theirs.p, g_nx, p_nx);
       g = Pair{std::move(g_me), std::move(g_nx)};
       p = Pair{std::move(p_me), std::move(p_nx)};
     }
@@ -551,7 +596,8 @@ extern "C" int mb_party_create(mb_ctx *ctx, int me, mb_transport_fn fn, void *us
   p->have_setup = false;
   mb_aes_expand(ctx->sid, &p->sync_cipher);  // public sync-key stream, the same on the three parties
   p->sync_counter = 0;
-  p->sends_reported = p->bytes_sent = 0;
+  p->sends_reported = p->bytes_sent = p->transfers = 0;
+  p->transport_seconds = p->sync_seconds = 0.0;
   *out = p;
   return MB_OK;
 }
@@ -564,6 +610,11 @@ extern "C" int mb_party_free(mb_party *p) {
 }
 
 extern "C" uint64_t mb_party_bytes_sent(const mb_party *p) { return p ? p->bytes_sent : 0; }
+// which: 0 host seconds inside the transport, 1 host seconds waiting for the stream before a send, 2 tensor sends
+extern "C" double mb_party_stat(const mb_party *p, int which) {
+  if (!p) return 0.0;
+  return which == 0 ? p->transport_seconds : which == 1 ? p->sync_seconds : (double)p->transfers;
+}
 
 // Waits for every posted send; call before the tensors involved are reused outside the party runtime.
 extern "C" int mb_party_flush(mb_party *p) {

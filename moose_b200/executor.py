@@ -112,16 +112,28 @@ class NcclComm:
     def transport(self, _user, mode, peer, buf, nbytes, on_device):
         """mb_transport_fn: raw buffers of the native executor.  Device payloads go straight from / into the
         tensor's memory; host buffers (headers, keys, seeds) are staged through a small device tensor for NCCL.
-        Modes: 0 receive, 1 send, 2 poll completed device sends, 3 wait for all of them."""
+        Modes: 0 receive, 1 send, 2 poll completed device sends, 3 wait for all of them, 4 grouped send + receive."""
         try:
             t = self.torch
-            if mode >= 2:
+            if mode in (2, 3):
                 while self._posted and (mode == 3 or self._posted[0].is_completed()):
                     self._posted.pop(0).wait()
                     if mode == 3 and self.dev.type == "cuda" and not self._posted:
                         t.cuda.synchronize(self.dev)
                     self._completed += 1
                 ctypes.cast(buf, ctypes.POINTER(ctypes.c_int64))[0] = self._completed
+                return 0
+            if mode == 4:  # grouped send + receive of two device buffers (ring exchange of the party runtime)
+                d = ctypes.cast(buf, ctypes.POINTER(SendRecv))[0]
+                sview = t.as_tensor(_DeviceBytes(d.send_buf, d.send_bytes), device=self.dev)
+                rview = t.as_tensor(_DeviceBytes(d.recv_buf, d.recv_bytes), device=self.dev)
+                ops = [self.dist.P2POp(self.dist.isend, sview, self.role_to_rank[d.send_peer.decode()]),
+                       self.dist.P2POp(self.dist.irecv, rview, self.role_to_rank[d.recv_peer.decode()])]
+                for req in self.dist.batch_isend_irecv(ops):
+                    req.wait()
+                done = t.cuda.Event()
+                done.record()
+                done.synchronize()
                 return 0
             other = self.role_to_rank[peer.decode()]
             if on_device:
@@ -176,6 +188,12 @@ class NcclComm:
         if kind == self.K_SHAPE:
             return tuple(shape)
         return None
+
+
+class SendRecv(ctypes.Structure):
+    """mb_sendrecv (include/moose_b200.h): argument of transport mode 4."""
+    _fields_ = [("send_peer", ctypes.c_char_p), ("send_buf", ctypes.c_void_p), ("send_bytes", ctypes.c_size_t),
+                ("recv_peer", ctypes.c_char_p), ("recv_buf", ctypes.c_void_p), ("recv_bytes", ctypes.c_size_t)]
 
 
 TRANSPORT_FN = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p, ctypes.c_void_p,

@@ -26,6 +26,70 @@ def roles_of(ops):
     return roles
 
 
+def run_fused_mlp(args):
+    """BASELINE config 5 on the party runtime: alice / bob / carole on three GPUs, reshares and openings over NCCL."""
+    import torch
+    import torch.distributed as dist
+    import moose_b200 as mb
+    from moose_b200.executor import NcclComm
+    from moose_b200.party_rt import PartyMLP, PartySession
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != 3:
+        raise SystemExit("the party runtime needs exactly 3 ranks")
+    roles = ["player0", "player1", "player2"]
+    torch.cuda.set_device(local_rank)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    sess = mb.Session(local_rank, args.session_id, None)
+    comm = NcclComm(dist, sess, {r: i for i, r in enumerate(roles)}, local_rank)
+    party = PartySession(sess, rank, comm.transport, roles)
+    dims, B = args.dims, args.mlp
+    ws = [np.random.default_rng(4 + l).normal(0, dims[l] ** -0.5, (dims[l], dims[l + 1])) for l in range(len(dims) - 1)]
+    bs = [np.random.default_rng(40 + l).normal(0, 0.1, dims[l + 1]) for l in range(len(dims) - 1)]
+    mlp = PartyMLP(party, ws, bs, mb.RING64, 23)
+    x = np.random.default_rng(3).uniform(0, 1, (B, dims[0]))
+    xf = sess.fixedpoint_encode(mb.RING64, 23, sess.from_host(mb.FLOAT64, x)) if rank == 0 else None
+    dist.barrier()
+    out = mlp.forward(xf, B)          # untimed: NCCL connections, scratch growth
+    party.flush()
+    sess.sync()
+    sent0, st0 = party.bytes_sent, party.stats()
+    dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.repeat):
+        out = mlp.forward(xf, B)
+        party.flush()
+        sess.sync()
+    dt = (time.perf_counter() - t0) / args.repeat
+    dist.barrier()
+    sent = torch.tensor([party.bytes_sent - sent0], dtype=torch.int64, device=f"cuda:{local_rank}")
+    dist.all_reduce(sent)
+    err = None
+    if out is not None:
+        h = x[:8]
+        for l in range(len(dims) - 1):
+            h = h @ ws[l] + bs[l]
+            if l < len(dims) - 2:
+                h = np.maximum(h, 0)
+        err = float(np.abs(out.to_host()[:8] - h).max())
+    st1 = party.stats()
+    mine = {k: (st1[k] - st0[k]) / args.repeat for k in st1}
+    gathered = [None] * world
+    dist.all_gather_object(gathered, mine)
+    if rank == 0:
+        print(json.dumps({"mode": "party-per-gpu (party runtime, fused party-sliced kernels)", "parties": roles,
+                          "per_party": gathered,
+                          "transport": "nccl send/recv",
+                          "workload": "mlp_" + "-".join(map(str, dims)) + f"_relu_ring64_fixed(14,23)_batch{B}",
+                          "rows_per_s": B / dt, "seconds_per_run": dt, "payload_bytes_per_run": int(sent[0]) // args.repeat,
+                          "max_abs_err_first_rows": err}), flush=True)
+    party.close()
+    sess.close()
+    dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--graph", default=None, help=".moose text or the .json(.gz) re-encoding of tests/golden")
@@ -33,6 +97,9 @@ def main():
                     help="BASELINE config 5: emit the lowered + networked MLP graph (moose_b200/lowering.py) for --dims on "
                          "Ring64 fixed(14,23) and run it with one party per GPU on a synthetic batch")
     ap.add_argument("--dims", type=int, nargs="+", default=[784, 512, 512, 10])
+    ap.add_argument("--fused", action="store_true",
+                    help="with --mlp: run the party runtime (csrc/party.cpp: party-sliced fused kernels, msb-pruned adder, "
+                         "seeds on the wire) instead of the per-op lowered graph")
     ap.add_argument("--session-id", default="b200-party")
     ap.add_argument("--repeat", type=int, default=1)
     ap.add_argument("--scale", type=int, nargs=3, metavar=("M", "K", "N"), default=None,
@@ -48,6 +115,8 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.mlp is not None and args.fused:
+        return run_fused_mlp(args)
     if args.mlp is not None:
         from moose_b200.lowering import Lowering, networking_pass, prune_pass
         ops = networking_pass(prune_pass(Lowering(64).mlp_program(len(args.dims) - 1, 23)))

@@ -14,7 +14,7 @@ from typing import Dict, List, Optional, Sequence
 import numpy as np
 
 from . import FLOAT64, RING64, RING128, Session, Tensor, _shape_arr, lib
-from .executor import TRANSPORT_FN
+from .executor import TRANSPORT_FN, SendRecv
 
 
 class PShare:
@@ -53,6 +53,10 @@ class PartySession:
     @property
     def bytes_sent(self) -> int:
         return int(lib().mb_party_bytes_sent(self._p))
+
+    def stats(self) -> Dict[str, float]:
+        f = lib().mb_party_stat
+        return {"transport_s": f(self._p, 0), "stream_wait_s": f(self._p, 1), "tensor_sends": int(f(self._p, 2))}
 
     def flush(self):
         self.sess._check(lib().mb_party_flush(self._p))
@@ -140,15 +144,18 @@ class LocalTransport:
     def endpoint(self, me: str, sess: Session):
         def fn(_user, mode, peer, buf, nbytes, on_device):
             try:
-                if mode >= 2:  # every send below is complete when it returns
+                if mode in (2, 3):  # every send below is complete when it returns
                     ctypes.cast(buf, ctypes.POINTER(ctypes.c_int64))[0] = fn.sent
                     return 0
+                if mode == 4:
+                    d = ctypes.cast(buf, ctypes.POINTER(SendRecv))[0]
+                    rc = fn(None, 1, d.send_peer, d.send_buf, d.send_bytes, 1)
+                    return rc or fn(None, 0, d.recv_peer, d.recv_buf, d.recv_bytes, 1)
                 other = peer.decode()
                 if mode == 1:
                     if on_device:
-                        if nbytes % 8:
-                            raise ValueError("device payloads are multiples of 8 bytes")
-                        stage = sess.alloc(RING64, (nbytes // 8,))
+                        # staged in whole 8-byte words: tensor allocations are padded to 16 bytes with zeros
+                        stage = sess.alloc(RING64, ((nbytes + 7) // 8,))
                         sess._check(lib().mb_tensor_copy_from_device(sess.ctx, stage.h, buf))
                         sess.sync()
                         fn.sent += 1
@@ -156,7 +163,7 @@ class LocalTransport:
                     else:
                         self.q[(me, other)].put(bytes((ctypes.c_uint8 * nbytes).from_address(buf)))
                 else:
-                    item = self.q[(other, me)].get(timeout=120)
+                    item = self.q[(other, me)].get(timeout=60)
                     if on_device:
                         # the staging tensor belongs to the sender's context: copy on ours after its copy is done
                         sess._check(lib().mb_tensor_copy_to_device(sess.ctx, item.h, buf))
