@@ -154,6 +154,27 @@ struct P {
     if (me == to) return recv_t(from);
     return T(c, nullptr);
   }
+  // The same when the receiver knows dtype and shape already (SPMD: it does almost everywhere): payload only.
+  T move_like(int from, int to, const mb_tensor *t, mb_dtype d, const mb_tensor *shape_of) {
+    if (me == from) {
+      sync_stream();
+      pt->transfers++;
+      if (t->nbytes) {
+        raw(1, to, t->dptr, t->nbytes, 1);
+        pt->in_flight.push_back(mb_tensor_retain(const_cast<mb_tensor *>(t)));
+      }
+      pt->bytes_sent += t->nbytes;
+      reap(false);
+    }
+    if (me == to) {
+      mb_tensor *r = nullptr;
+      ck(mb_tensor_new_detached(c, d, shape_of->rank, shape_of->shape, &r));
+      T out(c, r);
+      if (r->nbytes) raw(0, from, r->dptr, r->nbytes, 1);
+      return out;
+    }
+    return T(c, nullptr);
+  }
   void move_b(int from, int to, uint8_t *b, size_t n) {
     if (me == from) send_b(to, b, n);
     if (me == to) recv_b(from, b, n);
@@ -260,7 +281,7 @@ struct P {
   // the receiver adds its two shares and the third one, sent by the next party (convert.rs:295-311)
   T reveal(int receiver, const Pair &x) {
     const int sender = (receiver + 1) % 3;
-    T third = move(sender, receiver, x.b.p);
+    T third = move_like(sender, receiver, x.b.p, x.a.p->dtype, x.a.p);
     if (me != receiver) return T(c, nullptr);
     return add(add(x.a.p, x.b.p).p, third.p);
   }
@@ -332,10 +353,10 @@ struct P {
     if (me == 2) return Pair{prf(d, like, seed2), prf(d, like, seed1)};  // (y1', y0')
     T yp = prf(d, like, me == 0 ? seed1 : seed2);
     T diff = sub(y.p, yp.p);
-    T d1 = move(1, 0, diff.p);       // party 0 opens c = (y0 - y0') + (y1 - y1')
+    T d1 = move_like(1, 0, diff.p, d, like);       // party 0 opens c = (y0 - y0') + (y1 - y1')
     T cc(c, nullptr);
     if (me == 0) cc = add(diff.p, d1.p);
-    T c1 = move(0, 1, cc.p);
+    T c1 = move_like(0, 1, cc.p, d, like);
     if (me == 0) return Pair{std::move(yp), std::move(cc)};
     return Pair{std::move(c1), std::move(yp)};
   }
@@ -363,14 +384,14 @@ struct P {
     }
     for (int i = 0; i < 3; i++) move_b(2, 0, seeds[i], 16);
     T r1[3] = {T(c, nullptr), T(c, nullptr), T(c, nullptr)};
-    for (int i = 0; i < 3; i++) r1[i] = move(2, 1, m1[i].p);
+    for (int i = 0; i < 3; i++) r1[i] = move_like(2, 1, m1[i].p, d, like);
     T y(c, nullptr);
     if (me == 0) {
       T r0 = prf(d, like, seeds[0]), rtop0 = prf(d, like, seeds[1]), rmsb0 = prf(d, like, seeds[2]);
       T a0 = add(x.a.p, x.b.p);                                        // rep_to_adt: x0 + x1
       T up = fill(d, like, (u128)1 << (k - 1)), down = fill(d, like, (u128)1 << (k - amount - 1));
       T masked0 = add(add(a0.p, up.p).p, r0.p);
-      T masked1 = move(1, 0, nullptr);
+      T masked1 = move_like(1, 0, nullptr, d, like);
       T cc = add(masked0.p, masked1.p);
       T c_top = shr(amount + 1, shl(1, cc.p).p);
       T c_msb = shr(bits - 1, cc.p);
@@ -385,7 +406,7 @@ struct P {
       y = sub(add(sub(c_top.p, rtop0.p).p, shl(k - amount, ov.p).p).p, down.p);
     } else if (me == 1) {
       T masked1 = add(x.b.p, r1[0].p);                                 // a1 = x2, masked with r1
-      move(1, 0, masked1.p);
+      move_like(1, 0, masked1.p, d, like);
       T cbits = move(0, 1, nullptr);
       mb_tensor *cm = nullptr;
       ck(mb_ring_inject(c, d, 0, cbits.p, &cm));
