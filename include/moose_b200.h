@@ -480,6 +480,17 @@ int mb_exec_value(mb_exec *e, const char *op_name, int *kind, mb_tensor **tensor
 int mb_exec_output(mb_exec *e, int saved, const char *key, mb_tensor **tensor);
 const char *mb_exec_output_key(const mb_exec *e, int saved, int64_t i);
 
+/* Native NCCL binding of the transport: ncclSend / ncclRecv (grouped for mode 4) on a dedicated stream; libnccl is
+ * opened at run time.  One rank creates the unique id, the host distributes it (torch.distributed, a file, MPI);
+ * role_names[r] is the peer name of rank r.  Pass mb_nccl_transport_fn() and the handle as (fn, user) to
+ * mb_exec_set_transport / mb_party_create.  No counterpart in the reference (its transport is gRPC / TCP). */
+typedef struct mb_nccl_transport mb_nccl_transport;
+int mb_nccl_unique_id(uint8_t out[128]);
+int mb_nccl_transport_create(mb_ctx *ctx, const uint8_t unique_id[128], int rank, int nranks, const char *const *role_names,
+                             mb_nccl_transport **out);
+mb_transport_fn mb_nccl_transport_fn(void);
+int mb_nccl_transport_free(mb_nccl_transport *t);
+
 /* ------------------------------------------------------- party per process */
 
 /* ONE party of the replicated protocols per process / GPU (BASELINE config 5).  Party `me` holds the shares

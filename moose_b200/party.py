@@ -43,8 +43,16 @@ def run_fused_mlp(args):
     torch.cuda.set_device(local_rank)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     sess = mb.Session(local_rank, args.session_id, None)
-    comm = NcclComm(dist, sess, {r: i for i, r in enumerate(roles)}, local_rank)
-    party = PartySession(sess, rank, comm.transport, roles)
+    native = None
+    if args.native_nccl:
+        from moose_b200.party_rt import NativeNccl
+        box = [NativeNccl.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)          # bootstrap only: the unique id
+        native = NativeNccl(sess, box[0], rank, roles)
+        party = PartySession(sess, rank, native, roles)
+    else:
+        comm = NcclComm(dist, sess, {r: i for i, r in enumerate(roles)}, local_rank)
+        party = PartySession(sess, rank, comm.transport, roles)
     dims, B = args.dims, args.mlp
     ws = [np.random.default_rng(4 + l).normal(0, dims[l] ** -0.5, (dims[l], dims[l + 1])) for l in range(len(dims) - 1)]
     bs = [np.random.default_rng(40 + l).normal(0, 0.1, dims[l + 1]) for l in range(len(dims) - 1)]
@@ -81,11 +89,13 @@ def run_fused_mlp(args):
     if rank == 0:
         print(json.dumps({"mode": "party-per-gpu (party runtime, fused party-sliced kernels)", "parties": roles,
                           "per_party": gathered,
-                          "transport": "nccl send/recv",
+                          "transport": "ncclSend/ncclRecv from C++ (native)" if native else "nccl send/recv (torch.distributed)",
                           "workload": "mlp_" + "-".join(map(str, dims)) + f"_relu_ring64_fixed(14,23)_batch{B}",
                           "rows_per_s": B / dt, "seconds_per_run": dt, "payload_bytes_per_run": int(sent[0]) // args.repeat,
                           "max_abs_err_first_rows": err}), flush=True)
     party.close()
+    if native:
+        native.close()
     sess.close()
     dist.destroy_process_group()
 
@@ -97,6 +107,9 @@ def main():
                     help="BASELINE config 5: emit the lowered + networked MLP graph (moose_b200/lowering.py) for --dims on "
                          "Ring64 fixed(14,23) and run it with one party per GPU on a synthetic batch")
     ap.add_argument("--dims", type=int, nargs="+", default=[784, 512, 512, 10])
+    ap.add_argument("--native-nccl", action="store_true",
+                    help="with --fused: the library's own NCCL transport (ncclSend / ncclRecv from C++) instead of "
+                         "torch.distributed P2P")
     ap.add_argument("--fused", action="store_true",
                     help="with --mlp: run the party runtime (csrc/party.cpp: party-sliced fused kernels, msb-pruned adder, "
                          "seeds on the wire) instead of the per-op lowered graph")

@@ -17,6 +17,30 @@ from . import FLOAT64, RING64, RING128, Session, Tensor, _shape_arr, lib
 from .executor import TRANSPORT_FN, SendRecv
 
 
+class NativeNccl:
+    """The library's own NCCL transport (csrc/nccl_transport.cpp).  `unique_id` (128 bytes) comes from
+    NativeNccl.unique_id() on one rank and reaches the others through the host's bootstrap (torch.distributed here)."""
+
+    def __init__(self, sess: Session, unique_id: bytes, rank: int, role_names: Sequence[str]):
+        names = (ctypes.c_char_p * len(role_names))(*[n.encode() for n in role_names])
+        self._names, self.sess = names, sess
+        self.handle = ctypes.c_void_p()
+        sess._check(lib().mb_nccl_transport_create(sess.ctx, unique_id, rank, len(role_names), names, ctypes.byref(self.handle)))
+        self.fn = lib().mb_nccl_transport_fn()
+
+    @staticmethod
+    def unique_id() -> bytes:
+        buf = (ctypes.c_uint8 * 128)()
+        if lib().mb_nccl_unique_id(buf) != 0:
+            raise RuntimeError("mb_nccl_unique_id failed: " + (lib().mb_last_error(None) or b"").decode())
+        return bytes(buf)
+
+    def close(self):
+        if self.handle:
+            lib().mb_nccl_transport_free(self.handle)
+            self.handle = ctypes.c_void_p()
+
+
 class PShare:
     """This party's two shares (x_me, x_{me+1}) of a replicated tensor."""
 
@@ -39,11 +63,15 @@ class PartySession:
     def __init__(self, sess: Session, me: int, transport, role_names: Sequence[str] = ("player0", "player1", "player2")):
         """`transport`: a callable with the mb_transport_fn contract (mode, peer, buf, nbytes, on_device)."""
         self.sess, self.me = sess, me
-        self._cb = TRANSPORT_FN(transport)
         names = (ctypes.c_char_p * 3)(*[n.encode() for n in role_names])
         self._names = names
         self._p = ctypes.c_void_p()
-        sess._check(lib().mb_party_create(sess.ctx, me, self._cb, None, names, ctypes.byref(self._p)))
+        if isinstance(transport, NativeNccl):   # C function + handle: no interpreter in the transfer loop
+            self._cb, user = ctypes.c_void_p(transport.fn), transport.handle
+        else:
+            self._cb, user = TRANSPORT_FN(transport), None
+        self._transport = transport
+        sess._check(lib().mb_party_create(sess.ctx, me, self._cb, user, names, ctypes.byref(self._p)))
 
     def close(self):
         if self._p:
