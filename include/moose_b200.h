@@ -447,7 +447,10 @@ int mb_exec_free(mb_exec *e);
  *   2 poll: write to *(int64_t *)buf the number of device sends completed so far (in posting order);
  *   3 flush: wait for all posted sends, then report like 2;
  *   4 grouped exchange (party runtime only): buf points to an mb_sendrecv; send and receive the two device
- *     buffers concurrently and return when both are complete.
+ *     buffers concurrently and return when both are complete;
+ *   5 capabilities (party runtime only, optional): write a bit mask to *(int64_t *)buf.  Bit 0: device payloads are
+ *     ordered on the context's stream -- the caller need not synchronise the stream before a send, and a received
+ *     buffer is valid in stream order rather than at return.  A transport that does not know the mode leaves 0.
  * Return 0 on success.  The caller binds it to NCCL send/recv between the parties' GPUs. */
 typedef struct {
   const char *send_peer;
@@ -490,6 +493,24 @@ int mb_nccl_transport_create(mb_ctx *ctx, const uint8_t unique_id[128], int rank
                              mb_nccl_transport **out);
 mb_transport_fn mb_nccl_transport_fn(void);
 int mb_nccl_transport_free(mb_nccl_transport *t);
+
+/* Peer-memory binding of the transport for parties on the GPUs of one NVLink / NVSwitch node.  Every party owns an
+ * inbox in its HBM (per peer: a byte ring of `ring_bytes`, 0 = 1 GiB, and a ring of 4 KiB message slots); the peers
+ * map it (CUDA IPC between processes, directly between threads of one process) and a transfer is a copy into the
+ * receiver's ring over NVLink plus a release store of a cumulative byte counter.  Device payloads are enqueued on the
+ * context's stream on both sides (wait for space, copy, signal / wait for the counter, copy out, acknowledge): the
+ * callback returns at once, a received buffer is valid in stream order, and the caller need not synchronise before a
+ * send (mode 5 of the callback reports this as capability bit 0).  Start-up: create on every rank, exchange the
+ * 128-byte handles through the host (torch.distributed, a file, MPI), connect with all of them in rank order.  All
+ * ranks must have stopped communicating (a host barrier) before any of them frees its transport.
+ * No counterpart in the reference (its transport is gRPC / TCP). */
+typedef struct mb_peer_transport mb_peer_transport;
+int mb_peer_transport_create(mb_ctx *ctx, int rank, int nranks, const char *const *role_names, size_t ring_bytes,
+                             mb_peer_transport **out);
+int mb_peer_transport_handle(mb_peer_transport *t, uint8_t out[128]);
+int mb_peer_transport_connect(mb_peer_transport *t, const uint8_t *handles);
+mb_transport_fn mb_peer_transport_fn(void);
+int mb_peer_transport_free(mb_peer_transport *t);
 
 /* ------------------------------------------------------- party per process */
 

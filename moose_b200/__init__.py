@@ -120,6 +120,9 @@ ABI = {
     "mb_save_csv": [_P, _P, ctypes.c_char_p],
     "mb_nccl_unique_id": [_P], "mb_nccl_transport_create": [_P, _P, _I, _I, ctypes.POINTER(ctypes.c_char_p), _PP],
     "mb_nccl_transport_fn": [], "mb_nccl_transport_free": [_P],
+    "mb_peer_transport_create": [_P, _I, _I, ctypes.POINTER(ctypes.c_char_p), ctypes.c_size_t, _PP],
+    "mb_peer_transport_handle": [_P, _P], "mb_peer_transport_connect": [_P, _P],
+    "mb_peer_transport_fn": [], "mb_peer_transport_free": [_P],
     "mb_party_create": [_P, _I, _P, _P, ctypes.POINTER(ctypes.c_char_p), _PP], "mb_party_free": [_P],
     "mb_party_flush": [_P], "mb_party_bytes_sent": [_P], "mb_party_stat": [_P, _I], "mb_pshare_free": [_P, _P], "mb_pshare_tensor": [_P, _I],
     "mb_party_share": [_P, _I, _P, _I, _I, _I64P, _PP], "mb_party_reveal": [_P, _I, _P, _PP],
@@ -140,7 +143,7 @@ _RESTYPES = {
     "mb_last_error": ctypes.c_char_p, "mb_ctx_stream": _P, "mb_ctx_launch_count": _U64,
     "mb_tensor_shape": _I64P, "mb_tensor_numel": _I64, "mb_tensor_nbytes": ctypes.c_size_t,
     "mb_tensor_device_ptr": _P, "mb_rep_share_tensor": _P,
-    "mb_nccl_transport_fn": _P, "mb_party_bytes_sent": _U64, "mb_pshare_tensor": _P, "mb_party_stat": ctypes.c_double,
+    "mb_nccl_transport_fn": _P, "mb_peer_transport_fn": _P, "mb_party_bytes_sent": _U64, "mb_pshare_tensor": _P, "mb_party_stat": ctypes.c_double,
     "mb_graph_num_ops": _I64, "mb_graph_op_name": ctypes.c_char_p, "mb_exec_executed": _U64, "mb_exec_bytes_sent": _U64,
     "mb_exec_output_key": ctypes.c_char_p, "mb_exec_seconds": ctypes.c_double,
 }

@@ -228,6 +228,83 @@ __global__ void __launch_bounds__(AES_TPB_MID) adder_level_party_kernel(AesKey p
   }
 }
 
+// Bit planes [KBITS, n] of t0 +- t1 +- t2 +- t3 (bit j of `neg` set: term j is subtracted): the player-local sum a
+// party decomposes in the split (bits.rs:124-130 after the share-wise subtraction of LessOp, compare.rs:91-104).
+// Same tiling as split_planes_kernel.
+struct SplitTerms {
+  const void *t[4];
+  int n, neg;
+};
+template <typename T, int KBITS>
+__global__ void __launch_bounds__(TPB) party_split_kernel(SplitTerms terms, uint32_t *__restrict__ outB, int64_t n) {
+  constexpr int WARPS = TPB / 32;
+  constexpr int PL = KBITS / 32;
+  __shared__ uint4 tile[KBITS][WARPS];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int64_t ngroups = n / 128;
+  const int64_t nchunks = (ngroups + WARPS - 1) / WARPS;
+  for (int64_t c = blockIdx.x; c < nchunks; c += gridDim.x) {
+    const int64_t g0 = c * WARPS, g = g0 + w;
+    if (g < ngroups) {
+      uint32_t keep[PL][4];
+#pragma unroll
+      for (int it = 0; it < 4; it++) {
+        const int64_t e = g * 128 + it * 32 + lane;
+        T v = ((const T *)terms.t[0])[e];
+        if (terms.neg & 1) v = (T)0 - v;
+#pragma unroll
+        for (int j = 1; j < 4; j++)
+          if (j < terms.n) {
+            const T u = ((const T *)terms.t[j])[e];
+            v = (terms.neg >> j) & 1 ? (T)(v - u) : (T)(v + u);
+          }
+#pragma unroll
+        for (int h = 0; h < PL; h++) keep[h][it] = warp_transpose32((uint32_t)(v >> (32 * h)), lane);
+      }
+#pragma unroll
+      for (int q = 0; q < PL; q++) tile[q * 32 + lane][w] = make_uint4(keep[q][0], keep[q][1], keep[q][2], keep[q][3]);
+    }
+    __syncthreads();
+    uint4 *out = (uint4 *)outB;
+    const int64_t row_vecs = n / 128;
+    for (int idx = threadIdx.x; idx < KBITS * WARPS; idx += TPB) {
+      const int p = idx / WARPS, j = idx % WARPS;
+      if (g0 + j < ngroups) out[(int64_t)p * row_vecs + g0 + j] = tile[p][j];
+    }
+    __syncthreads();
+  }
+}
+
+// Split + first AND of the adder for ONE player (adder_init_kernel restricted to its component).  With
+// a = share_by_player0(B) = (R, B ^ R, 0) and b = (0, 0, C):  p0 = a ^ b = (R, B ^ R, C), g0 = AND(a, b) =
+// (0, (B ^ R) & C, R & C) ^ zero share.  `in`: B on player 0, C on players 1 and 2; `other`: B ^ R received from
+// player 0 (player 1 only).  Outputs: g (this player's component); p_new: R (players 0 and 2); p_send: B ^ R
+// (player 0 only, what it sends to player 1).
+__global__ void __launch_bounds__(AES_TPB_LIGHT) adder_init_party_kernel(int me, AesKey k_share, AesKey ka, AesKey kb,
+                                                                        const vec_t *__restrict__ in, const vec_t *__restrict__ other,
+                                                                        vec_t *__restrict__ g, vec_t *__restrict__ p_new,
+                                                                        vec_t *__restrict__ p_send, int64_t nvec) {
+  extern __shared__ __align__(16) uint32_t sT[];
+  aes_load_table(sT);
+  const AesLane L = aes_lane(sT);
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
+    const vec_t x = in[v];
+    const vec_t z = vxor(prf_vec<VK_BIT>(L, ka, (uint64_t)v), prf_vec<VK_BIT>(L, kb, (uint64_t)v));
+    if (me == 1) {
+      g[v] = vxor(vand(other[v], x), z);
+    } else {
+      const vec_t R = prf_vec<VK_BIT>(L, k_share, (uint64_t)v);
+      p_new[v] = R;
+      if (me == 0) {
+        p_send[v] = vxor(x, R);
+        g[v] = z;
+      } else {
+        g[v] = vxor(vand(R, x), z);
+      }
+    }
+  }
+}
+
 // z = shl_dim(g, 1) ^ p_store (misc.rs:236-240): z[q] = g[q-1] ^ p0[q], z[0] = p0[0].  Full decomposition.
 __global__ void __launch_bounds__(TPB) adder_final_full_kernel(PlanePtrs g, PlanePtrs p0, PlanePtrs z, int64_t nv, int k) {
   const int64_t total = (int64_t)k * nv;
@@ -530,6 +607,34 @@ int k_adder_plan_msb(int k, std::vector<LevelDesc> *levels_out, std::vector<int>
 }
 
 // keys: zero-share streams (me, me+1) of AND(p, g1), then of AND(p, p1).  g_in / p_in: this party's two components.
+// planes [k, shape...] of the signed sum of 1..4 ring tensors (element count a multiple of 128)
+int k_party_split(mb_ctx *ctx, const mb_tensor *const terms[], int nterms, int neg_mask, mb_tensor *out) {
+  SplitTerms t;
+  t.n = nterms;
+  t.neg = neg_mask;
+  for (int j = 0; j < 4; j++) t.t[j] = j < nterms ? terms[j]->dptr : nullptr;
+  const int64_t n = terms[0]->numel;
+  const int64_t nchunks = (n / 128 + TPB / 32 - 1) / (TPB / 32);
+  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(nchunks, (int64_t)ctx->sm_count * 8));
+  if (terms[0]->dtype == MB_RING128)
+    party_split_kernel<u128, 128><<<grid, TPB, 0, ctx->stream>>>(t, (uint32_t *)out->dptr, n);
+  else
+    party_split_kernel<uint64_t, 64><<<grid, TPB, 0, ctx->stream>>>(t, (uint32_t *)out->dptr, n);
+  MB_LAUNCH_CHECK(ctx);
+  return MB_OK;
+}
+
+// keys: [0] seed of player 0's sharing of B, [1], [2] this player's zero-share seeds of the first AND
+int k_party_adder_init(mb_ctx *ctx, int me, const AesKey keys[3], const mb_tensor *in, const mb_tensor *other, mb_tensor *g,
+                       mb_tensor *p_new, mb_tensor *p_send) {
+  const int64_t nvec = (int64_t)(in->nbytes / 16);
+  AES_LAUNCH(ctx, adder_init_party_kernel, AES_TPB_LIGHT, nvec, me, keys[0], keys[1], keys[2], (const vec_t *)in->dptr,
+             other ? (const vec_t *)other->dptr : nullptr, (vec_t *)g->dptr, p_new ? (vec_t *)p_new->dptr : nullptr,
+             p_send ? (vec_t *)p_send->dptr : nullptr, nvec);
+  MB_LAUNCH_CHECK(ctx);
+  return MB_OK;
+}
+
 int k_party_adder_level(mb_ctx *ctx, const AesKey keys[4], const LevelDesc &d, const mb_tensor *const g_in[2],
                         const mb_tensor *const p_in[2], mb_tensor *g_out, mb_tensor *p_out, int64_t nv) {
   PairPtrs g, p;

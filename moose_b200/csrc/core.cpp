@@ -188,14 +188,15 @@ extern "C" int mb_host_free_pinned(mb_ctx *ctx, void *ptr) {
 }
 
 int mb_scratch(mb_ctx *ctx, int slot, size_t bytes, void **out) {
+  // grown in stream order (no device-wide synchronisation: a peer may be waiting for work this thread has yet to
+  // enqueue, csrc/peer_transport.cu)
   if (ctx->scratch_bytes[slot] < bytes) {
     if (ctx->scratch[slot]) {
-      MB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-      MB_CUDA(ctx, cudaFree(ctx->scratch[slot]));
+      MB_CUDA(ctx, cudaFreeAsync(ctx->scratch[slot], ctx->stream));
       ctx->scratch[slot] = nullptr;
       ctx->scratch_bytes[slot] = 0;
     }
-    MB_CUDA(ctx, cudaMalloc(&ctx->scratch[slot], bytes));
+    MB_CUDA(ctx, cudaMallocAsync(&ctx->scratch[slot], bytes, ctx->stream));
     ctx->scratch_bytes[slot] = bytes;
   }
   *out = ctx->scratch[slot];

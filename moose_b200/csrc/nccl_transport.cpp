@@ -121,6 +121,10 @@ int nccl_transport_cb(void *user, int mode, const char *peer, void *buf, size_t 
   mb_nccl_transport *t = (mb_nccl_transport *)user;
   if (!t) return 1;
   CU(t, cudaSetDevice(t->ctx->device));
+  if (mode == 5) {  // capabilities: transfers run on this transport's own stream
+    *(int64_t *)buf = 0;
+    return 0;
+  }
   if (mode == 2 || mode == 3) {
     reap_events(t, mode == 3);
     if (mode == 3) CU(t, cudaStreamSynchronize(t->stream));

@@ -34,6 +34,7 @@ struct mb_party {
   void *user;
   std::string names[3];
   bool have_setup;
+  bool stream_ordered;  // transport capability bit 0: device payloads are ordered on the context's stream
   uint8_t keys[2][16];  // k_me (own) and k_{me+1} (copy received from the next party)
   AesKey sync_cipher;
   uint64_t sync_counter;
@@ -93,9 +94,16 @@ struct P {
     if (rc != 0) fail(MB_ERR_KERNEL, "party transport failed");
   }
   void sync_stream() {
+    if (pt->stream_ordered) return;
     const double t0 = now_s();
     ck(mb_ctx_sync(c));
     pt->sync_seconds += now_s() - t0;
+  }
+  // receive buffer: off the main stream's allocation order unless the transport writes it in stream order
+  mb_tensor *recv_buf(mb_dtype d, int rank, const int64_t *shape) {
+    mb_tensor *t = nullptr;
+    ck(pt->stream_ordered ? mb_tensor_new(c, d, rank, shape, &t) : mb_tensor_new_detached(c, d, rank, shape, &t));
+    return t;
   }
   void reap(bool all) {
     if (pt->in_flight.empty() && !all) return;
@@ -128,8 +136,7 @@ struct P {
     int64_t hdr[10] = {0};
     raw(0, peer, hdr, sizeof(hdr), 0);
     if (hdr[0] != 0 || hdr[2] < 0 || hdr[2] > MB_MAX_RANK) fail(MB_ERR_KERNEL, "party transport: expected a tensor");
-    mb_tensor *t = nullptr;
-    ck(mb_tensor_new_detached(c, (mb_dtype)hdr[1], (int)hdr[2], hdr + 3, &t));
+    mb_tensor *t = recv_buf((mb_dtype)hdr[1], (int)hdr[2], hdr + 3);
     T out(c, t);
     if ((int64_t)t->nbytes != hdr[9]) fail(MB_ERR_KERNEL, "party transport: payload size mismatch");
     if (t->nbytes) raw(0, peer, t->dptr, t->nbytes, 1);
@@ -167,8 +174,7 @@ struct P {
       reap(false);
     }
     if (me == to) {
-      mb_tensor *r = nullptr;
-      ck(mb_tensor_new_detached(c, d, shape_of->rank, shape_of->shape, &r));
+      mb_tensor *r = recv_buf(d, shape_of->rank, shape_of->shape);
       T out(c, r);
       if (r->nbytes) raw(0, from, r->dptr, r->nbytes, 1);
       return out;
@@ -182,8 +188,7 @@ struct P {
   // Every party hands its component to the previous party and gets the next party's, which has the same dtype and
   // shape: one grouped send + receive (transport mode 4), the three transfers run concurrently.
   T ring(const mb_tensor *mine) {
-    mb_tensor *t = nullptr;
-    ck(mb_tensor_new_detached(c, mine->dtype, mine->rank, mine->shape, &t));
+    mb_tensor *t = recv_buf(mine->dtype, mine->rank, mine->shape);
     T got(c, t);
     if (mine->nbytes == 0) return got;
     sync_stream();  // the payload is read by another stream / library
@@ -303,19 +308,40 @@ struct P {
   }
 
   // ---- bilinear: z_me = v_me + PRF(s_me) - PRF(s_{me+1}), then the reshare ring ---------------------------------
-  Pair finish_bilinear(T v) {
+  void zero_keys(AesKey kk[2]) {
     uint8_t sa[16], sb[16];
     zero_seeds(sa, sb);
-    const mb_dtype d = v.p->dtype;
-    T ra = prf(d, v.p, sa), rb = prf(d, v.p, sb);
-    T z = d == MB_BIT ? xor_(v.p, xor_(ra.p, rb.p).p) : add(v.p, sub(ra.p, rb.p).p);
-    ra = T(c, nullptr);
-    rb = T(c, nullptr);
-    T zn = ring(z.p);
-    return Pair{std::move(z), std::move(zn)};
+    mb_aes_expand(sa, &kk[0]);
+    mb_aes_expand(sb, &kk[1]);
+  }
+  T like_new(mb_dtype d, const mb_tensor *like) {
+    mb_tensor *t = nullptr;
+    ck(mb_tensor_new(c, d, like->rank, like->shape, &t));
+    return T(c, t);
+  }
+  Pair finish_bilinear(T v) {  // v is this party's own temporary: the zero share is added in place
+    AesKey kk[2];
+    zero_keys(kk);
+    ck(k_party_zero_add(c, kk, v.p, v.p));
+    T zn = ring(v.p);
+    return Pair{std::move(v), std::move(zn)};
+  }
+  static bool same_shape(const mb_tensor *a, const mb_tensor *b) {
+    if (a->rank != b->rank || a->dtype != b->dtype) return false;
+    for (int i = 0; i < a->rank; i++)
+      if (a->shape[i] != b->shape[i]) return false;
+    return true;
   }
   Pair pmul(const Pair &x, const Pair &y) {  // v = x_me (y_me + y_{me+1}) + x_{me+1} y_me
-    T v = add(mul(x.a.p, add(y.a.p, y.b.p).p).p, mul(x.b.p, y.a.p).p);
+    if (same_shape(x.a.p, y.a.p)) {  // one pass: products, zero share
+      AesKey kk[2];
+      zero_keys(kk);
+      T z = like_new(x.a.p->dtype, x.a.p);
+      ck(k_party_mul(c, kk, x.a.p, x.b.p, y.a.p, y.b.p, z.p));
+      T zn = ring(z.p);
+      return Pair{std::move(z), std::move(zn)};
+    }
+    T v = add(mul(x.a.p, add(y.a.p, y.b.p).p).p, mul(x.b.p, y.a.p).p);  // broadcasting operands
     return finish_bilinear(std::move(v));
   }
   Pair pdot(const Pair &x, const Pair &y) {
@@ -338,8 +364,9 @@ struct P {
   }
 
   // ---- adt_to_rep (convert.rs:392-497): additive (y0 at party 0, y1 at party 1), provider party 2 ------------------
-  Pair adt_to_rep(T y, const mb_tensor *like) {
-    uint8_t sk0[16], sk1[16], key[16], seed1[16], seed2[16];
+  // The provider's seeds: seed1 to party 0, seed2 to party 1 (it keeps both).
+  void adt_seeds(uint8_t seed1[16], uint8_t seed2[16]) {
+    uint8_t sk0[16], sk1[16], key[16];
     sync_key(sk0);
     sync_key(sk1);
     if (me == 2) {
@@ -349,10 +376,10 @@ struct P {
     }
     move_b(2, 0, seed1, 16);
     move_b(2, 1, seed2, 16);
-    const mb_dtype d = like->dtype;
+  }
+  // parties 0 / 1 hold yp = PRF(seed) and diff = y - yp already (fused into the step that produced y)
+  Pair adt_finish(T yp, T diff, mb_dtype d, const mb_tensor *like, const uint8_t seed1[16], const uint8_t seed2[16]) {
     if (me == 2) return Pair{prf(d, like, seed2), prf(d, like, seed1)};  // (y1', y0')
-    T yp = prf(d, like, me == 0 ? seed1 : seed2);
-    T diff = sub(y.p, yp.p);
     T d1 = move_like(1, 0, diff.p, d, like);       // party 0 opens c = (y0 - y0') + (y1 - y1')
     T cc(c, nullptr);
     if (me == 0) cc = add(diff.p, d1.p);
@@ -368,58 +395,53 @@ struct P {
     const unsigned bits = d == MB_RING128 ? 128 : 64, k = bits - 1;
     if (amount + 1 > k) fail(MB_ERR_INVALID_ARGUMENT, "trunc_pr: amount too large for the ring");
     // dealer (party 2): r, r_top, r_msb, additively shared: share 0 = PRF(seed) (the seed goes to party 0), share 1 to party 1
-    uint8_t key[16], seeds[3][16], sk[3][16];
+    uint8_t key[16], seeds[3][16], sk[3][16], seed1[16], seed2[16];
     for (int i = 0; i < 3; i++) sync_key(sk[i]);
     T m1[3] = {T(c, nullptr), T(c, nullptr), T(c, nullptr)};
     if (me == 2) {
-      T r = fresh(d, like);
-      T r_msb = shr(bits - 1, r.p);
-      T r_top = shr(amount + 1, shl(1, r.p).p);
+      AesKey kk[4];
       ck(mb_entropy16(c, key));
-      const mb_tensor *vals[3] = {r.p, r_top.p, r_msb.p};
+      mb_aes_expand(key, &kk[0]);  // r itself
+      ck(mb_entropy16(c, key));
       for (int i = 0; i < 3; i++) {
         derive(key, sk[i], seeds[i]);
-        m1[i] = sub(vals[i], prf(d, like, seeds[i]).p);
+        mb_aes_expand(seeds[i], &kk[1 + i]);
+        m1[i] = like_new(d, like);
       }
+      mb_tensor *const o[3] = {m1[0].p, m1[1].p, m1[2].p};
+      ck(k_party_trunc_dealer(c, kk, amount, o));
     }
     for (int i = 0; i < 3; i++) move_b(2, 0, seeds[i], 16);
+    adt_seeds(seed1, seed2);
     T r1[3] = {T(c, nullptr), T(c, nullptr), T(c, nullptr)};
     for (int i = 0; i < 3; i++) r1[i] = move_like(2, 1, m1[i].p, d, like);
-    T y(c, nullptr);
+    T yp(c, nullptr), diff(c, nullptr);
     if (me == 0) {
-      T r0 = prf(d, like, seeds[0]), rtop0 = prf(d, like, seeds[1]), rmsb0 = prf(d, like, seeds[2]);
-      T a0 = add(x.a.p, x.b.p);                                        // rep_to_adt: x0 + x1
-      T up = fill(d, like, (u128)1 << (k - 1)), down = fill(d, like, (u128)1 << (k - amount - 1));
-      T masked0 = add(add(a0.p, up.p).p, r0.p);
       T masked1 = move_like(1, 0, nullptr, d, like);
-      T cc = add(masked0.p, masked1.p);
-      T c_top = shr(amount + 1, shl(1, cc.p).p);
-      T c_msb = shr(bits - 1, cc.p);
-      {  // the opened top bit travels as a bit tensor (1/64 .. 1/128 of the ring tensor)
-        mb_tensor *cb = nullptr;
-        ck(mb_bit_extract(c, bits - 1, cc.p, &cb));
-        T cbits(c, cb);
-        move(0, 1, cbits.p);
-      }
-      T prod = mul(rmsb0.p, c_msb.p);
-      T ov = sub(sub(add(rmsb0.p, c_msb.p).p, prod.p).p, prod.p);    // r_msb + c_msb - 2 r_msb c_msb
-      y = sub(add(sub(c_top.p, rtop0.p).p, shl(k - amount, ov.p).p).p, down.p);
+      AesKey kk[4];
+      for (int i = 0; i < 3; i++) mb_aes_expand(seeds[i], &kk[i]);
+      mb_aes_expand(seed1, &kk[3]);
+      T cbits = like_new(MB_BIT, like);  // the opened top bit travels as a bit tensor (1/64 .. 1/128 of the ring tensor)
+      yp = like_new(d, like);
+      diff = like_new(d, like);
+      ck(k_party_trunc_p0(c, kk, amount, x.a.p, x.b.p, masked1.p, cbits.p, yp.p, diff.p));
+      move_like(0, 1, cbits.p, MB_BIT, like);
     } else if (me == 1) {
       T masked1 = add(x.b.p, r1[0].p);                                 // a1 = x2, masked with r1
       move_like(1, 0, masked1.p, d, like);
-      T cbits = move(0, 1, nullptr);
-      mb_tensor *cm = nullptr;
-      ck(mb_ring_inject(c, d, 0, cbits.p, &cm));
-      T c_msb(c, cm);
-      T prod = mul(r1[2].p, c_msb.p);
-      T ov = sub(sub(r1[2].p, prod.p).p, prod.p);
-      y = add(neg(r1[1].p).p, shl(k - amount, ov.p).p);
+      T cbits = move_like(0, 1, nullptr, MB_BIT, like);
+      AesKey kyp;
+      mb_aes_expand(seed2, &kyp);
+      yp = like_new(d, like);
+      diff = like_new(d, like);
+      ck(k_party_trunc_p1(c, kyp, amount, r1[1].p, r1[2].p, cbits.p, yp.p, diff.p));
     }
-    return adt_to_rep(std::move(y), like);
+    return adt_finish(std::move(yp), std::move(diff), d, like, seed1, seed2);
   }
 
   // ---- msb: split + msb-pruned Kogge-Stone on this party's components -----------------------------------------------
-  Pair msb(const Pair &x) {
+  // msb(x - y) (y may be null): the split decomposes this player's local sum of the difference directly
+  Pair msb_diff(const Pair &x, const Pair *y) {
     setup();
     const mb_tensor *like = x.a.p;
     const int k = like->dtype == MB_RING128 ? 128 : 64;
@@ -427,40 +449,55 @@ struct P {
     if (n == 0 || n % 128 || like->rank + 1 > MB_MAX_RANK)
       fail(MB_ERR_UNIMPLEMENTED, "party msb: element count must be a positive multiple of 128 (rank <= 5)");
     const int64_t nv = n / 128;
-    // operands of the adder: a = bits(x0 + x1) shared by party 0 as (R, B ^ R, 0); b = (0, 0, bits(x2))
-    uint8_t sk[16], seed[16];
-    sync_key(sk);
-    mb_tensor *tmp = nullptr;
-    T a0(c, nullptr), a1(c, nullptr), b0(c, nullptr), b1(c, nullptr);
-    if (me == 0) {
-      T left = add(x.a.p, x.b.p);
-      ck(mb_bit_decompose(c, left.p, &tmp));
-      T B(c, tmp);
-      derive(pt->keys[0], sk, seed);
-      a0 = prf(MB_BIT, B.p, seed);
-      a1 = xor_(B.p, a0.p);
-      move(0, 1, a1.p);
-      b0 = fill(MB_BIT, B.p, 0);
-      b1 = b0.clone();
-    } else if (me == 1) {
-      ck(mb_bit_decompose(c, x.b.p, &tmp));
-      b1 = T(c, tmp);
-      a0 = move(0, 1, nullptr);
-      a1 = fill(MB_BIT, b1.p, 0);
-      b0 = a1.clone();
-    } else {
-      ck(mb_bit_decompose(c, x.a.p, &tmp));
-      b0 = T(c, tmp);
-      derive(pt->keys[1], sk, seed);
-      a1 = prf(MB_BIT, b0.p, seed);
-      a0 = fill(MB_BIT, b0.p, 0);
-      b1 = a0.clone();
+    int64_t psh_all[MB_MAX_RANK];
+    psh_all[0] = k;
+    for (int r = 0; r < like->rank; r++) psh_all[r + 1] = like->shape[r];
+    auto planes = [&]() {
+      mb_tensor *t = nullptr;
+      ck(mb_tensor_new(c, MB_BIT, like->rank + 1, psh_all, &t));
+      return T(c, t);
+    };
+    // operands of the adder: a = bits(x0 + x1) shared by party 0 as (R, B ^ R, 0); b = (0, 0, bits(x2));
+    // p0 = a ^ b = (R, B ^ R, C), g0 = a & b = (0, (B ^ R) & C, R & C) ^ zero share
+    T own = planes();  // B on party 0, C = bits(x2) on parties 1 and 2
+    {
+      const mb_tensor *terms[4];
+      int nt = 0, neg = 0;
+      if (me == 0) {
+        terms[nt++] = x.a.p;
+        terms[nt++] = x.b.p;
+        if (y) { neg = 0xC; terms[nt++] = y->a.p; terms[nt++] = y->b.p; }
+      } else {
+        terms[nt++] = me == 1 ? x.b.p : x.a.p;
+        if (y) { neg = 0x2; terms[nt++] = me == 1 ? y->b.p : y->a.p; }
+      }
+      ck(k_party_split(c, terms, nt, neg, own.p));
     }
-    // g = a AND b, p = a XOR b on all planes
-    Pair A{std::move(a0), std::move(a1)}, Bp{std::move(b0), std::move(b1)};
-    Pair p0 = pxor(A, Bp);
-    T v = xor_(and_(A.a.p, xor_(Bp.a.p, Bp.b.p).p).p, and_(A.b.p, Bp.a.p).p);
-    Pair g = finish_bilinear(std::move(v));
+    uint8_t sk[16], seed[16] = {0};
+    sync_key(sk);
+    AesKey keys[3];
+    if (me == 0) derive(pt->keys[0], sk, seed);
+    if (me == 2) derive(pt->keys[1], sk, seed);
+    mb_aes_expand(seed, &keys[0]);
+    zero_keys(keys + 1);
+    T g_me = planes();
+    Pair p0{T(c, nullptr), T(c, nullptr)};
+    if (me == 0) {
+      T R = planes(), bR = planes();
+      ck(k_party_adder_init(c, 0, keys, own.p, nullptr, g_me.p, R.p, bR.p));
+      move_like(0, 1, bR.p, MB_BIT, own.p);
+      p0 = Pair{std::move(R), std::move(bR)};
+    } else if (me == 1) {
+      T bR = move_like(0, 1, nullptr, MB_BIT, own.p);
+      ck(k_party_adder_init(c, 1, keys, own.p, bR.p, g_me.p, nullptr, nullptr));
+      p0 = Pair{std::move(bR), std::move(own)};
+    } else {
+      T R = planes();
+      ck(k_party_adder_init(c, 2, keys, own.p, nullptr, g_me.p, R.p, nullptr));
+      p0 = Pair{std::move(own), std::move(R)};
+    }
+    T g_nx = ring(g_me.p);
+    Pair g{std::move(g_me), std::move(g_nx)};
     // pruned levels
     std::vector<LevelDesc> levels;
     std::vector<int> npo;
@@ -516,55 +553,53 @@ struct P {
 
   // ---- Z2 -> ring with a dabit from the dealer (party 2) --------------------------------------------------------------
   Pair ring_inject(mb_dtype ring, unsigned bit_idx, const Pair &x) {
-    const mb_tensor *like_b = x.a.p;
-    mb_tensor *lt = nullptr;
-    ck(mb_tensor_new(c, ring, like_b->rank, like_b->shape, &lt));
-    T like(c, lt);  // shape carrier for ring tensors (contents unused)
-    uint8_t key[16], sk_b[16], sk_br[16], seed_b[16], seed_br[16];
+    const mb_tensor *like = x.a.p;  // shape carrier (a bit tensor)
+    uint8_t key[16], sk_b[16], sk_br[16], seed_b[16], seed_br[16], seed1[16], seed2[16];
     sync_key(sk_b);
     sync_key(sk_br);
     T b1(c, nullptr), br1(c, nullptr);
     if (me == 2) {
-      T b = fresh(MB_BIT, like_b);
-      mb_tensor *brt = nullptr;
-      ck(mb_ring_inject(c, ring, 0, b.p, &brt));
-      T br(c, brt);
+      T b = fresh(MB_BIT, like);
       ck(mb_entropy16(c, key));
       derive(key, sk_b, seed_b);
       derive(key, sk_br, seed_br);
-      b1 = xor_(b.p, prf(MB_BIT, like_b, seed_b).p);
-      br1 = sub(br.p, prf(ring, like.p, seed_br).p);
+      b1 = xor_(b.p, prf(MB_BIT, like, seed_b).p);
+      AesKey kbr;
+      mb_aes_expand(seed_br, &kbr);
+      br1 = like_new(ring, like);
+      ck(k_party_dabit_dealer(c, kbr, b.p, br1.p));  // inject(b) - PRF(seed_br)
     }
     move_b(2, 0, seed_b, 16);
     move_b(2, 0, seed_br, 16);
-    T b1r = move(2, 1, b1.p);
-    T br1r = move(2, 1, br1.p);
-    T s(c, nullptr);
-    if (me == 0) {
-      T b0 = prf(MB_BIT, like_b, seed_b), br0 = prf(ring, like.p, seed_br);
-      T c0 = xor_(xor_(x.a.p, x.b.p).p, b0.p);             // rep_to_adt over Z2: x0 ^ x1, masked
-      T c1 = move(1, 0, nullptr);
-      T cbits = xor_(c0.p, c1.p);
-      move(0, 1, cbits.p);                                  // the opened bit c = x ^ b
-      mb_tensor *crt = nullptr;
-      ck(mb_ring_inject(c, ring, 0, cbits.p, &crt));
-      T cr(c, crt);
-      T prod = mul(br0.p, cr.p);
-      s = shl(bit_idx, sub(sub(add(br0.p, cr.p).p, prod.p).p, prod.p).p);   // b + c - 2 b c on share 0
-    } else if (me == 1) {
-      T c1 = xor_(x.b.p, b1r.p);
-      move(1, 0, c1.p);
-      T cbits = move(0, 1, nullptr);
-      mb_tensor *crt = nullptr;
-      ck(mb_ring_inject(c, ring, 0, cbits.p, &crt));
-      T cr(c, crt);
-      T prod = mul(br1r.p, cr.p);
-      s = shl(bit_idx, sub(sub(br1r.p, prod.p).p, prod.p).p);
+    adt_seeds(seed1, seed2);
+    T b1r = move_like(2, 1, b1.p, MB_BIT, like);
+    T br1r = move_like(2, 1, br1.p, ring, like);
+    T yp(c, nullptr), diff(c, nullptr);
+    if (me != 2) {
+      T cbits(c, nullptr);
+      if (me == 0) {
+        T c0 = xor_(xor_(x.a.p, x.b.p).p, prf(MB_BIT, like, seed_b).p);  // rep_to_adt over Z2: x0 ^ x1, masked
+        T c1 = move_like(1, 0, nullptr, MB_BIT, like);
+        cbits = xor_(c0.p, c1.p);
+        move_like(0, 1, cbits.p, MB_BIT, like);                          // the opened bit c = x ^ b
+      } else {
+        T c1 = xor_(x.b.p, b1r.p);
+        move_like(1, 0, c1.p, MB_BIT, like);
+        cbits = move_like(0, 1, nullptr, MB_BIT, like);
+      }
+      // s = (b_share + [party 0] c - 2 b_share c) << bit_idx, then yp = PRF(seed), diff = s - yp
+      AesKey kbr, kyp;
+      mb_aes_expand(seed_br, &kbr);
+      mb_aes_expand(me == 0 ? seed1 : seed2, &kyp);
+      yp = like_new(ring, like);
+      diff = like_new(ring, like);
+      ck(k_party_dabit_finish(c, kbr, kyp, me == 0, bit_idx, me == 0 ? nullptr : br1r.p, cbits.p, yp.p, diff.p));
     }
-    return adt_to_rep(std::move(s), like.p);
+    return adt_finish(std::move(yp), std::move(diff), ring, like, seed1, seed2);
   }
 
-  Pair less(const Pair &x, const Pair &y) { return msb(psub(x, y)); }
+  Pair msb(const Pair &x) { return msb_diff(x, nullptr); }
+  Pair less(const Pair &x, const Pair &y) { return msb_diff(x, &y); }
 
   // MaximumOp::kernel (softmax.rs:10-53) as a tree
   Pair maximum(std::vector<Pair> &xs, size_t lo, size_t hi) {
@@ -573,10 +608,15 @@ struct P {
     Pair m1 = maximum(xs, lo, mid), m2 = maximum(xs, mid, hi);
     const mb_dtype ring = m1.a.p->dtype;
     Pair lesser = ring_inject(ring, 0, less(m1, m2));
-    T ones = fill(ring, m1.a.p, 1);
-    Pair a = pmul(lesser, m2);
-    Pair b = pmul(public_sub(ones.p, lesser), m1);
-    return padd(a, b);
+    // lesser * m2 + (1 - lesser) * m1: both products and their zero shares in one pass, the sum reshared once
+    AesKey kk[4];
+    zero_keys(kk);
+    zero_keys(kk + 2);
+    T z = like_new(m1.a.p->dtype, m1.a.p);
+    const mb_tensor *sv[2] = {lesser.a.p, lesser.b.p}, *xv[2] = {m1.a.p, m1.b.p}, *yv[2] = {m2.a.p, m2.b.p};
+    ck(k_party_mux(c, kk, me, sv, xv, yv, z.p));
+    T zn = this->ring(z.p);
+    return Pair{std::move(z), std::move(zn)};
   }
 };
 
@@ -615,6 +655,9 @@ extern "C" int mb_party_create(mb_ctx *ctx, int me, mb_transport_fn fn, void *us
   p->user = user;
   for (int i = 0; i < 3; i++) p->names[i] = role_names[i] ? role_names[i] : "";
   p->have_setup = false;
+  int64_t caps = 0;
+  if (fn(user, 5, "", &caps, sizeof(caps), 0) != 0) caps = 0;  // optional mode: an error means "none"
+  p->stream_ordered = (caps & 1) != 0;
   mb_aes_expand(ctx->sid, &p->sync_cipher);  // public sync-key stream, the same on the three parties
   p->sync_counter = 0;
   p->sends_reported = p->bytes_sent = p->transfers = 0;

@@ -112,9 +112,13 @@ class NcclComm:
     def transport(self, _user, mode, peer, buf, nbytes, on_device):
         """mb_transport_fn: raw buffers of the native executor.  Device payloads go straight from / into the
         tensor's memory; host buffers (headers, keys, seeds) are staged through a small device tensor for NCCL.
-        Modes: 0 receive, 1 send, 2 poll completed device sends, 3 wait for all of them, 4 grouped send + receive."""
+        Modes: 0 receive, 1 send, 2 poll completed device sends, 3 wait for all of them, 4 grouped send + receive,
+        5 capabilities."""
         try:
             t = self.torch
+            if mode == 5:  # capabilities: none (transfers run on NCCL's stream)
+                ctypes.cast(buf, ctypes.POINTER(ctypes.c_int64))[0] = 0
+                return 0
             if mode in (2, 3):
                 while self._posted and (mode == 3 or self._posted[0].is_completed()):
                     self._posted.pop(0).wait()

@@ -44,35 +44,59 @@ def run_fused_mlp(args):
     dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     sess = mb.Session(local_rank, args.session_id, None)
     native = None
+    lanes = []          # --lanes K: K independent party sessions (own stream, own rings) working on B / K rows each
     if args.native_nccl:
         from moose_b200.party_rt import NativeNccl
         box = [NativeNccl.unique_id() if rank == 0 else None]
         dist.broadcast_object_list(box, src=0)          # bootstrap only: the unique id
         native = NativeNccl(sess, box[0], rank, roles)
         party = PartySession(sess, rank, native, roles)
+    elif args.peer_memory:
+        from moose_b200.party_rt import PeerMemory
+        for lane in range(args.lanes):
+            ls = sess if lane == 0 else mb.Session(local_rank, args.session_id, None)
+            pm = PeerMemory(ls, rank, roles, args.ring_mib << 20)
+            handles = [None] * world
+            dist.all_gather_object(handles, pm.handle_bytes())   # bootstrap only: the inbox handles
+            pm.connect(handles)
+            lanes.append((ls, pm, PartySession(ls, rank, pm, roles)))
+        dist.barrier()
+        native, party = lanes[0][1], lanes[0][2]
     else:
         comm = NcclComm(dist, sess, {r: i for i, r in enumerate(roles)}, local_rank)
         party = PartySession(sess, rank, comm.transport, roles)
+    if not lanes:
+        lanes = [(sess, native, party)]
     dims, B = args.dims, args.mlp
+    if B % len(lanes):
+        raise SystemExit("--lanes must divide the batch")
+    rows = B // len(lanes)
     ws = [np.random.default_rng(4 + l).normal(0, dims[l] ** -0.5, (dims[l], dims[l + 1])) for l in range(len(dims) - 1)]
     bs = [np.random.default_rng(40 + l).normal(0, 0.1, dims[l + 1]) for l in range(len(dims) - 1)]
-    mlp = PartyMLP(party, ws, bs, mb.RING64, 23)
+    mlps = [PartyMLP(pt, ws, bs, mb.RING64, 23) for _, _, pt in lanes]
     x = np.random.default_rng(3).uniform(0, 1, (B, dims[0]))
-    xf = sess.fixedpoint_encode(mb.RING64, 23, sess.from_host(mb.FLOAT64, x)) if rank == 0 else None
+    xfs = [ls.fixedpoint_encode(mb.RING64, 23, ls.from_host(mb.FLOAT64, x[i * rows:(i + 1) * rows])) if rank == 0 else None
+           for i, (ls, _, _) in enumerate(lanes)]
+
+    def run_once():
+        outs = [m.forward(xf, rows) for m, xf in zip(mlps, xfs)]   # enqueue only: no lane waits for its stream here
+        for ls, _, pt in lanes:
+            pt.flush()
+            ls.sync()
+        return outs
+
     dist.barrier()
-    out = mlp.forward(xf, B)          # untimed: NCCL connections, scratch growth
-    party.flush()
-    sess.sync()
-    sent0, st0 = party.bytes_sent, party.stats()
+    outs = run_once()          # untimed: connections, scratch growth
+    sent0 = sum(pt.bytes_sent for _, _, pt in lanes)
+    st0 = party.stats()
     dist.barrier()
     t0 = time.perf_counter()
     for _ in range(args.repeat):
-        out = mlp.forward(xf, B)
-        party.flush()
-        sess.sync()
+        outs = run_once()
     dt = (time.perf_counter() - t0) / args.repeat
     dist.barrier()
-    sent = torch.tensor([party.bytes_sent - sent0], dtype=torch.int64, device=f"cuda:{local_rank}")
+    out = outs[0]
+    sent = torch.tensor([sum(pt.bytes_sent for _, _, pt in lanes) - sent0], dtype=torch.int64, device=f"cuda:{local_rank}")
     dist.all_reduce(sent)
     err = None
     if out is not None:
@@ -89,13 +113,20 @@ def run_fused_mlp(args):
     if rank == 0:
         print(json.dumps({"mode": "party-per-gpu (party runtime, fused party-sliced kernels)", "parties": roles,
                           "per_party": gathered,
-                          "transport": "ncclSend/ncclRecv from C++ (native)" if native else "nccl send/recv (torch.distributed)",
+                          "transport": ("peer-memory rings over NVLink, stream-ordered (csrc/peer_transport.cu)" if args.peer_memory
+                                        else "ncclSend/ncclRecv from C++ (native)" if native
+                                        else "nccl send/recv (torch.distributed)"),
                           "workload": "mlp_" + "-".join(map(str, dims)) + f"_relu_ring64_fixed(14,23)_batch{B}",
-                          "rows_per_s": B / dt, "seconds_per_run": dt, "payload_bytes_per_run": int(sent[0]) // args.repeat,
+                          "lanes": len(lanes), "rows_per_s": B / dt, "seconds_per_run": dt, "payload_bytes_per_run": int(sent[0]) // args.repeat,
                           "max_abs_err_first_rows": err}), flush=True)
-    party.close()
-    if native:
-        native.close()
+    for _, _, pt in lanes:
+        pt.close()
+    dist.barrier()          # nobody writes into an inbox that is about to be freed
+    for ls, tr, _ in lanes:
+        if tr is not None:
+            tr.close()
+        if ls is not sess:
+            ls.close()
     sess.close()
     dist.destroy_process_group()
 
@@ -110,6 +141,13 @@ def main():
     ap.add_argument("--native-nccl", action="store_true",
                     help="with --fused: the library's own NCCL transport (ncclSend / ncclRecv from C++) instead of "
                          "torch.distributed P2P")
+    ap.add_argument("--peer-memory", action="store_true",
+                    help="with --fused: the peer-memory transport (rings in the receivers' HBM written over NVLink, every "
+                         "transfer ordered on the party's stream, no host synchronisation per transfer)")
+    ap.add_argument("--lanes", type=int, default=1,
+                    help="with --peer-memory: split the batch over this many independent party sessions (own stream and "
+                         "rings each); one lane's waits for its peers are filled by another lane's kernels")
+    ap.add_argument("--ring-mib", type=int, default=1024, help="with --peer-memory: bytes of one ring, in MiB")
     ap.add_argument("--fused", action="store_true",
                     help="with --mlp: run the party runtime (csrc/party.cpp: party-sliced fused kernels, msb-pruned adder, "
                          "seeds on the wire) instead of the per-op lowered graph")

@@ -41,6 +41,33 @@ class NativeNccl:
             self.handle = ctypes.c_void_p()
 
 
+class PeerMemory:
+    """The library's peer-memory transport (csrc/peer_transport.cu): rings in the receivers' HBM written over NVLink,
+    every transfer enqueued on the context's stream.  Start-up in two steps: create on every rank, hand the
+    128-byte `handle_bytes()` of all ranks (rank order) to `connect`.  Call `close()` only after a barrier."""
+
+    def __init__(self, sess: Session, rank: int, role_names: Sequence[str], ring_bytes: int = 0):
+        names = (ctypes.c_char_p * len(role_names))(*[n.encode() for n in role_names])
+        self._names, self.sess = names, sess
+        self.handle = ctypes.c_void_p()
+        sess._check(lib().mb_peer_transport_create(sess.ctx, rank, len(role_names), names, ring_bytes, ctypes.byref(self.handle)))
+        self.fn = lib().mb_peer_transport_fn()
+
+    def handle_bytes(self) -> bytes:
+        buf = (ctypes.c_uint8 * 128)()
+        self.sess._check(lib().mb_peer_transport_handle(self.handle, buf))
+        return bytes(buf)
+
+    def connect(self, handles: Sequence[bytes]):
+        blob = b"".join(handles)
+        self.sess._check(lib().mb_peer_transport_connect(self.handle, blob))
+
+    def close(self):
+        if self.handle:
+            lib().mb_peer_transport_free(self.handle)
+            self.handle = ctypes.c_void_p()
+
+
 class PShare:
     """This party's two shares (x_me, x_{me+1}) of a replicated tensor."""
 
@@ -66,7 +93,7 @@ class PartySession:
         names = (ctypes.c_char_p * 3)(*[n.encode() for n in role_names])
         self._names = names
         self._p = ctypes.c_void_p()
-        if isinstance(transport, NativeNccl):   # C function + handle: no interpreter in the transfer loop
+        if isinstance(transport, (NativeNccl, PeerMemory)):   # C function + handle: no interpreter in the transfer loop
             self._cb, user = ctypes.c_void_p(transport.fn), transport.handle
         else:
             self._cb, user = TRANSPORT_FN(transport), None
@@ -172,6 +199,9 @@ class LocalTransport:
     def endpoint(self, me: str, sess: Session):
         def fn(_user, mode, peer, buf, nbytes, on_device):
             try:
+                if mode == 5:  # capabilities: none
+                    ctypes.cast(buf, ctypes.POINTER(ctypes.c_int64))[0] = 0
+                    return 0
                 if mode in (2, 3):  # every send below is complete when it returns
                     ctypes.cast(buf, ctypes.POINTER(ctypes.c_int64))[0] = fn.sent
                     return 0

@@ -9,21 +9,42 @@ import pytest
 
 import moose_b200 as mb
 from moose_b200 import BIT, RING64, RING128
-from moose_b200.party_rt import LocalTransport, PartyMLP, PartySession
+from moose_b200.party_rt import LocalTransport, PartyMLP, PartySession, PeerMemory
 
 pytestmark = pytest.mark.gpu
 NAMES = ("player0", "player1", "player2")
 DT = {64: RING64, 128: RING128}
 
 
+_TRANSPORT = {"kind": "local"}
+
+
+@pytest.fixture(autouse=True, params=["local", "peer"])
+def transport_kind(request):
+    """Every test runs over the in-process queues and over the peer-memory rings (csrc/peer_transport.cu; three
+    contexts of one process on one GPU, 1 MiB rings so that payloads wrap and split into chunks)."""
+    _TRANSPORT["kind"] = request.param
+    yield request.param
+    _TRANSPORT["kind"] = "local"
+
+
 def run_parties(fn, session_id="party-test"):
-    lt = LocalTransport(NAMES)
     sessions = [mb.Session(0, session_id, bytes([17 * (i + 1)]) * 16) for i in range(3)]
+    peers = []
+    if _TRANSPORT["kind"] == "peer":
+        peers = [PeerMemory(sessions[i], i, NAMES, 1 << 20) for i in range(3)]
+        handles = [p.handle_bytes() for p in peers]
+        for p in peers:
+            p.connect(handles)
+        endpoints = peers
+    else:
+        lt = LocalTransport(NAMES)
+        endpoints = [lt.endpoint(NAMES[i], sessions[i]) for i in range(3)]
     results, errors = [None] * 3, []
 
     def worker(i):
         try:
-            ps = PartySession(sessions[i], i, lt.endpoint(NAMES[i], sessions[i]), NAMES)
+            ps = PartySession(sessions[i], i, endpoints[i], NAMES)
             results[i] = fn(ps)
             ps.flush()
             ps.close()
@@ -37,6 +58,8 @@ def run_parties(fn, session_id="party-test"):
         t.join(timeout=300)
     assert not errors, errors
     assert all(not t.is_alive() for t in threads), "a party is stuck"
+    for p in peers:
+        p.close()
     for s in sessions:
         s.close()
     return results
