@@ -448,7 +448,7 @@ int mb_exec_free(mb_exec *e);
  *   3 flush: wait for all posted sends, then report like 2;
  *   4 grouped exchange (party runtime only): buf points to an mb_sendrecv; send and receive the two device
  *     buffers concurrently and return when both are complete;
- *   5 capabilities (party runtime only, optional): write a bit mask to *(int64_t *)buf.  Bit 0: device payloads are
+ *   5 capabilities (optional): write a bit mask to *(int64_t *)buf.  Bit 0: device payloads are
  *     ordered on the context's stream -- the caller need not synchronise the stream before a send, and a received
  *     buffer is valid in stream order rather than at return.  A transport that does not know the mode leaves 0.
  * Return 0 on success.  The caller binds it to NCCL send/recv between the parties' GPUs. */

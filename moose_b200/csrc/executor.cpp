@@ -295,6 +295,7 @@ struct mb_exec {
   std::string role;
   mb_transport_fn transport;
   void *transport_user;
+  bool stream_ordered;  // transport capability bit 0 (mode 5): device payloads are ordered on the context's stream
   std::vector<Val> values;
   std::unordered_map<std::string, Val> bound;    // overrides / Input arguments by op name resp. arg_name
   std::map<std::string, int> outputs, saved;     // tag / key -> op index holding the value
@@ -365,6 +366,7 @@ struct Runner {
     return rc;
   }
   void sync() {
+    if (e->stream_ordered) return;
     const double t0 = now_s();
     ck(mb_ctx_sync(c));
     e->sync_seconds += now_s() - t0;
@@ -521,7 +523,8 @@ struct Runner {
     if (v.kind == V_TENSOR) {
       if (hdr[2] < 0 || hdr[2] > MB_MAX_RANK) fail(MB_ERR_KERNEL, "transport: bad tensor header");
       // receive buffer outside the stream order: the transfer can start while this party's kernels still run
-      ck(mb_tensor_new_detached(c, (mb_dtype)hdr[1], (int)hdr[2], hdr + 3, &v.t));
+      ck(e->stream_ordered ? mb_tensor_new(c, (mb_dtype)hdr[1], (int)hdr[2], hdr + 3, &v.t)
+                           : mb_tensor_new_detached(c, (mb_dtype)hdr[1], (int)hdr[2], hdr + 3, &v.t));
       if (mb_tensor_nbytes(v.t) != nbytes) fail(MB_ERR_KERNEL, "transport: payload size does not match the tensor header");
       if (nbytes && xfer(0, peer, mb_tensor_device_ptr(v.t), nbytes, 1) != 0)
         fail(MB_ERR_KERNEL, "transport: receive of payload from " + peer + " failed");
@@ -893,6 +896,7 @@ extern "C" int mb_exec_create(mb_ctx *ctx, const mb_graph *g, const char *role, 
   if (role) e->role = role;
   e->transport = nullptr;
   e->transport_user = nullptr;
+  e->stream_ordered = false;
   e->values.resize(g->ops.size());
   e->executed = e->bytes_sent = 0;
   e->transport_seconds = e->sync_seconds = 0.0;
@@ -915,6 +919,9 @@ extern "C" int mb_exec_set_transport(mb_exec *e, mb_transport_fn fn, void *user)
   if (!e) return mb_fail(nullptr, MB_ERR_INVALID_ARGUMENT, "mb_exec_set_transport: NULL executor");
   e->transport = fn;
   e->transport_user = user;
+  int64_t caps = 0;
+  if (fn && fn(user, 5, "", &caps, sizeof(caps), 0) != 0) caps = 0;  // optional mode: an error means "none"
+  e->stream_ordered = (caps & 1) != 0;
   return MB_OK;
 }
 

@@ -413,11 +413,16 @@ struct P {
     }
     for (int i = 0; i < 3; i++) move_b(2, 0, seeds[i], 16);
     adt_seeds(seed1, seed2);
+    // message order: r to the second player first (all it needs to answer the first player), its masked share to the
+    // first player, then r_top and r_msb behind it
     T r1[3] = {T(c, nullptr), T(c, nullptr), T(c, nullptr)};
-    for (int i = 0; i < 3; i++) r1[i] = move_like(2, 1, m1[i].p, d, like);
+    r1[0] = move_like(2, 1, m1[0].p, d, like);
+    T masked1(c, nullptr);
+    if (me == 1) masked1 = add(x.b.p, r1[0].p);                          // a1 = x2, masked with r1
+    masked1 = move_like(1, 0, masked1.p, d, like);
+    for (int i = 1; i < 3; i++) r1[i] = move_like(2, 1, m1[i].p, d, like);
     T yp(c, nullptr), diff(c, nullptr);
     if (me == 0) {
-      T masked1 = move_like(1, 0, nullptr, d, like);
       AesKey kk[4];
       for (int i = 0; i < 3; i++) mb_aes_expand(seeds[i], &kk[i]);
       mb_aes_expand(seed1, &kk[3]);
@@ -427,8 +432,6 @@ struct P {
       ck(k_party_trunc_p0(c, kk, amount, x.a.p, x.b.p, masked1.p, cbits.p, yp.p, diff.p));
       move_like(0, 1, cbits.p, MB_BIT, like);
     } else if (me == 1) {
-      T masked1 = add(x.b.p, r1[0].p);                                 // a1 = x2, masked with r1
-      move_like(1, 0, masked1.p, d, like);
       T cbits = move_like(0, 1, nullptr, MB_BIT, like);
       AesKey kyp;
       mb_aes_expand(seed2, &kyp);
@@ -572,21 +575,20 @@ struct P {
     move_b(2, 0, seed_b, 16);
     move_b(2, 0, seed_br, 16);
     adt_seeds(seed1, seed2);
+    // message order: the dealer's bit share, the second player's masked bit, the dealer's ring share (in flight while
+    // the first player opens c), the opened bit
     T b1r = move_like(2, 1, b1.p, MB_BIT, like);
+    T c0(c, nullptr), c1(c, nullptr);
+    if (me == 0) c0 = xor_(xor_(x.a.p, x.b.p).p, prf(MB_BIT, like, seed_b).p);  // rep_to_adt over Z2: x0 ^ x1, masked
+    if (me == 1) c1 = xor_(x.b.p, b1r.p);
+    c1 = move_like(1, 0, c1.p, MB_BIT, like);
     T br1r = move_like(2, 1, br1.p, ring, like);
     T yp(c, nullptr), diff(c, nullptr);
     if (me != 2) {
       T cbits(c, nullptr);
-      if (me == 0) {
-        T c0 = xor_(xor_(x.a.p, x.b.p).p, prf(MB_BIT, like, seed_b).p);  // rep_to_adt over Z2: x0 ^ x1, masked
-        T c1 = move_like(1, 0, nullptr, MB_BIT, like);
-        cbits = xor_(c0.p, c1.p);
-        move_like(0, 1, cbits.p, MB_BIT, like);                          // the opened bit c = x ^ b
-      } else {
-        T c1 = xor_(x.b.p, b1r.p);
-        move_like(1, 0, c1.p, MB_BIT, like);
-        cbits = move_like(0, 1, nullptr, MB_BIT, like);
-      }
+      if (me == 0) cbits = xor_(c0.p, c1.p);                               // the opened bit c = x ^ b
+      T got = move_like(0, 1, cbits.p, MB_BIT, like);
+      if (me == 1) cbits = std::move(got);
       // s = (b_share + [party 0] c - 2 b_share c) << bit_idx, then yp = PRF(seed), diff = s - yp
       AesKey kbr, kyp;
       mb_aes_expand(seed_br, &kbr);

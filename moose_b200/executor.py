@@ -292,7 +292,10 @@ class Executor:
         self.sess._check(lib().mb_exec_create(self.sess.ctx, self._graph, self.role.encode() if self.role else None,
                                               ctypes.byref(self._exec)))
         self.sess._check(lib().mb_exec_set_keep_values(self._exec, int(self.keep_values)))
-        if self.comm is not None:
+        if self.comm is not None and hasattr(self.comm, "fn"):   # a transport of the library: C function + handle
+            self._cb = ctypes.c_void_p(self.comm.fn)
+            self.sess._check(lib().mb_exec_set_transport(self._exec, self._cb, self.comm.handle))
+        elif self.comm is not None:
             self._cb = TRANSPORT_FN(self.comm.transport)
             self.sess._check(lib().mb_exec_set_transport(self._exec, self._cb, None))
         return self
@@ -302,7 +305,8 @@ class Executor:
             self.load(ops)
         for name, t in list(self.overrides.items()) + list((arguments or {}).items()):
             self.sess._check(lib().mb_exec_bind_tensor(self._exec, name.encode(), t.h))
-        if self.comm is not None:
+        native = self.comm is not None and hasattr(self.comm, "fn")
+        if self.comm is not None and not native:
             self.comm.flush()
             self.comm._posted, self.comm._completed = [], 0  # the executor counts completed sends per run
         try:
@@ -312,9 +316,10 @@ class Executor:
         self.executed = int(lib().mb_exec_executed(self._exec))
         self.transport_seconds = float(lib().mb_exec_seconds(self._exec, 0))
         self.sync_seconds = float(lib().mb_exec_seconds(self._exec, 1))
-        if self.comm is not None:
+        if self.comm is not None and not native:
             self.comm.flush()
-            self.comm.bytes_sent += int(lib().mb_exec_bytes_sent(self._exec))
+        if self.comm is not None:
+            self.comm.bytes_sent = getattr(self.comm, "bytes_sent", 0) + int(lib().mb_exec_bytes_sent(self._exec))
         for saved, store in ((0, self.outputs), (1, self.saved)):
             i = 0
             while True:

@@ -142,7 +142,7 @@ def main():
                     help="with --fused: the library's own NCCL transport (ncclSend / ncclRecv from C++) instead of "
                          "torch.distributed P2P")
     ap.add_argument("--peer-memory", action="store_true",
-                    help="with --fused: the peer-memory transport (rings in the receivers' HBM written over NVLink, every "
+                    help="the peer-memory transport (rings in the receivers' HBM written over NVLink, every "
                          "transfer ordered on the party's stream, no host synchronisation per transfer)")
     ap.add_argument("--lanes", type=int, default=1,
                     help="with --peer-memory: split the batch over this many independent party sessions (own stream and "
@@ -183,7 +183,14 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     role = roles[rank]
     sess = mb.Session(local_rank, args.session_id, None)  # OS entropy, like PrfKeyGen in the reference
-    comm = NcclComm(dist, sess, {r: i for i, r in enumerate(roles)}, local_rank)
+    if args.peer_memory:
+        from moose_b200.party_rt import PeerMemory
+        comm = PeerMemory(sess, rank, roles, args.ring_mib << 20)
+        handles = [None] * world
+        dist.all_gather_object(handles, comm.handle_bytes())   # bootstrap only: the inbox handles
+        comm.connect(handles)
+    else:
+        comm = NcclComm(dist, sess, {r: i for i, r in enumerate(roles)}, local_rank)
     # the two float constants, left operand first: decided by the constant's own shape ([1,3] . [3,1] in the exemplar)
     consts = [op for op in ops if op.kind == "Constant" and "Float64Tensor" in op.attrs.get("value", "")]
     consts.sort(key=lambda op: np.array(tx.parse_constant(op.attrs["value"])[1]).shape[0])
@@ -251,9 +258,16 @@ def main():
     if rank == 0:
         extra = {} if args.mlp is None else {"workload": "mlp_" + "-".join(map(str, args.dims)) + f"_relu_ring64_fixed(14,23)_batch{args.mlp}",
                                               "rows_per_s": args.mlp / dt}
-        print(json.dumps({"mode": "party-per-gpu", "parties": roles, "transport": "nccl send/recv", **extra,
+        print(json.dumps({"mode": "party-per-gpu", "parties": roles,
+                          "transport": "peer-memory rings over NVLink (csrc/peer_transport.cu)" if args.peer_memory else "nccl send/recv",
+                          **extra,
                           "ops": len(ops), "seconds_per_run": dt, "payload_bytes_per_run": int(sent[0]) // args.repeat,
                           "per_party": gathered}), flush=True)
+    if ex is not None:
+        ex.close()
+    dist.barrier()          # nobody writes into an inbox that is about to be freed
+    if args.peer_memory:
+        comm.close()
     sess.close()
     dist.destroy_process_group()
 

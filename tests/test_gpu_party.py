@@ -179,3 +179,60 @@ def test_party_mlp_matches_float():
             h = np.maximum(h, 0)
     assert np.abs(res[0][0] - h).max() < 1e-4 and res[1][0] is None
     assert all(r[1] > 0 for r in res)
+
+
+def test_lowered_graph_three_executors_over_peer_memory(transport_kind):
+    """The native executor in party-per-process mode over the peer-memory transport: the lowered + networked MLP
+    graph (moose_b200/lowering.py), one executor per party as threads on one GPU, every Send / Receive through the
+    rings (stream-ordered: no host synchronisation per transfer)."""
+    if transport_kind != "peer":
+        pytest.skip("one transport is enough here")
+    from moose_b200.executor import Executor
+    from moose_b200.lowering import Lowering, networking_pass, prune_pass
+
+    dims, batch = (6, 5, 4, 3), 4
+    rng = np.random.default_rng(0)
+    x = rng.uniform(0, 1, (batch, dims[0]))
+    ws = [rng.normal(0, dims[l] ** -0.5, (dims[l], dims[l + 1])) for l in range(3)]
+    bs = [rng.normal(0, 0.1, (1, dims[l + 1])) for l in range(3)]
+    want = x
+    for l in range(3):
+        want = want @ ws[l] + bs[l]
+        if l < 2:
+            want = np.maximum(want, 0)
+    net = networking_pass(prune_pass(Lowering(64).mlp_program(3, 23)))
+    sessions = [mb.Session(0, "peer-exec", None) for _ in range(3)]
+    peers = [PeerMemory(sessions[i], i, NAMES, 1 << 20) for i in range(3)]
+    handles = [p.handle_bytes() for p in peers]
+    for p in peers:
+        p.connect(handles)
+    results, errors = [None] * 3, []
+
+    def worker(i):
+        try:
+            s = sessions[i]
+            over = {}
+            for l in range(3):
+                over[f"w{l}"], over[f"b{l}"] = s.from_host(mb.FLOAT64, ws[l]), s.from_host(mb.FLOAT64, bs[l])
+            if i == 0:
+                over["x"] = s.from_host(mb.FLOAT64, x)
+            ex = Executor(s, role=NAMES[i], comm=peers[i], overrides=over, keep_values=False)
+            outs = ex.run(net)
+            results[i] = {k: v.to_host() for k, v in outs.items()}
+            s.sync()
+            ex.close()
+        except Exception as e:  # noqa: BLE001
+            errors.append((i, repr(e)))
+
+    threads = [threading.Thread(target=worker, args=(i,)) for i in range(3)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=200)
+    assert not errors, errors
+    assert all(not t.is_alive() for t in threads), "a party is stuck"
+    for p in peers:
+        p.close()
+    for s in sessions:
+        s.close()
+    assert np.abs(results[0]["output_0"] - want).max() < 1e-5
