@@ -450,7 +450,14 @@ int mb_exec_free(mb_exec *e);
  *     buffers concurrently and return when both are complete;
  *   5 capabilities (optional): write a bit mask to *(int64_t *)buf.  Bit 0: device payloads are
  *     ordered on the context's stream -- the caller need not synchronise the stream before a send, and a received
- *     buffer is valid in stream order rather than at return.  A transport that does not know the mode leaves 0.
+ *     buffer is valid in stream order rather than at return.  Bit 1: modes 6 / 7 exist.  A transport that does not
+ *     know the mode leaves 0;
+ *   6 reserve (only with capability bit 1): buf points to an mb_reserve; the transport sets `ptr` to device memory
+ *     of the RECEIVER (peer memory over NVLink) where the next payload of `nbytes` for `peer` goes, valid for work
+ *     enqueued on the context's stream after the call, or to NULL (the caller then sends the ordinary way);
+ *   7 publish: the payload reserved last for `peer` has been written by work enqueued on the context's stream; the
+ *     receiver's matching receive (mode 0 / 4 with the same size) may complete.  This is how a kernel that computes
+ *     a share also delivers it: its stores go to the local tensor and to the reserved peer memory.
  * Return 0 on success.  The caller binds it to NCCL send/recv between the parties' GPUs. */
 typedef struct {
   const char *send_peer;
@@ -460,6 +467,11 @@ typedef struct {
   void *recv_buf;
   size_t recv_bytes;
 } mb_sendrecv;
+typedef struct {
+  const char *peer;
+  size_t nbytes;
+  void *ptr;
+} mb_reserve;
 typedef int (*mb_transport_fn)(void *user, int mode, const char *peer_role, void *buf, size_t nbytes, int on_device);
 int mb_exec_set_transport(mb_exec *e, mb_transport_fn fn, void *user);
 /* Binds a tensor to an Input operation (by arg_name) or replaces the result of the named operation (e.g. the

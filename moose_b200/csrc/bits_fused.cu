@@ -194,7 +194,8 @@ struct PairPtrs {
 };
 __global__ void __launch_bounds__(AES_TPB_MID) adder_level_party_kernel(AesKey pg_a, AesKey pg_b, AesKey pp_a, AesKey pp_b, LevelDesc d,
                                                                        PairPtrs g_in, PairPtrs p_in, vec_t *__restrict__ g_out,
-                                                                       vec_t *__restrict__ p_out, int64_t nv) {
+                                                                       vec_t *__restrict__ p_out, vec_t *__restrict__ g_rem,
+                                                                       vec_t *__restrict__ p_rem, int64_t nv) {
   extern __shared__ __align__(16) uint32_t sT[];
   aes_load_table(sT);
   const AesLane L = aes_lane(sT);
@@ -220,10 +221,13 @@ __global__ void __launch_bounds__(AES_TPB_MID) adder_level_party_kernel(AesKey p
       }
     }
     vec_t z = vxor(vxor(vand(P0, vxor(Gs0, Gs1)), vand(P1, Gs0)), vxor(prf_vec<VK_BIT>(L, pg_a, pos), prf_vec<VK_BIT>(L, pg_b, pos)));
-    g_out[(int64_t)j * nv + v] = vxor(G0, z);
+    z = vxor(G0, z);
+    g_out[(int64_t)j * nv + v] = z;
+    if (g_rem) g_rem[(int64_t)j * nv + v] = z;  // the reshare: straight into the previous player's ring
     if (want_p) {
       z = vxor(vxor(vand(P0, vxor(Ps0, Ps1)), vand(P1, Ps0)), vxor(prf_vec<VK_BIT>(L, pp_a, pos), prf_vec<VK_BIT>(L, pp_b, pos)));
       p_out[(int64_t)d.pout[j] * nv + v] = z;
+      if (p_rem) p_rem[(int64_t)d.pout[j] * nv + v] = z;
     }
   }
 }
@@ -283,25 +287,29 @@ __global__ void __launch_bounds__(TPB) party_split_kernel(SplitTerms terms, uint
 __global__ void __launch_bounds__(AES_TPB_LIGHT) adder_init_party_kernel(int me, AesKey k_share, AesKey ka, AesKey kb,
                                                                         const vec_t *__restrict__ in, const vec_t *__restrict__ other,
                                                                         vec_t *__restrict__ g, vec_t *__restrict__ p_new,
-                                                                        vec_t *__restrict__ p_send, int64_t nvec) {
+                                                                        vec_t *__restrict__ p_send, vec_t *__restrict__ g_rem,
+                                                                        int64_t nvec) {
   extern __shared__ __align__(16) uint32_t sT[];
   aes_load_table(sT);
   const AesLane L = aes_lane(sT);
   for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
     const vec_t x = in[v];
     const vec_t z = vxor(prf_vec<VK_BIT>(L, ka, (uint64_t)v), prf_vec<VK_BIT>(L, kb, (uint64_t)v));
+    vec_t gv;
     if (me == 1) {
-      g[v] = vxor(vand(other[v], x), z);
+      gv = vxor(vand(other[v], x), z);
     } else {
       const vec_t R = prf_vec<VK_BIT>(L, k_share, (uint64_t)v);
       p_new[v] = R;
       if (me == 0) {
         p_send[v] = vxor(x, R);
-        g[v] = z;
+        gv = z;
       } else {
-        g[v] = vxor(vand(R, x), z);
+        gv = vxor(vand(R, x), z);
       }
     }
+    g[v] = gv;
+    if (g_rem) g_rem[v] = gv;  // the reshare of g0
   }
 }
 
@@ -626,24 +634,26 @@ int k_party_split(mb_ctx *ctx, const mb_tensor *const terms[], int nterms, int n
 
 // keys: [0] seed of player 0's sharing of B, [1], [2] this player's zero-share seeds of the first AND
 int k_party_adder_init(mb_ctx *ctx, int me, const AesKey keys[3], const mb_tensor *in, const mb_tensor *other, mb_tensor *g,
-                       mb_tensor *p_new, mb_tensor *p_send) {
+                       mb_tensor *p_new, mb_tensor *p_send, void *g_remote) {
   const int64_t nvec = (int64_t)(in->nbytes / 16);
   AES_LAUNCH(ctx, adder_init_party_kernel, AES_TPB_LIGHT, nvec, me, keys[0], keys[1], keys[2], (const vec_t *)in->dptr,
              other ? (const vec_t *)other->dptr : nullptr, (vec_t *)g->dptr, p_new ? (vec_t *)p_new->dptr : nullptr,
-             p_send ? (vec_t *)p_send->dptr : nullptr, nvec);
+             p_send ? (vec_t *)p_send->dptr : nullptr, (vec_t *)g_remote, nvec);
   MB_LAUNCH_CHECK(ctx);
   return MB_OK;
 }
 
 int k_party_adder_level(mb_ctx *ctx, const AesKey keys[4], const LevelDesc &d, const mb_tensor *const g_in[2],
-                        const mb_tensor *const p_in[2], mb_tensor *g_out, mb_tensor *p_out, int64_t nv) {
+                        const mb_tensor *const p_in[2], mb_tensor *g_out, mb_tensor *p_out, int64_t nv, void *remote) {
   PairPtrs g, p;
   for (int c = 0; c < 2; c++) {
     g.s[c] = (const vec_t *)g_in[c]->dptr;
     p.s[c] = (const vec_t *)p_in[c]->dptr;
   }
   AES_LAUNCH(ctx, adder_level_party_kernel, AES_TPB_MID, (int64_t)d.nout * nv, keys[0], keys[1], keys[2], keys[3], d, g, p,
-             (vec_t *)g_out->dptr, (vec_t *)p_out->dptr, nv);
+             (vec_t *)g_out->dptr, (vec_t *)p_out->dptr, (vec_t *)remote,
+             // g' and p' are two views of one buffer; the remote copy has the same layout
+             remote ? (vec_t *)((uint8_t *)remote + ((uint8_t *)p_out->dptr - (uint8_t *)g_out->dptr)) : nullptr, nv);
   MB_LAUNCH_CHECK(ctx);
   return MB_OK;
 }

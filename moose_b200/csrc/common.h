@@ -171,13 +171,15 @@ struct LevelDesc {
 int k_adder_plan_msb(int k, std::vector<LevelDesc> *levels_out, std::vector<int> *np_out, int *final_gslot);
 int k_party_split(mb_ctx *ctx, const mb_tensor *const terms[], int nterms, int neg_mask, mb_tensor *out);
 int k_party_adder_init(mb_ctx *ctx, int me, const AesKey keys[3], const mb_tensor *in, const mb_tensor *other, mb_tensor *g,
-                       mb_tensor *p_new, mb_tensor *p_send);
+                       mb_tensor *p_new, mb_tensor *p_send, void *g_remote);
 // party-sliced fused steps (party_fused.cu)
+// `remote` (may be NULL): device memory of the previous player (reserved through the transport) that receives the
+// same values as z -- the reshare is done by the kernel that computes the share
 int k_party_mul(mb_ctx *ctx, const AesKey kk[2], const mb_tensor *xa, const mb_tensor *xb, const mb_tensor *ya, const mb_tensor *yb,
-                mb_tensor *z);
-int k_party_zero_add(mb_ctx *ctx, const AesKey kk[2], const mb_tensor *v, mb_tensor *z);
+                mb_tensor *z, void *remote);
+int k_party_zero_add(mb_ctx *ctx, const AesKey kk[2], const mb_tensor *v, mb_tensor *z, void *remote);
 int k_party_mux(mb_ctx *ctx, const AesKey kk[4], int me, const mb_tensor *const s[2], const mb_tensor *const x[2],
-                const mb_tensor *const y[2], mb_tensor *z);
+                const mb_tensor *const y[2], mb_tensor *z, void *remote);
 int k_party_trunc_dealer(mb_ctx *ctx, const AesKey kk[4], unsigned amount, mb_tensor *const o[3]);
 int k_party_trunc_p0(mb_ctx *ctx, const AesKey kk[4], unsigned amount, const mb_tensor *xa, const mb_tensor *xb, const mb_tensor *masked1,
                      mb_tensor *cbits, mb_tensor *yp, mb_tensor *diff);
@@ -187,7 +189,7 @@ int k_party_dabit_dealer(mb_ctx *ctx, const AesKey &kbr, const mb_tensor *b, mb_
 int k_party_dabit_finish(mb_ctx *ctx, const AesKey &kbr, const AesKey &kyp, int first, unsigned bit_idx, const mb_tensor *br1,
                          const mb_tensor *cbits, mb_tensor *yp, mb_tensor *diff);
 int k_party_adder_level(mb_ctx *ctx, const AesKey keys[4], const LevelDesc &d, const mb_tensor *const g_in[2],
-                        const mb_tensor *const p_in[2], mb_tensor *g_out, mb_tensor *p_out, int64_t nv);
+                        const mb_tensor *const p_in[2], mb_tensor *g_out, mb_tensor *p_out, int64_t nv, void *remote);
 
 // Fused arithmetic->boolean conversion (bits_fused.cu)
 bool k_rep_adder_supported(const mb_tensor *x);

@@ -35,6 +35,7 @@ struct mb_party {
   std::string names[3];
   bool have_setup;
   bool stream_ordered;  // transport capability bit 0: device payloads are ordered on the context's stream
+  bool can_reserve;     // capability bit 1: a kernel may write its payload into the receiver's memory (modes 6 / 7)
   uint8_t keys[2][16];  // k_me (own) and k_{me+1} (copy received from the next party)
   AesKey sync_cipher;
   uint64_t sync_counter;
@@ -205,6 +206,27 @@ struct P {
     return got;
   }
 
+  // Reshare fused into the producing kernel: memory of the previous party for the next payload of `nbytes` (NULL:
+  // the transport cannot, or the payload is too large for its ring -- the kernel then writes locally only and
+  // ring_after() sends the ordinary way).
+  void *reserve_prev(size_t nbytes) {
+    if (!pt->can_reserve || nbytes == 0) return nullptr;
+    mb_reserve r{pt->names[pv].c_str(), nbytes, nullptr};
+    raw(6, -1, &r, sizeof(r), 1);
+    return r.ptr;
+  }
+  // Second half of ring(): the kernel enqueued since reserve_prev() has stored `mine` into `remote` as well.
+  T ring_after(const mb_tensor *mine, void *remote) {
+    if (!remote) return ring(mine);
+    mb_reserve r{pt->names[pv].c_str(), mine->nbytes, remote};
+    raw(7, -1, &r, sizeof(r), 1);
+    pt->transfers++;
+    pt->bytes_sent += mine->nbytes;
+    T got(c, recv_buf(mine->dtype, mine->rank, mine->shape));
+    raw(0, nx, got.p->dptr, got.p->nbytes, 1);
+    return got;
+  }
+
   // ---- keys ---------------------------------------------------------------------------------------------
   void sync_key(uint8_t out[16]) {
     uint8_t ctr[16] = {0};
@@ -322,8 +344,9 @@ struct P {
   Pair finish_bilinear(T v) {  // v is this party's own temporary: the zero share is added in place
     AesKey kk[2];
     zero_keys(kk);
-    ck(k_party_zero_add(c, kk, v.p, v.p));
-    T zn = ring(v.p);
+    void *remote = reserve_prev(v.p->nbytes);
+    ck(k_party_zero_add(c, kk, v.p, v.p, remote));
+    T zn = ring_after(v.p, remote);
     return Pair{std::move(v), std::move(zn)};
   }
   static bool same_shape(const mb_tensor *a, const mb_tensor *b) {
@@ -337,8 +360,9 @@ struct P {
       AesKey kk[2];
       zero_keys(kk);
       T z = like_new(x.a.p->dtype, x.a.p);
-      ck(k_party_mul(c, kk, x.a.p, x.b.p, y.a.p, y.b.p, z.p));
-      T zn = ring(z.p);
+      void *remote = reserve_prev(z.p->nbytes);
+      ck(k_party_mul(c, kk, x.a.p, x.b.p, y.a.p, y.b.p, z.p, remote));
+      T zn = ring_after(z.p, remote);
       return Pair{std::move(z), std::move(zn)};
     }
     T v = add(mul(x.a.p, add(y.a.p, y.b.p).p).p, mul(x.b.p, y.a.p).p);  // broadcasting operands
@@ -485,21 +509,25 @@ struct P {
     zero_keys(keys + 1);
     T g_me = planes();
     Pair p0{T(c, nullptr), T(c, nullptr)};
+    void *g_remote = nullptr;
     if (me == 0) {
       T R = planes(), bR = planes();
-      ck(k_party_adder_init(c, 0, keys, own.p, nullptr, g_me.p, R.p, bR.p));
+      g_remote = reserve_prev(g_me.p->nbytes);
+      ck(k_party_adder_init(c, 0, keys, own.p, nullptr, g_me.p, R.p, bR.p, g_remote));
       move_like(0, 1, bR.p, MB_BIT, own.p);
       p0 = Pair{std::move(R), std::move(bR)};
     } else if (me == 1) {
       T bR = move_like(0, 1, nullptr, MB_BIT, own.p);
-      ck(k_party_adder_init(c, 1, keys, own.p, bR.p, g_me.p, nullptr, nullptr));
+      g_remote = reserve_prev(g_me.p->nbytes);
+      ck(k_party_adder_init(c, 1, keys, own.p, bR.p, g_me.p, nullptr, nullptr, g_remote));
       p0 = Pair{std::move(bR), std::move(own)};
     } else {
       T R = planes();
-      ck(k_party_adder_init(c, 2, keys, own.p, nullptr, g_me.p, R.p, nullptr));
+      g_remote = reserve_prev(g_me.p->nbytes);
+      ck(k_party_adder_init(c, 2, keys, own.p, nullptr, g_me.p, R.p, nullptr, g_remote));
       p0 = Pair{std::move(own), std::move(R)};
     }
-    T g_nx = ring(g_me.p);
+    T g_nx = ring_after(g_me.p, g_remote);
     Pair g{std::move(g_me), std::move(g_nx)};
     // pruned levels
     std::vector<LevelDesc> levels;
@@ -544,8 +572,9 @@ struct P {
       T g_me(c, nullptr), p_me(c, nullptr), g_nx(c, nullptr), p_nx(c, nullptr);
       views(mine.p, g_me, p_me);
       const mb_tensor *gin[2] = {g.a.p, g.b.p}, *pin[2] = {p.a.p, p.b.p};
-      ck(k_party_adder_level(c, kk, levels[i], gin, pin, g_me.p, p_me.p, nv));
-      T theirs = ring(mine.p);
+      void *remote = reserve_prev(mine.p->nbytes);
+      ck(k_party_adder_level(c, kk, levels[i], gin, pin, g_me.p, p_me.p, nv, remote));
+      T theirs = ring_after(mine.p, remote);
       views(theirs.p, g_nx, p_nx);
       g = Pair{std::move(g_me), std::move(g_nx)};
       p = Pair{std::move(p_me), std::move(p_nx)};
@@ -616,8 +645,9 @@ struct P {
     zero_keys(kk + 2);
     T z = like_new(m1.a.p->dtype, m1.a.p);
     const mb_tensor *sv[2] = {lesser.a.p, lesser.b.p}, *xv[2] = {m1.a.p, m1.b.p}, *yv[2] = {m2.a.p, m2.b.p};
-    ck(k_party_mux(c, kk, me, sv, xv, yv, z.p));
-    T zn = this->ring(z.p);
+    void *remote = reserve_prev(z.p->nbytes);
+    ck(k_party_mux(c, kk, me, sv, xv, yv, z.p, remote));
+    T zn = ring_after(z.p, remote);
     return Pair{std::move(z), std::move(zn)};
   }
 };
@@ -660,6 +690,7 @@ extern "C" int mb_party_create(mb_ctx *ctx, int me, mb_transport_fn fn, void *us
   int64_t caps = 0;
   if (fn(user, 5, "", &caps, sizeof(caps), 0) != 0) caps = 0;  // optional mode: an error means "none"
   p->stream_ordered = (caps & 1) != 0;
+  p->can_reserve = (caps & 2) != 0 && !getenv("MB_PARTY_NO_REMOTE_STORES");
   mb_aes_expand(ctx->sid, &p->sync_cipher);  // public sync-key stream, the same on the three parties
   p->sync_counter = 0;
   p->sends_reported = p->bytes_sent = p->transfers = 0;

@@ -58,8 +58,8 @@ __device__ __forceinline__ vec_t bits_at(const uint32_t *__restrict__ bits, int6
 template <int K>
 __global__ void __launch_bounds__(AES_TPB_MID) party_mul_kernel(AesKey ka, AesKey kb, const vec_t *__restrict__ xa,
                                                                const vec_t *__restrict__ xb, const vec_t *__restrict__ ya,
-                                                               const vec_t *__restrict__ yb, vec_t *__restrict__ z, int64_t nvec,
-                                                               int64_t numel) {
+                                                               const vec_t *__restrict__ yb, vec_t *__restrict__ z,
+                                                               vec_t *__restrict__ remote, int64_t nvec, int64_t numel) {
   PRF_PROLOGUE();
   typedef VOps<K> O;
   VEC_LOOP(v, nvec) {
@@ -67,19 +67,21 @@ __global__ void __launch_bounds__(AES_TPB_MID) party_mul_kernel(AesKey ka, AesKe
     vec_t w = O::add(O::add(O::mul(a, O::add(c, d)), O::mul(b, c)), O::sub(prf_vec<K>(L, ka, (uint64_t)v), prf_vec<K>(L, kb, (uint64_t)v)));
     if (K == VK_BIT) w = bit_tail_mask(w, v, numel);
     z[v] = w;
+    if (remote) remote[v] = w;  // the reshare: the same value lands in the previous player's ring over NVLink
   }
 }
 
 // tail of DotOp::rep_rep_kernel (arith.rs:476-484): z_i = v_i + PRF(s_i) - PRF(s_{i+1}); z may alias v
 template <int K>
-__global__ void __launch_bounds__(AES_TPB_LIGHT) party_zero_add_kernel(AesKey ka, AesKey kb, const vec_t *v_in, vec_t *z, int64_t nvec,
-                                                                      int64_t numel) {
+__global__ void __launch_bounds__(AES_TPB_LIGHT) party_zero_add_kernel(AesKey ka, AesKey kb, const vec_t *v_in, vec_t *z,
+                                                                      vec_t *__restrict__ remote, int64_t nvec, int64_t numel) {
   PRF_PROLOGUE();
   typedef VOps<K> O;
   VEC_LOOP(v, nvec) {
     vec_t w = O::add(v_in[v], O::sub(prf_vec<K>(L, ka, (uint64_t)v), prf_vec<K>(L, kb, (uint64_t)v)));
     if (K == VK_BIT) w = bit_tail_mask(w, v, numel);
     z[v] = w;
+    if (remote) remote[v] = w;
   }
 }
 
@@ -91,7 +93,7 @@ __global__ void __launch_bounds__(AES_TPB_MID) party_mux_kernel(AesKey k1a, AesK
                                                                uint64_t one_b, const vec_t *__restrict__ sa, const vec_t *__restrict__ sb,
                                                                const vec_t *__restrict__ xa, const vec_t *__restrict__ xb,
                                                                const vec_t *__restrict__ ya, const vec_t *__restrict__ yb,
-                                                               vec_t *__restrict__ z, int64_t nvec) {
+                                                               vec_t *__restrict__ z, vec_t *__restrict__ remote, int64_t nvec) {
   PRF_PROLOGUE();
   typedef VOps<K> O;
   VEC_LOOP(v, nvec) {
@@ -102,7 +104,9 @@ __global__ void __launch_bounds__(AES_TPB_MID) party_mux_kernel(AesKey k1a, AesK
                            O::sub(prf_vec<K>(L, k1a, (uint64_t)v), prf_vec<K>(L, k1b, (uint64_t)v)));
     const vec_t q = O::add(O::add(O::mul(n0, O::add(x0, x1)), O::mul(n1, x0)),
                            O::sub(prf_vec<K>(L, k2a, (uint64_t)v), prf_vec<K>(L, k2b, (uint64_t)v)));
-    z[v] = O::add(p, q);
+    const vec_t w = O::add(p, q);
+    z[v] = w;
+    if (remote) remote[v] = w;
   }
 }
 
@@ -222,10 +226,10 @@ __global__ void __launch_bounds__(AES_TPB_LIGHT) dabit_finish_kernel(AesKey kbr,
 static int kind_of(mb_dtype d) { return d == MB_RING128 ? VK_RING128 : d == MB_BIT ? VK_BIT : VK_RING64; }
 
 int k_party_mul(mb_ctx *ctx, const AesKey kk[2], const mb_tensor *xa, const mb_tensor *xb, const mb_tensor *ya, const mb_tensor *yb,
-                mb_tensor *z) {
+                mb_tensor *z, void *remote) {
   if (z->numel == 0) return MB_OK;
   const int64_t nvec = vec_count(z);
-#define ARGS kk[0], kk[1], CVP(xa), CVP(xb), CVP(ya), CVP(yb), VP(z), nvec, z->numel
+#define ARGS kk[0], kk[1], CVP(xa), CVP(xb), CVP(ya), CVP(yb), VP(z), (vec_t *)remote, nvec, z->numel
   switch (kind_of(z->dtype)) {
     case VK_RING128: AES_LAUNCH(ctx, party_mul_kernel<VK_RING128>, AES_TPB_MID, nvec, ARGS); break;
     case VK_RING64: AES_LAUNCH(ctx, party_mul_kernel<VK_RING64>, AES_TPB_MID, nvec, ARGS); break;
@@ -236,10 +240,10 @@ int k_party_mul(mb_ctx *ctx, const AesKey kk[2], const mb_tensor *xa, const mb_t
   return MB_OK;
 }
 
-int k_party_zero_add(mb_ctx *ctx, const AesKey kk[2], const mb_tensor *v, mb_tensor *z) {
+int k_party_zero_add(mb_ctx *ctx, const AesKey kk[2], const mb_tensor *v, mb_tensor *z, void *remote) {
   if (z->numel == 0) return MB_OK;
   const int64_t nvec = vec_count(z);
-#define ARGS kk[0], kk[1], CVP(v), VP(z), nvec, z->numel
+#define ARGS kk[0], kk[1], CVP(v), VP(z), (vec_t *)remote, nvec, z->numel
   switch (kind_of(z->dtype)) {
     case VK_RING128: AES_LAUNCH(ctx, party_zero_add_kernel<VK_RING128>, AES_TPB_LIGHT, nvec, ARGS); break;
     case VK_RING64: AES_LAUNCH(ctx, party_zero_add_kernel<VK_RING64>, AES_TPB_LIGHT, nvec, ARGS); break;
@@ -253,13 +257,13 @@ int k_party_zero_add(mb_ctx *ctx, const AesKey kk[2], const mb_tensor *v, mb_ten
 // kk: zero-share keys of s * y (a, b) and of (1 - s) * x (a, b); me: this player's index (share 0 is the first share
 // of player 0 and the second share of player 2)
 int k_party_mux(mb_ctx *ctx, const AesKey kk[4], int me, const mb_tensor *const s[2], const mb_tensor *const x[2],
-                const mb_tensor *const y[2], mb_tensor *z) {
+                const mb_tensor *const y[2], mb_tensor *z, void *remote) {
   if (z->numel == 0) return MB_OK;
   const int64_t nvec = vec_count(z);
   const uint64_t one_a = me == 0, one_b = me == 2;
 #define CALL(KIND)                                                                                                              \
   AES_LAUNCH(ctx, party_mux_kernel<KIND>, AES_TPB_MID, nvec, kk[0], kk[1], kk[2], kk[3], one_a, one_b, CVP(s[0]), CVP(s[1]), \
-             CVP(x[0]), CVP(x[1]), CVP(y[0]), CVP(y[1]), VP(z), nvec)
+             CVP(x[0]), CVP(x[1]), CVP(y[0]), CVP(y[1]), VP(z), (vec_t *)remote, nvec)
   DISPATCH_RING(z->dtype, CALL);
 #undef CALL
   MB_LAUNCH_CHECK(ctx);

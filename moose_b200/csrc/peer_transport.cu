@@ -133,36 +133,58 @@ int peer_rank_of(mb_peer_transport *t, const char *name, int *out) {
   return 0;
 }
 
-// One chunk (<= ring / 2) of a device payload into q's ring, on the context's stream.
-int send_chunk(mb_peer_transport *t, int q, const uint8_t *src, size_t n) {
-  cudaStream_t s = t->ctx->stream;
+// A message (<= ring / 2, padded to 256 bytes) occupies contiguous ring space: when it does not fit before the end of
+// the ring both sides skip to the start (the skipped bytes count as sent / consumed).  Returns the position and
+// advances the cumulative counter past the message.
+inline size_t place(uint64_t &counter, size_t C, size_t padded, uint64_t *before) {
+  size_t pos = counter % C;
+  if (pos + padded > C) {
+    counter += C - pos;
+    pos = 0;
+  }
+  *before = counter;
+  counter += padded;
+  return pos;
+}
+
+// Ring space in q for a message of n bytes, on the context's stream: waits until the receiver has consumed enough,
+// returns where the message goes.  Whoever fills it (a copy, or the kernel that computes the payload) is followed
+// by publish().
+int reserve(mb_peer_transport *t, int q, size_t n, uint8_t **where) {
   const size_t C = t->ring_bytes, padded = round_up(n);
-  uint64_t &sent = t->sent_data[q];
-  uint64_t *mine = words(t->inbox, slot_of(t->rank, q)), *theirs = words(t->peer_in[q], slot_of(q, t->rank));
-  if (sent + padded > C && enqueue_wait(t, s, mine + W_DATA_ACK, sent + padded - C)) return 1;
-  uint8_t *ring = data_ring(t->peer_in[q], t->nranks, C, slot_of(q, t->rank));
-  const size_t pos = sent % C, first = n < C - pos ? n : C - pos;
-  PCU(t, cudaMemcpyAsync(ring + pos, src, first, cudaMemcpyDefault, s));
-  if (first < n) PCU(t, cudaMemcpyAsync(ring, src + first, n - first, cudaMemcpyDefault, s));
-  sent += padded;
-  k_peer_signal<<<1, 1, 0, s>>>(theirs + W_DATA_FLAG, sent);
+  uint64_t before = 0;
+  const size_t pos = place(t->sent_data[q], C, padded, &before);
+  uint64_t *mine = words(t->inbox, slot_of(t->rank, q));
+  if (t->sent_data[q] > C && enqueue_wait(t, t->ctx->stream, mine + W_DATA_ACK, t->sent_data[q] - C)) return 1;
+  *where = data_ring(t->peer_in[q], t->nranks, C, slot_of(q, t->rank)) + pos;
+  return 0;
+}
+int publish(mb_peer_transport *t, int q) {
+  uint64_t *theirs = words(t->peer_in[q], slot_of(q, t->rank));
+  k_peer_signal<<<1, 1, 0, t->ctx->stream>>>(theirs + W_DATA_FLAG, t->sent_data[q]);
   PCU(t, cudaGetLastError());
   return 0;
+}
+
+// One chunk (<= ring / 2) of a device payload into q's ring, on the context's stream.
+int send_chunk(mb_peer_transport *t, int q, const uint8_t *src, size_t n) {
+  uint8_t *where = nullptr;
+  if (reserve(t, q, n, &where)) return 1;
+  PCU(t, cudaMemcpyAsync(where, src, n, cudaMemcpyDefault, t->ctx->stream));
+  return publish(t, q);
 }
 
 // One chunk out of this party's ring for peer p, on the context's stream.
 int recv_chunk(mb_peer_transport *t, int p, uint8_t *dst, size_t n) {
   cudaStream_t s = t->ctx->stream;
   const size_t C = t->ring_bytes, padded = round_up(n);
-  uint64_t &got = t->recv_data[p];
+  uint64_t before = 0;
+  const size_t pos = place(t->recv_data[p], C, padded, &before);
   uint64_t *mine = words(t->inbox, slot_of(t->rank, p)), *theirs = words(t->peer_in[p], slot_of(p, t->rank));
-  if (enqueue_wait(t, s, mine + W_DATA_FLAG, got + padded)) return 1;
+  if (enqueue_wait(t, s, mine + W_DATA_FLAG, t->recv_data[p])) return 1;
   const uint8_t *ring = data_ring(t->inbox, t->nranks, C, slot_of(t->rank, p));
-  const size_t pos = got % C, first = n < C - pos ? n : C - pos;
-  PCU(t, cudaMemcpyAsync(dst, ring + pos, first, cudaMemcpyDeviceToDevice, s));
-  if (first < n) PCU(t, cudaMemcpyAsync(dst + first, ring, n - first, cudaMemcpyDeviceToDevice, s));
-  got += padded;
-  k_peer_signal<<<1, 1, 0, s>>>(theirs + W_DATA_ACK, got);
+  PCU(t, cudaMemcpyAsync(dst, ring + pos, n, cudaMemcpyDeviceToDevice, s));
+  k_peer_signal<<<1, 1, 0, s>>>(theirs + W_DATA_ACK, t->recv_data[p]);
   PCU(t, cudaGetLastError());
   return 0;
 }
@@ -234,8 +256,23 @@ int peer_transport_cb(void *user, int mode, const char *peer, void *buf, size_t 
   if (!t) return 1;
   if (!t->connected) return pfail(t, "not connected");
   PCU(t, cudaSetDevice(t->ctx->device));
-  if (mode == 5) {  // capabilities: device payloads are ordered on the context's stream
-    *(int64_t *)buf = 1;
+  if (mode == 5) {  // capabilities: device payloads are ordered on the context's stream; reserve / publish
+    *(int64_t *)buf = 3;
+    return 0;
+  }
+  if (mode == 6 || mode == 7) {  // the payload is written into the receiver's ring by the caller's own kernel
+    mb_reserve *r = (mb_reserve *)buf;
+    int to = 0;
+    if (peer_rank_of(t, r->peer, &to)) return 1;
+    if (mode == 7) {
+      t->posted++;
+      return publish(t, to);
+    }
+    r->ptr = nullptr;
+    if (r->nbytes == 0 || r->nbytes > t->ring_bytes / 2) return 0;  // the caller falls back to an ordinary send
+    uint8_t *where = nullptr;
+    if (reserve(t, to, r->nbytes, &where)) return 1;
+    r->ptr = where;
     return 0;
   }
   if (mode == 2 || mode == 3) {
