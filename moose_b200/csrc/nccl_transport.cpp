@@ -7,6 +7,7 @@
 
 #include <deque>
 #include <map>
+#include <mutex>
 
 #include "common.h"
 
@@ -30,10 +31,9 @@ struct NcclApi {
 
 NcclApi *nccl_api(std::string *err) {
   static NcclApi api;
-  static bool tried = false;
+  static std::once_flag once;
   static std::string why;
-  if (!tried) {
-    tried = true;
+  std::call_once(once, [] {
     for (const char *name : {"libnccl.so.2", "libnccl.so"}) {
       api.lib = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
       if (api.lib) break;
@@ -54,7 +54,7 @@ NcclApi *nccl_api(std::string *err) {
       LOAD(GetErrorString, "ncclGetErrorString")
 #undef LOAD
     }
-  }
+  });
   if (!why.empty()) {
     if (err) *err = why;
     return nullptr;
@@ -203,6 +203,9 @@ extern "C" int mb_nccl_transport_create(mb_ctx *ctx, const uint8_t unique_id[128
   t->nranks = nranks;
   t->next_slot = 0;
   t->completed = 0;
+  t->comm = nullptr;
+  t->stream = nullptr;
+  t->host_slots = t->dev_slots = nullptr;
   for (int i = 0; i < nranks; i++) t->rank_of[role_names[i] ? role_names[i] : ""] = i;
   NcclUniqueId id;
   memcpy(id.internal, unique_id, 128);
@@ -211,9 +214,13 @@ extern "C" int mb_nccl_transport_create(mb_ctx *ctx, const uint8_t unique_id[128
     delete t;
     return mb_fail(ctx, MB_ERR_KERNEL, std::string("ncclCommInitRank: ") + api->GetErrorString(r));
   }
-  MB_CUDA(ctx, cudaStreamCreateWithFlags(&t->stream, cudaStreamNonBlocking));
-  MB_CUDA(ctx, cudaMallocHost((void **)&t->host_slots, SLOTS * SLOT_BYTES));
-  MB_CUDA(ctx, cudaMalloc((void **)&t->dev_slots, SLOTS * SLOT_BYTES));
+  cudaError_t e = cudaStreamCreateWithFlags(&t->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaMallocHost((void **)&t->host_slots, SLOTS * SLOT_BYTES);
+  if (e == cudaSuccess) e = cudaMalloc((void **)&t->dev_slots, SLOTS * SLOT_BYTES);
+  if (e != cudaSuccess) {
+    mb_nccl_transport_free(t);
+    return mb_fail(ctx, MB_ERR_CUDA, std::string("mb_nccl_transport_create: ") + cudaGetErrorString(e));
+  }
   *out = t;
   return MB_OK;
 }
@@ -223,13 +230,13 @@ extern "C" mb_transport_fn mb_nccl_transport_fn(void) { return nccl_transport_cb
 extern "C" int mb_nccl_transport_free(mb_nccl_transport *t) {
   if (!t) return MB_OK;
   cudaSetDevice(t->ctx->device);
-  cudaStreamSynchronize(t->stream);
+  if (t->stream) cudaStreamSynchronize(t->stream);
   for (auto ev : t->posted) cudaEventDestroy(ev);
   for (auto ev : t->pool) cudaEventDestroy(ev);
-  t->api->CommDestroy(t->comm);
-  cudaFreeHost(t->host_slots);
-  cudaFree(t->dev_slots);
-  cudaStreamDestroy(t->stream);
+  if (t->comm) t->api->CommDestroy(t->comm);
+  if (t->host_slots) cudaFreeHost(t->host_slots);
+  if (t->dev_slots) cudaFree(t->dev_slots);
+  if (t->stream) cudaStreamDestroy(t->stream);
   delete t;
   return MB_OK;
 }

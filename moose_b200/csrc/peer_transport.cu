@@ -302,6 +302,8 @@ int peer_transport_cb(void *user, int mode, const char *peer, void *buf, size_t 
 
 }  // namespace
 
+static int peer_init(mb_peer_transport *t);
+
 extern "C" int mb_peer_transport_create(mb_ctx *ctx, int rank, int nranks, const char *const *role_names, size_t ring_bytes,
                                         mb_peer_transport **out) {
   if (!ctx || !role_names || !out || nranks < 2 || rank < 0 || rank >= nranks)
@@ -323,6 +325,23 @@ extern "C" int mb_peer_transport_create(mb_ctx *ctx, int rank, int nranks, const
   t->recv_data.assign(nranks, 0);
   t->peer_host.assign(nranks, nullptr);
   t->shm_mapped.assign(nranks, false);
+  t->inbox = nullptr;
+  t->status = nullptr;
+  t->host_in = nullptr;
+  const int rc = peer_init(t);
+  if (rc != MB_OK) {
+    mb_peer_transport_free(t);
+    return rc;
+  }
+  *out = t;
+  return MB_OK;
+}
+
+// allocations of mb_peer_transport_create; the caller frees the half-built transport when this fails
+static int peer_init(mb_peer_transport *t) {
+  mb_ctx *ctx = t->ctx;
+  const int nranks = t->nranks, rank = t->rank;
+  const size_t ring_bytes = t->ring_bytes;
   // cudaMalloc, not the context's pool: IPC handles exist for plain allocations only
   MB_CUDA(ctx, cudaMalloc((void **)&t->inbox, inbox_bytes(nranks, ring_bytes)));
   MB_CUDA(ctx, cudaMemset(t->inbox, 0, (size_t)(nranks - 1) * WORDS_BYTES));
@@ -343,7 +362,6 @@ extern "C" int mb_peer_transport_create(mb_ctx *ctx, int rank, int nranks, const
   if (seg == MAP_FAILED) return mb_fail(ctx, MB_ERR_KERNEL, "mb_peer_transport_create: mmap failed");
   t->host_in = (HostRing *)seg;
   MB_CUDA(ctx, cudaDeviceSynchronize());
-  *out = t;
   return MB_OK;
 }
 
@@ -411,9 +429,9 @@ extern "C" int mb_peer_transport_free(mb_peer_transport *t) {
     if (t->shm_mapped[q]) munmap(t->peer_host[q], host_segment_bytes(t->nranks));
   }
   if (t->host_in) munmap(t->host_in, host_segment_bytes(t->nranks));
-  shm_unlink(t->shm_name.c_str());
-  cudaFree(t->status);
-  cudaFree(t->inbox);
+  if (!t->shm_name.empty()) shm_unlink(t->shm_name.c_str());
+  if (t->status) cudaFree(t->status);
+  if (t->inbox) cudaFree(t->inbox);
   delete t;
   return MB_OK;
 }
