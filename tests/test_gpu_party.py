@@ -157,6 +157,33 @@ def test_msb_ring_inject_and_maximum(bits):
     assert np.array_equal(res[3], (xv < yv).astype(np.uint8))
 
 
+@pytest.mark.parametrize("bits", [64, 128])
+def test_ragged_sizes_mul_trunc_inject(bits):
+    """Element counts that fill neither a 16-byte vector (odd, Ring64) nor a 32-bit word of a bit tensor: the fused
+    party steps mask the padding (opened top bit of TruncPr packed by ballot, dabit bits read per element)."""
+    rng = np.random.default_rng(bits + 1)
+    shape = (3, 5)
+    xv, yv = rng.integers(-2 ** 30, 2 ** 30, shape), rng.integers(-2 ** 20, 2 ** 20, shape)
+    bv = rng.integers(0, 2, shape).astype(np.uint8)
+
+    def prog(p):
+        s = p.sess
+        x = p.share(0, ints(xv, bits, s) if p.me == 0 else None, DT[bits], shape)
+        y = p.share(2, ints(yv, bits, s) if p.me == 2 else None, DT[bits], shape)
+        b = p.share(1, s.from_bits(bv) if p.me == 1 else None, BIT, shape)
+        m = p.mul(x, y)
+        t = p.trunc_pr(7, m)
+        inj = p.ring_inject(DT[bits], 2, b)
+        r = [p.reveal(1, m), p.reveal(1, t), p.reveal(1, inj)]
+        return [v.to_host() if v is not None else None for v in r]
+
+    res = run_parties(prog)[1]
+    prod = xv.astype(object) * yv.astype(object)
+    assert np.array_equal(signed(res[0], bits), prod)
+    assert np.abs(signed(res[1], bits) - np.array([[int(v) >> 7 for v in row] for row in prod], dtype=object)).max() <= 1
+    assert np.array_equal(signed(res[2], bits), bv.astype(object) * 4)
+
+
 def test_party_mlp_matches_float():
     rng = np.random.default_rng(9)
     dims = (24, 16, 16, 4)
