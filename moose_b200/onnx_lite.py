@@ -1,0 +1,90 @@
+"""Minimal reader for the parts of an ONNX file the tree-ensemble predictors need (no onnx package in this image):
+walks the protobuf wire format of ModelProto -> graph -> node[op_type] -> attribute and graph.input[0] shape.
+Field numbers from the public onnx.proto: ModelProto.graph = 7; GraphProto.node = 1, input = 11; NodeProto.op_type = 4,
+attribute = 5; AttributeProto.name = 1, f = 2, i = 3, s = 4, floats = 7, ints = 8, strings = 9, type = 20;
+ValueInfoProto.type = 2; TypeProto.tensor_type = 1; Tensor.shape = 2; TensorShapeProto.dim = 1; Dimension.dim_value = 1."""
+import struct
+
+
+def _varint(b, i):
+    v, s = 0, 0
+    while True:
+        c = b[i]
+        i += 1
+        v |= (c & 0x7F) << s
+        s += 7
+        if not c & 0x80:
+            return v, i
+
+
+def fields(b):
+    """[(field number, wire type, value)] of one message; length-delimited values stay bytes."""
+    out, i = [], 0
+    while i < len(b):
+        key, i = _varint(b, i)
+        fn, wt = key >> 3, key & 7
+        if wt == 0:
+            v, i = _varint(b, i)
+        elif wt == 1:
+            v, i = b[i:i + 8], i + 8
+        elif wt == 2:
+            n, i = _varint(b, i)
+            v, i = b[i:i + n], i + n
+        elif wt == 5:
+            v, i = b[i:i + 4], i + 4
+        else:
+            raise ValueError(f"wire type {wt}")
+        out.append((fn, wt, v))
+    return out
+
+
+def _signed(v):
+    return v - (1 << 64) if v >= 1 << 63 else v
+
+
+def _attribute(b):
+    name, a = None, {"floats": [], "ints": [], "strings": []}
+    for fn, wt, v in fields(b):
+        if fn == 1:
+            name = v.decode()
+        elif fn == 2:
+            a["f"] = struct.unpack("<f", v)[0]
+        elif fn == 3:
+            a["i"] = _signed(v)
+        elif fn == 4:
+            a["s"] = v.decode()
+        elif fn == 7:
+            a["floats"] += list(struct.unpack(f"<{len(v) // 4}f", v)) if wt == 2 else [struct.unpack("<f", v)[0]]
+        elif fn == 8:
+            if wt == 2:
+                i = 0
+                while i < len(v):
+                    x, i = _varint(v, i)
+                    a["ints"].append(_signed(x))
+            else:
+                a["ints"].append(_signed(v))
+        elif fn == 9:
+            a["strings"].append(v.decode())
+    return name, a
+
+
+def find_node(model_bytes, op_type):
+    """Attributes {name: {...}} of the first node with this op_type, and the feature count of graph.input[0]."""
+    graph = next(v for fn, _, v in fields(model_bytes) if fn == 7)
+    n_features, node_attrs = None, None
+    for fn, _, v in fields(graph):
+        if fn == 1 and node_attrs is None:
+            fs = fields(v)
+            if any(f == 4 and val.decode() == op_type for f, _, val in fs):
+                node_attrs = dict(_attribute(val) for f, _, val in fs if f == 5)
+        elif fn == 11 and n_features is None:
+            ty = next(val for f, _, val in fields(v) if f == 2)
+            tensor = next(val for f, _, val in fields(ty) if f == 1)
+            shape = next(val for f, _, val in fields(tensor) if f == 2)
+            dims = []
+            for f, _, d in fields(shape):
+                if f == 1:
+                    dv = [val for g, _, val in fields(d) if g == 1]
+                    dims.append(dv[0] if dv else 0)
+            n_features = dims[1]
+    return node_attrs, n_features

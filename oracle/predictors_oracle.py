@@ -4,7 +4,8 @@ import numpy as np
 from . import moose_oracle as mo
 
 
-def mlp_forward_shared(sess, x_fixed, w_fixed, b_fixed, frac, relu_via="maximum", integral=14, post_transform="none"):
+def mlp_forward_shared(sess, x_fixed, w_fixed, b_fixed, frac, relu_via="maximum", integral=14, post_transform="none",
+                       bias_via="public"):
     bits = x_fixed.bits
     x = mo.rep_share(sess, x_fixed, 0)
     n = len(w_fixed)
@@ -12,7 +13,8 @@ def mlp_forward_shared(sess, x_fixed, w_fixed, b_fixed, frac, relu_via="maximum"
         w = mo.rep_share(sess, w_fixed[i], 0)
         y = mo.rep_trunc_pr(sess, frac, mo.rep_dot(sess, x, w))
         b = b_fixed[i]
-        z = mo.rep_add_mir(y, mo.MirTensor([b, b, b]))
+        # "share": AddOp::fixed_rep_kernel shares the mirrored bias from player 0 (fixedpoint/ops.rs:30-52)
+        z = mo.rep_add_mir(y, mo.MirTensor([b, b, b])) if bias_via == "public" else mo.rep_add(y, mo.rep_share(sess, b, 0))
         if i < n - 1:
             if relu_via == "maximum":
                 zeros = mo.rep_share(sess, mo.fill(bits, 0, z.shape), 1)
@@ -31,11 +33,11 @@ def mlp_forward_shared(sess, x_fixed, w_fixed, b_fixed, frac, relu_via="maximum"
     return x
 
 
-def mlp(sess, x, weights, biases, bits=64, frac=23, relu_via="maximum", integral=14, post_transform="none"):
+def mlp(sess, x, weights, biases, bits=64, frac=23, relu_via="maximum", integral=14, post_transform="none", bias_via="public"):
     xf = mo.fixed_encode(bits, x, frac)
     wf = [mo.fixed_encode(bits, np.asarray(w, dtype=np.float64), frac) for w in weights]
     bf = [mo.fixed_encode(bits, np.asarray(b, dtype=np.float64).reshape(1, -1), frac) for b in biases]
-    out = mlp_forward_shared(sess, xf, wf, bf, frac, relu_via, integral, post_transform)
+    out = mlp_forward_shared(sess, xf, wf, bf, frac, relu_via, integral, post_transform, bias_via)
     return out, mo.fixed_decode(mo.rep_reveal(out), frac)
 
 
@@ -52,4 +54,50 @@ def linear(sess, x, coeffs, intercepts, bits=128, frac=40, integral=24, post_tra
         y = mo.rep_div(sess, integral, frac, y, mo.rep_expand_dims([1], mo.rep_sum(1, y)))
     elif post_transform == "softmax":
         y = mo.rep_softmax(sess, 1, w.shape[1], integral, frac, y)
+    return y, mo.fixed_decode(mo.rep_reveal(y), frac)
+
+
+def tree_ensemble(sess, x, trees, n_features, base_score=0.0, learning_rate=1.0, n_classes=None, transform_output=False,
+                  tree_class_map=None, bits=128, frac=40, integral=24):
+    """pymoose/pymoose/predictors/tree_ensemble.py:33-62 (traversal), 83-114 (forest), 273-314 and 391-395 (post
+    transforms) on the oracle, in graph-construction order; constants are rank-0 (predictor.py:19-23).  Host operands
+    of replicated kernels are shared where the kernel shares them: x by alice in every index_axis
+    (fixedpoint/ops.rs:1085-1104), mirrored thresholds / the mirrored one by player 0 (mirrored/ops.rs:159-180), leaf
+    and base-score constants by carole (fixedpoint/ops.rs:2014-2051, 30-52)."""
+    const = lambda v: mo.fixed_encode(bits, np.array(float(v)), frac)
+    xf = mo.fixed_encode(bits, np.asarray(x, dtype=np.float64), frac)
+
+    def traverse(tree, node, feats):
+        if tree.left[node] == 0 and tree.right[node] == 0:
+            return const(learning_rate * tree.weights[node])
+        thr = mo.rep_share(sess, const(tree.split_conditions[node]), 0)
+        selector = mo.rep_less(sess, feats[tree.split_indices[node]], thr)
+        left = traverse(tree, tree.left[node], feats)
+        right = traverse(tree, tree.right[node], feats)
+        xs = left if isinstance(left, mo.RepTensor) else mo.rep_share(sess, left, 2)
+        ys = right if isinstance(right, mo.RepTensor) else mo.rep_share(sess, right, 2)
+        return mo.rep_mux(sess, mo.rep_ring_inject(sess, bits, 0, selector), xs, ys)
+
+    scores = []
+    for tree in trees:
+        feats = [mo.rep_index_axis(1, i, mo.rep_share(sess, xf, 0)) for i in range(n_features)]
+        scores.append(traverse(tree, 0, feats))
+    base = lambda: mo.rep_share(sess, const(base_score), 2)
+    if n_classes is None:
+        total = mo.rep_add_n(scores)
+        y = mo.rep_add(base(), total)
+    elif n_classes == 2:
+        logit = mo.rep_add(mo.rep_add_n(scores), base())
+        pos = mo.rep_sigmoid(sess, integral, frac, logit) if transform_output else logit
+        pos = mo.rep_expand_dims([1], pos)
+        one = mo.rep_share(sess, const(1.0), 0)
+        y = mo.rep_concat(1, [mo.rep_sub(one, pos), pos])
+    else:
+        per_class = [[] for _ in range(n_classes)]
+        for tree_ix, class_ix in tree_class_map.items():
+            per_class[class_ix].append(scores[tree_ix])
+        logits = [mo.rep_add(mo.rep_add_n(v), base()) for v in per_class]
+        y = mo.rep_concat(1, [mo.rep_expand_dims([1], v) for v in logits])
+        if transform_output:
+            y = mo.rep_softmax(sess, 1, n_classes, integral, frac, y)
     return y, mo.fixed_decode(mo.rep_reveal(y), frac)
