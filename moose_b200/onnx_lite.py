@@ -88,3 +88,72 @@ def find_node(model_bytes, op_type):
                     dims.append(dv[0] if dv else 0)
             n_features = dims[1]
     return node_attrs, n_features
+
+
+def _packed_ints(wt, v, acc):
+    if wt == 2:
+        i = 0
+        while i < len(v):
+            x, i = _varint(v, i)
+            acc.append(_signed(x))
+    else:
+        acc.append(_signed(v))
+
+
+def initializers(model_bytes):
+    """[(name, dims, data_type, float values)] of graph.initializer (GraphProto.initializer = 5; TensorProto.dims = 1,
+    data_type = 2, float_data = 4, name = 8, raw_data = 9; data_type 1 = FLOAT)."""
+    graph = next(v for fn, _, v in fields(model_bytes) if fn == 7)
+    out = []
+    for fn, _, v in fields(graph):
+        if fn != 5:
+            continue
+        name, dims, dtype, floats, raw = "", [], 0, [], b""
+        for f, wt, val in fields(v):
+            if f == 1:
+                _packed_ints(wt, val, dims)
+            elif f == 2:
+                dtype = val
+            elif f == 4:
+                floats += list(struct.unpack(f"<{len(val) // 4}f", val)) if wt == 2 else [struct.unpack("<f", val)[0]]
+            elif f == 8:
+                name = val.decode()
+            elif f == 9:
+                raw = val
+        if not floats and raw and dtype == 1:
+            floats = list(struct.unpack(f"<{len(raw) // 4}f", raw))
+        out.append((name, dims, dtype, floats))
+    return out
+
+
+def nodes(model_bytes):
+    """[(name, op_type, outputs)] of graph.node (NodeProto.output = 2, name = 3, op_type = 4)."""
+    graph = next(v for fn, _, v in fields(model_bytes) if fn == 7)
+    out = []
+    for fn, _, v in fields(graph):
+        if fn == 1:
+            name, op, outs = "", "", []
+            for f, _, val in fields(v):
+                if f == 2:
+                    outs.append(val.decode())
+                elif f == 3:
+                    name = val.decode()
+                elif f == 4:
+                    op = val.decode()
+            out.append((name, op, outs))
+    return out
+
+
+def input_features(model_bytes):
+    """dim_value of axis 1 of graph.input[0]."""
+    graph = next(v for fn, _, v in fields(model_bytes) if fn == 7)
+    first = next(v for fn, _, v in fields(graph) if fn == 11)
+    ty = next(val for f, _, val in fields(first) if f == 2)
+    tensor = next(val for f, _, val in fields(ty) if f == 1)
+    shape = next(val for f, _, val in fields(tensor) if f == 2)
+    dims = []
+    for f, _, d in fields(shape):
+        if f == 1:
+            dv = [val for g, _, val in fields(d) if g == 1]
+            dims.append(dv[0] if dv else 0)
+    return dims[1]

@@ -27,7 +27,7 @@ from . import FLOAT64, RING64, RING128, RepTensor, Session, Tensor
 class MLPPredictor:
     def __init__(self, sess: Session, weights: Sequence[np.ndarray], biases: Sequence[np.ndarray],
                  ring: int = RING64, frac: int = 23, relu_via: str = "maximum", integral: int = 14,
-                 post_transform: str = "none", bias_via: str = "public"):
+                 post_transform: str = "none", bias_via: str = "public", activation: str = "relu"):
         """post_transform: "none" (MLPRegressor) or "classifier" (MLPClassifier: softmax over the classes, or
         [1 - sigmoid, sigmoid] for one output; needs 2 * (integral + frac) <= ring bits, division.rs:33-38).
         bias_via: "share" is what the logical graph does -- AddOp's replicated kernel on abstract fixed tensors shares a
@@ -36,6 +36,9 @@ class MLPPredictor:
         expansion and two additions fewer.  "public" is the measured default of this round."""
         self.sess, self.ring, self.frac, self.relu_via = sess, ring, frac, relu_via
         self.bias_via = bias_via
+        if activation not in ("relu", "sigmoid", "identity"):   # Activation enum, multilayer_perceptron_predictor.py:69-78
+            raise ValueError("Invalid or unsupported activation function")
+        self.activation = activation
         self.integral, self.post = integral, post_transform
         enc = lambda a: sess.fixedpoint_encode(ring, frac, sess.from_host(FLOAT64, np.asarray(a, dtype=np.float64)))
         self.w: List[Tensor] = [enc(w) for w in weights]                      # [in, out] each
@@ -52,7 +55,9 @@ class MLPPredictor:
             w = s.share(self.w[i], 0)
             y = s.trunc_pr(self.frac, s.rep_dot(x, w))
             z = s.rep_add_public(y, self.b[i]) if self.bias_via == "public" else s.rep_add(y, s.share(self.b[i], 0))
-            if i < n - 1:
+            if i < n - 1 and self.activation == "sigmoid":
+                z = s.sigmoid(self.integral, self.frac, z)
+            elif i < n - 1 and self.activation == "relu":
                 if self.relu_via == "maximum":
                     zeros = s.share(s.fill(self.ring, 0, z.shape), 1)
                     z = s.maximum([zeros, z])
@@ -63,8 +68,12 @@ class MLPPredictor:
             n_classes = self.b[-1].shape[-1]
             if n_classes == 1:
                 pos = s.sigmoid(self.integral, self.frac, x)
-                one = s.fill(self.ring, 1 << self.frac, pos.shape)
-                x = s.rep_concat(1, [s.rep_public_sub(one, pos), pos])
+                if self.bias_via == "public":
+                    one = s.fill(self.ring, 1 << self.frac, pos.shape)
+                    x = s.rep_concat(1, [s.rep_public_sub(one, pos), pos])
+                else:   # the mirrored rank-0 one is shared by player 0 inside SubOp (fixedpoint/ops.rs, SubOp::fixed_rep_kernel)
+                    one = s.share(s.fixedpoint_encode(self.ring, self.frac, s.from_host(FLOAT64, np.array(1.0))), 0)
+                    x = s.rep_concat(1, [s.rep_sub(one, pos), pos])
             else:
                 x = s.softmax(1, n_classes, self.integral, self.frac, x)
         return x

@@ -5,7 +5,7 @@ from . import moose_oracle as mo
 
 
 def mlp_forward_shared(sess, x_fixed, w_fixed, b_fixed, frac, relu_via="maximum", integral=14, post_transform="none",
-                       bias_via="public"):
+                       bias_via="public", activation="relu"):
     bits = x_fixed.bits
     x = mo.rep_share(sess, x_fixed, 0)
     n = len(w_fixed)
@@ -15,7 +15,9 @@ def mlp_forward_shared(sess, x_fixed, w_fixed, b_fixed, frac, relu_via="maximum"
         b = b_fixed[i]
         # "share": AddOp::fixed_rep_kernel shares the mirrored bias from player 0 (fixedpoint/ops.rs:30-52)
         z = mo.rep_add_mir(y, mo.MirTensor([b, b, b])) if bias_via == "public" else mo.rep_add(y, mo.rep_share(sess, b, 0))
-        if i < n - 1:
+        if i < n - 1 and activation == "sigmoid":
+            z = mo.rep_sigmoid(sess, integral, frac, z)
+        elif i < n - 1 and activation == "relu":
             if relu_via == "maximum":
                 zeros = mo.rep_share(sess, mo.fill(bits, 0, z.shape), 1)
                 z = mo.rep_maximum(sess, [zeros, z])
@@ -26,18 +28,23 @@ def mlp_forward_shared(sess, x_fixed, w_fixed, b_fixed, frac, relu_via="maximum"
         n_classes = b_fixed[-1].shape[-1]
         if n_classes == 1:
             pos = mo.rep_sigmoid(sess, integral, frac, x)
-            one = mo.fill(bits, 1 << frac, pos.shape)
-            x = mo.rep_concat(1, [mo.rep_mir_sub(mo.MirTensor([one, one, one]), pos), pos])
+            if bias_via == "public":
+                one = mo.fill(bits, 1 << frac, pos.shape)
+                x = mo.rep_concat(1, [mo.rep_mir_sub(mo.MirTensor([one, one, one]), pos), pos])
+            else:
+                one = mo.rep_share(sess, mo.fixed_encode(bits, np.array(1.0), frac), 0)
+                x = mo.rep_concat(1, [mo.rep_sub(one, pos), pos])
         else:
             x = mo.rep_softmax(sess, 1, n_classes, integral, frac, x)
     return x
 
 
-def mlp(sess, x, weights, biases, bits=64, frac=23, relu_via="maximum", integral=14, post_transform="none", bias_via="public"):
+def mlp(sess, x, weights, biases, bits=64, frac=23, relu_via="maximum", integral=14, post_transform="none", bias_via="public",
+        activation="relu"):
     xf = mo.fixed_encode(bits, x, frac)
     wf = [mo.fixed_encode(bits, np.asarray(w, dtype=np.float64), frac) for w in weights]
     bf = [mo.fixed_encode(bits, np.asarray(b, dtype=np.float64).reshape(1, -1), frac) for b in biases]
-    out = mlp_forward_shared(sess, xf, wf, bf, frac, relu_via, integral, post_transform, bias_via)
+    out = mlp_forward_shared(sess, xf, wf, bf, frac, relu_via, integral, post_transform, bias_via, activation)
     return out, mo.fixed_decode(mo.rep_reveal(out), frac)
 
 
