@@ -23,7 +23,10 @@ same contract, which is what makes share-level bit-exact parity testable.
 Parity pinning: AES-CTR u64/u128 streams, DeriveSeed and SessionId hashing are
 pinned by the reference's golden vectors (tests/test_oracle_kat.py).  The
 get_bit() policy is pinned by 5 bits only -> "parity partially pinned" for raw
-bit-share streams; revealed values do not depend on it.
+bit-share streams; revealed values do not depend on it.  The protocol layer is
+pinned end to end by the reference's compiled graphs (tests/test_textual.py)
+and by the known answers of its predictor tests on its own ONNX fixtures
+(tests/test_tree_ensembles.py, test_linear_golden.py, test_mlp_golden.py).
 """
 from __future__ import annotations
 
