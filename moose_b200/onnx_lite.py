@@ -157,3 +157,11 @@ def input_features(model_bytes):
             dv = [val for g, _, val in fields(d) if g == 1]
             dims.append(dv[0] if dv else 0)
     return dims[1]
+
+
+def producer_name(model_bytes) -> str:
+    """ModelProto.producer_name = 2."""
+    for fn, wt, v in fields(model_bytes):
+        if fn == 2 and wt == 2:
+            return v.decode()
+    return ""

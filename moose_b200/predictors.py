@@ -264,3 +264,76 @@ class TreeEnsemblePredictor:
     def __call__(self, x: np.ndarray) -> np.ndarray:
         out = self.forward_shared(self.encode(x))
         return self.sess.fixedpoint_decode(self.frac, self.sess.reveal(out, 0)).to_host()
+
+
+# ---- generic dense networks (pymoose/pymoose/predictors/neural_network_predictor.py) ------------------------------------
+def neural_network_from_onnx(model_bytes: bytes):
+    """NeuralNetwork.from_onnx (neural_network_predictor.py:66-153): (weights [in, out] per layer, biases, activations)
+    of a PyTorch (Gemm) or TF-Keras (MatMul + BiasAdd) export."""
+    from . import onnx_lite as ol
+    ops = [op for _, op, _ in ol.nodes(model_bytes)]
+    acts = []
+    for i, op in enumerate(ops):
+        if op in ("Sigmoid", "Softmax", "Relu"):
+            acts.append(op.lower())
+        if i > 0 and op == "Gemm" and ops[i - 1] == "Gemm":
+            acts.append("identity")
+        if i > 2 and ops[i - 3:i + 1] == ["MatMul", "Add", "MatMul", "Add"]:
+            acts.append("identity")
+    ini = ol.initializers(model_bytes)
+    weights, biases = [], []
+    for name, dims, dtype, vals in ini:
+        if "weight" in name or "MatMul" in name:
+            if dtype != 1:
+                raise ValueError("Neural Network Weights must be of type FLOATS, found other.")
+            weights.append(np.asarray(vals[:dims[0] * dims[1]], dtype=np.float64).reshape(dims[0], dims[1]).T)
+    for name, dims, dtype, vals in ini:
+        if "bias" in name or "BiasAdd" in name:
+            if dtype != 1:
+                raise ValueError("Neural network biases must be of type FLOATS, found other.")
+            biases.append(np.asarray(vals[:dims[0]], dtype=np.float64))
+    if "tf" in ol.producer_name(model_bytes):      # Keras stores the layers last to first, weights transposed
+        weights, biases = [w.T for w in weights[::-1]], biases[::-1]
+    if ol.input_features(model_bytes) != weights[0].shape[0]:
+        raise ValueError("the input shape of the ONNX file does not match the first layer's weights")
+    return weights, biases, acts
+
+
+class NeuralNetworkPredictor:
+    """NeuralNetwork (neural_network_predictor.py:17-64): per layer dot with the mirrored weights (shared by player 0
+    inside DotOp), add of the mirrored bias (shared by player 0 inside AddOp, fixedpoint/ops.rs:30-52), then that
+    layer's activation -- sigmoid, relu = maximum([zeros@bob, z]), softmax(axis 1, upmost_index = n_classes) or none --
+    on EVERY layer, the last included."""
+
+    def __init__(self, sess: Session, weights, biases, activations, ring: int = RING128, frac: int = 40, integral: int = 24):
+        self.sess, self.ring, self.frac, self.integral = sess, ring, frac, integral
+        enc = lambda a: sess.fixedpoint_encode(ring, frac, sess.from_host(FLOAT64, np.asarray(a, dtype=np.float64)))
+        self.w = [enc(w) for w in weights]
+        self.b = [enc(np.asarray(b)) for b in biases]              # rank 1, broadcast over the batch
+        self.activations = list(activations)
+        self.n_classes = int(np.shape(biases[-1])[0])
+
+    def encode(self, x: np.ndarray) -> Tensor:
+        return self.sess.fixedpoint_encode(self.ring, self.frac, self.sess.from_host(FLOAT64, np.asarray(x, dtype=np.float64)))
+
+    def forward_shared(self, x_fixed: Tensor) -> RepTensor:
+        s = self.sess
+        x = s.share(x_fixed, 0)
+        for i in range(len(self.w)):
+            y = s.trunc_pr(self.frac, s.rep_dot(x, s.share(self.w[i], 0)))
+            z = s.rep_add(y, s.share(self.b[i], 0))
+            act = self.activations[i]
+            if act == "sigmoid":
+                z = s.sigmoid(self.integral, self.frac, z)
+            elif act == "relu":
+                z = s.maximum([s.share(s.fill(self.ring, 0, z.shape), 1), z])
+            elif act == "softmax":
+                z = s.softmax(1, self.n_classes, self.integral, self.frac, z)
+            elif act != "identity":
+                raise ValueError("Invalid or unsupported activation function")
+            x = z
+        return x
+
+    def __call__(self, x: np.ndarray) -> np.ndarray:
+        out = self.forward_shared(self.encode(x))
+        return self.sess.fixedpoint_decode(self.frac, self.sess.reveal(out, 0)).to_host()

@@ -108,3 +108,22 @@ def tree_ensemble(sess, x, trees, n_features, base_score=0.0, learning_rate=1.0,
         if transform_output:
             y = mo.rep_softmax(sess, 1, n_classes, integral, frac, y)
     return y, mo.fixed_decode(mo.rep_reveal(y), frac)
+
+
+def neural_network(sess, x, weights, biases, activations, bits=128, frac=40, integral=24):
+    """pymoose/pymoose/predictors/neural_network_predictor.py:17-64 on the oracle: dot (mirrored weights shared by
+    player 0), add (mirrored rank-1 bias shared by player 0), activation, on every layer."""
+    n_classes = int(np.shape(biases[-1])[0])
+    h = mo.rep_share(sess, mo.fixed_encode(bits, np.asarray(x, dtype=np.float64), frac), 0)
+    for w, b, act in zip(weights, biases, activations):
+        wr = mo.rep_share(sess, mo.fixed_encode(bits, np.asarray(w, dtype=np.float64), frac), 0)
+        y = mo.rep_trunc_pr(sess, frac, mo.rep_dot(sess, h, wr))
+        z = mo.rep_add(y, mo.rep_share(sess, mo.fixed_encode(bits, np.asarray(b, dtype=np.float64), frac), 0))
+        if act == "sigmoid":
+            z = mo.rep_sigmoid(sess, integral, frac, z)
+        elif act == "relu":
+            z = mo.rep_maximum(sess, [mo.rep_share(sess, mo.fill(bits, 0, z.shape), 1), z])
+        elif act == "softmax":
+            z = mo.rep_softmax(sess, 1, n_classes, integral, frac, z)
+        h = z
+    return h, mo.fixed_decode(mo.rep_reveal(h), frac)
