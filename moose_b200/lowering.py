@@ -364,6 +364,46 @@ class Lowering:
         self.output(reveal_to, self.fixed_decode(reveal_to, self.rep_reveal(x, reveal_to), frac), "output_0")
         return self.ops
 
+    def rep_index_axis(self, axis, index, x):
+        return self._sharewise(lambda i, a: self.index_axis(i, a, axis, index), x)
+
+    def rep_mux_bit(self, s_bits, x, y):
+        """MuxOp::rep_bit_selector_kernel (replicated/control_flow.rs:27-44): ring_inject(s) * (x - y) + y."""
+        s = self.rep_ring_inject(s_bits, 0)
+        return self.rep_add(self.rep_mul(s, self.rep_sub(x, y)), y)
+
+    def tree_regressor_program(self, trees, n_features: int, base_score: float, frac: int, learning_rate: float = 1.0,
+                               reveal_to: int = 1):
+        """pymoose TreeEnsembleRegressor (tree_ensemble.py:33-62, 83-114, 391-395) in the op order of
+        moose_b200/predictors.py::TreeEnsemblePredictor: input `x` at player 0, shared by every index_axis; mirrored
+        thresholds shared by player 0, leaf and base-score constants by player 2; add(base, add_n(scores)) revealed.
+        Constants are one-element tensors (they broadcast against the [batch] columns like the reference's rank-0
+        constants)."""
+        xh = self.fixed_encode(0, self.input(0, "x"), frac)
+        const = lambda h, v: self.fixed_encode(h, self.constant(h, [float(v)]), frac)
+
+        def traverse(tree, node, feats):
+            if tree.left[node] == 0 and tree.right[node] == 0:
+                return None, const(2, learning_rate * tree.weights[node])
+            thr = self.rep_share(const(0, tree.split_conditions[node]), 0)
+            selector = self.rep_less(feats[tree.split_indices[node]], thr)
+            lr, lh = traverse(tree, tree.left[node], feats)
+            rr, rh = traverse(tree, tree.right[node], feats)
+            xs = lr if lr is not None else self.rep_share(lh, 2)
+            ys = rr if rr is not None else self.rep_share(rh, 2)
+            return self.rep_mux_bit(selector, xs, ys), None
+
+        total = None
+        for tree in trees:
+            feats = [self.rep_index_axis(1, i, self.rep_share(xh, 0)) for i in range(n_features)]
+            score, leaf = traverse(tree, 0, feats)
+            if score is None:
+                raise NotImplementedError("degenerate tree (a single leaf)")
+            total = score if total is None else self.rep_add(total, score)      # add_n
+        y = self.rep_add(self.rep_share(const(2, base_score), 2), total)
+        self.output(reveal_to, self.fixed_decode(reveal_to, self.rep_reveal(y, reveal_to), frac), "output_0")
+        return self.ops
+
 
 def prune_pass(ops: List[Operation]) -> List[Operation]:
     """Drops operations no Output / Save depends on (compilation/pruning.rs)."""

@@ -7,6 +7,7 @@ import gzip
 import os
 
 import numpy as np
+import pytest
 
 from moose_b200 import textual as tx
 from moose_b200.executor import toposort
@@ -72,3 +73,28 @@ def test_mlp_graph_on_oracle_kernels():
     n = mb.lib().mb_graph_num_ops(g)
     assert [mb.lib().mb_graph_op_name(g, i).decode() for i in range(n)] == [o.name for o in toposort(net)]
     mb.lib().mb_graph_free(g)
+
+
+@pytest.mark.parametrize("name", ["xgboost_regressor", "random_forest_regressor", "gradient_boosting_regressor"])
+def test_tree_regressor_graph_reproduces_reference_answers(name):
+    """The lowered + networked tree-ensemble regressor (about 10^4 host operations) replayed on the oracle's kernels
+    gives the known answers of the reference's tree_ensemble_test.py for its ONNX fixture."""
+    import json
+    import os
+    from moose_b200.predictors import tree_ensemble_from_onnx_attributes
+    golden = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "tree_ensembles.json")))
+    m = golden["models"][name]
+    kw = tree_ensemble_from_onnx_attributes(m["attributes"], m["n_features"], "regressor")
+    ops = Lowering(128).tree_regressor_program(kw["trees"], kw["n_features"], kw["base_score"], 40)
+    net = networking_pass(prune_pass(ops))
+    assert all(o.placement_kind == "Host" for o in net)
+    _, outs = ro.replay(toposort(net), mo.Session("t", ENTROPY_KEY), tx.parse_constant, tx.attr_hex16,
+                        {"x": np.array(golden["input"], dtype=np.float64)})
+    np.testing.assert_almost_equal(outs["output_0"], np.array(m["expected"]), decimal=2)
+    if name == "xgboost_regressor":   # the native reader accepts the text and schedules it like the Python scheduler
+        import moose_b200 as mb
+        g = ctypes.c_void_p()
+        assert mb.lib().mb_graph_parse(None, tx.dumps_text(net).encode(), ctypes.byref(g)) == 0
+        n = mb.lib().mb_graph_num_ops(g)
+        assert [mb.lib().mb_graph_op_name(g, i).decode() for i in range(n)] == [o.name for o in toposort(net)]
+        mb.lib().mb_graph_free(g)

@@ -5,7 +5,7 @@
 #    when they pass, drop their skipif markers (tests/test_{linear,mlp,nn}_golden.py) and the note in DESIGN.md.
 # 2. the complete serial GPU suite with timing (the last complete run predates the peer-memory transport).
 mkdir -p gpurun_out
-MB_RUN_UNVERIFIED_GPU_TESTS=1 timeout 300 python -m pytest tests/test_linear_golden.py tests/test_mlp_golden.py tests/test_nn_golden.py \
+MB_RUN_UNVERIFIED_GPU_TESTS=1 timeout 300 python -m pytest tests/test_linear_golden.py tests/test_mlp_golden.py tests/test_nn_golden.py tests/test_gpu_replay.py \
   -m gpu -q 2>&1 | tail -15 | tee gpurun_out/todo_golden.log
 timeout 400 python -m pytest tests -m gpu -q --durations=15 2>&1 | tail -30 | tee gpurun_out/todo_full_suite.log
 timeout 90 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -2 | tee gpurun_out/todo_smoke.log
