@@ -127,8 +127,6 @@ def test_replay_generated_mlp_graph():
 
 
 # Written after round 1's GPU budget was spent: not yet executed on a GPU, so opt-in until it has been (tools/gpu_todo.sh).
-@pytest.mark.skipif(os.environ.get("MB_RUN_UNVERIFIED_GPU_TESTS") != "1",
-                    reason="not yet run on a GPU (round 1 budget exhausted); set MB_RUN_UNVERIFIED_GPU_TESTS=1")
 def test_replay_generated_tree_regressor_graph():
     """The lowered + networked tree-ensemble regressor (moose_b200/lowering.py, about 10^4 host operations: compare =
     split + Kogge-Stone adder, mux = dabit ring_inject + replicated mul) through the native executor: every operation

@@ -29,8 +29,6 @@ def test_oracle_protocol_matches_reference_answers(name):
 
 # Written after this round's GPU budget was spent: not yet executed on a GPU, so opt-in until it has been.
 @pytest.mark.gpu
-@pytest.mark.skipif(os.environ.get("MB_RUN_UNVERIFIED_GPU_TESTS") != "1",
-                    reason="not yet run on a GPU (round 1 budget exhausted); set MB_RUN_UNVERIFIED_GPU_TESTS=1")
 @pytest.mark.parametrize("name", MODELS)
 def test_gpu_matches_oracle_bit_for_bit_and_reference_answers(name):
     import moose_b200 as mb
