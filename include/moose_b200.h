@@ -95,6 +95,14 @@ uint64_t mb_ctx_launch_count(const mb_ctx *ctx);
  * since the last read and resets the counters.  kernel: 0 = tensor-pipe limb GEMM. */
 int mb_ctx_profile_enable(mb_ctx *ctx, int enable);
 int mb_ctx_profile_read(mb_ctx *ctx, int kernel, float *total_ms, uint64_t *launches);
+/* Per-kernel trace (measurement only; no counterpart in the reference, whose telemetry is
+ * moose/src/execution/asynchronous.rs tracing spans): while enabled, a CUDA event is recorded behind EVERY
+ * kernel this library launches on `ctx`.  mb_ctx_trace_read synchronises and writes one line per launcher,
+ * "name<TAB>launches<TAB>summed_ms<NL>", NUL-terminated, into buf (if cap suffices; *needed = bytes
+ * required), then starts a new interval.  A launch's time is the distance to the preceding event on the
+ * stream, i.e. its run time plus any memset / copy enqueued between the two launches. */
+int mb_ctx_trace_enable(mb_ctx *ctx, int enable);
+int mb_ctx_trace_read(mb_ctx *ctx, char *buf, size_t cap, size_t *needed);
 /* Page-locked host buffers for callers that stage tensors (H2D / D2H at full
  * PCIe rate); plain malloc'ed memory is accepted everywhere too. */
 int mb_host_alloc_pinned(mb_ctx *ctx, size_t nbytes, void **out);

@@ -66,6 +66,7 @@ ABI = {
     "mb_ctx_launch_count": [_P], "mb_ctx_set_gemm_mode": [_P, _I], "mb_ctx_set_fused_bits": [_P, _I],
     "mb_ctx_profile_enable": [_P, _I],
     "mb_ctx_profile_read": [_P, _I, ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_uint64)],
+    "mb_ctx_trace_enable": [_P, _I], "mb_ctx_trace_read": [_P, _P, ctypes.c_size_t, ctypes.POINTER(ctypes.c_size_t)],
     "mb_host_alloc_pinned": [_P, ctypes.c_size_t, _PP], "mb_host_free_pinned": [_P, _P],
     "mb_tensor_from_host": [_P, _I, _I, _I64P, _P, _PP], "mb_tensor_alloc": [_P, _I, _I, _I64P, _PP],
     "mb_tensor_to_host": [_P, _P, _P, ctypes.c_size_t], "mb_tensor_free": [_P, _P],
@@ -330,6 +331,20 @@ class Session:
         ms, n = ctypes.c_float(), ctypes.c_uint64()
         self._check(lib().mb_ctx_profile_read(self.ctx, kernel, ctypes.byref(ms), ctypes.byref(n)))
         return float(ms.value), int(n.value)
+
+    def trace_enable(self, on: bool = True):
+        self._check(lib().mb_ctx_trace_enable(self.ctx, 1 if on else 0))
+
+    def trace_read(self) -> dict:
+        """{launcher name: (launches, summed device ms)} since the trace was enabled / last read."""
+        need = ctypes.c_size_t()
+        buf = ctypes.create_string_buffer(1 << 16)
+        self._check(lib().mb_ctx_trace_read(self.ctx, buf, len(buf), ctypes.byref(need)))
+        out = {}
+        for line in buf.value.decode().splitlines():
+            name, n, ms = line.split("\t")
+            out[name] = (int(n), float(ms))
+        return out
 
     def pinned_empty(self, shape, dtype) -> np.ndarray:
         """numpy array backed by page-locked host memory (freed with the session)."""

@@ -59,7 +59,10 @@ struct mb_ctx {
   bool fused_bits;            // fused adder / ring_inject kernels (false = op-by-op composition, for A/B tests)
   int gemm_pair_mode;         // 0 = CTA pairs when possible, 1 = single-CTA tiles only (A/B comparison)
   std::atomic<uint64_t> launches;
+  std::mutex prof_mu;         // guards the event pool and the profile / trace lists
   bool profile;
+  bool trace;                 // per-kernel trace: one event behind every launch (mb_ctx_trace_*)
+  std::vector<std::pair<const char *, cudaEvent_t>> trace_events;  // (launcher name, event after the launch); name NULL = start marker
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;  // pending (start, stop) pairs
   std::vector<cudaEvent_t> prof_pool;
   // scratch for the limb GEMM (grown on demand, stream ordered)
@@ -85,11 +88,15 @@ int mb_fail(const mb_ctx *ctx, int code, const std::string &msg);
     if (_rc != MB_OK) return _rc; \
   } while (0)
 
-#define MB_LAUNCH_CHECK(ctx)                 \
-  do {                                       \
-    (ctx)->launches.fetch_add(1);            \
-    MB_CUDA((ctx), cudaGetLastError());      \
+// After every kernel launch: count it, and -- when the per-kernel trace is on (mb_ctx_trace_enable) -- record a CUDA
+// event behind it on the context's stream, tagged with the launcher's name.
+#define MB_LAUNCH_CHECK_AS(ctx, name)                     \
+  do {                                                    \
+    (ctx)->launches.fetch_add(1);                         \
+    MB_CUDA((ctx), cudaGetLastError());                   \
+    if ((ctx)->trace) MB_CHECK(mb_trace_mark((ctx), (name))); \
   } while (0)
+#define MB_LAUNCH_CHECK(ctx) MB_LAUNCH_CHECK_AS(ctx, __func__)
 
 // ---- tensors (tensor.cpp) ---------------------------------------------------
 static inline int mb_elem_bytes(mb_dtype d) { return d == MB_RING128 ? 16 : 8; }
@@ -103,6 +110,7 @@ bool mb_same_shape(const mb_tensor *a, const mb_tensor *b);
 int mb_scratch(mb_ctx *ctx, int slot, size_t bytes, void **out);
 int mb_prof_begin(mb_ctx *ctx, cudaEvent_t *start);  // no-ops unless profiling is enabled
 int mb_prof_end(mb_ctx *ctx, cudaEvent_t start);
+int mb_trace_mark(mb_ctx *ctx, const char *name);
 
 // ---- host-side crypto (blake3.cpp, aes_host.cpp) ----------------------------
 void mb_blake3_session_id(const char *s, size_t len, uint8_t out[16]);

@@ -33,6 +33,7 @@ extern "C" int mb_ctx_create(int device, mb_ctx **out) {
   ctx->gemm_round_barrier = getenv("MOOSE_B200_NO_ROUND_BARRIER") == nullptr;
   ctx->launches = 0;
   ctx->profile = false;
+  ctx->trace = false;
   memset(ctx->scratch, 0, sizeof(ctx->scratch));
   memset(ctx->scratch_bytes, 0, sizeof(ctx->scratch_bytes));
   MB_CUDA(ctx, cudaSetDevice(device));
@@ -64,6 +65,7 @@ extern "C" int mb_ctx_destroy(mb_ctx *ctx) {
     if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
   for (auto &pr : ctx->prof_events) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
   for (auto ev : ctx->prof_pool) cudaEventDestroy(ev);
+  for (auto &te : ctx->trace_events) cudaEventDestroy(te.second);
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
   cudaStreamDestroy(ctx->aux_stream);
@@ -142,6 +144,7 @@ static int prof_event(mb_ctx *ctx, cudaEvent_t *ev) {
 int mb_prof_begin(mb_ctx *ctx, cudaEvent_t *start) {
   *start = nullptr;
   if (!ctx->profile) return MB_OK;
+  std::lock_guard<std::mutex> lock(ctx->prof_mu);
   MB_CHECK(prof_event(ctx, start));
   MB_CUDA(ctx, cudaEventRecord(*start, ctx->stream));
   return MB_OK;
@@ -149,6 +152,7 @@ int mb_prof_begin(mb_ctx *ctx, cudaEvent_t *start) {
 int mb_prof_end(mb_ctx *ctx, cudaEvent_t start) {
   if (!start) return MB_OK;
   cudaEvent_t stop;
+  std::lock_guard<std::mutex> lock(ctx->prof_mu);
   MB_CHECK(prof_event(ctx, &stop));
   MB_CUDA(ctx, cudaEventRecord(stop, ctx->stream));
   ctx->prof_events.emplace_back(start, stop);
@@ -163,6 +167,7 @@ extern "C" int mb_ctx_profile_read(mb_ctx *ctx, int kernel, float *total_ms, uin
   if (!ctx || !total_ms || !launches || kernel != 0)
     return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_profile_read: bad argument");
   MB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  std::lock_guard<std::mutex> lock(ctx->prof_mu);
   float total = 0.f;
   for (auto &pr : ctx->prof_events) {
     float ms = 0.f;
@@ -176,6 +181,65 @@ extern "C" int mb_ctx_profile_read(mb_ctx *ctx, int kernel, float *total_ms, uin
   ctx->prof_events.clear();
   return MB_OK;
 }
+// ---- per-kernel trace ---------------------------------------------------------------------------------------------
+// One event behind every launch while the trace is on.  A launch's time is the distance to the event before it on the
+// same stream (the previous launch's event or the start marker): on a busy stream that is the kernel's run time plus
+// whatever memset / copy / allocation was enqueued between the two launches.
+int mb_trace_mark(mb_ctx *ctx, const char *name) {
+  cudaEvent_t ev;
+  std::lock_guard<std::mutex> lock(ctx->prof_mu);
+  MB_CHECK(prof_event(ctx, &ev));
+  MB_CUDA(ctx, cudaEventRecord(ev, ctx->stream));
+  ctx->trace_events.emplace_back(name, ev);
+  return MB_OK;
+}
+extern "C" int mb_ctx_trace_enable(mb_ctx *ctx, int enable) {
+  if (!ctx) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_trace_enable: NULL ctx");
+  {
+    std::lock_guard<std::mutex> lock(ctx->prof_mu);
+    for (auto &te : ctx->trace_events) ctx->prof_pool.push_back(te.second);
+    ctx->trace_events.clear();
+  }
+  ctx->trace = enable != 0;
+  if (ctx->trace) MB_CHECK(mb_trace_mark(ctx, nullptr));  // start marker
+  return MB_OK;
+}
+extern "C" int mb_ctx_trace_read(mb_ctx *ctx, char *buf, size_t cap, size_t *needed) {
+  if (!ctx || !needed) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_trace_read: NULL argument");
+  MB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  std::lock_guard<std::mutex> lock(ctx->prof_mu);
+  struct Acc { std::string name; uint64_t n; double ms; };
+  std::vector<Acc> acc;
+  for (size_t i = 1; i < ctx->trace_events.size(); i++) {
+    const auto &te = ctx->trace_events[i];
+    if (!te.first) continue;
+    float ms = 0.f;
+    MB_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->trace_events[i - 1].second, te.second));
+    size_t j = 0;
+    for (; j < acc.size(); j++)
+      if (acc[j].name == te.first) break;
+    if (j == acc.size()) acc.push_back(Acc{te.first, 0, 0.0});
+    acc[j].n++;
+    acc[j].ms += ms;
+  }
+  std::string text;
+  char line[256];
+  for (auto &a : acc) {
+    snprintf(line, sizeof(line), "%s\t%llu\t%.6f\n", a.name.c_str(), (unsigned long long)a.n, a.ms);
+    text += line;
+  }
+  *needed = text.size() + 1;
+  if (buf && cap >= text.size() + 1) memcpy(buf, text.c_str(), text.size() + 1);
+  // keep the last event as the new start marker so consecutive reads partition the stream
+  if (!ctx->trace_events.empty()) {
+    for (size_t i = 0; i + 1 < ctx->trace_events.size(); i++) ctx->prof_pool.push_back(ctx->trace_events[i].second);
+    auto last = ctx->trace_events.back();
+    ctx->trace_events.clear();
+    ctx->trace_events.emplace_back(nullptr, last.second);
+  }
+  return MB_OK;
+}
+
 extern "C" int mb_host_alloc_pinned(mb_ctx *ctx, size_t nbytes, void **out) {
   if (!ctx || !out) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_host_alloc_pinned: NULL argument");
   MB_CUDA(ctx, cudaSetDevice(ctx->device));

@@ -885,7 +885,7 @@ int k_gemm_limb_batched(mb_ctx *ctx, mb_dtype dtype, const LimbOperandA *As, int
       split_a_kernel<u128><<<(unsigned)((quads + 255) / 256), 256, 0, ctx->stream>>>((const u128 *)As[i].ptr, pa, M, K, Kp);
     else
       split_a_kernel<uint64_t><<<(unsigned)((quads + 255) / 256), 256, 0, ctx->stream>>>((const uint64_t *)As[i].ptr, pa, M, K, Kp);
-    MB_LAUNCH_CHECK(ctx);
+    MB_LAUNCH_CHECK_AS(ctx, "limb_split");
   }
   for (int i = 0; i < nB; i++) {
     uint8_t *pb = (uint8_t *)dB + (size_t)i * b_plane_bytes;
@@ -893,7 +893,7 @@ int k_gemm_limb_batched(mb_ctx *ctx, mb_dtype dtype, const LimbOperandA *As, int
       split_bt_kernel<u128><<<gb, 256, 0, ctx->stream>>>((const u128 *)Bs[i].b0, (const u128 *)Bs[i].b1, pb, K, N, Kp);
     else
       split_bt_kernel<uint64_t><<<gb, 256, 0, ctx->stream>>>((const uint64_t *)Bs[i].b0, (const uint64_t *)Bs[i].b1, pb, K, N, Kp);
-    MB_LAUNCH_CHECK(ctx);
+    MB_LAUNCH_CHECK_AS(ctx, "limb_split");
   }
 
   const bool use_pair = ctx->gemm_pair_mode != 1 && M >= 2 * BLOCK_M && N >= 128;
@@ -949,7 +949,7 @@ int k_gemm_limb_batched(mb_ctx *ctx, mb_dtype dtype, const LimbOperandA *As, int
     const int grid = (int)std::min<int64_t>(total, ctx->sm_count);
     limb_gemm_kernel<<<grid, NUM_THREADS, SMEM_BYTES, ctx->stream>>>(map_a, map_b, gp);
   }
-  MB_LAUNCH_CHECK(ctx);
+  MB_LAUNCH_CHECK_AS(ctx, "limb_gemm");
   MB_CHECK(mb_prof_end(ctx, prof_start));
 
   RecombineDesc rd;
@@ -962,7 +962,7 @@ int k_gemm_limb_batched(mb_ctx *ctx, mb_dtype dtype, const LimbOperandA *As, int
       recombine_kernel<u128><<<(unsigned)((MN + 255) / 256), 256, 0, ctx->stream>>>(pp, (u128 *)C[b], MN, rd);
     else
       recombine_kernel<uint64_t><<<(unsigned)((MN + 255) / 256), 256, 0, ctx->stream>>>(pp, (uint64_t *)C[b], MN, rd);
-    MB_LAUNCH_CHECK(ctx);
+    MB_LAUNCH_CHECK_AS(ctx, "limb_recombine");
   }
   return MB_OK;
 }

@@ -90,7 +90,7 @@ static int compare_op(mb_ctx *ctx, bool greater, const mb_tensor *x, const mb_te
       if (greater) compare_kernel<uint64_t, true><<<blocks(threads), TPB, 0, ctx->stream>>>((const uint64_t *)xs->dptr, (const uint64_t *)ys->dptr, o, n);
       else compare_kernel<uint64_t, false><<<blocks(threads), TPB, 0, ctx->stream>>>((const uint64_t *)xs->dptr, (const uint64_t *)ys->dptr, o, n);
     }
-    ctx->launches.fetch_add(1);
+    ctx->launches.fetch_add(1); if (ctx->trace) mb_trace_mark(ctx, "host_misc");
     if (cudaGetLastError() != cudaSuccess) rc = mb_fail(ctx, MB_ERR_CUDA, std::string(name) + ": launch failed");
   }
   mb_tensor_free(ctx, probe); mb_tensor_free(ctx, xb); mb_tensor_free(ctx, yb);
@@ -114,7 +114,7 @@ extern "C" int mb_mux(mb_ctx *ctx, const mb_tensor *s, const mb_tensor *x, const
       mux_kernel<u128><<<blocks(t->numel), TPB, 0, ctx->stream>>>((const uint32_t *)s->dptr, (const u128 *)x->dptr, (const u128 *)y->dptr, (u128 *)t->dptr, t->numel);
     else
       mux_kernel<uint64_t><<<blocks(t->numel), TPB, 0, ctx->stream>>>((const uint32_t *)s->dptr, (const uint64_t *)x->dptr, (const uint64_t *)y->dptr, (uint64_t *)t->dptr, t->numel);
-    ctx->launches.fetch_add(1);
+    ctx->launches.fetch_add(1); if (ctx->trace) mb_trace_mark(ctx, "host_misc");
   }
   *out = t;
   return MB_OK;
@@ -129,7 +129,7 @@ extern "C" int mb_sign(mb_ctx *ctx, const mb_tensor *x, mb_tensor **out) {
   if (t->numel) {
     if (x->dtype == MB_RING128) sign_kernel<u128><<<blocks(t->numel), TPB, 0, ctx->stream>>>((const u128 *)x->dptr, (u128 *)t->dptr, t->numel);
     else sign_kernel<uint64_t><<<blocks(t->numel), TPB, 0, ctx->stream>>>((const uint64_t *)x->dptr, (uint64_t *)t->dptr, t->numel);
-    ctx->launches.fetch_add(1);
+    ctx->launches.fetch_add(1); if (ctx->trace) mb_trace_mark(ctx, "host_misc");
   }
   *out = t;
   return MB_OK;
@@ -143,7 +143,7 @@ extern "C" int mb_cast_ring128_to_ring64(mb_ctx *ctx, const mb_tensor *x, mb_ten
   MB_CHECK(mb_tensor_new(ctx, MB_RING64, x->rank, x->shape, &t));
   if (t->numel) {
     cast128_64_kernel<<<blocks(t->numel), TPB, 0, ctx->stream>>>((const u128 *)x->dptr, (uint64_t *)t->dptr, t->numel);
-    ctx->launches.fetch_add(1);
+    ctx->launches.fetch_add(1); if (ctx->trace) mb_trace_mark(ctx, "host_misc");
   }
   *out = t;
   return MB_OK;
@@ -163,7 +163,7 @@ extern "C" int mb_maximum(mb_ctx *ctx, const mb_tensor *const *xs, int n, mb_ten
       max2_kernel<u128><<<blocks(acc->numel), TPB, 0, ctx->stream>>>((const u128 *)acc->dptr, (const u128 *)xs[i]->dptr, (u128 *)acc->dptr, acc->numel);
     else
       max2_kernel<uint64_t><<<blocks(acc->numel), TPB, 0, ctx->stream>>>((const uint64_t *)acc->dptr, (const uint64_t *)xs[i]->dptr, (uint64_t *)acc->dptr, acc->numel);
-    ctx->launches.fetch_add(1);
+    ctx->launches.fetch_add(1); if (ctx->trace) mb_trace_mark(ctx, "host_misc");
   }
   *out = acc;
   return MB_OK;

@@ -268,7 +268,7 @@ extern "C" int mb_transpose(mb_ctx *ctx, const mb_tensor *x, mb_tensor **out) {
         transpose2d_kernel<uint4><<<grid, 256, 0, ctx->stream>>>((const uint4 *)x->dptr, (uint4 *)t->dptr, x->shape[0], x->shape[1]);
       else
         transpose2d_kernel<uint64_t><<<grid, 256, 0, ctx->stream>>>((const uint64_t *)x->dptr, (uint64_t *)t->dptr, x->shape[0], x->shape[1]);
-      ctx->launches.fetch_add(1);
+      ctx->launches.fetch_add(1); if (ctx->trace) mb_trace_mark(ctx, "shape_ops");
       if (cudaGetLastError() != cudaSuccess) rc = mb_fail(ctx, MB_ERR_CUDA, "mb_transpose: launch failed");
     }
   } else {
@@ -315,7 +315,7 @@ extern "C" int mb_concat(mb_ctx *ctx, int axis, const mb_tensor *const *xs, int 
       if (nb == 0) continue;
       const int64_t words = ((pos + nb - 1) >> 5) - (pos >> 5) + 1;
       bit_append_kernel<<<blocks(words), TPB, 0, ctx->stream>>>((const uint32_t *)xs[i]->dptr, (int64_t)(xs[i]->alloc_bytes / 4), (uint32_t *)t->dptr, pos, nb);
-      ctx->launches.fetch_add(1);
+      ctx->launches.fetch_add(1); if (ctx->trace) mb_trace_mark(ctx, "shape_ops");
       if (cudaGetLastError() != cudaSuccess) rc = mb_fail(ctx, MB_ERR_CUDA, "mb_concat: launch failed");
       pos += nb;
     }
@@ -504,7 +504,7 @@ extern "C" int mb_div(mb_ctx *ctx, const mb_tensor *x, const mb_tensor *y, mb_te
         ring_div_kernel<u128><<<blocks(t->numel), TPB, 0, ctx->stream>>>((const u128 *)xs->dptr, (const u128 *)ys->dptr, (u128 *)t->dptr, t->numel, (int *)flagp);
       else
         ring_div_kernel<uint64_t><<<blocks(t->numel), TPB, 0, ctx->stream>>>((const uint64_t *)xs->dptr, (const uint64_t *)ys->dptr, (uint64_t *)t->dptr, t->numel, (int *)flagp);
-      ctx->launches.fetch_add(1);
+      ctx->launches.fetch_add(1); if (ctx->trace) mb_trace_mark(ctx, "shape_ops");
       cudaError_t e = cudaMemcpyAsync(&flag, flagp, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
       if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
       if (e != cudaSuccess) rc = mb_fail(ctx, MB_ERR_CUDA, cudaGetErrorString(e));
@@ -533,7 +533,7 @@ extern "C" int mb_bit_decompose_ring(mb_ctx *ctx, const mb_tensor *x, mb_tensor 
       ring_planes_kernel<u128, 128><<<blocks(x->numel), TPB, 0, ctx->stream>>>((const u128 *)x->dptr, (u128 *)t->dptr, x->numel);
     else
       ring_planes_kernel<uint64_t, 64><<<blocks(x->numel), TPB, 0, ctx->stream>>>((const uint64_t *)x->dptr, (uint64_t *)t->dptr, x->numel);
-    ctx->launches.fetch_add(1);
+    ctx->launches.fetch_add(1); if (ctx->trace) mb_trace_mark(ctx, "shape_ops");
     if (cudaGetLastError() != cudaSuccess) rc = mb_fail(ctx, MB_ERR_CUDA, "mb_bit_decompose_ring: launch failed");
   }
   return finish(ctx, rc, t, out);
@@ -569,7 +569,7 @@ extern "C" int mb_fixedpoint_mean(mb_ctx *ctx, int axis, uint64_t scaling_base, 
       else w = (uint64_t)(int64_t)up;
       scale_kernel<uint64_t><<<blocks(t->numel), TPB, 0, ctx->stream>>>((uint64_t *)t->dptr, w, t->numel);
     }
-    ctx->launches.fetch_add(1);
+    ctx->launches.fetch_add(1); if (ctx->trace) mb_trace_mark(ctx, "shape_ops");
     if (cudaGetLastError() != cudaSuccess) rc = mb_fail(ctx, MB_ERR_CUDA, "mb_fixedpoint_mean: launch failed");
   }
   return finish(ctx, rc, t, out);
@@ -596,7 +596,7 @@ extern "C" int mb_fixedpoint_argmax(mb_ctx *ctx, int axis, const mb_tensor *x, m
       argmax_kernel<u128><<<blocks(t->numel), TPB, 0, ctx->stream>>>((const u128 *)x->dptr, (uint64_t *)t->dptr, outer, x->shape[axis], inner);
     else
       argmax_kernel<uint64_t><<<blocks(t->numel), TPB, 0, ctx->stream>>>((const uint64_t *)x->dptr, (uint64_t *)t->dptr, outer, x->shape[axis], inner);
-    ctx->launches.fetch_add(1);
+    ctx->launches.fetch_add(1); if (ctx->trace) mb_trace_mark(ctx, "shape_ops");
     if (cudaGetLastError() != cudaSuccess) rc = mb_fail(ctx, MB_ERR_CUDA, "mb_fixedpoint_argmax: launch failed");
   }
   return finish(ctx, rc, t, out);

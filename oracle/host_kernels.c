@@ -217,6 +217,16 @@ void orc_sample_bits_unpacked(const uint8_t seed[16], uint64_t nbits, int policy
 
 /* bit_kernel: HostBitTensor from get_bit() calls, packed Lsb0. */
 void orc_sample_bits(const uint8_t seed[16], uint64_t nbits, int policy, uint8_t *out_packed) {
+  if (policy == 0) {
+    /* successive keystream bits, Lsb0 per byte, packed Lsb0: the packed tensor IS the keystream */
+    uint64_t nblocks = (nbits + 127) / 128;
+    uint8_t *buf = (uint8_t *)malloc(nblocks * 16 + 16);
+    orc_aes_ctr(seed, 0, nblocks, buf);
+    memcpy(out_packed, buf, (nbits + 7) / 8);
+    if (nbits & 7) out_packed[nbits >> 3] &= (uint8_t)((1u << (nbits & 7)) - 1);
+    free(buf);
+    return;
+  }
   uint8_t *tmp = (uint8_t *)malloc(nbits + 1);
   orc_sample_bits_unpacked(seed, nbits, policy, tmp);
   memset(out_packed, 0, (nbits + 7) / 8);
@@ -377,17 +387,39 @@ void orc_ring_inject128(const uint8_t *bits, uint64_t n, uint64_t bit_idx, u128 
 }
 /* ShlDimOp::host_bit_kernel (host/ops.rs:835-853): x is [bit_length, height];
  * out = zeros(height*amount) ++ x[0 .. height*(bit_length-amount)). */
+/* Copies `len` bits from src (starting at bit s0) to dst (starting at bit d0); dst bits outside the range are
+ * kept.  Same result as the bit-by-bit loop; whole bytes move with memcpy when the two offsets agree mod 8. */
+static void bitcopy(uint8_t *dst, uint64_t d0, const uint8_t *src, uint64_t s0, uint64_t len) {
+  uint64_t j = 0;
+  if (((d0 ^ s0) & 7) == 0) {
+    for (; j < len && ((d0 + j) & 7); j++) { uint64_t d = d0 + j; dst[d >> 3] = (uint8_t)((dst[d >> 3] & ~(1u << (d & 7))) | (getbit(src, s0 + j) << (d & 7))); }
+    uint64_t nbytes = (len - j) / 8;
+    memcpy(dst + ((d0 + j) >> 3), src + ((s0 + j) >> 3), nbytes);
+    j += nbytes * 8;
+  } else {
+    for (; j < len && ((d0 + j) & 7); j++) { uint64_t d = d0 + j; dst[d >> 3] = (uint8_t)((dst[d >> 3] & ~(1u << (d & 7))) | (getbit(src, s0 + j) << (d & 7))); }
+    const unsigned sh = (unsigned)((s0 + j) & 7);
+    const uint8_t *sp = src + ((s0 + j) >> 3);
+    uint8_t *dp = dst + ((d0 + j) >> 3);
+    uint64_t nbytes = (len - j) / 8;
+    for (uint64_t b = 0; b < nbytes; b++) dp[b] = (uint8_t)((sp[b] >> sh) | (sp[b + 1] << (8 - sh)));
+    j += nbytes * 8;
+  }
+  for (; j < len; j++) { uint64_t d = d0 + j; dst[d >> 3] = (uint8_t)((dst[d >> 3] & ~(1u << (d & 7))) | (getbit(src, s0 + j) << (d & 7))); }
+}
+/* ShlDimOp::host_bit_kernel (host/ops.rs:835-853): x is [bit_length, height];
+ * out = zeros(height*amount) ++ x[0 .. height*(bit_length-amount)). */
 void orc_shl_dim(const uint8_t *x, uint64_t height, uint64_t bit_length, uint64_t amount, uint8_t *out) {
   uint64_t total = height * bit_length;
   memset(out, 0, (total + 7) / 8);
   uint64_t off = height * amount;
-  for (uint64_t j = off; j < total; j++) setbit(out, j, getbit(x, j - off));
+  if (off < total) bitcopy(out, off, x, 0, total - off);
 }
 /* Copy a bit range [start, start+len) of x into out at bit 0 (index_axis /
  * slicing of bit tensors, bitarray.rs:85-108). */
 void orc_bit_copy_range(const uint8_t *x, uint64_t start, uint64_t len, uint8_t *out) {
   memset(out, 0, (len + 7) / 8);
-  for (uint64_t j = 0; j < len; j++) setbit(out, j, getbit(x, start + j));
+  bitcopy(out, 0, x, start, len);
 }
 void orc_bit_pack(const uint8_t *unpacked, uint64_t nbits, uint8_t *out) {
   memset(out, 0, (nbits + 7) / 8);

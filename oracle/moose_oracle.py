@@ -370,8 +370,13 @@ def sum_axis(x: Ring, axis: Optional[int]) -> Ring:
 def fill(bits: int, value: int, shape) -> Ring:
     """FillOp::host_ring64/128_kernel (host/ops.rs:1635-1655)."""
     shape = tuple(shape)
-    n = int(np.prod(shape, dtype=np.int64)) if len(shape) else 1
-    return Ring.from_ints(bits, [value] * n, shape)
+    v = int(value) % (1 << bits)
+    if bits == 64:
+        return Ring(64, np.full(shape, v, dtype=np.uint64))
+    out = np.empty(shape + (2,), dtype=np.uint64)
+    out[..., 0] = v & ((1 << 64) - 1)
+    out[..., 1] = v >> 64
+    return Ring(128, out)
 
 
 def fill_bits(value: int, shape) -> Bits:
