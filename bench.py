@@ -1,23 +1,30 @@
 #!/usr/bin/env python
-"""bench.py -- headline benchmark of the replicated-secret-sharing hot path.
+"""bench.py -- benchmark of the replicated-secret-sharing hot path (BASELINE.json: "MPC inference rows/sec
+(LogReg/MLP) at 1/2/4/8 B200; Ring128 matmul GOP/s").
 
-Workload at every N (BASELINE.json configs[1], the config the metric is quoted on):
-    Replicated Ring128 fixed(24,40) matmul 4096 x 4096 x 4096 + TruncPr(40),
-    synthetic shares, all three parties resident on one B200.
-One "step" = one replicated dot (DotOp::rep_rep_kernel) + one TruncPr
-(TruncPrOp::rep_kernel) over device-resident shares.  With --gpus N every rank runs
-that workload on its own GPU (independent sessions, no data-path collective: weak
-scaling); `value` is the job aggregate.
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload all|matmul|mlp|logreg|prf]
 
-Metric: ring GOP/s = 3 parties x 2 GEMMs x 2*M*N*K ring multiply-adds per step / time
-(SURVEY.md 8d).  `e2e` is the same metric through the C ABI starting from HOST buffers:
-H2D of the two plaintext fixed-point matrices from pinned memory, share, dot, trunc,
-reveal, D2H of the revealed product -- all inside the timed region.
+One run measures three workloads and prints ONE JSON line (stdout); the line's top-level fields are the matmul
+(BASELINE configs[1], the single-GPU config the metric is quoted on) and `workloads` carries the two predictors
+(each record is also printed on stderr as it finishes):
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--size S]
+  matmul  configs[1]  Replicated Ring128 fixed(24,40) 4096^3 dot + TruncPr(40), three parties on one B200.  A step =
+          one DotOp::rep_rep_kernel + one TruncPrOp::rep_kernel.  Unit: ring GOP/s = 3 parties x 2 GEMMs x 2MNK / t
+          (SURVEY.md 8d).  With --gpus N every rank runs its own copy (a 1-GPU config: "weak", replicas).
+  mlp     configs[3]  MLP 784-512-512-10, ReLU = maximum([0, z]), Ring64 fixed(14,23), batch 65536, logits revealed,
+          in the reference's op sequence (mirrored biases shared by player 0, fixedpoint/ops.rs:30-52).  Unit: rows/s.
+  logreg  configs[2]  LinearClassifier, 512 features, 2 classes, sigmoid, Ring128 fixed(24,40), batch 10^6.  rows/s.
 
---impl reference times the CPU restatement of the reference's kernels (oracle/, a port:
-the Rust reference cannot be built here) on the box's host cores on a bounded sample.
+With --gpus N the two predictors split ONE batch over the N ranks (rank g runs all three parties on rows
+[g*B/N, (g+1)*B/N), an independent session per GPU, no data-path collective): "strong" scaling.
+`value` is device time of the step with inputs resident in HBM; `e2e` starts from a host float64 batch in pinned
+memory and ends with the decoded outputs of ALL ranks in rank 0's host memory (H2D, encode, share, forward, reveal,
+decode, NCCL gather of the outputs, D2H inside the timed region).
+
+Each record carries `roofline` for its dominant kernel (from the library's per-kernel trace, a second pass of the same
+steps with one CUDA event behind every launch), a `kernels` table of the launchers behind 95 % of the step, and at N = 1
+a `cpu_baseline`: the oracle (a port of the reference's CPU kernels; the Rust reference cannot be built here) on a
+bounded sample.  --impl reference times that port on the box's host cores for the same three workloads.
 """
 import argparse
 import json
@@ -35,6 +42,10 @@ sys.path.insert(0, ROOT)
 FRAC = 40
 SESSION_ID = "b200-bench"
 ENTROPY_KEY = bytes(range(16))
+MLP_DIMS = (784, 512, 512, 10)
+MLP_FRAC, MLP_INT = 23, 14
+LOGREG_FEATS, LOGREG_FRAC, LOGREG_INT = 512, 40, 24
+L2_NOTE = "inputs larger than L2 (the shares of one step exceed 126 MB)"
 
 
 def ring_ops_per_step(M, K, N):
@@ -48,6 +59,10 @@ def fixed128(vals):
     lo = scaled.astype(np.uint64)
     hi = np.where(scaled < 0, np.uint64(0xFFFFFFFFFFFFFFFF), np.uint64(0)).astype(np.uint64)
     return np.stack([lo, hi], axis=-1)
+
+
+def log(msg):
+    print(msg, file=sys.stderr, flush=True)
 
 
 class ClockSampler:
@@ -74,7 +89,7 @@ class ClockSampler:
             self.proc = None
 
     def mark(self):
-        """The timed region starts here: rows read before count only if none arrives inside it (nvidia-smi needs
+        """A timed region starts here: rows read before count only if none arrives inside it (nvidia-smi needs
         100 ms and more to start, a short run can be over by then; the warm-up steps run the same load)."""
         self.first = len(self.rows)
 
@@ -82,22 +97,17 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.rows.append([c.strip() for c in line.split(",")])
 
-    def stop(self):
+    def snapshot(self):
+        """Clock summary of the rows since mark() (the sampler keeps running)."""
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         timed = self.rows[self.first:]
         source = "timed region"
         if not timed:
-            timed, source = self.rows, "warm-up steps (same load; the timed region was shorter than one sample)"
-        self.rows = timed
-        for r in self.rows:
+            timed, source = list(self.rows), "warm-up steps (same load; the timed region was shorter than one sample)"
+        for r in timed:
             try:
                 sm.append(float(r[1]))
                 mx.append(float(r[2]))
@@ -107,11 +117,22 @@ class ClockSampler:
             except Exception:
                 pass
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "power_w_max": max((float(r[3]) for r in self.rows if len(r) > 3 and r[3].replace('.', '', 1).isdigit()),
+                "power_w_max": max((float(r[3]) for r in timed if len(r) > 3 and r[3].replace('.', '', 1).isdigit()),
                                    default=None),
                 "samples": len(sm), "sampled_during": source, "reasons": sorted(reasons)}
 
+    def stop(self):
+        out = self.snapshot()
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+        return out
 
+
+# ---- multi-rank helpers (one process per GPU under torchrun; CPU tests pass backend="gloo") --------------------------
 def dist_setup(world, local_rank, backend=None):
     """One process per GPU (torchrun): returns torch.distributed or None.  `backend` defaults to nccl; the CPU
     tests of the multi-rank logic pass "gloo"."""
@@ -152,20 +173,137 @@ def reduce_sum_int(dist, value, local_rank=0):
 
 
 def aggregate_value(units_per_rank_step, steps, world, max_ms):
-    """Whole-job throughput: every rank processes the same number of units (weak scaling), time = max over ranks."""
+    """Whole-job throughput: every rank processes the same number of units, time = max over ranks."""
     return world * units_per_rank_step * steps / (max_ms * 1e-3)
+
+
+def shard_rows(batch, world, rank):
+    """Rows [lo, hi) of ONE batch that rank `rank` of `world` processes (equal slices; the batch sizes of the
+    BASELINE configs divide by 1, 2, 4 and 8)."""
+    if batch % world:
+        raise ValueError(f"batch {batch} does not split evenly over {world} ranks")
+    per = batch // world
+    return rank * per, (rank + 1) * per
+
+
+def gather_rows(dist, local, local_rank=0):
+    """Host-side gather of the revealed, decoded outputs: rank 0 gets the [B, cols] array in rank order (rows of rank
+    g are [g*B/N, (g+1)*B/N)), the others None.  `local` is this rank's [B/N, cols] float64 array (host)."""
+    if dist is None:
+        return local
+    import torch
+    dev = _reduce_device(dist, local_rank)
+    t = torch.from_numpy(np.ascontiguousarray(local)).to(dev)
+    world = dist.get_world_size()
+    bufs = [torch.empty_like(t) for _ in range(world)] if dist.get_rank() == 0 else None
+    dist.gather(t, bufs, dst=0)
+    if bufs is None:
+        return None
+    return torch.cat(bufs, dim=0).cpu().numpy()
+
+
+class _DevView:
+    """A library tensor's device memory as a __cuda_array_interface__ object (so torch / NCCL read it in place)."""
+
+    def __init__(self, ptr, shape, typestr="<f8"):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+
+class OutputGather:
+    """Per step: the decoded outputs of all ranks land in rank 0's pinned host memory.  N = 1: one D2H copy on the
+    drainer context.  N > 1: an NCCL gather straight out of the library's device tensor, enqueued behind the drainer
+    context's stream (torch ExternalStream), then rank 0's D2H copy of the gathered rows."""
+
+    def __init__(self, dist, drainer, local_rank, rows_local, cols, world, rank):
+        self.dist, self.drainer, self.rank, self.world = dist, drainer, rank, world
+        self.rows, self.cols = rows_local, cols
+        self.nbytes_local = rows_local * cols * 8
+        if dist is None:
+            self.host = [drainer.pinned_empty((rows_local, cols), np.float64) for _ in range(2)]
+            return
+        import torch
+        self.torch = torch
+        self.dev = torch.device("cuda", local_rank)
+        self.ext = torch.cuda.ExternalStream(drainer.stream, device=self.dev)
+        if rank == 0:
+            self.bufs = [torch.empty((rows_local, cols), dtype=torch.float64, device=self.dev) for _ in range(world)]
+            self.host_t = [torch.empty((rows_local * world, cols), dtype=torch.float64).pin_memory() for _ in range(2)]
+            self.host = [t.numpy() for t in self.host_t]
+
+    def step(self, i, r):
+        """r: this rank's decoded float64 tensor, already handed to the drainer context (r.sess = drainer)."""
+        if self.dist is None:
+            self.drainer.to_host_async(r, self.host[i % 2])
+            return
+        torch = self.torch
+        with torch.cuda.stream(self.ext):
+            t = torch.as_tensor(_DevView(r.device_ptr, (self.rows, self.cols)), device=self.dev)
+            self.dist.gather(t, self.bufs if self.rank == 0 else None, dst=0)
+            if self.rank == 0:
+                for g, b in enumerate(self.bufs):
+                    self.host_t[i % 2][g * self.rows:(g + 1) * self.rows].copy_(b, non_blocking=True)
+
+    def result(self, i):
+        return self.host[i % 2] if (self.dist is None or self.rank == 0) else None
 
 
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         with open(p) as f:
-            return json.load(f), "measured"
-    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+            return json.load(f), "measured (MEASURED_PEAKS.json)"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback (B200_PROFILING.md)"
 
 
-def cpu_baseline_run(size, threads, with_trunc=True):
-    """Oracle (CPU port of the reference kernels) on a size^3 sample of the workload."""
+def host_threads():
+    # all host threads the process may use (torchrun exports OMP_NUM_THREADS=1, so ask the OS, not OpenMP)
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+# ---- synthetic inputs (SURVEY.md 8d) ---------------------------------------------------------------------------------
+def mlp_model():
+    ws = [np.random.default_rng(4 + i).normal(0, MLP_DIMS[i] ** -0.5, (MLP_DIMS[i], MLP_DIMS[i + 1])) for i in range(3)]
+    bs = [np.random.default_rng(40 + i).normal(0, 0.1, MLP_DIMS[i + 1]) for i in range(3)]
+    return ws, bs
+
+
+def mlp_float(x, ws, bs):
+    h = x
+    for i in range(3):
+        h = h @ ws[i] + bs[i]
+        if i < 2:
+            h = np.maximum(h, 0)
+    return h
+
+
+def logreg_model():
+    coeffs = np.random.default_rng(2).normal(0, LOGREG_FEATS ** -0.5, (2, LOGREG_FEATS))
+    intercepts = np.random.default_rng(22).normal(0, 0.1, (1, 2))
+    return coeffs, intercepts
+
+
+def logreg_float(x, coeffs, intercepts):
+    return 1.0 / (1.0 + np.exp(-(x @ coeffs.T + intercepts)))
+
+
+def fill_uniform(buf, seed, lo, hi):
+    """Fills the (pinned) float64 matrix `buf` with U(lo, hi) in chunks (the LogReg batch is 4 GB)."""
+    rng = np.random.default_rng(seed)
+    rows = buf.shape[0]
+    step = max(1, (1 << 24) // max(buf.shape[1], 1))
+    for a in range(0, rows, step):
+        b = min(rows, a + step)
+        rng.random(out=buf[a:b])
+        if (lo, hi) != (0.0, 1.0):
+            buf[a:b] *= (hi - lo)
+            buf[a:b] += lo
+
+
+# ---- CPU legs (the oracle: a port of the reference's CPU kernels) ----------------------------------------------------
+def cpu_matmul(size, threads, with_trunc=True):
     from oracle import moose_oracle as mo
     rng = np.random.default_rng(0)
     a = mo.Ring(128, fixed128(rng.uniform(-1, 1, (size, size))))
@@ -182,92 +320,526 @@ def cpu_baseline_run(size, threads, with_trunc=True):
     return ring_ops_per_step(size, size, size) / dt / 1e9, dt
 
 
+cpu_baseline_run = cpu_matmul  # name used by round-1 callers
+
+
+def cpu_mlp(batch, threads):
+    from oracle import moose_oracle as mo, predictors_oracle as po
+    ws, bs = mlp_model()
+    x = np.random.default_rng(3).uniform(0, 1, (batch, MLP_DIMS[0]))
+    sess = mo.Session(SESSION_ID + "-mlp", ENTROPY_KEY)
+    mo.DOT_THREADS = threads
+    t0 = time.perf_counter()
+    _, dec = po.mlp(sess, x, ws, bs, bits=64, frac=MLP_FRAC, bias_via="share")
+    dt = time.perf_counter() - t0
+    mo.DOT_THREADS = 1
+    assert np.allclose(dec, mlp_float(x, ws, bs), atol=5e-3)
+    return batch / dt, dt
+
+
+def cpu_logreg(batch, threads):
+    from oracle import moose_oracle as mo, predictors_oracle as po
+    coeffs, intercepts = logreg_model()
+    x = np.random.default_rng(1).uniform(-1, 1, (batch, LOGREG_FEATS))
+    sess = mo.Session(SESSION_ID + "-logreg", ENTROPY_KEY)
+    mo.DOT_THREADS = threads
+    t0 = time.perf_counter()
+    _, dec = po.linear(sess, x, coeffs, intercepts, bits=128, frac=LOGREG_FRAC, integral=LOGREG_INT, post_transform="sigmoid")
+    dt = time.perf_counter() - t0
+    mo.DOT_THREADS = 1
+    assert np.allclose(dec, logreg_float(x, coeffs, intercepts), atol=2e-2)
+    return batch / dt, dt
+
+
+PORT_NOTE = ("CPU = the oracle, a port of the reference's host kernels and protocol op sequence (the Rust reference cannot be "
+             "built here); every host op single-threaded like the reference's ndarray kernels")
+
+
+def workload_names(batch_mlp, batch_logreg, size):
+    return {
+        "matmul": f"replicated_ring128_matmul_{size}x{size}x{size}_truncpr40",
+        "mlp": f"mlp_784-512-512-10_relu_ring64_fixed(14,23)_batch{batch_mlp}",
+        "logreg": f"logreg_512features_2classes_sigmoid_ring128_fixed(24,40)_batch{batch_logreg}",
+    }
+
+
+def matmul_config(name):
+    return {"workload": name, "fixed": "fixed(24,40)", "parties": "3 parties resident on each GPU; one independent session per GPU",
+            "l2": L2_NOTE}
+
+
+def predictor_config(name, world):
+    return {"workload": name, "parties": "3 parties resident on each GPU; one independent session per GPU",
+            "sharding": f"one batch split over {world} rank(s) by rows, no data-path collective; outputs gathered on rank 0",
+            "op_sequence": "reference's logical graph (mirrored weights / biases shared by player 0)", "l2": L2_NOTE}
+
+
 def run_reference(args, rank, world):
+    """--impl reference: the CPU port on the box's host cores, same three workloads, each step a bounded sample."""
     if rank != 0:
         return
-    # all host threads the process may use (torchrun exports OMP_NUM_THREADS=1, so ask the OS, not OpenMP)
-    try:
-        threads = len(os.sched_getaffinity(0))
-    except AttributeError:
-        threads = os.cpu_count() or 1
+    threads = host_threads()
+    names = workload_names(args.batch_mlp, args.batch_logreg, args.size)
+    sub_steps, sub_warm = max(1, min(args.steps, 3)), min(args.warmup, 1)
+
+    def timed(fn, arg, steps, warm, warm_arg):
+        for _ in range(warm):
+            fn(warm_arg, threads)
+        times = []
+        for _ in range(steps):
+            _, dt = fn(arg, threads)
+            times.append(dt)
+        return times
+
+    records = {}
+    if args.workload in ("all", "mlp"):
+        b = args.ref_batch_mlp
+        times = timed(cpu_mlp, b, sub_steps, sub_warm, 32)
+        v = b * len(times) / sum(times)
+        sample = f"batch {b} of the {args.batch_mlp}-row workload per step, full MLP forward incl. sharing; dot over {threads} threads (OpenMP), other host ops single-threaded"
+        records["mlp"] = {
+            "impl": "reference", "metric": "mlp_inference_rows_per_s", "value": v, "unit": "rows/s", "steps": len(times),
+            "warmup": sub_warm, "ms_per_step": 1e3 * sum(times) / len(times), "higher_is_better": True, "dtype": "u64",
+            "config": predictor_config(names["mlp"], world),
+            "cpu_baseline": {"value": v, "unit": "rows/s", "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        log(json.dumps(records["mlp"]))
+    if args.workload in ("all", "logreg"):
+        b = args.ref_batch_logreg
+        times = timed(cpu_logreg, b, sub_steps, sub_warm, 64)
+        v = b * len(times) / sum(times)
+        sample = f"batch {b} of the {args.batch_logreg}-row workload per step, full LinearClassifier forward incl. sharing and sigmoid; dot over {threads} threads, other host ops single-threaded"
+        records["logreg"] = {
+            "impl": "reference", "metric": "logreg_inference_rows_per_s", "value": v, "unit": "rows/s", "steps": len(times),
+            "warmup": sub_warm, "ms_per_step": 1e3 * sum(times) / len(times), "higher_is_better": True, "dtype": "u128",
+            "config": predictor_config(names["logreg"], world),
+            "cpu_baseline": {"value": v, "unit": "rows/s", "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        log(json.dumps(records["logreg"]))
+    if args.workload in ("mlp", "logreg"):
+        line = records[args.workload]
+        line.update({"n_gpus": args.gpus, "scaling": "strong", "vs_baseline": None, "data": "synthetic", "gpu_launches": 0})
+        print(json.dumps(line), flush=True)
+        return
+
     size = max(args.ref_size, 1024)
     for _ in range(min(args.warmup, 1)):
-        cpu_baseline_run(min(size, 128), threads)
-    vals, times = [], []
+        cpu_matmul(min(size, 128), threads)
+    times = []
     for _ in range(args.steps):
-        v, dt = cpu_baseline_run(size, threads)
-        vals.append(v)
+        _, dt = cpu_matmul(size, threads)
         times.append(dt)
     value = ring_ops_per_step(size, size, size) * len(times) / sum(times) / 1e9
-    sample = (f"replicated Ring128 dot {size}x{size}x{size} + TruncPr(40) per step (bounded sample of the 4096^3 "
-              f"workload; 9 host GEMMs like the reference, OpenMP over rows)")
+    sample = (f"replicated Ring128 dot {size}x{size}x{size} + TruncPr(40) per step (bounded sample of the {args.size}^3 "
+              f"workload; 9 host GEMMs like the reference, OpenMP over rows on {threads} threads)")
     line = {
         "impl": "reference", "metric": "replicated_ring128_matmul_gops", "value": value, "unit": "GOP/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * sum(times) / len(times), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u128", "data": "synthetic",
-        "config": {"workload": "replicated_ring128_matmul_4096x4096x4096_truncpr40",
-                   "fixed": "fixed(24,40)", "sample": sample},
+        "config": matmul_config(names["matmul"]), "sample": sample, "note": PORT_NOTE,
         "cpu_baseline": {"value": value, "unit": "GOP/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "GOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
+        "gpu_launches": 0, "workloads": records,
     }
     print(json.dumps(line), flush=True)
 
 
-def run_mlp(args):
-    """BASELINE configs[3]: MLP 784-512-512-10, ReLU = maximum([0, z]), fixed(14,23) on Ring64, logits revealed.
-    One step = one forward pass over a device-resident fixed-point batch (sharing included)."""
+# ---- GPU legs ----------------------------------------------------------------------------------------------------------
+class Env:
+    def __init__(self, args):
+        self.args = args
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        self.dist = None
+        self.peaks, self.peak_src = measured_peaks()
+        self.sampler = None
+        self.int8_peak = None     # measured TOP/s of a library int8 GEMM (peak probe), rank 0
+        self.prf_peak = None      # measured G AES blocks/s of the library's pure PRF kernel
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+
+
+def kernel_table(trace, steps):
+    """Per-launcher rows from the library trace, sorted by time; rates from the algorithmic work each launcher states."""
+    total = sum(v["ms"] for v in trace.values()) or 1.0
+    rows = []
+    for name, v in sorted(trace.items(), key=lambda kv: -kv[1]["ms"]):
+        s = v["ms"] * 1e-3
+        rows.append({"kernel": name, "launches_per_step": v["n"] / steps, "ms_per_step": v["ms"] / steps,
+                     "share": v["ms"] / total,
+                     "GBps": (v["bytes"] / s / 1e9) if s > 0 and v["bytes"] else None,
+                     "G_aes_blocks_per_s": (v["aes_blocks"] / s / 1e9) if s > 0 and v["aes_blocks"] else None,
+                     "int8_TOPs": (v["tensor_ops"] / s / 1e12) if s > 0 and v["tensor_ops"] else None})
+    return rows, total / steps
+
+
+def roofline_from(env, rows, traced_ms_per_step, traffic=None):
+    """`roofline` of the dominant launcher.  bound: "tensor" for the limb GEMM, else "hbm" (algorithmic bytes / time
+    against the measured copy bandwidth); PRF-consuming kernels also carry their AES-block rate against the measured
+    PRF peak, which is what actually bounds them."""
+    top = rows[0]
+    hbm = env.peaks["hbm_gbs"]
+    if top["int8_TOPs"]:
+        peak = env.int8_peak or 2.0 * env.peaks.get("bf16_tflops_sustained", env.peaks["bf16_tflops"])
+        src = ("int8 GEMM peak probe measured in this run" if env.int8_peak else
+               f"2 x bf16_tflops_sustained of {env.peak_src} (no int8 figure measured)")
+        r = {"kernel": top["kernel"], "bound": "tensor", "achieved": top["int8_TOPs"], "peak": peak, "unit": "TOP/s (int8)",
+             "frac": top["int8_TOPs"] / peak, "traffic": traffic, "peak_source": src}
+    else:
+        r = {"kernel": top["kernel"], "bound": "hbm", "achieved": top["GBps"], "peak": hbm, "unit": "GB/s",
+             "frac": (top["GBps"] / hbm) if top["GBps"] else None, "traffic": traffic,
+             "peak_source": f"hbm_gbs of {env.peak_src}"}
+        if top["G_aes_blocks_per_s"]:
+            r["prf"] = {"achieved": top["G_aes_blocks_per_s"], "peak": env.prf_peak, "unit": "G AES blocks/s",
+                        "frac": (top["G_aes_blocks_per_s"] / env.prf_peak) if env.prf_peak else None,
+                        "note": "the kernel expands PRF streams; the AES rate, not HBM, bounds it"}
+    r["avg_launch_ms"] = top["ms_per_step"] / max(top["launches_per_step"], 1e-9)
+    r["launches_per_step"] = top["launches_per_step"]
+    r["share_of_step"] = top["share"]
+    r["traced_ms_per_step"] = traced_ms_per_step
+    return r
+
+
+def trim(rows, frac=0.95, cap=12):
+    out, acc = [], 0.0
+    for r in rows:
+        out.append({k: (round(v, 4) if isinstance(v, float) else v) for k, v in r.items()})
+        acc += r["share"]
+        if acc >= frac or len(out) >= cap:
+            break
+    return out
+
+
+def probe_peaks(env):
+    """Rank 0, before the workloads: (1) the library's pure PRF kernel (SampleSeeded of 2^26 Ring128 elements, 1 GB of
+    keystream) = the measured PRF peak the PRF-consuming kernels are compared with; (2) an int8 tensor GEMM of a
+    library (torch._int_mm -> cuBLASLt, 8192^3), used ONLY as the measured int8 peak for the limb GEMM's fraction."""
     import moose_b200 as mb
-    from moose_b200.predictors import MLPPredictor
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    dist = dist_setup(world, local_rank)
-    dims = (784, 512, 512, 10)
-    rng = np.random.default_rng(3 + rank)
-    ws = [np.random.default_rng(4 + i).normal(0, dims[i] ** -0.5, (dims[i], dims[i + 1])) for i in range(3)]
-    bs = [np.random.default_rng(40 + i).normal(0, 0.1, dims[i + 1]) for i in range(3)]
-    sess = mb.Session(local_rank, f"{SESSION_ID}-mlp-{rank}", ENTROPY_KEY)
-    pred = MLPPredictor(sess, ws, bs, mb.RING64, 23, "maximum")
-    x = rng.uniform(0, 1, (args.batch, dims[0]))
-    xf = pred.encode(x)
-    for _ in range(args.warmup):
-        out = pred.forward_shared(xf)
+    sess = mb.Session(env.local_rank, f"{SESSION_ID}-probe", ENTROPY_KEY)
+    n = 1 << 26
+    for _ in range(2):
+        t = sess.sample_uniform_seeded(mb.RING128, (n,), bytes(16))
+    best = None
+    for _ in range(5):
+        sess.timer_start()
+        t = sess.sample_uniform_seeded(mb.RING128, (n,), bytes(16))
+        ms = sess.timer_stop()
+        best = ms if best is None else min(best, ms)
+    del t
+    env.prf_peak = n / (best * 1e-3) / 1e9
+    sess.close()
+    try:
+        import torch
+        dev = torch.device("cuda", env.local_rank)
+        m = 8192
+        a = torch.randint(-128, 127, (m, m), dtype=torch.int8, device=dev)
+        b = torch.randint(-128, 127, (m, m), dtype=torch.int8, device=dev)
+        for _ in range(3):
+            torch._int_mm(a, b)
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 20
+        e0.record()
+        for _ in range(reps):
+            torch._int_mm(a, b)
+        e1.record()
+        torch.cuda.synchronize(dev)
+        env.int8_peak = 2.0 * m ** 3 * reps / (e0.elapsed_time(e1) * 1e-3) / 1e12
+        del a, b
+        torch.cuda.empty_cache()
+    except Exception as e:  # no int8 GEMM in this torch build: the 2 x bf16 proxy stays
+        log(f"int8 peak probe unavailable: {e!r}")
+
+
+def pipelined(sess, loader, drainer, steps, load, compute, drain):
+    """Per step: the H2D of step i+1 (loader context) and the output path of step i-1 (drainer context) overlap the
+    kernels of step i; contexts are ordered with mb_ctx_wait."""
+    ins, keep = load(), None
+    for i in range(steps):
+        sess.wait(loader)                              # operands of step i are on the device
+        nxt = load() if i + 1 < steps else None        # prefetch: overlaps the kernels below
+        r = compute(ins)
+        r.sess = drainer                               # freed on the drainer's stream, after its copy
+        drainer.wait(sess)
+        drain(i, r)
+        loader.wait(sess)                              # the inputs are freed on the loader's stream after their last use
+        keep, ins = (ins, r), nxt                      # step i's tensors live until step i+1 has been enqueued
+        del r
+    del keep
+    drainer.sync()
+    loader.sync()
     sess.sync()
-    if dist is not None:
-        dist.barrier()
+
+
+def run_matmul(env):
+    import moose_b200 as mb
+    args, rank, world, lr = env.args, env.rank, env.world, env.local_rank
+    M = N = K = args.size
+    sess = mb.Session(lr, f"{SESSION_ID}-{rank}", ENTROPY_KEY)
+    rng = np.random.default_rng(rank)
+    hA = sess.pinned_empty((M, K, 2), np.uint64)
+    hB = sess.pinned_empty((K, N, 2), np.uint64)
+    hA[...] = fixed128(rng.uniform(-1, 1, (M, K)))
+    hB[...] = fixed128(rng.uniform(-1, 1, (K, N)))
+    x = sess.share(sess.from_host(mb.RING128, hA), 0)
+    y = sess.share(sess.from_host(mb.RING128, hB), 1)
+    sess.sync()
+
+    def step():
+        return sess.trunc_pr(FRAC, sess.rep_dot(x, y))
+
+    for _ in range(args.warmup):
+        out = step()
+    sess.sync()
+    # ---- kernel-only timed region (inputs resident in HBM) ----
+    sess.profile_enable(True)
+    sess.profile_read()
+    env.barrier()
+    sess.sync()
+    env.sampler.mark()
+    launches0 = sess.launch_count
+    sess.timer_start()
+    for _ in range(args.steps):
+        out = step()
+    ms = sess.timer_stop()
+    sess.sync()
+    env.barrier()
+    launches = sess.launch_count - launches0
+    clocks = env.sampler.snapshot()
+    gemm_ms, gemm_launches = sess.profile_read()
+    sess.profile_enable(False)
+    # ---- per-kernel trace pass (same steps) ----
+    sess.trace_enable(True)
+    for _ in range(args.steps):
+        out = step()
+    rows, traced = kernel_table(sess.trace_read(), args.steps)
+    sess.trace_enable(False)
+    del out
+
+    # ---- end-to-end timed region (host buffers in, host buffer out) ----
+    loader = mb.Session(lr, f"{SESSION_ID}-{rank}-loader", ENTROPY_KEY)
+    drainer = mb.Session(lr, f"{SESSION_ID}-{rank}-drainer", ENTROPY_KEY)
+    hOuts = [sess.pinned_empty((M, N, 2), np.uint64) for _ in range(2)]
+
+    def load():
+        return loader.from_host_async(mb.RING128, hA), loader.from_host_async(mb.RING128, hB)
+
+    def compute(ins):
+        a, b = ins
+        z = sess.trunc_pr(FRAC, sess.rep_dot(sess.share(a, 0), sess.share(b, 1)))
+        return sess.reveal(z, 0)
+
+    def drain(i, r):
+        drainer.to_host_async(r, hOuts[i % 2])
+
+    pipelined(sess, loader, drainer, 2, load, compute, drain)
+    env.barrier()
+    t0 = time.perf_counter()
+    pipelined(sess, loader, drainer, args.steps, load, compute, drain)
+    ms_e2e = 1e3 * (time.perf_counter() - t0)
+    env.barrier()
+    hOut = hOuts[(args.steps - 1) % 2]
+    ms, ms_e2e = reduce_max(env.dist, [ms, ms_e2e], lr)
+    launches = reduce_sum_int(env.dist, launches, lr)
+
+    # spot check: the revealed product decodes to A @ B (plaintext) within the TruncPr error
+    a0 = hA[:4, :, 0].astype(np.int64).astype(np.float64) / 2 ** FRAC
+    b0 = hB[:, :4, 0].astype(np.int64).astype(np.float64) / 2 ** FRAC
+    got = hOut[:4, :4, 0].astype(np.int64).astype(np.float64) / 2 ** FRAC
+    ok = bool(np.allclose(got, a0 @ b0, atol=K * 2.0 ** -FRAC * 4 + 2.0 ** -38))
+    h2d, d2h = int(hA.nbytes + hB.nbytes), int(hOut.nbytes)
+    loader.close()
+    drainer.close()
+    del x, y
+    sess.close()
+    if rank != 0:
+        return None
+    ops = ring_ops_per_step(M, K, N)
+    name = workload_names(args.batch_mlp, args.batch_logreg, args.size)["matmul"]
+    # the limb GEMM's own (start, stop) events inside the timed region
+    int8_ops = 3 * 2.0 * M * N * (2 * K) * 136
+    avg_ms = gemm_ms / max(gemm_launches, 1)
+    achieved = int8_ops / (avg_ms * 1e-3) / 1e12 if gemm_launches else None
+    peak = env.int8_peak or 2.0 * env.peaks.get("bf16_tflops_sustained", env.peaks["bf16_tflops"])
+    line = {
+        "metric": "replicated_ring128_matmul_gops", "value": aggregate_value(ops, args.steps, world, ms) / 1e9, "unit": "GOP/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u128", "data": "synthetic",
+        "config": matmul_config(name), "result_check": "ok" if ok else "MISMATCH",
+        "clocks": clocks,
+        "e2e": {"value": aggregate_value(ops, args.steps, world, ms_e2e) / 1e9, "unit": "GOP/s", "ms_per_step": ms_e2e / args.steps,
+                "pipelining": "per step: H2D of both operands and D2H of the result, pinned host memory; copies of "
+                              "steps i+1 / i-1 overlap the kernels of step i (loader / drainer contexts)",
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": int(launches),
+        "roofline": {"kernel": "limb_gemm_kernel_2cta", "bound": "tensor", "achieved": achieved, "peak": peak,
+                     "unit": "TOP/s (int8)", "frac": (achieved / peak) if achieved else None,
+                     # dram__bytes_read.sum + dram__bytes_write.sum of one launch (ncu --set full, profiles/); the
+                     # algorithmic operand + partial bytes of the launch are 2.4 GB + 4.0 GB
+                     "traffic": GEMM_TRAFFIC_BYTES if (M, K, N) == (4096, 4096, 4096) else None,
+                     "avg_launch_ms": avg_ms, "launches_timed": gemm_launches, "share_of_step": gemm_ms / ms if ms else None,
+                     "peak_source": ("int8 GEMM peak probe measured in this run (torch._int_mm 8192^3, library kernel, probe only)"
+                                     if env.int8_peak else f"2 x bf16_tflops_sustained of {env.peak_src} (no int8 figure measured)"),
+                     "peak_2x_bf16_sustained": 2.0 * env.peaks.get("bf16_tflops_sustained", env.peaks["bf16_tflops"])},
+        "kernels": trim(rows),
+        "peaks": {"hbm_gbs": env.peaks["hbm_gbs"], "int8_tops_probe": env.int8_peak, "prf_g_blocks_per_s": env.prf_peak,
+                  "source": env.peak_src},
+    }
+    return line
+
+
+GEMM_TRAFFIC_BYTES = 43.45e9   # profiles/r1_limb_gemm_2cta_roundbarrier_ncu_full_raw.csv
+
+
+def run_predictor(env, kind):
+    """mlp / logreg: one batch split by rows over the ranks; kernel-only value, trace pass, pipelined e2e with gather."""
+    import moose_b200 as mb
+    from moose_b200.predictors import LinearPredictor, MLPPredictor
+    args, rank, world, lr = env.args, env.rank, env.world, env.local_rank
+    if kind == "mlp":
+        B, cols_in, cols_out, ring, frac, seed = args.batch_mlp, MLP_DIMS[0], MLP_DIMS[-1], mb.RING64, MLP_FRAC, 3
+        lo_hi = (0.0, 1.0)
+    else:
+        B, cols_in, cols_out, ring, frac, seed = args.batch_logreg, LOGREG_FEATS, 2, mb.RING128, LOGREG_FRAC, 1
+        lo_hi = (-1.0, 1.0)
+    r0, r1 = shard_rows(B, world, rank)
+    rows_local = r1 - r0
+    sess = mb.Session(lr, f"{SESSION_ID}-{kind}-{rank}", ENTROPY_KEY)
+    if kind == "mlp":
+        ws, bs = mlp_model()
+        pred = MLPPredictor(sess, ws, bs, ring, frac, "maximum", integral=MLP_INT, bias_via="share")
+    else:
+        coeffs, intercepts = logreg_model()
+        pred = LinearPredictor(sess, coeffs, intercepts, ring, frac, LOGREG_INT, "sigmoid")
+    hX = sess.pinned_empty((rows_local, cols_in), np.float64)
+    fill_uniform(hX, seed * 1000 + rank, *lo_hi)
+    head = hX[:64].copy()
+
+    xf = pred.encode(hX)          # device-resident fixed-point batch
+    sess.sync()
+
+    def step():
+        return sess.reveal(pred.forward_shared(xf), 0)
+
+    for _ in range(args.warmup):
+        out = step()
+    sess.sync()
+    env.barrier()
+    sess.sync()
+    env.sampler.mark()
     l0 = sess.launch_count
     sess.timer_start()
     for _ in range(args.steps):
-        out = pred.forward_shared(xf)
+        out = step()
     ms = sess.timer_stop()
+    sess.sync()
+    env.barrier()
     launches = sess.launch_count - l0
-    ms = reduce_max(dist, [ms], local_rank)[0]
-    launches = reduce_sum_int(dist, launches, local_rank)
-    got = sess.fixedpoint_decode(23, sess.reveal(out)).to_host()[:64]
-    ref = x[:64]
-    for i in range(3):
-        ref = ref @ ws[i] + bs[i]
-        if i < 2:
-            ref = np.maximum(ref, 0)
-    if rank == 0:
-        print(json.dumps({
-            "metric": "mlp_inference_rows_per_s", "value": aggregate_value(args.batch, args.steps, world, ms),
-            "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "u64", "data": "synthetic",
-            "config": {"workload": f"mlp_784-512-512-10_relu_ring64_fixed(14,23)_batch{args.batch}",
-                       "max_abs_err_vs_float": float(np.abs(got - ref).max())},
-            "gpu_launches": int(launches)}), flush=True)
+    clocks = env.sampler.snapshot()
+    got = sess.fixedpoint_decode(frac, out).to_host()[:64]
+    # trace pass
+    sess.trace_enable(True)
+    for _ in range(args.steps):
+        out = step()
+    rows, traced = kernel_table(sess.trace_read(), args.steps)
+    sess.trace_enable(False)
+    del out, xf
+
+    # ---- end to end: host float64 batch -> decoded outputs of all ranks on rank 0's host ----
+    loader = mb.Session(lr, f"{SESSION_ID}-{kind}-{rank}-loader", ENTROPY_KEY)
+    drainer = mb.Session(lr, f"{SESSION_ID}-{kind}-{rank}-drainer", ENTROPY_KEY)
+    gather = OutputGather(env.dist, drainer, lr, rows_local, cols_out, world, rank)
+
+    def load():
+        return loader.from_host_async(mb.FLOAT64, hX)
+
+    def compute(xin):
+        x_fixed = sess.fixedpoint_encode(ring, frac, xin)
+        return sess.fixedpoint_decode(frac, sess.reveal(pred.forward_shared(x_fixed), 0))
+
+    pipelined(sess, loader, drainer, 2, load, compute, gather.step)
+    env.barrier()
+    t0 = time.perf_counter()
+    pipelined(sess, loader, drainer, args.steps, load, compute, gather.step)
+    if env.dist is not None:
+        import torch
+        torch.cuda.synchronize(lr)
+    ms_e2e = 1e3 * (time.perf_counter() - t0)
+    env.barrier()
+    final = gather.result(args.steps - 1)
+    ms, ms_e2e = reduce_max(env.dist, [ms, ms_e2e], lr)
+    launches = reduce_sum_int(env.dist, launches, lr)
+    if kind == "mlp":
+        ref = mlp_float(head, ws, bs)
+        tol = 5e-3
+    else:
+        ref = logreg_float(head, coeffs, intercepts)
+        tol = 2e-2   # the reference's classifier tests check 2 decimals (Goldschmidt at fixed(24,40), DESIGN.md section 2)
+    err = float(np.abs(got - ref).max())
+    ok = err < tol
+    if final is not None:
+        err_e2e = float(np.abs(final[:64] - ref).max())   # rank 0's rows come first
+        ok = ok and err_e2e < tol and final.shape == (B, cols_out) and bool(np.isfinite(final).all())
+    loader.close()
+    drainer.close()
+    del pred
     sess.close()
-    if dist is not None:
-        dist.destroy_process_group()
+    if rank != 0:
+        return None
+    names = workload_names(args.batch_mlp, args.batch_logreg, args.size)
+    rec = {
+        "metric": f"{kind}_inference_rows_per_s", "value": B * args.steps / (ms * 1e-3), "unit": "rows/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "u64" if kind == "mlp" else "u128", "data": "synthetic",
+        "config": predictor_config(names[kind], world),
+        "result_check": "ok" if ok else "MISMATCH", "max_abs_err_vs_float": err,
+        "clocks": clocks,
+        "e2e": {"value": B * args.steps / (ms_e2e * 1e-3), "unit": "rows/s", "ms_per_step": ms_e2e / args.steps,
+                "pipelining": "per step and rank: H2D of the float64 rows from pinned memory, encode, share, forward, reveal, "
+                              "decode; NCCL gather of the decoded outputs to rank 0 and its D2H; copies overlap the kernels of "
+                              "the neighbouring steps (loader / drainer contexts)",
+                "h2d_bytes_per_step": int(rows_local * cols_in * 8) * world, "d2h_bytes_per_step": int(B * cols_out * 8)},
+        "gpu_launches": int(launches),
+        "roofline": roofline_from(env, rows, traced),
+        "kernels": trim(rows),
+    }
+    return rec
+
+
+def add_cpu_baselines(env, line, records):
+    """Rank 0 at N = 1: the port on bounded samples, single-threaded host ops like the reference."""
+    args = env.args
+    threads = host_threads()
+    if line is not None:
+        v, dt = cpu_matmul(args.ref_size, 1)
+        line["cpu_baseline"] = {
+            "value": v, "unit": "GOP/s", "cores": 1, "kind": "port",
+            "sample": f"replicated Ring128 dot {args.ref_size}^3 + TruncPr(40), {dt:.1f} s; {PORT_NOTE}; box has {threads} usable cores"}
+    if "mlp" in records:
+        b = args.cpu_batch_mlp
+        v, dt = cpu_mlp(b, 1)
+        v3, dt3 = cpu_mlp(b, 3)
+        records["mlp"]["cpu_baseline"] = {
+            "value": v, "unit": "rows/s", "cores": 1, "kind": "port",
+            "sample": f"batch {b} of the {args.batch_mlp}-row workload, full forward, {dt:.1f} s; {PORT_NOTE}",
+            "three_threads": {"value": v3, "cores": 3, "seconds": dt3, "note": "dot over 3 threads (one per party's GEMMs)"}}
+    if "logreg" in records:
+        b = args.cpu_batch_logreg
+        v, dt = cpu_logreg(b, 1)
+        v3, dt3 = cpu_logreg(b, 3)
+        records["logreg"]["cpu_baseline"] = {
+            "value": v, "unit": "rows/s", "cores": 1, "kind": "port",
+            "sample": f"batch {b} of the {args.batch_logreg}-row workload, full forward incl. sigmoid, {dt:.1f} s; {PORT_NOTE}",
+            "three_threads": {"value": v3, "cores": 3, "seconds": dt3, "note": "dot over 3 threads"}}
 
 
 def run_prf(args):
     """PRF microbenchmark (the ceiling of the PRF-consuming kernels): SampleSeeded of a 4 GB Ring128 tensor.
-    Roofline: the T-table formulation does 148 shared-memory lookups per AES block (4 + 8 x 16 + 16) and an SM retires
+    Stated bound: the T-table formulation does 148 shared-memory lookups per AES block (4 + 8 x 16 + 16) and an SM retires
     one 32-lane LDS per clock, so peak = SMs x 32 x f_SM / 148 blocks/s at the SM clock sampled under load."""
     import moose_b200 as mb
     sess = mb.Session(0, f"{SESSION_ID}-prf", ENTROPY_KEY)
@@ -301,245 +873,61 @@ def run_prf(args):
     sess.close()
 
 
-def run_logreg(args):
-    """BASELINE configs[2]: LinearClassifier, 512 features, 2 classes, sigmoid post-transform, Ring128 fixed(24,40).
-    One step = share + bias concat + dot [B,513]x[513,2] + TruncPr + sigmoid over a device-resident fixed-point batch."""
-    import moose_b200 as mb
-    from moose_b200.predictors import LinearPredictor
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    dist = dist_setup(world, local_rank)
-    feats = 512
-    B = args.batch
-    coeffs = np.random.default_rng(2).normal(0, feats ** -0.5, (2, feats))
-    intercepts = np.random.default_rng(22).normal(0, 0.1, (1, 2))
-    sess = mb.Session(local_rank, f"{SESSION_ID}-logreg-{rank}", ENTROPY_KEY)
-    pred = LinearPredictor(sess, coeffs, intercepts, mb.RING128, 40, 24, "sigmoid")
-    rng = np.random.default_rng(1 + rank)
-    # build the fixed-point input on the device in chunks (the f64 matrix alone is 4 GB at B = 10^6)
-    x_head = None
-    chunks = []
-    for lo in range(0, B, 1 << 17):
-        n = min(1 << 17, B - lo)
-        xc = rng.uniform(-1, 1, (n, feats))
-        if x_head is None:
-            x_head = xc[:64].copy()
-        chunks.append(fixed128(xc))
-    xf = sess.from_host(mb.RING128, np.concatenate(chunks, axis=0))
-    del chunks
-    for _ in range(args.warmup):
-        out = pred.forward_shared(xf)
-    sess.sync()
-    if dist is not None:
-        dist.barrier()
-    l0 = sess.launch_count
-    sess.timer_start()
-    for _ in range(args.steps):
-        out = pred.forward_shared(xf)
-    ms = sess.timer_stop()
-    launches = reduce_sum_int(dist, sess.launch_count - l0, local_rank)
-    ms = reduce_max(dist, [ms], local_rank)[0]
-    got = sess.fixedpoint_decode(40, sess.reveal(out)).to_host()[:64]
-    ref = 1.0 / (1.0 + np.exp(-(x_head @ coeffs.T + intercepts)))
-    if rank == 0:
-        print(json.dumps({
-            "metric": "logreg_inference_rows_per_s", "value": aggregate_value(B, args.steps, world, ms),
-            "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "u128", "data": "synthetic",
-            "config": {"workload": f"logreg_512features_2classes_sigmoid_ring128_fixed(24,40)_batch{B}",
-                       "max_abs_err_vs_float": float(np.abs(got - ref).max())},
-            "gpu_launches": int(launches)}), flush=True)
-    sess.close()
-    if dist is not None:
-        dist.destroy_process_group()
-
-
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--size", type=int, default=4096, help="M=N=K (default: the BASELINE config, 4096)")
-    ap.add_argument("--ref-size", type=int, default=640, help="sample size of the CPU baseline arms")
+    ap.add_argument("--workload", default="all", choices=["all", "matmul", "mlp", "logreg", "prf"],
+                    help="all = matmul (the top-level fields) + mlp + logreg records in one line")
+    ap.add_argument("--size", type=int, default=4096, help="matmul M=N=K (default: the BASELINE config, 4096)")
+    ap.add_argument("--batch-mlp", type=int, default=65536)
+    ap.add_argument("--batch-logreg", type=int, default=1000000)
+    ap.add_argument("--batch", type=int, default=None, help="overrides the batch of --workload mlp / logreg")
+    ap.add_argument("--ref-size", type=int, default=640, help="matmul sample size of the CPU baseline (>= 1024 in --impl reference)")
+    ap.add_argument("--cpu-batch-mlp", type=int, default=256)
+    ap.add_argument("--cpu-batch-logreg", type=int, default=1024)
+    ap.add_argument("--ref-batch-mlp", type=int, default=512)
+    ap.add_argument("--ref-batch-logreg", type=int, default=2048)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="matmul", choices=["matmul", "mlp", "logreg", "prf"],
-                    help="matmul = BASELINE configs[1] (the bench contract); mlp = configs[3], a secondary line")
-    ap.add_argument("--batch", type=int, default=65536)
+    ap.add_argument("--no-peak-probe", action="store_true")
     args = ap.parse_args()
+    if args.batch is not None:
+        args.batch_mlp = args.batch_logreg = args.batch
     if args.workload == "prf":
         return run_prf(args)
-    if args.workload == "mlp":
-        return run_mlp(args)
-    if args.workload == "logreg":
-        return run_logreg(args)
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-
+    env = Env(args)
     if args.impl == "reference":
-        run_reference(args, rank, world)
-        return
+        return run_reference(args, env.rank, env.world)
 
-    import moose_b200 as mb
-    dist = dist_setup(world, local_rank)
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-
-    M = N = K = args.size
-    sess = mb.Session(local_rank, f"{SESSION_ID}-{rank}", ENTROPY_KEY)
-    rng = np.random.default_rng(rank)
-    # pinned host staging buffers with the plaintext fixed(24,40) operands
-    hA = sess.pinned_empty((M, K, 2), np.uint64)
-    hB = sess.pinned_empty((K, N, 2), np.uint64)
-    hA[...] = fixed128(rng.uniform(-1, 1, (M, K)))
-    hB[...] = fixed128(rng.uniform(-1, 1, (K, N)))
-    hOut = sess.pinned_empty((M, N, 2), np.uint64)
-
-    # device-resident shares for the kernel-only number
-    x = sess.share(sess.from_host(mb.RING128, hA), 0)
-    y = sess.share(sess.from_host(mb.RING128, hB), 1)
-    sess.sync()
-
-    def step():
-        z = sess.rep_dot(x, y)
-        return sess.trunc_pr(FRAC, z)
-
-    def step_e2e():
-        a = sess.from_host(mb.RING128, hA)
-        b = sess.from_host(mb.RING128, hB)
-        z = sess.trunc_pr(FRAC, sess.rep_dot(sess.share(a, 0), sess.share(b, 1)))
-        r = sess.reveal(z, 0)
-        sess._check(mb.lib().mb_tensor_to_host(sess.ctx, r.h, hOut.ctypes.data_as(mb._P), hOut.nbytes))
-
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    for _ in range(args.warmup):
-        out = step()
-    sess.sync()
-
-    # ---- kernel-only timed region (inputs resident in HBM; 6 x 268 MB of shares > 126 MB L2) ----
-    sess.profile_enable(True)
-    sess.profile_read()
-    barrier()
-    sess.sync()
-    sampler.mark()
-    launches0 = sess.launch_count
-    sess.timer_start()
-    for _ in range(args.steps):
-        out = step()
-    ms = sess.timer_stop()
-    sess.sync()
-    barrier()
-    launches = sess.launch_count - launches0
-    clocks = sampler.stop()
-    gemm_ms, gemm_launches = sess.profile_read()
-    sess.profile_enable(False)
-
-    # ---- end-to-end timed region (host buffers in, host buffer out) ----
-    # Every step copies its two operands from pinned host memory and its result back to pinned host memory inside the
-    # timed region.  The copies run on a loader and a drainer context (own streams) so that the H2D of step i+1 and
-    # the D2H of step i-1 overlap the kernels of step i; contexts are ordered with mb_ctx_wait.
-    loader = mb.Session(local_rank, f"{SESSION_ID}-{rank}-loader", ENTROPY_KEY)
-    drainer = mb.Session(local_rank, f"{SESSION_ID}-{rank}-drainer", ENTROPY_KEY)
-    hOuts = [hOut, sess.pinned_empty((M, N, 2), np.uint64)]
-
-    def load():
-        return loader.from_host_async(mb.RING128, hA), loader.from_host_async(mb.RING128, hB)
-
-    def run_e2e(steps):
-        ins, keep = load(), None
-        for i in range(steps):
-            sess.wait(loader)                              # operands of step i are on the device
-            nxt = load() if i + 1 < steps else None        # prefetch: overlaps the kernels below
-            a, b = ins
-            z = sess.trunc_pr(FRAC, sess.rep_dot(sess.share(a, 0), sess.share(b, 1)))
-            r = sess.reveal(z, 0)
-            r.sess = drainer                               # freed on the drainer's stream, after its copy
-            drainer.wait(sess)
-            drainer.to_host_async(r, hOuts[i % 2])
-            loader.wait(sess)                              # a, b are freed on the loader's stream after their last use
-            keep, ins = (a, b, r), nxt
-            del a, b, r, z
-        del keep
-        drainer.sync()
-        loader.sync()
-        sess.sync()
-
-    run_e2e(2)
-    barrier()
-    t0 = time.perf_counter()
-    run_e2e(args.steps)
-    ms_e2e = 1e3 * (time.perf_counter() - t0)
-    barrier()
-    hOut = hOuts[(args.steps - 1) % 2]
-
-    ms, ms_e2e = reduce_max(dist, [ms, ms_e2e], local_rank)
-    launches = reduce_sum_int(dist, launches, local_rank)
-
-    # spot check: the revealed product decodes to A @ B (plaintext) within the TruncPr error
-    ok = True
-    if rank == 0:
-        a0 = hA[:4, :, 0].astype(np.int64).astype(np.float64) / 2 ** FRAC
-        b0 = hB[:, :4, 0].astype(np.int64).astype(np.float64) / 2 ** FRAC
-        got = hOut[:4, :4, 0].astype(np.int64).astype(np.float64) / 2 ** FRAC
-        ok = bool(np.allclose(got, a0 @ b0, atol=K * 2.0 ** -FRAC * 4 + 2.0 ** -38))
-
-    if rank == 0:
-        ops = ring_ops_per_step(M, K, N)
-        value = aggregate_value(ops, args.steps, world, ms) / 1e9
-        e2e = aggregate_value(ops, args.steps, world, ms_e2e) / 1e9
-        peaks, peak_src = measured_peaks()
-        # dominant kernel: limb_gemm_kernel, one batched launch per step = 3 parties x ([M, 2K] x [2K, N] ring GEMM
-        # as 136 u8 x u8 limb GEMMs)
-        int8_ops_per_launch = 3 * 2.0 * M * N * (2 * K) * 136
-        avg_ms = gemm_ms / max(gemm_launches, 1)
-        achieved = int8_ops_per_launch / (avg_ms * 1e-3) / 1e12 if gemm_launches else None
-        peak = 2.0 * peaks.get("bf16_tflops_sustained", peaks["bf16_tflops"])
-        line = {
-            "metric": "replicated_ring128_matmul_gops", "value": value, "unit": "GOP/s", "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u128",
-            "data": "synthetic",
-            "config": {"workload": f"replicated_ring128_matmul_{M}x{K}x{N}_truncpr40", "fixed": "fixed(24,40)",
-                       "parties": "3 parties resident on each GPU; one independent session per GPU",
-                       "l2": "inputs larger than L2 (6 x 268 MB of shares vs 126 MB)",
-                       "result_check": "ok" if ok else "MISMATCH"},
-            "clocks": clocks,
-            "e2e": {"value": e2e, "unit": "GOP/s", "ms_per_step": ms_e2e / args.steps,
-                    "pipelining": "per step: H2D of both operands and D2H of the result, pinned host memory; copies of "
-                                  "steps i+1 / i-1 overlap the kernels of step i (loader / drainer contexts)",
-                    "h2d_bytes_per_step": int(hA.nbytes + hB.nbytes), "d2h_bytes_per_step": int(hOut.nbytes)},
-            "gpu_launches": int(launches),
-            "roofline": {"kernel": "limb_gemm_kernel", "bound": "tensor", "achieved": achieved, "peak": peak,
-                         "unit": "TOP/s (int8)", "frac": (achieved / peak) if achieved else None,
-                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full capture of this
-                         # command (profiles/r1_limb_gemm_2cta_roundbarrier_ncu_full_raw.csv); algorithmic operand +
-                         # partial bytes of the launch are 2.4 GB + 4.0 GB
-                         "traffic": 43.45e9 if (M, K, N) == (4096, 4096, 4096) else None,
-                         "avg_launch_ms": avg_ms, "launches_timed": gemm_launches,
-                         "share_of_step": gemm_ms / ms if ms else None,
-                         "peak_source": f"2 x bf16_tflops_sustained of {peak_src} MEASURED_PEAKS.json "
-                                        "(no int8 figure is measured; int8 dense = 2 x bf16 nominally)"},
-        }
-        if world == 1 and not args.no_cpu_baseline:
-            from oracle import moose_oracle as mo
-            v, dt = cpu_baseline_run(args.ref_size, 1)
-            line["cpu_baseline"] = {
-                "value": v, "unit": "GOP/s", "cores": 1, "kind": "port",
-                "sample": f"replicated Ring128 dot {args.ref_size}^3 + TruncPr(40), {dt:.1f} s, single-threaded host "
-                          "kernels like the reference (ndarray generic dot, SURVEY F9); box has "
-                          f"{os.cpu_count()} logical cores"}
+    env.dist = dist_setup(env.world, env.local_rank)
+    env.sampler = ClockSampler(env.local_rank)
+    env.sampler.start()
+    if not args.no_peak_probe:
+        probe_peaks(env)
+    line, records = None, {}
+    if args.workload in ("all", "matmul"):
+        line = run_matmul(env)
+    for kind in ("mlp", "logreg"):
+        if args.workload in ("all", kind):
+            rec = run_predictor(env, kind)
+            if rec is not None:
+                records[kind] = rec
+    env.sampler.stop()
+    if env.rank == 0:
+        if env.world == 1 and not args.no_cpu_baseline:
+            add_cpu_baselines(env, line, records)
+        for rec in records.values():
+            log(json.dumps(rec))
+        if line is None:                      # a single predictor workload: its record is the line
+            line = records[args.workload]
+        else:
+            line["workloads"] = records
         print(json.dumps(line), flush=True)
-
-    sess.close()
-    if dist is not None:
-        dist.destroy_process_group()
+    if env.dist is not None:
+        env.dist.destroy_process_group()
 
 
 if __name__ == "__main__":

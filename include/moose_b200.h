@@ -98,7 +98,8 @@ int mb_ctx_profile_read(mb_ctx *ctx, int kernel, float *total_ms, uint64_t *laun
 /* Per-kernel trace (measurement only; no counterpart in the reference, whose telemetry is
  * moose/src/execution/asynchronous.rs tracing spans): while enabled, a CUDA event is recorded behind EVERY
  * kernel this library launches on `ctx`.  mb_ctx_trace_read synchronises and writes one line per launcher,
- * "name<TAB>launches<TAB>summed_ms<NL>", NUL-terminated, into buf (if cap suffices; *needed = bytes
+ * "name<TAB>launches<TAB>summed_ms<TAB>hbm_bytes<TAB>aes_blocks<TAB>tensor_ops<NL>" (the last three: the
+ * algorithmic work the launcher states; 0 where it states none), NUL-terminated, into buf (if cap suffices; *needed = bytes
  * required), then starts a new interval.  A launch's time is the distance to the preceding event on the
  * stream, i.e. its run time plus any memset / copy enqueued between the two launches. */
 int mb_ctx_trace_enable(mb_ctx *ctx, int enable);
@@ -155,6 +156,12 @@ int mb_derive_seed(mb_ctx *ctx, const uint8_t sync_key[16], const uint8_t key[16
  * max_value >= 0 is MB_ERR_UNIMPLEMENTED (ops.rs:2025-2029). */
 int mb_sample_seeded(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape,
                      const uint8_t seed[16], int64_t max_value, mb_tensor **out);
+/* The same uniform stream (max_value = None) entered at AES block `first_block`: the tensor's 16-byte vector v is
+ * block first_block + v of AES-128-CTR(seed), i.e. what elements [first_block*16/w, ...) of a longer
+ * SampleSeededOp tensor hold (moose/src/host/ops.rs:1959-2017; aes-prng keeps incrementing one 128-bit counter).
+ * For callers that cut one logical tensor into row slices and for streams past 2^32 blocks. */
+int mb_sample_seeded_at(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape,
+                        const uint8_t seed[16], uint64_t first_block, mb_tensor **out);
 /* SampleOp::* (moose/src/host/ops.rs:1883-1957): seed drawn from the entropy source. */
 int mb_sample(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, int64_t max_value,
               mb_tensor **out);

@@ -66,6 +66,7 @@ ABI = {
     "mb_ctx_launch_count": [_P], "mb_ctx_set_gemm_mode": [_P, _I], "mb_ctx_set_fused_bits": [_P, _I],
     "mb_ctx_profile_enable": [_P, _I],
     "mb_ctx_profile_read": [_P, _I, ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_uint64)],
+    "mb_sample_seeded_at": [_P, _I, _I, _I64P, _U8P, _U64, _PP],
     "mb_ctx_trace_enable": [_P, _I], "mb_ctx_trace_read": [_P, _P, ctypes.c_size_t, ctypes.POINTER(ctypes.c_size_t)],
     "mb_host_alloc_pinned": [_P, ctypes.c_size_t, _PP], "mb_host_free_pinned": [_P, _P],
     "mb_tensor_from_host": [_P, _I, _I, _I64P, _P, _PP], "mb_tensor_alloc": [_P, _I, _I, _I64P, _PP],
@@ -336,14 +337,15 @@ class Session:
         self._check(lib().mb_ctx_trace_enable(self.ctx, 1 if on else 0))
 
     def trace_read(self) -> dict:
-        """{launcher name: (launches, summed device ms)} since the trace was enabled / last read."""
+        """{launcher name: {"n": launches, "ms": summed device ms, "bytes": algorithmic HBM bytes, "aes_blocks": ...,
+        "tensor_ops": ...}} since the trace was enabled / last read (work figures are 0 where a launcher states none)."""
         need = ctypes.c_size_t()
         buf = ctypes.create_string_buffer(1 << 16)
         self._check(lib().mb_ctx_trace_read(self.ctx, buf, len(buf), ctypes.byref(need)))
         out = {}
         for line in buf.value.decode().splitlines():
-            name, n, ms = line.split("\t")
-            out[name] = (int(n), float(ms))
+            name, n, ms, by, bl, ops = line.split("\t")
+            out[name] = {"n": int(n), "ms": float(ms), "bytes": float(by), "aes_blocks": float(bl), "tensor_ops": float(ops)}
         return out
 
     def pinned_empty(self, shape, dtype) -> np.ndarray:
@@ -450,6 +452,12 @@ class Session:
         out = self._out()
         mv = -1 if max_value is None else int(max_value)
         return self._t(lib().mb_sample_seeded(self.ctx, dtype, rank, arr, bytes(seed), mv, ctypes.byref(out)), out)
+
+    def sample_uniform_seeded_at(self, dtype: int, shape, seed: bytes, first_block: int) -> Tensor:
+        """Uniform seeded stream entered at AES block `first_block` (mb_sample_seeded_at)."""
+        arr, rank = _shape_arr(shape)
+        out = self._out()
+        return self._t(lib().mb_sample_seeded_at(self.ctx, dtype, rank, arr, bytes(seed), int(first_block), ctypes.byref(out)), out)
 
     def sample_bits_seeded(self, dtype: int, shape, seed: bytes) -> Tensor:
         return self.sample_uniform_seeded(dtype, shape, seed, max_value=1)

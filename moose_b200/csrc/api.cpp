@@ -32,7 +32,7 @@ extern "C" int mb_derive_seed(mb_ctx *ctx, const uint8_t sync_key[16], const uin
 }
 
 static int sample_with_seed(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, const uint8_t seed[16],
-                            int64_t max_value, mb_tensor **out) {
+                            int64_t max_value, mb_tensor **out, uint64_t first_block = 0) {
   MB_REQUIRE(ctx, out && (shape || rank == 0), MB_ERR_INVALID_ARGUMENT, "sample: NULL argument");
   MB_REQUIRE(ctx, dtype == MB_RING64 || dtype == MB_RING128 || dtype == MB_BIT, MB_ERR_TYPE_MISMATCH,
              "sample: dtype must be ring64, ring128 or bit");
@@ -51,7 +51,7 @@ static int sample_with_seed(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t
   mb_aes_expand(seed, &k);
   mb_tensor *t = nullptr;
   MB_CHECK(mb_tensor_new(ctx, dtype, rank, shape, &t));
-  int rc = k_sample(ctx, k, t, bits_as_ring);
+  int rc = k_sample(ctx, k, t, bits_as_ring, first_block);
   if (rc != MB_OK) {
     mb_tensor_free(ctx, t);
     return rc;
@@ -65,6 +65,13 @@ extern "C" int mb_sample_seeded(mb_ctx *ctx, mb_dtype dtype, int rank, const int
   MB_ENTER(ctx, "mb_sample_seeded");
   MB_REQUIRE(ctx, seed, MB_ERR_INVALID_ARGUMENT, "mb_sample_seeded: NULL seed");
   return sample_with_seed(ctx, dtype, rank, shape, seed, max_value, out);
+}
+
+extern "C" int mb_sample_seeded_at(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, const uint8_t seed[16],
+                                   uint64_t first_block, mb_tensor **out) {
+  MB_ENTER(ctx, "mb_sample_seeded_at");
+  MB_REQUIRE(ctx, seed, MB_ERR_INVALID_ARGUMENT, "mb_sample_seeded_at: NULL seed");
+  return sample_with_seed(ctx, dtype, rank, shape, seed, -1, out, first_block);
 }
 
 extern "C" int mb_sample(mb_ctx *ctx, mb_dtype dtype, int rank, const int64_t *shape, int64_t max_value, mb_tensor **out) {

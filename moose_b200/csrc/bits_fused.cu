@@ -429,7 +429,7 @@ int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only,
     else
       split_planes_kernel<uint64_t, 64><<<g, TPB, 0, ctx->stream>>>((const uint64_t *)x->s[0]->dptr, (const uint64_t *)x->s[1]->dptr,
                                                                    (const uint64_t *)x->s[2]->dptr, (uint32_t *)B->dptr, (uint32_t *)C->dptr, n);
-    MB_LAUNCH_CHECK_AS(ctx, "split_planes");
+    MB_LAUNCH_CHECK_W(ctx, "split_planes", 3.0 * n * (k / 8) + 2.0 * k * n / 8, 0, 0);
   }
 
   // 2. g0, p0 on all planes
@@ -440,7 +440,7 @@ int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only,
     const int64_t total = (int64_t)k * nv;
     AES_LAUNCH(ctx, adder_init_kernel, AES_TPB_LIGHT, total, keys[0], keys[1], keys[2], keys[3], (const vec_t *)B->dptr,
                (const vec_t *)C->dptr, ptrs_of(g.t), ptrs_of(p0.t), total);
-    MB_LAUNCH_CHECK_AS(ctx, "adder_init");
+    MB_LAUNCH_CHECK_W(ctx, "adder_init", 16.0 * total * 8, 4.0 * total, 0);
   }
 
   // 3. plane sets needed per level (all planes for the full decomposition)
@@ -512,7 +512,10 @@ int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only,
     const AesKey *kk = keys + 4 + 6 * i;
     AES_LAUNCH(ctx, adder_level_kernel, AES_TPB_384, (int64_t)d.nout * nv, kk[0], kk[1], kk[2], kk[3], kk[4], kk[5], d,
                ptrs_of(g.t), ptrs_of(p_cur->t), ptrs_of(g_next.t), ptrs_of(p_next.t), nv);
-    MB_LAUNCH_CHECK_AS(ctx, "adder_level");
+    {
+      const double items = (double)d.nout * nv, pfrac = d.nout ? (double)np_out / d.nout : 0.0;
+      MB_LAUNCH_CHECK_W(ctx, "adder_level", 16.0 * items * (12 + 3 + 3 * pfrac), items * (3 + 3 * pfrac), 0);
+    }
     g.swap(g_next);
     p.swap(p_next);
     p_cur = &p;
@@ -530,7 +533,7 @@ int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only,
     adder_final_full_kernel<<<(unsigned)std::min<int64_t>((total + TPB - 1) / TPB, (int64_t)ctx->sm_count * 16), TPB, 0,
                               ctx->stream>>>(ptrs_of(g.t), ptrs_of(p0.t), zp, nv, k);
   }
-  MB_LAUNCH_CHECK_AS(ctx, "adder_final");
+  MB_LAUNCH_CHECK_W(ctx, "adder_final", 16.0 * 9 * nv * (msb_only ? 1 : k), 0, 0);
   return MB_OK;
 }
 
@@ -547,7 +550,7 @@ int k_ring_inject_fused(mb_ctx *ctx, const AesKey &k_br0, const AesKey &k_y0, co
   else
     AES_LAUNCH(ctx, ring_inject_fused_kernel<VK_RING64>, AES_TPB_LIGHT, nvec, ARGS, bit_idx & 63);
 #undef ARGS
-  MB_LAUNCH_CHECK(ctx);
+  MB_LAUNCH_CHECK_W(ctx, "ring_inject_fused", 16.0 * nvec * 3 + 4.0 * t->numel / 8, 3.0 * nvec, 0);
   return MB_OK;
 }
 

@@ -48,6 +48,9 @@ struct mb_ctx {
   cudaEvent_t ev0, ev1;
   int sm_count;
   std::mutex mu;             // guards entropy, setup, last-error bookkeeping
+  std::mutex setup_mu;       // serialises the one-time generation of the replicated setup
+  std::mutex gemm_mu;        // limb GEMM: scratch lookup + split + GEMM + recombine are enqueued as one unit
+  bool gemm_registered;      // counted in the per-device tally of contexts that run limb GEMMs
   uint8_t sid[16];
   bool deterministic;
   uint8_t entropy_key[16];
@@ -62,7 +65,8 @@ struct mb_ctx {
   std::mutex prof_mu;         // guards the event pool and the profile / trace lists
   bool profile;
   bool trace;                 // per-kernel trace: one event behind every launch (mb_ctx_trace_*)
-  std::vector<std::pair<const char *, cudaEvent_t>> trace_events;  // (launcher name, event after the launch); name NULL = start marker
+  struct TraceRec { const char *name; cudaEvent_t ev; double bytes, aes_blocks, tensor_ops; };
+  std::vector<TraceRec> trace_events;  // event after each launch; name NULL = start marker
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;  // pending (start, stop) pairs
   std::vector<cudaEvent_t> prof_pool;
   // scratch for the limb GEMM (grown on demand, stream ordered)
@@ -90,12 +94,15 @@ int mb_fail(const mb_ctx *ctx, int code, const std::string &msg);
 
 // After every kernel launch: count it, and -- when the per-kernel trace is on (mb_ctx_trace_enable) -- record a CUDA
 // event behind it on the context's stream, tagged with the launcher's name.
-#define MB_LAUNCH_CHECK_AS(ctx, name)                     \
-  do {                                                    \
-    (ctx)->launches.fetch_add(1);                         \
-    MB_CUDA((ctx), cudaGetLastError());                   \
-    if ((ctx)->trace) MB_CHECK(mb_trace_mark((ctx), (name))); \
+// MB_LAUNCH_CHECK_W also states the launch's ALGORITHMIC work: HBM bytes (operands read + results
+// written, each once), AES blocks of PRF stream, int8 tensor operations -- what the roofline fractions are computed from.
+#define MB_LAUNCH_CHECK_W(ctx, name, bytes, aes_blocks, tensor_ops)                                                    \
+  do {                                                                                                                 \
+    (ctx)->launches.fetch_add(1);                                                                                      \
+    MB_CUDA((ctx), cudaGetLastError());                                                                                \
+    if ((ctx)->trace) MB_CHECK(mb_trace_mark((ctx), (name), (double)(bytes), (double)(aes_blocks), (double)(tensor_ops))); \
   } while (0)
+#define MB_LAUNCH_CHECK_AS(ctx, name) MB_LAUNCH_CHECK_W(ctx, name, 0, 0, 0)
 #define MB_LAUNCH_CHECK(ctx) MB_LAUNCH_CHECK_AS(ctx, __func__)
 
 // ---- tensors (tensor.cpp) ---------------------------------------------------
@@ -108,9 +115,11 @@ mb_tensor *mb_tensor_retain(mb_tensor *t);
 int mb_tensor_view(mb_ctx *ctx, const mb_tensor *parent, size_t byte_offset, int rank, const int64_t *shape, mb_tensor **out);
 bool mb_same_shape(const mb_tensor *a, const mb_tensor *b);
 int mb_scratch(mb_ctx *ctx, int slot, size_t bytes, void **out);
+// contexts on `device` that have launched the limb GEMM so far (the round barrier is used only by a sole one)
+int mb_gemm_ctx_register(mb_ctx *ctx);
 int mb_prof_begin(mb_ctx *ctx, cudaEvent_t *start);  // no-ops unless profiling is enabled
 int mb_prof_end(mb_ctx *ctx, cudaEvent_t start);
-int mb_trace_mark(mb_ctx *ctx, const char *name);
+int mb_trace_mark(mb_ctx *ctx, const char *name, double bytes = 0, double aes_blocks = 0, double tensor_ops = 0);
 
 // ---- host-side crypto (blake3.cpp, aes_host.cpp) ----------------------------
 void mb_blake3_session_id(const char *s, size_t len, uint8_t out[16]);
@@ -136,7 +145,7 @@ int k_fixed_encode(mb_ctx *ctx, const mb_tensor *x, double scale, mb_tensor *out
 int k_fixed_decode(mb_ctx *ctx, const mb_tensor *x, double scale, mb_tensor *out);
 int k_fixed_encode_raw(mb_ctx *ctx, const double *x_dev, mb_dtype ring, void *out_dev, int64_t n, double scale);
 
-int k_sample(mb_ctx *ctx, const AesKey &key, mb_tensor *out, bool bits_as_ring);
+int k_sample(mb_ctx *ctx, const AesKey &key, mb_tensor *out, bool bits_as_ring, uint64_t first_block = 0);
 
 int k_bit_decompose(mb_ctx *ctx, const mb_tensor *x, mb_tensor *out);
 int k_bit_extract(mb_ctx *ctx, unsigned bit_idx, const mb_tensor *x, mb_tensor *out);

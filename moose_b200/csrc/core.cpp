@@ -4,6 +4,7 @@
 #include <cstdlib>
 
 static thread_local std::string g_last_error;
+static std::atomic<int> g_gemm_ctxs[64];  // per device: contexts that have run the limb GEMM
 
 void mb_set_error(const mb_ctx *, const std::string &msg) { g_last_error = msg; }
 int mb_fail(const mb_ctx *ctx, int code, const std::string &msg) {
@@ -34,6 +35,7 @@ extern "C" int mb_ctx_create(int device, mb_ctx **out) {
   ctx->launches = 0;
   ctx->profile = false;
   ctx->trace = false;
+  ctx->gemm_registered = false;
   memset(ctx->scratch, 0, sizeof(ctx->scratch));
   memset(ctx->scratch_bytes, 0, sizeof(ctx->scratch_bytes));
   MB_CUDA(ctx, cudaSetDevice(device));
@@ -61,11 +63,12 @@ extern "C" int mb_ctx_destroy(mb_ctx *ctx) {
   if (!ctx) return MB_OK;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
+  if (ctx->gemm_registered) g_gemm_ctxs[ctx->device & 63].fetch_sub(1);
   for (int i = 0; i < 4; i++)
     if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
   for (auto &pr : ctx->prof_events) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
   for (auto ev : ctx->prof_pool) cudaEventDestroy(ev);
-  for (auto &te : ctx->trace_events) cudaEventDestroy(te.second);
+  for (auto &te : ctx->trace_events) cudaEventDestroy(te.ev);
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
   cudaStreamDestroy(ctx->aux_stream);
@@ -185,19 +188,19 @@ extern "C" int mb_ctx_profile_read(mb_ctx *ctx, int kernel, float *total_ms, uin
 // One event behind every launch while the trace is on.  A launch's time is the distance to the event before it on the
 // same stream (the previous launch's event or the start marker): on a busy stream that is the kernel's run time plus
 // whatever memset / copy / allocation was enqueued between the two launches.
-int mb_trace_mark(mb_ctx *ctx, const char *name) {
+int mb_trace_mark(mb_ctx *ctx, const char *name, double bytes, double aes_blocks, double tensor_ops) {
   cudaEvent_t ev;
   std::lock_guard<std::mutex> lock(ctx->prof_mu);
   MB_CHECK(prof_event(ctx, &ev));
   MB_CUDA(ctx, cudaEventRecord(ev, ctx->stream));
-  ctx->trace_events.emplace_back(name, ev);
+  ctx->trace_events.push_back(mb_ctx::TraceRec{name, ev, bytes, aes_blocks, tensor_ops});
   return MB_OK;
 }
 extern "C" int mb_ctx_trace_enable(mb_ctx *ctx, int enable) {
   if (!ctx) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_trace_enable: NULL ctx");
   {
     std::lock_guard<std::mutex> lock(ctx->prof_mu);
-    for (auto &te : ctx->trace_events) ctx->prof_pool.push_back(te.second);
+    for (auto &te : ctx->trace_events) ctx->prof_pool.push_back(te.ev);
     ctx->trace_events.clear();
   }
   ctx->trace = enable != 0;
@@ -208,34 +211,38 @@ extern "C" int mb_ctx_trace_read(mb_ctx *ctx, char *buf, size_t cap, size_t *nee
   if (!ctx || !needed) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_trace_read: NULL argument");
   MB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   std::lock_guard<std::mutex> lock(ctx->prof_mu);
-  struct Acc { std::string name; uint64_t n; double ms; };
+  struct Acc { std::string name; uint64_t n; double ms, bytes, blocks, ops; };
   std::vector<Acc> acc;
   for (size_t i = 1; i < ctx->trace_events.size(); i++) {
     const auto &te = ctx->trace_events[i];
-    if (!te.first) continue;
+    if (!te.name) continue;
     float ms = 0.f;
-    MB_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->trace_events[i - 1].second, te.second));
+    MB_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->trace_events[i - 1].ev, te.ev));
     size_t j = 0;
     for (; j < acc.size(); j++)
-      if (acc[j].name == te.first) break;
-    if (j == acc.size()) acc.push_back(Acc{te.first, 0, 0.0});
+      if (acc[j].name == te.name) break;
+    if (j == acc.size()) acc.push_back(Acc{te.name, 0, 0.0, 0.0, 0.0, 0.0});
     acc[j].n++;
     acc[j].ms += ms;
+    acc[j].bytes += te.bytes;
+    acc[j].blocks += te.aes_blocks;
+    acc[j].ops += te.tensor_ops;
   }
   std::string text;
-  char line[256];
+  char line[320];
   for (auto &a : acc) {
-    snprintf(line, sizeof(line), "%s\t%llu\t%.6f\n", a.name.c_str(), (unsigned long long)a.n, a.ms);
+    snprintf(line, sizeof(line), "%s\t%llu\t%.6f\t%.6e\t%.6e\t%.6e\n", a.name.c_str(), (unsigned long long)a.n, a.ms, a.bytes,
+             a.blocks, a.ops);
     text += line;
   }
   *needed = text.size() + 1;
   if (buf && cap >= text.size() + 1) memcpy(buf, text.c_str(), text.size() + 1);
   // keep the last event as the new start marker so consecutive reads partition the stream
   if (!ctx->trace_events.empty()) {
-    for (size_t i = 0; i + 1 < ctx->trace_events.size(); i++) ctx->prof_pool.push_back(ctx->trace_events[i].second);
+    for (size_t i = 0; i + 1 < ctx->trace_events.size(); i++) ctx->prof_pool.push_back(ctx->trace_events[i].ev);
     auto last = ctx->trace_events.back();
     ctx->trace_events.clear();
-    ctx->trace_events.emplace_back(nullptr, last.second);
+    ctx->trace_events.push_back(mb_ctx::TraceRec{nullptr, last.ev, 0, 0, 0});
   }
   return MB_OK;
 }
@@ -249,6 +256,14 @@ extern "C" int mb_host_alloc_pinned(mb_ctx *ctx, size_t nbytes, void **out) {
 extern "C" int mb_host_free_pinned(mb_ctx *ctx, void *ptr) {
   if (ptr) MB_CUDA(ctx, cudaFreeHost(ptr));
   return MB_OK;
+}
+
+int mb_gemm_ctx_register(mb_ctx *ctx) {
+  if (!ctx->gemm_registered) {
+    ctx->gemm_registered = true;
+    g_gemm_ctxs[ctx->device & 63].fetch_add(1);
+  }
+  return g_gemm_ctxs[ctx->device & 63].load();
 }
 
 int mb_scratch(mb_ctx *ctx, int slot, size_t bytes, void **out) {

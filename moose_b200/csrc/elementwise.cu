@@ -305,7 +305,7 @@ int k_ew_binary(mb_ctx *ctx, EwOp op, const mb_tensor *x, const mb_tensor *y, mb
       case EW_OR: LAUNCH_SAME(EW_OR) break;
     }
 #undef LAUNCH_SAME
-    MB_LAUNCH_CHECK(ctx);
+    MB_LAUNCH_CHECK_W(ctx, "ew_binary", 16.0 * nvec * 3, 0, 0);
     return MB_OK;
   }
   BcastDesc d;
@@ -363,7 +363,7 @@ int k_ew_binary3(mb_ctx *ctx, EwOp op, const mb_tensor *const x[3], const mb_ten
     case EW_OR: LAUNCH_SAME3(EW_OR) break;
   }
 #undef LAUNCH_SAME3
-  MB_LAUNCH_CHECK(ctx);
+  MB_LAUNCH_CHECK_W(ctx, "ew_binary3", 16.0 * nvec * 9, 0, 0);
   return MB_OK;
 }
 
@@ -387,7 +387,7 @@ int k_ew_unary3(mb_ctx *ctx, int mode, unsigned amount, const mb_tensor *const x
     unary3_kernel<false, M><<<g, TPB, 0, ctx->stream>>>(p, nvec, s);
   if (mode == 0) { LAUNCH_U3(0) } else if (mode == 1) { LAUNCH_U3(1) } else { LAUNCH_U3(2) }
 #undef LAUNCH_U3
-  MB_LAUNCH_CHECK(ctx);
+  MB_LAUNCH_CHECK_W(ctx, "ew_unary3", 16.0 * nvec * 6, 0, 0);
   return MB_OK;
 }
 
@@ -399,7 +399,7 @@ int k_ew_neg(mb_ctx *ctx, const mb_tensor *x, mb_tensor *out) {
     neg_kernel<true><<<g, TPB, 0, ctx->stream>>>((const ulonglong2 *)x->dptr, (ulonglong2 *)out->dptr, nvec);
   else
     neg_kernel<false><<<g, TPB, 0, ctx->stream>>>((const ulonglong2 *)x->dptr, (ulonglong2 *)out->dptr, nvec);
-  MB_LAUNCH_CHECK(ctx);
+  MB_LAUNCH_CHECK_W(ctx, "ew_neg", 16.0 * nvec * 2, 0, 0);
   return MB_OK;
 }
 

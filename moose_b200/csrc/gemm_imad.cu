@@ -187,7 +187,13 @@ int k_rep_dot_skinny(mb_ctx *ctx, mb_dtype dtype, const RepDotParts &parts, cons
                                                                   (const uint64_t *)ysum[2], (const uint64_t *)y[0], (const uint64_t *)y[1],
                                                                   (const uint64_t *)y[2], (uint64_t *)z[0], (uint64_t *)z[1],
                                                                   (uint64_t *)z[2], M, N);
-  MB_LAUNCH_CHECK(ctx);
+  {
+    const double w = dtype == MB_RING128 ? 16.0 : 8.0;
+    double kt = 0;
+    for (int i = 0; i < parts.n; i++) kt += (double)parts.p[i].K;
+    // every share of the left operand read once, the result written once (the weights stay in L2)
+    MB_LAUNCH_CHECK_W(ctx, "rep_dot_skinny", 3.0 * w * ((double)M * kt + (double)M * N), 0, 0);
+  }
   return MB_OK;
 }
 
@@ -205,7 +211,7 @@ int k_gemm_imad(mb_ctx *ctx, mb_dtype dtype, const void *A, const void *B, void 
       gemm_skinny_kernel<u128, 2><<<g, TPB, 0, ctx->stream>>>((const u128 *)A, (const u128 *)B, (u128 *)C, M, K, N, accumulate);
     else
       gemm_skinny_kernel<uint64_t, 4><<<g, TPB, 0, ctx->stream>>>((const uint64_t *)A, (const uint64_t *)B, (uint64_t *)C, M, K, N, accumulate);
-    MB_LAUNCH_CHECK(ctx);
+    MB_LAUNCH_CHECK_W(ctx, "gemm_skinny", (dtype == MB_RING128 ? 16.0 : 8.0) * ((double)M * K + (double)K * N + (double)M * N), 0, 0);
     return MB_OK;
   }
   dim3 grid((unsigned)((N + BN - 1) / BN), (unsigned)((M + BM - 1) / BM));
@@ -213,6 +219,6 @@ int k_gemm_imad(mb_ctx *ctx, mb_dtype dtype, const void *A, const void *B, void 
     gemm_tiled_kernel<u128><<<grid, TPB, 0, ctx->stream>>>((const u128 *)A, (const u128 *)B, (u128 *)C, M, K, N, accumulate);
   else
     gemm_tiled_kernel<uint64_t><<<grid, TPB, 0, ctx->stream>>>((const uint64_t *)A, (const uint64_t *)B, (uint64_t *)C, M, K, N, accumulate);
-  MB_LAUNCH_CHECK(ctx);
+  MB_LAUNCH_CHECK_W(ctx, "gemm_tiled", (dtype == MB_RING128 ? 16.0 : 8.0) * ((double)M * K + (double)K * N + (double)M * N), 0, 0);
   return MB_OK;
 }

@@ -75,6 +75,7 @@ struct GemmParams {
   int total_items;  // num_passes * nbatch * tiles_m * tiles_n
   unsigned long long *partials;  // [nbatch][num_passes][M][N] u64
   int *round_barrier;  // 2-CTA kernel: one zeroed counter per scheduling round (nullptr = free running)
+  int barrier_rounds;  // number of rounds; slot [barrier_rounds] is the `broken` flag (bounded waits)
 };
 
 // Work item j of CTA c in snake order over the flat list [pass rank][batch][tile].
@@ -531,17 +532,22 @@ limb_gemm_kernel_2cta(const __grid_constant__ CUtensorMap map_a, const __grid_co
           // Round barrier: no cluster starts loading work item `item` before every cluster has reached it.
           // Clusters working on tiles that share operand planes then stay within a few MMA steps of each other,
           // so a tile fetched by one is still in L2 when its neighbours ask for it (free-running clusters drift
-          // apart by more than the L2 holds and re-read the planes from HBM ~50x).  All CTAs of this persistent
-          // grid are co-resident (one per SM), so the spin cannot deadlock; only the TMA threads wait.
+          // apart by more than the L2 holds and re-read the planes from HBM ~50x).  Only the TMA threads wait.
+          // The grid is sized to what cudaOccupancyMaxActiveClusters reports, but nothing GUARANTEES that every
+          // cluster is resident (another context or process may hold SMs), so the wait is bounded: a cluster that
+          // waits longer than a round can plausibly last raises the `broken` flag (slot [rounds]) and from then on
+          // every cluster runs free -- slower through L2, never stuck, and the clusters not yet scheduled get their
+          // SMs when the resident ones finish.
           const int G = (int)(gridDim.x >> 1);
           const long long left = (long long)p.total_items - (long long)item * G;
           const int expect = (int)(left < G ? left : G);
           volatile int *bar = p.round_barrier + item;
+          volatile int *broken = p.round_barrier + p.barrier_rounds;
           if (leader) atomicAdd((int *)bar, 1);
           uint32_t spins = 0;
-          while (*bar < expect) {
+          while (*bar < expect && *broken == 0) {
             __nanosleep(64);
-            if (++spins > (1u << 26)) __trap();
+            if (++spins > (1u << 17)) *broken = 1;   // ~10-20 ms: two orders of magnitude above a round's skew
           }
         }
         const PassDesc pd = p.passes[w.pass];
@@ -825,6 +831,37 @@ bool plan_fits(mb_dtype dtype, int nterms, int64_t K, std::vector<PassDesc> &pas
 
 }  // namespace
 
+// Co-resident 2-CTA clusters of limb_gemm_kernel_2cta on the context's device (cached per device).
+static int max_active_clusters(mb_ctx *ctx, int *out) {
+  static std::mutex mu;
+  static int cached[64];
+  std::lock_guard<std::mutex> lock(mu);
+  int &c = cached[ctx->device & 63];
+  if (c == 0) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)(2 * (ctx->sm_count / 2)), 1, 1);
+    cfg.blockDim = dim3(NUM_THREADS, 1, 1);
+    cfg.dynamicSmemBytes = SMEM2_BYTES;
+    cudaLaunchAttribute attr;
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = 2;
+    attr.val.clusterDim.y = 1;
+    attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = 1;
+    int n = 0;
+    cudaError_t e = cudaOccupancyMaxActiveClusters(&n, (const void *)limb_gemm_kernel_2cta, &cfg);
+    if (e != cudaSuccess || n <= 0) {
+      (void)cudaGetLastError();
+      n = ctx->sm_count / 2;   // the query is advisory; the bounded round barrier keeps an optimistic grid safe
+    }
+    c = std::min(n, ctx->sm_count / 2);
+  }
+  *out = c;
+  return MB_OK;
+}
+
 // Shapes for which the tensor-pipe kernel is the better choice in automatic mode: enough work to fill
 // the 148 SMs with 128 x BLOCK_N tiles and to amortise the limb split / recombine passes.
 bool k_gemm_limb_preferred(int64_t M, int64_t K, int64_t N) {
@@ -850,6 +887,11 @@ int k_gemm_limb_batched(mb_ctx *ctx, mb_dtype dtype, const LimbOperandA *As, int
   const int L = dtype == MB_RING128 ? 16 : 8;
   const int64_t Kp = (K + BLOCK_K - 1) / BLOCK_K * BLOCK_K;
   const int block_n = N >= 256 ? 256 : (N >= 128 ? 128 : 64);
+  // Limb planes and partial sums live in per-context scratch: split -> GEMM -> recombine of one call must reach the
+  // stream as a unit, or two host threads calling mb_dot on one context would overwrite each other's planes
+  // (the reference runs every op as its own task, execution/asynchronous.rs:453-531).
+  std::lock_guard<std::mutex> gemm_lock(ctx->gemm_mu);
+  const bool sole_gemm_ctx = mb_gemm_ctx_register(ctx) == 1;
 
   std::vector<PassDesc> passes;
   std::vector<UnitDesc> units;
@@ -885,7 +927,7 @@ int k_gemm_limb_batched(mb_ctx *ctx, mb_dtype dtype, const LimbOperandA *As, int
       split_a_kernel<u128><<<(unsigned)((quads + 255) / 256), 256, 0, ctx->stream>>>((const u128 *)As[i].ptr, pa, M, K, Kp);
     else
       split_a_kernel<uint64_t><<<(unsigned)((quads + 255) / 256), 256, 0, ctx->stream>>>((const uint64_t *)As[i].ptr, pa, M, K, Kp);
-    MB_LAUNCH_CHECK_AS(ctx, "limb_split");
+    MB_LAUNCH_CHECK_W(ctx, "limb_split", 2.0 * L * M * K, 0, 0);
   }
   for (int i = 0; i < nB; i++) {
     uint8_t *pb = (uint8_t *)dB + (size_t)i * b_plane_bytes;
@@ -893,7 +935,7 @@ int k_gemm_limb_batched(mb_ctx *ctx, mb_dtype dtype, const LimbOperandA *As, int
       split_bt_kernel<u128><<<gb, 256, 0, ctx->stream>>>((const u128 *)Bs[i].b0, (const u128 *)Bs[i].b1, pb, K, N, Kp);
     else
       split_bt_kernel<uint64_t><<<gb, 256, 0, ctx->stream>>>((const uint64_t *)Bs[i].b0, (const uint64_t *)Bs[i].b1, pb, K, N, Kp);
-    MB_LAUNCH_CHECK_AS(ctx, "limb_split");
+    MB_LAUNCH_CHECK_W(ctx, "limb_split", (Bs[i].b1 ? 3.0 : 2.0) * L * N * K, 0, 0);
   }
 
   const bool use_pair = ctx->gemm_pair_mode != 1 && M >= 2 * BLOCK_M && N >= 128;
@@ -929,27 +971,38 @@ int k_gemm_limb_batched(mb_ctx *ctx, mb_dtype dtype, const LimbOperandA *As, int
   gp.total_items = (int)total;
   gp.partials = (unsigned long long *)dP;
 
+  // persistent grid: as many clusters as can be resident at once (per-GPC cluster placement, ~200 KB of shared memory
+  // and all 512 TMEM columns per CTA make that fewer than sm_count / 2 on some parts)
+  int clusters = 0;
+  if (pair) {
+    MB_CUDA(ctx, cudaFuncSetAttribute(limb_gemm_kernel_2cta, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES));
+    MB_CHECK(max_active_clusters(ctx, &clusters));
+    clusters = (int)std::min<int64_t>(total, clusters);
+  }
   gp.round_barrier = nullptr;
-  if (pair && ctx->gemm_round_barrier) {
-    const int clusters = (int)std::min<int64_t>(total, ctx->sm_count / 2);
+  gp.barrier_rounds = 0;
+  // the round barrier only pays (and is only safe to lean on) when this context has the GPU's tensor pipes to itself:
+  // with several contexts running limb GEMMs on one device (the in-process three-party mode) clusters of different
+  // launches hold each other's SMs, so those launches run free
+  if (pair && ctx->gemm_round_barrier && sole_gemm_ctx) {
     const int64_t rounds = (total + clusters - 1) / clusters;
     void *dR;
-    MB_CHECK(mb_scratch(ctx, 3, (size_t)rounds * sizeof(int), &dR));
-    MB_CUDA(ctx, cudaMemsetAsync(dR, 0, (size_t)rounds * sizeof(int), ctx->stream));
+    MB_CHECK(mb_scratch(ctx, 3, (size_t)(rounds + 1) * sizeof(int), &dR));
+    MB_CUDA(ctx, cudaMemsetAsync(dR, 0, (size_t)(rounds + 1) * sizeof(int), ctx->stream));
     gp.round_barrier = (int *)dR;
+    gp.barrier_rounds = (int)rounds;
   }
   cudaEvent_t prof_start;
   MB_CHECK(mb_prof_begin(ctx, &prof_start));
   if (pair) {
-    MB_CUDA(ctx, cudaFuncSetAttribute(limb_gemm_kernel_2cta, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES));
-    const int clusters = (int)std::min<int64_t>(total, ctx->sm_count / 2);
     limb_gemm_kernel_2cta<<<2 * clusters, NUM_THREADS, SMEM2_BYTES, ctx->stream>>>(map_a, map_b, gp);
   } else {
     MB_CUDA(ctx, cudaFuncSetAttribute(limb_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     const int grid = (int)std::min<int64_t>(total, ctx->sm_count);
     limb_gemm_kernel<<<grid, NUM_THREADS, SMEM_BYTES, ctx->stream>>>(map_a, map_b, gp);
   }
-  MB_LAUNCH_CHECK_AS(ctx, "limb_gemm");
+  MB_LAUNCH_CHECK_W(ctx, "limb_gemm", (double)a_bytes + (double)b_bytes + (double)part_bytes, 0,
+                    (double)nbatch * nterms * 2.0 * M * N * Kp * (L * (L + 1) / 2));
   MB_CHECK(mb_prof_end(ctx, prof_start));
 
   RecombineDesc rd;
@@ -962,7 +1015,7 @@ int k_gemm_limb_batched(mb_ctx *ctx, mb_dtype dtype, const LimbOperandA *As, int
       recombine_kernel<u128><<<(unsigned)((MN + 255) / 256), 256, 0, ctx->stream>>>(pp, (u128 *)C[b], MN, rd);
     else
       recombine_kernel<uint64_t><<<(unsigned)((MN + 255) / 256), 256, 0, ctx->stream>>>(pp, (uint64_t *)C[b], MN, rd);
-    MB_LAUNCH_CHECK_AS(ctx, "limb_recombine");
+    MB_LAUNCH_CHECK_W(ctx, "limb_recombine", (double)MN * (8.0 * passes.size() + L), 0, 0);
   }
   return MB_OK;
 }

@@ -219,7 +219,7 @@ int k_rep_share(mb_ctx *ctx, const AesKey &key, int owner, const mb_tensor *x, m
     case VK_RING64: AES_LAUNCH(ctx, share_kernel<VK_RING64>, AES_TPB_LIGHT, nvec, key, CVP(x), VP(prf), VP(diff), VP(zero), nvec, x->numel); break;
     case VK_BIT: AES_LAUNCH(ctx, share_kernel<VK_BIT>, AES_TPB_LIGHT, nvec, key, CVP(x), VP(prf), VP(diff), VP(zero), nvec, x->numel); break;
   }
-  MB_LAUNCH_CHECK(ctx);
+  MB_LAUNCH_CHECK_W(ctx, "share", 16.0 * nvec * 3, nvec, 0);
   return MB_OK;
 }
 
@@ -232,7 +232,7 @@ int k_rep_share_outsider(mb_ctx *ctx, const AesKey &k0, const AesKey &k1, const 
     case VK_RING64: AES_LAUNCH(ctx, share_outsider_kernel<VK_RING64>, AES_TPB_LIGHT, nvec, k0, k1, CVP(x), VP(o0), VP(o1), VP(o2), nvec, x->numel); break;
     case VK_BIT: AES_LAUNCH(ctx, share_outsider_kernel<VK_BIT>, AES_TPB_LIGHT, nvec, k0, k1, CVP(x), VP(o0), VP(o1), VP(o2), nvec, x->numel); break;
   }
-  MB_LAUNCH_CHECK(ctx);
+  MB_LAUNCH_CHECK_W(ctx, "share_outsider", 16.0 * nvec * 4, 2 * nvec, 0);
   return MB_OK;
 }
 
@@ -245,7 +245,7 @@ int k_reveal3(mb_ctx *ctx, const mb_tensor *a, const mb_tensor *b, const mb_tens
     case VK_RING64: reveal_kernel<VK_RING64><<<g, TPB, 0, ctx->stream>>>(CVP(a), CVP(b), CVP(c), VP(out), nvec); break;
     case VK_BIT: reveal_kernel<VK_BIT><<<g, TPB, 0, ctx->stream>>>(CVP(a), CVP(b), CVP(c), VP(out), nvec); break;
   }
-  MB_LAUNCH_CHECK(ctx);
+  MB_LAUNCH_CHECK_W(ctx, "reveal", 16.0 * nvec * 4, 0, 0);
   return MB_OK;
 }
 
@@ -261,7 +261,7 @@ int k_rep_mul(mb_ctx *ctx, const AesKey seeds[3], const mb_rep *x, const mb_rep 
     case VK_BIT: AES_LAUNCH(ctx, rep_mul_kernel<VK_BIT>, AES_TPB_MID, nvec, ARGS); break;
   }
 #undef ARGS
-  MB_LAUNCH_CHECK(ctx);
+  MB_LAUNCH_CHECK_W(ctx, "rep_mul", 16.0 * nvec * 9, 3 * nvec, 0);
   return MB_OK;
 }
 
@@ -276,7 +276,7 @@ int k_add_zero_share(mb_ctx *ctx, const AesKey seeds[3], mb_tensor *v[3], mb_ten
     case VK_BIT: AES_LAUNCH(ctx, add_zero_share_kernel<VK_BIT>, AES_TPB_LIGHT, nvec, ARGS); break;
   }
 #undef ARGS
-  MB_LAUNCH_CHECK(ctx);
+  MB_LAUNCH_CHECK_W(ctx, "add_zero_share", 16.0 * nvec * 6, 3 * nvec, 0);
   return MB_OK;
 }
 
@@ -301,6 +301,6 @@ int k_rep_trunc_pr(mb_ctx *ctx, const AesKey seeds[6], unsigned amount, const mb
   else
     AES_LAUNCH(ctx, trunc_pr_kernel<VK_RING64>, AES_TPB_MID, nvec, ARGS);
 #undef ARGS
-  MB_LAUNCH_CHECK(ctx);
+  MB_LAUNCH_CHECK_W(ctx, "trunc_pr", 16.0 * nvec * 6, 6 * nvec, 0);
   return MB_OK;
 }

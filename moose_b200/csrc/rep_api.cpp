@@ -70,12 +70,10 @@ bool rep_valid(const mb_rep *x) { return x && x->s[0] && x->s[1] && x->s[2]; }
 int ensure_setup(mb_ctx *ctx) {
   // RepSetup: k00, k11, k22 generated in this order (replicated/setup.rs:46-48);
   // k10 = k11, k21 = k22, k02 = k00 are relabelled copies (:50-52).
-  bool need;
-  {
-    std::lock_guard<std::mutex> lock(ctx->mu);
-    need = !ctx->have_setup;
-  }
-  if (need) {
+  // one thread generates the keys; concurrent callers (the reference runs every op as its own task,
+  // execution/asynchronous.rs:453-531) wait for it and then all use the same setup
+  std::lock_guard<std::mutex> setup_lock(ctx->setup_mu);
+  if (!ctx->have_setup) {
     uint8_t k[3][16];
     for (int i = 0; i < 3; i++) MB_CHECK(mb_entropy16(ctx, k[i]));
     std::lock_guard<std::mutex> lock(ctx->mu);

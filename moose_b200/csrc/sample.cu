@@ -14,12 +14,12 @@ constexpr int TPB = AES_TPB_LIGHT;
   } while (0)
 
 template <int K>
-__global__ void __launch_bounds__(TPB) sample_kernel(AesKey key, vec_t *__restrict__ out, int64_t nvec, int64_t numel) {
+__global__ void __launch_bounds__(TPB) sample_kernel(AesKey key, vec_t *__restrict__ out, int64_t nvec, int64_t numel, uint64_t first_block) {
   extern __shared__ __align__(16) uint32_t sT[];
   aes_load_table(sT);
   const AesLane sTl = aes_lane(sT);
   for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
-    vec_t r = prf_vec<K>(sTl, key, (uint64_t)v);
+    vec_t r = prf_vec<K>(sTl, key, first_block + (uint64_t)v);
     if (K == VK_BIT) r = bit_tail_mask(r, v, numel);
     out[v] = r;
   }
@@ -47,7 +47,7 @@ __global__ void __launch_bounds__(TPB) sample_bits_as_ring_kernel(AesKey key, T 
 
 }  // namespace
 
-int k_sample(mb_ctx *ctx, const AesKey &key, mb_tensor *out, bool bits_as_ring) {
+int k_sample(mb_ctx *ctx, const AesKey &key, mb_tensor *out, bool bits_as_ring, uint64_t first_block) {
   if (out->numel == 0) return MB_OK;
   int maxg = ctx->sm_count;  // one CTA per SM (aes.cuh)
   if (bits_as_ring) {
@@ -57,16 +57,16 @@ int k_sample(mb_ctx *ctx, const AesKey &key, mb_tensor *out, bool bits_as_ring) 
       AES_LAUNCH(ctx, sample_bits_as_ring_kernel<u128>, g, key, (u128 *)out->dptr, out->numel);
     else
       AES_LAUNCH(ctx, sample_bits_as_ring_kernel<uint64_t>, g, key, (uint64_t *)out->dptr, out->numel);
-    MB_LAUNCH_CHECK(ctx);
+    MB_LAUNCH_CHECK_W(ctx, "sample_bits_as_ring", (double)out->nbytes, (double)nblocks, 0);
     return MB_OK;
   }
   int64_t nvec = vec_count(out);
   int g = (int)std::min<int64_t>((nvec + TPB - 1) / TPB, maxg);
   switch (vec_kind(out->dtype)) {
-    case VK_RING128: AES_LAUNCH(ctx, sample_kernel<VK_RING128>, g, key, (vec_t *)out->dptr, nvec, out->numel); break;
-    case VK_RING64: AES_LAUNCH(ctx, sample_kernel<VK_RING64>, g, key, (vec_t *)out->dptr, nvec, out->numel); break;
-    case VK_BIT: AES_LAUNCH(ctx, sample_kernel<VK_BIT>, g, key, (vec_t *)out->dptr, nvec, out->numel); break;
+    case VK_RING128: AES_LAUNCH(ctx, sample_kernel<VK_RING128>, g, key, (vec_t *)out->dptr, nvec, out->numel, first_block); break;
+    case VK_RING64: AES_LAUNCH(ctx, sample_kernel<VK_RING64>, g, key, (vec_t *)out->dptr, nvec, out->numel, first_block); break;
+    case VK_BIT: AES_LAUNCH(ctx, sample_kernel<VK_BIT>, g, key, (vec_t *)out->dptr, nvec, out->numel, first_block); break;
   }
-  MB_LAUNCH_CHECK(ctx);
+  MB_LAUNCH_CHECK_W(ctx, "sample", 16.0 * nvec, (double)nvec, 0);
   return MB_OK;
 }

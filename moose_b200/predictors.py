@@ -12,7 +12,7 @@ libmoose_b200).  They follow pymoose/pymoose/predictors/{multilayer_perceptron,l
 
 Operands: x is a Host fixed-point tensor at alice (shared by party 0 inside the first dot,
 fixedpoint/ops.rs:788-812); weights and biases are mirrored fixed-point constants (weights are shared
-from mirrored player 0, mirrored/ops.rs:154-180; biases are added as public values, arith.rs:81-121);
+from mirrored player 0, mirrored/ops.rs:154-180; so are the biases inside AddOp, fixedpoint/ops.rs:30-52);
 the ReLU zeros are a Host tensor at bob (shared by party 1).
 """
 from __future__ import annotations
@@ -27,13 +27,13 @@ from . import FLOAT64, RING64, RING128, RepTensor, Session, Tensor
 class MLPPredictor:
     def __init__(self, sess: Session, weights: Sequence[np.ndarray], biases: Sequence[np.ndarray],
                  ring: int = RING64, frac: int = 23, relu_via: str = "maximum", integral: int = 14,
-                 post_transform: str = "none", bias_via: str = "public", activation: str = "relu"):
+                 post_transform: str = "none", bias_via: str = "share", activation: str = "relu"):
         """post_transform: "none" (MLPRegressor) or "classifier" (MLPClassifier: softmax over the classes, or
         [1 - sigmoid, sigmoid] for one output; needs 2 * (integral + frac) <= ring bits, division.rs:33-38).
         bias_via: "share" is what the logical graph does -- AddOp's replicated kernel on abstract fixed tensors shares a
         mirrored operand from player 0 first (fixedpoint/ops.rs:30-52, mirrored/ops.rs:159-180) -- and "public" adds
         it to share 0 only (the concrete rep + mirrored kernel, arith.rs:81-121): same revealed value, one PRF
-        expansion and two additions fewer.  "public" is the measured default of this round."""
+        expansion and two additions fewer.  "share", the reference's sequence, is the default and what bench.py measures."""
         self.sess, self.ring, self.frac, self.relu_via = sess, ring, frac, relu_via
         self.bias_via = bias_via
         if activation not in ("relu", "sigmoid", "identity"):   # Activation enum, multilayer_perceptron_predictor.py:69-78

@@ -5,7 +5,7 @@ from . import moose_oracle as mo
 
 
 def mlp_forward_shared(sess, x_fixed, w_fixed, b_fixed, frac, relu_via="maximum", integral=14, post_transform="none",
-                       bias_via="public", activation="relu"):
+                       bias_via="share", activation="relu"):
     bits = x_fixed.bits
     x = mo.rep_share(sess, x_fixed, 0)
     n = len(w_fixed)
@@ -39,7 +39,7 @@ def mlp_forward_shared(sess, x_fixed, w_fixed, b_fixed, frac, relu_via="maximum"
     return x
 
 
-def mlp(sess, x, weights, biases, bits=64, frac=23, relu_via="maximum", integral=14, post_transform="none", bias_via="public",
+def mlp(sess, x, weights, biases, bits=64, frac=23, relu_via="maximum", integral=14, post_transform="none", bias_via="share",
         activation="relu"):
     xf = mo.fixed_encode(bits, x, frac)
     wf = [mo.fixed_encode(bits, np.asarray(w, dtype=np.float64), frac) for w in weights]

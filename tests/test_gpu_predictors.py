@@ -50,18 +50,19 @@ def test_mlp_ring64_share_parity(dims, batch, relu_via):
         g.close()
 
 
-def test_mlp_bias_shared_from_the_mirrored_placement():
-    """bias_via="share": the mirrored bias goes through ShareOp at player 0 before the addition, as in the logical
-    graph (fixedpoint/ops.rs:30-52); same values as the public addition, share-level parity with the oracle."""
+def test_mlp_bias_added_as_a_public_value():
+    """bias_via="public": the mirrored bias is added to share 0 only (the concrete rep + mirrored kernel,
+    replicated/arith.rs:81-121) instead of going through ShareOp at player 0 as in the logical graph (the default,
+    fixedpoint/ops.rs:30-52, covered by test_mlp_ring64_share_parity); same values, share-level parity with the oracle."""
     rng = np.random.default_rng(8)
     dims, batch = (32, 16, 16, 4), 24
     ws, bs = make_mlp(rng, dims)
     x = rng.uniform(0, 1, (batch, dims[0]))
     g, o = mb.Session(0, SESSION_ID, ENTROPY_KEY), mo.Session(SESSION_ID, ENTROPY_KEY)
     try:
-        pred = MLPPredictor(g, ws, bs, mb.RING64, 23, "maximum", bias_via="share")
+        pred = MLPPredictor(g, ws, bs, mb.RING64, 23, "maximum", bias_via="public")
         gout = pred.forward_shared(pred.encode(x))
-        oout, odec = po.mlp(o, x, ws, bs, 64, 23, "maximum", bias_via="share")
+        oout, odec = po.mlp(o, x, ws, bs, 64, 23, "maximum", bias_via="public")
         assert same_rep(gout, oout)
         dec = g.fixedpoint_decode(23, g.reveal(gout)).to_host()
         assert np.array_equal(dec, odec)

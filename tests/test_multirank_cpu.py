@@ -101,3 +101,49 @@ def test_party_wire_format_over_gloo():
     assert res[0][0] == bytes(reversed(range(16)))
     for r in (0, 1):  # transport callback: both sides succeed, the receiver sees header and payload, no device sends pending
         assert res[r][1] == 0 and res[r][2] == [1, 0, 0, 0, 0, 0, 0, 0, 0, 16] and res[r][3] == bytes(range(100, 116)) and res[r][4] == 0
+
+
+def _shard_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update({"MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port), "RANK": str(rank),
+                       "WORLD_SIZE": str(world), "LOCAL_RANK": str(rank)})
+    import numpy as np
+    import bench
+    dist = bench.dist_setup(world, rank, backend="gloo")
+    batch, cols = 64, 3
+    lo, hi = bench.shard_rows(batch, world, rank)
+    full = np.arange(batch * cols, dtype=np.float64).reshape(batch, cols)
+    got = bench.gather_rows(dist, full[lo:hi] * 2.0, rank)        # each rank "computes" its rows of ONE batch
+    ms = bench.reduce_max(dist, [20.0 if rank == 0 else 25.0], rank)[0]
+    q.put((rank, (lo, hi), None if got is None else got.tolist(), batch * 4 / (ms * 1e-3)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_world2_batch_sharding_and_output_gather():
+    """one batch split by rows over the ranks (strong scaling), revealed outputs gathered on rank 0
+    in row order, rows/s = whole batch x steps / max-over-ranks time."""
+    import numpy as np
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29511 + os.getpid() % 90
+    procs = [ctx.Process(target=_shard_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = {r[0]: r[1:] for r in (q.get(timeout=120) for _ in range(world))}
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert res[0][0] == (0, 32) and res[1][0] == (32, 64)
+    assert res[1][1] is None
+    assert np.array_equal(np.array(res[0][1]), np.arange(64 * 3, dtype=np.float64).reshape(64, 3) * 2.0)
+    assert res[0][2] == pytest.approx(64 * 4 / 25e-3)
+
+
+def test_shard_rows_rejects_uneven_split():
+    sys.path.insert(0, ROOT)
+    import bench
+    assert bench.shard_rows(1000000, 8, 7) == (875000, 1000000)
+    with pytest.raises(ValueError):
+        bench.shard_rows(10, 4, 0)

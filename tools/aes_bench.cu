@@ -6,14 +6,24 @@
 #ifndef TPB
 #define TPB 256
 #endif
+#ifndef NB
+#define NB 1
+#endif
+// NB independent AES chains in flight per thread (vectors threadIdx + j * TPB of the CTA's chunk): the T-table rounds are
+// dependent shared-memory lookups, so what one thread cannot overlap the other warps of the SM must.
 __global__ void __launch_bounds__(TPB) prf_kernel(AesKey key, uint4 *__restrict__ out, int64_t nvec) {
   extern __shared__ __align__(16) uint32_t sT[];
   aes_load_table(sT);
   const AesLane a = aes_lane(sT);
-  for (int64_t v = (int64_t)blockIdx.x * TPB + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * TPB) {
-    uint32_t o[4];
-    aes_ctr_block(a, key, (uint64_t)v, o);
-    out[v] = make_uint4(o[0], o[1], o[2], o[3]);
+  for (int64_t base = (int64_t)blockIdx.x * TPB * NB; base < nvec; base += (int64_t)gridDim.x * TPB * NB) {
+    uint32_t o[NB][4];
+#pragma unroll
+    for (int j = 0; j < NB; j++) aes_ctr_block(a, key, (uint64_t)(base + threadIdx.x + j * TPB), o[j]);
+#pragma unroll
+    for (int j = 0; j < NB; j++) {
+      const int64_t v = base + threadIdx.x + j * TPB;
+      if (v < nvec) out[v] = make_uint4(o[j][0], o[j][1], o[j][2], o[j][3]);
+    }
   }
 }
 int main(int argc, char **argv) {
@@ -41,7 +51,7 @@ int main(int argc, char **argv) {
   float ms; cudaEventElapsedTime(&ms, e0, e1);
   uint4 h[2];
   cudaMemcpy(h, out, 32, cudaMemcpyDeviceToHost);
-  printf("abs=%d tpb=%d grid=%d: %.2f G blocks/s (%.1f GB/s), first block %08x %08x %08x %08x, err=%s\n", AES_ABS_TABLE, TPB, grid,
+  printf("abs=%d tpb=%d nb=%d grid=%d: %.2f G blocks/s (%.1f GB/s), first block %08x %08x %08x %08x, err=%s\n", AES_ABS_TABLE, TPB, NB, grid,
          5.0 * nvec / ms / 1e6, 5.0 * nvec * 16 / ms / 1e6, h[0].x, h[0].y, h[0].z, h[0].w, cudaGetErrorString(cudaGetLastError()));
   return 0;
 }
