@@ -810,6 +810,34 @@ def run_predictor(env, kind):
     return rec
 
 
+def run_party(env):
+    """BASELINE configs[4]: the MLP with alice / bob / carole on GPUs 0 / 1 / 2 (ranks 0..2 of a job with >= 4 ranks; the
+    other ranks wait), party-sliced fused kernels, reshares and openings stored into the receivers' HBM over NVLink
+    (csrc/peer_transport.cu).  Timed by the host clock around `repeat` full inferences bracketed by barriers: the three
+    streams wait for each other's messages, so no single device clock spans the run."""
+    import argparse as _ap
+    from moose_b200 import party as party_mod
+    args = env.args
+    group = env.dist.new_group([0, 1, 2])           # every rank of the job takes part in creating it
+    rec = None
+    if env.rank < 3:
+        pa = _ap.Namespace(session_id=f"{SESSION_ID}-party", native_nccl=False, peer_memory=True, lanes=1, ring_mib=1024,
+                           dims=list(MLP_DIMS), mlp=args.batch_mlp, repeat=max(args.steps, 1))
+        rec = party_mod.run_fused_mlp(pa, group=group)
+    env.barrier()
+    if env.rank != 0 or rec is None:
+        return None
+    ms = 1e3 * rec["seconds_per_run"]
+    return {"metric": "mlp_inference_rows_per_s", "value": rec["rows_per_s"], "unit": "rows/s", "n_gpus": 3, "ms": ms,
+            "ms_per_step": ms, "rows_per_s": rec["rows_per_s"], "steps": max(args.steps, 1), "warmup": 1,
+            "nvlink_bytes": rec["payload_bytes_per_run"], "transport": rec["transport"],
+            "config": {"workload": rec["workload"], "parties": "alice / bob / carole on GPUs 0 / 1 / 2, one process each"},
+            "max_abs_err_first_rows": rec["max_abs_err_first_rows"],
+            "result_check": "ok" if (rec["max_abs_err_first_rows"] is not None and rec["max_abs_err_first_rows"] < 5e-3) else "MISMATCH",
+            "timing": "host clock around the inferences, barriers on both sides (three dependent streams)",
+            "per_party": rec["per_party"]}
+
+
 def add_cpu_baselines(env, line, records):
     """Rank 0 at N = 1: the port on bounded samples, single-threaded host ops like the reference."""
     args = env.args
@@ -879,7 +907,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="all", choices=["all", "matmul", "mlp", "logreg", "prf"],
+    ap.add_argument("--workload", default="all", choices=["all", "matmul", "mlp", "logreg", "prf", "party"],
                     help="all = matmul (the top-level fields) + mlp + logreg records in one line")
     ap.add_argument("--size", type=int, default=4096, help="matmul M=N=K (default: the BASELINE config, 4096)")
     ap.add_argument("--batch-mlp", type=int, default=65536)
@@ -915,8 +943,15 @@ def main():
             rec = run_predictor(env, kind)
             if rec is not None:
                 records[kind] = rec
+    party = None
+    if env.world >= 4 and args.workload in ("all", "party"):
+        party = run_party(env)
     env.sampler.stop()
     if env.rank == 0:
+        if party is not None and line is not None:
+            line["party_per_gpu"] = party
+        elif party is not None:
+            line = party
         if env.world == 1 and not args.no_cpu_baseline:
             add_cpu_baselines(env, line, records)
         for rec in records.values():

@@ -331,18 +331,21 @@ __global__ void __launch_bounds__(TPB) adder_final_msb_kernel(PlanePtrs g, int64
   }
 }
 
-// RingInjectOp::rep_kernel after the dabit bits b, b0 have been expanded (they are n-bit tensors, 1/64 .. 1/128 of
-// the ring data): per ring vector
+// RingInjectOp::rep_kernel after the dabit bits b have been expanded (an n-bit tensor, 1/64 .. 1/128 of the ring
+// data): per ring vector
 //   c      = open(x + b_bin)                 = x0 ^ x1 ^ x2 ^ b                  (convert.rs:369-371)
 //   br     = ring(b), br0 = PRF(seed_br), br1 = br - br0                         (dabit.rs:50-66)
 //   s      = b_ring + c - 2 b_ring c   (public c lands on share 0)               (convert.rs:374-378)
 //   s    <<= bit_idx                                                             (convert.rs:379)
 //   adt_to_rep: y0 = PRF(seed1), y1 = PRF(seed2), cc = (s0 - y0) + (s1 - y1)     (convert.rs:426-447)
-// Output shares (y0, cc, y1).
+// Output shares (y0, cc, y1).  cc depends on the additive sharing (br0, br1) of the dabit only through
+// s0 + s1 = br xor c (c is a bit) = b xor (x xor b) = x, the shared bit itself: PRF(seed_br) cancels mod 2^k and so
+// does the dealer's bit b.  Neither is expanded (their entropy requests are still consumed, in order): two PRF streams
+// per ring vector, the same shares as the op-by-op protocol bit for bit.
 template <int K>
-__global__ void __launch_bounds__(AES_TPB_LIGHT) ring_inject_fused_kernel(AesKey k_br0, AesKey k_y0, AesKey k_y1,
+__global__ void __launch_bounds__(AES_TPB_LIGHT) ring_inject_fused_kernel(AesKey k_y0, AesKey k_y1,
                                                                const uint32_t *__restrict__ x0, const uint32_t *__restrict__ x1,
-                                                               const uint32_t *__restrict__ x2, const uint32_t *__restrict__ b,
+                                                               const uint32_t *__restrict__ x2,
                                                                vec_t *__restrict__ z0, vec_t *__restrict__ z1,
                                                                vec_t *__restrict__ z2, int64_t nvec, unsigned bit_idx) {
   extern __shared__ __align__(16) uint32_t sT[];
@@ -352,33 +355,19 @@ __global__ void __launch_bounds__(AES_TPB_LIGHT) ring_inject_fused_kernel(AesKey
   constexpr int EPV = K == VK_RING128 ? 1 : 2;  // ring elements per vector
   for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
     const int64_t e = v * EPV;
-    const uint32_t wb = b[e >> 5];
-    const uint32_t wc = x0[e >> 5] ^ x1[e >> 5] ^ x2[e >> 5] ^ wb;
+    const uint32_t ws = x0[e >> 5] ^ x1[e >> 5] ^ x2[e >> 5];   // c ^ b = the shared bit itself
     const unsigned sh = (unsigned)(e & 31);
-    vec_t br, c;
-    if (K == VK_RING128) {
-      br = make_ulonglong2((wb >> sh) & 1u, 0);
-      c = make_ulonglong2((wc >> sh) & 1u, 0);
-    } else {
-      br = make_ulonglong2((wb >> sh) & 1u, (wb >> (sh + 1)) & 1u);
-      c = make_ulonglong2((wc >> sh) & 1u, (wc >> (sh + 1)) & 1u);
-    }
-    const vec_t br0 = prf_vec<K>(L, k_br0, (uint64_t)v);
-    const vec_t br1 = O::sub(br, br0);
-    const vec_t m0 = O::mul01(br0, c), m1 = O::mul01(br1, c);
-    vec_t s0 = O::sub(O::sub(O::add(br0, c), m0), m0);
-    vec_t s1 = O::sub(O::sub(br1, m1), m1);
-    s0 = O::shl(s0, bit_idx);
-    s1 = O::shl(s1, bit_idx);
+    vec_t s;
+    if (K == VK_RING128) s = make_ulonglong2((ws >> sh) & 1u, 0);
+    else s = make_ulonglong2((ws >> sh) & 1u, (ws >> (sh + 1)) & 1u);
+    s = O::shl(s, bit_idx);
     const vec_t y0 = prf_vec<K>(L, k_y0, (uint64_t)v);
     const vec_t y1 = prf_vec<K>(L, k_y1, (uint64_t)v);
     z0[v] = y0;
-    z1[v] = O::add(O::sub(s0, y0), O::sub(s1, y1));
+    z1[v] = O::sub(O::sub(s, y0), y1);
     z2[v] = y1;
   }
 }
-
-
 
 PlanePtrs ptrs_of(mb_tensor *const t[3]) {
   PlanePtrs p;
@@ -537,20 +526,20 @@ int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only,
   return MB_OK;
 }
 
-// x: replicated bit shares (n bits); b: the dealer's dabit bits; out: ring shares (y0, cc, y1).
-int k_ring_inject_fused(mb_ctx *ctx, const AesKey &k_br0, const AesKey &k_y0, const AesKey &k_y1, unsigned bit_idx,
-                        const mb_rep *x, const mb_tensor *b, mb_tensor *out[3]) {
+// x: replicated bit shares (n bits); out: ring shares (y0, cc, y1).
+int k_ring_inject_fused(mb_ctx *ctx, const AesKey &k_y0, const AesKey &k_y1, unsigned bit_idx, const mb_rep *x,
+                        mb_tensor *out[3]) {
   const mb_tensor *t = out[0];
   if (t->numel == 0) return MB_OK;
   const int64_t nvec = vec_count(t);
-#define ARGS k_br0, k_y0, k_y1, (const uint32_t *)x->s[0]->dptr, (const uint32_t *)x->s[1]->dptr, (const uint32_t *)x->s[2]->dptr, \
-             (const uint32_t *)b->dptr, (vec_t *)out[0]->dptr, (vec_t *)out[1]->dptr, (vec_t *)out[2]->dptr, nvec
+#define ARGS k_y0, k_y1, (const uint32_t *)x->s[0]->dptr, (const uint32_t *)x->s[1]->dptr, (const uint32_t *)x->s[2]->dptr, \
+             (vec_t *)out[0]->dptr, (vec_t *)out[1]->dptr, (vec_t *)out[2]->dptr, nvec
   if (t->dtype == MB_RING128)
     AES_LAUNCH(ctx, ring_inject_fused_kernel<VK_RING128>, AES_TPB_LIGHT, nvec, ARGS, bit_idx & 127);
   else
     AES_LAUNCH(ctx, ring_inject_fused_kernel<VK_RING64>, AES_TPB_LIGHT, nvec, ARGS, bit_idx & 63);
 #undef ARGS
-  MB_LAUNCH_CHECK_W(ctx, "ring_inject_fused", 16.0 * nvec * 3 + 4.0 * t->numel / 8, 3.0 * nvec, 0);
+  MB_LAUNCH_CHECK_W(ctx, "ring_inject_fused", 16.0 * nvec * 3 + 4.0 * t->numel / 8, 2.0 * nvec, 0);
   return MB_OK;
 }
 

@@ -211,8 +211,8 @@ int k_party_adder_level(mb_ctx *ctx, const AesKey keys[4], const LevelDesc &d, c
 // Fused arithmetic->boolean conversion (bits_fused.cu)
 bool k_rep_adder_supported(const mb_tensor *x);
 int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only, mb_tensor *out[3]);
-int k_ring_inject_fused(mb_ctx *ctx, const AesKey &k_br0, const AesKey &k_y0, const AesKey &k_y1, unsigned bit_idx,
-                        const mb_rep *x, const mb_tensor *b, mb_tensor *out[3]);
+int k_ring_inject_fused(mb_ctx *ctx, const AesKey &k_y0, const AesKey &k_y1, unsigned bit_idx, const mb_rep *x,
+                        mb_tensor *out[3]);
 
 // Fused replicated kernels (rep.cu)
 int k_rep_share(mb_ctx *ctx, const AesKey &key, int owner, const mb_tensor *x, mb_tensor *o0, mb_tensor *o1,

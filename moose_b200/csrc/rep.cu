@@ -156,45 +156,35 @@ struct TruncParams {
 //       y = c_top - r_top + (overflow << (k-amount)) - 2^(k-amount-1)
 //   adt_to_rep (replicated/convert.rs:426-447,480-484): z0 = PRF(seed_1), z2 = PRF(seed_2),
 //       z1 = open(y - (z0, z2)).
-// Six PRF streams, 3 vectors read, 3 written.
+// With the three parties in one kernel only (z0, z1, z2) leave it, and z1 = y0 + y1 - z0 - z2 depends on the dealer's
+// three additive sharings only through their sums: PRF(seed_a), PRF(seed_b), PRF(seed_c) cancel mod 2^k
+// ((rm0 + c_msb - 2 rm0 c_msb) + (rm1 - 2 rm1 c_msb) = r_msb xor c_msb for a bit c_msb), so those streams are never
+// expanded -- the same values as the op-by-op protocol, bit for bit (tests/test_gpu_replicated.py).
+// Three PRF streams (r, z0, z2), 3 vectors read, 3 written.
 template <int K>
-__global__ void __launch_bounds__(AES_TPB_MID) trunc_pr_kernel(AesKey kr, AesKey ka, AesKey kb, AesKey kc, AesKey k1, AesKey k2,
-                                                       TruncParams p, const vec_t *__restrict__ x0,
-                                                       const vec_t *__restrict__ x1, const vec_t *__restrict__ x2,
-                                                       vec_t *__restrict__ z0, vec_t *__restrict__ z1,
-                                                       vec_t *__restrict__ z2, int64_t nvec) {
+__global__ void __launch_bounds__(AES_TPB_MID) trunc_pr_kernel(AesKey kr, AesKey k1, AesKey k2, TruncParams p,
+                                                       const vec_t *__restrict__ x0, const vec_t *__restrict__ x1,
+                                                       const vec_t *__restrict__ x2, vec_t *__restrict__ z0,
+                                                       vec_t *__restrict__ z1, vec_t *__restrict__ z2, int64_t nvec) {
   PRF_PROLOGUE();
   typedef VOps<K> O;
   const vec_t up = O::splat(p.up_lo, p.up_hi);
   const vec_t down = O::splat(p.down_lo, p.down_hi);
   VEC_LOOP(v, nvec) {
-    vec_t a0 = O::add(x0[v], x1[v]);
-    vec_t a1 = x2[v];
-    vec_t r = prf_vec<K>(sTl, kr, (uint64_t)v);
-    vec_t r0 = prf_vec<K>(sTl, ka, (uint64_t)v);
-    vec_t rt0 = prf_vec<K>(sTl, kb, (uint64_t)v);
-    vec_t rm0 = prf_vec<K>(sTl, kc, (uint64_t)v);
-    vec_t r_msb = O::shr(r, p.sh_msb);
-    vec_t r_top = O::shr(O::shl(r, 1), p.sh_top);
-    vec_t r1 = O::sub(r, r0);
-    vec_t rt1 = O::sub(r_top, rt0);
-    vec_t rm1 = O::sub(r_msb, rm0);
+    const vec_t a = O::add(O::add(x0[v], x1[v]), x2[v]);
+    const vec_t r = prf_vec<K>(sTl, kr, (uint64_t)v);
+    const vec_t w0 = prf_vec<K>(sTl, k1, (uint64_t)v);
+    const vec_t w2 = prf_vec<K>(sTl, k2, (uint64_t)v);
+    const vec_t r_msb = O::shr(r, p.sh_msb);
+    const vec_t r_top = O::shr(O::shl(r, 1), p.sh_top);
     // c = reveal(x_positive + r)
-    vec_t c = O::add(O::add(O::add(a0, up), r0), O::add(a1, r1));
-    vec_t c_top = O::shr(O::shl(c, 1), p.sh_top);
-    vec_t c_msb = O::shr(c, p.sh_msb);
-    // overflow shares: [rm0 + c_msb - 2 rm0 c_msb, rm1 - 2 rm1 c_msb]
-    vec_t m0 = O::mul01(rm0, c_msb);
-    vec_t m1 = O::mul01(rm1, c_msb);
-    vec_t ov0 = O::sub(O::sub(O::add(rm0, c_msb), m0), m0);
-    vec_t ov1 = O::sub(O::sub(rm1, m1), m1);
-    vec_t y0 = O::sub(O::add(O::sub(c_top, rt0), O::shl(ov0, p.sh_ov)), down);
-    vec_t y1 = O::add(O::neg(rt1), O::shl(ov1, p.sh_ov));
-    vec_t w0 = prf_vec<K>(sTl, k1, (uint64_t)v);
-    vec_t w2 = prf_vec<K>(sTl, k2, (uint64_t)v);
-    vec_t cc = O::add(O::sub(y0, w0), O::sub(y1, w2));
+    const vec_t c = O::add(O::add(a, up), r);
+    const vec_t c_top = O::shr(O::shl(c, 1), p.sh_top);
+    const vec_t c_msb = O::shr(c, p.sh_msb);
+    const vec_t ov = make_ulonglong2(r_msb.x ^ c_msb.x, r_msb.y ^ c_msb.y);   // both are 0 / 1 per element
+    const vec_t y = O::sub(O::add(O::sub(c_top, r_top), O::shl(ov, p.sh_ov)), down);
     z0[v] = w0;
-    z1[v] = cc;
+    z1[v] = O::sub(O::sub(y, w0), w2);
     z2[v] = w2;
   }
 }
@@ -294,13 +284,13 @@ int k_rep_trunc_pr(mb_ctx *ctx, const AesKey seeds[6], unsigned amount, const mb
   p.up_lo = (uint64_t)up; p.up_hi = (uint64_t)(up >> 64);
   p.down_lo = (uint64_t)down; p.down_hi = (uint64_t)(down >> 64);
   int64_t nvec = vec_count(t);
-#define ARGS seeds[0], seeds[1], seeds[2], seeds[3], seeds[4], seeds[5], p, CVP(x->s[0]), CVP(x->s[1]), CVP(x->s[2]), \
-             VP(z[0]), VP(z[1]), VP(z[2]), nvec
+  // seeds[1..3] (the dealer's additive sharings of r, r_top, r_msb) cancel in the outputs: see trunc_pr_kernel
+#define ARGS seeds[0], seeds[4], seeds[5], p, CVP(x->s[0]), CVP(x->s[1]), CVP(x->s[2]), VP(z[0]), VP(z[1]), VP(z[2]), nvec
   if (t->dtype == MB_RING128)
     AES_LAUNCH(ctx, trunc_pr_kernel<VK_RING128>, AES_TPB_MID, nvec, ARGS);
   else
     AES_LAUNCH(ctx, trunc_pr_kernel<VK_RING64>, AES_TPB_MID, nvec, ARGS);
 #undef ARGS
-  MB_LAUNCH_CHECK_W(ctx, "trunc_pr", 16.0 * nvec * 6, 6 * nvec, 0);
+  MB_LAUNCH_CHECK_W(ctx, "trunc_pr", 16.0 * nvec * 6, 3 * nvec, 0);
   return MB_OK;
 }

@@ -638,8 +638,9 @@ extern "C" int mb_rep_ring_inject(mb_ctx *ctx, mb_dtype ring, uint64_t bit_idx, 
   const mb_tensor *like = x->s[0];
   if (ctx->fused_bits) {
     // Entropy order: gen_dabit (dabit.rs:49-55): Sample seed, PrfKeyGen, 2 x SyncKey; adt_to_rep
-    // (convert.rs:426-431): 2 x SyncKey, PrfKeyGen.  The additive share b0 of the dabit bit cancels in the
-    // opened value c = x ^ b, so its stream (seed_b) is never expanded.
+    // (convert.rs:426-431): 2 x SyncKey, PrfKeyGen.  The dealer's bit b and both of its additive sharings cancel in
+    // the result (the opened value is x ^ b and b_ring + c - 2 b_ring c = b ^ c = x), so none of their streams is
+    // expanded; their entropy requests are consumed so that everything after this call sees the reference's order.
     uint8_t seed_bits[16], key[16], sync_b[16], sync_br[16], sync0[16], sync1[16], key2[16];
     MB_CHECK(mb_entropy16(ctx, seed_bits));
     MB_CHECK(mb_entropy16(ctx, key));
@@ -648,17 +649,12 @@ extern "C" int mb_rep_ring_inject(mb_ctx *ctx, mb_dtype ring, uint64_t bit_idx, 
     MB_CHECK(mb_entropy16(ctx, sync0));
     MB_CHECK(mb_entropy16(ctx, sync1));
     MB_CHECK(mb_entropy16(ctx, key2));
-    AesKey kb, k_br0, k_y0, k_y1;
-    mb_aes_expand(seed_bits, &kb);
-    seed_to_aes(ctx, sync_br, key, &k_br0);
+    AesKey k_y0, k_y1;
     seed_to_aes(ctx, sync0, key2, &k_y0);
     seed_to_aes(ctx, sync1, key2, &k_y1);
-    Tmp b(ctx);
-    MB_CHECK(b.alloc_like(like));
-    MB_CHECK(k_sample(ctx, kb, b.p, false));
     RepTmp z(ctx);
     MB_CHECK(rep_alloc(ctx, ring, like->rank, like->shape, &z.p));
-    MB_CHECK(k_ring_inject_fused(ctx, k_br0, k_y0, k_y1, (unsigned)bit_idx, x, b.p, z.p->s));
+    MB_CHECK(k_ring_inject_fused(ctx, k_y0, k_y1, (unsigned)bit_idx, x, z.p->s));
     *out = z.release();
     return MB_OK;
   }

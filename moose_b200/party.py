@@ -26,29 +26,34 @@ def roles_of(ops):
     return roles
 
 
-def run_fused_mlp(args):
-    """BASELINE config 5 on the party runtime: alice / bob / carole on three GPUs, reshares and openings over NCCL."""
+def run_fused_mlp(args, group=None):
+    """BASELINE config 5 on the party runtime: alice / bob / carole on three GPUs, reshares and openings over NCCL or
+    the peer-memory rings.  Stand-alone (torchrun with 3 ranks: initialises and destroys the process group, prints the
+    record) or, with `group` = a 3-rank subgroup of an initialised job (bench.py --gpus N >= 4 runs the parties on ranks
+    0..2), returns the record on the group's first rank."""
     import torch
     import torch.distributed as dist
     import moose_b200 as mb
     from moose_b200.executor import NcclComm
     from moose_b200.party_rt import PartyMLP, PartySession
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != 3:
-        raise SystemExit("the party runtime needs exactly 3 ranks")
+    own_group = group is None
+    if own_group:
+        if int(os.environ.get("WORLD_SIZE", "1")) != 3:
+            raise SystemExit("the party runtime needs exactly 3 ranks")
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    rank, world = dist.get_rank(group), 3
+    src0 = dist.get_global_rank(group, 0) if group is not None else 0
     roles = ["player0", "player1", "player2"]
-    torch.cuda.set_device(local_rank)
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     sess = mb.Session(local_rank, args.session_id, None)
     native = None
     lanes = []          # --lanes K: K independent party sessions (own stream, own rings) working on B / K rows each
     if args.native_nccl:
         from moose_b200.party_rt import NativeNccl
         box = [NativeNccl.unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(box, src=0)          # bootstrap only: the unique id
+        dist.broadcast_object_list(box, src=src0, group=group)          # bootstrap only: the unique id
         native = NativeNccl(sess, box[0], rank, roles)
         party = PartySession(sess, rank, native, roles)
     elif args.peer_memory:
@@ -57,10 +62,10 @@ def run_fused_mlp(args):
             ls = sess if lane == 0 else mb.Session(local_rank, args.session_id, None)
             pm = PeerMemory(ls, rank, roles, args.ring_mib << 20)
             handles = [None] * world
-            dist.all_gather_object(handles, pm.handle_bytes())   # bootstrap only: the inbox handles
+            dist.all_gather_object(handles, pm.handle_bytes(), group=group)   # bootstrap only: the inbox handles
             pm.connect(handles)
             lanes.append((ls, pm, PartySession(ls, rank, pm, roles)))
-        dist.barrier()
+        dist.barrier(group=group)
         native, party = lanes[0][1], lanes[0][2]
     else:
         comm = NcclComm(dist, sess, {r: i for i, r in enumerate(roles)}, local_rank)
@@ -85,19 +90,19 @@ def run_fused_mlp(args):
             ls.sync()
         return outs
 
-    dist.barrier()
+    dist.barrier(group=group)
     outs = run_once()          # untimed: connections, scratch growth
     sent0 = sum(pt.bytes_sent for _, _, pt in lanes)
     st0 = party.stats()
-    dist.barrier()
+    dist.barrier(group=group)
     t0 = time.perf_counter()
     for _ in range(args.repeat):
         outs = run_once()
     dt = (time.perf_counter() - t0) / args.repeat
-    dist.barrier()
+    dist.barrier(group=group)
     out = outs[0]
     sent = torch.tensor([sum(pt.bytes_sent for _, _, pt in lanes) - sent0], dtype=torch.int64, device=f"cuda:{local_rank}")
-    dist.all_reduce(sent)
+    dist.all_reduce(sent, group=group)
     err = None
     if out is not None:
         h = x[:8]
@@ -109,26 +114,31 @@ def run_fused_mlp(args):
     st1 = party.stats()
     mine = {k: (st1[k] - st0[k]) / args.repeat for k in st1}
     gathered = [None] * world
-    dist.all_gather_object(gathered, mine)
+    dist.all_gather_object(gathered, mine, group=group)
+    record = None
     if rank == 0:
-        print(json.dumps({"mode": "party-per-gpu (party runtime, fused party-sliced kernels)", "parties": roles,
+        record = ({"mode": "party-per-gpu (party runtime, fused party-sliced kernels)", "parties": roles,
                           "per_party": gathered,
                           "transport": ("peer-memory rings over NVLink, stream-ordered (csrc/peer_transport.cu)" if args.peer_memory
                                         else "ncclSend/ncclRecv from C++ (native)" if native
                                         else "nccl send/recv (torch.distributed)"),
                           "workload": "mlp_" + "-".join(map(str, dims)) + f"_relu_ring64_fixed(14,23)_batch{B}",
                           "lanes": len(lanes), "rows_per_s": B / dt, "seconds_per_run": dt, "payload_bytes_per_run": int(sent[0]) // args.repeat,
-                          "max_abs_err_first_rows": err}), flush=True)
+                          "max_abs_err_first_rows": err})
+        if own_group:
+            print(json.dumps(record), flush=True)
     for _, _, pt in lanes:
         pt.close()
-    dist.barrier()          # nobody writes into an inbox that is about to be freed
+    dist.barrier(group=group)          # nobody writes into an inbox that is about to be freed
     for ls, tr, _ in lanes:
         if tr is not None:
             tr.close()
         if ls is not sess:
             ls.close()
     sess.close()
-    dist.destroy_process_group()
+    if own_group:
+        dist.destroy_process_group()
+    return record
 
 
 def main():
