@@ -110,10 +110,11 @@ def _shard_worker(rank, world, port, q):
     import numpy as np
     import bench
     dist = bench.dist_setup(world, rank, backend="gloo")
-    batch, cols = 64, 3
-    lo, hi = bench.shard_rows(batch, world, rank)
+    batch, cols = 72, 3           # 9 blocks of 8 rows over 2 ranks: unequal slices (40 / 32 rows)
+    lo, hi = bench.shard_rows(batch, world, rank, granule=8)
     full = np.arange(batch * cols, dtype=np.float64).reshape(batch, cols)
-    got = bench.gather_rows(dist, full[lo:hi] * 2.0, rank)        # each rank "computes" its rows of ONE batch
+    rows_of = [b - a for a, b in (bench.shard_rows(batch, world, g, granule=8) for g in range(world))]
+    got = bench.gather_rows(dist, full[lo:hi] * 2.0, rank, rows_of)        # each rank "computes" its rows of ONE batch
     ms = bench.reduce_max(dist, [20.0 if rank == 0 else 25.0], rank)[0]
     q.put((rank, (lo, hi), None if got is None else got.tolist(), batch * 4 / (ms * 1e-3)))
     dist.barrier()
@@ -135,15 +136,17 @@ def test_world2_batch_sharding_and_output_gather():
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
-    assert res[0][0] == (0, 32) and res[1][0] == (32, 64)
+    assert res[0][0] == (0, 40) and res[1][0] == (40, 72)
     assert res[1][1] is None
-    assert np.array_equal(np.array(res[0][1]), np.arange(64 * 3, dtype=np.float64).reshape(64, 3) * 2.0)
-    assert res[0][2] == pytest.approx(64 * 4 / 25e-3)
+    assert np.array_equal(np.array(res[0][1]), np.arange(72 * 3, dtype=np.float64).reshape(72, 3) * 2.0)
+    assert res[0][2] == pytest.approx(72 * 4 / 25e-3)
 
 
-def test_shard_rows_rejects_uneven_split():
+def test_shard_rows_granule():
     sys.path.insert(0, ROOT)
     import bench
-    assert bench.shard_rows(1000000, 8, 7) == (875000, 1000000)
-    with pytest.raises(ValueError):
-        bench.shard_rows(10, 4, 0)
+    rows = [bench.shard_rows(1000000, 8, g) for g in range(8)]
+    assert rows[0] == (0, 125056) and rows[-1][1] == 1000000
+    assert all(a[1] == b[0] for a, b in zip(rows, rows[1:]))                    # contiguous, in rank order
+    assert all((hi - lo) % 64 == 0 and abs((hi - lo) - 125000) <= 64 for lo, hi in rows)
+    assert [bench.shard_rows(100, 4, g, granule=64) for g in range(4)] == [(0, 64), (64, 100), (100, 100), (100, 100)]
