@@ -17,7 +17,7 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "_obj")
 LIB = os.path.join(HERE, "libmoose_b200.so")
 SOURCES = ["core.cpp", "hostcrypto.cpp", "api.cpp", "rep_api.cpp", "rep_math.cpp", "rep_shape.cpp", "executor.cpp", "party.cpp", "nccl_transport.cpp", "peer_transport.cu", "party_fused.cu", "elementwise.cu", "sample.cu",
-           "rep.cu", "bits.cu", "bits_fused.cu", "host_misc.cu", "shape_ops.cu", "storage.cu", "gemm_imad.cu", "gemm_limb.cu"]
+           "rep.cu", "bits.cu", "bits_fused.cu", "math_fused.cu", "host_misc.cu", "shape_ops.cu", "storage.cu", "gemm_imad.cu", "gemm_limb.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
          "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function", "-x", "cu"]

@@ -214,6 +214,37 @@ int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only,
 int k_ring_inject_fused(mb_ctx *ctx, const AesKey &k_y0, const AesKey &k_y1, unsigned bit_idx, const mb_rep *x,
                         mb_tensor *out[3]);
 
+// Batched kernels of the fixed-point math protocols (math_fused.cu); descriptors travel as kernel parameters
+constexpr int MB_PREFIX_MAX_OPS = 32;
+struct PrefixLevel {             // one level of prefix_op on bit planes: W[dst] = OR(W[src], W[dst])
+  int nops;
+  short src[MB_PREFIX_MAX_OPS], dst[MB_PREFIX_MAX_OPS];
+  AesKey keys[MB_PREFIX_MAX_OPS][3];   // zero-share seeds of the AND inside each OR
+};
+constexpr int MB_INJECT_MAX_PLANES = 64;
+struct InjectSumDesc {           // out = base + (negate ? -1 : 1) * sum_i mult_i * (ring_inject(plane pa_i ^ plane pb_i) << shift_i)
+  int nplanes, negate;
+  short pa[MB_INJECT_MAX_PLANES], pb[MB_INJECT_MAX_PLANES];   // pb < 0: no second plane
+  unsigned char shift[MB_INJECT_MAX_PLANES], mult[MB_INJECT_MAX_PLANES];
+  AesKey keys[MB_INJECT_MAX_PLANES][2];  // adt_to_rep seeds (y0, y1) of each ring_inject
+};
+constexpr int MB_POW2_MAX_BITS = 32;
+struct Pow2Desc {                // Pow2FromBits over planes first_plane .. first_plane + count - 1
+  int count, first_plane;
+  unsigned char part_shift[MB_POW2_MAX_BITS], sel_shift[MB_POW2_MAX_BITS];
+  AesKey inject[MB_POW2_MAX_BITS][2];
+  AesKey zero[MB_POW2_MAX_BITS][3];
+};
+int k_planes_gather(mb_ctx *ctx, const mb_tensor *const src[3], const short *idx, int nplanes, mb_tensor *const W[3], int64_t n);
+int k_prefix_or_level(mb_ctx *ctx, const PrefixLevel &lv, mb_tensor *const W[3], int64_t n);
+int k_inject_sum(mb_ctx *ctx, const InjectSumDesc &d, const mb_tensor *const W[3], int64_t n, const mb_rep *base, mb_tensor *const out[3]);
+int k_pow2_bits(mb_ctx *ctx, const Pow2Desc &d, const mb_tensor *const W[3], int64_t n, const mb_rep *x_abs, mb_tensor *const out_d[3],
+                mb_tensor *const out_rest[3]);
+// key derivation in the reference's entropy order, shared by the per-op entry points and the batched paths (rep_api.cpp)
+int mb_draw_zero_seeds(mb_ctx *ctx, AesKey seeds[3]);      // gen_zero_share: 3 x SyncKey (after the one-time setup)
+int mb_draw_inject_keys(mb_ctx *ctx, AesKey keys[2]);      // ring_inject: dabit (4 requests) + adt_to_rep (3): returns (y0, y1)
+int mb_draw_trunc_keys(mb_ctx *ctx, AesKey keys[3]);       // trunc_pr: mask (5 requests) + adt_to_rep (3): returns (r, y0, y1)
+
 // Fused replicated kernels (rep.cu)
 int k_rep_share(mb_ctx *ctx, const AesKey &key, int owner, const mb_tensor *x, mb_tensor *o0, mb_tensor *o1,
                 mb_tensor *o2);

@@ -1,0 +1,264 @@
+// Batched kernels for the replicated fixed-point math protocols: what the reference runs as
+// hundreds of tiny replicated ops per call -- and round 1 launched one by one -- in a handful of launches.
+//
+//   prefix_or_level_kernel   one level of prefix_op (replicated/misc.rs:5-40) over bit planes: up to 32 independent
+//                            OR(a, b) = a ^ b ^ AND(a, b), each AND a replicated multiplication over Z2 with its own
+//                            zero share (replicated/arith.rs:317-367, zero_share.rs:82-156)
+//   inject_sum_kernel        sum_i m_i * (ring_inject(z_i) << s_i) over up to 64 bit planes (top_most_index,
+//                            replicated/division.rs:176-205; the higher bits of Pow2, replicated/exp.rs:50-70): every plane
+//                            goes through RingInjectOp::rep_kernel with its own dabit and adt_to_rep seeds
+//                            (replicated/convert.rs:316-390); shifts and sums are local, so only the sum is written
+//   pow2_bits_kernel         Pow2FromBits (replicated/exp.rs:124-157): the first integral-precision higher bits are
+//                            injected, turned into selectors and multiplied up in registers (a chain of replicated
+//                            multiplications, one zero share each)
+//
+// Every PRF stream is the stream the op-by-op protocol uses for the same value (the host draws the keys in the
+// reference's op order, csrc/rep_math.cpp), every value is computed with the same arithmetic mod 2^k, so the shares
+// are identical bit for bit (tests/test_gpu_math.py).  Keys travel as kernel parameters (up to 25 KB).
+#include "vecops.cuh"
+
+namespace {
+
+#define AES_LAUNCH(ctx, kern, tpb, items, ...)                                                                  \
+  do {                                                                                                          \
+    MB_CUDA((ctx), cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, AES_SMEM_BYTES));    \
+    kern<<<aes_grid((ctx), (items), (tpb)), (tpb), AES_SMEM_BYTES, (ctx)->stream>>>(__VA_ARGS__);               \
+  } while (0)
+
+inline int aes_grid(mb_ctx *ctx, int64_t items, int tpb) {
+  return (int)std::max<int64_t>(1, std::min<int64_t>((items + tpb - 1) / tpb, (int64_t)ctx->sm_count));
+}
+
+__device__ __forceinline__ vec_t vx(vec_t a, vec_t b) { return make_ulonglong2(a.x ^ b.x, a.y ^ b.y); }
+__device__ __forceinline__ vec_t va(vec_t a, vec_t b) { return make_ulonglong2(a.x & b.x, a.y & b.y); }
+
+struct Planes3 {
+  vec_t *s[3];
+};
+
+// W[dst] = OR(W[src], W[dst]) for the ops of one prefix level.  Ops of a level touch disjoint destinations and never
+// read a plane another op of the level writes (misc.rs:14-24), so they run concurrently; a CTA walks (op, vector)
+// items with the op index uniform per iteration block.
+__global__ void __launch_bounds__(AES_TPB_MID) prefix_or_level_kernel(const __grid_constant__ PrefixLevel lv, Planes3 W, int64_t nv) {
+  extern __shared__ __align__(16) uint32_t sT[];
+  aes_load_table(sT);
+  const AesLane L = aes_lane(sT);
+  const int64_t total = (int64_t)lv.nops * nv;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int op = (int)(t / nv);
+    const int64_t v = t - (int64_t)op * nv;
+    const int64_t ia = (int64_t)lv.src[op] * nv + v, ib = (int64_t)lv.dst[op] * nv + v;
+    const vec_t a0 = W.s[0][ia], a1 = W.s[1][ia], a2 = W.s[2][ia];
+    const vec_t b0 = W.s[0][ib], b1 = W.s[1][ib], b2 = W.s[2][ib];
+    const vec_t r0 = prf_vec<VK_BIT>(L, lv.keys[op][0], (uint64_t)v);
+    const vec_t r1 = prf_vec<VK_BIT>(L, lv.keys[op][1], (uint64_t)v);
+    const vec_t r2 = prf_vec<VK_BIT>(L, lv.keys[op][2], (uint64_t)v);
+    // AND: z_i = a_i b_i ^ a_i b_{i+1} ^ a_{i+1} b_i ^ r_i ^ r_{i+1};  OR = (a ^ b) ^ AND (share-wise)
+    const vec_t z0 = vx(vx(va(a0, vx(b0, b1)), va(a1, b0)), vx(r0, r1));
+    const vec_t z1 = vx(vx(va(a1, vx(b1, b2)), va(a2, b1)), vx(r1, r2));
+    const vec_t z2 = vx(vx(va(a2, vx(b2, b0)), va(a0, b2)), vx(r2, r0));
+    W.s[0][ib] = vx(vx(a0, b0), z0);
+    W.s[1][ib] = vx(vx(a1, b1), z1);
+    W.s[2][ib] = vx(vx(a2, b2), z2);
+  }
+}
+
+// W[i] = plane idx[i] of the [k, n] bit tensors `src` (n % 128 == 0: planes are whole vectors).
+struct GatherDesc {
+  int nplanes;
+  short idx[128];
+};
+__global__ void planes_gather_kernel(const __grid_constant__ GatherDesc d, Planes3 src, Planes3 W, int64_t nv) {
+  const int64_t total = (int64_t)d.nplanes * nv;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int p = (int)(t / nv);
+    const int64_t v = t - (int64_t)p * nv;
+#pragma unroll
+    for (int i = 0; i < 3; i++) W.s[i][t] = src.s[i][(int64_t)d.idx[p] * nv + v];
+  }
+}
+
+struct Bits3 {
+  const uint32_t *s[3];
+};
+struct Ring3 {
+  vec_t *s[3];
+};
+struct CRing3 {
+  const vec_t *s[3];
+};
+
+// The shared bit of element e in plane p (the XOR of the three shares: the value ring_inject opens and re-shares).
+__device__ __forceinline__ uint32_t plane_word(const Bits3 &W, int p, int64_t n, int64_t e) {
+  const int64_t w = ((int64_t)p * n + e) >> 5;
+  return W.s[0][w] ^ W.s[1][w] ^ W.s[2][w];
+}
+
+// out = base + sign * sum_i mult_i * (inject(z_i) << shift_i),  z_i = plane pa_i ^ plane pb_i (pb_i < 0: none).
+// inject(z) = (y0, z - y0 - y1, y1) with y0, y1 the adt_to_rep streams of that call (bits_fused.cu,
+// ring_inject_fused_kernel).
+template <int K>
+__global__ void __launch_bounds__(AES_TPB_MID) inject_sum_kernel(const __grid_constant__ InjectSumDesc d, Bits3 W, int64_t n,
+                                                                 CRing3 base, Ring3 out, int64_t nvec) {
+  extern __shared__ __align__(16) uint32_t sT[];
+  aes_load_table(sT);
+  const AesLane L = aes_lane(sT);
+  typedef VOps<K> O;
+  constexpr int EPV = K == VK_RING128 ? 1 : 2;
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t e = v * EPV;
+    const unsigned sh = (unsigned)(e & 31);
+    vec_t acc0 = O::zero(), acc1 = O::zero(), acc2 = O::zero();
+    for (int i = 0; i < d.nplanes; i++) {
+      if (d.mult[i] == 0) continue;   // the value is never used (its keys were still drawn, in order)
+      uint32_t w = plane_word(W, d.pa[i], n, e);
+      if (d.pb[i] >= 0) w ^= plane_word(W, d.pb[i], n, e);
+      vec_t s;
+      if (K == VK_RING128) s = make_ulonglong2((w >> sh) & 1u, 0);
+      else s = make_ulonglong2((w >> sh) & 1u, (w >> (sh + 1)) & 1u);
+      const vec_t y0 = prf_vec<K>(L, d.keys[i][0], (uint64_t)v);
+      const vec_t y1 = prf_vec<K>(L, d.keys[i][1], (uint64_t)v);
+      const vec_t c = O::sub(O::sub(s, y0), y1);
+      for (int m = 0; m < d.mult[i]; m++) {
+        acc0 = O::add(acc0, O::shl(y0, d.shift[i]));
+        acc1 = O::add(acc1, O::shl(c, d.shift[i]));
+        acc2 = O::add(acc2, O::shl(y1, d.shift[i]));
+      }
+    }
+    if (d.negate) {
+      acc0 = O::neg(acc0);
+      acc1 = O::neg(acc1);
+      acc2 = O::neg(acc2);
+    }
+    if (base.s[0]) {
+      acc0 = O::add(base.s[0][v], acc0);
+      acc1 = O::add(base.s[1][v], acc1);
+      acc2 = O::add(base.s[2][v], acc2);
+    }
+    out.s[0][v] = acc0;
+    out.s[1][v] = acc1;
+    out.s[2][v] = acc2;
+  }
+}
+
+// Pow2 (replicated/exp.rs:50-80, 124-157) on the first `count` higher bits of |x| (planes first_plane .. of `W`):
+//   hb_i  = ring_inject(plane_i)                                  (keys.inject[i])
+//   part  = sum_i hb_i << (f + i)                                 (the integral part collected so far)
+//   sel_i = (hb_i << (2^i mod width)) + (ones - hb_i),  ones = (1, 0, 0)
+//   d     = ones * sel_0 * sel_1 * ... (replicated multiplications, zero share keys.zero[i])
+// Outputs: d and rest = x_abs - part.
+template <int K>
+__global__ void __launch_bounds__(AES_TPB_384) pow2_bits_kernel(const __grid_constant__ Pow2Desc d, Bits3 W, int64_t n, CRing3 x_abs,
+                                                                Ring3 out_d, Ring3 out_rest, int64_t nvec) {
+  extern __shared__ __align__(16) uint32_t sT[];
+  aes_load_table(sT);
+  const AesLane L = aes_lane(sT);
+  typedef VOps<K> O;
+  constexpr int EPV = K == VK_RING128 ? 1 : 2;
+  const vec_t one = O::splat(1, 0);
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t e = v * EPV;
+    const unsigned sh = (unsigned)(e & 31);
+    vec_t p0 = O::zero(), p1 = O::zero(), p2 = O::zero();      // part
+    vec_t a0 = one, a1 = O::zero(), a2 = O::zero();            // running product, starts as ones = (1, 0, 0)
+    for (int i = 0; i < d.count; i++) {
+      const uint32_t w = plane_word(W, d.first_plane + i, n, e);
+      vec_t s;
+      if (K == VK_RING128) s = make_ulonglong2((w >> sh) & 1u, 0);
+      else s = make_ulonglong2((w >> sh) & 1u, (w >> (sh + 1)) & 1u);
+      const vec_t h0 = prf_vec<K>(L, d.inject[i][0], (uint64_t)v);
+      const vec_t h2 = prf_vec<K>(L, d.inject[i][1], (uint64_t)v);
+      const vec_t h1 = O::sub(O::sub(s, h0), h2);
+      p0 = O::add(p0, O::shl(h0, d.part_shift[i]));
+      p1 = O::add(p1, O::shl(h1, d.part_shift[i]));
+      p2 = O::add(p2, O::shl(h2, d.part_shift[i]));
+      // selector: pos + (ones - hb)
+      const vec_t b0 = O::add(O::shl(h0, d.sel_shift[i]), O::sub(one, h0));
+      const vec_t b1 = O::add(O::shl(h1, d.sel_shift[i]), O::neg(h1));
+      const vec_t b2 = O::add(O::shl(h2, d.sel_shift[i]), O::neg(h2));
+      const vec_t r0 = prf_vec<K>(L, d.zero[i][0], (uint64_t)v);
+      const vec_t r1 = prf_vec<K>(L, d.zero[i][1], (uint64_t)v);
+      const vec_t r2 = prf_vec<K>(L, d.zero[i][2], (uint64_t)v);
+      const vec_t z0 = O::add(O::add(O::mul(a0, O::add(b0, b1)), O::mul(a1, b0)), O::sub(r0, r1));
+      const vec_t z1 = O::add(O::add(O::mul(a1, O::add(b1, b2)), O::mul(a2, b1)), O::sub(r1, r2));
+      const vec_t z2 = O::add(O::add(O::mul(a2, O::add(b2, b0)), O::mul(a0, b2)), O::sub(r2, r0));
+      a0 = z0; a1 = z1; a2 = z2;
+    }
+    out_d.s[0][v] = a0;
+    out_d.s[1][v] = a1;
+    out_d.s[2][v] = a2;
+    out_rest.s[0][v] = O::sub(x_abs.s[0][v], p0);
+    out_rest.s[1][v] = O::sub(x_abs.s[1][v], p1);
+    out_rest.s[2][v] = O::sub(x_abs.s[2][v], p2);
+  }
+}
+
+}  // namespace
+
+int k_planes_gather(mb_ctx *ctx, const mb_tensor *const src[3], const short *idx, int nplanes, mb_tensor *const W[3], int64_t n) {
+  if (nplanes < 1 || nplanes > 128 || n % 128) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "planes_gather: bad plane count / ragged planes");
+  GatherDesc d;
+  d.nplanes = nplanes;
+  for (int i = 0; i < nplanes; i++) d.idx[i] = idx[i];
+  const int64_t nv = n / 128, total = nv * nplanes;
+  Planes3 s, w;
+  for (int i = 0; i < 3; i++) { s.s[i] = (vec_t *)src[i]->dptr; w.s[i] = (vec_t *)W[i]->dptr; }
+  planes_gather_kernel<<<(unsigned)std::min<int64_t>((total + 255) / 256, (int64_t)ctx->sm_count * 8), 256, 0, ctx->stream>>>(d, s, w, nv);
+  MB_LAUNCH_CHECK_W(ctx, "planes_gather", 16.0 * total * 6, 0, 0);
+  return MB_OK;
+}
+
+int k_prefix_or_level(mb_ctx *ctx, const PrefixLevel &lv, mb_tensor *const W[3], int64_t n) {
+  if (lv.nops < 1 || lv.nops > MB_PREFIX_MAX_OPS || n % 128) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "prefix_or_level: bad level");
+  const int64_t nv = n / 128;
+  Planes3 w;
+  for (int i = 0; i < 3; i++) w.s[i] = (vec_t *)W[i]->dptr;
+  const int64_t total = nv * lv.nops;
+  AES_LAUNCH(ctx, prefix_or_level_kernel, AES_TPB_MID, total, lv, w, nv);
+  MB_LAUNCH_CHECK_W(ctx, "prefix_or_level", 16.0 * total * 9, 3.0 * total, 0);
+  return MB_OK;
+}
+
+int k_inject_sum(mb_ctx *ctx, const InjectSumDesc &d, const mb_tensor *const W[3], int64_t n, const mb_rep *base, mb_tensor *const out[3]) {
+  if (d.nplanes < 1 || d.nplanes > MB_INJECT_MAX_PLANES || n % 128) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "inject_sum: bad descriptor");
+  const mb_tensor *t = out[0];
+  const int64_t nvec = vec_count(t);
+  Bits3 w;
+  Ring3 o;
+  CRing3 b;
+  for (int i = 0; i < 3; i++) {
+    w.s[i] = (const uint32_t *)W[i]->dptr;
+    o.s[i] = (vec_t *)out[i]->dptr;
+    b.s[i] = base ? (const vec_t *)base->s[i]->dptr : nullptr;
+  }
+  int live = 0;
+  for (int i = 0; i < d.nplanes; i++) live += d.mult[i] != 0;
+  if (t->dtype == MB_RING128)
+    AES_LAUNCH(ctx, inject_sum_kernel<VK_RING128>, AES_TPB_MID, nvec, d, w, n, b, o, nvec);
+  else
+    AES_LAUNCH(ctx, inject_sum_kernel<VK_RING64>, AES_TPB_MID, nvec, d, w, n, b, o, nvec);
+  MB_LAUNCH_CHECK_W(ctx, "inject_sum", 16.0 * nvec * (3 + (base ? 3 : 0)) + 3.0 * live * n / 8, 2.0 * live * nvec, 0);
+  return MB_OK;
+}
+
+int k_pow2_bits(mb_ctx *ctx, const Pow2Desc &d, const mb_tensor *const W[3], int64_t n, const mb_rep *x_abs, mb_tensor *const out_d[3],
+                mb_tensor *const out_rest[3]) {
+  if (d.count < 1 || d.count > MB_POW2_MAX_BITS || n % 128) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "pow2_bits: bad descriptor");
+  const mb_tensor *t = out_d[0];
+  const int64_t nvec = vec_count(t);
+  Bits3 w;
+  Ring3 od, orr;
+  CRing3 xa;
+  for (int i = 0; i < 3; i++) {
+    w.s[i] = (const uint32_t *)W[i]->dptr;
+    od.s[i] = (vec_t *)out_d[i]->dptr;
+    orr.s[i] = (vec_t *)out_rest[i]->dptr;
+    xa.s[i] = (const vec_t *)x_abs->s[i]->dptr;
+  }
+  if (t->dtype == MB_RING128)
+    AES_LAUNCH(ctx, pow2_bits_kernel<VK_RING128>, AES_TPB_384, nvec, d, w, n, xa, od, orr, nvec);
+  else
+    AES_LAUNCH(ctx, pow2_bits_kernel<VK_RING64>, AES_TPB_384, nvec, d, w, n, xa, od, orr, nvec);
+  MB_LAUNCH_CHECK_W(ctx, "pow2_bits", 16.0 * nvec * 9 + 3.0 * d.count * n / 8, 5.0 * d.count * nvec, 0);
+  return MB_OK;
+}

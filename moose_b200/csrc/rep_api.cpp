@@ -99,6 +99,44 @@ int gen_zero_seeds(mb_ctx *ctx, AesKey seeds[3]) {
   return MB_OK;
 }
 
+}  // namespace
+
+int mb_draw_zero_seeds(mb_ctx *ctx, AesKey seeds[3]) { return gen_zero_seeds(ctx, seeds); }
+
+// RingInjectOp::rep_kernel: gen_dabit (dabit.rs:49-55): Sample seed, PrfKeyGen, 2 x SyncKey; adt_to_rep
+// (convert.rs:426-431): 2 x SyncKey, PrfKeyGen.  Only the adt_to_rep streams survive in the result.
+int mb_draw_inject_keys(mb_ctx *ctx, AesKey keys[2]) {
+  uint8_t seed_bits[16], key[16], sync_b[16], sync_br[16], sync0[16], sync1[16], key2[16];
+  MB_CHECK(mb_entropy16(ctx, seed_bits));
+  MB_CHECK(mb_entropy16(ctx, key));
+  MB_CHECK(mb_entropy16(ctx, sync_b));
+  MB_CHECK(mb_entropy16(ctx, sync_br));
+  MB_CHECK(mb_entropy16(ctx, sync0));
+  MB_CHECK(mb_entropy16(ctx, sync1));
+  MB_CHECK(mb_entropy16(ctx, key2));
+  seed_to_aes(ctx, sync0, key2, &keys[0]);
+  seed_to_aes(ctx, sync1, key2, &keys[1]);
+  return MB_OK;
+}
+
+// TruncPrOp::rep_kernel: gen_trunc_mask (trunc.rs:45-63): Sample seed, PrfKeyGen, 3 x SyncKey::random();
+// adt_to_rep (convert.rs:426-431): 2 x SyncKey::random(), PrfKeyGen.  (r, y0, y1) survive in the result.
+int mb_draw_trunc_keys(mb_ctx *ctx, AesKey keys[3]) {
+  uint8_t seed_r[16], key[16], sync[3][16], sync0[16], sync1[16], key2[16];
+  MB_CHECK(mb_entropy16(ctx, seed_r));
+  MB_CHECK(mb_entropy16(ctx, key));
+  for (int i = 0; i < 3; i++) MB_CHECK(mb_entropy16(ctx, sync[i]));
+  MB_CHECK(mb_entropy16(ctx, sync0));
+  MB_CHECK(mb_entropy16(ctx, sync1));
+  MB_CHECK(mb_entropy16(ctx, key2));
+  mb_aes_expand(seed_r, &keys[0]);
+  seed_to_aes(ctx, sync0, key2, &keys[1]);
+  seed_to_aes(ctx, sync1, key2, &keys[2]);
+  return MB_OK;
+}
+
+namespace {
+
 // three fresh tensors shaped like `like`
 int alloc3(mb_ctx *ctx, const mb_tensor *like, mb_tensor *z[3]) {
   z[0] = z[1] = z[2] = nullptr;

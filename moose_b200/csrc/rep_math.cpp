@@ -8,6 +8,8 @@
 // matches the op-by-op protocol.  No arithmetic happens on the host.
 #include "common.h"
 
+#include <cstdlib>
+
 namespace {
 
 struct Err { int code; };
@@ -115,8 +117,80 @@ R sign_from_msb(mb_ctx *c, const R &msb) {
   return pub_sub(c, ones, dbl);
 }
 
+// Owning triple of freshly allocated tensors (working planes / results of the batched kernels).
+struct T3 {
+  mb_ctx *c;
+  mb_tensor *t[3];
+  explicit T3(mb_ctx *c_) : c(c_) { t[0] = t[1] = t[2] = nullptr; }
+  ~T3() { for (int i = 0; i < 3; i++) if (t[i]) mb_tensor_free(c, t[i]); }
+  T3(const T3 &) = delete;
+  T3 &operator=(const T3 &) = delete;
+  void alloc(mb_dtype d, int rank, const int64_t *shape) { for (int i = 0; i < 3; i++) ck(mb_tensor_new(c, d, rank, shape, &t[i])); }
+  R to_rep() {
+    mb_rep *q = nullptr;
+    ck(mb_rep_from_shares(c, t[0], t[1], t[2], &q));   // retains the tensors; ours are dropped by the destructor
+    return R(c, q);
+  }
+};
+
+// The batched kernels (math_fused.cu) work on whole 128-bit plane vectors and on the three-launch-free layouts.
+bool batched_ok(mb_ctx *c, const R &x) {
+  static const bool off = getenv("MOOSE_B200_NO_BATCHED_MATH") != nullptr;
+  const mb_tensor *t = x.like();
+  return !off && c->fused_bits && mb_is_ring(t->dtype) && t->numel > 0 && t->numel % 128 == 0 &&
+         mb_same_shape(x.p->s[1], t) && mb_same_shape(x.p->s[2], t);
+}
+
+// top_most_index (division.rs:146-206) with the prefix-or as one launch per level over a plane buffer and the
+// max_bits ring_injects + shifts + sum as one launch.  Keys are drawn in the reference's op order: the ANDs of prefix_or
+// level by level (misc.rs:14-24), then the ring_injects for i = 0 .. max_bits - 1.
+R top_most_index_batched(mb_ctx *c, int max_bits, const R &x) {
+  R x_bits = bitdec(c, x);
+  const int64_t n = x.like()->numel;
+  T3 W(c);
+  const int64_t wshape[2] = {max_bits, n};
+  W.alloc(MB_BIT, 2, wshape);
+  short idx[128];
+  for (int i = 0; i < max_bits; i++) idx[i] = (short)(max_bits - i - 1);   // x_rev
+  ck(k_planes_gather(c, x_bits.p->s, idx, max_bits, W.t, n));
+  int log_r = 0;
+  while ((1 << log_r) < max_bits) log_r++;
+  for (int i = 0; i < log_r; i++) {
+    PrefixLevel lv;
+    lv.nops = 0;
+    for (int j = 0; j < (1 << log_r) / (1 << (i + 1)); j++) {
+      const int y = (1 << i) + j * (1 << (i + 1)) - 1;
+      for (int k = 1; k < (1 << i) + 1; k++)
+        if (y + k < max_bits) {
+          lv.src[lv.nops] = (short)y;
+          lv.dst[lv.nops] = (short)(y + k);
+          ck(mb_draw_zero_seeds(c, lv.keys[lv.nops]));
+          lv.nops++;
+        }
+    }
+    if (lv.nops) ck(k_prefix_or_level(c, lv, W.t, n));
+  }
+  // y = reverse(W); z[i] = y[i] - y[i+1] (i < max_bits - 1), z[max_bits-1] = y[max_bits-1];
+  // res = (inject(z[max_bits-1]) << 0) + sum_{i >= 1} inject(z[i]) << (max_bits - i - 1)   (division.rs:196-203)
+  InjectSumDesc d;
+  d.nplanes = max_bits;
+  d.negate = 0;
+  for (int i = 0; i < max_bits; i++) {
+    d.pa[i] = (short)(max_bits - 1 - i);
+    d.pb[i] = (short)(i < max_bits - 1 ? max_bits - 2 - i : -1);
+    d.shift[i] = (unsigned char)(max_bits - i - 1);
+    d.mult[i] = (unsigned char)((i >= 1 ? 1 : 0) + (i == max_bits - 1 ? 1 : 0));
+    ck(mb_draw_inject_keys(c, d.keys[i]));
+  }
+  T3 out(c);
+  out.alloc(x.like()->dtype, x.like()->rank, x.like()->shape);
+  ck(k_inject_sum(c, d, W.t, n, nullptr, out.t));
+  return out.to_rep();
+}
+
 // division.rs:146-206
 R top_most_index(mb_ctx *c, int max_bits, const R &x) {
+  if (batched_ok(c, x) && max_bits >= 2 && max_bits <= MB_INJECT_MAX_PLANES) return top_most_index_batched(c, max_bits, x);
   R x_bits = bitdec(c, x);
   std::vector<R> y;
   for (int i = 0; i < max_bits; i++) y.push_back(index0(c, max_bits - i - 1, x_bits));
@@ -242,6 +316,52 @@ R rep_pow2(mb_ctx *c, int i_prec, int f_prec, const R &x) {
   R msb = inject(c, ring, 0, index0(c, bits - 1, x_bits));
   R abs_x = mux(c, msb, neg(c, x), x);
   R absolute_bits = bitdec(c, abs_x);
+  if (batched_ok(c, x) && i_prec >= 1 && i_prec <= MB_POW2_MAX_BITS && i_prec <= bits - f_prec) {
+    // The higher bits (ring_inject of planes f .. bits-1), their weighted sum, the fractional part and Pow2FromBits
+    // in 1 + ceil((bits - f - i) / 64) launches.  Keys in the reference's op order: every ring_inject first
+    // (exp.rs:50-58), then the i_prec multiplications of pow2_from_bits (exp.rs:150-153).
+    const int nhigh = bits - f_prec;
+    const int64_t n = x.like()->numel;
+    std::vector<AesKey> ik((size_t)nhigh * 2);
+    for (int i = 0; i < nhigh; i++) ck(mb_draw_inject_keys(c, &ik[2 * (size_t)i]));
+    Pow2Desc pd;
+    pd.count = i_prec;
+    pd.first_plane = f_prec;
+    for (int i = 0; i < i_prec; i++) {
+      pd.part_shift[i] = (unsigned char)((f_prec + i) & (bits - 1));
+      pd.sel_shift[i] = (unsigned char)(((uint64_t)1 << i) & (uint64_t)(bits - 1));   // Rust masks the shift amount
+      pd.inject[i][0] = ik[2 * (size_t)i];
+      pd.inject[i][1] = ik[2 * (size_t)i + 1];
+      ck(mb_draw_zero_seeds(c, pd.zero[i]));
+    }
+    T3 d3(c), rest(c);
+    d3.alloc(ring, x.like()->rank, x.like()->shape);
+    rest.alloc(ring, x.like()->rank, x.like()->shape);
+    ck(k_pow2_bits(c, pd, absolute_bits.p->s, n, abs_x.p, d3.t, rest.t));
+    R fractional_part = rest.to_rep();
+    for (int lo = i_prec; lo < nhigh; lo += MB_INJECT_MAX_PLANES) {
+      InjectSumDesc sd;
+      sd.nplanes = std::min(MB_INJECT_MAX_PLANES, nhigh - lo);
+      sd.negate = 1;
+      for (int j = 0; j < sd.nplanes; j++) {
+        sd.pa[j] = (short)(f_prec + lo + j);
+        sd.pb[j] = -1;
+        sd.shift[j] = (unsigned char)((f_prec + lo + j) & (bits - 1));
+        sd.mult[j] = 1;
+        sd.keys[j][0] = ik[2 * (size_t)(lo + j)];
+        sd.keys[j][1] = ik[2 * (size_t)(lo + j) + 1];
+      }
+      T3 next(c);
+      next.alloc(ring, x.like()->rank, x.like()->shape);
+      ck(k_inject_sum(c, sd, absolute_bits.p->s, n, fractional_part.p, next.t));
+      fractional_part = next.to_rep();
+    }
+    R d = d3.to_rep();
+    R g = exp_from_parts(c, d, fractional_part, f_prec, f_prec + i_prec);
+    R one_fixed = shl(c, (uint64_t)f_prec, rep_fill(c, x.like(), 1));
+    R inverse = rep_div(c, i_prec, f_prec, one_fixed, g);
+    return mux(c, msb, inverse, g);
+  }
   std::vector<R> higher_bits;
   for (int i = f_prec; i < bits; i++) higher_bits.push_back(inject(c, ring, 0, index0(c, i, absolute_bits)));
   R acc = rep_fill(c, x.like(), 0);

@@ -115,3 +115,48 @@ def test_greater_and_fill():
     gf, of = g.rep_fill(RING128, 12345, (2, 3)), mo.rep_fill(128, 12345, (2, 3))
     assert same_rep(gf, of)
     g.close()
+
+
+@pytest.mark.parametrize("bits,i_p,f_p,shape", [(128, 24, 40, (64, 2)), (128, 20, 20, (256,)), (64, 10, 15, (128,)), (128, 8, 27, (3, 128))])
+def test_batched_math_paths_share_parity(bits, i_p, f_p, shape):
+    """Element counts that are multiples of 128 take the batched kernels of csrc/math_fused.cu (prefix-or levels,
+    inject + sum, Pow2FromBits in registers) instead of one launch per replicated op: same shares as the oracle's
+    op-by-op protocol, bit for bit, for division (top_most_index), pow2 / exp (higher bits) and sigmoid."""
+    g, o = pair()
+    rng = np.random.default_rng(hash((bits, i_p, f_p, shape)) % 2 ** 32)
+    lim = min(6.0, 0.6 * (i_p - 1))
+    xs = rng.uniform(-lim, lim, shape)
+    ys = rng.uniform(0.3, 2.0 ** min(i_p - 2, 5), shape)
+    gx, ox = shared(g, o, bits, f_p, xs)
+    gy, oy = shared(g, o, bits, f_p, ys, owner=1)
+    l0 = g.launch_count
+    gz, oz = g.rep_div(i_p, f_p, gx, gy), mo.rep_div(o, i_p, f_p, ox, oy)
+    div_launches = g.launch_count - l0
+    assert same_rep(gz, oz)
+    assert div_launches < 120, div_launches          # ~1000 when every replicated op is its own launch
+    if bits == 128:   # pow2 / exp / sigmoid need 2 (i + f) <= ring bits for their inner division
+        gp, op = g.rep_pow2(i_p, f_p, gx), mo.rep_pow2(o, i_p, f_p, ox)
+        assert same_rep(gp, op)
+        l0 = g.launch_count
+        gs, os_ = g.sigmoid(i_p, f_p, gx), mo.rep_sigmoid(o, i_p, f_p, ox)
+        sig_launches = g.launch_count - l0
+        assert same_rep(gs, os_)
+        assert sig_launches < 600, sig_launches
+        assert np.abs(decode(g, f_p, gs) - 1.0 / (1.0 + np.exp(-xs))).max() < 2e-2
+    g.close()
+
+
+def test_batched_and_op_by_op_paths_agree():
+    """A/B inside the library: the same call with the batched paths switched off (fused bit kernels off selects the
+    op-by-op composition everywhere) yields the same shares."""
+    xs = np.random.default_rng(11).uniform(-4, 4, (128,))
+    outs = []
+    for fused in (True, False):
+        g, _ = pair()
+        g.set_fused_bits(fused)
+        gx = g.share(g.fixedpoint_encode(RING128, 27, g.from_host(mb.FLOAT64, xs)), 0)
+        s = g.sigmoid(8, 27, gx)
+        outs.append([s.share(i).to_host() for i in range(3)])
+        g.close()
+    for i in range(3):
+        assert np.array_equal(outs[0][i], outs[1][i])
