@@ -235,6 +235,21 @@ struct Pow2Desc {                // Pow2FromBits over planes first_plane .. firs
   AesKey inject[MB_POW2_MAX_BITS][2];
   AesKey zero[MB_POW2_MAX_BITS][3];
 };
+constexpr int MB_MULTRUNC_MAX_OPS = 16;
+struct MulTruncLevel {           // P[dst] = trunc_pr(P[src] * P[dst]) for a batch of ops of one prefix-mul level
+  int nops;
+  short src[MB_MULTRUNC_MAX_OPS], dst[MB_MULTRUNC_MAX_OPS];
+  AesKey keys[MB_MULTRUNC_MAX_OPS][6];  // zero share (3), then trunc (r, y0, y1)
+};
+constexpr int MB_POLY_MAX_COEFFS = 104;
+struct PolyCombine {             // out = trunc_pr(sum_{i < degree} P[i] * coeff[i + 1]) + coeff[0]
+  int degree;
+  uint64_t coeff_lo[MB_POLY_MAX_COEFFS], coeff_hi[MB_POLY_MAX_COEFFS];
+  AesKey keys[3];
+};
+int k_replicate(mb_ctx *ctx, const mb_rep *x, mb_tensor *const P[3], int slots);
+int k_mul_trunc_level(mb_ctx *ctx, const MulTruncLevel &lv, unsigned amount, mb_tensor *const P[3], int64_t nvec);
+int k_poly_combine(mb_ctx *ctx, const PolyCombine &pc, unsigned amount, mb_tensor *const P[3], mb_tensor *const out[3]);
 int k_planes_gather(mb_ctx *ctx, const mb_tensor *const src[3], const short *idx, int nplanes, mb_tensor *const W[3], int64_t n);
 int k_prefix_or_level(mb_ctx *ctx, const PrefixLevel &lv, mb_tensor *const W[3], int64_t n);
 int k_inject_sum(mb_ctx *ctx, const InjectSumDesc &d, const mb_tensor *const W[3], int64_t n, const mb_rep *base, mb_tensor *const out[3]);

@@ -193,6 +193,110 @@ __global__ void __launch_bounds__(AES_TPB_384) pow2_bits_kernel(const __grid_con
   }
 }
 
+// ---- PolynomialEval (fixedpoint/mod.rs:95-151) ------------------------------------------------------------------------
+struct TruncP {
+  unsigned sh_msb, sh_top, sh_ov;
+  uint64_t up_lo, up_hi, down_lo, down_hi;
+};
+inline TruncP make_trunc_p(mb_dtype dt, unsigned amount) {   // same constants as k_rep_trunc_pr (rep.cu)
+  const unsigned Lb = dt == MB_RING128 ? 128 : 64, k = Lb - 1;
+  TruncP p;
+  p.sh_msb = Lb - 1;
+  p.sh_top = (amount + 1) & (Lb - 1);
+  p.sh_ov = (k - amount) & (Lb - 1);
+  const u128 up = (u128)1 << ((k - 1) & (Lb - 1)), down = (u128)1 << ((k - amount - 1) & (Lb - 1));
+  p.up_lo = (uint64_t)up; p.up_hi = (uint64_t)(up >> 64);
+  p.down_lo = (uint64_t)down; p.down_hi = (uint64_t)(down >> 64);
+  return p;
+}
+// TruncPr of the replicated value (a0, a1, a2) with the three surviving streams (r, w0, w2): see trunc_pr_kernel (rep.cu)
+template <int K>
+__device__ __forceinline__ void trunc3(const TruncP &p, vec_t up, vec_t down, vec_t a0, vec_t a1, vec_t a2, vec_t r, vec_t w0, vec_t w2,
+                                       vec_t &z1) {
+  typedef VOps<K> O;
+  const vec_t a = O::add(O::add(a0, a1), a2);
+  const vec_t r_msb = O::shr(r, p.sh_msb);
+  const vec_t r_top = O::shr(O::shl(r, 1), p.sh_top);
+  const vec_t c = O::add(O::add(a, up), r);
+  const vec_t c_top = O::shr(O::shl(c, 1), p.sh_top);
+  const vec_t c_msb = O::shr(c, p.sh_msb);
+  const vec_t ov = make_ulonglong2(r_msb.x ^ c_msb.x, r_msb.y ^ c_msb.y);
+  const vec_t y = O::sub(O::add(O::sub(c_top, r_top), O::shl(ov, p.sh_ov)), down);
+  z1 = O::sub(O::sub(y, w0), w2);
+}
+
+// One batch of a prefix-mul level: P[dst] = trunc_pr(P[src] * P[dst]) for up to 16 ops (keys: zero share of the
+// multiplication -- unused, see below -- then (r, y0, y1) of the truncation).  P is a [slots, n] ring buffer per share.
+template <int K>
+__global__ void __launch_bounds__(AES_TPB_384) mul_trunc_level_kernel(const __grid_constant__ MulTruncLevel lv, TruncP tp, Ring3 P, int64_t nvec) {
+  extern __shared__ __align__(16) uint32_t sT[];
+  aes_load_table(sT);
+  const AesLane L = aes_lane(sT);
+  typedef VOps<K> O;
+  const vec_t up = O::splat(tp.up_lo, tp.up_hi), down = O::splat(tp.down_lo, tp.down_hi);
+  const int64_t total = (int64_t)lv.nops * nvec;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int op = (int)(t / nvec);
+    const int64_t v = t - (int64_t)op * nvec;
+    const int64_t ia = (int64_t)lv.src[op] * nvec + v, ib = (int64_t)lv.dst[op] * nvec + v;
+    const vec_t a0 = P.s[0][ia], a1 = P.s[1][ia], a2 = P.s[2][ia];
+    const vec_t b0 = P.s[0][ib], b1 = P.s[1][ib], b2 = P.s[2][ib];
+    // The product's zero share (keys[op][0..2]) sums to zero over the three shares and the truncation opens only that
+    // sum, so its streams are not expanded (their entropy requests were drawn, in order).
+    const vec_t m0 = O::add(O::mul(a0, O::add(b0, b1)), O::mul(a1, b0));
+    const vec_t m1 = O::add(O::mul(a1, O::add(b1, b2)), O::mul(a2, b1));
+    const vec_t m2 = O::add(O::mul(a2, O::add(b2, b0)), O::mul(a0, b2));
+    const vec_t r = prf_vec<K>(L, lv.keys[op][3], (uint64_t)v);
+    const vec_t w0 = prf_vec<K>(L, lv.keys[op][4], (uint64_t)v);
+    const vec_t w2 = prf_vec<K>(L, lv.keys[op][5], (uint64_t)v);
+    vec_t z1;
+    trunc3<K>(tp, up, down, m0, m1, m2, r, w0, w2, z1);
+    P.s[0][ib] = w0;
+    P.s[1][ib] = z1;
+    P.s[2][ib] = w2;
+  }
+}
+
+// P[i] = x for i < slots (the `degree` copies of x that prefix_op starts from)
+__global__ void replicate_kernel(CRing3 x, Ring3 P, int slots, int64_t nvec) {
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+      const vec_t a = x.s[i][v];
+      for (int j = 0; j < slots; j++) P.s[i][(int64_t)j * nvec + v] = a;
+    }
+  }
+}
+
+// out = trunc_pr(sum_i P[i] * c_{i+1}) + c_0 (public constants; c_0 lands on share 0)
+template <int K>
+__global__ void __launch_bounds__(AES_TPB_MID) poly_combine_kernel(const __grid_constant__ PolyCombine pc, TruncP tp, Ring3 P, Ring3 out,
+                                                                   int64_t nvec) {
+  extern __shared__ __align__(16) uint32_t sT[];
+  aes_load_table(sT);
+  const AesLane L = aes_lane(sT);
+  typedef VOps<K> O;
+  const vec_t up = O::splat(tp.up_lo, tp.up_hi), down = O::splat(tp.down_lo, tp.down_hi);
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
+    vec_t s0 = O::zero(), s1 = O::zero(), s2 = O::zero();
+    for (int i = 0; i < pc.degree; i++) {
+      const vec_t cf = O::splat(pc.coeff_lo[i + 1], pc.coeff_hi[i + 1]);
+      const int64_t ix = (int64_t)i * nvec + v;
+      s0 = O::add(s0, O::mul(P.s[0][ix], cf));
+      s1 = O::add(s1, O::mul(P.s[1][ix], cf));
+      s2 = O::add(s2, O::mul(P.s[2][ix], cf));
+    }
+    const vec_t r = prf_vec<K>(L, pc.keys[0], (uint64_t)v);
+    const vec_t w0 = prf_vec<K>(L, pc.keys[1], (uint64_t)v);
+    const vec_t w2 = prf_vec<K>(L, pc.keys[2], (uint64_t)v);
+    vec_t z1;
+    trunc3<K>(tp, up, down, s0, s1, s2, r, w0, w2, z1);
+    out.s[0][v] = O::add(w0, O::splat(pc.coeff_lo[0], pc.coeff_hi[0]));
+    out.s[1][v] = z1;
+    out.s[2][v] = w2;
+  }
+}
+
 }  // namespace
 
 int k_planes_gather(mb_ctx *ctx, const mb_tensor *const src[3], const short *idx, int nplanes, mb_tensor *const W[3], int64_t n) {
@@ -260,5 +364,45 @@ int k_pow2_bits(mb_ctx *ctx, const Pow2Desc &d, const mb_tensor *const W[3], int
   else
     AES_LAUNCH(ctx, pow2_bits_kernel<VK_RING64>, AES_TPB_384, nvec, d, w, n, xa, od, orr, nvec);
   MB_LAUNCH_CHECK_W(ctx, "pow2_bits", 16.0 * nvec * 9 + 3.0 * d.count * n / 8, 5.0 * d.count * nvec, 0);
+  return MB_OK;
+}
+
+int k_replicate(mb_ctx *ctx, const mb_rep *x, mb_tensor *const P[3], int slots) {
+  const int64_t nvec = vec_count(x->s[0]);
+  CRing3 xs;
+  Ring3 ps;
+  for (int i = 0; i < 3; i++) { xs.s[i] = (const vec_t *)x->s[i]->dptr; ps.s[i] = (vec_t *)P[i]->dptr; }
+  replicate_kernel<<<(unsigned)std::min<int64_t>((nvec + 255) / 256, (int64_t)ctx->sm_count * 8), 256, 0, ctx->stream>>>(xs, ps, slots, nvec);
+  MB_LAUNCH_CHECK_W(ctx, "replicate", 16.0 * nvec * 3 * (1 + slots), 0, 0);
+  return MB_OK;
+}
+
+int k_mul_trunc_level(mb_ctx *ctx, const MulTruncLevel &lv, unsigned amount, mb_tensor *const P[3], int64_t nvec) {
+  if (lv.nops < 1 || lv.nops > MB_MULTRUNC_MAX_OPS) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mul_trunc_level: bad level");
+  const mb_dtype dt = P[0]->dtype;
+  const TruncP tp = make_trunc_p(dt, amount);
+  Ring3 ps;
+  for (int i = 0; i < 3; i++) ps.s[i] = (vec_t *)P[i]->dptr;
+  const int64_t total = nvec * lv.nops;
+  if (dt == MB_RING128)
+    AES_LAUNCH(ctx, mul_trunc_level_kernel<VK_RING128>, AES_TPB_384, total, lv, tp, ps, nvec);
+  else
+    AES_LAUNCH(ctx, mul_trunc_level_kernel<VK_RING64>, AES_TPB_384, total, lv, tp, ps, nvec);
+  MB_LAUNCH_CHECK_W(ctx, "mul_trunc_level", 16.0 * total * 9, 3.0 * total, 0);
+  return MB_OK;
+}
+
+int k_poly_combine(mb_ctx *ctx, const PolyCombine &pc, unsigned amount, mb_tensor *const P[3], mb_tensor *const out[3]) {
+  if (pc.degree < 1 || pc.degree >= MB_POLY_MAX_COEFFS) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "poly_combine: bad degree");
+  const mb_dtype dt = out[0]->dtype;
+  const TruncP tp = make_trunc_p(dt, amount);
+  const int64_t nvec = vec_count(out[0]);
+  Ring3 ps, os;
+  for (int i = 0; i < 3; i++) { ps.s[i] = (vec_t *)P[i]->dptr; os.s[i] = (vec_t *)out[i]->dptr; }
+  if (dt == MB_RING128)
+    AES_LAUNCH(ctx, poly_combine_kernel<VK_RING128>, AES_TPB_MID, nvec, pc, tp, ps, os, nvec);
+  else
+    AES_LAUNCH(ctx, poly_combine_kernel<VK_RING64>, AES_TPB_MID, nvec, pc, tp, ps, os, nvec);
+  MB_LAUNCH_CHECK_W(ctx, "poly_combine", 16.0 * nvec * 3 * (pc.degree + 1), 3.0 * nvec, 0);
   return MB_OK;
 }

@@ -273,6 +273,52 @@ R polynomial_eval(mb_ctx *c, int f_prec, const double *coeff, int ncoeff, const 
     mb_fail(c, MB_ERR_INVALID_ARGUMENT, "polynomial_eval: no coefficient above the precision");
     throw Err{MB_ERR_INVALID_ARGUMENT};
   }
+  if (batched_ok(c, x) && degree + 1 <= MB_POLY_MAX_COEFFS) {
+    // prefix_op over `degree` copies of x with op = trunc_pr(mul(a, b)): one launch per batch of <= 16 ops of a level,
+    // then the weighted sum, its truncation and the constant term in one launch.  Keys per op in the reference's order
+    // (multiplication, then truncation), level by level as prefix_op walks them (misc.rs:14-24).
+    const int64_t nvec = x.like()->numel * (bits / 8) / 16;
+    T3 P(c);
+    int64_t pshape[MB_MAX_RANK + 1];
+    pshape[0] = degree;
+    for (int i = 0; i < x.like()->rank; i++) pshape[i + 1] = x.like()->shape[i];
+    if (x.like()->rank + 1 > MB_MAX_RANK) { const int64_t flat[2] = {degree, x.like()->numel}; P.alloc(ring_of(x), 2, flat); }
+    else P.alloc(ring_of(x), x.like()->rank + 1, pshape);
+    ck(k_replicate(c, x.p, P.t, degree));
+    int log_r = 0;
+    while ((1 << log_r) < degree) log_r++;
+    for (int i = 0; i < log_r; i++) {
+      MulTruncLevel lv;
+      lv.nops = 0;
+      for (int j = 0; j < (1 << log_r) / (1 << (i + 1)); j++) {
+        const int y = (1 << i) + j * (1 << (i + 1)) - 1;
+        for (int k = 1; k < (1 << i) + 1; k++)
+          if (y + k < degree) {
+            lv.src[lv.nops] = (short)y;
+            lv.dst[lv.nops] = (short)(y + k);
+            ck(mb_draw_zero_seeds(c, lv.keys[lv.nops]));
+            ck(mb_draw_trunc_keys(c, lv.keys[lv.nops] + 3));
+            if (++lv.nops == MB_MULTRUNC_MAX_OPS) {
+              ck(k_mul_trunc_level(c, lv, (unsigned)f_prec, P.t, nvec));
+              lv.nops = 0;
+            }
+          }
+      }
+      if (lv.nops) ck(k_mul_trunc_level(c, lv, (unsigned)f_prec, P.t, nvec));
+    }
+    PolyCombine pc;
+    pc.degree = degree;
+    for (int i = 0; i <= degree; i++) {
+      const u128 v = fixed_constant(bits, coeff[i], (unsigned)f_prec);
+      pc.coeff_lo[i] = (uint64_t)v;
+      pc.coeff_hi[i] = (uint64_t)(v >> 64);
+    }
+    ck(mb_draw_trunc_keys(c, pc.keys));
+    T3 out(c);
+    out.alloc(ring_of(x), x.like()->rank, x.like()->shape);
+    ck(k_poly_combine(c, pc, (unsigned)f_prec, P.t, out.t));
+    return out.to_rep();
+  }
   std::vector<T> coeffs;
   for (int i = 0; i <= degree; i++) coeffs.push_back(pub_fill(c, x.like(), fixed_constant(bits, coeff[i], (unsigned)f_prec)));
   std::vector<R> pre;
