@@ -342,6 +342,14 @@ int mb_rep_dot_concat(mb_ctx *ctx, const mb_rep *const *xs, int n, const mb_rep 
  * rep_to_adt (additive/convert.rs:12-79) + TruncPrProvider::trunc_pr
  * (additive/trunc.rs:22-65,114-169) + AdtToRepOp (replicated/convert.rs:392-497). */
 int mb_rep_trunc_pr(mb_ctx *ctx, uint32_t amount, const mb_rep *x, mb_rep **out);
+/* Fixed-point dot / mul as the logical layer issues them: DotOp / MulOp::rep_rep_kernel followed by
+ * TruncPrOp::rep_kernel (moose/src/fixedpoint/ops.rs:761-928, 548-672; moose/src/logical/ops.rs:776-821, 553-600).
+ * Same entropy requests and the same result shares as mb_rep_dot / mb_rep_mul + mb_rep_trunc_pr; the product's
+ * zero share cancels in the value TruncPr opens and is not expanded.  mb_rep_fixed_dot_concat takes the left operand
+ * as the concatenation along axis 1 of `n` tensors (mb_rep_dot_concat). */
+int mb_rep_fixed_dot(mb_ctx *ctx, uint32_t amount, const mb_rep *x, const mb_rep *y, mb_rep **out);
+int mb_rep_fixed_dot_concat(mb_ctx *ctx, uint32_t amount, const mb_rep *const *xs, int n, const mb_rep *y, mb_rep **out);
+int mb_rep_fixed_mul(mb_ctx *ctx, uint32_t amount, const mb_rep *x, const mb_rep *y, mb_rep **out);
 /* BitDecomposeOp::rep_ring_kernel (moose/src/replicated/bits.rs:6-20,84-134;
  * misc.rs:176-242): replicated bit shares of shape [k, shape...]. */
 int mb_rep_bit_decompose(mb_ctx *ctx, const mb_rep *x, mb_rep **out);

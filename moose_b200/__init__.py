@@ -114,7 +114,8 @@ ABI = {
     "mb_rep_diag": [_P, _P, _PP], "mb_rep_concat": [_P, _I, _PP, _I, _PP], "mb_rep_add_n": [_P, _PP, _I, _PP],
     "mb_rep_sum": [_P, _P, _I, _PP], "mb_rep_cast_ring128_to_ring64": [_P, _P, _PP],
     "mb_rep_fixedpoint_mean": [_P, _I, _U64, _U32, _P, _PP], "mb_rep_abs": [_P, _P, _PP],
-    "mb_rep_dot_concat": [_P, _PP, _I, _P, _PP], "mb_rep_equal": [_P, _P, _P, _PP], "mb_rep_log2": [_P, _U32, _U32, _P, _PP], "mb_rep_log": [_P, _U32, _U32, _P, _PP],
+    "mb_rep_dot_concat": [_P, _PP, _I, _P, _PP], "mb_rep_fixed_dot": [_P, _U32, _P, _P, _PP],
+    "mb_rep_fixed_dot_concat": [_P, _U32, _PP, _I, _P, _PP], "mb_rep_fixed_mul": [_P, _U32, _P, _P, _PP], "mb_rep_equal": [_P, _P, _P, _PP], "mb_rep_log2": [_P, _U32, _U32, _P, _PP], "mb_rep_log": [_P, _U32, _U32, _P, _PP],
     "mb_rep_sqrt": [_P, _U32, _U32, _P, _PP],
     "mb_rep_softmax": [_P, _I, _I, _U32, _U32, _P, _PP], "mb_rep_argmax": [_P, _I, _I, _P, _PP],
     "mb_load_npy": [_P, ctypes.c_char_p, _PP], "mb_load_npy_fixed": [_P, ctypes.c_char_p, _I, _U32, _PP],
@@ -803,6 +804,20 @@ class Session:
         arr = (ctypes.c_void_p * max(len(xs), 1))(*[x.h for x in xs])
         out = self._out()
         return self._r(lib().mb_rep_dot_concat(self.ctx, arr, len(xs), y.h, ctypes.byref(out)), out)
+
+    def fixed_dot(self, amount: int, x, y) -> RepTensor:
+        """trunc_pr(amount, rep_dot(x, y)) in one call (same shares; the product's zero share is never expanded)."""
+        out = self._out()
+        return self._r(lib().mb_rep_fixed_dot(self.ctx, amount, x.h, y.h, ctypes.byref(out)), out)
+
+    def fixed_dot_concat(self, amount: int, xs, y) -> RepTensor:
+        arr = (ctypes.c_void_p * max(len(xs), 1))(*[x.h for x in xs])
+        out = self._out()
+        return self._r(lib().mb_rep_fixed_dot_concat(self.ctx, amount, arr, len(xs), y.h, ctypes.byref(out)), out)
+
+    def fixed_mul(self, amount: int, x, y) -> RepTensor:
+        out = self._out()
+        return self._r(lib().mb_rep_fixed_mul(self.ctx, amount, x.h, y.h, ctypes.byref(out)), out)
 
     def rep_add_n(self, xs) -> RepTensor:
         arr = (ctypes.c_void_p * max(len(xs), 1))(*[x.h for x in xs])

@@ -257,6 +257,32 @@ __global__ void __launch_bounds__(AES_TPB_384) mul_trunc_level_kernel(const __gr
   }
 }
 
+// trunc_pr(x * y) on separate tensors (mb_rep_fixed_mul): the product's zero share cancels in the opened sum
+template <int K>
+__global__ void __launch_bounds__(AES_TPB_MID) mul_trunc_kernel(AesKey kr, AesKey k1, AesKey k2, TruncP tp, CRing3 x, CRing3 y, Ring3 out,
+                                                                int64_t nvec) {
+  extern __shared__ __align__(16) uint32_t sT[];
+  aes_load_table(sT);
+  const AesLane L = aes_lane(sT);
+  typedef VOps<K> O;
+  const vec_t up = O::splat(tp.up_lo, tp.up_hi), down = O::splat(tp.down_lo, tp.down_hi);
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
+    const vec_t a0 = x.s[0][v], a1 = x.s[1][v], a2 = x.s[2][v];
+    const vec_t b0 = y.s[0][v], b1 = y.s[1][v], b2 = y.s[2][v];
+    const vec_t m0 = O::add(O::mul(a0, O::add(b0, b1)), O::mul(a1, b0));
+    const vec_t m1 = O::add(O::mul(a1, O::add(b1, b2)), O::mul(a2, b1));
+    const vec_t m2 = O::add(O::mul(a2, O::add(b2, b0)), O::mul(a0, b2));
+    const vec_t r = prf_vec<K>(L, kr, (uint64_t)v);
+    const vec_t w0 = prf_vec<K>(L, k1, (uint64_t)v);
+    const vec_t w2 = prf_vec<K>(L, k2, (uint64_t)v);
+    vec_t z1;
+    trunc3<K>(tp, up, down, m0, m1, m2, r, w0, w2, z1);
+    out.s[0][v] = w0;
+    out.s[1][v] = z1;
+    out.s[2][v] = w2;
+  }
+}
+
 // P[i] = x for i < slots (the `degree` copies of x that prefix_op starts from)
 __global__ void replicate_kernel(CRing3 x, Ring3 P, int slots, int64_t nvec) {
   for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
@@ -404,5 +430,20 @@ int k_poly_combine(mb_ctx *ctx, const PolyCombine &pc, unsigned amount, mb_tenso
   else
     AES_LAUNCH(ctx, poly_combine_kernel<VK_RING64>, AES_TPB_MID, nvec, pc, tp, ps, os, nvec);
   MB_LAUNCH_CHECK_W(ctx, "poly_combine", 16.0 * nvec * 3 * (pc.degree + 1), 3.0 * nvec, 0);
+  return MB_OK;
+}
+
+int k_mul_trunc(mb_ctx *ctx, const AesKey tk[3], unsigned amount, const mb_rep *x, const mb_rep *y, mb_tensor *const out[3]) {
+  const mb_dtype dt = out[0]->dtype;
+  const TruncP tp = make_trunc_p(dt, amount);
+  const int64_t nvec = vec_count(out[0]);
+  CRing3 xs, ys;
+  Ring3 os;
+  for (int i = 0; i < 3; i++) { xs.s[i] = (const vec_t *)x->s[i]->dptr; ys.s[i] = (const vec_t *)y->s[i]->dptr; os.s[i] = (vec_t *)out[i]->dptr; }
+  if (dt == MB_RING128)
+    AES_LAUNCH(ctx, mul_trunc_kernel<VK_RING128>, AES_TPB_MID, nvec, tk[0], tk[1], tk[2], tp, xs, ys, os, nvec);
+  else
+    AES_LAUNCH(ctx, mul_trunc_kernel<VK_RING64>, AES_TPB_MID, nvec, tk[0], tk[1], tk[2], tp, xs, ys, os, nvec);
+  MB_LAUNCH_CHECK_W(ctx, "mul_trunc", 16.0 * nvec * 9, 3.0 * nvec, 0);
   return MB_OK;
 }

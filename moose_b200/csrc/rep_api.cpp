@@ -425,7 +425,8 @@ static int rep_dot_skinny(mb_ctx *ctx, mb_dtype dt, const RepDotParts &parts, co
 // dot(concatenate(xs, axis = 1), y) without materialising the concatenation when the skinny kernel applies
 // (LinearPredictor's bias trick, pymoose linear_predictor.py:33-58: the [B, 1 + features] operand is 8 GB per share
 // at BASELINE config 3).  Same values, same zero share, hence the same shares as ConcatOp + DotOp.
-extern "C" int mb_rep_dot_concat(mb_ctx *ctx, const mb_rep *const *xs, int n, const mb_rep *y, mb_rep **out) {
+static int rep_dot_core(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, bool zero_share, mb_rep **out);
+static int rep_dot_concat_core(mb_ctx *ctx, const mb_rep *const *xs, int n, const mb_rep *y, bool zero_share, mb_rep **out) {
   MB_ENTER(ctx, "mb_rep_dot_concat");
   MB_REQUIRE(ctx, xs && n > 0 && rep_valid(y) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_dot_concat: NULL argument");
   const mb_dtype dt = y->s[0]->dtype;
@@ -444,7 +445,7 @@ extern "C" int mb_rep_dot_concat(mb_ctx *ctx, const mb_rep *const *xs, int n, co
   if (!fused) {
     RepTmp cat(ctx);
     MB_CHECK(mb_rep_concat(ctx, 1, xs, n, &cat.p));
-    return mb_rep_dot(ctx, cat.p, y, out);
+    return rep_dot_core(ctx, cat.p, y, zero_share, out);
   }
   RepDotParts parts;
   parts.n = n;
@@ -461,12 +462,17 @@ extern "C" int mb_rep_dot_concat(mb_ctx *ctx, const mb_rep *const *xs, int n, co
   MB_CHECK(rep_dot_skinny(ctx, dt, parts, y, z.p, M, N));
   AesKey seeds[3];
   MB_CHECK(gen_zero_seeds(ctx, seeds));
-  MB_CHECK(k_add_zero_share(ctx, seeds, z.p->s, z.p->s));
+  if (zero_share) MB_CHECK(k_add_zero_share(ctx, seeds, z.p->s, z.p->s));
   *out = z.release();
   return MB_OK;
 }
+extern "C" int mb_rep_dot_concat(mb_ctx *ctx, const mb_rep *const *xs, int n, const mb_rep *y, mb_rep **out) {
+  return rep_dot_concat_core(ctx, xs, n, y, true, out);
+}
 
-extern "C" int mb_rep_dot(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out) {
+// zero_share = false: the products v_i without alpha_i (the zero share's entropy requests are still drawn, in order) --
+// for callers that only open the sum v_0 + v_1 + v_2, where the alphas cancel (the fused fixed-point dot below)
+static int rep_dot_core(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, bool zero_share, mb_rep **out) {
   MB_ENTER(ctx, "mb_rep_dot");
   MB_REQUIRE(ctx, rep_valid(x) && rep_valid(y) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_dot: NULL argument");
   mb_dtype dt = x->s[0]->dtype;
@@ -516,7 +522,46 @@ extern "C" int mb_rep_dot(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep 
   }
   AesKey seeds[3];
   MB_CHECK(gen_zero_seeds(ctx, seeds));
-  MB_CHECK(k_add_zero_share(ctx, seeds, z.p->s, z.p->s));
+  if (zero_share) MB_CHECK(k_add_zero_share(ctx, seeds, z.p->s, z.p->s));
+  *out = z.release();
+  return MB_OK;
+}
+extern "C" int mb_rep_dot(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out) { return rep_dot_core(ctx, x, y, true, out); }
+
+// Fixed-point dot / mul of the logical layer: DotOp / MulOp followed by TruncPrOp (fixedpoint/ops.rs:761-928, 548-672;
+// logical/ops.rs:776-821, 553-600).  With the three parties in one process only the truncated shares leave the call, and
+// TruncPr opens x_0 + x_1 + x_2, in which the product's zero share cancels: its streams are never expanded and the
+// separate pass that adds it disappears.  Entropy is drawn exactly as by mb_rep_dot + mb_rep_trunc_pr, so the result
+// shares are those of the two-call sequence bit for bit (tests/test_gpu_replicated.py).
+extern "C" int mb_rep_fixed_dot(mb_ctx *ctx, uint32_t amount, const mb_rep *x, const mb_rep *y, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_fixed_dot");
+  RepTmp v(ctx);
+  MB_CHECK(rep_dot_core(ctx, x, y, !ctx->fused_bits, &v.p));   // fused kernels off (A/B tests): the two-call sequence
+  return mb_rep_trunc_pr(ctx, amount, v.p, out);
+}
+extern "C" int mb_rep_fixed_dot_concat(mb_ctx *ctx, uint32_t amount, const mb_rep *const *xs, int n, const mb_rep *y, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_fixed_dot_concat");
+  RepTmp v(ctx);
+  MB_CHECK(rep_dot_concat_core(ctx, xs, n, y, !ctx->fused_bits, &v.p));
+  return mb_rep_trunc_pr(ctx, amount, v.p, out);
+}
+extern "C" int mb_rep_fixed_mul(mb_ctx *ctx, uint32_t amount, const mb_rep *x, const mb_rep *y, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_fixed_mul");
+  MB_REQUIRE(ctx, rep_valid(x) && rep_valid(y) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_fixed_mul: NULL argument");
+  const mb_dtype dt = x->s[0]->dtype;
+  const bool same = mb_is_ring(dt) && dt == y->s[0]->dtype && mb_same_shape(x->s[0], y->s[0]) && uniform_shapes(x, y) && x->s[0]->numel > 0;
+  const unsigned k = (dt == MB_RING128 ? 128 : 64) - 1;
+  if (!same || amount + 1 > k || !ctx->fused_bits) {   // broadcasting operands / argument errors: the two-call sequence handles and reports them
+    RepTmp m(ctx);
+    MB_CHECK(mb_rep_mul(ctx, x, y, &m.p));
+    return mb_rep_trunc_pr(ctx, amount, m.p, out);
+  }
+  AesKey zero[3], tk[3];
+  MB_CHECK(gen_zero_seeds(ctx, zero));          // drawn, not expanded
+  MB_CHECK(mb_draw_trunc_keys(ctx, tk));
+  RepTmp z(ctx);
+  MB_CHECK(rep_alloc_like(ctx, x->s[0], &z.p));
+  MB_CHECK(k_mul_trunc(ctx, tk, amount, x, y, z.p->s));
   *out = z.release();
   return MB_OK;
 }

@@ -141,6 +141,26 @@ bool batched_ok(mb_ctx *c, const R &x) {
          mb_same_shape(x.p->s[1], t) && mb_same_shape(x.p->s[2], t);
 }
 
+// trunc_pr(amount, mul(a, b)) with the truncation keys given (the caller drew the multiplication's zero-share seeds and
+// these keys in the reference's order): one pass, the zero share cancels in the opened sum (math_fused.cu).
+bool same_shapes(const R &a, const R &b) {
+  for (int i = 0; i < 3; i++)
+    if (!mb_same_shape(a.p->s[i], a.like()) || !mb_same_shape(b.p->s[i], a.like())) return false;
+  return a.like()->dtype == b.like()->dtype;
+}
+R mul_trunc_with(mb_ctx *c, const AesKey tk[3], int amount, const R &a, const R &b) {
+  T3 out(c);
+  out.alloc(a.like()->dtype, a.like()->rank, a.like()->shape);
+  ck(k_mul_trunc(c, tk, (unsigned)amount, a.p, b.p, out.t));
+  return out.to_rep();
+}
+// trunc(amount, mul(a, b)) as the reference issues it: mul's entropy, then trunc's
+R mul_trunc(mb_ctx *c, int amount, const R &a, const R &b) {
+  mb_rep *q = nullptr;
+  ck(mb_rep_fixed_mul(c, (uint32_t)amount, a.p, b.p, &q));
+  return R(c, q);
+}
+
 // top_most_index (division.rs:146-206) with the prefix-or as one launch per level over a plane buffer and the
 // max_bits ring_injects + shifts + sum as one launch.  Keys are drawn in the reference's op order: the ANDs of prefix_or
 // level by level (misc.rs:14-24), then the ring_injects for i = 0 .. max_bits - 1.
@@ -227,8 +247,7 @@ R approximate_reciprocal(mb_ctx *c, int i_prec, int f_prec, const R &x) {
   div_norm(c, total, x, upshifted, signed_topmost);
   T alpha = pub_fill(c, x.like(), fixed_constant(bits_of(x), 2.9142, (unsigned)total));
   R d = pub_sub(c, alpha, shl(c, 1, upshifted));
-  R w = mul(c, d, signed_topmost);
-  return trunc(c, (uint32_t)(2 * i_prec), w);
+  return mul_trunc(c, 2 * i_prec, d, signed_topmost);
 }
 
 // DivOp::rep_rep_kernel (division.rs:5-86)
@@ -245,16 +264,28 @@ R rep_div(mb_ctx *c, int i_prec, int f_prec, const R &x, const R &y) {
   T alpha = pub_fill(c, x.like(), fixed_constant(bits, 1.0, (unsigned)(2 * f_prec)));
   R init_prod = mul(c, y, w);  // broadcast to x's shape happens inside the share-wise ops below
   R a = pub_sub(c, alpha, init_prod);
-  R b = mul(c, x, w);
-  b = trunc(c, (uint32_t)f_prec, b);
+  R b = mul_trunc(c, f_prec, x, w);
   for (int i = 0; i < theta; i++) {
+    R a1 = add_pub(c, a, alpha);
+    if (c->fused_bits && a.like()->numel > 0 && same_shapes(a, b) && same_shapes(a, a1) && 2 * f_prec + 1 <= bits - 1) {
+      // reference order (division.rs:67-73): mul, mul, trunc, trunc -- draw in that order, then two fused passes
+      AesKey z0[3], z1[3], t0[3], t1[3];
+      ck(mb_draw_zero_seeds(c, z0));
+      ck(mb_draw_zero_seeds(c, z1));
+      ck(mb_draw_trunc_keys(c, t0));
+      ck(mb_draw_trunc_keys(c, t1));
+      R na = mul_trunc_with(c, t0, 2 * f_prec, a, a);
+      R nb = mul_trunc_with(c, t1, 2 * f_prec, b, a1);
+      a = std::move(na);
+      b = std::move(nb);
+      continue;
+    }
     R next_a = mul(c, a, a);
-    R next_b = mul(c, b, add_pub(c, a, alpha));
+    R next_b = mul(c, b, a1);
     a = trunc(c, (uint32_t)(2 * f_prec), next_a);
     b = trunc(c, (uint32_t)(2 * f_prec), next_b);
   }
-  b = mul(c, b, add_pub(c, a, alpha));
-  return trunc(c, (uint32_t)(2 * f_prec), b);
+  return mul_trunc(c, 2 * f_prec, b, add_pub(c, a, alpha));
 }
 
 const double P_1045[100] = {
@@ -350,8 +381,7 @@ R exp_from_parts(mb_ctx *c, const R &e_int, const R &e_frac, int f, int k) {
   const int amount = k - 2 - f;
   R x = shl(c, (uint64_t)amount, e_frac);
   R e_approx = polynomial_eval(c, k - 2, x);
-  R e_prod = mul(c, e_int, e_approx);
-  return trunc(c, (uint32_t)amount, e_prod);
+  return mul_trunc(c, amount, e_int, e_approx);
 }
 
 // Pow2Op::rep_rep_kernel (exp.rs:11-111)

@@ -53,7 +53,7 @@ class MLPPredictor:
         n = len(self.w)
         for i in range(n):
             w = s.share(self.w[i], 0)
-            y = s.trunc_pr(self.frac, s.rep_dot(x, w))
+            y = s.fixed_dot(self.frac, x, w)
             z = s.rep_add_public(y, self.b[i]) if self.bias_via == "public" else s.rep_add(y, s.share(self.b[i], 0))
             if i < n - 1 and self.activation == "sigmoid":
                 z = s.sigmoid(self.integral, self.frac, z)
@@ -103,7 +103,7 @@ class LinearPredictor:
         bias = s.share(s.fill(self.ring, 1 << self.frac, (x_fixed.shape[0], 1)), 1)  # bias_trick at bob
         x = s.share(x_fixed, 0)
         w = s.share(self.w, 0)
-        y = s.trunc_pr(self.frac, s.rep_dot_concat([bias, x], w))  # = dot(concatenate([bias, x], axis=1), w)
+        y = s.fixed_dot_concat(self.frac, [bias, x], w)  # = trunc_pr(dot(concatenate([bias, x], axis=1), w))
         if self.post == "sigmoid":
             y = s.sigmoid(self.integral, self.frac, y)
         elif self.post == "normalized_sigmoid":
@@ -320,7 +320,7 @@ class NeuralNetworkPredictor:
         s = self.sess
         x = s.share(x_fixed, 0)
         for i in range(len(self.w)):
-            y = s.trunc_pr(self.frac, s.rep_dot(x, s.share(self.w[i], 0)))
+            y = s.fixed_dot(self.frac, x, s.share(self.w[i], 0))
             z = s.rep_add(y, s.share(self.b[i], 0))
             act = self.activations[i]
             if act == "sigmoid":

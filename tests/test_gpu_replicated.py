@@ -221,3 +221,33 @@ def test_rep_dot_parity_tensor_pipe(bits, M, K, N):
     assert same_rep(gz, oz)
     assert same_ring(g.reveal(gz), mo.dot(mo.Ring(bits, a), mo.Ring(bits, b)))
     g.close()
+
+
+@pytest.mark.parametrize("bits,frac", [(64, 23), (128, 40)])
+def test_fixed_dot_and_fixed_mul_equal_the_two_call_sequence(bits, frac):
+    """mb_rep_fixed_dot / _dot_concat / _fixed_mul = DotOp / MulOp followed by TruncPrOp (fixedpoint/ops.rs:761-928,
+    548-672): the same entropy requests, the same result shares as the oracle's rep_dot / rep_mul + rep_trunc_pr, and
+    the entropy source is left where the two-call sequence leaves it (the next op's shares agree too)."""
+    g, o = pair()
+    rng = np.random.default_rng(bits)
+    for (M, K, N) in [(70, 33, 9), (256, 128, 64), (64, 513, 2)]:
+        a, b = rng.uniform(-1, 1, (M, K)), rng.uniform(-1, 1, (K, N))
+        gx = g.share(g.fixedpoint_encode(DT[bits], frac, g.from_host(mb.FLOAT64, a)), 0)
+        gy = g.share(g.fixedpoint_encode(DT[bits], frac, g.from_host(mb.FLOAT64, b)), 1)
+        ox, oy = mo.rep_share(o, mo.fixed_encode(bits, a, frac), 0), mo.rep_share(o, mo.fixed_encode(bits, b, frac), 1)
+        gz = g.fixed_dot(frac, gx, gy)
+        oz = mo.rep_trunc_pr(o, frac, mo.rep_dot(o, ox, oy))
+        assert same_rep(gz, oz)
+        gz2 = g.fixed_dot_concat(frac, [gx, gx], g.rep_concat(0, [gy, gy]))
+        oz2 = mo.rep_trunc_pr(o, frac, mo.rep_dot(o, mo.rep_concat(1, [ox, ox]), mo.rep_concat(0, [oy, oy])))
+        assert same_rep(gz2, oz2)
+        gm = g.fixed_mul(frac, gz, gz2)
+        om = mo.rep_trunc_pr(o, frac, mo.rep_mul(o, oz, oz2))
+        assert same_rep(gm, om)
+        assert np.abs(g.fixedpoint_decode(frac, g.reveal(gz)).to_host() - a @ b).max() < 1e-3
+    # broadcasting operands fall back to the two-call sequence, still the same shares
+    gs = g.share(g.fixedpoint_encode(DT[bits], frac, g.from_host(mb.FLOAT64, np.array([[0.5]]))), 2)
+    os_ = mo.rep_share(o, mo.fixed_encode(bits, np.array([[0.5]]), frac), 2)
+    assert same_rep(g.fixed_mul(frac, gz, gs), mo.rep_trunc_pr(o, frac, mo.rep_mul(o, oz, os_)))
+    assert same_rep(g.rep_mul(gz, gz), mo.rep_mul(o, oz, oz))       # entropy positions still agree afterwards
+    g.close()
