@@ -20,7 +20,7 @@ SOURCES = ["core.cpp", "hostcrypto.cpp", "api.cpp", "rep_api.cpp", "rep_math.cpp
            "rep.cu", "bits.cu", "bits_fused.cu", "math_fused.cu", "host_misc.cu", "shape_ops.cu", "storage.cu", "gemm_imad.cu", "gemm_limb.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-         "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function", "-x", "cu"]
+         "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function", "-x", "cu"] + os.environ.get("MOOSE_B200_NVCC_FLAGS", "").split()
 
 
 def _deps_mtime() -> float:

@@ -28,8 +28,12 @@
 #define AES_SMEM_BYTES (0x20000 - 1024)
 // block sizes by register budget: <= 64, <= 128, <= 255 registers per thread
 #define AES_TPB_LIGHT 1024
+#ifndef AES_TPB_MID
 #define AES_TPB_MID 512
+#endif
+#ifndef AES_TPB_384
 #define AES_TPB_384 384  /* <= 170 registers */
+#endif
 #define AES_TPB_HEAVY 256
 
 // Te0[x] = {2*S[x], S[x], S[x], 3*S[x]} as a little-endian word (one copy per translation unit,

@@ -98,7 +98,7 @@ __device__ __forceinline__ uint32_t plane_word(const Bits3 &W, int p, int64_t n,
 // inject(z) = (y0, z - y0 - y1, y1) with y0, y1 the adt_to_rep streams of that call (bits_fused.cu,
 // ring_inject_fused_kernel).
 template <int K>
-__global__ void __launch_bounds__(AES_TPB_MID) inject_sum_kernel(const __grid_constant__ InjectSumDesc d, Bits3 W, int64_t n,
+__global__ void __launch_bounds__(AES_TPB_LIGHT) inject_sum_kernel(const __grid_constant__ InjectSumDesc d, Bits3 W, int64_t n,
                                                                  CRing3 base, Ring3 out, int64_t nvec) {
   extern __shared__ __align__(16) uint32_t sT[];
   aes_load_table(sT);
@@ -228,7 +228,7 @@ __device__ __forceinline__ void trunc3(const TruncP &p, vec_t up, vec_t down, ve
 // One batch of a prefix-mul level: P[dst] = trunc_pr(P[src] * P[dst]) for up to 16 ops (keys: zero share of the
 // multiplication -- unused, see below -- then (r, y0, y1) of the truncation).  P is a [slots, n] ring buffer per share.
 template <int K>
-__global__ void __launch_bounds__(AES_TPB_384) mul_trunc_level_kernel(const __grid_constant__ MulTruncLevel lv, TruncP tp, Ring3 P, int64_t nvec) {
+__global__ void __launch_bounds__(AES_TPB_LIGHT) mul_trunc_level_kernel(const __grid_constant__ MulTruncLevel lv, TruncP tp, Ring3 P, int64_t nvec) {
   extern __shared__ __align__(16) uint32_t sT[];
   aes_load_table(sT);
   const AesLane L = aes_lane(sT);
@@ -259,7 +259,7 @@ __global__ void __launch_bounds__(AES_TPB_384) mul_trunc_level_kernel(const __gr
 
 // trunc_pr(x * y) on separate tensors (mb_rep_fixed_mul): the product's zero share cancels in the opened sum
 template <int K>
-__global__ void __launch_bounds__(AES_TPB_MID) mul_trunc_kernel(AesKey kr, AesKey k1, AesKey k2, TruncP tp, CRing3 x, CRing3 y, Ring3 out,
+__global__ void __launch_bounds__(AES_TPB_LIGHT) mul_trunc_kernel(AesKey kr, AesKey k1, AesKey k2, TruncP tp, CRing3 x, CRing3 y, Ring3 out,
                                                                 int64_t nvec) {
   extern __shared__ __align__(16) uint32_t sT[];
   aes_load_table(sT);
@@ -364,9 +364,9 @@ int k_inject_sum(mb_ctx *ctx, const InjectSumDesc &d, const mb_tensor *const W[3
   int live = 0;
   for (int i = 0; i < d.nplanes; i++) live += d.mult[i] != 0;
   if (t->dtype == MB_RING128)
-    AES_LAUNCH(ctx, inject_sum_kernel<VK_RING128>, AES_TPB_MID, nvec, d, w, n, b, o, nvec);
+    AES_LAUNCH(ctx, inject_sum_kernel<VK_RING128>, AES_TPB_LIGHT, nvec, d, w, n, b, o, nvec);
   else
-    AES_LAUNCH(ctx, inject_sum_kernel<VK_RING64>, AES_TPB_MID, nvec, d, w, n, b, o, nvec);
+    AES_LAUNCH(ctx, inject_sum_kernel<VK_RING64>, AES_TPB_LIGHT, nvec, d, w, n, b, o, nvec);
   MB_LAUNCH_CHECK_W(ctx, "inject_sum", 16.0 * nvec * (3 + (base ? 3 : 0)) + 3.0 * live * n / 8, 2.0 * live * nvec, 0);
   return MB_OK;
 }
@@ -411,9 +411,9 @@ int k_mul_trunc_level(mb_ctx *ctx, const MulTruncLevel &lv, unsigned amount, mb_
   for (int i = 0; i < 3; i++) ps.s[i] = (vec_t *)P[i]->dptr;
   const int64_t total = nvec * lv.nops;
   if (dt == MB_RING128)
-    AES_LAUNCH(ctx, mul_trunc_level_kernel<VK_RING128>, AES_TPB_384, total, lv, tp, ps, nvec);
+    AES_LAUNCH(ctx, mul_trunc_level_kernel<VK_RING128>, AES_TPB_LIGHT, total, lv, tp, ps, nvec);
   else
-    AES_LAUNCH(ctx, mul_trunc_level_kernel<VK_RING64>, AES_TPB_384, total, lv, tp, ps, nvec);
+    AES_LAUNCH(ctx, mul_trunc_level_kernel<VK_RING64>, AES_TPB_LIGHT, total, lv, tp, ps, nvec);
   MB_LAUNCH_CHECK_W(ctx, "mul_trunc_level", 16.0 * total * 9, 3.0 * total, 0);
   return MB_OK;
 }
@@ -441,9 +441,9 @@ int k_mul_trunc(mb_ctx *ctx, const AesKey tk[3], unsigned amount, const mb_rep *
   Ring3 os;
   for (int i = 0; i < 3; i++) { xs.s[i] = (const vec_t *)x->s[i]->dptr; ys.s[i] = (const vec_t *)y->s[i]->dptr; os.s[i] = (vec_t *)out[i]->dptr; }
   if (dt == MB_RING128)
-    AES_LAUNCH(ctx, mul_trunc_kernel<VK_RING128>, AES_TPB_MID, nvec, tk[0], tk[1], tk[2], tp, xs, ys, os, nvec);
+    AES_LAUNCH(ctx, mul_trunc_kernel<VK_RING128>, AES_TPB_LIGHT, nvec, tk[0], tk[1], tk[2], tp, xs, ys, os, nvec);
   else
-    AES_LAUNCH(ctx, mul_trunc_kernel<VK_RING64>, AES_TPB_MID, nvec, tk[0], tk[1], tk[2], tp, xs, ys, os, nvec);
+    AES_LAUNCH(ctx, mul_trunc_kernel<VK_RING64>, AES_TPB_LIGHT, nvec, tk[0], tk[1], tk[2], tp, xs, ys, os, nvec);
   MB_LAUNCH_CHECK_W(ctx, "mul_trunc", 16.0 * nvec * 9, 3.0 * nvec, 0);
   return MB_OK;
 }
