@@ -93,6 +93,10 @@ uint64_t mb_ctx_launch_count(const mb_ctx *ctx);
  * ring-GEMM main kernel are bracketed by CUDA events on the context stream.
  * mb_ctx_profile_read synchronises, returns the summed duration and launch count
  * since the last read and resets the counters.  kernel: 0 = tensor-pipe limb GEMM. */
+/* The PRF-consuming kernels run one CTA per SM that fills the SM's register file.  A context whose GPU also hosts
+ * long-lived small kernels of other streams (the spin waits of the peer-memory transport with several party lanes)
+ * leaves `count` SMs free so that its grids still run in one wave.  No counterpart in the reference. */
+int mb_ctx_reserve_sms(mb_ctx *ctx, int count);
 int mb_ctx_profile_enable(mb_ctx *ctx, int enable);
 int mb_ctx_profile_read(mb_ctx *ctx, int kernel, float *total_ms, uint64_t *launches);
 /* Per-kernel trace (measurement only; no counterpart in the reference, whose telemetry is

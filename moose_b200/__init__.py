@@ -67,7 +67,7 @@ ABI = {
     "mb_ctx_profile_enable": [_P, _I],
     "mb_ctx_profile_read": [_P, _I, ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_uint64)],
     "mb_sample_seeded_at": [_P, _I, _I, _I64P, _U8P, _U64, _PP],
-    "mb_ctx_trace_enable": [_P, _I], "mb_ctx_trace_read": [_P, _P, ctypes.c_size_t, ctypes.POINTER(ctypes.c_size_t)],
+    "mb_ctx_reserve_sms": [_P, _I], "mb_ctx_trace_enable": [_P, _I], "mb_ctx_trace_read": [_P, _P, ctypes.c_size_t, ctypes.POINTER(ctypes.c_size_t)],
     "mb_host_alloc_pinned": [_P, ctypes.c_size_t, _PP], "mb_host_free_pinned": [_P, _P],
     "mb_tensor_from_host": [_P, _I, _I, _I64P, _P, _PP], "mb_tensor_alloc": [_P, _I, _I, _I64P, _PP],
     "mb_tensor_to_host": [_P, _P, _P, ctypes.c_size_t], "mb_tensor_free": [_P, _P],
@@ -333,6 +333,9 @@ class Session:
         ms, n = ctypes.c_float(), ctypes.c_uint64()
         self._check(lib().mb_ctx_profile_read(self.ctx, kernel, ctypes.byref(ms), ctypes.byref(n)))
         return float(ms.value), int(n.value)
+
+    def reserve_sms(self, count: int):
+        self._check(lib().mb_ctx_reserve_sms(self.ctx, int(count)))
 
     def trace_enable(self, on: bool = True):
         self._check(lib().mb_ctx_trace_enable(self.ctx, 1 if on else 0))

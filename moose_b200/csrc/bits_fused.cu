@@ -24,7 +24,7 @@ constexpr int TPB = 256;
 
 // one CTA per SM: the AES table takes the CTA's shared-memory window up to 0x20000 (aes.cuh)
 inline int aes_grid(mb_ctx *ctx, int64_t items, int tpb) {
-  return (int)std::max<int64_t>(1, std::min<int64_t>((items + tpb - 1) / tpb, (int64_t)ctx->sm_count));
+  return (int)std::max<int64_t>(1, std::min<int64_t>((items + tpb - 1) / tpb, (int64_t)mb_aes_sms(ctx)));
 }
 
 #define AES_LAUNCH(ctx, kern, tpb, items, ...)                                                                  \

@@ -50,6 +50,7 @@ struct mb_ctx {
   std::mutex mu;             // guards entropy, setup, last-error bookkeeping
   std::mutex setup_mu;       // serialises the one-time generation of the replicated setup
   std::mutex gemm_mu;        // limb GEMM: scratch lookup + split + GEMM + recombine are enqueued as one unit
+  int reserve_sms;           // SMs the PRF kernels (one CTA per SM, whole register file) leave free for resident waits
   bool gemm_registered;      // counted in the per-device tally of contexts that run limb GEMMs
   uint8_t sid[16];
   bool deterministic;
@@ -114,6 +115,10 @@ mb_tensor *mb_tensor_retain(mb_tensor *t);
 // Zero-copy view of `nbytes`-aligned contents of `parent` starting at byte_offset (must be a multiple of 16).
 int mb_tensor_view(mb_ctx *ctx, const mb_tensor *parent, size_t byte_offset, int rank, const int64_t *shape, mb_tensor **out);
 bool mb_same_shape(const mb_tensor *a, const mb_tensor *b);
+// CTAs of a PRF kernel (one per SM): a 1024-thread CTA at 64 registers takes an SM's whole register file, so on a GPU
+// where other streams keep small kernels resident (the spin waits of the peer-memory transport, several party lanes) a
+// grid of sm_count CTAs runs in two waves; such contexts reserve a few SMs (mb_ctx_reserve_sms).
+static inline int mb_aes_sms(const mb_ctx *ctx) { return ctx->sm_count - ctx->reserve_sms > 0 ? ctx->sm_count - ctx->reserve_sms : 1; }
 int mb_scratch(mb_ctx *ctx, int slot, size_t bytes, void **out);
 // contexts on `device` that have launched the limb GEMM so far (the round barrier is used only by a sole one)
 int mb_gemm_ctx_register(mb_ctx *ctx);

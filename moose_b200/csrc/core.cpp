@@ -36,6 +36,7 @@ extern "C" int mb_ctx_create(int device, mb_ctx **out) {
   ctx->profile = false;
   ctx->trace = false;
   ctx->gemm_registered = false;
+  ctx->reserve_sms = 0;
   memset(ctx->scratch, 0, sizeof(ctx->scratch));
   memset(ctx->scratch_bytes, 0, sizeof(ctx->scratch_bytes));
   MB_CUDA(ctx, cudaSetDevice(device));
@@ -125,6 +126,11 @@ extern "C" uint64_t mb_ctx_launch_count(const mb_ctx *ctx) { return ctx ? ctx->l
 extern "C" int mb_ctx_set_fused_bits(mb_ctx *ctx, int enable) {
   if (!ctx) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_set_fused_bits: NULL ctx");
   ctx->fused_bits = enable != 0;
+  return MB_OK;
+}
+extern "C" int mb_ctx_reserve_sms(mb_ctx *ctx, int count) {
+  if (!ctx || count < 0 || count > 64) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "mb_ctx_reserve_sms: bad count");
+  ctx->reserve_sms = count;
   return MB_OK;
 }
 extern "C" int mb_ctx_set_gemm_mode(mb_ctx *ctx, int mode) {

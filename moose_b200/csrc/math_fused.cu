@@ -26,7 +26,7 @@ namespace {
   } while (0)
 
 inline int aes_grid(mb_ctx *ctx, int64_t items, int tpb) {
-  return (int)std::max<int64_t>(1, std::min<int64_t>((items + tpb - 1) / tpb, (int64_t)ctx->sm_count));
+  return (int)std::max<int64_t>(1, std::min<int64_t>((items + tpb - 1) / tpb, (int64_t)mb_aes_sms(ctx)));
 }
 
 __device__ __forceinline__ vec_t vx(vec_t a, vec_t b) { return make_ulonglong2(a.x ^ b.x, a.y ^ b.y); }

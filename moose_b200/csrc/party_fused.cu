@@ -7,7 +7,7 @@
 namespace {
 
 int aes_grid(mb_ctx *ctx, int64_t items, int tpb) {
-  return (int)std::max<int64_t>(1, std::min<int64_t>((items + tpb - 1) / tpb, (int64_t)ctx->sm_count));
+  return (int)std::max<int64_t>(1, std::min<int64_t>((items + tpb - 1) / tpb, (int64_t)mb_aes_sms(ctx)));
 }
 
 #define AES_LAUNCH(ctx, kern, tpb, items, ...)                                                                  \

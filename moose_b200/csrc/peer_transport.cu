@@ -113,6 +113,7 @@ int pfail(mb_peer_transport *t, const std::string &m) {
 // process on one GPU block each other for good; not used.)
 int enqueue_wait(mb_peer_transport *t, cudaStream_t s, uint64_t *word, uint64_t target) {
   k_peer_wait<<<1, 1, 0, s>>>(word, target, t->status);
+  if (t->ctx->trace && s == t->ctx->stream) mb_trace_mark(t->ctx, "peer_wait");   // time spent waiting for the peer
   return 0;
 }
 
@@ -163,6 +164,7 @@ int publish(mb_peer_transport *t, int q) {
   uint64_t *theirs = words(t->peer_in[q], slot_of(q, t->rank));
   k_peer_signal<<<1, 1, 0, t->ctx->stream>>>(theirs + W_DATA_FLAG, t->sent_data[q]);
   PCU(t, cudaGetLastError());
+  if (t->ctx->trace) mb_trace_mark(t->ctx, "peer_publish");
   return 0;
 }
 
@@ -171,6 +173,7 @@ int send_chunk(mb_peer_transport *t, int q, const uint8_t *src, size_t n) {
   uint8_t *where = nullptr;
   if (reserve(t, q, n, &where)) return 1;
   PCU(t, cudaMemcpyAsync(where, src, n, cudaMemcpyDefault, t->ctx->stream));
+  if (t->ctx->trace) mb_trace_mark(t->ctx, "peer_copy_into_ring", (double)n);
   return publish(t, q);
 }
 
@@ -184,8 +187,10 @@ int recv_chunk(mb_peer_transport *t, int p, uint8_t *dst, size_t n) {
   if (enqueue_wait(t, s, mine + W_DATA_FLAG, t->recv_data[p])) return 1;
   const uint8_t *ring = data_ring(t->inbox, t->nranks, C, slot_of(t->rank, p));
   PCU(t, cudaMemcpyAsync(dst, ring + pos, n, cudaMemcpyDeviceToDevice, s));
+  if (t->ctx->trace && s == t->ctx->stream) mb_trace_mark(t->ctx, "peer_copy_out_of_ring", 2.0 * (double)n);
   k_peer_signal<<<1, 1, 0, s>>>(theirs + W_DATA_ACK, t->recv_data[p]);
   PCU(t, cudaGetLastError());
+  if (t->ctx->trace && s == t->ctx->stream) mb_trace_mark(t->ctx, "peer_ack");
   return 0;
 }
 

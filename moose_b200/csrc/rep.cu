@@ -191,7 +191,7 @@ __global__ void __launch_bounds__(AES_TPB_MID) trunc_pr_kernel(AesKey kr, AesKey
 
 // one CTA per SM: the AES table takes the CTA's shared-memory window up to 0x20000 (aes.cuh)
 inline int aes_grid_for(mb_ctx *ctx, int64_t nvec, int tpb) {
-  return (int)std::max<int64_t>(1, std::min<int64_t>((nvec + tpb - 1) / tpb, (int64_t)ctx->sm_count));
+  return (int)std::max<int64_t>(1, std::min<int64_t>((nvec + tpb - 1) / tpb, (int64_t)mb_aes_sms(ctx)));
 }
 
 }  // namespace

@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(TPB) sample_bits_as_ring_kernel(AesKey key, T 
 
 int k_sample(mb_ctx *ctx, const AesKey &key, mb_tensor *out, bool bits_as_ring, uint64_t first_block) {
   if (out->numel == 0) return MB_OK;
-  int maxg = ctx->sm_count;  // one CTA per SM (aes.cuh)
+  int maxg = mb_aes_sms(ctx);  // one CTA per SM (aes.cuh)
   if (bits_as_ring) {
     int64_t nblocks = (out->numel + 127) / 128;
     int g = (int)std::min<int64_t>((nblocks + TPB - 1) / TPB, maxg);

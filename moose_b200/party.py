@@ -60,6 +60,9 @@ def run_fused_mlp(args, group=None):
         from moose_b200.party_rt import PeerMemory
         for lane in range(args.lanes):
             ls = sess if lane == 0 else mb.Session(local_rank, args.session_id, None)
+            # the other lanes' spin waits stay resident on some SMs: leave those free so PRF grids run in one wave
+            reserve = getattr(args, "reserve_sms", None)
+            ls.reserve_sms(max(0, args.lanes - 1) if reserve is None else reserve)
             pm = PeerMemory(ls, rank, roles, args.ring_mib << 20)
             handles = [None] * world
             dist.all_gather_object(handles, pm.handle_bytes(), group=group)   # bootstrap only: the inbox handles
@@ -84,7 +87,26 @@ def run_fused_mlp(args, group=None):
            for i, (ls, _, _) in enumerate(lanes)]
 
     def run_once():
-        outs = [m.forward(xf, rows) for m, xf in zip(mlps, xfs)]   # enqueue only: no lane waits for its stream here
+        if len(lanes) == 1:
+            outs = [mlps[0].forward(xfs[0], rows)]
+        else:
+            # one host thread per lane: a lane's host side waits for its peers' host messages (keys, seeds), which
+            # arrive at the pace of the slowest party, so lanes enqueued from one thread run one after the other
+            import threading
+            outs, errs = [None] * len(lanes), []
+
+            def work(i):
+                try:
+                    outs[i] = mlps[i].forward(xfs[i], rows)
+                except BaseException as e:  # noqa: BLE001
+                    errs.append(e)
+            ts = [threading.Thread(target=work, args=(i,)) for i in range(len(lanes))]
+            for t in ts:
+                t.start()
+            for t in ts:
+                t.join()
+            if errs:
+                raise errs[0]
         for ls, _, pt in lanes:
             pt.flush()
             ls.sync()
@@ -100,6 +122,15 @@ def run_fused_mlp(args, group=None):
         outs = run_once()
     dt = (time.perf_counter() - t0) / args.repeat
     dist.barrier(group=group)
+    trace = None
+    if getattr(args, "trace", False):      # one more inference with an event behind every launch: busy vs waiting per party
+        for ls, _, _ in lanes:
+            ls.trace_enable(True)
+        run_once()
+        trace = [ls.trace_read() for ls, _, _ in lanes]
+        for ls, _, _ in lanes:
+            ls.trace_enable(False)
+        dist.barrier(group=group)
     out = outs[0]
     sent = torch.tensor([sum(pt.bytes_sent for _, _, pt in lanes) - sent0], dtype=torch.int64, device=f"cuda:{local_rank}")
     dist.all_reduce(sent, group=group)
@@ -113,6 +144,8 @@ def run_fused_mlp(args, group=None):
         err = float(np.abs(out.to_host()[:8] - h).max())
     st1 = party.stats()
     mine = {k: (st1[k] - st0[k]) / args.repeat for k in st1}
+    if trace is not None:
+        mine["trace_ms"] = [{k: round(v["ms"], 3) for k, v in sorted(t.items(), key=lambda kv: -kv[1]["ms"])} for t in trace]
     gathered = [None] * world
     dist.all_gather_object(gathered, mine, group=group)
     record = None
@@ -158,6 +191,9 @@ def main():
                     help="with --peer-memory: split the batch over this many independent party sessions (own stream and "
                          "rings each); one lane's waits for its peers are filled by another lane's kernels")
     ap.add_argument("--ring-mib", type=int, default=1024, help="with --peer-memory: bytes of one ring, in MiB")
+    ap.add_argument("--trace", action="store_true", help="with --fused: per-launcher device time of one inference per party")
+    ap.add_argument("--reserve-sms", type=int, default=None,
+                    help="with --lanes: SMs the PRF kernels leave free (default lanes - 1: one resident wait per other lane)")
     ap.add_argument("--fused", action="store_true",
                     help="with --mlp: run the party runtime (csrc/party.cpp: party-sliced fused kernels, msb-pruned adder, "
                          "seeds on the wire) instead of the per-op lowered graph")
