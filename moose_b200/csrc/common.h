@@ -16,6 +16,7 @@
 #include "../../include/moose_b200.h"
 
 typedef unsigned __int128 u128;
+constexpr int64_t MB_MAX_NUMEL = (int64_t)1 << 40;   // 16 TB of Ring128: beyond any device; rejects wrapped / hostile shapes
 
 struct mb_tensor {
   mb_dtype dtype;

@@ -311,10 +311,12 @@ static int tensor_new_on(mb_ctx *ctx, cudaStream_t stream, mb_dtype dtype, int r
   if (rank < 0 || rank > MB_MAX_RANK) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "tensor: rank out of range");
   if (dtype != MB_RING64 && dtype != MB_RING128 && dtype != MB_BIT && dtype != MB_FLOAT64)
     return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "tensor: bad dtype");
+  // shapes can come straight off the wire (a peer's 10-word header): the element count must not wrap
   int64_t numel = 1;
   for (int i = 0; i < rank; i++) {
     if (shape[i] < 0) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "tensor: negative dimension");
-    numel *= shape[i];
+    if (__builtin_mul_overflow(numel, shape[i], &numel) || numel > MB_MAX_NUMEL)
+      return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "tensor: element count overflows / exceeds 2^40");
   }
   mb_tensor *t = new mb_tensor();
   t->dtype = dtype;
@@ -445,7 +447,9 @@ extern "C" int mb_tensor_free(mb_ctx *ctx, mb_tensor *t) {
 int mb_tensor_view(mb_ctx *ctx, const mb_tensor *parent, size_t byte_offset, int rank, const int64_t *shape, mb_tensor **out) {
   if (!ctx || !parent || !out || rank < 0 || rank > MB_MAX_RANK) return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "view: bad argument");
   int64_t numel = 1;
-  for (int i = 0; i < rank; i++) numel *= shape[i];
+  for (int i = 0; i < rank; i++)
+    if (shape[i] < 0 || __builtin_mul_overflow(numel, shape[i], &numel) || numel > MB_MAX_NUMEL)
+      return mb_fail(ctx, MB_ERR_INVALID_ARGUMENT, "view: bad shape");
   mb_tensor *t = new mb_tensor();
   t->dtype = parent->dtype;
   t->rank = rank;

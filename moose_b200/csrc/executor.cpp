@@ -519,9 +519,14 @@ struct Runner {
     if (xfer(0, peer, hdr, sizeof(hdr), 0) != 0) fail(MB_ERR_KERNEL, "transport: receive of header from " + peer + " failed");
     Val v;
     v.kind = (ValKind)hdr[0];
+    if (hdr[9] < 0) fail(MB_ERR_KERNEL, "transport: negative payload size in a header from " + peer);
     const size_t nbytes = (size_t)hdr[9];
+    if ((v.kind == V_BYTES || v.kind == V_STRING) && nbytes > 4096)   // host payloads travel in 4096-byte transport slots
+      fail(MB_ERR_KERNEL, "transport: host payload larger than a transport slot in a header from " + peer);
     if (v.kind == V_TENSOR) {
       if (hdr[2] < 0 || hdr[2] > MB_MAX_RANK) fail(MB_ERR_KERNEL, "transport: bad tensor header");
+      if (hdr[1] != MB_RING64 && hdr[1] != MB_RING128 && hdr[1] != MB_BIT && hdr[1] != MB_FLOAT64)
+        fail(MB_ERR_KERNEL, "transport: unknown dtype in a tensor header from " + peer);
       // receive buffer outside the stream order: the transfer can start while this party's kernels still run
       ck(e->stream_ordered ? mb_tensor_new(c, (mb_dtype)hdr[1], (int)hdr[2], hdr + 3, &v.t)
                            : mb_tensor_new_detached(c, (mb_dtype)hdr[1], (int)hdr[2], hdr + 3, &v.t));

@@ -78,6 +78,8 @@ struct mb_nccl_transport {
   uint8_t *host_slots;  // pinned, SLOTS x SLOT_BYTES
   uint8_t *dev_slots;
   int next_slot;
+  cudaEvent_t slot_done[64];  // recorded behind the last send that used the slot
+  bool slot_busy[64];
   std::deque<cudaEvent_t> posted;  // device sends in flight, oldest first
   std::vector<cudaEvent_t> pool;
   int64_t completed;
@@ -163,10 +165,18 @@ int nccl_transport_cb(void *user, int mode, const char *peer, void *buf, size_t 
   const int slot = t->next_slot;
   t->next_slot = (t->next_slot + 1) % SLOTS;
   uint8_t *h = t->host_slots + (size_t)slot * SLOT_BYTES, *dv = t->dev_slots + (size_t)slot * SLOT_BYTES;
+  // A send returns before its H2D copy and ncclSend have run (the Send blocks the stream until the peer posts its
+  // Recv): the slot is reused only after the event recorded behind its last use has completed.
+  if (t->slot_busy[slot]) {
+    CU(t, cudaEventSynchronize(t->slot_done[slot]));
+    t->slot_busy[slot] = false;
+  }
   if (mode == 1) {
     memcpy(h, buf, nbytes);
     CU(t, cudaMemcpyAsync(dv, h, nbytes, cudaMemcpyHostToDevice, t->stream));
     NC(t, t->api->Send(dv, nbytes, NCCL_UINT8, other, t->comm, t->stream));
+    CU(t, cudaEventRecord(t->slot_done[slot], t->stream));
+    t->slot_busy[slot] = true;
   } else {
     NC(t, t->api->Recv(dv, nbytes, NCCL_UINT8, other, t->comm, t->stream));
     CU(t, cudaMemcpyAsync(h, dv, nbytes, cudaMemcpyDeviceToHost, t->stream));
@@ -206,6 +216,7 @@ extern "C" int mb_nccl_transport_create(mb_ctx *ctx, const uint8_t unique_id[128
   t->comm = nullptr;
   t->stream = nullptr;
   t->host_slots = t->dev_slots = nullptr;
+  for (int i = 0; i < SLOTS; i++) { t->slot_done[i] = nullptr; t->slot_busy[i] = false; }
   for (int i = 0; i < nranks; i++) t->rank_of[role_names[i] ? role_names[i] : ""] = i;
   NcclUniqueId id;
   memcpy(id.internal, unique_id, 128);
@@ -217,6 +228,7 @@ extern "C" int mb_nccl_transport_create(mb_ctx *ctx, const uint8_t unique_id[128
   cudaError_t e = cudaStreamCreateWithFlags(&t->stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaMallocHost((void **)&t->host_slots, SLOTS * SLOT_BYTES);
   if (e == cudaSuccess) e = cudaMalloc((void **)&t->dev_slots, SLOTS * SLOT_BYTES);
+  for (int i = 0; i < SLOTS && e == cudaSuccess; i++) e = cudaEventCreateWithFlags(&t->slot_done[i], cudaEventDisableTiming);
   if (e != cudaSuccess) {
     mb_nccl_transport_free(t);
     return mb_fail(ctx, MB_ERR_CUDA, std::string("mb_nccl_transport_create: ") + cudaGetErrorString(e));
@@ -233,6 +245,8 @@ extern "C" int mb_nccl_transport_free(mb_nccl_transport *t) {
   if (t->stream) cudaStreamSynchronize(t->stream);
   for (auto ev : t->posted) cudaEventDestroy(ev);
   for (auto ev : t->pool) cudaEventDestroy(ev);
+  for (int i = 0; i < SLOTS; i++)
+    if (t->slot_done[i]) cudaEventDestroy(t->slot_done[i]);
   if (t->comm) t->api->CommDestroy(t->comm);
   if (t->host_slots) cudaFreeHost(t->host_slots);
   if (t->dev_slots) cudaFree(t->dev_slots);

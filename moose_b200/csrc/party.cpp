@@ -137,6 +137,8 @@ struct P {
     int64_t hdr[10] = {0};
     raw(0, peer, hdr, sizeof(hdr), 0);
     if (hdr[0] != 0 || hdr[2] < 0 || hdr[2] > MB_MAX_RANK) fail(MB_ERR_KERNEL, "party transport: expected a tensor");
+    if (hdr[1] != MB_RING64 && hdr[1] != MB_RING128 && hdr[1] != MB_BIT && hdr[1] != MB_FLOAT64)
+      fail(MB_ERR_KERNEL, "party transport: unknown dtype in a tensor header");
     mb_tensor *t = recv_buf((mb_dtype)hdr[1], (int)hdr[2], hdr + 3);
     T out(c, t);
     if ((int64_t)t->nbytes != hdr[9]) fail(MB_ERR_KERNEL, "party transport: payload size mismatch");

@@ -19,6 +19,8 @@
 
 #include "common.h"
 
+#include <cstdlib>
+
 namespace {
 
 constexpr size_t CTRL_SLOT = 4096;  // host payloads: headers, keys, seeds, short strings
@@ -57,12 +59,16 @@ __device__ __forceinline__ uint64_t globaltimer_ns() {
   return t;
 }
 
-// one thread: spin until *word >= target; gives up after WAIT_NS and raises *status (checked by flush)
-__global__ void k_peer_wait(const uint64_t *word, uint64_t target, int *status) {
+// one thread: spin until *word >= target; gives up after `wait_ns` and raises *status (checked by flush).  The
+// failure is sticky: once *status is set, later waits return at once and later signals publish nothing, so no
+// acknowledgement or data flag goes out for bytes that never arrived and the peers time out in turn instead of
+// computing on stale ring contents.
+__global__ void k_peer_wait(const uint64_t *word, uint64_t target, int *status, uint64_t wait_ns) {
+  if (*(volatile int *)status) return;
   const uint64_t t0 = globaltimer_ns();
   while (ld_acquire_sys(word) < target) {
     __nanosleep(200);
-    if (globaltimer_ns() - t0 > WAIT_NS) {
+    if (globaltimer_ns() - t0 > wait_ns) {
       *status = 1;
       return;
     }
@@ -70,7 +76,8 @@ __global__ void k_peer_wait(const uint64_t *word, uint64_t target, int *status) 
 }
 
 // one thread: everything before this kernel in the stream (the copy) is complete; publish the counter
-__global__ void k_peer_signal(uint64_t *word, uint64_t value) {
+__global__ void k_peer_signal(uint64_t *word, uint64_t value, const int *status) {
+  if (*(volatile const int *)status) return;
   __threadfence_system();
   asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(word), "l"(value) : "memory");
 }
@@ -91,6 +98,7 @@ struct mb_peer_transport {
   std::vector<HostRing *> peer_host;  // peer_host[q]: q's segment mapped here
   std::vector<bool> shm_mapped;
   int *status;  // device word: a wait timed out
+  uint64_t wait_ns;  // give-up time of a device-side wait (MOOSE_B200_PEER_TIMEOUT_S, default 60 s)
   int64_t posted;
   bool connected;
 };
@@ -112,7 +120,7 @@ int pfail(mb_peer_transport *t, const std::string &m) {
 // were measured instead: 48.1 ms against 43.3 ms per MLP batch with processes per GPU, and three contexts of one
 // process on one GPU block each other for good; not used.)
 int enqueue_wait(mb_peer_transport *t, cudaStream_t s, uint64_t *word, uint64_t target) {
-  k_peer_wait<<<1, 1, 0, s>>>(word, target, t->status);
+  k_peer_wait<<<1, 1, 0, s>>>(word, target, t->status, t->wait_ns);
   if (t->ctx->trace && s == t->ctx->stream) mb_trace_mark(t->ctx, "peer_wait");   // time spent waiting for the peer
   return 0;
 }
@@ -162,7 +170,7 @@ int reserve(mb_peer_transport *t, int q, size_t n, uint8_t **where) {
 }
 int publish(mb_peer_transport *t, int q) {
   uint64_t *theirs = words(t->peer_in[q], slot_of(q, t->rank));
-  k_peer_signal<<<1, 1, 0, t->ctx->stream>>>(theirs + W_DATA_FLAG, t->sent_data[q]);
+  k_peer_signal<<<1, 1, 0, t->ctx->stream>>>(theirs + W_DATA_FLAG, t->sent_data[q], t->status);
   PCU(t, cudaGetLastError());
   if (t->ctx->trace) mb_trace_mark(t->ctx, "peer_publish");
   return 0;
@@ -188,7 +196,7 @@ int recv_chunk(mb_peer_transport *t, int p, uint8_t *dst, size_t n) {
   const uint8_t *ring = data_ring(t->inbox, t->nranks, C, slot_of(t->rank, p));
   PCU(t, cudaMemcpyAsync(dst, ring + pos, n, cudaMemcpyDeviceToDevice, s));
   if (t->ctx->trace && s == t->ctx->stream) mb_trace_mark(t->ctx, "peer_copy_out_of_ring", 2.0 * (double)n);
-  k_peer_signal<<<1, 1, 0, s>>>(theirs + W_DATA_ACK, t->recv_data[p]);
+  k_peer_signal<<<1, 1, 0, s>>>(theirs + W_DATA_ACK, t->recv_data[p], t->status);
   PCU(t, cudaGetLastError());
   if (t->ctx->trace && s == t->ctx->stream) mb_trace_mark(t->ctx, "peer_ack");
   return 0;
@@ -332,6 +340,11 @@ extern "C" int mb_peer_transport_create(mb_ctx *ctx, int rank, int nranks, const
   t->shm_mapped.assign(nranks, false);
   t->inbox = nullptr;
   t->status = nullptr;
+  t->wait_ns = WAIT_NS;
+  if (const char *e = getenv("MOOSE_B200_PEER_TIMEOUT_S")) {
+    const double sec = atof(e);
+    if (sec > 0) t->wait_ns = (uint64_t)(sec * 1e9);
+  }
   t->host_in = nullptr;
   const int rc = peer_init(t);
   if (rc != MB_OK) {

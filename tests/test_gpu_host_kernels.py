@@ -353,3 +353,11 @@ def test_async_transfers_across_contexts():
     finally:
         for s in (loader, compute, drainer):
             s.close()
+
+
+def test_tensor_shapes_that_wrap_the_element_count_are_rejected(sess):
+    """Shapes can come off the wire (a peer's header): [2^32, 2^32] must not wrap to 0 elements."""
+    for shape in [(1 << 32, 1 << 32), (1 << 62, 4), (1 << 41,)]:
+        with pytest.raises(mb.MooseB200Error):
+            sess.alloc(RING64, shape)
+    assert sess.alloc(RING64, (0, 5)).numel == 0
