@@ -316,6 +316,14 @@ int mb_rep_free(mb_ctx *ctx, mb_rep *x);
 int mb_rep_setup(mb_ctx *ctx);
 /* ShareOp::ring_kernel (moose/src/replicated/convert.rs:49-160). */
 int mb_rep_share(mb_ctx *ctx, const mb_tensor *x, int owner, mb_rep **out);
+/* ShareOp::ring_kernel by a placement member (moose/src/replicated/convert.rs:72-129) with the expansion of
+ * the owner's PRF share postponed into the consumer: the sync key is drawn at this call (the reference's entropy
+ * order); mb_rep_dot_concat / mb_rep_fixed_dot_concat with a skinny right operand compute x_owner = PRF(seed),
+ * x_{owner+1} = x - x_owner, x_{owner+2} = 0 inside the dot kernel (same values, never written to memory);
+ * mb_rep_materialize writes the three share tensors like mb_rep_share.  Other entry points reject a handle that is
+ * still deferred (MB_ERR_INVALID_ARGUMENT). */
+int mb_rep_share_deferred(mb_ctx *ctx, const mb_tensor *x, int owner, mb_rep **out);
+int mb_rep_materialize(mb_ctx *ctx, mb_rep *x);
 /* RevealOp::host_ring_kernel (moose/src/replicated/convert.rs:280-313). */
 int mb_rep_reveal(mb_ctx *ctx, const mb_rep *x, int receiver, mb_tensor **out);
 /* AddOp/SubOp::rep_rep_kernel (moose/src/replicated/arith.rs:7-37,197-228);

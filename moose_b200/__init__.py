@@ -96,6 +96,7 @@ ABI = {
     "mb_bit_decompose_ring": [_P, _P, _PP], "mb_fixedpoint_mean": [_P, _I, _U64, _U32, _P, _PP],
     "mb_fixedpoint_argmax": [_P, _I, _P, _PP],
     "mb_rep_from_shares": [_P, _P, _P, _P, _PP], "mb_rep_share_tensor": [_P, _I], "mb_rep_free": [_P, _P],
+    "mb_rep_share_deferred": [_P, _P, _I, _PP], "mb_rep_materialize": [_P, _P],
     "mb_rep_setup": [_P], "mb_rep_share": [_P, _P, _I, _PP], "mb_rep_reveal": [_P, _P, _I, _PP],
     "mb_rep_add": [_P, _P, _P, _PP], "mb_rep_sub": [_P, _P, _P, _PP], "mb_rep_neg": [_P, _P, _PP],
     "mb_rep_shl": [_P, _U64, _P, _PP],
@@ -249,6 +250,7 @@ class RepTensor:
         self.h = None
 
     def share(self, i: int) -> Tensor:
+        self.sess._check(lib().mb_rep_materialize(self.sess.ctx, self.h))   # no-op unless the sharing was deferred
         return Tensor(self.sess, lib().mb_rep_share_tensor(self.h, i), owned=False)
 
     @property
@@ -667,8 +669,12 @@ class Session:
         out = self._out()
         return self._r(lib().mb_rep_from_shares(self.ctx, x0.h, x1.h, x2.h, ctypes.byref(out)), out)
 
-    def share(self, x: Tensor, owner: int = 0) -> RepTensor:
+    def share(self, x: Tensor, owner: int = 0, deferred: bool = False) -> RepTensor:
+        """ShareOp.  deferred=True (placement members only): the key is drawn now, the shares are expanded inside the
+        skinny dot that consumes them (rep_dot_concat / fixed_dot_concat) or on first access."""
         out = self._out()
+        if deferred:
+            return self._r(lib().mb_rep_share_deferred(self.ctx, x.h, owner, ctypes.byref(out)), out)
         return self._r(lib().mb_rep_share(self.ctx, x.h, owner, ctypes.byref(out)), out)
 
     def reveal(self, x: RepTensor, receiver: int = 0) -> Tensor:

@@ -31,8 +31,11 @@ struct mb_tensor {
   mb_tensor *parent;    // non-null: dptr points into parent's allocation (a retained, immutable view)
 };
 
+struct AesKey;
+struct mb_rep_deferred;   // a sharing whose PRF expansion is postponed into its consumer (rep_api.cpp)
 struct mb_rep {
   mb_tensor *s[3];
+  mb_rep_deferred *deferred;  // non-null: s[] are NULL until mb_rep_materialize
 };
 
 // AES-128 expanded key as 44 little-endian column words, plus the round-1 constants of the counter-mode
@@ -166,9 +169,15 @@ int k_gemm_imad(mb_ctx *ctx, mb_dtype dtype, const void *A, const void *B, void 
 // Skinny replicated dot, three parties in one pass; the left operand is the concatenation along K of `n` parts.
 struct RepDotPart { const void *x[3]; int64_t K; int64_t krow0; };
 struct RepDotParts { int n; RepDotPart p[4]; };
+// Parts whose sharing is deferred (ShareOp by a placement member, replicated/convert.rs:72-129): x_owner = PRF(key),
+// x_{owner+1} = plain - PRF(key), x_{owner+2} = 0, expanded inside the dot instead of written out and read back.
+struct RepDotDeferred { int owner[4]; const void *plain[4]; AesKey key[4]; };  // owner < 0: the part is materialised
 bool k_rep_dot_skinny_supported(int64_t M, int64_t N);
 int k_rep_dot_skinny(mb_ctx *ctx, mb_dtype dtype, const RepDotParts &parts, const void *const ysum[3], const void *const y[3],
                      void *const z[3], int64_t M, int64_t N);
+bool k_rep_dot_skinny_deferred_supported(mb_dtype dtype, const RepDotParts &parts, int64_t N);
+int k_rep_dot_skinny_deferred(mb_ctx *ctx, mb_dtype dtype, const RepDotParts &parts, const RepDotDeferred &lazy, const void *const ysum[3],
+                              const void *const y[3], void *const z[3], int64_t M, int64_t N);
 bool k_gemm_limb_supported(mb_dtype dtype, int64_t M, int64_t K, int64_t N);
 bool k_gemm_limb_preferred(int64_t M, int64_t K, int64_t N);
 // C = sum_t A_t * B_t for nterms (1 or 2) operand pairs, optional fused epilogue.
@@ -266,6 +275,12 @@ int k_pow2_bits(mb_ctx *ctx, const Pow2Desc &d, const mb_tensor *const W[3], int
 int mb_draw_zero_seeds(mb_ctx *ctx, AesKey seeds[3]);      // gen_zero_share: 3 x SyncKey (after the one-time setup)
 int mb_draw_inject_keys(mb_ctx *ctx, AesKey keys[2]);      // ring_inject: dabit (4 requests) + adt_to_rep (3): returns (y0, y1)
 int mb_draw_trunc_keys(mb_ctx *ctx, AesKey keys[3]);       // trunc_pr: mask (5 requests) + adt_to_rep (3): returns (r, y0, y1)
+
+struct mb_rep_deferred {   // see mb_rep_share_deferred (rep_api.cpp)
+  mb_tensor *src;          // the plain tensor (retained)
+  AesKey key;              // PRF stream of the owner's share
+  int owner;
+};
 
 // Fused replicated kernels (rep.cu)
 int k_rep_share(mb_ctx *ctx, const AesKey &key, int owner, const mb_tensor *x, mb_tensor *o0, mb_tensor *o1,

@@ -7,7 +7,7 @@
 //  * small / ragged problems (unit tests, KATs, rank-1 operands).
 // Integer arithmetic mod 2^k is associative and commutative, so the summation
 // order does not affect the result: bit-exact against ndarray's generic dot.
-#include "common.h"
+#include "vecops.cuh"
 
 namespace {
 
@@ -170,9 +170,142 @@ __global__ void __launch_bounds__(TPB) rep_dot_skinny_kernel(RepDotParts parts, 
   }
 }
 
+// One deferred part of one row (owner O, compile time): party O holds (r, d), party O+1 holds (d, 0), party O+2 holds
+// (0, r) with r = PRF block of the element, d = plain - r -- four products per element and output column:
+//   v_O     += r * (y_O + y_{O+1}) + d * y_O,   v_{O+1} += d * (y_{O+1} + y_{O+2}),   v_{O+2} += r * y_{O+2}
+template <typename T, int NC, int O>
+__device__ __forceinline__ void deferred_part(const AesLane &L, const AesKey &key, const T *__restrict__ xp, int64_t e0, int64_t K, int64_t r0,
+                                              int64_t N, int lane, const T *__restrict__ ybo, const T *__restrict__ ybn,
+                                              const T *__restrict__ yo, const T *__restrict__ yp, T (&acc)[3][NC]) {
+  constexpr int EPV = 16 / (int)sizeof(T);
+  constexpr int VK = sizeof(T) == 16 ? VK_RING128 : VK_RING64;
+  for (int64_t k = (int64_t)lane * EPV; k < K; k += 32 * EPV) {
+    const vec_t rv = prf_vec<VK>(L, key, (uint64_t)((e0 + k) / EPV));
+#pragma unroll
+    for (int e = 0; e < EPV; e++) {
+      T r;
+      if (sizeof(T) == 16) r = (T)v128(rv);
+      else r = (T)(e == 0 ? rv.x : rv.y);
+      const T d = xp[k + e] - r;
+      const int64_t row = (r0 + k + e) * N;
+#pragma unroll
+      for (int j = 0; j < NC; j++)
+        if (j < N) {
+          acc[O][j] += r * ybo[row + j] + d * yo[row + j];
+          acc[(O + 1) % 3][j] += d * ybn[row + j];
+          acc[(O + 2) % 3][j] += r * yp[row + j];
+        }
+    }
+  }
+}
+
+// The same with the PRF in the kernel: parts with lazy.owner[p] >= 0 are read from their PLAIN tensor and shared on the
+// fly (x_owner = PRF block of the element's vector, x_{owner+1} = plain - x_owner, x_{owner+2} = 0), exactly the values
+// share_kernel (rep.cu) would have written -- 8 GB per share at BASELINE config 3 that are neither written nor read.
+// One CTA per SM (the AES table), one warp per row; a lane takes the EPV = 16 / sizeof(T) elements of one AES block.
+template <typename T, int NC>
+__global__ void __launch_bounds__(AES_TPB_LIGHT) rep_dot_skinny_prf_kernel(RepDotParts parts, const __grid_constant__ RepDotDeferred lazy,
+                                                                           const T *__restrict__ yb0, const T *__restrict__ yb1,
+                                                                           const T *__restrict__ yb2, const T *__restrict__ y0,
+                                                                           const T *__restrict__ y1, const T *__restrict__ y2,
+                                                                           T *__restrict__ z0, T *__restrict__ z1, T *__restrict__ z2,
+                                                                           int64_t M, int64_t N) {
+  extern __shared__ __align__(16) uint32_t sT[];
+  aes_load_table(sT);
+  const AesLane L = aes_lane(sT);
+  constexpr int EPV = 16 / (int)sizeof(T);
+  constexpr int VK = sizeof(T) == 16 ? VK_RING128 : VK_RING64;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t m = warp; m < M; m += nwarps) {
+    T acc[3][NC];
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+      for (int j = 0; j < NC; j++) acc[i][j] = 0;
+    for (int p = 0; p < parts.n; p++) {
+      const int64_t K = parts.p[p].K, r0 = parts.p[p].krow0;
+      const int o = lazy.owner[p];
+      if (o < 0) {
+        const T *a0p = (const T *)parts.p[p].x[0] + m * K, *a1p = (const T *)parts.p[p].x[1] + m * K,
+                *a2p = (const T *)parts.p[p].x[2] + m * K;
+        for (int64_t k = lane; k < K; k += 32) {
+          const T a0 = a0p[k], a1 = a1p[k], a2 = a2p[k];
+          const int64_t row = (r0 + k) * N;
+#pragma unroll
+          for (int j = 0; j < NC; j++)
+            if (j < N) {
+              acc[0][j] += a0 * yb0[row + j] + a1 * y0[row + j];
+              acc[1][j] += a1 * yb1[row + j] + a2 * y1[row + j];
+              acc[2][j] += a2 * yb2[row + j] + a0 * y2[row + j];
+            }
+        }
+      } else {
+        const T *xp = (const T *)lazy.plain[p] + m * K;
+        if (o == 0) deferred_part<T, NC, 0>(L, lazy.key[p], xp, m * K, K, r0, N, lane, yb0, yb1, y0, y2, acc);
+        else if (o == 1) deferred_part<T, NC, 1>(L, lazy.key[p], xp, m * K, K, r0, N, lane, yb1, yb2, y1, y0, acc);
+        else deferred_part<T, NC, 2>(L, lazy.key[p], xp, m * K, K, r0, N, lane, yb2, yb0, y2, y1, acc);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+      for (int j = 0; j < NC; j++) {
+        T v = acc[i][j];
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+          uint64_t lo = __shfl_xor_sync(0xffffffffu, (uint64_t)v, off);
+          if (sizeof(T) == 16) {
+            uint64_t hi = __shfl_xor_sync(0xffffffffu, (uint64_t)((u128)v >> 64), off);
+            v += (T)(((u128)hi << 64) | lo);
+          } else {
+            v += (T)lo;
+          }
+        }
+        if (lane == 0 && j < N) (i == 0 ? z0 : i == 1 ? z1 : z2)[m * N + j] = v;
+      }
+  }
+}
+
 }  // namespace
 
 bool k_rep_dot_skinny_supported(int64_t M, int64_t N) { return N <= 32 && M >= 64; }
+
+// the PRF is evaluated once per element only if all output columns fit one register chunk; rows must start on AES blocks
+bool k_rep_dot_skinny_deferred_supported(mb_dtype dtype, const RepDotParts &parts, int64_t N) {
+  const int epv = dtype == MB_RING128 ? 1 : 2, nc = dtype == MB_RING128 ? 2 : 4;
+  if (N > nc) return false;
+  for (int p = 0; p < parts.n; p++)
+    if (parts.p[p].K % epv) return false;
+  return true;
+}
+
+int k_rep_dot_skinny_deferred(mb_ctx *ctx, mb_dtype dtype, const RepDotParts &parts, const RepDotDeferred &lazy, const void *const ysum[3],
+                              const void *const y[3], void *const z[3], int64_t M, int64_t N) {
+  if (M == 0 || N == 0) return MB_OK;
+  const int g = (int)std::max<int64_t>(1, std::min<int64_t>((M * 32 + AES_TPB_LIGHT - 1) / AES_TPB_LIGHT, (int64_t)mb_aes_sms(ctx)));
+  double kt = 0, kprf = 0, kmat = 0;
+  for (int i = 0; i < parts.n; i++) {
+    kt += (double)parts.p[i].K;
+    if (lazy.owner[i] >= 0) kprf += (double)parts.p[i].K; else kmat += (double)parts.p[i].K;
+  }
+  const double w = dtype == MB_RING128 ? 16.0 : 8.0;
+  if (dtype == MB_RING128) {
+    MB_CUDA(ctx, cudaFuncSetAttribute(rep_dot_skinny_prf_kernel<u128, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, AES_SMEM_BYTES));
+    rep_dot_skinny_prf_kernel<u128, 2><<<g, AES_TPB_LIGHT, AES_SMEM_BYTES, ctx->stream>>>(
+        parts, lazy, (const u128 *)ysum[0], (const u128 *)ysum[1], (const u128 *)ysum[2], (const u128 *)y[0], (const u128 *)y[1],
+        (const u128 *)y[2], (u128 *)z[0], (u128 *)z[1], (u128 *)z[2], M, N);
+  } else {
+    MB_CUDA(ctx, cudaFuncSetAttribute(rep_dot_skinny_prf_kernel<uint64_t, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, AES_SMEM_BYTES));
+    rep_dot_skinny_prf_kernel<uint64_t, 4><<<g, AES_TPB_LIGHT, AES_SMEM_BYTES, ctx->stream>>>(
+        parts, lazy, (const uint64_t *)ysum[0], (const uint64_t *)ysum[1], (const uint64_t *)ysum[2], (const uint64_t *)y[0],
+        (const uint64_t *)y[1], (const uint64_t *)y[2], (uint64_t *)z[0], (uint64_t *)z[1], (uint64_t *)z[2], M, N);
+  }
+  // plain operand read once, materialised parts three shares once, result written once; one AES block per 16 plain bytes
+  MB_LAUNCH_CHECK_W(ctx, "rep_dot_skinny_deferred", w * ((double)M * (kprf + 3.0 * kmat) + 3.0 * M * N), (double)M * kprf * w / 16.0, 0);
+  return MB_OK;
+}
 
 int k_rep_dot_skinny(mb_ctx *ctx, mb_dtype dtype, const RepDotParts &parts, const void *const ysum[3], const void *const y[3],
                      void *const z[3], int64_t M, int64_t N) {

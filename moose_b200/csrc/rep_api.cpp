@@ -44,6 +44,7 @@ struct RepTmp {
 mb_rep *rep_make(mb_tensor *a, mb_tensor *b, mb_tensor *c) {
   mb_rep *r = new mb_rep();
   r->s[0] = a; r->s[1] = b; r->s[2] = c;
+  r->deferred = nullptr;
   return r;
 }
 
@@ -66,6 +67,7 @@ int rep_alloc(mb_ctx *ctx, mb_dtype d, int rank, const int64_t *shape, mb_rep **
 }
 
 bool rep_valid(const mb_rep *x) { return x && x->s[0] && x->s[1] && x->s[2]; }
+int alloc3(mb_ctx *ctx, const mb_tensor *like, mb_tensor *z[3]);
 
 int ensure_setup(mb_ctx *ctx) {
   // RepSetup: k00, k11, k22 generated in this order (replicated/setup.rs:46-48);
@@ -214,6 +216,10 @@ extern "C" const mb_tensor *mb_rep_share_tensor(const mb_rep *x, int i) { return
 extern "C" int mb_rep_free(mb_ctx *ctx, mb_rep *x) {
   if (!x) return MB_OK;
   for (int i = 0; i < 3; i++) mb_tensor_free(ctx, x->s[i]);
+  if (x->deferred) {
+    mb_tensor_free(ctx, x->deferred->src);
+    delete x->deferred;
+  }
   delete x;
   return MB_OK;
 }
@@ -249,6 +255,45 @@ extern "C" int mb_rep_share(mb_ctx *ctx, const mb_tensor *x, int owner, mb_rep *
     MB_CHECK(k_rep_share_outsider(ctx, k0, k1, x, r.p->s[0], r.p->s[1], r.p->s[2]));
   }
   *out = r.release();
+  return MB_OK;
+}
+
+// ShareOp by a placement member with the PRF expansion postponed: the sync key is drawn NOW (the reference's entropy
+// order), the shares x_owner = PRF(seed), x_{owner+1} = x - x_owner, x_{owner+2} = 0 are produced by the consumer --
+// mb_rep_dot_concat / mb_rep_fixed_dot_concat expand them inside the skinny dot kernel -- or by mb_rep_materialize.
+// Any other entry point rejects a deferred handle as a NULL argument (it has no share tensors yet).
+extern "C" int mb_rep_share_deferred(mb_ctx *ctx, const mb_tensor *x, int owner, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_share_deferred");
+  MB_REQUIRE(ctx, x && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_share_deferred: NULL argument");
+  MB_REQUIRE(ctx, mb_is_ring(x->dtype), MB_ERR_TYPE_MISMATCH, "mb_rep_share_deferred: needs a ring tensor");
+  MB_REQUIRE(ctx, owner >= 0 && owner <= 2, MB_ERR_INVALID_ARGUMENT, "mb_rep_share_deferred: owner must be a placement member (0..2)");
+  MB_CHECK(ensure_setup(ctx));
+  uint8_t sync[16];
+  MB_CHECK(mb_entropy16(ctx, sync));
+  mb_rep *r = rep_make(nullptr, nullptr, nullptr);
+  r->deferred = new mb_rep_deferred();
+  r->deferred->src = mb_tensor_retain(const_cast<mb_tensor *>(x));
+  r->deferred->owner = owner;
+  seed_to_aes(ctx, sync, ctx->setup_keys[owner], &r->deferred->key);
+  *out = r;
+  return MB_OK;
+}
+extern "C" int mb_rep_materialize(mb_ctx *ctx, mb_rep *x) {
+  MB_ENTER(ctx, "mb_rep_materialize");
+  MB_REQUIRE(ctx, x, MB_ERR_INVALID_ARGUMENT, "mb_rep_materialize: NULL argument");
+  if (!x->deferred) return MB_OK;
+  mb_rep_deferred *d = x->deferred;
+  mb_tensor *z[3];
+  MB_CHECK(alloc3(ctx, d->src, z));
+  int rc = k_rep_share(ctx, d->key, d->owner, d->src, z[0], z[1], z[2]);
+  if (rc != MB_OK) {
+    for (int i = 0; i < 3; i++) mb_tensor_free(ctx, z[i]);
+    return rc;
+  }
+  for (int i = 0; i < 3; i++) x->s[i] = z[i];
+  mb_tensor_free(ctx, d->src);
+  delete d;
+  x->deferred = nullptr;
   return MB_OK;
 }
 
@@ -422,6 +467,18 @@ static int rep_dot_skinny(mb_ctx *ctx, mb_dtype dt, const RepDotParts &parts, co
   return k_rep_dot_skinny(ctx, dt, parts, ysum, yy, zz, M, N);
 }
 
+static int rep_dot_skinny_deferred(mb_ctx *ctx, mb_dtype dt, const RepDotParts &parts, const RepDotDeferred &lazy, const mb_rep *y, mb_rep *z,
+                                   int64_t M, int64_t N) {
+  Tmp ys0(ctx), ys1(ctx), ys2(ctx);
+  MB_CHECK(mb_add(ctx, y->s[0], y->s[1], &ys0.p));
+  MB_CHECK(mb_add(ctx, y->s[1], y->s[2], &ys1.p));
+  MB_CHECK(mb_add(ctx, y->s[2], y->s[0], &ys2.p));
+  const void *ysum[3] = {ys0.p->dptr, ys1.p->dptr, ys2.p->dptr};
+  const void *yy[3] = {y->s[0]->dptr, y->s[1]->dptr, y->s[2]->dptr};
+  void *zz[3] = {z->s[0]->dptr, z->s[1]->dptr, z->s[2]->dptr};
+  return k_rep_dot_skinny_deferred(ctx, dt, parts, lazy, ysum, yy, zz, M, N);
+}
+
 // dot(concatenate(xs, axis = 1), y) without materialising the concatenation when the skinny kernel applies
 // (LinearPredictor's bias trick, pymoose linear_predictor.py:33-58: the [B, 1 + features] operand is 8 GB per share
 // at BASELINE config 3).  Same values, same zero share, hence the same shares as ConcatOp + DotOp.
@@ -432,9 +489,11 @@ static int rep_dot_concat_core(mb_ctx *ctx, const mb_rep *const *xs, int n, cons
   const mb_dtype dt = y->s[0]->dtype;
   bool fused = n <= 4 && mb_is_ring(dt) && y->s[0]->rank == 2 && ctx->gemm_mode != 2;
   int64_t M = 0, Ktot = 0;
+  bool any_deferred = false;
   for (int p = 0; p < n; p++) {
-    MB_REQUIRE(ctx, rep_valid(xs[p]), MB_ERR_INVALID_ARGUMENT, "mb_rep_dot_concat: NULL argument");
-    const mb_tensor *t = xs[p]->s[0];
+    MB_REQUIRE(ctx, xs[p] && (rep_valid(xs[p]) || xs[p]->deferred), MB_ERR_INVALID_ARGUMENT, "mb_rep_dot_concat: NULL argument");
+    const mb_tensor *t = xs[p]->deferred ? xs[p]->deferred->src : xs[p]->s[0];
+    any_deferred = any_deferred || xs[p]->deferred;
     if (t->dtype != dt || t->rank != 2 || (p && t->shape[0] != M)) fused = false;
     if (p == 0) M = t->rank ? t->shape[0] : 0;
     Ktot += t->rank == 2 ? t->shape[1] : 0;
@@ -442,24 +501,38 @@ static int rep_dot_concat_core(mb_ctx *ctx, const mb_rep *const *xs, int n, cons
   const int64_t N = y->s[0]->rank == 2 ? y->s[0]->shape[1] : 0;
   fused = fused && Ktot == y->s[0]->shape[0] && k_rep_dot_skinny_supported(M, N) &&
           !(ctx->gemm_mode == 0 && k_gemm_limb_supported(dt, M, 2 * Ktot, N) && k_gemm_limb_preferred(M, 2 * Ktot, N));
+  RepDotParts parts;
+  RepDotDeferred lazy;
+  if (fused) {
+    parts.n = n;
+    int64_t row = 0;
+    for (int p = 0; p < n; p++) {
+      const mb_rep_deferred *d = xs[p]->deferred;
+      lazy.owner[p] = d ? d->owner : -1;
+      lazy.plain[p] = d ? d->src->dptr : nullptr;
+      if (d) lazy.key[p] = d->key;
+      for (int i = 0; i < 3; i++) parts.p[p].x[i] = d ? nullptr : xs[p]->s[i]->dptr;
+      parts.p[p].K = d ? d->src->shape[1] : xs[p]->s[0]->shape[1];
+      parts.p[p].krow0 = row;
+      row += parts.p[p].K;
+    }
+  }
+  const bool in_kernel = fused && any_deferred && ctx->fused_bits && k_rep_dot_skinny_deferred_supported(dt, parts, N);
+  if (any_deferred && !in_kernel) {
+    // no kernel expands the sharing for this shape: write the shares out (what mb_rep_share would have done) and go on
+    for (int p = 0; p < n; p++) MB_CHECK(mb_rep_materialize(ctx, const_cast<mb_rep *>(xs[p])));
+    return rep_dot_concat_core(ctx, xs, n, y, zero_share, out);
+  }
   if (!fused) {
     RepTmp cat(ctx);
     MB_CHECK(mb_rep_concat(ctx, 1, xs, n, &cat.p));
     return rep_dot_core(ctx, cat.p, y, zero_share, out);
   }
-  RepDotParts parts;
-  parts.n = n;
-  int64_t row = 0;
-  for (int p = 0; p < n; p++) {
-    for (int i = 0; i < 3; i++) parts.p[p].x[i] = xs[p]->s[i]->dptr;
-    parts.p[p].K = xs[p]->s[0]->shape[1];
-    parts.p[p].krow0 = row;
-    row += parts.p[p].K;
-  }
   RepTmp z(ctx);
   const int64_t oshape[2] = {M, N};
   MB_CHECK(rep_alloc(ctx, dt, 2, oshape, &z.p));
-  MB_CHECK(rep_dot_skinny(ctx, dt, parts, y, z.p, M, N));
+  if (in_kernel) MB_CHECK(rep_dot_skinny_deferred(ctx, dt, parts, lazy, y, z.p, M, N));
+  else MB_CHECK(rep_dot_skinny(ctx, dt, parts, y, z.p, M, N));
   AesKey seeds[3];
   MB_CHECK(gen_zero_seeds(ctx, seeds));
   if (zero_share) MB_CHECK(k_add_zero_share(ctx, seeds, z.p->s, z.p->s));

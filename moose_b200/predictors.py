@@ -101,7 +101,7 @@ class LinearPredictor:
         """x_fixed: [B, features] fixed-point host tensor at alice (no bias column)."""
         s = self.sess
         bias = s.share(s.fill(self.ring, 1 << self.frac, (x_fixed.shape[0], 1)), 1)  # bias_trick at bob
-        x = s.share(x_fixed, 0)
+        x = s.share(x_fixed, 0, deferred=True)   # the [B, features] sharing is expanded inside the dot, never stored
         w = s.share(self.w, 0)
         y = s.fixed_dot_concat(self.frac, [bias, x], w)  # = trunc_pr(dot(concatenate([bias, x], axis=1), w))
         if self.post == "sigmoid":

@@ -251,3 +251,34 @@ def test_fixed_dot_and_fixed_mul_equal_the_two_call_sequence(bits, frac):
     assert same_rep(g.fixed_mul(frac, gz, gs), mo.rep_trunc_pr(o, frac, mo.rep_mul(o, oz, os_)))
     assert same_rep(g.rep_mul(gz, gz), mo.rep_mul(o, oz, oz))       # entropy positions still agree afterwards
     g.close()
+
+
+@pytest.mark.parametrize("bits,frac,N", [(128, 40, 2), (64, 23, 4), (64, 23, 3), (128, 40, 5)])
+@pytest.mark.parametrize("owner", [0, 1, 2])
+def test_deferred_share_expanded_inside_the_skinny_dot(bits, frac, N, owner):
+    """mb_rep_share_deferred + mb_rep_(fixed_)dot_concat: the owner's PRF share is expanded inside the dot kernel (or,
+    where no kernel takes it -- N = 5 on Ring128 here -- written out first); the result shares are those of ShareOp +
+    ConcatOp + DotOp (+ TruncPrOp) on the oracle, and accessing a share of the deferred handle materialises exactly
+    what ShareOp writes."""
+    g, o = pair()
+    rng = np.random.default_rng(bits + N + owner)
+    M, K = 96, 34
+    a, b = rng.uniform(-1, 1, (M, K)), rng.uniform(-1, 1, (K + 1, N))
+    ones = np.ones((M, 1))
+    ga, gb, g1 = (g.fixedpoint_encode(DT[bits], frac, g.from_host(mb.FLOAT64, v)) for v in (a, b, ones))
+    oa, ob, o1 = (mo.fixed_encode(bits, v, frac) for v in (a, b, ones))
+    gbias, obias = g.share(g1, 1), mo.rep_share(o, o1, 1)
+    gx = g.share(ga, owner, deferred=True)
+    ox = mo.rep_share(o, oa, owner)
+    gw, ow = g.share(gb, 0), mo.rep_share(o, ob, 0)
+    with pytest.raises(mb.MooseB200Error):
+        g.rep_add(gx, gx)                       # a deferred handle is only accepted by its consumers
+    gz = g.fixed_dot_concat(frac, [gbias, gx], gw)
+    oz = mo.rep_trunc_pr(o, frac, mo.rep_dot(o, mo.rep_concat(1, [obias, ox]), ow))
+    assert same_rep(gz, oz)
+    gz2 = g.rep_dot_concat([gbias, gx], gw)     # with the zero share
+    oz2 = mo.rep_dot(o, mo.rep_concat(1, [obias, ox]), ow)
+    assert same_rep(gz2, oz2)
+    assert same_rep(gx, ox)                     # materialised on access: exactly ShareOp's tensors
+    assert same_rep(g.rep_add(gx, gx), mo.rep_add(ox, ox))
+    g.close()
