@@ -263,6 +263,7 @@ struct PolyCombine {             // out = trunc_pr(sum_{i < degree} P[i] * coeff
   AesKey keys[3];
 };
 int k_mul_trunc(mb_ctx *ctx, const AesKey tk[3], unsigned amount, const mb_rep *x, const mb_rep *y, mb_tensor *const out[3]);
+int k_maximum_select(mb_ctx *ctx, const AesKey keys[8], const mb_rep *lesser, const mb_rep *m1, const mb_rep *m2, mb_tensor *const out[3]);
 int k_replicate(mb_ctx *ctx, const mb_rep *x, mb_tensor *const P[3], int slots);
 int k_mul_trunc_level(mb_ctx *ctx, const MulTruncLevel &lv, unsigned amount, mb_tensor *const P[3], int64_t nvec);
 int k_poly_combine(mb_ctx *ctx, const PolyCombine &pc, unsigned amount, mb_tensor *const P[3], mb_tensor *const out[3]);

@@ -283,6 +283,49 @@ __global__ void __launch_bounds__(AES_TPB_LIGHT) mul_trunc_kernel(AesKey kr, Aes
   }
 }
 
+// The select of MaximumOp (replicated/softmax.rs:40-50) after the comparison bit: with l = ring_inject(lesser, 0)
+//   out = l * m2 + (ones - l) * m1          (two replicated multiplications, a public subtraction, an addition)
+// in one pass: reads the bit shares and the six ring shares, writes three; 2 + 3 + 3 PRF streams.
+//   l = (y0, s - y0 - y1, y1)   [s = the shared bit]      om = (1 - l_0, -l_1, -l_2)      (arith.rs:230-273)
+template <int K>
+__global__ void __launch_bounds__(AES_TPB_MID) maximum_select_kernel(AesKey ky0, AesKey ky1, AesKey a0k, AesKey a1k, AesKey a2k, AesKey b0k,
+                                                                     AesKey b1k, AesKey b2k, Bits3 lesser, CRing3 m1, CRing3 m2, Ring3 out,
+                                                                     int64_t nvec) {
+  extern __shared__ __align__(16) uint32_t sT[];
+  aes_load_table(sT);
+  const AesLane L = aes_lane(sT);
+  typedef VOps<K> O;
+  constexpr int EPV = K == VK_RING128 ? 1 : 2;
+  const vec_t one = O::splat(1, 0);
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t e = v * EPV;
+    const uint32_t w = plane_word(lesser, 0, 0, e);
+    const unsigned sh = (unsigned)(e & 31);
+    vec_t s;
+    if (K == VK_RING128) s = make_ulonglong2((w >> sh) & 1u, 0);
+    else s = make_ulonglong2((w >> sh) & 1u, (w >> (sh + 1)) & 1u);
+    const vec_t l0 = prf_vec<K>(L, ky0, (uint64_t)v);
+    const vec_t l2 = prf_vec<K>(L, ky1, (uint64_t)v);
+    const vec_t l1 = O::sub(O::sub(s, l0), l2);
+    const vec_t p0 = m2.s[0][v], p1 = m2.s[1][v], p2 = m2.s[2][v];
+    const vec_t q0 = m1.s[0][v], q1 = m1.s[1][v], q2 = m1.s[2][v];
+    const vec_t ra0 = prf_vec<K>(L, a0k, (uint64_t)v), ra1 = prf_vec<K>(L, a1k, (uint64_t)v), ra2 = prf_vec<K>(L, a2k, (uint64_t)v);
+    // a = l * m2
+    const vec_t a0 = O::add(O::add(O::mul(l0, O::add(p0, p1)), O::mul(l1, p0)), O::sub(ra0, ra1));
+    const vec_t a1 = O::add(O::add(O::mul(l1, O::add(p1, p2)), O::mul(l2, p1)), O::sub(ra1, ra2));
+    const vec_t a2 = O::add(O::add(O::mul(l2, O::add(p2, p0)), O::mul(l0, p2)), O::sub(ra2, ra0));
+    // b = (ones - l) * m1
+    const vec_t n0 = O::sub(one, l0), n1 = O::neg(l1), n2 = O::neg(l2);
+    const vec_t rb0 = prf_vec<K>(L, b0k, (uint64_t)v), rb1 = prf_vec<K>(L, b1k, (uint64_t)v), rb2 = prf_vec<K>(L, b2k, (uint64_t)v);
+    const vec_t b0 = O::add(O::add(O::mul(n0, O::add(q0, q1)), O::mul(n1, q0)), O::sub(rb0, rb1));
+    const vec_t b1 = O::add(O::add(O::mul(n1, O::add(q1, q2)), O::mul(n2, q1)), O::sub(rb1, rb2));
+    const vec_t b2 = O::add(O::add(O::mul(n2, O::add(q2, q0)), O::mul(n0, q2)), O::sub(rb2, rb0));
+    out.s[0][v] = O::add(a0, b0);
+    out.s[1][v] = O::add(a1, b1);
+    out.s[2][v] = O::add(a2, b2);
+  }
+}
+
 // P[i] = x for i < slots (the `degree` copies of x that prefix_op starts from)
 __global__ void replicate_kernel(CRing3 x, Ring3 P, int slots, int64_t nvec) {
   for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
@@ -445,5 +488,29 @@ int k_mul_trunc(mb_ctx *ctx, const AesKey tk[3], unsigned amount, const mb_rep *
   else
     AES_LAUNCH(ctx, mul_trunc_kernel<VK_RING64>, AES_TPB_LIGHT, nvec, tk[0], tk[1], tk[2], tp, xs, ys, os, nvec);
   MB_LAUNCH_CHECK_W(ctx, "mul_trunc", 16.0 * nvec * 9, 3.0 * nvec, 0);
+  return MB_OK;
+}
+
+// keys: inject (y0, y1), zero share of l * m2 (3), zero share of (ones - l) * m1 (3)
+int k_maximum_select(mb_ctx *ctx, const AesKey keys[8], const mb_rep *lesser, const mb_rep *m1, const mb_rep *m2, mb_tensor *const out[3]) {
+  const mb_tensor *t = out[0];
+  if (t->numel == 0) return MB_OK;
+  const int64_t nvec = vec_count(t);
+  Bits3 lb;
+  CRing3 a, b;
+  Ring3 o;
+  for (int i = 0; i < 3; i++) {
+    lb.s[i] = (const uint32_t *)lesser->s[i]->dptr;
+    a.s[i] = (const vec_t *)m1->s[i]->dptr;
+    b.s[i] = (const vec_t *)m2->s[i]->dptr;
+    o.s[i] = (vec_t *)out[i]->dptr;
+  }
+#define ARGS keys[0], keys[1], keys[2], keys[3], keys[4], keys[5], keys[6], keys[7], lb, a, b, o, nvec
+  if (t->dtype == MB_RING128)
+    AES_LAUNCH(ctx, maximum_select_kernel<VK_RING128>, AES_TPB_MID, nvec, ARGS);
+  else
+    AES_LAUNCH(ctx, maximum_select_kernel<VK_RING64>, AES_TPB_MID, nvec, ARGS);
+#undef ARGS
+  MB_LAUNCH_CHECK_W(ctx, "maximum_select", 16.0 * nvec * 9 + 3.0 * t->numel / 8, 8.0 * nvec, 0);
   return MB_OK;
 }

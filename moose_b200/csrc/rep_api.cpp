@@ -891,6 +891,20 @@ extern "C" int mb_rep_maximum(mb_ctx *ctx, const mb_rep *const *xs, int n, mb_re
   mb_dtype dt = m1.p->s[0]->dtype;
   RepTmp lesser(ctx), lr(ctx), a(ctx), om(ctx), b(ctx);
   MB_CHECK(mb_rep_less(ctx, m1.p, m2.p, &lesser.p));
+  if (ctx->fused_bits && mb_is_ring(dt) && uniform_shapes(m1.p, m2.p) && m1.p->s[0]->numel > 0 && mb_same_shape(lesser.p->s[0], m1.p->s[0]) &&
+      lesser.p->s[0]->dtype == MB_BIT) {
+    // ring_inject, the two multiplications, the public subtraction and the addition in one pass; keys in the op order
+    // below (ring_inject, mul, mul)
+    AesKey keys[8];
+    MB_CHECK(mb_draw_inject_keys(ctx, keys));
+    MB_CHECK(gen_zero_seeds(ctx, keys + 2));
+    MB_CHECK(gen_zero_seeds(ctx, keys + 5));
+    RepTmp z(ctx);
+    MB_CHECK(rep_alloc_like(ctx, m1.p->s[0], &z.p));
+    MB_CHECK(k_maximum_select(ctx, keys, lesser.p, m1.p, m2.p, z.p->s));
+    *out = z.release();
+    return MB_OK;
+  }
   MB_CHECK(mb_rep_ring_inject(ctx, dt, 0, lesser.p, &lr.p));
   Tmp ones(ctx);
   MB_CHECK(mb_fill(ctx, dt, lr.p->s[0]->rank, lr.p->s[0]->shape, 1, 0, &ones.p));
