@@ -88,3 +88,15 @@ def test_generated_rust_ffi_is_in_sync():
     assert open(path).read() == before
     import moose_b200 as mb
     assert set(re.findall(r"pub fn (mb_\w+)\(", before)) == set(mb.ABI)
+
+
+def test_rust_shim_source_calls_only_declared_entry_points():
+    """integration/rust/host_b200.rs (the kernel bodies a Moose maintainer adds; source only, no Rust toolchain here)
+    must bind entry points that exist in the generated extern block and therefore in the header."""
+    src = open(os.path.join(ROOT, "integration", "rust", "host_b200.rs")).read()
+    ffi = open(os.path.join(ROOT, "integration", "rust", "b200_ffi.rs")).read()
+    used = set(re.findall(r"\b(mb_[a-z0-9_]+)\s*\(", src))
+    declared = set(re.findall(r"pub fn (mb_[a-z0-9_]+)", ffi))
+    assert len(used) > 25
+    assert not (used - declared), sorted(used - declared)
+    assert declared == set(declared_symbols())      # the generated block tracks the header
