@@ -8,6 +8,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -123,6 +124,31 @@ bool mb_same_shape(const mb_tensor *a, const mb_tensor *b);
 // where other streams keep small kernels resident (the spin waits of the peer-memory transport, several party lanes) a
 // grid of sm_count CTAs runs in two waves; such contexts reserve a few SMs (mb_ctx_reserve_sms).
 static inline int mb_aes_sms(const mb_ctx *ctx) { return ctx->sm_count - ctx->reserve_sms > 0 ? ctx->sm_count - ctx->reserve_sms : 1; }
+// Launch shape of a PRF kernel over `items` grid-stride items: one CTA per SM, and a block size (<= tpb_max, a multiple
+// of 32) chosen so that every thread gets the same number of items.  With full blocks a tensor of 1.65 waves
+// (250 000 vectors on 148 x 1024 threads: a LogReg slice at 8 GPUs) leaves 35 % of the threads idle in the last wave.
+struct mb_aes_cfg_t { int grid_dim, block_dim; };
+static inline mb_aes_cfg_t mb_aes_cfg(const mb_ctx *ctx, int64_t items, int tpb_max) {
+  const int64_t sms = mb_aes_sms(ctx);
+  if (items <= 0) return mb_aes_cfg_t{1, 32};
+  static const bool full_blocks = getenv("MOOSE_B200_FULL_BLOCKS") != nullptr;   // A/B: the fixed block size of round 1
+  const int64_t per_wave = sms * tpb_max;
+  const int64_t iters = (items + per_wave - 1) / per_wave;
+  // Only where it matters: beyond a few waves the idle tail is a few per cent, and odd block sizes were measured to
+  // cost more than that on long loops (inject_sum over 2 M vectors: 22.1 ms at 992 threads against 15.8 ms at 1024).
+  if (full_blocks || iters > 3) {
+    const int64_t g = (items + tpb_max - 1) / tpb_max;
+    return mb_aes_cfg_t{(int)(g < sms ? g : sms), tpb_max};
+  }
+  const int64_t threads = (items + iters - 1) / iters;
+  if (threads < sms * 128) {   // tiny: few CTAs of 128 threads
+    const int64_t g = (threads + 127) / 128;
+    return mb_aes_cfg_t{(int)(g < 1 ? 1 : g), 128};
+  }
+  int64_t tpb = ((threads + sms - 1) / sms + 31) / 32 * 32;
+  if (tpb > tpb_max) tpb = tpb_max;
+  return mb_aes_cfg_t{(int)sms, (int)tpb};
+}
 int mb_scratch(mb_ctx *ctx, int slot, size_t bytes, void **out);
 // contexts on `device` that have launched the limb GEMM so far (the round barrier is used only by a sole one)
 int mb_gemm_ctx_register(mb_ctx *ctx);

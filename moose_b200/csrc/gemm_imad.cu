@@ -284,7 +284,7 @@ bool k_rep_dot_skinny_deferred_supported(mb_dtype dtype, const RepDotParts &part
 int k_rep_dot_skinny_deferred(mb_ctx *ctx, mb_dtype dtype, const RepDotParts &parts, const RepDotDeferred &lazy, const void *const ysum[3],
                               const void *const y[3], void *const z[3], int64_t M, int64_t N) {
   if (M == 0 || N == 0) return MB_OK;
-  const int g = (int)std::max<int64_t>(1, std::min<int64_t>((M * 32 + AES_TPB_LIGHT - 1) / AES_TPB_LIGHT, (int64_t)mb_aes_sms(ctx)));
+  const mb_aes_cfg_t cfg = mb_aes_cfg(ctx, M * 32, AES_TPB_LIGHT);   // one warp per row
   double kt = 0, kprf = 0, kmat = 0;
   for (int i = 0; i < parts.n; i++) {
     kt += (double)parts.p[i].K;
@@ -293,12 +293,12 @@ int k_rep_dot_skinny_deferred(mb_ctx *ctx, mb_dtype dtype, const RepDotParts &pa
   const double w = dtype == MB_RING128 ? 16.0 : 8.0;
   if (dtype == MB_RING128) {
     MB_CUDA(ctx, cudaFuncSetAttribute(rep_dot_skinny_prf_kernel<u128, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, AES_SMEM_BYTES));
-    rep_dot_skinny_prf_kernel<u128, 2><<<g, AES_TPB_LIGHT, AES_SMEM_BYTES, ctx->stream>>>(
+    rep_dot_skinny_prf_kernel<u128, 2><<<cfg.grid_dim, cfg.block_dim, AES_SMEM_BYTES, ctx->stream>>>(
         parts, lazy, (const u128 *)ysum[0], (const u128 *)ysum[1], (const u128 *)ysum[2], (const u128 *)y[0], (const u128 *)y[1],
         (const u128 *)y[2], (u128 *)z[0], (u128 *)z[1], (u128 *)z[2], M, N);
   } else {
     MB_CUDA(ctx, cudaFuncSetAttribute(rep_dot_skinny_prf_kernel<uint64_t, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, AES_SMEM_BYTES));
-    rep_dot_skinny_prf_kernel<uint64_t, 4><<<g, AES_TPB_LIGHT, AES_SMEM_BYTES, ctx->stream>>>(
+    rep_dot_skinny_prf_kernel<uint64_t, 4><<<cfg.grid_dim, cfg.block_dim, AES_SMEM_BYTES, ctx->stream>>>(
         parts, lazy, (const uint64_t *)ysum[0], (const uint64_t *)ysum[1], (const uint64_t *)ysum[2], (const uint64_t *)y[0],
         (const uint64_t *)y[1], (const uint64_t *)y[2], (uint64_t *)z[0], (uint64_t *)z[1], (uint64_t *)z[2], M, N);
   }

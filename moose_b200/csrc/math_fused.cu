@@ -22,7 +22,8 @@ namespace {
 #define AES_LAUNCH(ctx, kern, tpb, items, ...)                                                                  \
   do {                                                                                                          \
     MB_CUDA((ctx), cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, AES_SMEM_BYTES));    \
-    kern<<<aes_grid((ctx), (items), (tpb)), (tpb), AES_SMEM_BYTES, (ctx)->stream>>>(__VA_ARGS__);               \
+    const mb_aes_cfg_t _cfg = mb_aes_cfg((ctx), (items), (tpb));                                                \
+    kern<<<_cfg.grid_dim, _cfg.block_dim, AES_SMEM_BYTES, (ctx)->stream>>>(__VA_ARGS__);                                  \
   } while (0)
 
 inline int aes_grid(mb_ctx *ctx, int64_t items, int tpb) {

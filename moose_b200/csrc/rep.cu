@@ -22,7 +22,8 @@ constexpr int TPB = 256;
 #define AES_LAUNCH(ctx, kern, tpb, nvec, ...)                                                                   \
   do {                                                                                                          \
     MB_CUDA((ctx), cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, AES_SMEM_BYTES));    \
-    kern<<<aes_grid_for((ctx), (nvec), (tpb)), (tpb), AES_SMEM_BYTES, (ctx)->stream>>>(__VA_ARGS__);           \
+    const mb_aes_cfg_t _cfg = mb_aes_cfg((ctx), (nvec), (tpb));                                                 \
+    kern<<<_cfg.grid_dim, _cfg.block_dim, AES_SMEM_BYTES, (ctx)->stream>>>(__VA_ARGS__);                                  \
   } while (0)
 
 #define VEC_LOOP(v, nvec) \

@@ -10,7 +10,7 @@ constexpr int TPB = AES_TPB_LIGHT;
 #define AES_LAUNCH(ctx, kern, grid, ...)                                                                        \
   do {                                                                                                          \
     MB_CUDA((ctx), cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, AES_SMEM_BYTES));    \
-    kern<<<(grid), TPB, AES_SMEM_BYTES, (ctx)->stream>>>(__VA_ARGS__);                                          \
+    kern<<<(grid).grid_dim, (grid).block_dim, AES_SMEM_BYTES, (ctx)->stream>>>(__VA_ARGS__);                              \
   } while (0)
 
 template <int K>
@@ -49,10 +49,9 @@ __global__ void __launch_bounds__(TPB) sample_bits_as_ring_kernel(AesKey key, T 
 
 int k_sample(mb_ctx *ctx, const AesKey &key, mb_tensor *out, bool bits_as_ring, uint64_t first_block) {
   if (out->numel == 0) return MB_OK;
-  int maxg = mb_aes_sms(ctx);  // one CTA per SM (aes.cuh)
   if (bits_as_ring) {
     int64_t nblocks = (out->numel + 127) / 128;
-    int g = (int)std::min<int64_t>((nblocks + TPB - 1) / TPB, maxg);
+    const mb_aes_cfg_t g = mb_aes_cfg(ctx, nblocks, TPB);
     if (out->dtype == MB_RING128)
       AES_LAUNCH(ctx, sample_bits_as_ring_kernel<u128>, g, key, (u128 *)out->dptr, out->numel);
     else
@@ -61,7 +60,7 @@ int k_sample(mb_ctx *ctx, const AesKey &key, mb_tensor *out, bool bits_as_ring, 
     return MB_OK;
   }
   int64_t nvec = vec_count(out);
-  int g = (int)std::min<int64_t>((nvec + TPB - 1) / TPB, maxg);
+  const mb_aes_cfg_t g = mb_aes_cfg(ctx, nvec, TPB);
   switch (vec_kind(out->dtype)) {
     case VK_RING128: AES_LAUNCH(ctx, sample_kernel<VK_RING128>, g, key, (vec_t *)out->dptr, nvec, out->numel, first_block); break;
     case VK_RING64: AES_LAUNCH(ctx, sample_kernel<VK_RING64>, g, key, (vec_t *)out->dptr, nvec, out->numel, first_block); break;
