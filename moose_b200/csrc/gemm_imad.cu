@@ -170,6 +170,65 @@ __global__ void __launch_bounds__(TPB) rep_dot_skinny_kernel(RepDotParts parts, 
   }
 }
 
+// Narrow right operand on Ring64 (N <= 16, even; the last layer of the MLP: [65536, 512] x [512, 10]): ONE LANE PER ROW.
+// The warp-per-row kernel above spends one load per product on the weights; here a lane keeps the 3 x N accumulators
+// of its row in registers and walks k, so the weights are warp-uniform (broadcast) vector loads shared by 32 rows and
+// the x shares are read one cache line per lane per 16 k.  v_i = x_i . (y_i + y_{i+1}) + x_{i+1} . y_i  (arith.rs:461-469)
+template <int N>
+__global__ void __launch_bounds__(128) rep_dot_rowlane_kernel(const uint64_t *__restrict__ x0, const uint64_t *__restrict__ x1,
+                                                              const uint64_t *__restrict__ x2, const uint64_t *__restrict__ yb0,
+                                                              const uint64_t *__restrict__ yb1, const uint64_t *__restrict__ yb2,
+                                                              const uint64_t *__restrict__ y0, const uint64_t *__restrict__ y1,
+                                                              const uint64_t *__restrict__ y2, uint64_t *__restrict__ z0,
+                                                              uint64_t *__restrict__ z1, uint64_t *__restrict__ z2, int64_t M, int64_t K) {
+  // x tile of the CTA's 128 rows x KC columns per share, staged through shared memory: global loads run along k
+  // (coalesced), a lane then reads its own row (row stride KC + 1 words of 8 bytes: conflict free)
+  constexpr int KC = 8, LD = KC + 1;   // 3 x 128 x 9 x 8 bytes = 27 KB of static shared memory
+  __shared__ uint64_t sx[3][128 * LD];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int64_t mb = (int64_t)blockIdx.x * 128; mb < M; mb += (int64_t)gridDim.x * 128) {
+    const int64_t m = mb + threadIdx.x;
+    uint64_t a0[N], a1[N], a2[N];
+#pragma unroll
+    for (int j = 0; j < N; j++) a0[j] = a1[j] = a2[j] = 0;
+    for (int64_t k0 = 0; k0 < K; k0 += KC) {
+      __syncthreads();
+      // a 32-lane access loads four rows of KC = 8 columns (64-byte segments)
+      for (int r = warp * 4 + (lane >> 3); r < 128; r += 16) {
+        const int64_t gm = mb + r, gk = k0 + (lane & 7);
+        const bool ok = gm < M && gk < K;
+        sx[0][r * LD + (lane & 7)] = ok ? x0[gm * K + gk] : 0;
+        sx[1][r * LD + (lane & 7)] = ok ? x1[gm * K + gk] : 0;
+        sx[2][r * LD + (lane & 7)] = ok ? x2[gm * K + gk] : 0;
+      }
+      __syncthreads();
+      const int kc = (int)(K - k0 < KC ? K - k0 : KC);
+      for (int kk = 0; kk < kc; kk++) {
+        const int64_t k = k0 + kk;
+        const uint64_t u0 = sx[0][threadIdx.x * LD + kk], u1 = sx[1][threadIdx.x * LD + kk], u2 = sx[2][threadIdx.x * LD + kk];
+        const ulonglong2 *rb0 = (const ulonglong2 *)(yb0 + k * N), *rb1 = (const ulonglong2 *)(yb1 + k * N), *rb2 = (const ulonglong2 *)(yb2 + k * N);
+        const ulonglong2 *r0 = (const ulonglong2 *)(y0 + k * N), *r1 = (const ulonglong2 *)(y1 + k * N), *r2 = (const ulonglong2 *)(y2 + k * N);
+#pragma unroll
+        for (int j = 0; j < N / 2; j++) {
+          const ulonglong2 b0 = __ldg(rb0 + j), b1 = __ldg(rb1 + j), b2 = __ldg(rb2 + j);
+          const ulonglong2 c0 = __ldg(r0 + j), c1 = __ldg(r1 + j), c2 = __ldg(r2 + j);
+          a0[2 * j] += u0 * b0.x + u1 * c0.x;  a0[2 * j + 1] += u0 * b0.y + u1 * c0.y;
+          a1[2 * j] += u1 * b1.x + u2 * c1.x;  a1[2 * j + 1] += u1 * b1.y + u2 * c1.y;
+          a2[2 * j] += u2 * b2.x + u0 * c2.x;  a2[2 * j + 1] += u2 * b2.y + u0 * c2.y;
+        }
+      }
+    }
+    if (m < M) {
+#pragma unroll
+      for (int j = 0; j < N; j++) {
+        z0[m * N + j] = a0[j];
+        z1[m * N + j] = a1[j];
+        z2[m * N + j] = a2[j];
+      }
+    }
+  }
+}
+
 // One deferred part of one row (owner O, compile time): party O holds (r, d), party O+1 holds (d, 0), party O+2 holds
 // (0, r) with r = PRF block of the element, d = plain - r -- four products per element and output column:
 //   v_O     += r * (y_O + y_{O+1}) + d * y_O,   v_{O+1} += d * (y_{O+1} + y_{O+2}),   v_{O+2} += r * y_{O+2}
@@ -310,6 +369,23 @@ int k_rep_dot_skinny_deferred(mb_ctx *ctx, mb_dtype dtype, const RepDotParts &pa
 int k_rep_dot_skinny(mb_ctx *ctx, mb_dtype dtype, const RepDotParts &parts, const void *const ysum[3], const void *const y[3],
                      void *const z[3], int64_t M, int64_t N) {
   if (M == 0 || N == 0) return MB_OK;
+  if (dtype == MB_RING64 && parts.n == 1 && M >= 4096 && N % 2 == 0 && N >= 2 && N <= 16) {   // one lane per row
+    const uint64_t *x0 = (const uint64_t *)parts.p[0].x[0], *x1 = (const uint64_t *)parts.p[0].x[1], *x2 = (const uint64_t *)parts.p[0].x[2];
+    const int64_t K = parts.p[0].K;
+    const int g = (int)std::min<int64_t>((M + 127) / 128, (int64_t)ctx->sm_count * 8);
+#define ROWLANE(NN)                                                                                                                  \
+  case NN:                                                                                                                           \
+    rep_dot_rowlane_kernel<NN><<<g, 128, 0, ctx->stream>>>(x0, x1, x2, (const uint64_t *)ysum[0], (const uint64_t *)ysum[1],           \
+                                                           (const uint64_t *)ysum[2], (const uint64_t *)y[0], (const uint64_t *)y[1], \
+                                                           (const uint64_t *)y[2], (uint64_t *)z[0], (uint64_t *)z[1], (uint64_t *)z[2], M, K); \
+    break;
+    switch ((int)N) {
+      ROWLANE(2) ROWLANE(4) ROWLANE(6) ROWLANE(8) ROWLANE(10) ROWLANE(12) ROWLANE(14) ROWLANE(16)
+    }
+#undef ROWLANE
+    MB_LAUNCH_CHECK_W(ctx, "rep_dot_rowlane", 3.0 * 8.0 * ((double)M * K + (double)M * N), 0, 0);
+    return MB_OK;
+  }
   const int g = (int)std::min<int64_t>((M * 32 + TPB - 1) / TPB, (int64_t)ctx->sm_count * 16);
   if (dtype == MB_RING128)
     rep_dot_skinny_kernel<u128, 2><<<g, TPB, 0, ctx->stream>>>(parts, (const u128 *)ysum[0], (const u128 *)ysum[1], (const u128 *)ysum[2],

@@ -282,3 +282,17 @@ def test_deferred_share_expanded_inside_the_skinny_dot(bits, frac, N, owner):
     assert same_rep(gx, ox)                     # materialised on access: exactly ShareOp's tensors
     assert same_rep(g.rep_add(gx, gx), mo.rep_add(ox, ox))
     g.close()
+
+
+@pytest.mark.parametrize("N", [2, 10, 16])
+def test_rep_dot_tall_left_operand_narrow_right_ring64(N):
+    """[M, K] x [K, N] with M >= 4096 and an even N <= 16 on Ring64 takes the one-lane-per-row kernel
+    (csrc/gemm_imad.cu, rep_dot_rowlane_kernel: the last layer of the MLP): share-level parity, ragged M."""
+    g, o = pair()
+    rng = np.random.default_rng(N)
+    M, K = 4096 + 37, 70
+    a, b = rand_ring(rng, 64, (M, K)), rand_ring(rng, 64, (K, N))
+    gx, gy = g.share(g.from_host(RING64, a), 0), g.share(g.from_host(RING64, b), 2)
+    ox, oy = mo.rep_share(o, mo.Ring(64, a), 0), mo.rep_share(o, mo.Ring(64, b), 2)
+    assert same_rep(g.rep_dot(gx, gy), mo.rep_dot(o, ox, oy))
+    g.close()
