@@ -720,7 +720,11 @@ def run_matmul(env):
     return line
 
 
-GEMM_TRAFFIC_BYTES = 43.45e9   # profiles/r1_limb_gemm_2cta_roundbarrier_ncu_full_raw.csv
+GEMM_TRAFFIC_BYTES = 43.43e9   # profiles/r2_matmul_step_ncu_full_raw.csv
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the kernels that dominate the predictor steps, from the
+# `ncu --set full` captures of one step at the BASELINE batch sizes on one GPU (profiles/r2_ncu_kernel_table.md)
+TRAFFIC_BYTES = {("mlp", "limb_gemm"): 9.06e9, ("mlp", "maximum_select"): 2.40e9, ("mlp", "adder_level"): 0.74e9,
+                 ("logreg", "rep_dot_skinny_deferred"): 8.40e9, ("logreg", "inject_sum"): 0.129e9, ("logreg", "adder_level"): 0.27e9}
 
 
 def run_predictor(env, kind):
@@ -835,7 +839,8 @@ def run_predictor(env, kind):
                               "the neighbouring steps (loader / drainer contexts)",
                 "h2d_bytes_per_step": int(B * cols_in * 8), "d2h_bytes_per_step": int(B * cols_out * 8)},
         "gpu_launches": int(launches),
-        "roofline": roofline_from(env, rows, traced),
+        "roofline": roofline_from(env, rows, traced,
+                                  TRAFFIC_BYTES.get((kind, rows[0]["kernel"])) if (world == 1 and B == (65536 if kind == "mlp" else 1000000)) else None),
         "kernels": trim(rows),
     }
     return rec
