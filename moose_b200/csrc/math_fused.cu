@@ -40,7 +40,7 @@ struct Planes3 {
 // W[dst] = OR(W[src], W[dst]) for the ops of one prefix level.  Ops of a level touch disjoint destinations and never
 // read a plane another op of the level writes (misc.rs:14-24), so they run concurrently; a CTA walks (op, vector)
 // items with the op index uniform per iteration block.
-__global__ void __launch_bounds__(AES_TPB_MID) prefix_or_level_kernel(const __grid_constant__ PrefixLevel lv, Planes3 W, int64_t nv) {
+__global__ void __launch_bounds__(768) prefix_or_level_kernel(const __grid_constant__ PrefixLevel lv, Planes3 W, int64_t nv) {
   extern __shared__ __align__(16) uint32_t sT[];
   aes_load_table(sT);
   const AesLane L = aes_lane(sT);
@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(AES_TPB_LIGHT) inject_sum_kernel(const __grid_
 //   d     = ones * sel_0 * sel_1 * ... (replicated multiplications, zero share keys.zero[i])
 // Outputs: d and rest = x_abs - part.
 template <int K>
-__global__ void __launch_bounds__(AES_TPB_384) pow2_bits_kernel(const __grid_constant__ Pow2Desc d, Bits3 W, int64_t n, CRing3 x_abs,
+__global__ void __launch_bounds__(768) pow2_bits_kernel(const __grid_constant__ Pow2Desc d, Bits3 W, int64_t n, CRing3 x_abs,
                                                                 Ring3 out_d, Ring3 out_rest, int64_t nvec) {
   extern __shared__ __align__(16) uint32_t sT[];
   aes_load_table(sT);
@@ -388,7 +388,7 @@ int k_prefix_or_level(mb_ctx *ctx, const PrefixLevel &lv, mb_tensor *const W[3],
   Planes3 w;
   for (int i = 0; i < 3; i++) w.s[i] = (vec_t *)W[i]->dptr;
   const int64_t total = nv * lv.nops;
-  AES_LAUNCH(ctx, prefix_or_level_kernel, AES_TPB_MID, total, lv, w, nv);
+  AES_LAUNCH(ctx, prefix_or_level_kernel, 768, total, lv, w, nv);
   MB_LAUNCH_CHECK_W(ctx, "prefix_or_level", 16.0 * total * 9, 3.0 * total, 0);
   return MB_OK;
 }
@@ -430,9 +430,9 @@ int k_pow2_bits(mb_ctx *ctx, const Pow2Desc &d, const mb_tensor *const W[3], int
     xa.s[i] = (const vec_t *)x_abs->s[i]->dptr;
   }
   if (t->dtype == MB_RING128)
-    AES_LAUNCH(ctx, pow2_bits_kernel<VK_RING128>, AES_TPB_384, nvec, d, w, n, xa, od, orr, nvec);
+    AES_LAUNCH(ctx, pow2_bits_kernel<VK_RING128>, 768, nvec, d, w, n, xa, od, orr, nvec);
   else
-    AES_LAUNCH(ctx, pow2_bits_kernel<VK_RING64>, AES_TPB_384, nvec, d, w, n, xa, od, orr, nvec);
+    AES_LAUNCH(ctx, pow2_bits_kernel<VK_RING64>, 768, nvec, d, w, n, xa, od, orr, nvec);
   MB_LAUNCH_CHECK_W(ctx, "pow2_bits", 16.0 * nvec * 9 + 3.0 * d.count * n / 8, 5.0 * d.count * nvec, 0);
   return MB_OK;
 }

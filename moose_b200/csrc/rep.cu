@@ -163,7 +163,7 @@ struct TruncParams {
 // expanded -- the same values as the op-by-op protocol, bit for bit (tests/test_gpu_replicated.py).
 // Three PRF streams (r, z0, z2), 3 vectors read, 3 written.
 template <int K>
-__global__ void __launch_bounds__(AES_TPB_MID) trunc_pr_kernel(AesKey kr, AesKey k1, AesKey k2, TruncParams p,
+__global__ void __launch_bounds__(AES_TPB_LIGHT) trunc_pr_kernel(AesKey kr, AesKey k1, AesKey k2, TruncParams p,
                                                        const vec_t *__restrict__ x0, const vec_t *__restrict__ x1,
                                                        const vec_t *__restrict__ x2, vec_t *__restrict__ z0,
                                                        vec_t *__restrict__ z1, vec_t *__restrict__ z2, int64_t nvec) {
@@ -288,9 +288,9 @@ int k_rep_trunc_pr(mb_ctx *ctx, const AesKey seeds[6], unsigned amount, const mb
   // seeds[1..3] (the dealer's additive sharings of r, r_top, r_msb) cancel in the outputs: see trunc_pr_kernel
 #define ARGS seeds[0], seeds[4], seeds[5], p, CVP(x->s[0]), CVP(x->s[1]), CVP(x->s[2]), VP(z[0]), VP(z[1]), VP(z[2]), nvec
   if (t->dtype == MB_RING128)
-    AES_LAUNCH(ctx, trunc_pr_kernel<VK_RING128>, AES_TPB_MID, nvec, ARGS);
+    AES_LAUNCH(ctx, trunc_pr_kernel<VK_RING128>, AES_TPB_LIGHT, nvec, ARGS);
   else
-    AES_LAUNCH(ctx, trunc_pr_kernel<VK_RING64>, AES_TPB_MID, nvec, ARGS);
+    AES_LAUNCH(ctx, trunc_pr_kernel<VK_RING64>, AES_TPB_LIGHT, nvec, ARGS);
 #undef ARGS
   MB_LAUNCH_CHECK_W(ctx, "trunc_pr", 16.0 * nvec * 6, 3 * nvec, 0);
   return MB_OK;
