@@ -369,7 +369,7 @@ int k_rep_dot_skinny_deferred(mb_ctx *ctx, mb_dtype dtype, const RepDotParts &pa
 int k_rep_dot_skinny(mb_ctx *ctx, mb_dtype dtype, const RepDotParts &parts, const void *const ysum[3], const void *const y[3],
                      void *const z[3], int64_t M, int64_t N) {
   if (M == 0 || N == 0) return MB_OK;
-  if (dtype == MB_RING64 && parts.n == 1 && M >= 4096 && N % 2 == 0 && N >= 2 && N <= 16) {   // one lane per row
+  if (dtype == MB_RING64 && parts.n == 1 && M >= 128 * 2 * (int64_t)ctx->sm_count && N % 2 == 0 && N >= 2 && N <= 16) {   // one lane per row: needs >= 2 CTAs of 128 rows per SM
     const uint64_t *x0 = (const uint64_t *)parts.p[0].x[0], *x1 = (const uint64_t *)parts.p[0].x[1], *x2 = (const uint64_t *)parts.p[0].x[2];
     const int64_t K = parts.p[0].K;
     const int g = (int)std::min<int64_t>((M + 127) / 128, (int64_t)ctx->sm_count * 8);

@@ -286,11 +286,11 @@ def test_deferred_share_expanded_inside_the_skinny_dot(bits, frac, N, owner):
 
 @pytest.mark.parametrize("N", [2, 10, 16])
 def test_rep_dot_tall_left_operand_narrow_right_ring64(N):
-    """[M, K] x [K, N] with M >= 4096 and an even N <= 16 on Ring64 takes the one-lane-per-row kernel
+    """[M, K] x [K, N] with M >= 256 rows per SM and an even N <= 16 on Ring64 takes the one-lane-per-row kernel
     (csrc/gemm_imad.cu, rep_dot_rowlane_kernel: the last layer of the MLP): share-level parity, ragged M."""
     g, o = pair()
     rng = np.random.default_rng(N)
-    M, K = 4096 + 37, 70
+    M, K = 256 * 148 + 37, 24
     a, b = rand_ring(rng, 64, (M, K)), rand_ring(rng, 64, (K, N))
     gx, gy = g.share(g.from_host(RING64, a), 0), g.share(g.from_host(RING64, b), 2)
     ox, oy = mo.rep_share(o, mo.Ring(64, a), 0), mo.rep_share(o, mo.Ring(64, b), 2)
