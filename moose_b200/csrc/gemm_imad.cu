@@ -229,6 +229,14 @@ __global__ void __launch_bounds__(128) rep_dot_rowlane_kernel(const uint64_t *__
   }
 }
 
+// measured on the LogReg input (10^6 x 512 Ring128): 1024 threads / no unroll 17.0 ms, 512 / 2 15.6 ms, 512 / 4 16.2 ms,
+// 768 / 2 17.9 ms (spills)
+#ifndef SKINNY_PRF_TPB
+#define SKINNY_PRF_TPB 512
+#endif
+#ifndef SKINNY_PRF_UNROLL
+#define SKINNY_PRF_UNROLL 2
+#endif
 // One deferred part of one row (owner O, compile time): party O holds (r, d), party O+1 holds (d, 0), party O+2 holds
 // (0, r) with r = PRF block of the element, d = plain - r -- four products per element and output column:
 //   v_O     += r * (y_O + y_{O+1}) + d * y_O,   v_{O+1} += d * (y_{O+1} + y_{O+2}),   v_{O+2} += r * y_{O+2}
@@ -238,6 +246,8 @@ __device__ __forceinline__ void deferred_part(const AesLane &L, const AesKey &ke
                                               const T *__restrict__ yo, const T *__restrict__ yp, T (&acc)[3][NC]) {
   constexpr int EPV = 16 / (int)sizeof(T);
   constexpr int VK = sizeof(T) == 16 ? VK_RING128 : VK_RING64;
+  constexpr int UNROLL = SKINNY_PRF_UNROLL;
+#pragma unroll UNROLL
   for (int64_t k = (int64_t)lane * EPV; k < K; k += 32 * EPV) {
     const vec_t rv = prf_vec<VK>(L, key, (uint64_t)((e0 + k) / EPV));
 #pragma unroll
@@ -263,7 +273,7 @@ __device__ __forceinline__ void deferred_part(const AesLane &L, const AesKey &ke
 // share_kernel (rep.cu) would have written -- 8 GB per share at BASELINE config 3 that are neither written nor read.
 // One CTA per SM (the AES table), one warp per row; a lane takes the EPV = 16 / sizeof(T) elements of one AES block.
 template <typename T, int NC>
-__global__ void __launch_bounds__(AES_TPB_LIGHT) rep_dot_skinny_prf_kernel(RepDotParts parts, const __grid_constant__ RepDotDeferred lazy,
+__global__ void __launch_bounds__(SKINNY_PRF_TPB) rep_dot_skinny_prf_kernel(RepDotParts parts, const __grid_constant__ RepDotDeferred lazy,
                                                                            const T *__restrict__ yb0, const T *__restrict__ yb1,
                                                                            const T *__restrict__ yb2, const T *__restrict__ y0,
                                                                            const T *__restrict__ y1, const T *__restrict__ y2,
@@ -343,7 +353,7 @@ bool k_rep_dot_skinny_deferred_supported(mb_dtype dtype, const RepDotParts &part
 int k_rep_dot_skinny_deferred(mb_ctx *ctx, mb_dtype dtype, const RepDotParts &parts, const RepDotDeferred &lazy, const void *const ysum[3],
                               const void *const y[3], void *const z[3], int64_t M, int64_t N) {
   if (M == 0 || N == 0) return MB_OK;
-  const mb_aes_cfg_t cfg = mb_aes_cfg(ctx, M * 32, AES_TPB_LIGHT);   // one warp per row
+  const mb_aes_cfg_t cfg = mb_aes_cfg(ctx, M * 32, SKINNY_PRF_TPB);   // one warp per row
   double kt = 0, kprf = 0, kmat = 0;
   for (int i = 0; i < parts.n; i++) {
     kt += (double)parts.p[i].K;
