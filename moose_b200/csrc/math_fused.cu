@@ -98,8 +98,14 @@ __device__ __forceinline__ uint32_t plane_word(const Bits3 &W, int p, int64_t n,
 // out = base + sign * sum_i mult_i * (inject(z_i) << shift_i),  z_i = plane pa_i ^ plane pb_i (pb_i < 0: none).
 // inject(z) = (y0, z - y0 - y1, y1) with y0, y1 the adt_to_rep streams of that call (bits_fused.cu,
 // ring_inject_fused_kernel).
+#ifndef INJECT_SUM_TPB
+#define INJECT_SUM_TPB AES_TPB_LIGHT
+#endif
+#ifndef INJECT_SUM_UNROLL
+#define INJECT_SUM_UNROLL 1
+#endif
 template <int K>
-__global__ void __launch_bounds__(AES_TPB_LIGHT) inject_sum_kernel(const __grid_constant__ InjectSumDesc d, Bits3 W, int64_t n,
+__global__ void __launch_bounds__(INJECT_SUM_TPB) inject_sum_kernel(const __grid_constant__ InjectSumDesc d, Bits3 W, int64_t n,
                                                                  CRing3 base, Ring3 out, int64_t nvec) {
   extern __shared__ __align__(16) uint32_t sT[];
   aes_load_table(sT);
@@ -110,6 +116,8 @@ __global__ void __launch_bounds__(AES_TPB_LIGHT) inject_sum_kernel(const __grid_
     const int64_t e = v * EPV;
     const unsigned sh = (unsigned)(e & 31);
     vec_t acc0 = O::zero(), acc1 = O::zero(), acc2 = O::zero();
+    constexpr int UNROLL = INJECT_SUM_UNROLL;
+#pragma unroll UNROLL
     for (int i = 0; i < d.nplanes; i++) {
       if (d.mult[i] == 0) continue;   // the value is never used (its keys were still drawn, in order)
       uint32_t w = plane_word(W, d.pa[i], n, e);
@@ -408,9 +416,9 @@ int k_inject_sum(mb_ctx *ctx, const InjectSumDesc &d, const mb_tensor *const W[3
   int live = 0;
   for (int i = 0; i < d.nplanes; i++) live += d.mult[i] != 0;
   if (t->dtype == MB_RING128)
-    AES_LAUNCH(ctx, inject_sum_kernel<VK_RING128>, AES_TPB_LIGHT, nvec, d, w, n, b, o, nvec);
+    AES_LAUNCH(ctx, inject_sum_kernel<VK_RING128>, INJECT_SUM_TPB, nvec, d, w, n, b, o, nvec);
   else
-    AES_LAUNCH(ctx, inject_sum_kernel<VK_RING64>, AES_TPB_LIGHT, nvec, d, w, n, b, o, nvec);
+    AES_LAUNCH(ctx, inject_sum_kernel<VK_RING64>, INJECT_SUM_TPB, nvec, d, w, n, b, o, nvec);
   MB_LAUNCH_CHECK_W(ctx, "inject_sum", 16.0 * nvec * (3 + (base ? 3 : 0)) + 3.0 * live * n / 8, 2.0 * live * nvec, 0);
   return MB_OK;
 }
