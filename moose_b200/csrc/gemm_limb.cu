@@ -862,10 +862,13 @@ static int max_active_clusters(mb_ctx *ctx, int *out) {
   return MB_OK;
 }
 
-// Shapes for which the tensor-pipe kernel is the better choice in automatic mode: enough work to fill
-// the 148 SMs with 128 x BLOCK_N tiles and to amortise the limb split / recombine passes.
+// Shapes for which the tensor-pipe kernel is the better choice in automatic mode.  Measured
+// (tools/gemm_crossover.py, profiles/r2_gemm_imad_vs_tensor_crossover.md): it wins on every shape it supports, from
+// 128^3 (0.030 ms against 0.045 ms for the IMAD kernel on Ring64, 0.035 against 0.104 on Ring128) to 65536 x 784 x 512
+// (5.6x / 9.5x), split and recombine passes included -- so the IMAD kernels serve only what the tensor-pipe kernel does
+// not take (M < 128, K < 128, N < 64 or odd) and the skinny right operands.
 bool k_gemm_limb_preferred(int64_t M, int64_t K, int64_t N) {
-  return N >= 64 && (double)M * (double)N * (double)K >= (double)(1 << 27);
+  return N >= 64 && (double)M * (double)N * (double)K >= (double)(1 << 21);
 }
 
 bool k_gemm_limb_supported(mb_dtype dtype, int64_t M, int64_t K, int64_t N) {
