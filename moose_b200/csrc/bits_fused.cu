@@ -401,11 +401,14 @@ bool k_rep_adder_supported(const mb_tensor *x) { return mb_is_ring(x->dtype) && 
 
 // keys: [0] split share seed, [1..3] first AND, then per level i: [4 + 6i .. 4 + 6i + 2] = AND(p, g1),
 // [4 + 6i + 3 .. 4 + 6i + 5] = AND(p, p1).  out[3]: bit tensors of shape [k, shape...] (full) or [shape...] (msb).
-int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only, mb_tensor *out[3]) {
+int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only, mb_tensor *out[3], int out_planes) {
   const mb_tensor *x0 = x->s[0];
   const int k = x0->dtype == MB_RING128 ? 128 : 64;
   const int levels = k == 128 ? 7 : 6;
   const int64_t n = x0->numel, nv = n / 128;
+  // full decomposition of which only planes 0 .. kout-1 will be read (carries only travel upwards, so the higher
+  // planes are never computed; they are left zero): top_most_index reads max_bits <= k / 2 planes
+  const int kout = msb_only ? k : std::max(1, std::min(out_planes > 0 ? out_planes : k, k));
 
   // 1. bit planes of x0 + x1 and of x2
   mb_tensor *B = nullptr, *C = nullptr;
@@ -431,7 +434,7 @@ int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only,
   MB_CHECK(g.alloc(k, n));
   MB_CHECK(p0.alloc(k, n));
   {
-    const int64_t total = (int64_t)k * nv;
+    const int64_t total = (int64_t)kout * nv;
     AES_LAUNCH(ctx, adder_init_kernel, AES_TPB_LIGHT, total, keys[0], keys[1], keys[2], keys[3], (const vec_t *)B->dptr,
                (const vec_t *)C->dptr, ptrs_of(g.t), ptrs_of(p0.t), total);
     MB_LAUNCH_CHECK_W(ctx, "adder_init", 16.0 * total * 8, 4.0 * total, 0);
@@ -465,8 +468,11 @@ int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only,
       np = p2;
     }
   } else {
+    // z[q] = g_final[q - 1] ^ p0[q] for q < kout: g and p of planes 0 .. kout-2 on every level (all planes when kout = k:
+    // g of plane k-1 is computed by the reference too, and nothing distinguishes it here)
+    const int top = kout == k ? k : kout - 1;
     for (int i = 0; i <= levels; i++)
-      for (int q = 0; q < k; q++) {
+      for (int q = 0; q < top; q++) {
         need_g[i].push_back(q);
         if (i < levels) need_p[i].push_back(q);  // p after the last level is never read (misc.rs:236-240)
       }
@@ -523,11 +529,14 @@ int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only,
     adder_final_msb_kernel<<<(unsigned)std::max<int64_t>(1, (nv + TPB - 1) / TPB), TPB, 0, ctx->stream>>>(
         ptrs_of(g.t), (int64_t)gslot[k - 2], ptrs_of(p0.t), zp, nv, k);
   } else {
-    const int64_t total = (int64_t)k * nv;
+    const int64_t total = (int64_t)kout * nv;
     adder_final_full_kernel<<<(unsigned)std::min<int64_t>((total + TPB - 1) / TPB, (int64_t)ctx->sm_count * 16), TPB, 0,
-                              ctx->stream>>>(ptrs_of(g.t), ptrs_of(p0.t), zp, nv, k);
+                              ctx->stream>>>(ptrs_of(g.t), ptrs_of(p0.t), zp, nv, kout);
+    if (kout < k)
+      for (int i = 0; i < 3; i++)
+        MB_CUDA(ctx, cudaMemsetAsync((char *)out[i]->dptr + (size_t)kout * nv * 16, 0, (size_t)(k - kout) * nv * 16, ctx->stream));
   }
-  MB_LAUNCH_CHECK_W(ctx, "adder_final", 16.0 * 9 * nv * (msb_only ? 1 : k), 0, 0);
+  MB_LAUNCH_CHECK_W(ctx, "adder_final", 16.0 * 9 * nv * (msb_only ? 1 : kout), 0, 0);
   return MB_OK;
 }
 

@@ -704,7 +704,7 @@ extern "C" int mb_rep_shl_dim(mb_ctx *ctx, uint64_t amount, uint64_t bit_length,
 
 // Fused split + Kogge-Stone adder (bits_fused.cu).  Seeds are derived in the order the op-by-op protocol draws
 // them: share of bits(x0+x1) by player0 (setup, 1 sync key), first AND (3), then per level AND(p,g1) (3), AND(p,p1) (3).
-static int rep_adder_fused(mb_ctx *ctx, const mb_rep *x, bool msb_only, mb_rep **out) {
+static int rep_adder_fused(mb_ctx *ctx, const mb_rep *x, bool msb_only, mb_rep **out, int out_planes = 0) {
   const mb_tensor *x0 = x->s[0];
   const int k = x0->dtype == MB_RING128 ? 128 : 64;
   const int levels = k == 128 ? 7 : 6;
@@ -724,7 +724,7 @@ static int rep_adder_fused(mb_ctx *ctx, const mb_rep *x, bool msb_only, mb_rep *
   for (int d = 0; d < x0->rank; d++) shape[rank++] = x0->shape[d];
   RepTmp z(ctx);
   MB_CHECK(rep_alloc(ctx, MB_BIT, rank, shape, &z.p));
-  MB_CHECK(k_rep_adder(ctx, keys.data(), x, msb_only, z.p->s));
+  MB_CHECK(k_rep_adder(ctx, keys.data(), x, msb_only, z.p->s, out_planes));
   *out = z.release();
   return MB_OK;
 }
@@ -772,6 +772,12 @@ extern "C" int mb_rep_bit_decompose(mb_ctx *ctx, const mb_rep *x, mb_rep **out) 
   RepTmp c(ctx);
   MB_CHECK(mb_rep_shl_dim(ctx, 1, L, g.p, &c.p));
   return mb_rep_add(ctx, c.p, p_store.p, out);
+}
+
+int mb_rep_bit_decompose_low(mb_ctx *ctx, const mb_rep *x, int planes, mb_rep **out) {
+  if (ctx && ctx->fused_bits && rep_valid(x) && mb_is_ring(x->s[0]->dtype) && x->s[0]->rank < MB_MAX_RANK && k_rep_adder_supported(x->s[0]))
+    return rep_adder_fused(ctx, x, false, out, planes);
+  return mb_rep_bit_decompose(ctx, x, out);
 }
 
 extern "C" int mb_rep_msb(mb_ctx *ctx, const mb_rep *x, mb_rep **out) {

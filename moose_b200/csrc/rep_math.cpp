@@ -165,7 +165,9 @@ R mul_trunc(mb_ctx *c, int amount, const R &a, const R &b) {
 // max_bits ring_injects + shifts + sum as one launch.  Keys are drawn in the reference's op order: the ANDs of prefix_or
 // level by level (misc.rs:14-24), then the ring_injects for i = 0 .. max_bits - 1.
 R top_most_index_batched(mb_ctx *c, int max_bits, const R &x) {
-  R x_bits = bitdec(c, x);
+  mb_rep *xq = nullptr;
+  ck(mb_rep_bit_decompose_low(c, x.p, max_bits, &xq));   // only planes 0 .. max_bits-1 are read below
+  R x_bits(c, xq);
   const int64_t n = x.like()->numel;
   T3 W(c);
   const int64_t wshape[2] = {max_bits, n};
@@ -388,8 +390,9 @@ R exp_from_parts(mb_ctx *c, const R &e_int, const R &e_frac, int f, int k) {
 R rep_pow2(mb_ctx *c, int i_prec, int f_prec, const R &x) {
   const int bits = bits_of(x);
   const mb_dtype ring = ring_of(x);
-  R x_bits = bitdec(c, x);
-  R msb = inject(c, ring, 0, index0(c, bits - 1, x_bits));
+  // only the sign plane of this decomposition is read: the msb-pruned adder computes exactly that plane (the same
+  // entropy requests, the same shares as plane bits-1 of the full decomposition)
+  R msb = inject(c, ring, 0, batched_ok(c, x) ? msb_bit(c, x) : index0(c, bits - 1, bitdec(c, x)));
   R abs_x = mux(c, msb, neg(c, x), x);
   R absolute_bits = bitdec(c, abs_x);
   if (batched_ok(c, x) && i_prec >= 1 && i_prec <= MB_POW2_MAX_BITS && i_prec <= bits - f_prec) {
