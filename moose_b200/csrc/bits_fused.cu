@@ -58,8 +58,9 @@ __device__ __forceinline__ uint32_t warp_transpose32(uint32_t x, int lane) {
 // 128-byte line per store instead of eight scattered 16-byte pieces.
 template <typename T, int KBITS>
 __global__ void __launch_bounds__(TPB) split_planes_kernel(const T *__restrict__ x0, const T *__restrict__ x1,
-                                                          const T *__restrict__ x2, uint32_t *__restrict__ outB,
-                                                          uint32_t *__restrict__ outC, int64_t n) {
+                                                          const T *__restrict__ x2, const T *__restrict__ y0,
+                                                          const T *__restrict__ y1, const T *__restrict__ y2,
+                                                          uint32_t *__restrict__ outB, uint32_t *__restrict__ outC, int64_t n) {
   constexpr int WARPS = TPB / 32;
   constexpr int PL = KBITS / 32;
   __shared__ uint4 tile[KBITS][WARPS];
@@ -75,6 +76,8 @@ __global__ void __launch_bounds__(TPB) split_planes_kernel(const T *__restrict__
       for (int it = 0; it < 4; it++) {
         const int64_t e = g * 128 + it * 32 + lane;
         T v = second ? x2[e] : (T)(x0[e] + x1[e]);
+        // y != NULL: the operand is the share-wise difference x - y (LessOp, compare.rs:91-104), never materialised
+        if (y0) v = second ? (T)(v - y2[e]) : (T)(v - y0[e] - y1[e]);
 #pragma unroll
         for (int h = 0; h < PL; h++) keep[h][it] = warp_transpose32((uint32_t)(v >> (32 * h)), lane);
       }
@@ -401,7 +404,7 @@ bool k_rep_adder_supported(const mb_tensor *x) { return mb_is_ring(x->dtype) && 
 
 // keys: [0] split share seed, [1..3] first AND, then per level i: [4 + 6i .. 4 + 6i + 2] = AND(p, g1),
 // [4 + 6i + 3 .. 4 + 6i + 5] = AND(p, p1).  out[3]: bit tensors of shape [k, shape...] (full) or [shape...] (msb).
-int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only, mb_tensor *out[3], int out_planes) {
+int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only, mb_tensor *out[3], int out_planes, const mb_rep *minus) {
   const mb_tensor *x0 = x->s[0];
   const int k = x0->dtype == MB_RING128 ? 128 : 64;
   const int levels = k == 128 ? 7 : 6;
@@ -422,11 +425,16 @@ int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only,
     const int g = (int)std::min<int64_t>((warps * 32 + TPB - 1) / TPB, (int64_t)ctx->sm_count * 8);
     if (k == 128)
       split_planes_kernel<u128, 128><<<g, TPB, 0, ctx->stream>>>((const u128 *)x->s[0]->dptr, (const u128 *)x->s[1]->dptr,
-                                                                (const u128 *)x->s[2]->dptr, (uint32_t *)B->dptr, (uint32_t *)C->dptr, n);
+                                                                (const u128 *)x->s[2]->dptr, minus ? (const u128 *)minus->s[0]->dptr : nullptr,
+                                                                minus ? (const u128 *)minus->s[1]->dptr : nullptr,
+                                                                minus ? (const u128 *)minus->s[2]->dptr : nullptr, (uint32_t *)B->dptr,
+                                                                (uint32_t *)C->dptr, n);
     else
-      split_planes_kernel<uint64_t, 64><<<g, TPB, 0, ctx->stream>>>((const uint64_t *)x->s[0]->dptr, (const uint64_t *)x->s[1]->dptr,
-                                                                   (const uint64_t *)x->s[2]->dptr, (uint32_t *)B->dptr, (uint32_t *)C->dptr, n);
-    MB_LAUNCH_CHECK_W(ctx, "split_planes", 3.0 * n * (k / 8) + 2.0 * k * n / 8, 0, 0);
+      split_planes_kernel<uint64_t, 64><<<g, TPB, 0, ctx->stream>>>(
+          (const uint64_t *)x->s[0]->dptr, (const uint64_t *)x->s[1]->dptr, (const uint64_t *)x->s[2]->dptr,
+          minus ? (const uint64_t *)minus->s[0]->dptr : nullptr, minus ? (const uint64_t *)minus->s[1]->dptr : nullptr,
+          minus ? (const uint64_t *)minus->s[2]->dptr : nullptr, (uint32_t *)B->dptr, (uint32_t *)C->dptr, n);
+    MB_LAUNCH_CHECK_W(ctx, "split_planes", (minus ? 6.0 : 3.0) * n * (k / 8) + 2.0 * k * n / 8, 0, 0);
   }
 
   // 2. g0, p0 on all planes

@@ -252,7 +252,8 @@ int k_party_adder_level(mb_ctx *ctx, const AesKey keys[4], const LevelDesc &d, c
 // Fused arithmetic->boolean conversion (bits_fused.cu)
 bool k_rep_adder_supported(const mb_tensor *x);
 // out_planes (full decomposition only): planes 0 .. out_planes-1 are computed, the rest of the [k, n] result is zero (0 = all)
-int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only, mb_tensor *out[3], int out_planes = 0);
+// minus (may be NULL): the adder decomposes x - minus, the subtraction folded into the split
+int k_rep_adder(mb_ctx *ctx, const AesKey *keys, const mb_rep *x, bool msb_only, mb_tensor *out[3], int out_planes = 0, const mb_rep *minus = nullptr);
 // BitDecomposeOp::rep_ring_kernel of which the caller reads only planes 0 .. planes-1 (same entropy requests, same values there)
 int mb_rep_bit_decompose_low(mb_ctx *ctx, const mb_rep *x, int planes, mb_rep **out);
 int k_ring_inject_fused(mb_ctx *ctx, const AesKey &k_y0, const AesKey &k_y1, unsigned bit_idx, const mb_rep *x,

@@ -704,7 +704,7 @@ extern "C" int mb_rep_shl_dim(mb_ctx *ctx, uint64_t amount, uint64_t bit_length,
 
 // Fused split + Kogge-Stone adder (bits_fused.cu).  Seeds are derived in the order the op-by-op protocol draws
 // them: share of bits(x0+x1) by player0 (setup, 1 sync key), first AND (3), then per level AND(p,g1) (3), AND(p,p1) (3).
-static int rep_adder_fused(mb_ctx *ctx, const mb_rep *x, bool msb_only, mb_rep **out, int out_planes = 0) {
+static int rep_adder_fused(mb_ctx *ctx, const mb_rep *x, bool msb_only, mb_rep **out, int out_planes = 0, const mb_rep *minus = nullptr) {
   const mb_tensor *x0 = x->s[0];
   const int k = x0->dtype == MB_RING128 ? 128 : 64;
   const int levels = k == 128 ? 7 : 6;
@@ -724,7 +724,7 @@ static int rep_adder_fused(mb_ctx *ctx, const mb_rep *x, bool msb_only, mb_rep *
   for (int d = 0; d < x0->rank; d++) shape[rank++] = x0->shape[d];
   RepTmp z(ctx);
   MB_CHECK(rep_alloc(ctx, MB_BIT, rank, shape, &z.p));
-  MB_CHECK(k_rep_adder(ctx, keys.data(), x, msb_only, z.p->s, out_planes));
+  MB_CHECK(k_rep_adder(ctx, keys.data(), x, msb_only, z.p->s, out_planes, minus));
   *out = z.release();
   return MB_OK;
 }
@@ -871,6 +871,11 @@ extern "C" int mb_rep_ring_inject(mb_ctx *ctx, mb_dtype ring, uint64_t bit_idx, 
 
 extern "C" int mb_rep_less(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out) {
   MB_ENTER(ctx, "mb_rep_less");
+  // msb(x - y): the share-wise subtraction is folded into the adder's split when both operands are plain ring
+  // tensors of one shape (no entropy is involved in the subtraction, so the order of requests is untouched)
+  if (ctx->fused_bits && rep_valid(x) && rep_valid(y) && out && mb_is_ring(x->s[0]->dtype) && x->s[0]->dtype == y->s[0]->dtype &&
+      uniform_shapes(x, y) && k_rep_adder_supported(x->s[0]))
+    return rep_adder_fused(ctx, x, true, out, 0, y);
   RepTmp d(ctx);
   MB_CHECK(mb_rep_sub(ctx, x, y, &d.p));
   return mb_rep_msb(ctx, d.p, out);
