@@ -22,7 +22,12 @@
  *    sizes;
  *  - all device work of a context is issued on that context's CUDA stream and
  *    is asynchronous; mb_tensor_to_host / mb_ctx_sync synchronise;
- *  - thread safe: concurrent calls on one context serialise on its stream;
+ *  - thread safe: concurrent calls on one context (Moose runs every op as its own
+ *    tokio task, moose/src/execution/asynchronous.rs:453-531) serialise on its stream;
+ *    a call's launches reach the stream as one unit where they share per-context
+ *    scratch (the tensor-pipe GEMM), the entropy source, the one-time replicated
+ *    setup and the event pools are guarded.  A deferred sharing handle
+ *    (mb_rep_share_deferred) must not be consumed by two threads at once;
  *  - there is NO CPU fallback: creating a context without a CUDA device fails.
  *
  * Layouts: MB_RING64 = uint64_t, MB_RING128 = little-endian 128-bit integer
