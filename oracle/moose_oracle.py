@@ -976,6 +976,20 @@ def rep_mux(sess: Session, s: RepTensor, x: RepTensor, y: RepTensor) -> RepTenso
     return rep_add(rep_mul(sess, s, rep_sub(x, y)), y)
 
 
+def rep_mux_bit_selector(sess: Session, bits: int, s: RepTensor, x: RepTensor, y: RepTensor) -> RepTensor:
+    """MuxOp::rep_bit_selector_kernel (replicated/control_flow.rs:27-45): ring_inject(s) then s*(x-y)+y."""
+    return rep_mux(sess, rep_ring_inject(sess, bits, 0, s), x, y)
+
+
+def rep_bit_compose(sess: Session, bits: int, x: RepTensor) -> RepTensor:
+    """BitComposeOp::rep_kernel (replicated/bits.rs:23-46): sum_i ring_inject(i, plane i), folded from zeros."""
+    planes = [rep_index(i, x) for i in range(bits)]
+    acc = rep_fill(bits, 0, planes[0].shares[0][0].shape)
+    for i, plane in enumerate(planes):
+        acc = rep_add(acc, rep_ring_inject(sess, bits, i, plane))
+    return acc
+
+
 def mir_fill(bits: int, value: int, shape) -> MirTensor:
     v = fill(bits, value, shape)
     return MirTensor([v, v, v])
@@ -1058,6 +1072,11 @@ def prefix_op(sess, xs, op):
 def prefix_or(sess, xs):
     """misc.rs:30-40: or(x, y) = xor(xor(x, y), and(x, y))."""
     return prefix_op(sess, xs, lambda s, x, y: rep_xor(rep_xor(x, y), rep_and(s, x, y)))
+
+
+def prefix_and(sess, xs):
+    """misc.rs:42-52 (used only by the reference's tests)."""
+    return prefix_op(sess, xs, lambda s, x, y: rep_and(s, x, y))
 
 
 def sign_from_msb(bits: int, msb_ring: RepTensor) -> RepTensor:
