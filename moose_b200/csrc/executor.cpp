@@ -113,24 +113,6 @@ size_t matching_close(const std::string &s, size_t open_idx) {
   throw ParseErr{"unbalanced brackets in '" + s.substr(0, 60) + "'"};
 }
 
-size_t matching_open(const std::string &s, size_t close_idx) {
-  int depth = 0;
-  bool in_str = false;
-  for (size_t i = close_idx + 1; i-- > 0;) {
-    const char ch = s[i];
-    if (in_str) {
-      if (ch == '"' && (i == 0 || s[i - 1] != '\\')) in_str = false;
-    } else if (ch == '"') {
-      in_str = true;
-    } else if (is_close(s, i)) {
-      depth++;
-    } else if (is_open(ch)) {
-      if (--depth == 0) return i;
-    }
-  }
-  throw ParseErr{"unbalanced brackets in '" + s.substr(0, 60) + "'"};
-}
-
 GOp parse_line(const std::string &raw) {
   const std::string line = trim(raw);
   GOp op;
@@ -167,17 +149,30 @@ GOp parse_line(const std::string &raw) {
   if (po == std::string::npos || plc.back() != ')') throw ParseErr{"bad placement '" + plc + "' in " + op.name};
   op.plc_kind = plc.substr(0, po);
   op.owners = split_top(plc.substr(po + 1, plc.size() - po - 2));
-  if (body.empty() || body.back() != ')') throw ParseErr{"missing input list in " + op.name};
-  const size_t io = matching_open(body, body.size() - 1);
-  op.inputs = split_top(body.substr(io + 1, body.size() - io - 2));
-  const std::string sig = trim(body.substr(0, io));
-  if (sig.empty() || (sig[0] != '(' && sig[0] != '[')) throw ParseErr{"bad signature '" + sig + "' in " + op.name};
-  op.variadic = sig[0] == '[';
-  const size_t se = matching_close(sig, 0);
-  op.in_types = split_top(sig.substr(1, se - 1));
-  const std::string after = trim(sig.substr(se + 1));
+  // signature, then the OPTIONAL argument list: a nullary operation may be written without "()"
+  // (moose/src/textual/parsing.rs:176 `opt(argument_list)`); a type is alphanumeric with an optional <...>
+  // (parsing.rs:497-507), so it never ends in ')'
+  if (body.empty() || (body[0] != '(' && body[0] != '[')) throw ParseErr{"bad signature '" + body + "' in " + op.name};
+  op.variadic = body[0] == '[';
+  const size_t se = matching_close(body, 0);
+  op.in_types = split_top(body.substr(1, se - 1));
+  std::string after = trim(body.substr(se + 1));
   if (after.size() < 2 || after[0] != '-' || after[1] != '>') throw ParseErr{"missing '->' in signature of " + op.name};
-  op.out_type = trim(after.substr(2));
+  after = trim(after.substr(2));
+  size_t te = 0;
+  while (te < after.size() && isalnum((unsigned char)after[te])) te++;
+  if (te == 0) throw ParseErr{"missing output type in " + op.name};
+  if (te < after.size() && after[te] == '<') {
+    const size_t gt = after.find('>', te);
+    if (gt == std::string::npos) throw ParseErr{"unbalanced '<' in the output type of " + op.name};
+    te = gt + 1;
+  }
+  op.out_type = after.substr(0, te);
+  const std::string tail = trim(after.substr(te));
+  if (!tail.empty()) {
+    if (tail[0] != '(' || matching_close(tail, 0) != tail.size() - 1) throw ParseErr{"bad input list '" + tail + "' in " + op.name};
+    op.inputs = split_top(tail.substr(1, tail.size() - 2));
+  }
   return op;
 }
 

@@ -156,20 +156,28 @@ def parse_line(line: str) -> Operation:
     if not pm:
         raise ParseError(f"bad placement {plc!r} in {name}")
     placement_kind, owners = pm.group(1), [o.strip() for o in _split_top(pm.group(2))]
-    if not body.endswith(")"):
-        raise ParseError(f"missing input list in {name}")
-    op_idx = _matching_open(body, len(body) - 1)
-    inputs = _split_top(body[op_idx + 1:-1])
-    sig = body[:op_idx].strip()
-    variadic = sig.startswith("[")
-    if not (sig.startswith("(") or variadic):
-        raise ParseError(f"bad signature {sig!r} in {name}")
-    end = _matching_close(sig, 0)
-    input_types = _split_top(sig[1:end])
-    after = sig[end + 1:].strip()
+    # signature first, then the OPTIONAL argument list (parsing.rs:176 `opt(argument_list)`: a nullary operation may
+    # be written without "()"); a type is alphanumeric with an optional <...> (parsing.rs:497-507), never "(...)"
+    variadic = body.startswith("[")
+    if not (body.startswith("(") or variadic):
+        raise ParseError(f"bad signature {body!r} in {name}")
+    end = _matching_close(body, 0)
+    input_types = _split_top(body[1:end])
+    after = body[end + 1:].strip()
     if not after.startswith("->"):
         raise ParseError(f"missing '->' in signature of {name}")
-    output_type = after[2:].strip()
+    after = after[2:].strip()
+    tm = re.match(r"^[A-Za-z0-9]+(<[^>]*>)?", after)
+    if not tm:
+        raise ParseError(f"missing output type in {name}")
+    output_type = tm.group(0)
+    tail = after[tm.end():].strip()
+    if not tail:
+        inputs = []
+    elif tail.startswith("(") and _matching_close(tail, 0) == len(tail) - 1:
+        inputs = _split_top(tail[1:-1])
+    else:
+        raise ParseError(f"bad input list {tail!r} in {name}")
     return Operation(name, kind, attrs, input_types, variadic, output_type, inputs, placement_kind, owners)
 
 

@@ -19,7 +19,14 @@ def replay(ops_in_order, sess: mo.Session, parse_constant, attr_hex16, arguments
             v = sess.derive_seed(attr_hex16(op, "sync_key"), x[0])
         elif k == "Constant":
             ty, val = parse_constant(op.attrs["value"])
-            v = np.array(val, dtype=np.float64) if ty in ("HostFloat64Tensor", "Float64Tensor") else val
+            if ty in ("HostFloat64Tensor", "Float64Tensor"):
+                v = np.array(val, dtype=np.float64)
+            elif ty in _RING_BITS:
+                v = mo.Ring.from_ints(_RING_BITS[ty], val)
+            elif ty == "HostBitTensor":
+                v = mo.Bits.from_array(np.array(val, dtype=np.uint8))
+            else:
+                v = val
         elif k == "Input":
             v = np.asarray(arguments[op.attrs["arg_name"].strip('"')], dtype=np.float64)
         elif k == "RingFixedpointEncode":

@@ -216,3 +216,18 @@ def test_int2fl_equal_log_sqrt_reference_vectors():
     xs = np.array([1.0, 2.5, 3.0, 4.0, 5.0])
     X = mo.rep_share(s, mo.fixed_encode(128, xs, 30), 0)
     assert np.abs(mo.fixed_decode(mo.rep_reveal(mo.rep_log(s, 10, 30, X)), 30) - np.log(xs)).max() < 0.001
+
+
+def test_bit_and_ring_fill_sum_reference_vectors():
+    """host/mod.rs:954-1009 (bit_fill, bit_xor, bit_or, bit_and), :1089-1116 (ring_fill, ring_sum with / without axis)."""
+    assert mo.fill_bits(1, (2,)).to_array().tolist() == [1, 1]
+    zero, one = mo.fill_bits(0, (5,)), mo.fill_bits(1, (5,))
+    truth = {"xor": [one, one, zero, zero], "or": [one, one, one, zero], "and": [zero, zero, one, zero]}
+    for op, want in truth.items():
+        got = [mo.bit_op(op, a, b) for a, b in ((zero, one), (one, zero), (one, one), (zero, zero))]
+        assert got == want, op
+    assert ints(mo.fill(64, 1, (2,))) == [1, 1]
+    x = mo.Ring.from_ints(64, [[1, 2], [3, 4]])
+    assert ints(mo.sum_axis(x, 0)) == [4, 6]
+    s = mo.sum_axis(x, None)
+    assert s.shape == () and ints(s) == [10]

@@ -125,3 +125,77 @@ def test_native_parser_matches_python_order():
     g = ctypes.c_void_p()
     assert lib.mb_graph_parse(None, b"x = Add (a, b) @Host(alice)\n", ctypes.byref(g)) == -1
     assert lib.mb_graph_parse(None, b"x = Add: (T, T) -> T (a, x) @Host(alice)\n", ctypes.byref(g)) == -1  # cycle
+    # a nullary operation may leave out its "()" (textual/parsing.rs:176), as the reference's executor tests write them
+    src = ("x = Constant{value=HostRing64Tensor([3])}: () -> HostRing64Tensor @Host(alice)\n"
+           "s = Shape: (HostRing64Tensor) -> HostShape (x) @Host(alice)\n"
+           "t = Mul: (Tensor<Fixed128(24, 40)>, Tensor<Fixed128(24, 40)>) -> Tensor<Fixed128(24, 40)> (x, x) @Replicated(alice, bob, carole)\n")
+    assert lib.mb_graph_parse(None, src.encode(), ctypes.byref(g)) == 0 and lib.mb_graph_num_ops(g) == 3
+    lib.mb_graph_free(g)
+    ops = tx.parse_computation(src)
+    assert ops[0].inputs == [] and ops[1].inputs == ["x"] and ops[2].output_type == "Tensor<Fixed128(24, 40)>"
+    assert ops[2].inputs == ["x", "x"] and ops[2].owners == ["alice", "bob", "carole"]
+    with pytest.raises(tx.ParseError):
+        tx.parse_line("x = Add: (T, T) -> T junk @Host(alice)")
+
+
+def _replay_text(source):
+    ops = tx.parse_computation("\n".join(line.strip() for line in source.strip().splitlines()))
+    return ro.replay(toposort(ops), mo.Session("foobar", bytes(range(16))), tx.parse_constant, tx.attr_hex16)
+
+
+@pytest.mark.parametrize("op,expected", [("Add", [5]), ("Mul", [6]), ("Sub", [1])])
+def test_reference_ring_binop_graphs(op, expected):
+    """moose/src/execution/mod.rs:741-771 (test_ring_binop_invocation)."""
+    vals, _ = _replay_text(f"""
+        x = Constant{{value=HostRing64Tensor([3])}}: () -> HostRing64Tensor @Host(alice)
+        y = Constant{{value=HostRing64Tensor([2])}}: () -> HostRing64Tensor @Host(alice)
+        res = {op} : (HostRing64Tensor, HostRing64Tensor) -> HostRing64Tensor (x, y) @Host(alice)
+        output = Output{{tag = "output_0"}} : (HostRing64Tensor) -> HostRing64Tensor (res) @Host(alice)""")
+    assert vals["res"].to_ints().tolist() == expected
+
+
+@pytest.mark.parametrize("x,y,expected", [
+    ("[[1, 2], [3, 4]]", "[[1, 0], [0, 1]]", [[1, 2], [3, 4]]),
+    ("[[1, 2], [3, 4]]", "[1, 1]", [3, 7]),
+    ("[1, 1]", "[[1, 2], [3, 4]]", [4, 6]),
+])
+def test_reference_ring_dot_graphs(x, y, expected):
+    """moose/src/execution/mod.rs:773-846 (test_ring_dot_invocation)."""
+    vals, _ = _replay_text(f"""
+        x = Constant{{value=HostRing64Tensor({x})}}: () -> HostRing64Tensor @Host(alice)
+        y = Constant{{value=HostRing64Tensor({y})}}: () -> HostRing64Tensor @Host(alice)
+        res = Dot : (HostRing64Tensor, HostRing64Tensor) -> HostRing64Tensor (x, y) @Host(alice)
+        output = Output{{tag = "output_0"}} : (HostRing64Tensor) -> HostRing64Tensor (res) @Host(alice)""")
+    assert vals["res"].to_ints().tolist() == expected
+
+
+@pytest.mark.parametrize("ty,shape", [("Ring64", "2"), ("Ring128", "2"), ("Ring64", "2, 1"), ("Ring64", "2, 2"),
+                                      ("Ring64", "1, 2"), ("Ring128", "2, 3")])
+def test_reference_fill_graphs(ty, shape):
+    """moose/src/execution/mod.rs:848-918 (test_fill)."""
+    vals, _ = _replay_text(f"""
+        shape = Constant{{value=HostShape([{shape}])}}: () -> HostShape @Host(alice)
+        res = Fill {{value = {ty}(1)}} : (HostShape) -> Host{ty}Tensor (shape) @Host(alice)
+        output = Output{{tag = "output_0"}} : (Host{ty}Tensor) -> Host{ty}Tensor (res) @Host(alice)""")
+    dims = tuple(int(d) for d in shape.split(","))
+    assert vals["res"].bits == int(ty[4:]) and vals["res"].shape == dims
+    assert vals["res"].to_ints().reshape(-1).tolist() == [1] * int(np.prod(dims))
+
+
+@pytest.mark.parametrize("ty", ["HostRing64Tensor", "HostRing128Tensor"])
+def test_reference_shr_and_sample_graphs(ty):
+    """moose/src/execution/mod.rs:920-956 (test_ring_bitwise_ops) and :200-222 (test_constants_sample_ring)."""
+    vals, _ = _replay_text("""
+        x = Constant{value=HostRing64Tensor([4, 4])}: () -> HostRing64Tensor @Host(alice)
+        res = Shr {amount = 1}: (HostRing64Tensor) -> HostRing64Tensor (x) @Host(alice)
+        output = Output{tag = "output_0"}: (HostRing64Tensor) -> HostRing64Tensor (res) @Host(alice)""".replace("HostRing64Tensor", ty))
+    assert vals["res"].to_ints().tolist() == [2, 2]
+    vals, _ = _replay_text("""
+        seed = Constant{value=HostSeed(00000000000000000000000000000000)}: () -> HostSeed @Host(alice)
+        xshape = Constant{value=HostShape([2, 2])}: () -> HostShape @Host(alice)
+        sampled = SampleSeeded{}: (HostShape, HostSeed) -> HostRing64Tensor (xshape, seed) @Host(alice)
+        shape = Shape: (HostRing64Tensor) -> HostShape (sampled) @Host(alice)
+        output = Output{tag = "output_0"}: (HostShape) -> HostShape (shape) @Host(alice)""".replace("HostRing64Tensor", ty))
+    assert tuple(vals["shape"]) == (2, 2)
+    want = mo.sample_uniform_seeded(int(ty[8:-6]), (2, 2), bytes(16))
+    assert vals["sampled"] == want
