@@ -376,8 +376,13 @@ int mb_rep_msb(mb_ctx *ctx, const mb_rep *x, mb_rep **out_bits);
  * gen_dabit (additive/dabit.rs:38-69). */
 int mb_rep_ring_inject(mb_ctx *ctx, mb_dtype ring, uint64_t bit_idx, const mb_rep *x_bits,
                        mb_rep **out);
-/* MuxOp::rep_kernel (moose/src/replicated/control_flow.rs:9-25). */
+/* MuxOp::rep_kernel (moose/src/replicated/control_flow.rs:9-25): s*(x-y)+y with a
+ * ring selector; a replicated BIT selector takes rep_bit_selector_kernel
+ * (control_flow.rs:27-45): ring_inject(s, 0) first. */
 int mb_rep_mux(mb_ctx *ctx, const mb_rep *s, const mb_rep *x, const mb_rep *y, mb_rep **out);
+/* BitComposeOp::rep_kernel (moose/src/replicated/bits.rs:23-46): replicated bit
+ * planes [k, shape...] -> ring value, sum_i ring_inject(i, plane_i). */
+int mb_rep_bit_compose(mb_ctx *ctx, mb_dtype ring, const mb_rep *x_bits, mb_rep **out);
 /* LessOp::rep_kernel (moose/src/replicated/compare.rs:91-104). */
 int mb_rep_less(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep **out_bits);
 /* MaximumOp::kernel (moose/src/replicated/softmax.rs:10-53). */

@@ -105,6 +105,7 @@ ABI = {
     "mb_rep_mul": [_P, _P, _P, _PP], "mb_rep_dot": [_P, _P, _P, _PP], "mb_rep_trunc_pr": [_P, _U32, _P, _PP],
     "mb_rep_bit_decompose": [_P, _P, _PP], "mb_rep_msb": [_P, _P, _PP],
     "mb_rep_ring_inject": [_P, _I, _U64, _P, _PP], "mb_rep_mux": [_P, _P, _P, _P, _PP],
+    "mb_rep_bit_compose": [_P, _I, _P, _PP],
     "mb_rep_less": [_P, _P, _P, _PP], "mb_rep_maximum": [_P, _PP, _I, _PP], "mb_rep_relu": [_P, _P, _PP],
     "mb_rep_fill": [_P, _I, _I, _I64P, _U64, _U64, _PP], "mb_rep_greater": [_P, _P, _P, _PP],
     "mb_rep_div": [_P, _U32, _U32, _P, _P, _PP], "mb_rep_pow2": [_P, _U32, _U32, _P, _PP],
@@ -723,8 +724,14 @@ class Session:
         return self._r(lib().mb_rep_ring_inject(self.ctx, ring, bit_idx, x.h, ctypes.byref(out)), out)
 
     def mux(self, s, x, y) -> RepTensor:
+        """s*(x-y)+y; `s` is a replicated ring value or replicated bits (control_flow.rs:9-45)."""
         out = self._out()
         return self._r(lib().mb_rep_mux(self.ctx, s.h, x.h, y.h, ctypes.byref(out)), out)
+
+    def bit_compose(self, ring: int, x_bits) -> RepTensor:
+        """BitComposeOp::rep_kernel (replicated/bits.rs:23-46): planes [k, shape...] -> ring value."""
+        out = self._out()
+        return self._r(lib().mb_rep_bit_compose(self.ctx, ring, x_bits.h, ctypes.byref(out)), out)
 
     def maximum(self, xs: Sequence[RepTensor]) -> RepTensor:
         arr = (ctypes.c_void_p * max(len(xs), 1))(*[x.h for x in xs])

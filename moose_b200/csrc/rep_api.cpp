@@ -883,10 +883,39 @@ extern "C" int mb_rep_less(mb_ctx *ctx, const mb_rep *x, const mb_rep *y, mb_rep
 
 extern "C" int mb_rep_mux(mb_ctx *ctx, const mb_rep *s, const mb_rep *x, const mb_rep *y, mb_rep **out) {
   MB_ENTER(ctx, "mb_rep_mux");
-  RepTmp d(ctx), m(ctx);
+  MB_REQUIRE(ctx, rep_valid(s) && rep_valid(x) && rep_valid(y) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_mux: NULL argument");
+  RepTmp sr(ctx), d(ctx), m(ctx);
+  if (s->s[0]->dtype == MB_BIT && mb_is_ring(x->s[0]->dtype)) {
+    // rep_bit_selector_kernel (control_flow.rs:27-45): the selector is injected into the ring first
+    MB_CHECK(mb_rep_ring_inject(ctx, x->s[0]->dtype, 0, s, &sr.p));
+    s = sr.p;
+  }
   MB_CHECK(mb_rep_sub(ctx, x, y, &d.p));
   MB_CHECK(mb_rep_mul(ctx, s, d.p, &m.p));
   return mb_rep_add(ctx, m.p, y, out);
+}
+
+// BitComposeOp::rep_kernel (replicated/bits.rs:23-46): fold over the k planes, acc = acc + ring_inject(i, plane_i),
+// starting from a replicated zero; one dabit per plane, drawn in plane order like the reference's fold.
+extern "C" int mb_rep_bit_compose(mb_ctx *ctx, mb_dtype ring, const mb_rep *x_bits, mb_rep **out) {
+  MB_ENTER(ctx, "mb_rep_bit_compose");
+  MB_REQUIRE(ctx, rep_valid(x_bits) && out, MB_ERR_INVALID_ARGUMENT, "mb_rep_bit_compose: NULL argument");
+  MB_REQUIRE(ctx, mb_is_ring(ring), MB_ERR_TYPE_MISMATCH, "mb_rep_bit_compose: the result type must be a ring");
+  const mb_tensor *p = x_bits->s[0];
+  const int64_t k = ring == MB_RING64 ? 64 : 128;
+  MB_REQUIRE(ctx, p->dtype == MB_BIT, MB_ERR_TYPE_MISMATCH, "mb_rep_bit_compose: needs replicated bit planes");
+  MB_REQUIRE(ctx, p->rank >= 1 && p->shape[0] == k, MB_ERR_INVALID_ARGUMENT, "mb_rep_bit_compose: axis 0 must hold one plane per ring bit");
+  RepTmp acc(ctx);
+  MB_CHECK(mb_rep_fill(ctx, ring, p->rank - 1, p->shape + 1, 0, 0, &acc.p));
+  for (int64_t i = 0; i < k; i++) {
+    RepTmp plane(ctx), inj(ctx), next(ctx);
+    MB_CHECK(mb_rep_index_axis0(ctx, i, x_bits, &plane.p));
+    MB_CHECK(mb_rep_ring_inject(ctx, ring, (uint64_t)i, plane.p, &inj.p));
+    MB_CHECK(mb_rep_add(ctx, acc.p, inj.p, &next.p));
+    std::swap(acc.p, next.p);
+  }
+  *out = acc.release();
+  return MB_OK;
 }
 
 extern "C" int mb_rep_maximum(mb_ctx *ctx, const mb_rep *const *xs, int n, mb_rep **out) {

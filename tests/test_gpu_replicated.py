@@ -296,3 +296,46 @@ def test_rep_dot_tall_left_operand_narrow_right_ring64(N):
     ox, oy = mo.rep_share(o, mo.Ring(64, a), 0), mo.rep_share(o, mo.Ring(64, b), 2)
     assert same_rep(g.rep_dot(gx, gy), mo.rep_dot(o, ox, oy))
     g.close()
+
+
+@pytest.mark.parametrize("bits", [64, 128])
+def test_mux_with_ring_and_bit_selectors(bits):
+    """replicated/control_flow.rs:53-123 (test_mux, test_bit_selector_mux): s*(x-y)+y with the selector as a ring
+    value and as replicated bits (ring_inject first), share-level parity and the reference's decoded answers."""
+    g, o = pair()
+    enc = lambda v: [int(t * 2 ** 24) for t in v]
+    for sel, xs, ys, want in [([1, 0, 1, 0], [1.0, 2.0, 3.0, 4.0], [4.0, 5.0, 6.0, -1.0], [1.0, 5.0, 3.0, -1.0]),
+                              ([1, 1, 0], [1.0, 2.0, 3.0], [4.0, 5.0, 6.0], [1.0, 2.0, 6.0])]:
+        n = len(sel)
+        gx, ox = g.share(g.from_ints(DT[bits], enc(xs), (n,)), 0), mo.rep_share(o, mo.Ring.from_ints(bits, enc(xs)), 0)
+        gy, oy = g.share(g.from_ints(DT[bits], enc(ys), (n,)), 1), mo.rep_share(o, mo.Ring.from_ints(bits, enc(ys)), 1)
+        b = np.array(sel, dtype=np.uint8)
+        gs, os_ = g.share(g.from_bits(b), 0), mo.rep_share(o, mo.Bits.from_array(b), 0)
+        gm, om = g.mux(gs, gx, gy), mo.rep_mux_bit_selector(o, bits, os_, ox, oy)
+        assert same_rep(gm, om)
+        assert [v / 2 ** 24 for v in signed(g.reveal(gm).to_ints().reshape(-1), bits)] == want
+        gr, orr = g.share(g.from_ints(DT[bits], sel, (n,)), 2), mo.rep_share(o, mo.Ring.from_ints(bits, sel), 2)
+        gm, om = g.mux(gr, gx, gy), mo.rep_mux(o, orr, ox, oy)
+        assert same_rep(gm, om)
+        assert [v / 2 ** 24 for v in signed(g.reveal(gm).to_ints().reshape(-1), bits)] == want
+    g.close()
+
+
+@pytest.mark.parametrize("bits", [64, 128])
+@pytest.mark.parametrize("shape", [(3,), (128,), (5, 7)])
+def test_bit_compose_inverts_bit_decompose(bits, shape):
+    """replicated/mod.rs:1107-1139 (rep_bit_compose tests): compose(decompose(x)) == x, every share equal to the
+    oracle's fold of k ring_injects."""
+    g, o = pair()
+    rng = np.random.default_rng(21)
+    a = rand_ring(rng, bits, shape)
+    if shape == (3,):
+        a = mo.Ring.from_ints(bits, [1073741823, 0, 6]).data
+    gx, ox = g.share(g.from_host(DT[bits], a), 0), mo.rep_share(o, mo.Ring(bits, a), 0)
+    gb, ob = g.rep_bit_decompose(gx), mo.rep_bit_decompose(o, ox)
+    gc, oc = g.bit_compose(DT[bits], gb), mo.rep_bit_compose(o, bits, ob)
+    assert same_rep(gc, oc)
+    assert np.array_equal(g.reveal(gc).to_host(), a)
+    with pytest.raises(mb.MooseB200Error):
+        g.bit_compose(DT[bits], gx)          # not bit planes
+    g.close()
