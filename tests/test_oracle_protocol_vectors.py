@@ -117,3 +117,26 @@ def test_prefix_mul_and_polynomial_reference_vectors(bits):
     assert [int(decoded(p, f)[0]) for p in pre] == [1, 2, 6, 24]
     y = mo.polynomial_eval(sess, f, [1.0, 2.0, 3.0], fixed(sess, bits, f, [1.0, 2.0, 3.0, 4.0]))
     assert np.abs(decoded(y, f) - np.array([6.0, 17.0, 34.0, 57.0])).max() < 2.0 ** -13   # a few truncation units
+
+
+@pytest.mark.parametrize("bits", [64, 128])
+def test_trunc_pr_and_msb_fuzz_like_the_reference(bits):
+    """test_fuzzy_rep_trunc64/128 (mod.rs:960-978; inputs (x >> 2) - 1, amount < bits - 2, result within one unit of
+    x >> amount), test_fuzzy_adt_trunc64/128 (additive/trunc.rs:272-286: the same bound on the two-party form) and
+    test_fuzzy_rep_msb64/128 (mod.rs:1014-1030)."""
+    rng = np.random.default_rng(bits)
+    sess = mo.Session("vectors", KEY)
+    mod = 1 << bits
+    for _ in range(12):
+        n = int(rng.integers(1, 5))
+        raw = [((int.from_bytes(rng.bytes(bits // 8), "little") >> 2) - 1) % mod for _ in range(n)]
+        amount = int(rng.integers(0, bits - 2))
+        x = rep(sess, bits, raw, owner=2)
+        got = mo.rep_reveal(mo.rep_trunc_pr(sess, amount, x), 2).to_ints().reshape(-1)
+        assert all((int(g) - (v >> amount)) % mod in (0, 1, mod - 1) for g, v in zip(got, raw)), (raw, amount)
+        adt = mo.adt_trunc_pr(sess, amount, mo.rep_to_adt(x))
+        got = mo.adt_reveal(adt).to_ints().reshape(-1)
+        assert all((int(g) - (v >> amount)) % mod in (0, 1, mod - 1) for g, v in zip(got, raw)), (raw, amount)
+        full = [int.from_bytes(rng.bytes(bits // 8), "little") for _ in range(n)]
+        msb = mo.rep_reveal(mo.rep_msb_ring(sess, rep(sess, bits, full))).to_ints().reshape(-1)
+        assert [int(m) for m in msb] == [v >> (bits - 1) for v in full]
