@@ -265,6 +265,20 @@ def test_fixedpoint_encode_decode(sess, bits, frac):
                           mo.fixed_decode(mo.Ring(bits, w), frac))
 
 
+RING_FIXEDPOINT = {(64, 16): [65536, 18446744073709420544, 196608, 18446744073709289472],
+                   (128, 80): [1208925819614629174706176, 340282366920936045611735378173418799104,
+                               3626777458843887524118528, 340282366920933627760096148915069386752]}
+
+
+@pytest.mark.parametrize("bits,frac", list(RING_FIXEDPOINT))
+def test_ring_fixedpoint_reference_vector(sess, bits, frac):
+    """fixedpoint/ops.rs:2575-2627 (ring_fixedpoint): [1, -2, 3, -4] at 2^16 on Ring64 and at 2^80 on Ring128."""
+    v = np.array([1.0, -2.0, 3.0, -4.0])
+    e = sess.fixedpoint_encode(DT[bits], frac, sess.from_host(FLOAT64, v))
+    assert ints(e) == RING_FIXEDPOINT[(bits, frac)]
+    assert np.array_equal(sess.fixedpoint_decode(frac, e).to_host(), v)
+
+
 @pytest.mark.parametrize("mode", [2, 3])
 @pytest.mark.parametrize("bits", [64, 128])
 @pytest.mark.parametrize("M,K,N", [(128, 128, 64), (128, 256, 256), (256, 128, 128), (300, 200, 130), (129, 1000, 514),

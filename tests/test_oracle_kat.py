@@ -124,6 +124,13 @@ def test_fixed_encode_decode():
     assert np.allclose(mo.fixed_decode(e, 40), v, atol=2 ** -40)
     e = mo.fixed_encode(64, v, 23)
     assert ints(e) == [int(t * 2 ** 23) % (1 << 64) for t in v]
+    # fixedpoint/ops.rs:2575-2627 (ring_fixedpoint)
+    v = np.array([1.0, -2.0, 3.0, -4.0])
+    assert ints(mo.fixed_encode(64, v, 16)) == [65536, 18446744073709420544, 196608, 18446744073709289472]
+    e = mo.fixed_encode(128, v, 80)
+    assert ints(e) == [1208925819614629174706176, 340282366920936045611735378173418799104,
+                       3626777458843887524118528, 340282366920933627760096148915069386752]
+    assert np.array_equal(mo.fixed_decode(e, 80), v) and np.array_equal(mo.fixed_decode(mo.fixed_encode(64, v, 16), 16), v)
 
 
 def test_elementwise_against_python_ints():
