@@ -202,6 +202,11 @@ def main():
     ap.add_argument("--scale", type=int, nargs=3, metavar=("M", "K", "N"), default=None,
                     help="replace the two HostFloat64Tensor constants of the graph by U(-1,1) matrices [M,K] and [K,N]")
     args = ap.parse_args()
+    if args.lanes > 1:
+        # every lane's context owns two streams and parks spinning wait kernels on them; with more such streams than
+        # hardware queues (8 by default) a signal can be queued behind another lane's wait.  Must be set before the
+        # process creates its CUDA context.  (A lead for the 4-lane hang of DESIGN.md section 6, not re-measured.)
+        os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 
     import torch
     import torch.distributed as dist
