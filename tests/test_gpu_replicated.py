@@ -339,3 +339,45 @@ def test_bit_compose_inverts_bit_decompose(bits, shape):
     with pytest.raises(mb.MooseB200Error):
         g.bit_compose(DT[bits], gx)          # not bit planes
     g.close()
+
+
+@pytest.mark.parametrize("bits", [64, 128])
+@pytest.mark.parametrize("shape", [(0,), (0, 5), (3, 0)])
+def test_empty_tensors_through_the_replicated_layer(bits, shape):
+    """Zero-element tensors (ndarray handles them; the reference's kernels are shape-generic): every protocol returns
+    the empty shape, draws the same entropy requests as on the oracle -- checked by a non-empty multiplication after
+    them, share by share -- and a dot with an empty contraction axis is the zero matrix plus the zero share."""
+    g, o = pair()
+    a = np.zeros(shape + ((2,) if bits == 128 else ()), dtype=np.uint64)
+    gx, ox = g.share(g.from_host(DT[bits], a), 0), mo.rep_share(o, mo.Ring(bits, a), 0)
+    gy, oy = g.share(g.from_host(DT[bits], a), 1), mo.rep_share(o, mo.Ring(bits, a), 1)
+    steps = [
+        (lambda: g.rep_add(gx, gy), lambda: mo.rep_add(ox, oy)),
+        (lambda: g.rep_mul(gx, gy), lambda: mo.rep_mul(o, ox, oy)),
+        (lambda: g.trunc_pr(5, gx), lambda: mo.rep_trunc_pr(o, 5, ox)),
+        (lambda: g.msb(gx), lambda: mo.rep_msb(o, ox)),
+        (lambda: g.rep_bit_decompose(gx), lambda: mo.rep_bit_decompose(o, ox)),
+        (lambda: g.relu(gx), lambda: mo.rep_relu(o, ox)),
+        (lambda: g.maximum([gx, gy]), lambda: mo.rep_maximum(o, [ox, oy])),
+        (lambda: g.rep_less(gx, gy), lambda: mo.rep_less(o, ox, oy)),
+    ]
+    for gf, of in steps:
+        gr, orr = gf(), of()
+        assert same_rep(gr, orr)
+    assert g.reveal(g.relu(gx)).shape == shape and mo.rep_reveal(mo.rep_relu(o, ox)).shape == shape
+    if len(shape) == 2:
+        rng = np.random.default_rng(3)
+        other = (shape[1], 2)
+        b = rand_ring(rng, bits, other)
+        gb, ob = g.share(g.from_host(DT[bits], b), 2), mo.rep_share(o, mo.Ring(bits, b), 2)
+        gd, od = g.rep_dot(gx, gb), mo.rep_dot(o, ox, ob)
+        assert same_rep(gd, od)
+        r = g.reveal(gd)
+        assert r.shape == (shape[0], 2) and not r.to_host().any()
+    # entropy still in step: a non-empty product after the empty calls
+    rng = np.random.default_rng(4)
+    p, q = rand_ring(rng, bits, (9,)), rand_ring(rng, bits, (9,))
+    gp, op = g.share(g.from_host(DT[bits], p), 0), mo.rep_share(o, mo.Ring(bits, p), 0)
+    gq, oq = g.share(g.from_host(DT[bits], q), 1), mo.rep_share(o, mo.Ring(bits, q), 1)
+    assert same_rep(g.rep_mul(gp, gq), mo.rep_mul(o, op, oq))
+    g.close()
