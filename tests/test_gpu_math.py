@@ -160,3 +160,20 @@ def test_batched_and_op_by_op_paths_agree():
         g.close()
     for i in range(3):
         assert np.array_equal(outs[0][i], outs[1][i])
+
+
+@pytest.mark.parametrize("bits,i_p,f_p", [(64, 8, 10), (128, 24, 40)])
+def test_math_on_zero_element_tensors(bits, i_p, f_p):
+    """Division, exp and sigmoid of an empty batch: empty results, the reference's entropy requests still drawn (a
+    non-empty sigmoid after them equals the oracle's share by share)."""
+    g, o = pair()
+    empty = np.zeros((0, 2))
+    gx, ox = shared(g, o, bits, f_p, empty, 0)
+    gy, oy = shared(g, o, bits, f_p, empty, 1)
+    for gr, orr in ((g.rep_div(i_p, f_p, gx, gy), mo.rep_div(o, i_p, f_p, ox, oy)),
+                    (g.rep_exp(i_p, f_p, gx), mo.rep_exp(o, i_p, f_p, ox)),
+                    (g.sigmoid(i_p, f_p, gx), mo.rep_sigmoid(o, i_p, f_p, ox))):
+        assert same_rep(gr, orr) and g.reveal(gr).shape == (0, 2)
+    gz, oz = shared(g, o, bits, f_p, [[0.5, -1.25]], 2)
+    assert same_rep(g.sigmoid(i_p, f_p, gz), mo.rep_sigmoid(o, i_p, f_p, oz))
+    g.close()
