@@ -104,3 +104,47 @@ def test_mirrored_constant_round_trip():
     v = np.array([1.5, 2.3, 3, 3], dtype=np.float64)
     ring = mo.Ring.from_ints(BITS, [mo.fixed_constant(BITS, float(t), 27) for t in v])
     close(mo.fixed_decode(ring, 27), v, 7)
+
+
+def test_boolean_ops_less_greater_mux_with_bit_selector_and_concat():
+    """boolean_ops_test.py:21-110: less / greater on the replicated placement, `mux(z_less, x, y)` with the replicated
+    bit as selector (MuxOp::rep_bit_selector_kernel), and the concatenation of the bit tensor with itself."""
+    sess = mo.Session("pymoose", KEY)
+    x, y = np.array([1.5, 2.3, 3, 3]), np.array([-1.0, 4.0, 3, 2])
+    xs, ys = shared(sess, x, 27, 1), shared(sess, y, 27, 1)
+    less, greater = mo.rep_less(sess, xs, ys), mo.rep_greater(sess, xs, ys)
+    assert mo.rep_reveal(less).to_array().tolist() == (x < y).astype(int).tolist()
+    assert mo.rep_reveal(greater).to_array().tolist() == (x > y).astype(int).tolist()
+    mux = mo.rep_mux_bit_selector(sess, BITS, less, xs, ys)
+    close(opened(mux, 27), (x < y) * x + (1 - (x < y)) * y, 7)
+    twice = mo.rep_concat(0, [less, less])
+    assert mo.rep_reveal(twice).to_array().tolist() == np.concatenate([x < y, x < y]).astype(int).tolist()
+
+
+@pytest.mark.parametrize("axis,expected", [
+    (0, [[1.0, 2.0, 3.0], [1.0, 2.0, 3.0], [4.0, 5.0, 6.0], [7.0, 8.0, 9.0]]),
+    (1, [[1.0, 2.0, 3.0, 1.0, 2.0, 3.0, 4.0, 5.0, 6.0, 7.0, 8.0, 9.0]])])
+def test_concat_of_four_owners(axis, expected):
+    """concat_test.py:19-72."""
+    sess = mo.Session("pymoose", KEY)
+    parts = [shared(sess, [[1.0, 2.0, 3.0]], 23, 0), shared(sess, [[1.0, 2.0, 3.0]], 23, 0),
+             shared(sess, [[4.0, 5.0, 6.0]], 23, 1), shared(sess, [[7.0, 8.0, 9.0]], 23, 2)]
+    assert np.array_equal(opened(mo.rep_concat(axis, parts), 23, receiver=1), np.array(expected))
+
+
+def test_share_wise_shape_operators():
+    """reshape_test.py:20-50 ([[1,2],[3,4]] -> [1,4]), slicing_test.py:120-146 (x[1:, 1:2]), squeeze_test.py and
+    transpose_test.py on the replicated placement: share-wise, so the opened value is numpy's."""
+    sess = mo.Session("pymoose", KEY)
+    x = np.array([[1.0, 2.0], [3.0, 4.0]])
+    xs = shared(sess, x, 27, 1)
+    reshaped = mo.RepTensor([[v.reshape((1, 4)) for v in row] for row in xs.shares])
+    assert np.array_equal(opened(reshaped, 27, 1), x.reshape(1, 4))
+    assert np.array_equal(opened(mo.rep_transpose(xs), 27, 1), x.T)
+    v = np.array([[1, 23.0, 321, 30.321, 321], [32.0, 321, 5, 3.0, 32.0]])
+    vs = shared(sess, v, 27, 1)
+    sliced = mo.RepTensor([[mo.slice_ring([(1, None, None), (1, 2, None)], t) for t in row] for row in vs.shares])
+    close(opened(sliced, 27, 1), v[1:, 1:2], 7)
+    one = shared(sess, np.array([[[1.0], [2.0]]]), 23, 0)
+    assert opened(mo.rep_squeeze(None, one), 23).shape == (2,)
+    assert opened(mo.rep_squeeze(2, one), 23).shape == (1, 2)
