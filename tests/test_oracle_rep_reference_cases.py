@@ -154,3 +154,34 @@ def test_additive_sharing_arithmetic_reference_case():
     assert ints(mo.add(x.shares[0], r)) == [8, 10, 12] and ints(x.shares[1]) == [4, 5, 6]   # r at alice
     assert ints(x.shares[0]) == [1, 2, 3] and ints(mo.add(x.shares[1], r)) == [11, 13, 15]  # r at bob
     assert ints(mo.adt_reveal(mo.AdtTensor(z))) == [13, 17, 21]
+
+
+def test_identity_mean_add_n_sum_diag_index_reference_cases():
+    """replicated/mod.rs:281-292 (share / reveal identity), :371-391 (mean_as_fixedpoint + trunc_pr -> 2.0 within 0.01),
+    :394-423 (add_n over three owners, Ring64 and Ring128), :426-437 (sum without axis), :441-478 (diag on ring and bit
+    tensors), :480-515 (index_axis 0, 1), :517-552 (index of a replicated bit array)."""
+    sess = mo.Session("vectors", KEY)
+    assert ints(mo.rep_reveal(shared(sess, 64, [1, 2, 3]))) == [1, 2, 3]
+    x = mo.rep_share(sess, mo.fixed_encode(64, np.array([1.0, 2.0, 3.0]), 24), 0)
+    mean = mo.rep_trunc_pr(sess, 24, mo.rep_fixedpoint_mean(None, 2, 24, x))
+    assert abs(2.0 - float(mo.fixed_decode(mo.rep_reveal(mean), 24))) < 0.01
+    parts = [shared(sess, 64, [1, 2, 3], 0), shared(sess, 64, [2, 3, 4], 1), shared(sess, 64, [5, 12, 13], 2)]
+    assert ints(mo.rep_reveal(mo.rep_add_n(parts))) == [8, 17, 20]
+    parts = [shared(sess, 128, [1, 2, 3, 2, 3, 4], 0, (2, 3)), shared(sess, 128, [2, 3, 4, 2, 3, 4], 1, (2, 3)),
+             shared(sess, 128, [5, 12, 13, 1, 2, 3], 2, (2, 3))]
+    total = mo.rep_reveal(mo.rep_add_n(parts))
+    assert total.shape == (2, 3) and ints(total) == [8, 17, 20, 5, 8, 11]
+    s = mo.rep_reveal(mo.rep_sum(None, shared(sess, 64, [1, 2, 3])))
+    assert s.shape == () and ints(s) == [6]
+    for bits in (64, 128):
+        m = shared(sess, bits, [1, 2, 3, 4], shape=(2, 2))
+        d = mo.RepTensor([[mo.diag(v) for v in row] for row in m.shares])
+        assert ints(mo.rep_reveal(d)) == [1, 4]
+        cube = shared(sess, bits, [1, 2, 3, 4, 4, 5, 6, 7], shape=(2, 2, 2))
+        got = mo.rep_reveal(mo.rep_index_axis(0, 1, cube))
+        assert got.shape == (2, 2) and ints(got) == [4, 5, 6, 7]
+    b = mo.rep_share(sess, mo.Bits.from_array(np.array([[1, 0], [1, 1]], dtype=np.uint8)), 0)
+    d = mo.RepTensor([[mo.diag(v) for v in row] for row in b.shares])
+    assert mo.rep_reveal(d).to_array().tolist() == [1, 1]
+    assert mo.rep_reveal(mo.rep_index(0, b)).to_array().tolist() == [1, 0]
+    assert mo.rep_reveal(mo.rep_index_axis(0, 1, b)).to_array().tolist() == [1, 1]
