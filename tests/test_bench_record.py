@@ -58,3 +58,31 @@ def test_both_arms_name_the_same_config():
     assert bench.predictor_config(names["mlp"], 4) == bench.predictor_config(names["mlp"], 4)
     assert set(bench.matmul_config(names["matmul"])) == {"workload", "fixed", "parties", "l2"}
     assert bench.ring_ops_per_step(4096, 4096, 4096) == 3 * 2 * 2 * 4096 ** 3
+
+
+@pytest.mark.parametrize("name", ["r2_bench_n1_steps20.json", "r2_bench_n8.json", "r2_bench_reference_arm.json"])
+def test_committed_records_carry_the_contract_fields(name):
+    """The records under profiles/ are lines bench.py printed on B200 boxes: every key the bench contract names is
+    there, on the top-level (matmul) record and on the MLP / LogReg records under `workloads`."""
+    import json
+    rec = json.load(open(os.path.join(ROOT, "profiles", name)))
+    base = {"metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+            "vs_baseline", "dtype", "data", "config", "e2e"}
+    if rec["n_gpus"] == 1 or rec.get("impl") == "reference":       # the CPU baseline is timed at N = 1 only
+        base.add("cpu_baseline")
+    assert base <= set(rec) and rec["vs_baseline"] is None and "workload" in rec["config"] and "model" not in rec["config"]
+    assert {"value", "unit", "h2d_bytes_per_step", "d2h_bytes_per_step"} <= set(rec["e2e"])
+    if "cpu_baseline" in base:
+        assert {"value", "unit", "cores", "kind", "sample"} <= set(rec["cpu_baseline"]) and rec["cpu_baseline"]["kind"] == "port"
+    if rec.get("impl") == "reference":
+        assert rec["e2e"]["h2d_bytes_per_step"] == 0 and rec["e2e"]["value"] == rec["value"]
+        return
+    records = [rec] + [rec["workloads"][k] for k in ("mlp", "logreg")]
+    for r in records:
+        assert r["gpu_launches"] > 0 and r["e2e"]["h2d_bytes_per_step"] > 0 and r["e2e"]["value"] != r["value"]
+        assert {"sm_mhz", "sm_max_mhz", "reasons"} <= set(r["clocks"])
+        roof = r["roofline"]
+        assert {"bound", "achieved", "peak", "unit", "frac", "traffic"} <= set(roof) and roof["bound"] in ("hbm", "tensor")
+        assert roof["frac"] == pytest.approx(roof["achieved"] / roof["peak"], rel=1e-3)
+        assert not set(r["clocks"]["reasons"]) & {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"}
+    assert rec["n_gpus"] in (1, 8) and (rec["n_gpus"] == 1 or "party_per_gpu" in rec)
