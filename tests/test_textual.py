@@ -199,3 +199,53 @@ def test_reference_shr_and_sample_graphs(ty):
     assert tuple(vals["shape"]) == (2, 2)
     want = mo.sample_uniform_seeded(int(ty[8:-6]), (2, 2), bytes(16))
     assert vals["sampled"] == want
+
+
+def test_random_graphs_parse_and_schedule_alike_in_python_and_native():
+    """Differential test of the two readers / schedulers on seeded random DAGs: operations in shuffled textual order,
+    attributes with nested brackets and quoted strings, nullary operations with and without "()", variadic
+    signatures, parametrised types, Send / Receive pairs.  Same operation count, same execution order, and the text
+    round-trips through the Python reader."""
+    import ctypes
+    import random
+    import moose_b200 as mb
+    lib = mb.lib()
+    roles = ["alice", "bob", "carole"]
+    for seed in range(25):
+        rnd = random.Random(seed)
+        lines, names = [], []
+        for i in range(rnd.randint(3, 40)):
+            name, role = f"op_{seed}_{i}", rnd.choice(roles)
+            k = rnd.randint(0, min(3, len(names)))
+            ins = rnd.sample(names, k)
+            ty = rnd.choice(["HostRing64Tensor", "HostRing128Tensor", "HostBitTensor", "Tensor<Fixed128(24, 40)>"])
+            if k == 0:
+                attrs = rnd.choice(['{value = HostShape([2, 3])}', '{value=HostString("a, (b) = ]c")}', ""])
+                arglist = rnd.choice([" ()", ""])
+                lines.append(f"{name} = Constant{attrs}: () -> {ty}{arglist} @Host({role})")
+            elif rnd.random() < 0.25:
+                sig = f"[{ty}]"
+                lines.append(f"{name} = AddN: {sig} -> {ty} ({', '.join(ins)}) @Host({role})")
+            elif rnd.random() < 0.3:
+                key = "%032x" % rnd.getrandbits(128)
+                peer = rnd.choice([r for r in roles if r != role])
+                lines.append(f'{name} = Send{{rendezvous_key = {key}, receiver = "{peer}"}}: ({ty}) -> HostUnit ({ins[0]}) @Host({role})')
+                names.append(name)
+                name = name + "_r"
+                lines.append(f'{name} = Receive{{rendezvous_key = {key}, sender = "{role}"}}: () -> {ty} () @Host({peer})')
+            else:
+                attrs = rnd.choice(["", "{amount = 3}", "{slice = {start = 1, end = 4, step = 2}}", "{axis = [0, 1]}"])
+                sig = "(" + ", ".join([ty] * k) + ")"
+                lines.append(f"{name} = Op{i % 7}{attrs}: {sig} -> {ty} ({', '.join(ins)}) @Host({role})")
+            names.append(name)
+        rnd.shuffle(lines)
+        text = "\n".join(lines) + "\n"
+        ops = tx.parse_computation(text)
+        assert len(ops) == len(lines)
+        assert tx.parse_computation(tx.dumps_text(ops)) == ops
+        g = ctypes.c_void_p()
+        assert lib.mb_graph_parse(None, text.encode(), ctypes.byref(g)) == 0, (seed, lib.mb_last_error(None))
+        n = lib.mb_graph_num_ops(g)
+        native = [lib.mb_graph_op_name(g, i).decode() for i in range(n)]
+        lib.mb_graph_free(g)
+        assert native == [op.name for op in toposort(ops)], seed
